@@ -1,0 +1,119 @@
+// ash_internal.cuh — context layout and kernel launch prototypes shared by the .cu files.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <string>
+#include "../../include/ashcuda.h"
+
+namespace ash {
+
+constexpr int kMaxMips = 16;
+
+// Hi-Z pyramid in HBM: mip 0 is the depth buffer itself (PIN-3: aliased, never copied), mips 1..
+// live back to back in one allocation, each level's offset rounded up to 4 floats (16 B).
+struct Pyramid {
+    const float* mip0;
+    float*       mips;              // base of levels >= 1
+    uint32_t     w[kMaxMips], h[kMaxMips];
+    uint32_t     off[kMaxMips];     // float offset of level l (l >= 1) inside `mips`
+    int          levels;            // levels_built (PIN-4)
+    int          fast_levels;       // levels 1..fast_levels reduce inside one 64x64 depth tile
+};
+
+struct BloomChain {
+    void*    d[ASH_MAX_BLOOM_MIPS + 1];   // d[k]: RGBA16F D_k, overwritten in place by U_k
+    uint32_t w[ASH_MAX_BLOOM_MIPS + 1], h[ASH_MAX_BLOOM_MIPS + 1];
+    uint32_t mips;
+};
+
+// One candidate light after the per-view prepass: view-space centre + radius, original index.
+struct LightCand { float x, y, z, r; };
+
+}  // namespace ash
+
+struct ashcuda_ctx {
+    int          device = 0;
+    cudaStream_t stream = nullptr;
+    bool         own_stream = false;
+    uint32_t     W = 0, H = 0, tiles_x = 0, tiles_y = 0;
+    AshCudaConfig cfg{};
+    std::string  err;
+    uint64_t     launches = 0;
+
+    // depth + pyramid
+    const float* depth = nullptr;      // current mip 0 (owned copy or borrowed)
+    float*       depth_owned = nullptr;
+    ash::Pyramid pyr{};
+    uint32_t*    tile_minmax = nullptr;   // tiles * 2
+    uint32_t*    depth_range = nullptr;   // [min bits, max bits] over the frame
+    uint32_t*    counters = nullptr;      // [0] depth-kernel ticket, [1] cull ticket, ...
+    bool         have_depth = false, have_pyramid = false;
+
+    // occlusion cull
+    const AshCullObjectData*      objs = nullptr;
+    AshCullObjectData*            objs_owned = nullptr;
+    const AshIndirectDrawCommand* draws_in = nullptr;
+    AshIndirectDrawCommand*       draws_in_owned = nullptr;
+    uint32_t  n_objs = 0, n_draws = 0;
+    uint32_t* visibility = nullptr;
+    uint32_t* vis_bits = nullptr;
+    uint32_t* cta_counts = nullptr;
+    AshIndirectDrawCommand* draws_out = nullptr;
+    uint32_t* visible_count = nullptr;
+
+    // light cull
+    const AshGpuLight* lights = nullptr;
+    AshGpuLight*       lights_owned = nullptr;
+    uint32_t  n_lights = 0;
+    AshCullingCameraData* camera_dev = nullptr;
+    AshCullingCameraData  camera_host{};
+    bool      have_camera = false;
+    ash::LightCand* cand = nullptr;
+    uint32_t* cand_idx = nullptr;
+    uint32_t* cand_count = nullptr;
+    uint32_t* tile_data = nullptr;
+    AshViewStats* stats = nullptr;
+
+    // post chain (RGBA16F = 8 B / texel)
+    const void* color = nullptr;
+    void*       color_owned = nullptr;
+    const void* velocity = nullptr;
+    void*       velocity_owned = nullptr;
+    void*       taa[2] = {nullptr, nullptr};   // ping-pong: taa[taa_cur] = latest resolve
+    int         taa_cur = 0;
+    bool        have_color = false, history_valid = false, taa_ran = false;
+    void*       bloom_t = nullptr;             // T = D_0 for the staged path
+    ash::BloomChain bloom{};
+    bool        bloom_valid = false;
+    void*       ldr8 = nullptr;
+};
+
+namespace ash {
+
+// each returns cudaGetLastError() after launching on `s`; *launches is incremented per kernel
+cudaError_t launch_depth_pyramid(const Pyramid& p, uint32_t* tile_minmax, uint32_t tiles_x,
+                                 uint32_t* depth_range, uint32_t* ticket, cudaStream_t s,
+                                 uint64_t* launches);
+cudaError_t launch_occlusion_cull(const AshCullObjectData* objs, const AshIndirectDrawCommand* draws_in,
+                                  const AshCullingPushConstants& pc, const Pyramid& p,
+                                  uint32_t* visibility, uint32_t* vis_bits, uint32_t* cta_counts,
+                                  AshIndirectDrawCommand* draws_out, uint32_t* visible_count,
+                                  AshViewStats* stats, cudaStream_t s, uint64_t* launches);
+cudaError_t launch_light_cull(const AshGpuLight* lights, const AshLightCullingPushConstants& pc,
+                              const AshCullingCameraData* cam_dev, const uint32_t* tile_minmax,
+                              uint32_t* depth_range, LightCand* cand, uint32_t* cand_idx,
+                              uint32_t* cand_count, uint32_t* tile_data, AshViewStats* stats,
+                              cudaStream_t s, uint64_t* launches);
+cudaError_t launch_taa(const void* cur, const void* hist, const void* vel, void* out,
+                       const AshTaaPushConstants& pc, cudaStream_t s, uint64_t* launches);
+cudaError_t launch_bloom_threshold(const void* hdr, void* out, uint32_t W, uint32_t H, float threshold,
+                                   cudaStream_t s, uint64_t* launches);
+cudaError_t launch_bloom_downsample(const void* src, uint32_t sw, uint32_t sh, void* dst, uint32_t dw,
+                                    uint32_t dh, cudaStream_t s, uint64_t* launches);
+cudaError_t launch_bloom_upsample_add(const void* src, uint32_t sw, uint32_t sh, void* dst, uint32_t dw,
+                                      uint32_t dh, float intensity, cudaStream_t s, uint64_t* launches);
+cudaError_t launch_tonemap(const void* hdr, const void* bloom_or_null, void* ldr8, uint32_t W, uint32_t H,
+                           const AshPostProcessPushConstants& pc, uint32_t srgb, cudaStream_t s,
+                           uint64_t* launches);
+
+}  // namespace ash

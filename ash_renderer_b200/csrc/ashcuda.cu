@@ -1,0 +1,435 @@
+// ashcuda.cu — the C ABI (include/ashcuda.h): context, buffers, stage dispatch.
+// Plays the role of the reference's LightCullingPipeline (vulkan/light_culling_pipeline.rs:41-351:
+// create buffers, upload, dispatch, expose the output buffer, free in Drop) for every stage.
+#include <cstdio>
+#include <cstring>
+#include <new>
+#include "ash_internal.cuh"
+
+using namespace ash;
+
+static thread_local std::string g_create_error;
+
+#define ASH_CUDA(ctx, call)                                                              \
+    do {                                                                                 \
+        cudaError_t e__ = (call);                                                        \
+        if (e__ != cudaSuccess) {                                                        \
+            (ctx)->err = std::string(#call) + ": " + cudaGetErrorString(e__);            \
+            return e__ == cudaErrorMemoryAllocation ? ASH_ERR_OUT_OF_MEMORY : ASH_ERR_DEVICE; \
+        }                                                                                \
+    } while (0)
+
+static int fail(ashcuda_ctx* c, int code, const char* msg) {
+    if (c) c->err = msg;
+    return code;
+}
+
+template <typename T>
+static cudaError_t dmalloc(T** p, size_t n) {
+    return cudaMalloc(reinterpret_cast<void**>(p), n ? n : 16);
+}
+
+static int hiz_level_count(uint32_t W, uint32_t H) {     // PIN-4: floor(log2(max(W,H))) + 1
+    uint32_t m = W > H ? W : H;
+    int n = 1;
+    while (m > 1) { m >>= 1; ++n; }
+    return n;
+}
+
+extern "C" {
+
+const char* ashcuda_version(void) { return "ashcuda 0.1.0 (sm_100a)"; }
+
+void ashcuda_default_config(AshCudaConfig* cfg) {
+    if (!cfg) return;
+    memset(cfg, 0, sizeof(*cfg));
+    cfg->max_objects = ASH_DEFAULT_MAX_OBJECTS;     // occlusion_culling.rs:18
+    cfg->max_lights = ASH_DEFAULT_MAX_LIGHTS;       // features/light_culling.rs:17
+    cfg->max_draws = 4096;
+    cfg->hiz_levels = ASH_DEFAULT_HIZ_LEVELS;       // occlusion_culling.rs:21
+    cfg->bloom_mips = 5;                            // features/bloom.rs:29
+    cfg->enable_post = 1;
+    cfg->srgb_encode = 0;
+}
+
+const char* ashcuda_last_error(ashcuda_ctx* ctx) {
+    return ctx ? ctx->err.c_str() : g_create_error.c_str();
+}
+
+void ashcuda_destroy(ashcuda_ctx* c) {
+    if (!c) return;
+    cudaSetDevice(c->device);
+    if (c->stream) cudaStreamSynchronize(c->stream);
+    void* owned[] = {c->depth_owned, c->pyr.mips, c->tile_minmax, c->depth_range, c->counters,
+                     c->objs_owned, c->draws_in_owned, c->visibility, c->vis_bits, c->cta_counts,
+                     c->draws_out, c->visible_count, c->lights_owned, c->camera_dev, c->cand,
+                     c->cand_idx, c->cand_count, c->tile_data, c->stats, c->color_owned,
+                     c->velocity_owned, c->taa[0], c->taa[1], c->bloom_t, c->ldr8};
+    for (void* p : owned) if (p) cudaFree(p);
+    for (uint32_t k = 1; k <= ASH_MAX_BLOOM_MIPS; ++k) if (c->bloom.d[k]) cudaFree(c->bloom.d[k]);
+    if (c->own_stream && c->stream) cudaStreamDestroy(c->stream);
+    delete c;
+}
+
+static int create_impl(ashcuda_ctx* c) {
+    const uint32_t W = c->W, H = c->H;
+    const size_t P = (size_t)W * H;
+    ASH_CUDA(c, cudaSetDevice(c->device));
+    ASH_CUDA(c, cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+    c->own_stream = true;
+    // ---- pyramid geometry (PIN-3/4)
+    Pyramid& p = c->pyr;
+    p.levels = hiz_level_count(W, H);
+    p.w[0] = W; p.h[0] = H; p.off[0] = 0;
+    uint32_t off = 0;
+    for (int l = 1; l < p.levels; ++l) {
+        p.w[l] = p.w[l - 1] / 2 ? p.w[l - 1] / 2 : 1;
+        p.h[l] = p.h[l - 1] / 2 ? p.h[l - 1] / 2 : 1;
+        p.off[l] = off;
+        off += (p.w[l] * p.h[l] + 3u) & ~3u;
+    }
+    int f = 0;     // levels reducible inside one 64x64 tile: clean 2x halving in both dimensions
+    while (f < 6 && f + 1 < p.levels && (W >> (f + 1)) >= 1 && (H >> (f + 1)) >= 1) ++f;
+    p.fast_levels = f;
+    c->tiles_x = (W + 15u) / 16u;
+    c->tiles_y = (H + 15u) / 16u;
+    const size_t tiles = (size_t)c->tiles_x * c->tiles_y;
+    ASH_CUDA(c, dmalloc(&c->depth_owned, P * 4));
+    ASH_CUDA(c, dmalloc(&p.mips, (size_t)off * 4));
+    ASH_CUDA(c, dmalloc(&c->tile_minmax, tiles * 8));
+    ASH_CUDA(c, dmalloc(&c->depth_range, 8));
+    ASH_CUDA(c, dmalloc(&c->counters, 64));
+    ASH_CUDA(c, cudaMemsetAsync(c->depth_range, 0xFF, 8, c->stream));
+    ASH_CUDA(c, cudaMemsetAsync(c->counters, 0, 64, c->stream));
+    // ---- cull
+    const size_t N = c->cfg.max_objects;
+    ASH_CUDA(c, dmalloc(&c->objs_owned, N * sizeof(AshCullObjectData)));
+    ASH_CUDA(c, dmalloc(&c->draws_in_owned, (size_t)c->cfg.max_draws * sizeof(AshIndirectDrawCommand)));
+    ASH_CUDA(c, dmalloc(&c->visibility, N * 4));
+    ASH_CUDA(c, dmalloc(&c->vis_bits, ((N + 31) / 32) * 4));
+    ASH_CUDA(c, dmalloc(&c->cta_counts, ((N + 255) / 256) * 4));
+    ASH_CUDA(c, dmalloc(&c->draws_out, N * sizeof(AshIndirectDrawCommand)));
+    ASH_CUDA(c, dmalloc(&c->visible_count, 4));
+    ASH_CUDA(c, cudaMemsetAsync(c->visible_count, 0, 4, c->stream));
+    // ---- lights
+    const size_t L = c->cfg.max_lights;
+    ASH_CUDA(c, dmalloc(&c->lights_owned, L * sizeof(AshGpuLight)));
+    ASH_CUDA(c, dmalloc(&c->camera_dev, sizeof(AshCullingCameraData)));
+    ASH_CUDA(c, dmalloc(&c->cand, L * sizeof(LightCand)));
+    ASH_CUDA(c, dmalloc(&c->cand_idx, L * 4));
+    ASH_CUDA(c, dmalloc(&c->cand_count, 4));
+    ASH_CUDA(c, dmalloc(&c->tile_data, tiles * ASH_TILE_STRIDE * 4));    // light_culling_pipeline.rs:55-56
+    ASH_CUDA(c, dmalloc(&c->stats, sizeof(AshViewStats)));
+    ASH_CUDA(c, cudaMemsetAsync(c->stats, 0, sizeof(AshViewStats), c->stream));
+    // ---- post chain
+    if (c->cfg.enable_post) {
+        ASH_CUDA(c, dmalloc(&c->color_owned, P * 8));
+        ASH_CUDA(c, dmalloc(&c->velocity_owned, P * 4));
+        ASH_CUDA(c, dmalloc(&c->taa[0], P * 8));
+        ASH_CUDA(c, dmalloc(&c->taa[1], P * 8));
+        ASH_CUDA(c, dmalloc(&c->bloom_t, P * 8));
+        ASH_CUDA(c, dmalloc(&c->ldr8, P * 4));
+        BloomChain& b = c->bloom;
+        b.mips = c->cfg.bloom_mips;
+        b.w[0] = W; b.h[0] = H; b.d[0] = c->bloom_t;
+        for (uint32_t k = 1; k <= b.mips; ++k) {     // PIN-9: extent max(1, floor(prev/2))
+            b.w[k] = b.w[k - 1] / 2 ? b.w[k - 1] / 2 : 1;
+            b.h[k] = b.h[k - 1] / 2 ? b.h[k - 1] / 2 : 1;
+            ASH_CUDA(c, dmalloc(&b.d[k], (size_t)b.w[k] * b.h[k] * 8));
+        }
+    }
+    ASH_CUDA(c, cudaStreamSynchronize(c->stream));
+    return ASH_OK;
+}
+
+int ashcuda_create(ashcuda_ctx** out, int device, uint32_t width, uint32_t height,
+                   const AshCudaConfig* cfg_or_null) {
+    if (!out) { g_create_error = "ashcuda_create: out is NULL"; return ASH_ERR_INVALID; }
+    *out = nullptr;
+    if (width == 0 || height == 0 || width > 32768 || height > 32768) {
+        g_create_error = "ashcuda_create: bad extent";
+        return ASH_ERR_INVALID;
+    }
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || device < 0 || device >= ndev) {   // no CPU fallback: fail loudly
+        g_create_error = std::string("ashcuda_create: no usable CUDA device (") +
+                         (e != cudaSuccess ? cudaGetErrorString(e) : "device index out of range") + ")";
+        return ASH_ERR_DEVICE;
+    }
+    ashcuda_ctx* c = new (std::nothrow) ashcuda_ctx();
+    if (!c) { g_create_error = "out of host memory"; return ASH_ERR_OUT_OF_MEMORY; }
+    c->device = device; c->W = width; c->H = height;
+    if (cfg_or_null) c->cfg = *cfg_or_null; else ashcuda_default_config(&c->cfg);
+    if (c->cfg.bloom_mips > ASH_MAX_BLOOM_MIPS || c->cfg.hiz_levels == 0) {
+        g_create_error = "ashcuda_create: bad config"; delete c; return ASH_ERR_INVALID;
+    }
+    int rc = create_impl(c);
+    if (rc != ASH_OK) { g_create_error = c->err; ashcuda_destroy(c); return rc; }
+    *out = c;
+    return ASH_OK;
+}
+
+int ashcuda_set_stream(ashcuda_ctx* c, void* cuda_stream) {
+    if (!c) return ASH_ERR_INVALID;
+    ASH_CUDA(c, cudaSetDevice(c->device));
+    ASH_CUDA(c, cudaStreamSynchronize(c->stream));
+    if (c->own_stream) { cudaStreamDestroy(c->stream); c->own_stream = false; }
+    if (cuda_stream) { c->stream = static_cast<cudaStream_t>(cuda_stream); }
+    else { ASH_CUDA(c, cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking)); c->own_stream = true; }
+    return ASH_OK;
+}
+
+// ------------------------------------------------------------------------------ inputs
+int ashcuda_set_depth(ashcuda_ctx* c, const float* depth, int on_device) {
+    if (!c || !depth) return fail(c, ASH_ERR_INVALID, "set_depth: null");
+    ASH_CUDA(c, cudaSetDevice(c->device));
+    if (on_device) c->depth = depth;
+    else {
+        ASH_CUDA(c, cudaMemcpyAsync(c->depth_owned, depth, (size_t)c->W * c->H * 4, cudaMemcpyHostToDevice, c->stream));
+        c->depth = c->depth_owned;
+    }
+    c->pyr.mip0 = c->depth;
+    c->have_depth = true;
+    c->have_pyramid = false;
+    return ASH_OK;
+}
+
+int ashcuda_set_objects(ashcuda_ctx* c, const AshCullObjectData* objs, uint32_t n,
+                        const AshIndirectDrawCommand* draws_in, uint32_t n_draws, int on_device) {
+    if (!c || (n && !objs) || (n_draws && !draws_in)) return fail(c, ASH_ERR_INVALID, "set_objects: null");
+    if (n > c->cfg.max_objects) return fail(c, ASH_ERR_INVALID, "set_objects: n > max_objects");
+    ASH_CUDA(c, cudaSetDevice(c->device));
+    if (on_device) { c->objs = objs; c->draws_in = draws_in; }
+    else {
+        if (n_draws > c->cfg.max_draws) return fail(c, ASH_ERR_INVALID, "set_objects: n_draws > max_draws");
+        if (n) ASH_CUDA(c, cudaMemcpyAsync(c->objs_owned, objs, (size_t)n * sizeof(*objs), cudaMemcpyHostToDevice, c->stream));
+        if (n_draws) ASH_CUDA(c, cudaMemcpyAsync(c->draws_in_owned, draws_in, (size_t)n_draws * sizeof(*draws_in), cudaMemcpyHostToDevice, c->stream));
+        c->objs = c->objs_owned; c->draws_in = c->draws_in_owned;
+    }
+    c->n_objs = n; c->n_draws = n_draws;
+    return ASH_OK;
+}
+
+int ashcuda_set_lights(ashcuda_ctx* c, const AshGpuLight* lights, uint32_t n, int on_device) {
+    if (!c || (n && !lights)) return fail(c, ASH_ERR_INVALID, "set_lights: null");
+    if (n > c->cfg.max_lights) return fail(c, ASH_ERR_INVALID, "set_lights: n > max_lights");
+    ASH_CUDA(c, cudaSetDevice(c->device));
+    if (on_device) c->lights = lights;
+    else {
+        if (n) ASH_CUDA(c, cudaMemcpyAsync(c->lights_owned, lights, (size_t)n * sizeof(*lights), cudaMemcpyHostToDevice, c->stream));
+        c->lights = c->lights_owned;
+    }
+    c->n_lights = n;
+    return ASH_OK;
+}
+
+int ashcuda_set_camera(ashcuda_ctx* c, const AshCullingCameraData* cam) {
+    if (!c || !cam) return fail(c, ASH_ERR_INVALID, "set_camera: null");
+    ASH_CUDA(c, cudaSetDevice(c->device));
+    c->camera_host = *cam;   // pageable source is staged by the runtime before the call returns
+    ASH_CUDA(c, cudaMemcpyAsync(c->camera_dev, cam, sizeof(*cam), cudaMemcpyHostToDevice, c->stream));
+    c->have_camera = true;
+    return ASH_OK;
+}
+
+int ashcuda_set_color(ashcuda_ctx* c, const void* hdr, const void* vel, int on_device) {
+    if (!c || !hdr) return fail(c, ASH_ERR_INVALID, "set_color: null");
+    if (!c->cfg.enable_post) return fail(c, ASH_ERR_NOT_INITIALIZED, "set_color: post chain disabled in config");
+    ASH_CUDA(c, cudaSetDevice(c->device));
+    const size_t P = (size_t)c->W * c->H;
+    if (on_device) { c->color = hdr; c->velocity = vel; }
+    else {
+        ASH_CUDA(c, cudaMemcpyAsync(c->color_owned, hdr, P * 8, cudaMemcpyHostToDevice, c->stream));
+        c->color = c->color_owned;
+        if (vel) { ASH_CUDA(c, cudaMemcpyAsync(c->velocity_owned, vel, P * 4, cudaMemcpyHostToDevice, c->stream)); c->velocity = c->velocity_owned; }
+        else c->velocity = nullptr;
+    }
+    c->have_color = true;
+    c->taa_ran = false;
+    c->bloom_valid = false;
+    return ASH_OK;
+}
+
+int ashcuda_taa_reset_history(ashcuda_ctx* c) {
+    if (!c) return ASH_ERR_INVALID;
+    c->history_valid = false;
+    return ASH_OK;
+}
+
+// ------------------------------------------------------------------------------ stages
+int ashcuda_hiz_build(ashcuda_ctx* c) {
+    if (!c) return ASH_ERR_INVALID;
+    if (!c->have_depth) return fail(c, ASH_ERR_NOT_INITIALIZED, "hiz_build: no depth buffer set");
+    ASH_CUDA(c, cudaSetDevice(c->device));
+    // the frame's depth range accumulates by atomics: start from the identity
+    ASH_CUDA(c, cudaMemsetAsync(c->depth_range, 0xFF, 8, c->stream));
+    ASH_CUDA(c, launch_depth_pyramid(c->pyr, c->tile_minmax, c->tiles_x, c->depth_range, c->counters,
+                                     c->stream, &c->launches));
+    c->have_pyramid = true;
+    return ASH_OK;
+}
+
+int ashcuda_occlusion_cull(ashcuda_ctx* c, const AshCullingPushConstants* pc) {
+    if (!c || !pc) return fail(c, ASH_ERR_INVALID, "occlusion_cull: null");
+    if (!c->have_depth) return fail(c, ASH_ERR_NOT_INITIALIZED, "occlusion_cull: no depth buffer set");
+    if (pc->object_count > c->n_objs) return fail(c, ASH_ERR_INVALID, "occlusion_cull: objectCount > uploaded objects");
+    if (pc->hiz_levels == 0 || (int)pc->hiz_levels > c->pyr.levels)
+        return fail(c, ASH_ERR_INVALID, "occlusion_cull: hizLevels outside [1, levels_built]");
+    ASH_CUDA(c, cudaSetDevice(c->device));
+    if (!c->have_pyramid) { int rc = ashcuda_hiz_build(c); if (rc) return rc; }
+    if (pc->object_count == 0) {     // PIN-8: visibleCount is zeroed before each dispatch
+        ASH_CUDA(c, cudaMemsetAsync(c->visible_count, 0, 4, c->stream));
+        return ASH_OK;
+    }
+    ASH_CUDA(c, launch_occlusion_cull(c->objs, c->draws_in, *pc, c->pyr, c->visibility, c->vis_bits,
+                                      c->cta_counts, c->draws_out, c->visible_count, c->stats,
+                                      c->stream, &c->launches));
+    return ASH_OK;
+}
+
+int ashcuda_light_cull(ashcuda_ctx* c, const AshLightCullingPushConstants* pc) {
+    if (!c || !pc) return fail(c, ASH_ERR_INVALID, "light_cull: null");
+    if (!c->have_depth) return fail(c, ASH_ERR_NOT_INITIALIZED, "light_cull: no depth buffer set");
+    if (!c->have_camera) return fail(c, ASH_ERR_NOT_INITIALIZED, "light_cull: no camera uploaded");
+    if (pc->screen_size[0] != c->W || pc->screen_size[1] != c->H)
+        return fail(c, ASH_ERR_INVALID, "light_cull: screenSize differs from the context extent");
+    if (pc->light_count > c->n_lights) return fail(c, ASH_ERR_INVALID, "light_cull: lightCount > uploaded lights");
+    ASH_CUDA(c, cudaSetDevice(c->device));
+    if (!c->have_pyramid) { int rc = ashcuda_hiz_build(c); if (rc) return rc; }
+    ASH_CUDA(c, launch_light_cull(c->lights, *pc, c->camera_dev, c->tile_minmax, c->depth_range, c->cand,
+                                  c->cand_idx, c->cand_count, c->tile_data, c->stats, c->stream,
+                                  &c->launches));
+    return ASH_OK;
+}
+
+static bool taa_extent_ok(const ashcuda_ctx* c, const AshTaaPushConstants* pc) {
+    return (uint32_t)pc->screen_params[0] == c->W && (uint32_t)pc->screen_params[1] == c->H;
+}
+
+int ashcuda_taa_resolve(ashcuda_ctx* c, const AshTaaPushConstants* pc) {
+    if (!c || !pc) return fail(c, ASH_ERR_INVALID, "taa_resolve: null");
+    if (!c->have_color) return fail(c, ASH_ERR_NOT_INITIALIZED, "taa_resolve: no colour buffer set");
+    if (!taa_extent_ok(c, pc)) return fail(c, ASH_ERR_INVALID, "taa_resolve: screenParams differ from the context extent");
+    ASH_CUDA(c, cudaSetDevice(c->device));
+    // PIN-12: history(t) = output(t-1); first frame (or after reset_history) history = current colour
+    const void* hist = c->history_valid ? c->taa[c->taa_cur] : c->color;
+    void* out = c->taa[c->taa_cur ^ 1];
+    ASH_CUDA(c, launch_taa(c->color, hist, c->velocity, out, *pc, c->stream, &c->launches));
+    c->taa_cur ^= 1;
+    c->history_valid = true;
+    c->taa_ran = true;
+    c->bloom_valid = false;
+    return ASH_OK;
+}
+
+static const void* resolved_color(const ashcuda_ctx* c) { return c->taa_ran ? c->taa[c->taa_cur] : c->color; }
+
+int ashcuda_bloom(ashcuda_ctx* c, const AshBloomParams* bp) {
+    if (!c || !bp) return fail(c, ASH_ERR_INVALID, "bloom: null");
+    if (!c->have_color) return fail(c, ASH_ERR_NOT_INITIALIZED, "bloom: no colour buffer set");
+    if (bp->mip_count > c->bloom.mips) return fail(c, ASH_ERR_INVALID, "bloom: mip_count > config bloom_mips");
+    ASH_CUDA(c, cudaSetDevice(c->device));
+    BloomChain& b = c->bloom;
+    ASH_CUDA(c, launch_bloom_threshold(resolved_color(c), b.d[0], c->W, c->H, bp->threshold, c->stream, &c->launches));
+    for (uint32_t k = 1; k <= bp->mip_count; ++k)
+        ASH_CUDA(c, launch_bloom_downsample(b.d[k - 1], b.w[k - 1], b.h[k - 1], b.d[k], b.w[k], b.h[k], c->stream, &c->launches));
+    for (int k = (int)bp->mip_count - 1; k >= 0; --k)
+        ASH_CUDA(c, launch_bloom_upsample_add(b.d[k + 1], b.w[k + 1], b.h[k + 1], b.d[k], b.w[k], b.h[k],
+                                              bp->upsample_intensity, c->stream, &c->launches));
+    c->bloom_valid = true;
+    return ASH_OK;
+}
+
+int ashcuda_tonemap(ashcuda_ctx* c, const AshPostProcessPushConstants* pc) {
+    if (!c || !pc) return fail(c, ASH_ERR_INVALID, "tonemap: null");
+    if (!c->have_color) return fail(c, ASH_ERR_NOT_INITIALIZED, "tonemap: no colour buffer set");
+    ASH_CUDA(c, cudaSetDevice(c->device));
+    ASH_CUDA(c, launch_tonemap(resolved_color(c), c->bloom_valid ? c->bloom.d[0] : nullptr, c->ldr8, c->W, c->H,
+                               *pc, c->cfg.srgb_encode, c->stream, &c->launches));
+    return ASH_OK;
+}
+
+int ashcuda_view_run(ashcuda_ctx* c, const AshCudaViewParams* vp) {
+    if (!c || !vp) return fail(c, ASH_ERR_INVALID, "view_run: null");
+    int rc = ASH_OK;
+    const uint32_t st = vp->stages;
+    if (st & (ASH_STAGE_LIGHTS)) { rc = ashcuda_set_camera(c, &vp->camera); if (rc) return rc; }
+    if (st & ASH_STAGE_HIZ) { rc = ashcuda_hiz_build(c); if (rc) return rc; }
+    if (st & ASH_STAGE_CULL) { rc = ashcuda_occlusion_cull(c, &vp->cull); if (rc) return rc; }
+    if (st & ASH_STAGE_LIGHTS) { rc = ashcuda_light_cull(c, &vp->light); if (rc) return rc; }
+    if (st & ASH_STAGE_TAA) { rc = ashcuda_taa_resolve(c, &vp->taa); if (rc) return rc; }
+    if (st & ASH_STAGE_BLOOM) { rc = ashcuda_bloom(c, &vp->bloom); if (rc) return rc; }
+    if (st & ASH_STAGE_TONEMAP) { rc = ashcuda_tonemap(c, &vp->post); if (rc) return rc; }
+    ASH_CUDA(c, cudaMemcpyAsync(&c->stats->view_id, &vp->view_id, 4, cudaMemcpyHostToDevice, c->stream));
+    return ASH_OK;
+}
+
+// ------------------------------------------------------------------------------ outputs
+int ashcuda_hiz_level_count(ashcuda_ctx* c) { return c ? c->pyr.levels : ASH_ERR_INVALID; }
+
+int ashcuda_mip_extent(ashcuda_ctx* c, int which, uint32_t* w, uint32_t* h) {
+    if (!c || !w || !h) return ASH_ERR_INVALID;
+    if (which >= 0x200 && which <= 0x200 + (int)c->bloom.mips && c->cfg.enable_post) { *w = c->bloom.w[which - 0x200]; *h = c->bloom.h[which - 0x200]; return ASH_OK; }
+    if (which >= 0x100 && which < 0x100 + c->pyr.levels) { *w = c->pyr.w[which - 0x100]; *h = c->pyr.h[which - 0x100]; return ASH_OK; }
+    return fail(c, ASH_ERR_NOT_FOUND, "mip_extent: unknown mip");
+}
+
+int ashcuda_get(ashcuda_ctx* c, int which, void** dev_ptr, size_t* bytes) {
+    if (!c || !dev_ptr || !bytes) return fail(c, ASH_ERR_INVALID, "get: null");
+    const size_t P = (size_t)c->W * c->H, tiles = (size_t)c->tiles_x * c->tiles_y;
+    void* p = nullptr; size_t n = 0;
+    if (which >= 0x200 && which <= 0x200 + (int)ASH_MAX_BLOOM_MIPS) {
+        const int k = which - 0x200;
+        if (!c->cfg.enable_post || k > (int)c->bloom.mips) return fail(c, ASH_ERR_NOT_FOUND, "get: no such bloom mip");
+        p = c->bloom.d[k]; n = (size_t)c->bloom.w[k] * c->bloom.h[k] * 8;
+    } else if (which >= 0x100 && which < 0x100 + kMaxMips) {
+        const int l = which - 0x100;
+        if (l >= c->pyr.levels) return fail(c, ASH_ERR_NOT_FOUND, "get: no such Hi-Z mip");
+        p = l == 0 ? const_cast<float*>(c->depth) : c->pyr.mips + c->pyr.off[l];
+        n = (size_t)c->pyr.w[l] * c->pyr.h[l] * 4;
+    } else switch (which) {
+        case ASH_BUF_VISIBILITY:      p = c->visibility; n = (size_t)c->n_objs * 4; break;
+        case ASH_BUF_DRAWS_OUT:       p = c->draws_out; n = (size_t)c->n_objs * sizeof(AshIndirectDrawCommand); break;
+        case ASH_BUF_VISIBLE_COUNT:   p = c->visible_count; n = 4; break;
+        case ASH_BUF_TILE_DATA:       p = c->tile_data; n = tiles * ASH_TILE_STRIDE * 4; break;
+        case ASH_BUF_TAA_OUT:         p = c->taa[c->taa_cur]; n = P * 8; break;
+        case ASH_BUF_LDR8:            p = c->ldr8; n = P * 4; break;
+        case ASH_BUF_STATS:           p = c->stats; n = sizeof(AshViewStats); break;
+        case ASH_BUF_TILE_MINMAX:     p = c->tile_minmax; n = tiles * 8; break;
+        case ASH_BUF_VISIBILITY_BITS: p = c->vis_bits; n = (((size_t)c->n_objs + 31) / 32) * 4; break;
+        case ASH_BUF_BLOOM_THRESHOLD: p = c->bloom_t; n = P * 8; break;
+        default: return fail(c, ASH_ERR_NOT_FOUND, "get: unknown buffer id");
+    }
+    if (!p) return fail(c, ASH_ERR_NOT_FOUND, "get: buffer not allocated (post chain disabled?)");
+    *dev_ptr = p; *bytes = n;
+    return ASH_OK;
+}
+
+int ashcuda_readback_async(ashcuda_ctx* c, int which, void* host_dst, size_t bytes) {
+    void* p; size_t n;
+    int rc = ashcuda_get(c, which, &p, &n);
+    if (rc) return rc;
+    if (!host_dst || bytes > n) return fail(c, ASH_ERR_INVALID, "readback: bad destination or size");
+    ASH_CUDA(c, cudaSetDevice(c->device));
+    ASH_CUDA(c, cudaMemcpyAsync(host_dst, p, bytes, cudaMemcpyDeviceToHost, c->stream));
+    return ASH_OK;
+}
+
+int ashcuda_readback(ashcuda_ctx* c, int which, void* host_dst, size_t bytes) {
+    int rc = ashcuda_readback_async(c, which, host_dst, bytes);
+    if (rc) return rc;
+    ASH_CUDA(c, cudaStreamSynchronize(c->stream));
+    return ASH_OK;
+}
+
+int ashcuda_sync(ashcuda_ctx* c) {
+    if (!c) return ASH_ERR_INVALID;
+    ASH_CUDA(c, cudaSetDevice(c->device));
+    ASH_CUDA(c, cudaStreamSynchronize(c->stream));
+    return ASH_OK;
+}
+
+uint64_t ashcuda_kernel_launches(ashcuda_ctx* c) { return c ? c->launches : 0; }
+
+}  // extern "C"

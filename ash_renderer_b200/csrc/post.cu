@@ -1,0 +1,277 @@
+// post.cu — TAA resolve, bloom threshold / downsample / upsample, ACES tonemap (staged path:
+// one kernel per reference shader dispatch; the fused per-view pipeline lives in post_fused.cu).
+//
+// All colour targets are RGBA16F (8 B / texel, renderer/hdr_framebuffer.rs:34, taa_resolve.comp:19),
+// sampled LINEAR + CLAMP_TO_EDGE with 8-bit sub-texel weights (PIN-6).  A tap that lands on a
+// texel centre of a same-sized image (error << 1/512 texel for extents <= 4096) therefore equals
+// that texel exactly; CENTER=true kernels fetch it directly, CENTER=false kernels run the general
+// sampler for every tap (any extent).  Arithmetic is the pinned-order IEEE sequence of ash_math.cuh,
+// so outputs are bit-identical to the reference semantics, not merely within tolerance.
+#include "ash_internal.cuh"
+#include "ash_math.cuh"
+
+namespace ash {
+
+struct Tex16 { const uint2* p; int W, H; };
+
+__device__ __forceinline__ V4 fetch16(const Tex16& t, int x, int y) {
+    return unpack_rgba16f(__ldg(t.p + (size_t)y * t.W + x));
+}
+__device__ __forceinline__ V4 fetch16_clamped(const Tex16& t, int x, int y) {
+    return fetch16(t, min(max(x, 0), t.W - 1), min(max(y, 0), t.H - 1));
+}
+__device__ __forceinline__ V4 texture16(const Tex16& t, float u, float v) {
+    int x0, x1, y0, y1; float fx, fy;
+    bilinear_setup(u, t.W, x0, x1, fx);
+    bilinear_setup(v, t.H, y0, y1, fy);
+    const V4 a = fetch16(t, x0, y0), b = fetch16(t, x1, y0), c = fetch16(t, x0, y1), d = fetch16(t, x1, y1);
+    const V4 top = {lerp1(a.x, b.x, fx), lerp1(a.y, b.y, fx), lerp1(a.z, b.z, fx), lerp1(a.w, b.w, fx)};
+    const V4 bot = {lerp1(c.x, d.x, fx), lerp1(c.y, d.y, fx), lerp1(c.z, d.z, fx), lerp1(c.w, d.w, fx)};
+    return {lerp1(top.x, bot.x, fy), lerp1(top.y, bot.y, fy), lerp1(top.z, bot.z, fy), lerp1(top.w, bot.w, fy)};
+}
+__device__ __forceinline__ V3 rgb(V4 v) { return {v.x, v.y, v.z}; }
+
+// ---------------------------------------------------------------- TAA (taa_resolve.comp)
+__device__ __forceinline__ V3 rgb_to_ycocg(V3 c) {                        // :34-40
+    return {fadd(fadd(fmul(0.25f, c.x), fmul(0.5f, c.y)), fmul(0.25f, c.z)),
+            fsub(fmul(0.5f, c.x), fmul(0.5f, c.z)),
+            fsub(fadd(fmul(-0.25f, c.x), fmul(0.5f, c.y)), fmul(0.25f, c.z))};
+}
+__device__ __forceinline__ V3 ycocg_to_rgb(V3 c) {                        // :43-52
+    return {fsub(fadd(c.x, c.y), c.z), fadd(c.x, c.z), fsub(fsub(c.x, c.y), c.z)};
+}
+__device__ __forceinline__ V3 taa_tonemap(V3 c) {                         // :55-57
+    return {fdiv(c.x, fadd(1.0f, c.x)), fdiv(c.y, fadd(1.0f, c.y)), fdiv(c.z, fadd(1.0f, c.z))};
+}
+__device__ __forceinline__ V3 taa_untonemap(V3 c) {                       // :59-61
+    return {fdiv(c.x, fadd(fsub(1.0f, c.x), 0.0001f)), fdiv(c.y, fadd(fsub(1.0f, c.y), 0.0001f)),
+            fdiv(c.z, fadd(fsub(1.0f, c.z), 0.0001f))};
+}
+__device__ __forceinline__ V3 clip_aabb(V3 mn, V3 mx, V3 hist) {          // :64-77
+    const V3 center = scale3(add3(mx, mn), 0.5f);
+    const V3 half = adds3(scale3(sub3(mx, mn), 0.5f), 0.001f);
+    const V3 delta = sub3(hist, center);
+    const V3 v = div3(delta, half);
+    const float maxv = gmax(gmax(fabsf(v.x), fabsf(v.y)), fabsf(v.z));
+    if (maxv > 1.0f) return add3(center, divs3(delta, maxv));
+    return hist;
+}
+
+template <bool CENTER, bool HAS_VEL>
+__global__ void __launch_bounds__(256)
+k_taa_resolve(Tex16 cur, Tex16 hist, const __half2* __restrict__ vel, uint2* __restrict__ out,
+              AshTaaPushConstants pc) {
+    const int x = blockIdx.x * 32 + (threadIdx.x & 31), y = blockIdx.y * 8 + (threadIdx.x >> 5);
+    const int W = cur.W, H = cur.H;
+    if (x >= W || y >= H) return;
+    const float sw = pc.screen_params[0], sh = pc.screen_params[1];
+    const float u = fdiv(fadd((float)x, 0.5f), sw), v = fdiv(fadd((float)y, 0.5f), sh);     // :92
+    float vx = 0.0f, vy = 0.0f;
+    if (HAS_VEL) {
+        if (CENTER) {
+            const float2 q = __half22float2(__ldg(vel + (size_t)y * W + x));
+            vx = q.x; vy = q.y;
+        } else {
+            int x0, x1, y0, y1; float fx, fy;
+            bilinear_setup(u, W, x0, x1, fx); bilinear_setup(v, H, y0, y1, fy);
+            const float2 a = __half22float2(__ldg(vel + (size_t)y0 * W + x0)), b = __half22float2(__ldg(vel + (size_t)y0 * W + x1));
+            const float2 c = __half22float2(__ldg(vel + (size_t)y1 * W + x0)), d = __half22float2(__ldg(vel + (size_t)y1 * W + x1));
+            vx = lerp1(lerp1(a.x, b.x, fx), lerp1(c.x, d.x, fx), fy);
+            vy = lerp1(lerp1(a.y, b.y, fx), lerp1(c.y, d.y, fx), fy);
+        }
+    }
+    if (length2(vx, vy) < 0.0001f) {                                                       // :97-99
+        vx = fdiv(fsub(pc.jitter[0], pc.prev_jitter[0]), sw);
+        vy = fdiv(fsub(pc.jitter[1], pc.prev_jitter[1]), sh);
+    }
+    const float hu = gclamp(fsub(u, vx), 0.0f, 1.0f), hv = gclamp(fsub(v, vy), 0.0f, 1.0f); // :102
+    const V3 c = CENTER ? rgb(fetch16(cur, x, y)) : rgb(texture16(cur, u, v));             // :105
+    V3 h = rgb(texture16(hist, hu, hv));                                                   // :108
+    if (pc.params[1] > 0.5f) {                                                             // :112-142
+        V3 mn, mx;
+#pragma unroll
+        for (int dy = -1; dy <= 1; ++dy)
+#pragma unroll
+            for (int dx = -1; dx <= 1; ++dx) {
+                V3 s;
+                if (CENTER) s = rgb(fetch16_clamped(cur, x + dx, y + dy));
+                else s = rgb(texture16(cur, fadd(u, fmul((float)dx, pc.screen_params[2])),
+                                       fadd(v, fmul((float)dy, pc.screen_params[3]))));
+                s = rgb_to_ycocg(taa_tonemap(s));
+                if (dy == -1 && dx == -1) { mn = s; mx = s; } else { mn = min3(mn, s); mx = max3(mx, s); }
+            }
+        const V3 ctr = scale3(add3(mn, mx), 0.5f), ext = scale3(sub3(mx, mn), 0.5f);       // :132-135
+        mn = sub3(ctr, scale3(ext, 1.25f));
+        mx = add3(ctr, scale3(ext, 1.25f));
+        const V3 hy = rgb_to_ycocg(taa_tonemap(h));
+        h = taa_untonemap(ycocg_to_rgb(clip_aabb(mn, mx, hy)));                            // :140-141
+    }
+    float blend = pc.params[0];                                                            // :145-150
+    if (pc.params[2] > 0.5f) {
+        const float vl = length2(fmul(vx, sw), fmul(vy, sh));
+        blend = fmul(blend, gclamp(fsub(1.0f, fmul(vl, 0.1f)), 0.0f, 1.0f));
+    }
+    if (hu < 0.0f || hu > 1.0f || hv < 0.0f || hv > 1.0f) blend = 0.0f;                    // :153-156
+    const float ib = fsub(1.0f, blend);                                                    // mix(), :159
+    out[(size_t)y * W + x] = pack_rgba16f(fadd(fmul(c.x, ib), fmul(h.x, blend)), fadd(fmul(c.y, ib), fmul(h.y, blend)),
+                                          fadd(fmul(c.z, ib), fmul(h.z, blend)), 1.0f);
+}
+
+cudaError_t launch_taa(const void* cur, const void* hist, const void* vel, void* out,
+                       const AshTaaPushConstants& pc, cudaStream_t s, uint64_t* launches) {
+    const int W = (int)pc.screen_params[0], H = (int)pc.screen_params[1];
+    const Tex16 c{static_cast<const uint2*>(cur), W, H}, h{static_cast<const uint2*>(hist), W, H};
+    const dim3 grid((W + 31) / 32, (H + 7) / 8);
+    const bool center = W <= 4096 && H <= 4096;
+    const __half2* v = static_cast<const __half2*>(vel);
+    uint2* o = static_cast<uint2*>(out);
+    if (center) { if (v) k_taa_resolve<true, true><<<grid, 256, 0, s>>>(c, h, v, o, pc); else k_taa_resolve<true, false><<<grid, 256, 0, s>>>(c, h, v, o, pc); }
+    else        { if (v) k_taa_resolve<false, true><<<grid, 256, 0, s>>>(c, h, v, o, pc); else k_taa_resolve<false, false><<<grid, 256, 0, s>>>(c, h, v, o, pc); }
+    ++*launches;
+    return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------- bloom threshold (bloom_threshold.frag:18-35)
+__device__ __forceinline__ V3 soft_threshold(V3 c, float threshold) {
+    const float knee = 0.5f;                                                               // :32
+    const float br = gmax(c.x, gmax(c.y, c.z));
+    float soft = fadd(fsub(br, threshold), knee);
+    soft = gclamp(soft, 0.0f, fmul(2.0f, knee));
+    soft = fdiv(fmul(soft, soft), fadd(fmul(4.0f, knee), 0.00001f));
+    float contrib = gmax(soft, fsub(br, threshold));
+    contrib = fdiv(contrib, gmax(br, 0.00001f));
+    return scale3(c, contrib);
+}
+
+template <bool CENTER>
+__global__ void __launch_bounds__(256)
+k_bloom_threshold(Tex16 hdr, uint2* __restrict__ out, float threshold) {
+    const int x = blockIdx.x * 32 + (threadIdx.x & 31), y = blockIdx.y * 8 + (threadIdx.x >> 5);
+    if (x >= hdr.W || y >= hdr.H) return;
+    V3 c;
+    if (CENTER) c = rgb(fetch16(hdr, x, y));
+    else c = rgb(texture16(hdr, fdiv(fadd((float)x, 0.5f), (float)hdr.W), fdiv(fadd((float)y, 0.5f), (float)hdr.H)));
+    const V3 b = soft_threshold(c, threshold);
+    out[(size_t)y * hdr.W + x] = pack_rgba16f(b.x, b.y, b.z, 1.0f);
+}
+
+cudaError_t launch_bloom_threshold(const void* hdr, void* out, uint32_t W, uint32_t H, float threshold,
+                                   cudaStream_t s, uint64_t* launches) {
+    const Tex16 t{static_cast<const uint2*>(hdr), (int)W, (int)H};
+    const dim3 grid((W + 31) / 32, (H + 7) / 8);
+    if (W <= 4096 && H <= 4096) k_bloom_threshold<true><<<grid, 256, 0, s>>>(t, static_cast<uint2*>(out), threshold);
+    else k_bloom_threshold<false><<<grid, 256, 0, s>>>(t, static_cast<uint2*>(out), threshold);
+    ++*launches;
+    return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------- bloom downsample (bloom_downsample.frag:16-108)
+__global__ void __launch_bounds__(256)
+k_bloom_downsample(Tex16 src, uint2* __restrict__ dst, int dw, int dh) {
+    const int x = blockIdx.x * 32 + (threadIdx.x & 31), y = blockIdx.y * 8 + (threadIdx.x >> 5);
+    if (x >= dw || y >= dh) return;
+    const float dx = fdiv(1.0f, (float)src.W), dy = fdiv(1.0f, (float)src.H);              // texelSize, :11
+    const float u = fdiv(fadd((float)x, 0.5f), (float)dw), v = fdiv(fadd((float)y, 0.5f), (float)dh);
+    // tap order centre,a,b,c,d,e,f,g,h (:22-34), weights (:87-101)
+    const float ou[9] = {0.0f, -dx, dx, -dx, dx, -dx, dx, 0.0f, 0.0f};
+    const float ov[9] = {0.0f, -dy, -dy, dy, dy, 0.0f, 0.0f, -dy, dy};
+    const float wt[9] = {0.25f, 0.0625f, 0.0625f, 0.0625f, 0.0625f, 0.125f, 0.125f, 0.125f, 0.125f};
+    V3 res = {0.0f, 0.0f, 0.0f};
+    float sum = 0.0f;
+#pragma unroll
+    for (int k = 0; k < 9; ++k) {
+        const V3 s = rgb(texture16(src, fadd(u, ou[k]), fadd(v, ov[k])));
+        const float w = fdiv(1.0f, fadd(1.0f, dot3(s, v3(0.2126f, 0.7152f, 0.0722f))));
+        res = add3(res, scale3(scale3(s, w), wt[k]));
+        sum = fadd(sum, fmul(w, wt[k]));
+    }
+    dst[(size_t)y * dw + x] = pack_rgba16f(fdiv(res.x, sum), fdiv(res.y, sum), fdiv(res.z, sum), 1.0f);   // :107
+}
+
+cudaError_t launch_bloom_downsample(const void* src, uint32_t sw, uint32_t sh, void* dst, uint32_t dw,
+                                    uint32_t dh, cudaStream_t s, uint64_t* launches) {
+    const Tex16 t{static_cast<const uint2*>(src), (int)sw, (int)sh};
+    const dim3 grid((dw + 31) / 32, (dh + 7) / 8);
+    k_bloom_downsample<<<grid, 256, 0, s>>>(t, static_cast<uint2*>(dst), (int)dw, (int)dh);
+    ++*launches;
+    return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------- bloom upsample + additive blend (bloom_upsample.frag:16-41, PIN-9)
+__global__ void __launch_bounds__(256)
+k_bloom_upsample_add(Tex16 src, uint2* __restrict__ dst, int dw, int dh, float intensity) {
+    const int x = blockIdx.x * 32 + (threadIdx.x & 31), y = blockIdx.y * 8 + (threadIdx.x >> 5);
+    if (x >= dw || y >= dh) return;
+    const float dx = fmul(fdiv(1.0f, (float)src.W), 0.5f), dy = fmul(fdiv(1.0f, (float)src.H), 0.5f);   // :18
+    const float u = fdiv(fadd((float)x, 0.5f), (float)dw), v = fdiv(fadd((float)y, 0.5f), (float)dh);
+    const V3 s0 = rgb(texture16(src, fadd(u, fmul(-dx, 2.0f)), fadd(v, 0.0f)));            // :21-29
+    const V3 s1 = rgb(texture16(src, fadd(u, -dx), fadd(v, -dy)));
+    const V3 s2 = rgb(texture16(src, fadd(u, 0.0f), fadd(v, fmul(-dy, 2.0f))));
+    const V3 s3 = rgb(texture16(src, fadd(u, dx), fadd(v, -dy)));
+    const V3 s4 = rgb(texture16(src, fadd(u, fmul(dx, 2.0f)), fadd(v, 0.0f)));
+    const V3 s5 = rgb(texture16(src, fadd(u, dx), fadd(v, dy)));
+    const V3 s6 = rgb(texture16(src, fadd(u, 0.0f), fadd(v, fmul(dy, 2.0f))));
+    const V3 s7 = rgb(texture16(src, fadd(u, -dx), fadd(v, dy)));
+    const V3 s8 = rgb(texture16(src, u, v));
+    V3 r = scale3(s8, 4.0f);                                                               // :32-38
+    r = add3(r, scale3(add3(add3(add3(s1, s3), s5), s7), 2.0f));
+    r = add3(r, add3(add3(add3(s0, s2), s4), s6));
+    r = divs3(r, 16.0f);
+    r = scale3(r, intensity);
+    const V4 d = unpack_rgba16f(dst[(size_t)y * dw + x]);
+    dst[(size_t)y * dw + x] = pack_rgba16f(fadd(r.x, d.x), fadd(r.y, d.y), fadd(r.z, d.z), 1.0f);
+}
+
+cudaError_t launch_bloom_upsample_add(const void* src, uint32_t sw, uint32_t sh, void* dst, uint32_t dw,
+                                      uint32_t dh, float intensity, cudaStream_t s, uint64_t* launches) {
+    const Tex16 t{static_cast<const uint2*>(src), (int)sw, (int)sh};
+    const dim3 grid((dw + 31) / 32, (dh + 7) / 8);
+    k_bloom_upsample_add<<<grid, 256, 0, s>>>(t, static_cast<uint2*>(dst), (int)dw, (int)dh, intensity);
+    ++*launches;
+    return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------- tonemap (tonemapping.frag:20-49, PIN-11)
+__device__ __forceinline__ float aces(float x) {                                           // :20-27
+    return gclamp(fdiv(fmul(x, fadd(fmul(2.51f, x), 0.03f)), fadd(fmul(x, fadd(fmul(2.43f, x), 0.59f)), 0.14f)), 0.0f, 1.0f);
+}
+__device__ __forceinline__ uint32_t to_unorm8(float l) {
+    return (uint32_t)floorf(fadd(fmul(gclamp(l, 0.0f, 1.0f), 255.0f), 0.5f));
+}
+
+template <bool CENTER>
+__global__ void __launch_bounds__(256)
+k_tonemap(Tex16 hdr, Tex16 bloom, uint32_t* __restrict__ ldr8, AshPostProcessPushConstants pc) {
+    const int x = blockIdx.x * 32 + (threadIdx.x & 31), y = blockIdx.y * 8 + (threadIdx.x >> 5);
+    if (x >= hdr.W || y >= hdr.H) return;
+    V3 c, b = {0.0f, 0.0f, 0.0f};
+    if (CENTER) {
+        c = rgb(fetch16(hdr, x, y));
+        if (bloom.p) b = rgb(fetch16(bloom, x, y));
+    } else {
+        const float u = fdiv(fadd((float)x, 0.5f), (float)hdr.W), v = fdiv(fadd((float)y, 0.5f), (float)hdr.H);
+        c = rgb(texture16(hdr, u, v));
+        if (bloom.p) b = rgb(texture16(bloom, u, v));
+    }
+    c = add3(c, scale3(b, pc.bloom_intensity));                                            // :38
+    c = scale3(c, pc.exposure);                                                            // :41
+    const float ig = fdiv(1.0f, pc.gamma);
+    const uint32_t r8 = to_unorm8(powf(aces(c.x), ig));                                    // :44-47
+    const uint32_t g8 = to_unorm8(powf(aces(c.y), ig));
+    const uint32_t b8 = to_unorm8(powf(aces(c.z), ig));
+    ldr8[(size_t)y * hdr.W + x] = r8 | (g8 << 8) | (b8 << 16) | 0xFF000000u;
+}
+
+cudaError_t launch_tonemap(const void* hdr, const void* bloom_or_null, void* ldr8, uint32_t W, uint32_t H,
+                           const AshPostProcessPushConstants& pc, uint32_t srgb, cudaStream_t s,
+                           uint64_t* launches) {
+    (void)srgb;
+    const Tex16 h{static_cast<const uint2*>(hdr), (int)W, (int)H}, b{static_cast<const uint2*>(bloom_or_null), (int)W, (int)H};
+    const dim3 grid((W + 31) / 32, (H + 7) / 8);
+    if (W <= 4096 && H <= 4096) k_tonemap<true><<<grid, 256, 0, s>>>(h, b, static_cast<uint32_t*>(ldr8), pc);
+    else k_tonemap<false><<<grid, 256, 0, s>>>(h, b, static_cast<uint32_t*>(ldr8), pc);
+    ++*launches;
+    return cudaGetLastError();
+}
+
+}  // namespace ash

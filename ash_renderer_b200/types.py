@@ -1,0 +1,62 @@
+"""POD layouts of the reference's #[repr(C)] structs as numpy dtypes (host-side mirror).
+
+Sizes are the reference's: CullObjectData 112 B (occlusion_culling.rs:72-91, test :311-314),
+IndirectDrawCommand 20 B (:114-120), CullingPushConstants 96 B (:125-136), GpuLight 64 B
+(features/light_culling.rs:28-37), LightCullingPushConstants 16 B (:69-76), CullingCameraData
+208 B (:81-86), TaaPushConstants 48 B (temporal_aa.rs:86-97), PostProcessPushConstants 16 B
+(fullscreen_pass.rs:152-163).  include/ashcuda.h declares the same layouts for C.
+"""
+import numpy as np
+
+CULL_OBJECT = np.dtype([("center", "<f4", 4), ("extents", "<f4", 4), ("model", "<f4", (4, 4)),
+                        ("draw_index", "<u4"), ("lod_bias", "<f4"), ("flags", "<u4"),
+                        ("_padding", "<u4")])
+DRAW_COMMAND = np.dtype([("index_count", "<u4"), ("instance_count", "<u4"), ("first_index", "<u4"),
+                         ("vertex_offset", "<i4"), ("first_instance", "<u4")])
+GPU_LIGHT = np.dtype([("position", "<f4", 4), ("color", "<f4", 4), ("direction", "<f4", 4),
+                      ("params", "<f4", 4)])
+CULLING_PC = np.dtype([("view_proj", "<f4", (4, 4)), ("screen_params", "<f4", 4),
+                       ("object_count", "<u4"), ("hiz_levels", "<u4"), ("_padding", "<u4", 2)])
+LIGHT_PC = np.dtype([("screen_size", "<u4", 2), ("light_count", "<u4"), ("_padding", "<u4")])
+CAMERA_DATA = np.dtype([("view", "<f4", (4, 4)), ("projection", "<f4", (4, 4)),
+                        ("inv_projection", "<f4", (4, 4)), ("camera_pos", "<f4", 4)])
+TAA_PC = np.dtype([("screen_params", "<f4", 4), ("params", "<f4", 4), ("jitter", "<f4", 2),
+                   ("prev_jitter", "<f4", 2)])
+POST_PC = np.dtype([("exposure", "<f4"), ("gamma", "<f4"), ("bloom_intensity", "<f4"),
+                    ("_padding", "<f4")])
+BLOOM_PARAMS = np.dtype([("threshold", "<f4"), ("upsample_intensity", "<f4"), ("mip_count", "<u4"),
+                         ("_padding", "<u4")])
+CONFIG = np.dtype([("max_objects", "<u4"), ("max_lights", "<u4"), ("max_draws", "<u4"),
+                   ("hiz_levels", "<u4"), ("bloom_mips", "<u4"), ("enable_post", "<u4"),
+                   ("srgb_encode", "<u4"), ("_reserved", "<u4", 9)])
+VIEW_STATS = np.dtype([("view_id", "<u4"), ("total_objects", "<u4"), ("visible_objects", "<u4"),
+                       ("tiles", "<u4"), ("sum_tile_lights", "<u4"), ("max_tile_lights", "<u4"),
+                       ("overflow_tiles", "<u4"), ("candidate_lights", "<u4")])
+VIEW_PARAMS = np.dtype([("cull", CULLING_PC), ("light", LIGHT_PC), ("camera", CAMERA_DATA),
+                        ("taa", TAA_PC), ("bloom", BLOOM_PARAMS), ("post", POST_PC),
+                        ("view_id", "<u4"), ("stages", "<u4"), ("_padding", "<u4", 2)])
+
+assert CULL_OBJECT.itemsize == 112 and DRAW_COMMAND.itemsize == 20 and CULLING_PC.itemsize == 96
+assert GPU_LIGHT.itemsize == 64 and LIGHT_PC.itemsize == 16 and CAMERA_DATA.itemsize == 208
+assert TAA_PC.itemsize == 48 and POST_PC.itemsize == 16 and BLOOM_PARAMS.itemsize == 16
+assert CONFIG.itemsize == 64 and VIEW_STATS.itemsize == 32
+assert VIEW_PARAMS.itemsize == 96 + 16 + 208 + 48 + 16 + 16 + 16
+
+TILE_SIZE = 16
+MAX_LIGHTS_PER_TILE = 256
+TILE_STRIDE = 257
+
+STAGE_HIZ, STAGE_CULL, STAGE_LIGHTS, STAGE_TAA, STAGE_BLOOM, STAGE_TONEMAP = 1, 2, 4, 8, 16, 32
+STAGE_ALL = 0x3F
+
+BUF_VISIBILITY, BUF_DRAWS_OUT, BUF_VISIBLE_COUNT, BUF_TILE_DATA = 1, 2, 3, 4
+BUF_TAA_OUT, BUF_LDR8, BUF_STATS, BUF_TILE_MINMAX, BUF_VISIBILITY_BITS = 5, 6, 7, 8, 9
+BUF_BLOOM_THRESHOLD = 10
+
+
+def BUF_HIZ_MIP(i):
+    return 0x100 + i
+
+
+def BUF_BLOOM_MIP(i):
+    return 0x200 + i

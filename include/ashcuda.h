@@ -1,0 +1,237 @@
+/* ashcuda.h — C ABI of libashcuda, the sm_100a CUDA backend for Ash-Renderer's per-frame
+ * data-parallel compute path (Hi-Z pyramid, frustum + Hi-Z occlusion cull, 16x16 tiled light
+ * cull, TAA resolve, bloom threshold/down/up, ACES tonemap).
+ *
+ * Every POD struct below is byte-identical to the reference's #[repr(C)] Rust struct it names
+ * (paths relative to the reference repo), so a Rust `extern "C"` block can pass `&T` straight
+ * through.  Every entry point cites the reference interface it replaces.
+ *
+ * Conventions: return 0 (ASH_OK) on success, a negative ASH_ERR_* otherwise; never aborts, never
+ * throws across the boundary.  One ctx = one CUDA device + one stream, used by one thread at a
+ * time (the reference's `RenderFeature: Send`, not `Sync` — features/feature_trait.rs:25).
+ * Stage calls only enqueue work on the ctx stream; ashcuda_sync / ashcuda_readback wait.
+ * There is no CPU fallback: without a CUDA device ashcuda_create fails with ASH_ERR_DEVICE.
+ */
+#ifndef ASHCUDA_H
+#define ASHCUDA_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ---- status codes (mirror `enum AshError`, src/error.rs:12-29) -------------------------- */
+#define ASH_OK                   0
+#define ASH_ERR_DEVICE          -1 /* VulkanError / DeviceInitFailed: a CUDA call failed      */
+#define ASH_ERR_NOT_INITIALIZED -2 /* FeatureNotInitialized: a stage ran before its inputs    */
+#define ASH_ERR_NOT_FOUND       -3 /* ResourceNotFound: unknown buffer id / mip               */
+#define ASH_ERR_INVALID         -4 /* bad argument (null, zero extent, size mismatch)         */
+#define ASH_ERR_OUT_OF_MEMORY   -5 /* cudaMalloc failed                                       */
+
+/* ---- constants (reference defaults; all are runtime-overridable via AshCudaConfig) ------- */
+#define ASH_TILE_SIZE            16u  /* features/light_culling.rs:23, light_culling.comp:9-10 */
+#define ASH_MAX_LIGHTS_PER_TILE 256u  /* features/light_culling.rs:20, light_culling.comp:15   */
+#define ASH_TILE_STRIDE         257u  /* light_culling.comp:119                                */
+#define ASH_DEFAULT_HIZ_LEVELS   10u  /* occlusion_culling.rs:21                               */
+#define ASH_DEFAULT_MAX_LIGHTS 1024u  /* features/light_culling.rs:17 (host cap, lifted here)  */
+#define ASH_DEFAULT_MAX_OBJECTS 65536u/* occlusion_culling.rs:18      (host cap, lifted here)  */
+#define ASH_MAX_BLOOM_MIPS        8u
+
+/* ---- POD structs ------------------------------------------------------------------------ */
+
+/* CullBoundingBox, occlusion_culling.rs:26-31 ; BoundingBox, occlusion_cull.comp:14-17 */
+typedef struct AshCullBoundingBox {
+    float center[4];
+    float extents[4];
+} AshCullBoundingBox;
+
+/* CullObjectData (112 B), occlusion_culling.rs:72-91 ; ObjectData, occlusion_cull.comp:19-26.
+ * model[c] is COLUMN c (the Rust fields are named model_row* but hold to_cols_array_2d()). */
+typedef struct AshCullObjectData {
+    AshCullBoundingBox bounds;
+    float    model[4][4];
+    uint32_t draw_index;
+    float    lod_bias;
+    uint32_t flags;      /* bit 0 = enabled */
+    uint32_t _padding;
+} AshCullObjectData;
+
+/* IndirectDrawCommand (20 B), occlusion_culling.rs:114-120 ; DrawCommand, occlusion_cull.comp:28-34 */
+typedef struct AshIndirectDrawCommand {
+    uint32_t index_count;
+    uint32_t instance_count;
+    uint32_t first_index;
+    int32_t  vertex_offset;
+    uint32_t first_instance;
+} AshIndirectDrawCommand;
+
+/* CullingPushConstants (96 B), occlusion_culling.rs:125-136 ; occlusion_cull.comp:69-75 */
+typedef struct AshCullingPushConstants {
+    float    view_proj[4][4];   /* column-major: view_proj[c] is column c */
+    float    screen_params[4];  /* w, h, 1/w, 1/h */
+    uint32_t object_count;
+    uint32_t hiz_levels;
+    uint32_t _padding[2];
+} AshCullingPushConstants;
+
+/* GpuLight (64 B), features/light_culling.rs:28-37 ; Light, light_culling.comp:18-23 */
+typedef struct AshGpuLight {
+    float position[4];   /* xyz, radius */
+    float color[4];      /* rgb, intensity */
+    float direction[4];  /* xyz, type (0 point, 1 spot, 2 directional) */
+    float params[4];     /* inner, outer, falloff, enabled */
+} AshGpuLight;
+
+/* LightCullingPushConstants (16 B), features/light_culling.rs:69-76 ; light_culling.comp:26-30 */
+typedef struct AshLightCullingPushConstants {
+    uint32_t screen_size[2];
+    uint32_t light_count;
+    uint32_t _padding;
+} AshLightCullingPushConstants;
+
+/* CullingCameraData (208 B), features/light_culling.rs:81-86 ; CameraData, light_culling.comp:48-53 */
+typedef struct AshCullingCameraData {
+    float view[4][4];
+    float projection[4][4];
+    float inv_projection[4][4];
+    float camera_pos[4];
+} AshCullingCameraData;
+
+/* TaaPushConstants (48 B), temporal_aa.rs:86-97 ; taa_resolve.comp:22-27 */
+typedef struct AshTaaPushConstants {
+    float screen_params[4];  /* w, h, 1/w, 1/h */
+    float params[4];         /* blend, colour clamp on, velocity rejection on, pad */
+    float jitter[2];
+    float prev_jitter[2];
+} AshTaaPushConstants;
+
+/* PostProcessPushConstants (16 B), fullscreen_pass.rs:152-163 ; tonemapping.frag:11-16 */
+typedef struct AshPostProcessPushConstants {
+    float exposure;
+    float gamma;
+    float bloom_intensity;
+    float _padding;
+} AshPostProcessPushConstants;
+
+/* Bloom chain parameters: BloomConfig (features/bloom.rs:9-33) as the three bloom shaders see
+ * it (bloom_threshold.frag:10-15, bloom_downsample.frag:10-14, bloom_upsample.frag:10-14). */
+typedef struct AshBloomParams {
+    float    threshold;           /* bloom.rs:27  = 0.8 */
+    float    upsample_intensity;  /* bloom_upsample.frag:12, 1.0 in the pinned chain */
+    uint32_t mip_count;           /* bloom.rs:29  = 5   */
+    uint32_t _padding;
+} AshBloomParams;
+
+/* Library configuration; zero-initialise then call ashcuda_default_config(). */
+typedef struct AshCudaConfig {
+    uint32_t max_objects;     /* capacity of the object/visibility/draw buffers            */
+    uint32_t max_lights;      /* capacity of the light buffer                              */
+    uint32_t max_draws;       /* capacity of the draw-command template buffer              */
+    uint32_t hiz_levels;      /* value pushed as hizLevels is min(levels_built, this)      */
+    uint32_t bloom_mips;      /* bloom chain depth allocated (<= ASH_MAX_BLOOM_MIPS)       */
+    uint32_t enable_post;     /* 0: allocate no colour/TAA/bloom/LDR targets               */
+    uint32_t srgb_encode;     /* 1: extra sRGB OETF on the 8-bit store (swapchain.rs:81-88) */
+    uint32_t _reserved[9];
+} AshCudaConfig;
+
+/* Per-view statistics (OcclusionStats, occlusion_culling.rs:152-185 + tile list stats).
+ * This 32-byte record is the only thing exchanged between GPUs (allgather). */
+typedef struct AshViewStats {
+    uint32_t view_id;
+    uint32_t total_objects;
+    uint32_t visible_objects;
+    uint32_t tiles;
+    uint32_t sum_tile_lights;
+    uint32_t max_tile_lights;
+    uint32_t overflow_tiles;   /* tiles whose true count exceeded 256 */
+    uint32_t candidate_lights; /* lights surviving the per-view depth-slab prefilter */
+} AshViewStats;
+
+/* Everything that changes per view-frame, for ashcuda_view_run. */
+typedef struct AshCudaViewParams {
+    AshCullingPushConstants      cull;
+    AshLightCullingPushConstants light;
+    AshCullingCameraData         camera;
+    AshTaaPushConstants          taa;
+    AshBloomParams               bloom;
+    AshPostProcessPushConstants  post;
+    uint32_t view_id;
+    uint32_t stages;           /* bitmask of ASH_STAGE_* */
+    uint32_t _padding[2];
+} AshCudaViewParams;
+
+#define ASH_STAGE_HIZ        0x01u
+#define ASH_STAGE_CULL       0x02u
+#define ASH_STAGE_LIGHTS     0x04u
+#define ASH_STAGE_TAA        0x08u
+#define ASH_STAGE_BLOOM      0x10u
+#define ASH_STAGE_TONEMAP    0x20u
+#define ASH_STAGE_ALL        0x3Fu
+
+/* Buffer ids for ashcuda_get / ashcuda_readback. */
+#define ASH_BUF_HIZ_MIP(i)    (0x100 + (i)) /* fp32 W_i x H_i; mip 0 is the depth buffer      */
+#define ASH_BUF_BLOOM_MIP(i)  (0x200 + (i)) /* RGBA16F; i=0 is U_0 (the bloom buffer)          */
+#define ASH_BUF_VISIBILITY     1  /* u32[object_count]                    (binding 3)         */
+#define ASH_BUF_DRAWS_OUT      2  /* AshIndirectDrawCommand[visible]      (binding 4)         */
+#define ASH_BUF_VISIBLE_COUNT  3  /* u32                                  (binding 5)         */
+#define ASH_BUF_TILE_DATA      4  /* u32[tiles*257]                       (light binding 2)   */
+#define ASH_BUF_TAA_OUT        5  /* RGBA16F W x H (this frame's resolve = next history)      */
+#define ASH_BUF_LDR8           6  /* RGBA8 W x H                                               */
+#define ASH_BUF_STATS          7  /* AshViewStats                                              */
+#define ASH_BUF_TILE_MINMAX    8  /* u32[tiles*2]: float bits of tile min/max depth            */
+#define ASH_BUF_VISIBILITY_BITS 9 /* u32[ceil(n/32)] 1 bit per object                          */
+#define ASH_BUF_BLOOM_THRESHOLD 10/* RGBA16F W x H: T = D_0 (staged path only)                 */
+
+typedef struct ashcuda_ctx ashcuda_ctx;
+
+/* --- lifetime: replaces LightCullingPipeline::new / Drop (vulkan/light_culling_pipeline.rs:41-243,
+ *     332-351), ComputePipeline::new (vulkan/compute_pipeline.rs:17-64), HdrFramebuffer::new
+ *     (renderer/hdr_framebuffer.rs:25-110). */
+void ashcuda_default_config(AshCudaConfig* cfg);
+int  ashcuda_create(ashcuda_ctx** out, int device, uint32_t width, uint32_t height,
+                    const AshCudaConfig* cfg_or_null);
+void ashcuda_destroy(ashcuda_ctx* ctx);                       /* NULL is a no-op */
+int  ashcuda_set_stream(ashcuda_ctx* ctx, void* cuda_stream); /* adopt a caller stream (NULL = own) */
+
+/* --- inputs.  on_device=0: host pointer, copied with cudaMemcpyAsync on the ctx stream.
+ *     on_device=1: device pointer, BORROWED (zero-copy) until replaced; caller keeps it alive.
+ *     Replaces upload_lights / upload_camera (light_culling_pipeline.rs:248-281), the descriptor
+ *     writes of :161-205, and OcclusionCulling::object_data uploads (occlusion_culling.rs:247-249). */
+int ashcuda_set_depth  (ashcuda_ctx*, const float* depth_wh, int on_device);
+int ashcuda_set_objects(ashcuda_ctx*, const AshCullObjectData* objs, uint32_t n,
+                        const AshIndirectDrawCommand* draws_in, uint32_t n_draws, int on_device);
+int ashcuda_set_lights (ashcuda_ctx*, const AshGpuLight* lights, uint32_t n, int on_device);
+int ashcuda_set_camera (ashcuda_ctx*, const AshCullingCameraData* cam);
+int ashcuda_set_color  (ashcuda_ctx*, const void* hdr_rgba16f, const void* velocity_rg16f_or_null,
+                        int on_device);
+/* TemporalAA::reset_history (temporal_aa.rs:203-207): next resolve uses current colour as history */
+int ashcuda_taa_reset_history(ashcuda_ctx*);
+
+/* --- stages: one per reference shader dispatch. */
+int ashcuda_hiz_build     (ashcuda_ctx*);                                        /* hiz_generate.comp x levels */
+int ashcuda_occlusion_cull(ashcuda_ctx*, const AshCullingPushConstants*);        /* occlusion_cull.comp        */
+int ashcuda_light_cull    (ashcuda_ctx*, const AshLightCullingPushConstants*);   /* LightCullingPipeline::dispatch, :286-319 */
+int ashcuda_taa_resolve   (ashcuda_ctx*, const AshTaaPushConstants*);            /* taa_resolve.comp           */
+int ashcuda_bloom         (ashcuda_ctx*, const AshBloomParams*);                 /* bloom_{threshold,downsample,upsample}.frag */
+int ashcuda_tonemap       (ashcuda_ctx*, const AshPostProcessPushConstants*);    /* tonemapping.frag           */
+/* the whole view-frame in one call, fused kernels, same results as the staged calls */
+int ashcuda_view_run      (ashcuda_ctx*, const AshCudaViewParams*);
+
+/* --- outputs: device pointers owned by ctx, valid until the next call that rewrites them.
+ *     Replaces LightCullingPipeline::tile_buffer / tile_buffer_size (:322-330). */
+int ashcuda_get     (ashcuda_ctx*, int which, void** dev_ptr, size_t* bytes);
+int ashcuda_readback(ashcuda_ctx*, int which, void* host_dst, size_t bytes);  /* syncs the stream */
+int ashcuda_readback_async(ashcuda_ctx*, int which, void* host_dst, size_t bytes); /* no sync */
+int ashcuda_sync    (ashcuda_ctx*);
+int ashcuda_hiz_level_count(ashcuda_ctx*);                     /* levels_built (PIN-4) */
+int ashcuda_mip_extent(ashcuda_ctx*, int which, uint32_t* w, uint32_t* h);
+uint64_t ashcuda_kernel_launches(ashcuda_ctx*);                /* kernels launched so far by this ctx */
+const char* ashcuda_last_error(ashcuda_ctx*);                  /* NULL ctx: last create error */
+const char* ashcuda_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ASHCUDA_H */

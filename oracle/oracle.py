@@ -1,0 +1,202 @@
+"""ctypes/numpy front-end of the CPU oracle (oracle/ash_oracle.cpp).
+
+TEST INFRASTRUCTURE ONLY: imported by tests/, __graft_entry__.smoke() and bench.py's
+cpu_baseline / --impl reference legs.  The product package (ash_renderer_b200/) never imports it.
+Parity is unpinned by the reference (see the header of ash_oracle.cpp).
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB_PATH = os.path.join(_HERE, "libashoracle.so")
+
+TILE_STRIDE = 257
+
+OBJECT_DTYPE = np.dtype([("center", "<f4", 4), ("extents", "<f4", 4), ("model", "<f4", (4, 4)),
+                         ("draw_index", "<u4"), ("lod_bias", "<f4"), ("flags", "<u4"), ("_padding", "<u4")])
+DRAW_DTYPE = np.dtype([("index_count", "<u4"), ("instance_count", "<u4"), ("first_index", "<u4"),
+                       ("vertex_offset", "<i4"), ("first_instance", "<u4")])
+LIGHT_DTYPE = np.dtype([("position", "<f4", 4), ("color", "<f4", 4), ("direction", "<f4", 4),
+                        ("params", "<f4", 4)])
+CULL_PC_DTYPE = np.dtype([("view_proj", "<f4", (4, 4)), ("screen_params", "<f4", 4),
+                          ("object_count", "<u4"), ("hiz_levels", "<u4"), ("_padding", "<u4", 2)])
+LIGHT_PC_DTYPE = np.dtype([("screen_size", "<u4", 2), ("light_count", "<u4"), ("_padding", "<u4")])
+CAMERA_DTYPE = np.dtype([("view", "<f4", (4, 4)), ("projection", "<f4", (4, 4)),
+                         ("inv_projection", "<f4", (4, 4)), ("camera_pos", "<f4", 4)])
+TAA_PC_DTYPE = np.dtype([("screen_params", "<f4", 4), ("params", "<f4", 4), ("jitter", "<f4", 2),
+                         ("prev_jitter", "<f4", 2)])
+POST_PC_DTYPE = np.dtype([("exposure", "<f4"), ("gamma", "<f4"), ("bloom_intensity", "<f4"),
+                          ("_padding", "<f4")])
+
+
+def build(force=False):
+    """Compile libashoracle.so with the committed Makefile (g++ -O2 -fopenmp -ffp-contract=off)."""
+    src = os.path.join(_HERE, "ash_oracle.cpp")
+    if (not force and os.path.exists(_LIB_PATH)
+            and os.path.getmtime(_LIB_PATH) >= os.path.getmtime(src)):
+        return _LIB_PATH
+    env = dict(os.environ)
+    env.pop("CXX", None)
+    subprocess.run(["make", "-C", _HERE, "-B" if force else "-s"], check=True, env=env,
+                   stdout=subprocess.DEVNULL)
+    return _LIB_PATH
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        build()
+        _lib = C.CDLL(_LIB_PATH)
+        _lib.ash_oracle_hiz_build.restype = C.c_size_t
+        _lib.ash_oracle_occlusion_cull.restype = C.c_uint32
+        _lib.ash_oracle_halton.restype = C.c_float
+        _lib.ash_oracle_halton.argtypes = [C.c_uint32, C.c_uint32]
+        _lib.ash_oracle_h2f.restype = C.c_float
+        _lib.ash_oracle_f2h.restype = C.c_uint16
+        _lib.ash_oracle_f2h.argtypes = [C.c_float]
+    return _lib
+
+
+def _p(a):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+def _c(a, dtype):
+    a = np.ascontiguousarray(a, dtype=dtype)
+    return a
+
+
+def num_threads():
+    return int(lib().ash_oracle_num_threads())
+
+
+# ---------------------------------------------------------------- Hi-Z
+def mip_extents(W, H):
+    """[(w,h)] for mips 0..levels-1, PIN-3/4: floor halving, floor(log2(max))+1 levels."""
+    n = int(lib().ash_oracle_hiz_level_count(int(W), int(H)))
+    out, w, h = [(W, H)], W, H
+    for _ in range(1, n):
+        w, h = max(1, w // 2), max(1, h // 2)
+        out.append((w, h))
+    return out
+
+
+def hiz_build(depth):
+    """depth: (H,W) f32 -> list of mips [mip1, mip2, ...] (each (h,w) f32) and the flat buffer."""
+    depth = _c(depth, np.float32)
+    H, W = depth.shape
+    ext = mip_extents(W, H)
+    total = sum(w * h for (w, h) in ext[1:])
+    flat = np.empty(max(total, 1), np.float32)
+    n = lib().ash_oracle_hiz_build(_p(depth), W, H, _p(flat))
+    assert n == total
+    mips, off = [], 0
+    for (w, h) in ext[1:]:
+        mips.append(flat[off:off + w * h].reshape(h, w))
+        off += w * h
+    return mips, flat
+
+
+# ---------------------------------------------------------------- occlusion cull
+def occlusion_cull(objs, draws_in, pc, depth, mips_flat=None):
+    objs = _c(objs, OBJECT_DTYPE)
+    draws_in = _c(draws_in, DRAW_DTYPE)
+    pc = _c(pc, CULL_PC_DTYPE).reshape(1)
+    depth = _c(depth, np.float32)
+    H, W = depth.shape
+    if mips_flat is None:
+        _, mips_flat = hiz_build(depth)
+    n = int(pc["object_count"][0])
+    vis = np.zeros(max(n, 1), np.uint32)
+    draws_out = np.zeros(max(n, 1), DRAW_DTYPE)
+    cnt = lib().ash_oracle_occlusion_cull(_p(objs), _p(draws_in), _p(pc), _p(depth), _p(mips_flat),
+                                          W, H, _p(vis), _p(draws_out))
+    return vis[:n], draws_out[:cnt], int(cnt)
+
+
+# ---------------------------------------------------------------- light cull
+def light_cull(lights, pc, cam, depth):
+    lights = _c(lights, LIGHT_DTYPE)
+    pc = _c(pc, LIGHT_PC_DTYPE).reshape(1)
+    cam = _c(cam, CAMERA_DTYPE).reshape(1)
+    depth = _c(depth, np.float32)
+    W, H = int(pc["screen_size"][0][0]), int(pc["screen_size"][0][1])
+    assert depth.shape == (H, W)
+    tiles = ((W + 15) // 16) * ((H + 15) // 16)
+    tile_data = np.full(tiles * TILE_STRIDE, 0xFFFFFFFF, np.uint32)
+    true_counts = np.zeros(tiles, np.uint32)
+    minmax = np.zeros(tiles * 2, np.uint32)
+    lib().ash_oracle_light_cull(_p(lights), _p(pc), _p(cam), _p(depth), _p(tile_data), _p(true_counts),
+                                _p(minmax))
+    return tile_data.reshape(tiles, TILE_STRIDE), true_counts, minmax.reshape(tiles, 2)
+
+
+# ---------------------------------------------------------------- post chain
+def taa_resolve(current, history, velocity, pc):
+    """current/history: (H,W,4) float16; velocity: (H,W,2) float16 or None."""
+    current = _c(current, np.float16)
+    history = _c(history, np.float16)
+    velocity = None if velocity is None else _c(velocity, np.float16)
+    pc = _c(pc, TAA_PC_DTYPE).reshape(1)
+    out = np.empty_like(current)
+    lib().ash_oracle_taa_resolve(_p(current), _p(history), _p(velocity), _p(pc), _p(out))
+    return out
+
+
+def halton(index, base):
+    return float(lib().ash_oracle_halton(int(index), int(base)))
+
+
+def bloom_threshold(hdr, threshold):
+    hdr = _c(hdr, np.float16)
+    H, W, _ = hdr.shape
+    out = np.empty_like(hdr)
+    lib().ash_oracle_bloom_threshold(_p(hdr), W, H, C.c_float(threshold), _p(out))
+    return out
+
+
+def bloom_downsample(src):
+    src = _c(src, np.float16)
+    sh, sw, _ = src.shape
+    dw, dh = max(1, sw // 2), max(1, sh // 2)
+    dst = np.empty((dh, dw, 4), np.float16)
+    lib().ash_oracle_bloom_downsample(_p(src), sw, sh, _p(dst), dw, dh)
+    return dst
+
+
+def bloom_upsample_add(src, dst, intensity=1.0):
+    """returns RN16(dst + upsample(src)); dst is not modified."""
+    src = _c(src, np.float16)
+    out = np.array(dst, dtype=np.float16, order="C", copy=True)
+    sh, sw, _ = src.shape
+    dh, dw, _ = out.shape
+    lib().ash_oracle_bloom_upsample_add(_p(src), sw, sh, _p(out), dw, dh, C.c_float(intensity))
+    return out
+
+
+def bloom_chain(hdr, threshold=0.8, mip_count=5, intensity=1.0):
+    """PIN-9 topology. Returns (U list [U_0..U_mip_count], D list [D_0..D_mip_count])."""
+    D = [bloom_threshold(hdr, threshold)]
+    for _ in range(mip_count):
+        D.append(bloom_downsample(D[-1]))
+    U = [None] * (mip_count + 1)
+    U[mip_count] = D[mip_count]
+    for k in range(mip_count - 1, -1, -1):
+        U[k] = bloom_upsample_add(U[k + 1], D[k], intensity)
+    return U, D
+
+
+def tonemap(hdr, bloom, pc):
+    hdr = _c(hdr, np.float16)
+    bloom = None if bloom is None else _c(bloom, np.float16)
+    pc = _c(pc, POST_PC_DTYPE).reshape(1)
+    H, W, _ = hdr.shape
+    out = np.empty((H, W, 4), np.uint8)
+    lib().ash_oracle_tonemap(_p(hdr), _p(bloom), W, H, _p(pc), _p(out))
+    return out
