@@ -3,6 +3,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <string>
+#include <vector>
 #include "../../include/ashcuda.h"
 
 namespace ash {
@@ -29,6 +30,40 @@ struct BloomChain {
 // One candidate light after the per-view prepass: view-space centre + radius, original index.
 struct LightCand { float x, y, z, r; };
 
+// Per-kernel-class device timing (ashcuda_profile_kernels / ashcuda_kernel_time_ms): CUDA events
+// recorded on the ctx stream around each launch of a selected class, resolved lazily on query.
+struct Profiler {
+    struct Span { int id; cudaEvent_t a, b; };
+    uint32_t mask = 0;
+    std::vector<Span> open;                 // recorded, not yet resolved
+    std::vector<cudaEvent_t> pool;          // free events
+    double   ms[ASH_KERNEL_COUNT] = {};
+    uint64_t n[ASH_KERNEL_COUNT] = {};
+    cudaEvent_t get();
+    void resolve();
+    void release_all();
+};
+
+// What every launch wrapper needs: the stream, the launch counter, the optional profiler.
+struct Launch {
+    cudaStream_t s;
+    uint64_t*    launches;
+    Profiler*    prof;
+};
+// RAII: counts the launch and brackets it with events when its class is being profiled.
+struct Timed {
+    const Launch& L; int id; cudaEvent_t b = nullptr;
+    Timed(const Launch& l, int kid) : L(l), id(kid) {
+        ++*L.launches;
+        if (L.prof && (L.prof->mask >> id & 1u)) {
+            cudaEvent_t a = L.prof->get(); b = L.prof->get();
+            cudaEventRecord(a, L.s);
+            L.prof->open.push_back({id, a, b});
+        }
+    }
+    ~Timed() { if (b) cudaEventRecord(b, L.s); }
+};
+
 }  // namespace ash
 
 struct ashcuda_ctx {
@@ -39,6 +74,8 @@ struct ashcuda_ctx {
     AshCudaConfig cfg{};
     std::string  err;
     uint64_t     launches = 0;
+    ash::Profiler prof;
+    ash::Launch  L() { return ash::Launch{stream, &launches, &prof}; }
 
     // depth + pyramid
     const float* depth = nullptr;      // current mip 0 (owned copy or borrowed)
@@ -92,28 +129,26 @@ namespace ash {
 
 // each returns cudaGetLastError() after launching on `s`; *launches is incremented per kernel
 cudaError_t launch_depth_pyramid(const Pyramid& p, uint32_t* tile_minmax, uint32_t tiles_x,
-                                 uint32_t* depth_range, uint32_t* ticket, cudaStream_t s,
-                                 uint64_t* launches);
+                                 uint32_t* depth_range, uint32_t* ticket, const Launch& L);
 cudaError_t launch_occlusion_cull(const AshCullObjectData* objs, const AshIndirectDrawCommand* draws_in,
                                   const AshCullingPushConstants& pc, const Pyramid& p,
                                   uint32_t* visibility, uint32_t* vis_bits, uint32_t* cta_counts,
                                   AshIndirectDrawCommand* draws_out, uint32_t* visible_count,
-                                  AshViewStats* stats, cudaStream_t s, uint64_t* launches);
+                                  AshViewStats* stats, const Launch& L);
 cudaError_t launch_light_cull(const AshGpuLight* lights, const AshLightCullingPushConstants& pc,
                               const AshCullingCameraData* cam_dev, const uint32_t* tile_minmax,
                               uint32_t* depth_range, LightCand* cand, uint32_t* cand_idx,
                               uint32_t* cand_count, uint32_t* tile_data, AshViewStats* stats,
-                              cudaStream_t s, uint64_t* launches);
+                              const Launch& L);
 cudaError_t launch_taa(const void* cur, const void* hist, const void* vel, void* out,
-                       const AshTaaPushConstants& pc, cudaStream_t s, uint64_t* launches);
+                       const AshTaaPushConstants& pc, const Launch& L);
 cudaError_t launch_bloom_threshold(const void* hdr, void* out, uint32_t W, uint32_t H, float threshold,
-                                   cudaStream_t s, uint64_t* launches);
+                                   const Launch& L);
 cudaError_t launch_bloom_downsample(const void* src, uint32_t sw, uint32_t sh, void* dst, uint32_t dw,
-                                    uint32_t dh, cudaStream_t s, uint64_t* launches);
+                                    uint32_t dh, const Launch& L);
 cudaError_t launch_bloom_upsample_add(const void* src, uint32_t sw, uint32_t sh, void* dst, uint32_t dw,
-                                      uint32_t dh, float intensity, cudaStream_t s, uint64_t* launches);
+                                      uint32_t dh, float intensity, const Launch& L);
 cudaError_t launch_tonemap(const void* hdr, const void* bloom_or_null, void* ldr8, uint32_t W, uint32_t H,
-                           const AshPostProcessPushConstants& pc, uint32_t srgb, cudaStream_t s,
-                           uint64_t* launches);
+                           const AshPostProcessPushConstants& pc, uint32_t srgb, const Launch& L);
 
 }  // namespace ash

@@ -10,6 +10,27 @@ using namespace ash;
 
 static thread_local std::string g_create_error;
 
+// ---------------------------------------------------------------- Profiler (ash_internal.cuh)
+cudaEvent_t ash::Profiler::get() {
+    if (!pool.empty()) { cudaEvent_t e = pool.back(); pool.pop_back(); return e; }
+    cudaEvent_t e = nullptr;
+    cudaEventCreate(&e);
+    return e;
+}
+void ash::Profiler::resolve() {      // caller has synchronised the stream
+    for (const Span& sp : open) {
+        float t = 0.0f;
+        if (cudaEventElapsedTime(&t, sp.a, sp.b) == cudaSuccess) { ms[sp.id] += t; ++n[sp.id]; }
+        pool.push_back(sp.a); pool.push_back(sp.b);
+    }
+    open.clear();
+}
+void ash::Profiler::release_all() {
+    for (const Span& sp : open) { cudaEventDestroy(sp.a); cudaEventDestroy(sp.b); }
+    for (cudaEvent_t e : pool) cudaEventDestroy(e);
+    open.clear(); pool.clear();
+}
+
 #define ASH_CUDA(ctx, call)                                                              \
     do {                                                                                 \
         cudaError_t e__ = (call);                                                        \
@@ -67,6 +88,7 @@ void ashcuda_destroy(ashcuda_ctx* c) {
                      c->velocity_owned, c->taa[0], c->taa[1], c->bloom_t, c->ldr8};
     for (void* p : owned) if (p) cudaFree(p);
     for (uint32_t k = 1; k <= ASH_MAX_BLOOM_MIPS; ++k) if (c->bloom.d[k]) cudaFree(c->bloom.d[k]);
+    c->prof.release_all();
     if (c->own_stream && c->stream) cudaStreamDestroy(c->stream);
     delete c;
 }
@@ -265,7 +287,7 @@ int ashcuda_hiz_build(ashcuda_ctx* c) {
     // the frame's depth range accumulates by atomics: start from the identity
     ASH_CUDA(c, cudaMemsetAsync(c->depth_range, 0xFF, 8, c->stream));
     ASH_CUDA(c, launch_depth_pyramid(c->pyr, c->tile_minmax, c->tiles_x, c->depth_range, c->counters,
-                                     c->stream, &c->launches));
+                                     c->L()));
     c->have_pyramid = true;
     return ASH_OK;
 }
@@ -284,7 +306,7 @@ int ashcuda_occlusion_cull(ashcuda_ctx* c, const AshCullingPushConstants* pc) {
     }
     ASH_CUDA(c, launch_occlusion_cull(c->objs, c->draws_in, *pc, c->pyr, c->visibility, c->vis_bits,
                                       c->cta_counts, c->draws_out, c->visible_count, c->stats,
-                                      c->stream, &c->launches));
+                                      c->L()));
     return ASH_OK;
 }
 
@@ -298,8 +320,7 @@ int ashcuda_light_cull(ashcuda_ctx* c, const AshLightCullingPushConstants* pc) {
     ASH_CUDA(c, cudaSetDevice(c->device));
     if (!c->have_pyramid) { int rc = ashcuda_hiz_build(c); if (rc) return rc; }
     ASH_CUDA(c, launch_light_cull(c->lights, *pc, c->camera_dev, c->tile_minmax, c->depth_range, c->cand,
-                                  c->cand_idx, c->cand_count, c->tile_data, c->stats, c->stream,
-                                  &c->launches));
+                                  c->cand_idx, c->cand_count, c->tile_data, c->stats, c->L()));
     return ASH_OK;
 }
 
@@ -315,7 +336,7 @@ int ashcuda_taa_resolve(ashcuda_ctx* c, const AshTaaPushConstants* pc) {
     // PIN-12: history(t) = output(t-1); first frame (or after reset_history) history = current colour
     const void* hist = c->history_valid ? c->taa[c->taa_cur] : c->color;
     void* out = c->taa[c->taa_cur ^ 1];
-    ASH_CUDA(c, launch_taa(c->color, hist, c->velocity, out, *pc, c->stream, &c->launches));
+    ASH_CUDA(c, launch_taa(c->color, hist, c->velocity, out, *pc, c->L()));
     c->taa_cur ^= 1;
     c->history_valid = true;
     c->taa_ran = true;
@@ -331,12 +352,12 @@ int ashcuda_bloom(ashcuda_ctx* c, const AshBloomParams* bp) {
     if (bp->mip_count > c->bloom.mips) return fail(c, ASH_ERR_INVALID, "bloom: mip_count > config bloom_mips");
     ASH_CUDA(c, cudaSetDevice(c->device));
     BloomChain& b = c->bloom;
-    ASH_CUDA(c, launch_bloom_threshold(resolved_color(c), b.d[0], c->W, c->H, bp->threshold, c->stream, &c->launches));
+    ASH_CUDA(c, launch_bloom_threshold(resolved_color(c), b.d[0], c->W, c->H, bp->threshold, c->L()));
     for (uint32_t k = 1; k <= bp->mip_count; ++k)
-        ASH_CUDA(c, launch_bloom_downsample(b.d[k - 1], b.w[k - 1], b.h[k - 1], b.d[k], b.w[k], b.h[k], c->stream, &c->launches));
+        ASH_CUDA(c, launch_bloom_downsample(b.d[k - 1], b.w[k - 1], b.h[k - 1], b.d[k], b.w[k], b.h[k], c->L()));
     for (int k = (int)bp->mip_count - 1; k >= 0; --k)
         ASH_CUDA(c, launch_bloom_upsample_add(b.d[k + 1], b.w[k + 1], b.h[k + 1], b.d[k], b.w[k], b.h[k],
-                                              bp->upsample_intensity, c->stream, &c->launches));
+                                              bp->upsample_intensity, c->L()));
     c->bloom_valid = true;
     return ASH_OK;
 }
@@ -346,7 +367,7 @@ int ashcuda_tonemap(ashcuda_ctx* c, const AshPostProcessPushConstants* pc) {
     if (!c->have_color) return fail(c, ASH_ERR_NOT_INITIALIZED, "tonemap: no colour buffer set");
     ASH_CUDA(c, cudaSetDevice(c->device));
     ASH_CUDA(c, launch_tonemap(resolved_color(c), c->bloom_valid ? c->bloom.d[0] : nullptr, c->ldr8, c->W, c->H,
-                               *pc, c->cfg.srgb_encode, c->stream, &c->launches));
+                               *pc, c->cfg.srgb_encode, c->L()));
     return ASH_OK;
 }
 
@@ -431,5 +452,47 @@ int ashcuda_sync(ashcuda_ctx* c) {
 }
 
 uint64_t ashcuda_kernel_launches(ashcuda_ctx* c) { return c ? c->launches : 0; }
+
+int ashcuda_profile_kernels(ashcuda_ctx* c, uint32_t mask) {
+    if (!c) return ASH_ERR_INVALID;
+    c->prof.mask = mask & ((1u << ASH_KERNEL_COUNT) - 1u);
+    return ASH_OK;
+}
+
+int ashcuda_kernel_time_ms(ashcuda_ctx* c, int k, float* ms, uint64_t* launches) {
+    if (!c || !ms || !launches || k < 0 || k >= ASH_KERNEL_COUNT) return fail(c, ASH_ERR_INVALID, "kernel_time_ms: bad argument");
+    ASH_CUDA(c, cudaSetDevice(c->device));
+    ASH_CUDA(c, cudaStreamSynchronize(c->stream));
+    c->prof.resolve();
+    *ms = (float)c->prof.ms[k]; *launches = c->prof.n[k];
+    c->prof.ms[k] = 0.0; c->prof.n[k] = 0;
+    return ASH_OK;
+}
+
+int ashcuda_upload_view(ashcuda_ctx* c, const float* depth, const void* hdr, const void* vel) {
+    if (!c) return ASH_ERR_INVALID;
+    int rc = ASH_OK;
+    if (depth) { rc = ashcuda_set_depth(c, depth, 0); if (rc) return rc; }
+    if (hdr) { rc = ashcuda_set_color(c, hdr, vel, 0); if (rc) return rc; }
+    return ASH_OK;
+}
+
+int ashcuda_download_view(ashcuda_ctx* c, uint32_t* visibility, uint32_t* tile_data, uint8_t* ldr8,
+                          AshViewStats* stats, uint32_t* visible_count) {
+    if (!c) return ASH_ERR_INVALID;
+    ASH_CUDA(c, cudaSetDevice(c->device));
+    const size_t P = (size_t)c->W * c->H, tiles = (size_t)c->tiles_x * c->tiles_y;
+    if (visibility && c->n_objs)
+        ASH_CUDA(c, cudaMemcpyAsync(visibility, c->visibility, (size_t)c->n_objs * 4, cudaMemcpyDeviceToHost, c->stream));
+    if (tile_data)
+        ASH_CUDA(c, cudaMemcpyAsync(tile_data, c->tile_data, tiles * ASH_TILE_STRIDE * 4, cudaMemcpyDeviceToHost, c->stream));
+    if (ldr8) {
+        if (!c->ldr8) return fail(c, ASH_ERR_NOT_FOUND, "download_view: post chain disabled");
+        ASH_CUDA(c, cudaMemcpyAsync(ldr8, c->ldr8, P * 4, cudaMemcpyDeviceToHost, c->stream));
+    }
+    if (stats) ASH_CUDA(c, cudaMemcpyAsync(stats, c->stats, sizeof(AshViewStats), cudaMemcpyDeviceToHost, c->stream));
+    if (visible_count) ASH_CUDA(c, cudaMemcpyAsync(visible_count, c->visible_count, 4, cudaMemcpyDeviceToHost, c->stream));
+    return ASH_OK;
+}
 
 }  // extern "C"

@@ -188,13 +188,12 @@ k_depth_pyramid(Pyramid p, uint32_t* __restrict__ tile_minmax, uint32_t tiles_x,
 }
 
 cudaError_t launch_depth_pyramid(const Pyramid& p, uint32_t* tile_minmax, uint32_t tiles_x,
-                                 uint32_t* depth_range, uint32_t* ticket, cudaStream_t s,
-                                 uint64_t* launches) {
+                                 uint32_t* depth_range, uint32_t* ticket, const Launch& L) {
     dim3 grid((p.w[0] + 63u) / 64u, (p.h[0] + 63u) / 64u);
     const bool vec = (p.w[0] % 4u == 0u) && ((reinterpret_cast<uintptr_t>(p.mip0) & 15u) == 0u);
-    if (vec) k_depth_pyramid<true><<<grid, 256, 0, s>>>(p, tile_minmax, tiles_x, depth_range, ticket);
-    else     k_depth_pyramid<false><<<grid, 256, 0, s>>>(p, tile_minmax, tiles_x, depth_range, ticket);
-    ++*launches;
+    Timed timed(L, ASH_KERNEL_DEPTH_PYRAMID);
+    if (vec) k_depth_pyramid<true><<<grid, 256, 0, L.s>>>(p, tile_minmax, tiles_x, depth_range, ticket);
+    else     k_depth_pyramid<false><<<grid, 256, 0, L.s>>>(p, tile_minmax, tiles_x, depth_range, ticket);
     return cudaGetLastError();
 }
 

@@ -180,18 +180,20 @@ cudaError_t launch_light_cull(const AshGpuLight* lights, const AshLightCullingPu
                               const AshCullingCameraData* cam_dev, const uint32_t* tile_minmax,
                               uint32_t* depth_range, LightCand* cand, uint32_t* cand_idx,
                               uint32_t* cand_count, uint32_t* tile_data, AshViewStats* stats,
-                              cudaStream_t s, uint64_t* launches) {
+                              const Launch& L) {
     const uint32_t W = pc.screen_size[0], H = pc.screen_size[1];
     const uint32_t tiles_x = (W + 15u) / 16u, tiles_y = (H + 15u) / 16u, tiles = tiles_x * tiles_y;
-    k_light_prepass<<<1, kPrepassThreads, 0, s>>>(lights, pc.light_count, cam_dev, depth_range, cand,
-                                                  cand_idx, cand_count, stats, tiles);
-    ++*launches;
+    {
+        Timed timed(L, ASH_KERNEL_LIGHT_PREPASS);
+        k_light_prepass<<<1, kPrepassThreads, 0, L.s>>>(lights, pc.light_count, cam_dev, depth_range, cand,
+                                                      cand_idx, cand_count, stats, tiles);
+    }
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return e;
-    k_light_tiles<<<(tiles + kTileWarps - 1) / kTileWarps, kTileWarps * 32, 0, s>>>(
+    Timed timed(L, ASH_KERNEL_LIGHT_TILES);
+    k_light_tiles<<<(tiles + kTileWarps - 1) / kTileWarps, kTileWarps * 32, 0, L.s>>>(
         cam_dev, W, H, tiles_x, tiles, pc.light_count, tile_minmax, cand, cand_idx, cand_count,
         tile_data, stats);
-    ++*launches;
     return cudaGetLastError();
 }
 

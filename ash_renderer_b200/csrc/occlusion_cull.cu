@@ -171,7 +171,7 @@ cudaError_t launch_occlusion_cull(const AshCullObjectData* objs, const AshIndire
                                   const AshCullingPushConstants& pc, const Pyramid& p,
                                   uint32_t* visibility, uint32_t* vis_bits, uint32_t* cta_counts,
                                   AshIndirectDrawCommand* draws_out, uint32_t* visible_count,
-                                  AshViewStats* stats, cudaStream_t s, uint64_t* launches) {
+                                  AshViewStats* stats, const Launch& L) {
     CullParams cp;
     for (int c = 0; c < 4; ++c)
         cp.vp.c[c] = {pc.view_proj[c][0], pc.view_proj[c][1], pc.view_proj[c][2], pc.view_proj[c][3]};
@@ -180,13 +180,15 @@ cudaError_t launch_occlusion_cull(const AshCullObjectData* objs, const AshIndire
     cp.object_count = pc.object_count;
     cp.hiz_levels = pc.hiz_levels;
     const uint32_t grid = (pc.object_count + kCullThreads - 1) / kCullThreads;
-    k_occlusion_cull<<<grid, kCullThreads, 0, s>>>(objs, cp, p, visibility, vis_bits, cta_counts);
-    ++*launches;
+    {
+        Timed timed(L, ASH_KERNEL_OCCLUSION_CULL);
+        k_occlusion_cull<<<grid, kCullThreads, 0, L.s>>>(objs, cp, p, visibility, vis_bits, cta_counts);
+    }
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return e;
-    k_cull_compact<<<grid, kCullThreads, 0, s>>>(objs, draws_in, pc.object_count, vis_bits, cta_counts,
+    Timed timed(L, ASH_KERNEL_CULL_COMPACT);
+    k_cull_compact<<<grid, kCullThreads, 0, L.s>>>(objs, draws_in, pc.object_count, vis_bits, cta_counts,
                                                  draws_out, visible_count, stats);
-    ++*launches;
     return cudaGetLastError();
 }
 

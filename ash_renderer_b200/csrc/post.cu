@@ -118,16 +118,16 @@ k_taa_resolve(Tex16 cur, Tex16 hist, const __half2* __restrict__ vel, uint2* __r
 }
 
 cudaError_t launch_taa(const void* cur, const void* hist, const void* vel, void* out,
-                       const AshTaaPushConstants& pc, cudaStream_t s, uint64_t* launches) {
+                       const AshTaaPushConstants& pc, const Launch& L) {
     const int W = (int)pc.screen_params[0], H = (int)pc.screen_params[1];
     const Tex16 c{static_cast<const uint2*>(cur), W, H}, h{static_cast<const uint2*>(hist), W, H};
     const dim3 grid((W + 31) / 32, (H + 7) / 8);
+    Timed timed(L, ASH_KERNEL_TAA);
     const bool center = W <= 4096 && H <= 4096;
     const __half2* v = static_cast<const __half2*>(vel);
     uint2* o = static_cast<uint2*>(out);
-    if (center) { if (v) k_taa_resolve<true, true><<<grid, 256, 0, s>>>(c, h, v, o, pc); else k_taa_resolve<true, false><<<grid, 256, 0, s>>>(c, h, v, o, pc); }
-    else        { if (v) k_taa_resolve<false, true><<<grid, 256, 0, s>>>(c, h, v, o, pc); else k_taa_resolve<false, false><<<grid, 256, 0, s>>>(c, h, v, o, pc); }
-    ++*launches;
+    if (center) { if (v) k_taa_resolve<true, true><<<grid, 256, 0, L.s>>>(c, h, v, o, pc); else k_taa_resolve<true, false><<<grid, 256, 0, L.s>>>(c, h, v, o, pc); }
+    else        { if (v) k_taa_resolve<false, true><<<grid, 256, 0, L.s>>>(c, h, v, o, pc); else k_taa_resolve<false, false><<<grid, 256, 0, L.s>>>(c, h, v, o, pc); }
     return cudaGetLastError();
 }
 
@@ -156,12 +156,12 @@ k_bloom_threshold(Tex16 hdr, uint2* __restrict__ out, float threshold) {
 }
 
 cudaError_t launch_bloom_threshold(const void* hdr, void* out, uint32_t W, uint32_t H, float threshold,
-                                   cudaStream_t s, uint64_t* launches) {
+                                   const Launch& L) {
     const Tex16 t{static_cast<const uint2*>(hdr), (int)W, (int)H};
     const dim3 grid((W + 31) / 32, (H + 7) / 8);
-    if (W <= 4096 && H <= 4096) k_bloom_threshold<true><<<grid, 256, 0, s>>>(t, static_cast<uint2*>(out), threshold);
-    else k_bloom_threshold<false><<<grid, 256, 0, s>>>(t, static_cast<uint2*>(out), threshold);
-    ++*launches;
+    Timed timed(L, ASH_KERNEL_BLOOM_THRESHOLD);
+    if (W <= 4096 && H <= 4096) k_bloom_threshold<true><<<grid, 256, 0, L.s>>>(t, static_cast<uint2*>(out), threshold);
+    else k_bloom_threshold<false><<<grid, 256, 0, L.s>>>(t, static_cast<uint2*>(out), threshold);
     return cudaGetLastError();
 }
 
@@ -189,11 +189,11 @@ k_bloom_downsample(Tex16 src, uint2* __restrict__ dst, int dw, int dh) {
 }
 
 cudaError_t launch_bloom_downsample(const void* src, uint32_t sw, uint32_t sh, void* dst, uint32_t dw,
-                                    uint32_t dh, cudaStream_t s, uint64_t* launches) {
+                                    uint32_t dh, const Launch& L) {
     const Tex16 t{static_cast<const uint2*>(src), (int)sw, (int)sh};
     const dim3 grid((dw + 31) / 32, (dh + 7) / 8);
-    k_bloom_downsample<<<grid, 256, 0, s>>>(t, static_cast<uint2*>(dst), (int)dw, (int)dh);
-    ++*launches;
+    Timed timed(L, ASH_KERNEL_BLOOM_DOWNSAMPLE);
+    k_bloom_downsample<<<grid, 256, 0, L.s>>>(t, static_cast<uint2*>(dst), (int)dw, (int)dh);
     return cudaGetLastError();
 }
 
@@ -223,11 +223,11 @@ k_bloom_upsample_add(Tex16 src, uint2* __restrict__ dst, int dw, int dh, float i
 }
 
 cudaError_t launch_bloom_upsample_add(const void* src, uint32_t sw, uint32_t sh, void* dst, uint32_t dw,
-                                      uint32_t dh, float intensity, cudaStream_t s, uint64_t* launches) {
+                                      uint32_t dh, float intensity, const Launch& L) {
     const Tex16 t{static_cast<const uint2*>(src), (int)sw, (int)sh};
     const dim3 grid((dw + 31) / 32, (dh + 7) / 8);
-    k_bloom_upsample_add<<<grid, 256, 0, s>>>(t, static_cast<uint2*>(dst), (int)dw, (int)dh, intensity);
-    ++*launches;
+    Timed timed(L, ASH_KERNEL_BLOOM_UPSAMPLE);
+    k_bloom_upsample_add<<<grid, 256, 0, L.s>>>(t, static_cast<uint2*>(dst), (int)dw, (int)dh, intensity);
     return cudaGetLastError();
 }
 
@@ -263,14 +263,13 @@ k_tonemap(Tex16 hdr, Tex16 bloom, uint32_t* __restrict__ ldr8, AshPostProcessPus
 }
 
 cudaError_t launch_tonemap(const void* hdr, const void* bloom_or_null, void* ldr8, uint32_t W, uint32_t H,
-                           const AshPostProcessPushConstants& pc, uint32_t srgb, cudaStream_t s,
-                           uint64_t* launches) {
+                           const AshPostProcessPushConstants& pc, uint32_t srgb, const Launch& L) {
     (void)srgb;
     const Tex16 h{static_cast<const uint2*>(hdr), (int)W, (int)H}, b{static_cast<const uint2*>(bloom_or_null), (int)W, (int)H};
     const dim3 grid((W + 31) / 32, (H + 7) / 8);
-    if (W <= 4096 && H <= 4096) k_tonemap<true><<<grid, 256, 0, s>>>(h, b, static_cast<uint32_t*>(ldr8), pc);
-    else k_tonemap<false><<<grid, 256, 0, s>>>(h, b, static_cast<uint32_t*>(ldr8), pc);
-    ++*launches;
+    Timed timed(L, ASH_KERNEL_TONEMAP);
+    if (W <= 4096 && H <= 4096) k_tonemap<true><<<grid, 256, 0, L.s>>>(h, b, static_cast<uint32_t*>(ldr8), pc);
+    else k_tonemap<false><<<grid, 256, 0, L.s>>>(h, b, static_cast<uint32_t*>(ldr8), pc);
     return cudaGetLastError();
 }
 

@@ -60,3 +60,9 @@ def BUF_HIZ_MIP(i):
 
 def BUF_BLOOM_MIP(i):
     return 0x200 + i
+
+# kernel classes (ashcuda_profile_kernels / ashcuda_kernel_time_ms)
+(KERNEL_DEPTH_PYRAMID, KERNEL_OCCLUSION_CULL, KERNEL_CULL_COMPACT, KERNEL_LIGHT_PREPASS, KERNEL_LIGHT_TILES,
+ KERNEL_TAA, KERNEL_BLOOM_THRESHOLD, KERNEL_BLOOM_DOWNSAMPLE, KERNEL_BLOOM_UPSAMPLE, KERNEL_TONEMAP,
+ KERNEL_TAA_THRESHOLD, KERNEL_UPSAMPLE_TONEMAP) = range(12)
+KERNEL_COUNT = 12

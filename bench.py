@@ -1,0 +1,463 @@
+#!/usr/bin/env python
+"""bench.py — 4K views/sec of the per-frame compute path (Hi-Z + cull + light cull + TAA + bloom + tonemap).
+
+One step = one frame of each of `--views` independent camera views of the BASELINE.json config-5
+scene (3840x2160, 100k instances, 8192 lights), every view with its own depth buffer, HDR colour
+buffer and TAA history.  Views shard across GPUs (weak scaling: `--views` per GPU, no data-path
+collective; one all_gather of the 32-byte per-view stats records at the end).
+
+  value  : views/s with the per-view inputs already resident in HBM (CUDA events, max over ranks)
+  e2e    : views/s through the host-buffer API: pinned host depth+HDR -> H2D -> view_run -> D2H of
+           visibility, tile lists, 8-bit image and stats, every view, inside the timed region
+  roofline : the dominant kernel class's algorithmic bytes per launch / its mean launch duration
+             (CUDA events recorded by the library on the launching stream during the timed region)
+  cpu_baseline : the CPU oracle (oracle/, OpenMP) on a bounded sample of the same workload
+  --impl reference : the CPU oracle alone (the reference has no CPU implementation of this path
+             and its Vulkan path cannot run here: see DESIGN.md), same metric/config.
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+W, H = 3840, 2160
+N_OBJECTS_GRID = (50, 50, 40)      # 100 000 instances
+N_LIGHTS = 8192
+HIZ_LEVELS = 12                    # "full pyramid" (PIN-4)
+METRIC, UNIT = "4k_views_per_sec", "views/s"
+
+
+def workload_name():
+    return (f"cfg5: {W}x{H}, {np.prod(N_OBJECTS_GRID)} instances, {N_LIGHTS} lights, full Hi-Z ({HIZ_LEVELS} levels) + "
+            "occlusion cull + 16x16 light cull + TAA + bloom(5) + ACES tonemap, 1 frame per view per step")
+
+
+# ------------------------------------------------------------------ synthetic scene / views
+def fibonacci_camera(i, n, rng):
+    from ash_renderer_b200 import synth
+    k = i + 0.5
+    phi = np.arccos(1 - 2 * k / n)
+    theta = np.pi * (1 + 5 ** 0.5) * k
+    r = rng.uniform(30.0, 60.0)
+    eye = r * np.array([np.cos(theta) * np.sin(phi), np.cos(phi) * 0.6, np.sin(theta) * np.sin(phi)])
+    target = rng.uniform(-5.0, 5.0, 3)
+    return synth.Camera(eye, target, W, H, near=0.5, far=200.0)
+
+
+def make_scene():
+    from ash_renderer_b200 import synth
+    objs, draws = synth.make_objects(N_OBJECTS_GRID, spacing=2.0, seed=5, jitter=0.4)
+    lights = synth.make_lights(N_LIGHTS, extent=60.0, rmin=1.0, rmax=6.0, seed=5)
+    return objs, draws, lights
+
+
+def make_view_inputs(view_id, n_total, objs):
+    """(camera, depth fp32 HxW, hdr fp16 HxWx4) for one view; deterministic in view_id."""
+    from ash_renderer_b200 import synth
+    rng = np.random.default_rng(1000 + view_id)
+    cam = fibonacci_camera(view_id, n_total, rng)
+    depth = synth.splat_depth(objs[:: 8], cam, shrink=0.7)            # coherent occluders from 1/8 of the instances
+    hdr = synth.HdrSequence(W, H, seed=5 + view_id, n_discs=120).frame(0.0, 0.0)
+    return cam, depth, hdr
+
+
+def view_params(cam, n_objs, n_lights, taa_pc, view_id):
+    from ash_renderer_b200 import types as T
+    vp = np.zeros(1, T.VIEW_PARAMS)
+    vp["cull"] = cam.cull_pc(n_objs, HIZ_LEVELS)
+    vp["light"] = cam.light_pc(n_lights)
+    vp["camera"] = cam.camera_data()
+    vp["taa"] = taa_pc
+    vp["bloom"]["threshold"], vp["bloom"]["upsample_intensity"], vp["bloom"]["mip_count"] = 0.8, 1.0, 5
+    vp["post"]["exposure"], vp["post"]["gamma"], vp["post"]["bloom_intensity"] = 1.0, 2.2, 0.5
+    vp["view_id"], vp["stages"] = view_id, T.STAGE_ALL
+    return vp
+
+
+# ------------------------------------------------------------------ algorithmic bytes
+def algorithmic_bytes(kclass, n_objs, n_lights, st):
+    from ash_renderer_b200 import types as T  # noqa: F401
+    P = W * H
+    c = 8
+    mips = []
+    w, h = W, H
+    while max(w, h) > 1:
+        w, h = max(1, w // 2), max(1, h // 2)
+        mips.append(w * h)
+    tiles = ((W + 15) // 16) * ((H + 15) // 16)
+    bl = [P]
+    w, h = W, H
+    for _ in range(5):
+        w, h = max(1, w // 2), max(1, h // 2)
+        bl.append(w * h)
+    V, cand, sum_l = int(st["visible_objects"]), int(st["candidate_lights"]), int(st["sum_tile_lights"])
+    table = {
+        0: 4 * P + 4 * sum(mips) + 8 * tiles,                                # depth read once, mips + tile min/max written
+        1: 112 * n_objs + 4 * n_objs + 4 * n_objs + n_objs // 8,             # objects, visibility, one Hi-Z texel, bit mask
+        2: n_objs // 8 + 4 * V + 40 * V + 4,                                 # mask, draw index, command in+out
+        3: 64 * n_lights + 208 + 20 * cand,
+        4: 8 * tiles + 20 * cand + 4 * (tiles + sum_l),
+        5: 3 * c * P,
+        6: 2 * c * P,
+        7: c * sum(bl[k - 1] + bl[k] for k in range(1, 6)) / 5.0,            # mean per launch (5 launches)
+        8: c * sum(bl[k + 1] + 2 * bl[k] for k in range(0, 5)) / 5.0,
+        9: 2 * c * P + 4 * P,
+        10: 4 * c * P,                                                       # fused TAA + threshold: cur, hist in; out, T out
+        11: c * (bl[1] + 2 * P) + 4 * P,                                     # fused last upsample + tonemap
+    }
+    return float(table[kclass])
+
+
+KERNEL_NAMES = ["depth_pyramid", "occlusion_cull", "cull_compact", "light_prepass", "light_tiles", "taa_resolve",
+                "bloom_threshold", "bloom_downsample", "bloom_upsample", "tonemap", "taa_threshold_fused",
+                "upsample_tonemap_fused"]
+
+
+# ------------------------------------------------------------------ clocks sampling (B200_PROFILING.md)
+class ClockSampler:
+    Q = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        sm, mx, reasons, power = [], [], set(), []
+        for r in self.rows:
+            if len(r) < 7:
+                continue
+            try:
+                sm.append(float(r[0])); mx.append(float(r[1])); power.append(float(r[2]))
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "power_w_max": max(power) if power else None, "samples": len(sm), "reasons": sorted(reasons)}
+
+
+# ------------------------------------------------------------------ CPU oracle arm
+def oracle_view(oracle, objs, draws, lights, cam, depth, hdr, hist, taa_pc):
+    from ash_renderer_b200 import types as T
+    mips, flat = oracle.hiz_build(depth)
+    vis, dout, cnt = oracle.occlusion_cull(objs, draws, cam.cull_pc(len(objs), HIZ_LEVELS), depth, flat)
+    td, _, _ = oracle.light_cull(lights, cam.light_pc(len(lights)), cam.camera_data(), depth)
+    taa = oracle.taa_resolve(hdr, hist, None, taa_pc)
+    U, _ = oracle.bloom_chain(taa, 0.8, 5)
+    pc = np.zeros(1, T.POST_PC)
+    pc["exposure"], pc["gamma"], pc["bloom_intensity"] = 1.0, 2.2, 0.5
+    ldr = oracle.tonemap(taa, U[0], pc)
+    return cnt, int(td[:, 0].sum()), taa, ldr
+
+
+def cpu_oracle_rate(objs, draws, lights, views, taa_pc, max_views, budget_s):
+    """views/s of the OpenMP oracle on up to `max_views` full 4K views (bounded by `budget_s`)."""
+    from oracle import oracle
+    oracle.build()
+    times = []
+    t_all = time.perf_counter()
+    for i in range(max_views):
+        cam, depth, hdr = views[i % len(views)]
+        t0 = time.perf_counter()
+        oracle_view(oracle, objs, draws, lights, cam, depth, hdr, hdr, taa_pc)
+        times.append(time.perf_counter() - t0)
+        if time.perf_counter() - t_all > budget_s:
+            break
+    return len(times) / sum(times), oracle.num_threads(), len(times)
+
+
+def taa_pc_default():
+    from ash_renderer_b200.host import TemporalAA
+    t = TemporalAA()
+    t.begin_frame(); t.begin_frame()
+    return t.push_constants(W, H)
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    objs, draws, lights = make_scene()
+    n_views = 2
+    views = [make_view_inputs(v, 1024, objs) for v in range(n_views)]
+    pc = taa_pc_default()
+    from oracle import oracle
+    oracle.build()
+    for i in range(args.warmup):
+        if i >= 1:
+            break                                          # one warm-up view is enough to page everything in
+        cam, depth, hdr = views[0]
+        oracle_view(oracle, objs, draws, lights, cam, depth, hdr, hdr, pc)
+    t0 = time.perf_counter()
+    for k in range(args.steps):
+        cam, depth, hdr = views[k % n_views]
+        oracle_view(oracle, objs, draws, lights, cam, depth, hdr, hdr, pc)
+    dt = time.perf_counter() - t0
+    v = args.steps / dt
+    sample = f"{args.steps} steps x 1 full 4K view each (bounded sample of the {args.views}-view step)"
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": min(args.warmup, 1), "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": workload_name(), "views_per_step": 1, "note": "CPU oracle port of the reference GLSL; "
+                   "the reference has no CPU implementation and its Vulkan path is unavailable on this box"},
+        "cpu_baseline": {"value": v, "unit": UNIT, "cores": oracle.num_threads(), "kind": "port", "sample": sample},
+        "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }))
+
+
+# ------------------------------------------------------------------ CUDA arm
+def run_cuda(args):
+    import torch
+    import torch.distributed as dist
+    from ash_renderer_b200 import backend, types as T
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    B = args.views
+    objs, draws, lights = make_scene()
+    n_objs, n_lights = len(objs), len(lights)
+    total_views = B * world
+    distinct = min(B, args.distinct)
+    taa_pc = taa_pc_default()
+
+    # scene: replicated once per GPU, shared (borrowed) by every view slot
+    d_objs = torch.from_numpy(objs.view(np.uint8)).cuda()
+    d_draws = torch.from_numpy(draws.view(np.uint8)).cuda()
+    d_lights = torch.from_numpy(lights.view(np.uint8)).cuda()
+
+    host_views = [make_view_inputs(rank * B + v, max(total_views, 1024), objs) for v in range(distinct)]
+    streams = [torch.cuda.Stream() for _ in range(args.streams)]
+    slots = []
+    for v in range(B):
+        cam, depth, hdr = host_views[v % distinct]
+        c = backend.Context(W, H, device=local, max_objects=n_objs, max_lights=n_lights, hiz_levels=HIZ_LEVELS)
+        c.set_stream(streams[v % args.streams].cuda_stream)
+        c.set_objects(d_objs, d_draws)
+        c.upload_lights(d_lights)
+        slot = {"ctx": c, "vp": view_params(cam, n_objs, n_lights, taa_pc, rank * B + v),
+                "d_depth": torch.from_numpy(depth).cuda(), "d_hdr": torch.from_numpy(hdr.view(np.uint16)).cuda(),
+                "h_depth": torch.from_numpy(depth).pin_memory(), "h_hdr": torch.from_numpy(hdr.view(np.uint16)).pin_memory()}
+        tiles = ((W + 15) // 16) * ((H + 15) // 16)
+        slot["o_vis"] = torch.empty(n_objs, dtype=torch.int32).pin_memory()
+        slot["o_td"] = torch.empty(tiles * 257, dtype=torch.int32).pin_memory()
+        slot["o_ldr"] = torch.empty(W * H * 4, dtype=torch.uint8).pin_memory()
+        slot["o_st"] = torch.empty(8, dtype=torch.int32).pin_memory()
+        slot["o_cnt"] = torch.empty(1, dtype=torch.int32).pin_memory()
+        slots.append(slot)
+    torch.cuda.synchronize()
+
+    main = torch.cuda.current_stream()
+
+    def fence_start():
+        ev = torch.cuda.Event(enable_timing=True)
+        ev.record(main)
+        for s in streams:
+            s.wait_event(ev)
+        return ev
+
+    def fence_stop():
+        for s in streams:
+            e = torch.cuda.Event()
+            e.record(s)
+            main.wait_event(e)
+        ev = torch.cuda.Event(enable_timing=True)
+        ev.record(main)
+        return ev
+
+    def step_resident():
+        for s in slots:
+            c = s["ctx"]
+            c.set_depth(s["d_depth"])
+            c.set_color(s["d_hdr"], None)
+            c.view_run(s["vp"])
+
+    def step_e2e():
+        for s in slots:
+            c = s["ctx"]
+            c.upload_view(s["h_depth"], s["h_hdr"])
+            c.view_run(s["vp"])
+            c.download_view(s["o_vis"], s["o_td"], s["o_ldr"], s["o_st"], s["o_cnt"])
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(step_fn, steps, warmup):
+        for _ in range(warmup):
+            step_fn()
+        barrier()
+        a = fence_start()
+        for _ in range(steps):
+            step_fn()
+        b = fence_stop()
+        barrier()
+        ms = a.elapsed_time(b)
+        if world > 1:
+            t = torch.tensor([ms], device="cuda", dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        return ms
+
+    # ---- device-resident throughput (the `value`)
+    for s in slots:
+        s["ctx"].profile_kernels(0)
+    timed(step_resident, 1, max(args.warmup, 3) - 1)       # warm-up (also fills every TAA history)
+    for s in slots:
+        s["ctx"].profile_kernels((1 << T.KERNEL_COUNT) - 1)
+        for k in range(T.KERNEL_COUNT):
+            s["ctx"].kernel_time_ms(k)                     # reset accumulators
+    launches0 = sum(s["ctx"].kernel_launches() for s in slots)
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+        time.sleep(0.3)
+    ms = timed(step_resident, args.steps, 1)
+    clocks = sampler.stop() if rank == 0 else None
+    launches_per_step = (sum(s["ctx"].kernel_launches() for s in slots) - launches0) / (args.steps + 1)
+    value = total_views * args.steps / (ms * 1e-3)
+
+    # per-kernel-class device time over the timed region (events recorded by the library)
+    ktime = np.zeros(T.KERNEL_COUNT)
+    kcount = np.zeros(T.KERNEL_COUNT)
+    for s in slots:
+        for k in range(T.KERNEL_COUNT):
+            t, n = s["ctx"].kernel_time_ms(k)
+            ktime[k] += t
+            kcount[k] += n
+        s["ctx"].profile_kernels(0)
+    stats = [s["ctx"].stats() for s in slots]
+    st_mean = {f: float(np.mean([st[f] for st in stats])) for f in T.VIEW_STATS.names}
+
+    # ---- end-to-end through host buffers
+    e2e_ms = timed(step_e2e, args.steps, 2)
+    e2e_value = total_views * args.steps / (e2e_ms * 1e-3)
+    tiles = ((W + 15) // 16) * ((H + 15) // 16)
+    h2d = B * (W * H * 4 + W * H * 8 + T.VIEW_PARAMS.itemsize)   # depth + HDR + the per-view parameter block
+    d2h = B * (n_objs * 4 + tiles * 257 * 4 + W * H * 4 + 32 + 4)
+    # sanity: the e2e outputs equal the resident path's
+    chk = slots[0]
+    assert int(chk["o_cnt"][0]) == int(stats[0]["visible_objects"]), "e2e result differs from resident result"
+
+    # ---- stats all_gather (the only inter-GPU exchange; 32 B per view)
+    st_arr = np.stack([np.frombuffer(st.tobytes(), np.uint32) for st in stats]).astype(np.int32)
+    if world > 1:
+        mine = torch.from_numpy(st_arr).cuda()
+        allst = torch.empty((world * B, 8), dtype=torch.int32, device="cuda")
+        dist.all_gather_into_tensor(allst, mine)
+        st_all = allst.cpu().numpy()
+    else:
+        st_all = st_arr
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except OSError:
+        pass
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    peak_src = "MEASURED_PEAKS.json hbm_gbs (measured copy)" if "hbm_gbs" in peaks else "fallback 6650 GB/s (B200_PROFILING.md)"
+    kernels = {}
+    for k in range(T.KERNEL_COUNT):
+        if kcount[k] == 0:
+            continue
+        avg_ms = ktime[k] / kcount[k]
+        ab = algorithmic_bytes(k, n_objs, n_lights, st_mean)
+        kernels[KERNEL_NAMES[k]] = {"launches_per_view": kcount[k] / (B * (args.steps + 1)), "avg_ms": avg_ms,
+                                    "alg_bytes_per_launch": ab, "gbs": ab / (avg_ms * 1e-3) / 1e9,
+                                    "share_of_kernel_time": ktime[k] / ktime.sum()}
+    dom = max(range(T.KERNEL_COUNT), key=lambda k: ktime[k])
+    dom_k = kernels[KERNEL_NAMES[dom]]
+    # whole-view roofline: compulsory bytes of the staged path / measured time per view
+    view_bytes = sum(algorithmic_bytes(k, n_objs, n_lights, st_mean) * kcount[k] / (B * (args.steps + 1))
+                     for k in range(T.KERNEL_COUNT) if kcount[k])
+    per_view_s = ms * 1e-3 / (B * args.steps)
+
+    # ---- CPU baseline (bounded sample: up to 2 full 4K views, ~10-30 s)
+    cpu_v, cpu_cores, cpu_n = cpu_oracle_rate(objs, draws, lights, host_views, taa_pc, max_views=args.cpu_views, budget_s=20.0)
+
+    out = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+        "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic",
+        "config": {"workload": workload_name(), "views_per_gpu_per_step": B, "distinct_view_inputs_per_gpu": distinct,
+                   "streams": args.streams, "l2": f"inputs larger than L2: {B} views x 99.5 MB of depth+HDR per step per GPU",
+                   "visible_fraction_mean": st_mean["visible_objects"] / n_objs,
+                   "candidate_lights_mean": st_mean["candidate_lights"],
+                   "lights_per_tile_mean": st_mean["sum_tile_lights"] / tiles, "lights_per_tile_max": int(st_all[:, 5].max())},
+        "clocks": clocks,
+        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
+                "ms_per_step": e2e_ms / args.steps},
+        "gpu_launches": int(round(launches_per_step * args.steps)),
+        "roofline": {"bound": "hbm", "kernel": KERNEL_NAMES[dom], "achieved": dom_k["gbs"], "peak": peak, "unit": "GB/s",
+                     "frac": dom_k["gbs"] / peak, "traffic": None, "peak_source": peak_src,
+                     "whole_view": {"alg_bytes_per_view_staged": view_bytes, "gbs": view_bytes / per_view_s / 1e9,
+                                    "frac": view_bytes / per_view_s / 1e9 / peak}},
+        "kernels": kernels,
+        "cpu_baseline": {"value": cpu_v, "unit": UNIT, "cores": cpu_cores, "kind": "port",
+                         "sample": f"{cpu_n} full 4K view(s) of the same workload through the OpenMP CPU oracle"},
+    }
+    print(json.dumps(out))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="cuda", choices=["cuda", "reference"])
+    ap.add_argument("--views", type=int, default=16, help="views per GPU per step")
+    ap.add_argument("--distinct", type=int, default=4, help="distinct synthetic depth/HDR inputs generated per GPU (host setup cost)")
+    ap.add_argument("--streams", type=int, default=4)
+    ap.add_argument("--cpu-views", type=int, default=2)
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_cuda(args)
+
+
+if __name__ == "__main__":
+    main()

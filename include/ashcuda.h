@@ -184,6 +184,22 @@ typedef struct AshCudaViewParams {
 #define ASH_BUF_VISIBILITY_BITS 9 /* u32[ceil(n/32)] 1 bit per object                          */
 #define ASH_BUF_BLOOM_THRESHOLD 10/* RGBA16F W x H: T = D_0 (staged path only)                 */
 
+/* Kernel classes for ashcuda_profile_kernels / ashcuda_kernel_time_ms (device-time accounting;
+ * the Vulkan-timestamp TimingScopes of diagnostics/gpu_profiler.rs:25-44 play this role upstream). */
+#define ASH_KERNEL_DEPTH_PYRAMID    0  /* Hi-Z mips + tile min/max, one pass over depth          */
+#define ASH_KERNEL_OCCLUSION_CULL   1
+#define ASH_KERNEL_CULL_COMPACT     2
+#define ASH_KERNEL_LIGHT_PREPASS    3
+#define ASH_KERNEL_LIGHT_TILES      4
+#define ASH_KERNEL_TAA              5
+#define ASH_KERNEL_BLOOM_THRESHOLD  6
+#define ASH_KERNEL_BLOOM_DOWNSAMPLE 7
+#define ASH_KERNEL_BLOOM_UPSAMPLE   8
+#define ASH_KERNEL_TONEMAP          9
+#define ASH_KERNEL_TAA_THRESHOLD   10  /* fused: TAA resolve + bloom threshold                   */
+#define ASH_KERNEL_UPSAMPLE_TONEMAP 11 /* fused: last bloom upsample + tonemap + 8-bit pack      */
+#define ASH_KERNEL_COUNT           12
+
 typedef struct ashcuda_ctx ashcuda_ctx;
 
 /* --- lifetime: replaces LightCullingPipeline::new / Drop (vulkan/light_culling_pipeline.rs:41-243,
@@ -219,6 +235,16 @@ int ashcuda_tonemap       (ashcuda_ctx*, const AshPostProcessPushConstants*);   
 /* the whole view-frame in one call, fused kernels, same results as the staged calls */
 int ashcuda_view_run      (ashcuda_ctx*, const AshCudaViewParams*);
 
+/* --- whole-view host I/O for callers whose frame data lives in host memory (the e2e path):
+ *     upload = set_depth + set_color from host pointers (pinned memory makes the copies async);
+ *     download = async device->host copies of the view's results on the ctx stream; any pointer may
+ *     be NULL to skip that buffer.  Sizes: visibility 4*object_count, tile_data 4*257*tiles,
+ *     ldr8 4*W*H, stats sizeof(AshViewStats), visible_count 4. Call ashcuda_sync before reading. */
+int ashcuda_upload_view  (ashcuda_ctx*, const float* depth_wh, const void* hdr_rgba16f,
+                          const void* velocity_rg16f_or_null);
+int ashcuda_download_view(ashcuda_ctx*, uint32_t* visibility, uint32_t* tile_data, uint8_t* ldr8,
+                          AshViewStats* stats, uint32_t* visible_count);
+
 /* --- outputs: device pointers owned by ctx, valid until the next call that rewrites them.
  *     Replaces LightCullingPipeline::tile_buffer / tile_buffer_size (:322-330). */
 int ashcuda_get     (ashcuda_ctx*, int which, void** dev_ptr, size_t* bytes);
@@ -228,6 +254,11 @@ int ashcuda_sync    (ashcuda_ctx*);
 int ashcuda_hiz_level_count(ashcuda_ctx*);                     /* levels_built (PIN-4) */
 int ashcuda_mip_extent(ashcuda_ctx*, int which, uint32_t* w, uint32_t* h);
 uint64_t ashcuda_kernel_launches(ashcuda_ctx*);                /* kernels launched so far by this ctx */
+/* Device-time accounting: launches of the classes in `mask` (bit ASH_KERNEL_*) are bracketed by
+ * CUDA events on the ctx stream.  ashcuda_kernel_time_ms syncs the stream, returns the time and
+ * launch count accumulated for one class since the previous query of it, and resets them. */
+int ashcuda_profile_kernels(ashcuda_ctx*, uint32_t mask);
+int ashcuda_kernel_time_ms(ashcuda_ctx*, int kernel_class, float* ms, uint64_t* launches);
 const char* ashcuda_last_error(ashcuda_ctx*);                  /* NULL ctx: last create error */
 const char* ashcuda_version(void);
 

@@ -1,0 +1,477 @@
+"""Parity of the CUDA path (through the C ABI) against the CPU oracle on the same seeded inputs.
+
+Bars: Hi-Z mips, tile min/max, visibility masks, visible counts, ordered draw
+commands and per-tile light lists BIT-EXACT; RGBA16F images bit-exact (the kernels execute the
+oracle's IEEE operation sequence) with a fall-back tolerance of 1 fp16 ulp stated where used;
+8-bit output within 1 LSB (powf differs by ulps between glibc and CUDA).
+"""
+import os
+
+import numpy as np
+import pytest
+
+from ash_renderer_b200 import synth, types as T
+
+pytestmark = pytest.mark.gpu
+
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "oracle_small.npz")
+
+
+def _ctx(backend, W, H, **cfg):
+    cfg.setdefault("max_objects", 131072)
+    cfg.setdefault("max_lights", 8192)
+    return backend.Context(W, H, **cfg)
+
+
+def _taa_pc(W, H, blend=0.9, clamp=1.0, vel=1.0, jitter=(0.25, -0.16666667), prev=(0.0, 0.0)):
+    pc = np.zeros(1, T.TAA_PC)
+    w, h = np.float32(W), np.float32(H)
+    pc["screen_params"][0] = [w, h, np.float32(1) / w, np.float32(1) / h]
+    pc["params"][0] = [blend, clamp, vel, 0.0]
+    pc["jitter"][0], pc["prev_jitter"][0] = jitter, prev
+    return pc
+
+
+def _post_pc(exposure=1.0, gamma=2.2, bloom_intensity=0.5):
+    pc = np.zeros(1, T.POST_PC)
+    pc["exposure"], pc["gamma"], pc["bloom_intensity"] = exposure, gamma, bloom_intensity
+    return pc
+
+
+def _bloom_params(threshold=0.8, mips=5, intensity=1.0):
+    bp = np.zeros(1, T.BLOOM_PARAMS)
+    bp["threshold"], bp["upsample_intensity"], bp["mip_count"] = threshold, intensity, mips
+    return bp
+
+
+def _assert_half_images_equal(got, ref, what):
+    g, r = np.ascontiguousarray(got).view(np.uint16), np.ascontiguousarray(ref).view(np.uint16)
+    if np.array_equal(g, r):
+        return
+    # report in fp16 ulps (sign-magnitude -> monotone integer)
+    def mono(u):
+        u = u.astype(np.int32)
+        return np.where(u & 0x8000, -(u & 0x7FFF), u)
+    d = np.abs(mono(g) - mono(r))
+    raise AssertionError(f"{what}: {int((d > 0).sum())} of {d.size} halfs differ, max {int(d.max())} fp16 ulp")
+
+
+# ------------------------------------------------------------------ Hi-Z + tile min/max
+@pytest.mark.parametrize("W,H", [(64, 64), (67, 45), (1, 1), (2, 1), (1, 7), (130, 70), (255, 257),
+                                 (1920, 1080), (3840, 2160), (2048, 1024), (1000, 3)])
+def test_hiz_pyramid_bit_exact(backend, oracle, W, H):
+    depth = synth.random_depth(W, H, seed=W + H)
+    mips, _ = oracle.hiz_build(depth)
+    with _ctx(backend, W, H, enable_post=0) as c:
+        c.set_depth(depth)
+        c.hiz_build()
+        assert c.hiz_level_count() == len(mips) + 1
+        assert np.array_equal(c.hiz_mip(0), depth)
+        for l, m in enumerate(mips, start=1):
+            got = c.hiz_mip(l)
+            assert got.shape == m.shape
+            assert np.array_equal(got.view(np.uint32), m.view(np.uint32)), f"mip {l}"
+        # tile min/max == light_culling.comp:130-143 on float bits
+        lights = synth.make_lights(1, seed=1)
+        cam = synth.Camera((0, 0, 5), (0, 0, 0), W, H)
+        _, _, mm = oracle.light_cull(lights, cam.light_pc(1), cam.camera_data(), depth)
+        got = c.readback(T.BUF_TILE_MINMAX, np.uint32).reshape(-1, 2)
+        assert np.array_equal(got, mm)
+
+
+def test_hiz_device_pointer_input_and_rebuild(backend, oracle):
+    import torch
+    W, H = 512, 256
+    d0, d1 = synth.random_depth(W, H, seed=1), synth.random_depth(W, H, seed=2)
+    t0, t1 = torch.from_numpy(d0).cuda(), torch.from_numpy(d1).cuda()
+    torch.cuda.synchronize()
+    with _ctx(backend, W, H, enable_post=0) as c:
+        for t, d in ((t0, d0), (t1, d1), (t0, d0)):
+            c.set_depth(t)                       # borrowed, zero-copy
+            c.hiz_build()
+            mips, _ = oracle.hiz_build(d)
+            for l, m in enumerate(mips, start=1):
+                assert np.array_equal(c.hiz_mip(l), m)
+
+
+# ------------------------------------------------------------------ occlusion cull
+def _cull_scene(W, H, grid, seed, eye=(0.0, 2.0, 22.0), disabled=0.05, spacing=2.0):
+    cam = synth.Camera(eye, (0, 0, 0), W, H)
+    objs, draws = synth.make_objects(grid, spacing=spacing, seed=seed, jitter=0.3, disabled_frac=disabled)
+    depth = synth.splat_depth(objs, cam)
+    return cam, objs, draws, depth
+
+
+@pytest.mark.parametrize("W,H,grid,levels", [
+    (320, 180, (6, 6, 6), 8), (200, 120, (7, 5, 3), 3), (1920, 1080, (10, 10, 10), 10),
+    (3840, 2160, (25, 20, 20), 12), (3840, 2160, (25, 20, 20), 10), (1024, 1024, (40, 50, 50), 11),
+    (67, 45, (3, 3, 3), 1)])
+def test_occlusion_cull_bit_exact(backend, oracle, W, H, grid, levels):
+    cam, objs, draws, depth = _cull_scene(W, H, grid, seed=W + grid[0])
+    pc = cam.cull_pc(len(objs), levels)
+    vis, dout, cnt = oracle.occlusion_cull(objs, draws, pc, depth)
+    with _ctx(backend, W, H, enable_post=0, hiz_levels=levels) as c:
+        c.set_depth(depth)
+        c.set_objects(objs, draws)
+        c.hiz_build()
+        c.occlusion_cull(pc)
+        got = c.visibility()
+        assert np.array_equal(got, vis)
+        assert c.visible_count() == cnt
+        assert np.array_equal(c.draws_out(cnt), dout)                       # PIN-7 ascending order
+        bits = c.readback(T.BUF_VISIBILITY_BITS, np.uint32)
+        assert np.array_equal(np.unpackbits(bits.view(np.uint8), bitorder="little")[:len(vis)], vis.astype(np.uint8))
+        st = c.stats()
+        assert st["total_objects"] == len(objs) and st["visible_objects"] == cnt
+    assert 0 < cnt < len(objs)
+
+
+def test_occlusion_cull_edge_cases(backend, oracle):
+    W, H = 128, 96
+    cam = synth.Camera((0, 0, 10), (0, 0, 0), W, H)
+    objs, draws = synth.make_objects((1, 1, 1), seed=1)
+    objs = np.repeat(objs, 70)                      # 70: not a multiple of the warp / CTA size
+    objs["model"][1][3][:3] = [0, 0, 50]
+    objs["model"][2][3][:3] = [0, 0, 9.9]           # clip.w <= 0 -> visible
+    objs["flags"][3] = 0
+    objs["flags"][4] = 2
+    objs["extents"][5] = 0
+    objs["model"][6][0][:3] = [0.6, 0.8, 0.0]       # rotated model: extents use column lengths only
+    objs["model"][6][1][:3] = [-0.8, 0.6, 0.0]
+    objs["extents"][7][:3] = [1e30, 1e30, 1e30]     # overflow to inf/NaN inside the projection
+    objs["center"][8][:3] = [np.nan, 0, 0]
+    for depth_val in (1.0, 0.0, 0.97):
+        depth = np.full((H, W), depth_val, np.float32)
+        pc = cam.cull_pc(len(objs), 8)
+        vis, dout, cnt = oracle.occlusion_cull(objs, draws, pc, depth)
+        with _ctx(backend, W, H, enable_post=0) as c:
+            c.set_depth(depth)
+            c.set_objects(objs, draws)
+            c.occlusion_cull(pc)                    # builds the pyramid on demand
+            assert np.array_equal(c.visibility(), vis)
+            assert c.visible_count() == cnt
+            assert np.array_equal(c.draws_out(cnt), dout)
+            # objectCount smaller than the uploaded array; then zero objects
+            pc2 = cam.cull_pc(33, 8)
+            vis2, dout2, cnt2 = oracle.occlusion_cull(objs, draws, pc2, depth)
+            c.occlusion_cull(pc2)
+            assert c.visible_count() == cnt2 and np.array_equal(c.visibility()[:33], vis2)
+            c.occlusion_cull(cam.cull_pc(0, 8))
+            assert c.visible_count() == 0
+
+
+# ------------------------------------------------------------------ light cull
+def _compare_tile_lists(got, ref):
+    assert got.shape == ref.shape
+    assert np.array_equal(got[:, 0], ref[:, 0]), "per-tile counts"
+    cnt = ref[:, 0].astype(np.int64)
+    mask = np.arange(256)[None, :] < cnt[:, None]
+    assert np.array_equal(got[:, 1:][mask], ref[:, 1:][mask]), "per-tile index lists"   # PIN-8: valid prefix only
+
+
+@pytest.mark.parametrize("W,H,n_lights,extent,eye", [
+    (200, 120, 300, 10.0, (0.0, 2.0, 22.0)), (1920, 1080, 256, 10.0, (0.0, 2.0, 22.0)),
+    (3840, 2160, 4096, 30.0, (0.0, 2.0, 40.0)), (3840, 2160, 8192, 30.0, (5.0, 3.0, 12.0)),
+    (67, 45, 33, 5.0, (0.0, 0.0, 6.0)), (1000, 3, 100, 5.0, (0.0, 0.0, 6.0))])
+def test_light_cull_bit_exact(backend, oracle, W, H, n_lights, extent, eye):
+    cam = synth.Camera(eye, (0, 0, 0), W, H)
+    objs, _ = synth.make_objects((6, 6, 6), seed=3)
+    depth = synth.splat_depth(objs, cam)
+    # centre half the lights on the camera so that the (raw-depth) near/far planes keep many
+    lights = synth.make_lights(n_lights, extent=extent, seed=W + n_lights, center=(0, 0, 0))
+    half = n_lights // 2
+    lights["position"][:half, :3] = (lights["position"][:half, :3] * np.float32(0.2) + np.asarray(eye, np.float32))
+    pc, cd = cam.light_pc(n_lights), cam.camera_data()
+    ref, true_counts, _ = oracle.light_cull(lights, pc, cd, depth)
+    with _ctx(backend, W, H, enable_post=0) as c:
+        c.set_depth(depth)
+        c.upload_lights(lights)
+        c.upload_camera(cd)
+        c.hiz_build()
+        c.light_cull(pc)
+        _compare_tile_lists(c.tile_data(), ref)
+        st = c.stats()
+        assert st["tiles"] == len(ref)
+        assert st["sum_tile_lights"] == int(ref[:, 0].sum())
+        assert st["max_tile_lights"] == int(ref[:, 0].max())
+        assert st["overflow_tiles"] == int((true_counts > 256).sum())
+    assert ref[:, 0].max() > 0
+
+
+def test_light_cull_overflow_zero_lights_and_disabled(backend, oracle):
+    W, H = 64, 48
+    cam = synth.Camera((0, 0, 5), (0, 0, 0), W, H)
+    depth = synth.random_depth(W, H, seed=4)
+    lights = synth.make_lights(700, extent=0.2, rmin=50, rmax=60, seed=9, n_directional=3, enabled_p=0.9,
+                               center=(0, 0, 5))
+    cd = cam.camera_data()
+    with _ctx(backend, W, H, enable_post=0) as c:
+        c.set_depth(depth)
+        c.upload_camera(cd)
+        c.upload_lights(lights)
+        for n in (700, 256, 257, 1, 0):
+            pc = cam.light_pc(n)
+            ref, true_counts, _ = oracle.light_cull(lights[:n], pc, cd, depth)
+            c.light_cull(pc)
+            _compare_tile_lists(c.tile_data(), ref)
+            assert c.stats()["overflow_tiles"] == int((true_counts > 256).sum())
+        allowed = lights.copy()
+        allowed["params"][:, 3] = 0.0                # all disabled
+        c.upload_lights(allowed)
+        c.light_cull(cam.light_pc(700))
+        assert np.all(c.tile_data()[:, 0] == 0)
+
+
+# ------------------------------------------------------------------ TAA
+@pytest.mark.parametrize("W,H,with_vel", [(200, 120, True), (200, 120, False), (67, 45, True),
+                                          (1920, 1080, False), (33, 9, False)])
+def test_taa_bit_exact(backend, oracle, W, H, with_vel):
+    cur, hist = synth.random_hdr(W, H, seed=1), synth.random_hdr(W, H, seed=2)
+    vel = synth.random_velocity(W, H, seed=3) if with_vel else None
+    with _ctx(backend, W, H) as c:
+        for kw in (dict(), dict(clamp=0.0), dict(vel=0.0, jitter=(-0.4, 0.3), prev=(0.45, -0.45)), dict(blend=0.0)):
+            pc = _taa_pc(W, H, **kw)
+            # frame 0: history = current colour (PIN-12); frame 1: history = previous resolve
+            c.taa_reset_history()
+            c.set_color(hist, None)
+            c.taa_resolve(_taa_pc(W, H, blend=1.0, clamp=0.0, vel=0.0, jitter=(0, 0)))   # out = hist exactly
+            assert np.array_equal(c.taa_out()[..., :3], hist[..., :3])
+            ref_hist = c.taa_out()
+            c.set_color(cur, vel)
+            c.taa_resolve(pc)
+            ref = oracle.taa_resolve(cur, ref_hist, vel, pc)
+            _assert_half_images_equal(c.taa_out(), ref, f"taa {kw}")
+
+
+def test_taa_sequence_halton_16_frames(backend, oracle):
+    from ash_renderer_b200.host import TemporalAA
+    W, H = 160, 96
+    seq = synth.HdrSequence(W, H, seed=4, n_discs=20)
+    taa = TemporalAA()
+    hist = None
+    with _ctx(backend, W, H) as c:
+        for t in range(18):
+            taa.begin_frame()
+            j = taa.current_jitter()
+            frame = seq.frame(float(j[0]), float(j[1]))
+            pc = taa.push_constants(W, H)
+            c.set_color(frame, None)
+            c.taa_resolve(pc)
+            ref = oracle.taa_resolve(frame, frame if hist is None else hist, None, pc)
+            _assert_half_images_equal(c.taa_out(), ref, f"frame {t}")
+            hist = ref
+
+
+# ------------------------------------------------------------------ bloom + tonemap
+@pytest.mark.parametrize("W,H,mips", [(200, 120, 5), (67, 45, 5), (1920, 1080, 5), (64, 64, 3), (33, 9, 2), (256, 256, 8)])
+def test_bloom_chain_bit_exact(backend, oracle, W, H, mips):
+    hdr = synth.random_hdr(W, H, seed=W)
+    U, D = oracle.bloom_chain(hdr, 0.8, mips)
+    with _ctx(backend, W, H, bloom_mips=mips) as c:
+        c.set_color(hdr, None)
+        c.bloom(_bloom_params(0.8, mips))
+        for k in range(mips + 1):
+            _assert_half_images_equal(c.bloom_mip(k), U[k], f"U_{k}")
+
+
+@pytest.mark.parametrize("W,H", [(200, 120), (1920, 1080), (67, 45)])
+def test_tonemap_within_one_lsb(backend, oracle, W, H):
+    hdr = synth.random_hdr(W, H, seed=5)
+    pc = _post_pc()
+    with _ctx(backend, W, H) as c:
+        c.set_color(hdr, None)
+        c.tonemap(pc)                                   # no bloom computed: bloom term absent
+        ref = oracle.tonemap(hdr, None, pc)
+        d = np.abs(c.ldr8().astype(np.int16) - ref.astype(np.int16))
+        assert d.max() <= 1 and (d > 0).mean() < 0.01
+        c.bloom(_bloom_params())
+        c.tonemap(pc)
+        U, _ = oracle.bloom_chain(hdr, 0.8, 5)
+        ref = oracle.tonemap(hdr, U[0], pc)
+        d = np.abs(c.ldr8().astype(np.int16) - ref.astype(np.int16))
+        assert d.max() <= 1 and (d > 0).mean() < 0.01
+        assert np.all(c.ldr8()[..., 3] == 255)
+
+
+# ------------------------------------------------------------------ whole view
+def _view_params(cam, n_objs, n_lights, hiz_levels, W, H, taa_pc, stages=T.STAGE_ALL, view_id=7):
+    vp = np.zeros(1, T.VIEW_PARAMS)
+    vp["cull"] = cam.cull_pc(n_objs, hiz_levels)
+    vp["light"] = cam.light_pc(n_lights)
+    vp["camera"] = cam.camera_data()
+    vp["taa"] = taa_pc
+    vp["bloom"] = _bloom_params()
+    vp["post"] = _post_pc()
+    vp["view_id"], vp["stages"] = view_id, stages
+    return vp
+
+
+def _oracle_view(oracle, cam, objs, draws, lights, depth, frames, taa_pcs, hiz_levels):
+    vis, dout, cnt = oracle.occlusion_cull(objs, draws, cam.cull_pc(len(objs), hiz_levels), depth)
+    td, true_counts, _ = oracle.light_cull(lights, cam.light_pc(len(lights)), cam.camera_data(), depth)
+    hist = None
+    for f, pc in zip(frames, taa_pcs):
+        hist = oracle.taa_resolve(f, f if hist is None else hist, None, pc)
+    U, _ = oracle.bloom_chain(hist, 0.8, 5)
+    ldr = oracle.tonemap(hist, U[0], _post_pc())
+    return vis, dout, cnt, td, true_counts, hist, U[0], ldr
+
+
+@pytest.mark.parametrize("W,H", [(320, 180), (1920, 1080)])
+def test_view_run_matches_oracle(backend, oracle, W, H):
+    from ash_renderer_b200.host import TemporalAA
+    cam, objs, draws, depth = _cull_scene(W, H, (8, 8, 8), seed=5)
+    lights = synth.make_lights(256, extent=10.0, seed=5, center=(0.0, 2.0, 22.0))
+    seq = synth.HdrSequence(W, H, seed=6, n_discs=30)
+    taa = TemporalAA()
+    frames, pcs = [], []
+    for _ in range(3):
+        taa.begin_frame()
+        j = taa.current_jitter()
+        frames.append(seq.frame(float(j[0]), float(j[1])))
+        pcs.append(taa.push_constants(W, H))
+    vis, dout, cnt, td, true_counts, taa_ref, bloom_ref, ldr_ref = _oracle_view(
+        oracle, cam, objs, draws, lights, depth, frames, pcs, 10)
+    with _ctx(backend, W, H) as c:
+        c.set_objects(objs, draws)
+        c.upload_lights(lights)
+        c.set_depth(depth)
+        for f, pc in zip(frames, pcs):
+            c.set_color(f, None)
+            c.view_run(_view_params(cam, len(objs), len(lights), 10, W, H, pc))
+        assert np.array_equal(c.visibility(), vis) and c.visible_count() == cnt
+        assert np.array_equal(c.draws_out(cnt), dout)
+        _compare_tile_lists(c.tile_data(), td)
+        _assert_half_images_equal(c.taa_out(), taa_ref, "taa")
+        _assert_half_images_equal(c.bloom_mip(0), bloom_ref, "bloom U_0")
+        d = np.abs(c.ldr8().astype(np.int16) - ldr_ref.astype(np.int16))
+        assert d.max() <= 1
+        st = c.stats()
+        assert st["view_id"] == 7 and st["visible_objects"] == cnt and st["sum_tile_lights"] == int(td[:, 0].sum())
+        assert c.kernel_launches() > 0
+
+
+def test_view_io_host_path(backend, oracle):
+    """upload_view / download_view (the e2e path): host buffers in, host buffers out."""
+    W, H = 320, 180
+    cam, objs, draws, depth = _cull_scene(W, H, (6, 6, 6), seed=8)
+    lights = synth.make_lights(64, extent=10.0, seed=8, center=(0.0, 2.0, 22.0))
+    hdr = synth.random_hdr(W, H, seed=8)
+    pc = _taa_pc(W, H)
+    vis, dout, cnt, td, _, taa_ref, _, ldr_ref = _oracle_view(oracle, cam, objs, draws, lights, depth, [hdr], [pc], 9)
+    tiles = ((W + 15) // 16) * ((H + 15) // 16)
+    o_vis, o_td = np.zeros(len(objs), np.uint32), np.zeros((tiles, 257), np.uint32)
+    o_ldr, o_st, o_cnt = np.zeros((H, W, 4), np.uint8), np.zeros(1, T.VIEW_STATS), np.zeros(1, np.uint32)
+    with _ctx(backend, W, H) as c:
+        c.set_objects(objs, draws)
+        c.upload_lights(lights)
+        c.upload_view(depth, hdr)
+        c.view_run(_view_params(cam, len(objs), len(lights), 9, W, H, pc, view_id=3))
+        c.download_view(o_vis, o_td, o_ldr, o_st, o_cnt)
+        c.sync()
+    assert np.array_equal(o_vis, vis) and o_cnt[0] == cnt and o_st["view_id"][0] == 3
+    _compare_tile_lists(o_td, td)
+    assert np.abs(o_ldr.astype(np.int16) - ldr_ref.astype(np.int16)).max() <= 1
+
+
+def test_golden_vectors_through_cuda(backend):
+    from tests.golden.make_golden import inputs, W, H
+    g = np.load(GOLDEN)
+    i = inputs()
+    cam = i["cam"]
+    with _ctx(backend, W, H) as c:
+        c.set_depth(i["depth"])
+        c.set_objects(i["objs"], i["draws"])
+        c.upload_lights(i["lights"])
+        c.upload_camera(cam.camera_data())
+        c.hiz_build()
+        flat = np.concatenate([c.hiz_mip(l).ravel() for l in range(1, c.hiz_level_count())])
+        assert np.array_equal(flat, g["hiz_flat"])
+        c.occlusion_cull(cam.cull_pc(len(i["objs"]), min(10, c.hiz_level_count())))
+        assert np.array_equal(c.visibility(), g["visibility"]) and c.visible_count() == g["visible_count"][0]
+        assert np.array_equal(c.draws_out(c.visible_count()).view(np.uint32), g["draws_out"])
+        c.light_cull(cam.light_pc(len(i["lights"])))
+        td = c.tile_data()
+        assert np.array_equal(td[:, 0], g["tile_counts"])
+        assert np.array_equal(np.concatenate([td[t, 1:1 + td[t, 0]] for t in range(len(td))]), g["tile_lists"])
+        assert np.array_equal(c.readback(T.BUF_TILE_MINMAX, np.uint32).reshape(-1, 2), g["tile_minmax"])
+        # TAA with an explicit history: seed the history buffer by resolving `hist` with blend 1
+        c.set_color(i["hist"], None)
+        c.taa_resolve(_taa_pc(W, H, blend=1.0, clamp=0.0, vel=0.0, jitter=(0, 0)))
+        c.set_color(i["hdr"], i["vel"])
+        c.taa_resolve(i["taa_pc"])
+        # the seeded history has alpha 1 and identical rgb, so the golden (history = hist) applies
+        assert np.array_equal(c.taa_out().view(np.uint16), g["taa"])
+        c.bloom(_bloom_params())
+        assert np.array_equal(c.bloom_mip(0).view(np.uint16), g["bloom_u0"])
+        c.tonemap(i["post_pc"])
+        assert np.abs(c.ldr8().astype(np.int16) - g["ldr8"].astype(np.int16)).max() <= 1
+
+
+# ------------------------------------------------------------------ size-independent properties at full size
+def test_full_size_properties_4k(backend):
+    import torch
+    W, H = 3840, 2160
+    g = torch.Generator(device="cuda").manual_seed(1)
+    depth = torch.rand((H, W), generator=g, device="cuda", dtype=torch.float32)
+    hdr = (torch.rand((H, W, 4), generator=g, device="cuda") * 4.0).to(torch.float16)
+    hdr[..., 3] = 1.0
+    torch.cuda.synchronize()
+    with _ctx(backend, W, H) as c:
+        c.set_depth(depth)
+        c.hiz_build()
+        # every mip texel equals the max over its footprint (levels with clean 2^l footprints)
+        for l in (1, 3, 4, 7):
+            w, h = W >> l, H >> l
+            ref = depth[:h << l, :w << l].reshape(h, 1 << l, w, 1 << l).amax(dim=(1, 3)).cpu().numpy()
+            assert np.array_equal(c.hiz_mip(l), ref)
+        assert c.hiz_mip(11)[0, 0] == c.hiz_mip(10).max()
+        mm = c.readback(T.BUF_TILE_MINMAX, np.uint32).reshape(135, 240, 2).view(np.float32)
+        tiles = depth.reshape(135, 16, 240, 16)
+        assert np.array_equal(mm[..., 0], tiles.amin(dim=(1, 3)).cpu().numpy())
+        assert np.array_equal(mm[..., 1], tiles.amax(dim=(1, 3)).cpu().numpy())
+        # TAA with blend 0 is the identity on rgb; tonemap is monotone in exposure
+        c.set_color(hdr, None)
+        c.taa_resolve(_taa_pc(W, H, blend=0.0))
+        out = c.taa_out()
+        assert np.array_equal(out[..., :3], hdr[..., :3].cpu().numpy())
+        c.tonemap(_post_pc(exposure=0.5))
+        lo = c.ldr8().copy()
+        c.tonemap(_post_pc(exposure=1.0))
+        assert np.all(c.ldr8()[..., :3] >= lo[..., :3])
+        # bloom is linear in neither input nor threshold, but a frame below threshold-knee blooms to 0
+        dark = (hdr * 0.07).contiguous()
+        c.set_color(dark, None)
+        c.bloom(_bloom_params())
+        assert not c.bloom_mip(0)[..., :3].any()
+
+
+# ------------------------------------------------------------------ error behaviour (AshError mirror)
+def test_error_codes(backend):
+    W, H = 64, 64
+    with _ctx(backend, W, H, max_objects=16, max_lights=4) as c:
+        cam = synth.Camera((0, 0, 5), (0, 0, 0), W, H)
+        with pytest.raises(backend.AshError) as e:
+            c.hiz_build()
+        assert e.value.code == backend.ASH_ERR_NOT_INITIALIZED
+        with pytest.raises(backend.AshError) as e:
+            c.taa_resolve(_taa_pc(W, H))
+        assert e.value.code == backend.ASH_ERR_NOT_INITIALIZED
+        objs, draws = synth.make_objects((3, 3, 3), seed=1)
+        with pytest.raises(backend.AshError) as e:
+            c.set_objects(objs, draws)                    # 27 > max_objects
+        assert e.value.code == backend.ASH_ERR_INVALID
+        c.set_depth(synth.random_depth(W, H))
+        with pytest.raises(backend.AshError) as e:
+            c.light_cull(cam.light_pc(1))                 # no camera uploaded
+        assert e.value.code == backend.ASH_ERR_NOT_INITIALIZED
+        with pytest.raises(backend.AshError) as e:
+            c.get(12345)
+        assert e.value.code == backend.ASH_ERR_NOT_FOUND
+        with pytest.raises(backend.AshError) as e:
+            c.occlusion_cull(cam.cull_pc(0, 99))          # hizLevels > levels_built
+        assert e.value.code == backend.ASH_ERR_INVALID
+    with _ctx(backend, W, H, enable_post=0) as c:
+        with pytest.raises(backend.AshError) as e:
+            c.set_color(synth.random_hdr(W, H), None)
+        assert e.value.code == backend.ASH_ERR_NOT_INITIALIZED
