@@ -184,6 +184,8 @@ def cpu_oracle_rate(objs, draws, lights, views, taa_pc, max_views, budget_s):
     """views/s of the OpenMP oracle on up to `max_views` full 4K views (bounded by `budget_s`)."""
     from oracle import oracle
     oracle.build()
+    if max_views <= 0:
+        return None, oracle.num_threads(), 0
     times = []
     t_all = time.perf_counter()
     for i in range(max_views):

@@ -330,15 +330,16 @@ def test_view_run_matches_oracle(backend, oracle, W, H):
         j = taa.current_jitter()
         frames.append(seq.frame(float(j[0]), float(j[1])))
         pcs.append(taa.push_constants(W, H))
+    levels = min(10, len(oracle.mip_extents(W, H)))
     vis, dout, cnt, td, true_counts, taa_ref, bloom_ref, ldr_ref = _oracle_view(
-        oracle, cam, objs, draws, lights, depth, frames, pcs, 10)
+        oracle, cam, objs, draws, lights, depth, frames, pcs, levels)
     with _ctx(backend, W, H) as c:
         c.set_objects(objs, draws)
         c.upload_lights(lights)
         c.set_depth(depth)
         for f, pc in zip(frames, pcs):
             c.set_color(f, None)
-            c.view_run(_view_params(cam, len(objs), len(lights), 10, W, H, pc))
+            c.view_run(_view_params(cam, len(objs), len(lights), levels, W, H, pc))
         assert np.array_equal(c.visibility(), vis) and c.visible_count() == cnt
         assert np.array_equal(c.draws_out(cnt), dout)
         _compare_tile_lists(c.tile_data(), td)
@@ -425,7 +426,7 @@ def test_full_size_properties_4k(backend):
             w, h = W >> l, H >> l
             ref = depth[:h << l, :w << l].reshape(h, 1 << l, w, 1 << l).amax(dim=(1, 3)).cpu().numpy()
             assert np.array_equal(c.hiz_mip(l), ref)
-        assert c.hiz_mip(11)[0, 0] == c.hiz_mip(10).max()
+        assert c.hiz_mip(11)[0, 0] == c.hiz_mip(10)[:2, :2].max()     # floor sizing drops the odd third column (3x2 -> 1x1)
         mm = c.readback(T.BUF_TILE_MINMAX, np.uint32).reshape(135, 240, 2).view(np.float32)
         tiles = depth.reshape(135, 16, 240, 16)
         assert np.array_equal(mm[..., 0], tiles.amin(dim=(1, 3)).cpu().numpy())
