@@ -30,6 +30,7 @@ EXPORTS = [
     "ashcuda_view_run", "ashcuda_get", "ashcuda_readback", "ashcuda_readback_async", "ashcuda_sync",
     "ashcuda_hiz_level_count", "ashcuda_mip_extent", "ashcuda_kernel_launches", "ashcuda_last_error",
     "ashcuda_version", "ashcuda_profile_kernels", "ashcuda_kernel_time_ms", "ashcuda_upload_view", "ashcuda_download_view",
+    "ashcuda_debug_exact_taps",
 ]
 
 
@@ -83,6 +84,7 @@ def load_library():
         "ashcuda_version": (C.c_char_p, []),
         "ashcuda_profile_kernels": (i32, [vp, u32]),
         "ashcuda_kernel_time_ms": (i32, [vp, i32, C.POINTER(C.c_float), C.POINTER(C.c_uint64)]),
+        "ashcuda_debug_exact_taps": (i32, [i32, i32, i32, C.c_float, C.c_float]),
         "ashcuda_upload_view": (i32, [vp, vp, vp, vp]),
         "ashcuda_download_view": (i32, [vp, vp, vp, vp, vp, vp]),
     }

@@ -25,6 +25,8 @@ struct BloomChain {
     void*    d[ASH_MAX_BLOOM_MIPS + 1];   // d[k]: RGBA16F D_k, overwritten in place by U_k
     uint32_t w[ASH_MAX_BLOOM_MIPS + 1], h[ASH_MAX_BLOOM_MIPS + 1];
     uint32_t mips;
+    bool     down_fast[ASH_MAX_BLOOM_MIPS + 1];   // [k]: level k-1 -> k may use k_downsample_fast
+    bool     up_fast[ASH_MAX_BLOOM_MIPS + 1];     // [k]: level k+1 -> k may use k_upsample_fast
 };
 
 // One candidate light after the per-view prepass: view-space centre + radius, original index.
@@ -123,6 +125,9 @@ struct ashcuda_ctx {
     ash::BloomChain bloom{};
     bool        bloom_valid = false;
     void*       ldr8 = nullptr;
+    bool        center_exact = false;          // (x+0.5)/W taps hit texel x exactly (exact_taps.cu)
+    float       taa_chk[4] = {0, 0, 0, 0};     // screen_params the TAA tap check was last run for
+    bool        taa_exact = false;
 };
 
 namespace ash {
@@ -140,15 +145,35 @@ cudaError_t launch_light_cull(const AshGpuLight* lights, const AshLightCullingPu
                               uint32_t* depth_range, LightCand* cand, uint32_t* cand_idx,
                               uint32_t* cand_count, uint32_t* tile_data, AshViewStats* stats,
                               const Launch& L);
+// `center`: the exact-tap checks passed, so centre / +-1 texel taps may be fetched directly
 cudaError_t launch_taa(const void* cur, const void* hist, const void* vel, void* out,
-                       const AshTaaPushConstants& pc, const Launch& L);
+                       const AshTaaPushConstants& pc, bool center, const Launch& L);
 cudaError_t launch_bloom_threshold(const void* hdr, void* out, uint32_t W, uint32_t H, float threshold,
-                                   const Launch& L);
+                                   bool center, const Launch& L);
 cudaError_t launch_bloom_downsample(const void* src, uint32_t sw, uint32_t sh, void* dst, uint32_t dw,
                                     uint32_t dh, const Launch& L);
 cudaError_t launch_bloom_upsample_add(const void* src, uint32_t sw, uint32_t sh, void* dst, uint32_t dw,
                                       uint32_t dh, float intensity, const Launch& L);
 cudaError_t launch_tonemap(const void* hdr, const void* bloom_or_null, void* ldr8, uint32_t W, uint32_t H,
-                           const AshPostProcessPushConstants& pc, uint32_t srgb, const Launch& L);
+                           const AshPostProcessPushConstants& pc, bool center, const Launch& L);
+
+// ---- fast post kernels (post_fast.cu): bit-identical to the general ones, valid when the exact-tap
+//      checks below hold for the extents involved
+cudaError_t launch_taa_fast(const void* cur, const void* hist, void* out, void* thr_or_null,
+                            const AshTaaPushConstants& pc, float threshold, const Launch& L);
+cudaError_t launch_bloom_downsample_fast(const void* src, uint32_t sw, uint32_t sh, void* dst, uint32_t dw,
+                                         uint32_t dh, const Launch& L);
+cudaError_t launch_bloom_upsample_fast(const void* src, uint32_t sw, uint32_t sh, void* dst, float intensity,
+                                       const Launch& L);
+cudaError_t launch_upsample_tonemap_fast(const void* src, uint32_t sw, uint32_t sh, void* dst, float intensity,
+                                         const void* hdr, void* ldr8, const AshPostProcessPushConstants& pc,
+                                         bool store_u, const Launch& L);
+cudaError_t launch_tonemap_fast(const void* hdr, const void* bloom_or_null, void* ldr8, uint32_t W, uint32_t H,
+                                const AshPostProcessPushConstants& pc, const Launch& L);
+// ---- exact-tap validation (exact_taps.cu), host side, O(n) per axis
+bool axis_center_exact(int n, float size_f);
+bool axis_taa_taps_exact(int n, float size_f, float inv);
+bool axis_down_taps_exact(int sn, int dn);
+bool axis_up_taps_exact(int sn, int dn);
 
 }  // namespace ash

@@ -159,6 +159,13 @@ static int create_impl(ashcuda_ctx* c) {
             b.h[k] = b.h[k - 1] / 2 ? b.h[k - 1] / 2 : 1;
             ASH_CUDA(c, dmalloc(&b.d[k], (size_t)b.w[k] * b.h[k] * 8));
         }
+        // which levels may run the fast kernels: every sampler shortcut is validated here, per extent
+        c->center_exact = axis_center_exact((int)W, (float)W) && axis_center_exact((int)H, (float)H);
+        for (uint32_t k = 0; k <= ASH_MAX_BLOOM_MIPS; ++k) b.down_fast[k] = b.up_fast[k] = false;
+        for (uint32_t k = 1; k <= b.mips; ++k) {
+            b.down_fast[k] = axis_down_taps_exact((int)b.w[k - 1], (int)b.w[k]) && axis_down_taps_exact((int)b.h[k - 1], (int)b.h[k]);
+            b.up_fast[k - 1] = axis_up_taps_exact((int)b.w[k], (int)b.w[k - 1]) && axis_up_taps_exact((int)b.h[k], (int)b.h[k - 1]);
+        }
     }
     ASH_CUDA(c, cudaStreamSynchronize(c->stream));
     return ASH_OK;
@@ -328,15 +335,40 @@ static bool taa_extent_ok(const ashcuda_ctx* c, const AshTaaPushConstants* pc) {
     return (uint32_t)pc->screen_params[0] == c->W && (uint32_t)pc->screen_params[1] == c->H;
 }
 
-int ashcuda_taa_resolve(ashcuda_ctx* c, const AshTaaPushConstants* pc) {
-    if (!c || !pc) return fail(c, ASH_ERR_INVALID, "taa_resolve: null");
+// the 3x3 taps of taa_resolve.comp:118 depend on the caller's screenParams: validate once per value
+static bool taa_taps_exact(ashcuda_ctx* c, const AshTaaPushConstants* pc) {
+    if (memcmp(c->taa_chk, pc->screen_params, sizeof(c->taa_chk)) != 0) {
+        memcpy(c->taa_chk, pc->screen_params, sizeof(c->taa_chk));
+        c->taa_exact = axis_taa_taps_exact((int)c->W, pc->screen_params[0], pc->screen_params[2]) &&
+                       axis_taa_taps_exact((int)c->H, pc->screen_params[1], pc->screen_params[3]);
+    }
+    return c->taa_exact;
+}
+
+// thr_or_null != NULL fuses the bloom threshold of the resolved frame into the resolve (view_run)
+static int taa_resolve_impl(ashcuda_ctx* c, const AshTaaPushConstants* pc, void* thr_or_null, float threshold, bool* fused) {
     if (!c->have_color) return fail(c, ASH_ERR_NOT_INITIALIZED, "taa_resolve: no colour buffer set");
     if (!taa_extent_ok(c, pc)) return fail(c, ASH_ERR_INVALID, "taa_resolve: screenParams differ from the context extent");
     ASH_CUDA(c, cudaSetDevice(c->device));
     // PIN-12: history(t) = output(t-1); first frame (or after reset_history) history = current colour
     const void* hist = c->history_valid ? c->taa[c->taa_cur] : c->color;
     void* out = c->taa[c->taa_cur ^ 1];
-    ASH_CUDA(c, launch_taa(c->color, hist, c->velocity, out, *pc, c->L()));
+    const bool exact = taa_taps_exact(c, pc);
+    *fused = false;
+    if (exact && !c->velocity) {
+        ASH_CUDA(c, launch_taa_fast(c->color, hist, out, thr_or_null, *pc, threshold, c->L()));
+        *fused = thr_or_null != nullptr;
+    } else {
+        ASH_CUDA(c, launch_taa(c->color, hist, c->velocity, out, *pc, exact, c->L()));
+    }
+    return ASH_OK;
+}
+
+int ashcuda_taa_resolve(ashcuda_ctx* c, const AshTaaPushConstants* pc) {
+    if (!c || !pc) return fail(c, ASH_ERR_INVALID, "taa_resolve: null");
+    bool fused;
+    int rc = taa_resolve_impl(c, pc, nullptr, 0.0f, &fused);
+    if (rc) return rc;
     c->taa_cur ^= 1;
     c->history_valid = true;
     c->taa_ran = true;
@@ -346,18 +378,36 @@ int ashcuda_taa_resolve(ashcuda_ctx* c, const AshTaaPushConstants* pc) {
 
 static const void* resolved_color(const ashcuda_ctx* c) { return c->taa_ran ? c->taa[c->taa_cur] : c->color; }
 
+static int bloom_down(ashcuda_ctx* c, uint32_t mips) {          // D_k = downsample(D_{k-1}), PIN-9
+    BloomChain& b = c->bloom;
+    for (uint32_t k = 1; k <= mips; ++k) {
+        if (b.down_fast[k]) ASH_CUDA(c, launch_bloom_downsample_fast(b.d[k - 1], b.w[k - 1], b.h[k - 1], b.d[k], b.w[k], b.h[k], c->L()));
+        else ASH_CUDA(c, launch_bloom_downsample(b.d[k - 1], b.w[k - 1], b.h[k - 1], b.d[k], b.w[k], b.h[k], c->L()));
+    }
+    return ASH_OK;
+}
+
+static int bloom_up(ashcuda_ctx* c, const AshBloomParams* bp, int last) {   // U_k = D_k + upsample(U_{k+1}), k >= last
+    BloomChain& b = c->bloom;
+    for (int k = (int)bp->mip_count - 1; k >= last; --k) {
+        if (b.up_fast[k]) ASH_CUDA(c, launch_bloom_upsample_fast(b.d[k + 1], b.w[k + 1], b.h[k + 1], b.d[k], bp->upsample_intensity, c->L()));
+        else ASH_CUDA(c, launch_bloom_upsample_add(b.d[k + 1], b.w[k + 1], b.h[k + 1], b.d[k], b.w[k], b.h[k],
+                                                   bp->upsample_intensity, c->L()));
+    }
+    return ASH_OK;
+}
+
 int ashcuda_bloom(ashcuda_ctx* c, const AshBloomParams* bp) {
     if (!c || !bp) return fail(c, ASH_ERR_INVALID, "bloom: null");
     if (!c->have_color) return fail(c, ASH_ERR_NOT_INITIALIZED, "bloom: no colour buffer set");
     if (bp->mip_count > c->bloom.mips) return fail(c, ASH_ERR_INVALID, "bloom: mip_count > config bloom_mips");
     ASH_CUDA(c, cudaSetDevice(c->device));
     BloomChain& b = c->bloom;
-    ASH_CUDA(c, launch_bloom_threshold(resolved_color(c), b.d[0], c->W, c->H, bp->threshold, c->L()));
-    for (uint32_t k = 1; k <= bp->mip_count; ++k)
-        ASH_CUDA(c, launch_bloom_downsample(b.d[k - 1], b.w[k - 1], b.h[k - 1], b.d[k], b.w[k], b.h[k], c->L()));
-    for (int k = (int)bp->mip_count - 1; k >= 0; --k)
-        ASH_CUDA(c, launch_bloom_upsample_add(b.d[k + 1], b.w[k + 1], b.h[k + 1], b.d[k], b.w[k], b.h[k],
-                                              bp->upsample_intensity, c->L()));
+    ASH_CUDA(c, launch_bloom_threshold(resolved_color(c), b.d[0], c->W, c->H, bp->threshold, c->center_exact, c->L()));
+    int rc = bloom_down(c, bp->mip_count);
+    if (rc) return rc;
+    rc = bloom_up(c, bp, 0);
+    if (rc) return rc;
     c->bloom_valid = true;
     return ASH_OK;
 }
@@ -366,8 +416,11 @@ int ashcuda_tonemap(ashcuda_ctx* c, const AshPostProcessPushConstants* pc) {
     if (!c || !pc) return fail(c, ASH_ERR_INVALID, "tonemap: null");
     if (!c->have_color) return fail(c, ASH_ERR_NOT_INITIALIZED, "tonemap: no colour buffer set");
     ASH_CUDA(c, cudaSetDevice(c->device));
-    ASH_CUDA(c, launch_tonemap(resolved_color(c), c->bloom_valid ? c->bloom.d[0] : nullptr, c->ldr8, c->W, c->H,
-                               *pc, c->cfg.srgb_encode, c->L()));
+    const void* bloom = c->bloom_valid ? c->bloom.d[0] : nullptr;
+    if (c->center_exact && ((size_t)c->W * c->H) % 2 == 0)
+        ASH_CUDA(c, launch_tonemap_fast(resolved_color(c), bloom, c->ldr8, c->W, c->H, *pc, c->L()));
+    else
+        ASH_CUDA(c, launch_tonemap(resolved_color(c), bloom, c->ldr8, c->W, c->H, *pc, c->center_exact, c->L()));
     return ASH_OK;
 }
 
@@ -379,9 +432,36 @@ int ashcuda_view_run(ashcuda_ctx* c, const AshCudaViewParams* vp) {
     if (st & ASH_STAGE_HIZ) { rc = ashcuda_hiz_build(c); if (rc) return rc; }
     if (st & ASH_STAGE_CULL) { rc = ashcuda_occlusion_cull(c, &vp->cull); if (rc) return rc; }
     if (st & ASH_STAGE_LIGHTS) { rc = ashcuda_light_cull(c, &vp->light); if (rc) return rc; }
-    if (st & ASH_STAGE_TAA) { rc = ashcuda_taa_resolve(c, &vp->taa); if (rc) return rc; }
-    if (st & ASH_STAGE_BLOOM) { rc = ashcuda_bloom(c, &vp->bloom); if (rc) return rc; }
-    if (st & ASH_STAGE_TONEMAP) { rc = ashcuda_tonemap(c, &vp->post); if (rc) return rc; }
+    // ---- post chain: TAA+threshold fused, bloom chain, last upsample + tonemap fused (same results
+    //      as the staged calls; falls back to them stage by stage when a fast kernel does not apply)
+    const bool want_bloom = (st & ASH_STAGE_BLOOM) != 0;
+    if (want_bloom && vp->bloom.mip_count > c->bloom.mips) return fail(c, ASH_ERR_INVALID, "view_run: mip_count > config bloom_mips");
+    bool thr_done = false;
+    if (st & ASH_STAGE_TAA) {
+        rc = taa_resolve_impl(c, &vp->taa, want_bloom ? c->bloom.d[0] : nullptr, vp->bloom.threshold, &thr_done);
+        if (rc) return rc;
+        c->taa_cur ^= 1; c->history_valid = true; c->taa_ran = true; c->bloom_valid = false;
+    }
+    bool tonemap_done = false;
+    if (want_bloom) {
+        if (!c->have_color) return fail(c, ASH_ERR_NOT_INITIALIZED, "bloom: no colour buffer set");
+        BloomChain& b = c->bloom;
+        if (!thr_done)
+            ASH_CUDA(c, launch_bloom_threshold(resolved_color(c), b.d[0], c->W, c->H, vp->bloom.threshold, c->center_exact, c->L()));
+        rc = bloom_down(c, vp->bloom.mip_count); if (rc) return rc;
+        const bool fuse_last = (st & ASH_STAGE_TONEMAP) && vp->bloom.mip_count >= 1 && b.up_fast[0];
+        rc = bloom_up(c, &vp->bloom, fuse_last ? 1 : 0); if (rc) return rc;
+        if (fuse_last) {
+            const bool keep = (st & ASH_STAGE_KEEP_BLOOM) != 0;
+            ASH_CUDA(c, launch_upsample_tonemap_fast(b.d[1], b.w[1], b.h[1], b.d[0], vp->bloom.upsample_intensity,
+                                                     resolved_color(c), c->ldr8, vp->post, keep, c->L()));
+            c->bloom_valid = keep;          // without KEEP_BLOOM, U_0 is never materialised (d[0] still holds D_0)
+            tonemap_done = true;
+        } else {
+            c->bloom_valid = true;
+        }
+    }
+    if ((st & ASH_STAGE_TONEMAP) && !tonemap_done) { rc = ashcuda_tonemap(c, &vp->post); if (rc) return rc; }
     ASH_CUDA(c, cudaMemcpyAsync(&c->stats->view_id, &vp->view_id, 4, cudaMemcpyHostToDevice, c->stream));
     return ASH_OK;
 }
@@ -449,6 +529,16 @@ int ashcuda_sync(ashcuda_ctx* c) {
     ASH_CUDA(c, cudaSetDevice(c->device));
     ASH_CUDA(c, cudaStreamSynchronize(c->stream));
     return ASH_OK;
+}
+
+int ashcuda_debug_exact_taps(int kind, int n_src, int n_dst, float size_f, float inv) {
+    switch (kind) {
+        case 0: return axis_center_exact(n_dst, size_f) ? 1 : 0;
+        case 1: return axis_taa_taps_exact(n_dst, size_f, inv) ? 1 : 0;
+        case 2: return axis_down_taps_exact(n_src, n_dst) ? 1 : 0;
+        case 3: return axis_up_taps_exact(n_src, n_dst) ? 1 : 0;
+        default: return 0;
+    }
 }
 
 uint64_t ashcuda_kernel_launches(ashcuda_ctx* c) { return c ? c->launches : 0; }

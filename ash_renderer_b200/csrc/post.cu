@@ -7,55 +7,9 @@
 // that texel exactly; CENTER=true kernels fetch it directly, CENTER=false kernels run the general
 // sampler for every tap (any extent).  Arithmetic is the pinned-order IEEE sequence of ash_math.cuh,
 // so outputs are bit-identical to the reference semantics, not merely within tolerance.
-#include "ash_internal.cuh"
-#include "ash_math.cuh"
+#include "post_math.cuh"
 
 namespace ash {
-
-struct Tex16 { const uint2* p; int W, H; };
-
-__device__ __forceinline__ V4 fetch16(const Tex16& t, int x, int y) {
-    return unpack_rgba16f(__ldg(t.p + (size_t)y * t.W + x));
-}
-__device__ __forceinline__ V4 fetch16_clamped(const Tex16& t, int x, int y) {
-    return fetch16(t, min(max(x, 0), t.W - 1), min(max(y, 0), t.H - 1));
-}
-__device__ __forceinline__ V4 texture16(const Tex16& t, float u, float v) {
-    int x0, x1, y0, y1; float fx, fy;
-    bilinear_setup(u, t.W, x0, x1, fx);
-    bilinear_setup(v, t.H, y0, y1, fy);
-    const V4 a = fetch16(t, x0, y0), b = fetch16(t, x1, y0), c = fetch16(t, x0, y1), d = fetch16(t, x1, y1);
-    const V4 top = {lerp1(a.x, b.x, fx), lerp1(a.y, b.y, fx), lerp1(a.z, b.z, fx), lerp1(a.w, b.w, fx)};
-    const V4 bot = {lerp1(c.x, d.x, fx), lerp1(c.y, d.y, fx), lerp1(c.z, d.z, fx), lerp1(c.w, d.w, fx)};
-    return {lerp1(top.x, bot.x, fy), lerp1(top.y, bot.y, fy), lerp1(top.z, bot.z, fy), lerp1(top.w, bot.w, fy)};
-}
-__device__ __forceinline__ V3 rgb(V4 v) { return {v.x, v.y, v.z}; }
-
-// ---------------------------------------------------------------- TAA (taa_resolve.comp)
-__device__ __forceinline__ V3 rgb_to_ycocg(V3 c) {                        // :34-40
-    return {fadd(fadd(fmul(0.25f, c.x), fmul(0.5f, c.y)), fmul(0.25f, c.z)),
-            fsub(fmul(0.5f, c.x), fmul(0.5f, c.z)),
-            fsub(fadd(fmul(-0.25f, c.x), fmul(0.5f, c.y)), fmul(0.25f, c.z))};
-}
-__device__ __forceinline__ V3 ycocg_to_rgb(V3 c) {                        // :43-52
-    return {fsub(fadd(c.x, c.y), c.z), fadd(c.x, c.z), fsub(fsub(c.x, c.y), c.z)};
-}
-__device__ __forceinline__ V3 taa_tonemap(V3 c) {                         // :55-57
-    return {fdiv(c.x, fadd(1.0f, c.x)), fdiv(c.y, fadd(1.0f, c.y)), fdiv(c.z, fadd(1.0f, c.z))};
-}
-__device__ __forceinline__ V3 taa_untonemap(V3 c) {                       // :59-61
-    return {fdiv(c.x, fadd(fsub(1.0f, c.x), 0.0001f)), fdiv(c.y, fadd(fsub(1.0f, c.y), 0.0001f)),
-            fdiv(c.z, fadd(fsub(1.0f, c.z), 0.0001f))};
-}
-__device__ __forceinline__ V3 clip_aabb(V3 mn, V3 mx, V3 hist) {          // :64-77
-    const V3 center = scale3(add3(mx, mn), 0.5f);
-    const V3 half = adds3(scale3(sub3(mx, mn), 0.5f), 0.001f);
-    const V3 delta = sub3(hist, center);
-    const V3 v = div3(delta, half);
-    const float maxv = gmax(gmax(fabsf(v.x), fabsf(v.y)), fabsf(v.z));
-    if (maxv > 1.0f) return add3(center, divs3(delta, maxv));
-    return hist;
-}
 
 template <bool CENTER, bool HAS_VEL>
 __global__ void __launch_bounds__(256)
@@ -118,12 +72,11 @@ k_taa_resolve(Tex16 cur, Tex16 hist, const __half2* __restrict__ vel, uint2* __r
 }
 
 cudaError_t launch_taa(const void* cur, const void* hist, const void* vel, void* out,
-                       const AshTaaPushConstants& pc, const Launch& L) {
+                       const AshTaaPushConstants& pc, bool center, const Launch& L) {
     const int W = (int)pc.screen_params[0], H = (int)pc.screen_params[1];
     const Tex16 c{static_cast<const uint2*>(cur), W, H}, h{static_cast<const uint2*>(hist), W, H};
     const dim3 grid((W + 31) / 32, (H + 7) / 8);
     Timed timed(L, ASH_KERNEL_TAA);
-    const bool center = W <= 4096 && H <= 4096;
     const __half2* v = static_cast<const __half2*>(vel);
     uint2* o = static_cast<uint2*>(out);
     if (center) { if (v) k_taa_resolve<true, true><<<grid, 256, 0, L.s>>>(c, h, v, o, pc); else k_taa_resolve<true, false><<<grid, 256, 0, L.s>>>(c, h, v, o, pc); }
@@ -132,17 +85,6 @@ cudaError_t launch_taa(const void* cur, const void* hist, const void* vel, void*
 }
 
 // ---------------------------------------------------------------- bloom threshold (bloom_threshold.frag:18-35)
-__device__ __forceinline__ V3 soft_threshold(V3 c, float threshold) {
-    const float knee = 0.5f;                                                               // :32
-    const float br = gmax(c.x, gmax(c.y, c.z));
-    float soft = fadd(fsub(br, threshold), knee);
-    soft = gclamp(soft, 0.0f, fmul(2.0f, knee));
-    soft = fdiv(fmul(soft, soft), fadd(fmul(4.0f, knee), 0.00001f));
-    float contrib = gmax(soft, fsub(br, threshold));
-    contrib = fdiv(contrib, gmax(br, 0.00001f));
-    return scale3(c, contrib);
-}
-
 template <bool CENTER>
 __global__ void __launch_bounds__(256)
 k_bloom_threshold(Tex16 hdr, uint2* __restrict__ out, float threshold) {
@@ -156,11 +98,11 @@ k_bloom_threshold(Tex16 hdr, uint2* __restrict__ out, float threshold) {
 }
 
 cudaError_t launch_bloom_threshold(const void* hdr, void* out, uint32_t W, uint32_t H, float threshold,
-                                   const Launch& L) {
+                                   bool center, const Launch& L) {
     const Tex16 t{static_cast<const uint2*>(hdr), (int)W, (int)H};
     const dim3 grid((W + 31) / 32, (H + 7) / 8);
     Timed timed(L, ASH_KERNEL_BLOOM_THRESHOLD);
-    if (W <= 4096 && H <= 4096) k_bloom_threshold<true><<<grid, 256, 0, L.s>>>(t, static_cast<uint2*>(out), threshold);
+    if (center) k_bloom_threshold<true><<<grid, 256, 0, L.s>>>(t, static_cast<uint2*>(out), threshold);
     else k_bloom_threshold<false><<<grid, 256, 0, L.s>>>(t, static_cast<uint2*>(out), threshold);
     return cudaGetLastError();
 }
@@ -232,13 +174,6 @@ cudaError_t launch_bloom_upsample_add(const void* src, uint32_t sw, uint32_t sh,
 }
 
 // ---------------------------------------------------------------- tonemap (tonemapping.frag:20-49, PIN-11)
-__device__ __forceinline__ float aces(float x) {                                           // :20-27
-    return gclamp(fdiv(fmul(x, fadd(fmul(2.51f, x), 0.03f)), fadd(fmul(x, fadd(fmul(2.43f, x), 0.59f)), 0.14f)), 0.0f, 1.0f);
-}
-__device__ __forceinline__ uint32_t to_unorm8(float l) {
-    return (uint32_t)floorf(fadd(fmul(gclamp(l, 0.0f, 1.0f), 255.0f), 0.5f));
-}
-
 template <bool CENTER>
 __global__ void __launch_bounds__(256)
 k_tonemap(Tex16 hdr, Tex16 bloom, uint32_t* __restrict__ ldr8, AshPostProcessPushConstants pc) {
@@ -263,12 +198,11 @@ k_tonemap(Tex16 hdr, Tex16 bloom, uint32_t* __restrict__ ldr8, AshPostProcessPus
 }
 
 cudaError_t launch_tonemap(const void* hdr, const void* bloom_or_null, void* ldr8, uint32_t W, uint32_t H,
-                           const AshPostProcessPushConstants& pc, uint32_t srgb, const Launch& L) {
-    (void)srgb;
+                           const AshPostProcessPushConstants& pc, bool center, const Launch& L) {
     const Tex16 h{static_cast<const uint2*>(hdr), (int)W, (int)H}, b{static_cast<const uint2*>(bloom_or_null), (int)W, (int)H};
     const dim3 grid((W + 31) / 32, (H + 7) / 8);
     Timed timed(L, ASH_KERNEL_TONEMAP);
-    if (W <= 4096 && H <= 4096) k_tonemap<true><<<grid, 256, 0, L.s>>>(h, b, static_cast<uint32_t*>(ldr8), pc);
+    if (center) k_tonemap<true><<<grid, 256, 0, L.s>>>(h, b, static_cast<uint32_t*>(ldr8), pc);
     else k_tonemap<false><<<grid, 256, 0, L.s>>>(h, b, static_cast<uint32_t*>(ldr8), pc);
     return cudaGetLastError();
 }

@@ -1,0 +1,382 @@
+// post_fast.cu — the post chain as it runs at 4K: tiled, fused kernels that are BIT-IDENTICAL to the
+// general one-thread-per-pixel kernels of post.cu (and therefore to the reference semantics) but do
+// a fraction of the work:
+//
+//   k_taa_fast           TAA resolve (+ fused bloom threshold): the tonemapped YCoCg neighbourhood is
+//                        computed once per texel into shared memory instead of 9x per pixel; each
+//                        thread resolves a 1x4 pixel strip and shares the row-wise min/max.
+//   k_downsample_fast    2:1 Karis downsample: every tap of the pinned sampler lands exactly midway
+//                        between 4 texels, so the 9 taps are 2x2 box sums over one 4x4 window.
+//   k_upsample_fast      1:2 tent upsample + additive blend (+ fused ACES tonemap / 8-bit pack for the
+//                        last level): weights are exactly 1/4, 3/4; each thread makes a 2x2 block and
+//                        shares the horizontal lerps between its two rows.
+//
+// Why identical: (1) exact_taps.cu proves, per extent, that the sampler selects exactly the texels
+// and weights assumed here; (2) scaling by a power of two commutes with IEEE rounding (no fp32
+// subnormals can arise from fp16 texels), so factors 1/2, 1/4, 1/16 are deferred; (3) a product that
+// is exactly representable (fp16 texel x 3, x * 2^k) may feed an FMA without changing the single
+// rounding of the following add.  Every other operation is the pinned IEEE sequence of ash_math.cuh.
+// Preconditions: colour texels are finite and carry no negative zeros.
+#include "post_math.cuh"
+
+namespace ash {
+
+__device__ __forceinline__ float fma_exact(float a, float b, float c) { return __fmaf_rn(a, b, c); }
+__device__ __forceinline__ V3 unpack_rgb(uint2 t) { V4 v = unpack_rgba16f(t); return {v.x, v.y, v.z}; }
+
+// =====================================================================================================
+// TAA resolve (+ bloom threshold) — taa_resolve.comp:83-167 (+ bloom_threshold.frag:18-35)
+// No velocity buffer (PIN-12: velocity == 0 -> jitter-delta branch, uniform over the frame).
+// CTA = 32x32 pixels, 256 threads, thread = 1x4 strip.
+// =====================================================================================================
+__device__ __forceinline__ V3 clip_aabb_fast(V3 mn, V3 mx, V3 hist) {       // :64-77
+    const V3 center = scale3(add3(mx, mn), 0.5f);
+    const V3 half = adds3(scale3(sub3(mx, mn), 0.5f), 0.001f);
+    const V3 delta = sub3(hist, center);
+    // RN(|d|/h) > 1  <=>  |d| > h  for h >= 0.001 (a float above h is at least h + ulp(h) > h(1 + 2^-24))
+    if (fabsf(delta.x) > half.x || fabsf(delta.y) > half.y || fabsf(delta.z) > half.z) {
+        const V3 v = div3(delta, half);
+        const float maxv = fmaxf(fmaxf(fabsf(v.x), fabsf(v.y)), fabsf(v.z));
+        return add3(center, divs3(delta, maxv));
+    }
+    return hist;
+}
+
+template <bool THRESH>
+__global__ void __launch_bounds__(256, 2)
+k_taa_fast(Tex16 cur, Tex16 hist, uint2* __restrict__ out, uint2* __restrict__ thr,
+           AshTaaPushConstants pc, float threshold) {
+    __shared__ float4 s_nb[34][34];
+    const int W = cur.W, H = cur.H;
+    const int x0 = blockIdx.x * 32, y0 = blockIdx.y * 32;
+    const bool clamp_on = pc.params[1] > 0.5f;
+    if (clamp_on) {
+        for (int idx = threadIdx.x; idx < 34 * 34; idx += 256) {
+            const int r = idx / 34, c = idx - r * 34;
+            const int gx = min(max(x0 - 1 + c, 0), W - 1), gy = min(max(y0 - 1 + r, 0), H - 1);
+            const V3 s = rgb_to_ycocg(taa_tonemap(unpack_rgb(__ldg(cur.p + (size_t)gy * W + gx))));   // :120
+            s_nb[r][c] = make_float4(s.x, s.y, s.z, 0.0f);
+        }
+    }
+    __syncthreads();
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    const int x = x0 + tx, yb = y0 + 4 * ty;
+    if (x >= W || yb >= H) return;
+
+    const float sw = pc.screen_params[0], sh = pc.screen_params[1];
+    const float u = fdiv(fadd((float)x, 0.5f), sw);                                        // :92
+    const float vx = fdiv(fsub(pc.jitter[0], pc.prev_jitter[0]), sw);                      // :97-99
+    const float vy = fdiv(fsub(pc.jitter[1], pc.prev_jitter[1]), sh);
+    const float hu = gclamp(fsub(u, vx), 0.0f, 1.0f);                                      // :102
+    int hx0, hx1; float fx;
+    bilinear_setup(hu, W, hx0, hx1, fx);
+    float blend = pc.params[0];                                                            // :145-150
+    if (pc.params[2] > 0.5f) {
+        const float vl = length2(fmul(vx, sw), fmul(vy, sh));
+        blend = fmul(blend, gclamp(fsub(1.0f, fmul(vl, 0.1f)), 0.0f, 1.0f));
+    }
+    const float ib = fsub(1.0f, blend);
+    const float ifx = fsub(1.0f, fx);
+
+    // row-wise min / max of the 3 horizontal neighbours, for the 6 rows this strip touches
+    V3 rmn[6], rmx[6];
+    if (clamp_on) {
+#pragma unroll
+        for (int r = 0; r < 6; ++r) {
+            const float4 a = s_nb[4 * ty + r][tx], b = s_nb[4 * ty + r][tx + 1], c = s_nb[4 * ty + r][tx + 2];
+            rmn[r] = {fminf(fminf(a.x, b.x), c.x), fminf(fminf(a.y, b.y), c.y), fminf(fminf(a.z, b.z), c.z)};
+            rmx[r] = {fmaxf(fmaxf(a.x, b.x), c.x), fmaxf(fmaxf(a.y, b.y), c.y), fmaxf(fmaxf(a.z, b.z), c.z)};
+        }
+    }
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const int y = yb + k;
+        if (y >= H) break;
+        const float v = fdiv(fadd((float)y, 0.5f), sh);
+        const float hv = gclamp(fsub(v, vy), 0.0f, 1.0f);
+        int hy0, hy1; float fy;
+        bilinear_setup(hv, H, hy0, hy1, fy);
+        const V3 c = unpack_rgb(__ldg(cur.p + (size_t)y * W + x));                         // :105 (centre tap == texel)
+        V3 h;                                                                              // :108 bilinear history
+        {
+            const V3 a = unpack_rgb(__ldg(hist.p + (size_t)hy0 * W + hx0)), b = unpack_rgb(__ldg(hist.p + (size_t)hy0 * W + hx1));
+            const V3 cc = unpack_rgb(__ldg(hist.p + (size_t)hy1 * W + hx0)), d = unpack_rgb(__ldg(hist.p + (size_t)hy1 * W + hx1));
+            const float ify = fsub(1.0f, fy);
+            const V3 top = {fadd(fmul(a.x, ifx), fmul(b.x, fx)), fadd(fmul(a.y, ifx), fmul(b.y, fx)), fadd(fmul(a.z, ifx), fmul(b.z, fx))};
+            const V3 bot = {fadd(fmul(cc.x, ifx), fmul(d.x, fx)), fadd(fmul(cc.y, ifx), fmul(d.y, fx)), fadd(fmul(cc.z, ifx), fmul(d.z, fx))};
+            h = {fadd(fmul(top.x, ify), fmul(bot.x, fy)), fadd(fmul(top.y, ify), fmul(bot.y, fy)), fadd(fmul(top.z, ify), fmul(bot.z, fy))};
+        }
+        if (clamp_on) {                                                                    // :112-142
+            V3 mn = {fminf(fminf(rmn[k].x, rmn[k + 1].x), rmn[k + 2].x), fminf(fminf(rmn[k].y, rmn[k + 1].y), rmn[k + 2].y),
+                     fminf(fminf(rmn[k].z, rmn[k + 1].z), rmn[k + 2].z)};
+            V3 mx = {fmaxf(fmaxf(rmx[k].x, rmx[k + 1].x), rmx[k + 2].x), fmaxf(fmaxf(rmx[k].y, rmx[k + 1].y), rmx[k + 2].y),
+                     fmaxf(fmaxf(rmx[k].z, rmx[k + 1].z), rmx[k + 2].z)};
+            const V3 ctr = scale3(add3(mn, mx), 0.5f), ext = scale3(sub3(mx, mn), 0.5f);   // :132-135
+            mn = sub3(ctr, scale3(ext, 1.25f));
+            mx = add3(ctr, scale3(ext, 1.25f));
+            const V3 hy = rgb_to_ycocg(taa_tonemap(h));
+            h = taa_untonemap(ycocg_to_rgb(clip_aabb_fast(mn, mx, hy)));                   // :140-141
+        }
+        const uint2 o = pack_rgba16f(fadd(fmul(c.x, ib), fmul(h.x, blend)), fadd(fmul(c.y, ib), fmul(h.y, blend)),
+                                     fadd(fmul(c.z, ib), fmul(h.z, blend)), 1.0f);         // mix(), :159
+        out[(size_t)y * W + x] = o;
+        if (THRESH) {                      // bloom threshold of the resolved texel as stored (fp16)
+            const V3 b = soft_threshold(unpack_rgb(o), threshold);
+            thr[(size_t)y * W + x] = pack_rgba16f(b.x, b.y, b.z, 1.0f);
+        }
+    }
+}
+
+cudaError_t launch_taa_fast(const void* cur, const void* hist, void* out, void* thr_or_null,
+                            const AshTaaPushConstants& pc, float threshold, const Launch& L) {
+    const int W = (int)pc.screen_params[0], H = (int)pc.screen_params[1];
+    const Tex16 c{static_cast<const uint2*>(cur), W, H}, h{static_cast<const uint2*>(hist), W, H};
+    const dim3 grid((W + 31) / 32, (H + 31) / 32);
+    if (thr_or_null) {
+        Timed timed(L, ASH_KERNEL_TAA_THRESHOLD);
+        k_taa_fast<true><<<grid, 256, 0, L.s>>>(c, h, static_cast<uint2*>(out), static_cast<uint2*>(thr_or_null), pc, threshold);
+    } else {
+        Timed timed(L, ASH_KERNEL_TAA);
+        k_taa_fast<false><<<grid, 256, 0, L.s>>>(c, h, static_cast<uint2*>(out), nullptr, pc, threshold);
+    }
+    return cudaGetLastError();
+}
+
+// =====================================================================================================
+// Bloom downsample, source extent == 2 x destination extent (bloom_downsample.frag:16-108)
+// CTA = 32x8 destination pixels; source tile 66x18 texels staged in shared memory as fp16.
+// =====================================================================================================
+__global__ void __launch_bounds__(256)
+k_downsample_fast(const uint2* __restrict__ src, int sw, int sh, uint2* __restrict__ dst, int dw, int dh) {
+    __shared__ __align__(16) uint2 s_t[18][66];
+    const int x0 = blockIdx.x * 32, y0 = blockIdx.y * 8;
+    for (int idx = threadIdx.x; idx < 18 * 66; idx += 256) {
+        const int r = idx / 66, c = idx - r * 66;
+        const int gx = min(max(2 * x0 - 1 + c, 0), sw - 1), gy = min(max(2 * y0 - 1 + r, 0), sh - 1);   // CLAMP_TO_EDGE
+        s_t[r][c] = __ldg(src + (size_t)gy * sw + gx);
+    }
+    __syncthreads();
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    const int x = x0 + tx, y = y0 + ty;
+    if (x >= dw || y >= dh) return;
+
+    // 4x4 window: window (i,j) = source texel (2x-1+i, 2y-1+j)
+    V3 hs[4][3];     // hs[j][i] = t[j][i] + t[j][i+1]            (= 2 * horizontal lerp at 1/2)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        const uint4 p0 = *reinterpret_cast<const uint4*>(&s_t[2 * ty + j][2 * tx]);
+        const uint4 p1 = *reinterpret_cast<const uint4*>(&s_t[2 * ty + j][2 * tx + 2]);
+        const V3 t0 = unpack_rgb(make_uint2(p0.x, p0.y)), t1 = unpack_rgb(make_uint2(p0.z, p0.w));
+        const V3 t2 = unpack_rgb(make_uint2(p1.x, p1.y)), t3 = unpack_rgb(make_uint2(p1.z, p1.w));
+        hs[j][0] = add3(t0, t1); hs[j][1] = add3(t1, t2); hs[j][2] = add3(t2, t3);
+    }
+    V3 res = {0.0f, 0.0f, 0.0f};
+    float sum = 0.0f;
+    // tap(i,j): 4 * bilinear sample whose 2x2 footprint starts at window (i,j); s = tap/4
+    auto tap = [&](int i, int j, float wt) {
+        const V3 t4 = add3(hs[j][i], hs[j + 1][i]);
+        const float luma4 = fadd(fadd(fmul(t4.x, 0.2126f), fmul(t4.y, 0.7152f)), fmul(t4.z, 0.0722f));
+        const float w = fdiv(1.0f, fma_exact(luma4, 0.25f, 1.0f));          // 1 / (1 + luma)        :87-101
+        const float k = 0.25f * wt;                                          // power of two
+        res = {fma_exact(fmul(t4.x, w), k, res.x), fma_exact(fmul(t4.y, w), k, res.y), fma_exact(fmul(t4.z, w), k, res.z)};
+        sum = fma_exact(w, wt, sum);
+    };
+    tap(1, 1, 0.25f);                                                        // centre
+    tap(0, 0, 0.0625f); tap(2, 0, 0.0625f); tap(0, 2, 0.0625f); tap(2, 2, 0.0625f);   // a b c d   :25-28
+    tap(0, 1, 0.125f);  tap(2, 1, 0.125f);  tap(1, 0, 0.125f);  tap(1, 2, 0.125f);    // e f g h   :31-34
+    dst[(size_t)y * dw + x] = pack_rgba16f(fdiv(res.x, sum), fdiv(res.y, sum), fdiv(res.z, sum), 1.0f);   // :107
+}
+
+cudaError_t launch_bloom_downsample_fast(const void* src, uint32_t sw, uint32_t sh, void* dst, uint32_t dw,
+                                         uint32_t dh, const Launch& L) {
+    const dim3 grid((dw + 31) / 32, (dh + 7) / 8);
+    Timed timed(L, ASH_KERNEL_BLOOM_DOWNSAMPLE);
+    k_downsample_fast<<<grid, 256, 0, L.s>>>(static_cast<const uint2*>(src), (int)sw, (int)sh,
+                                             static_cast<uint2*>(dst), (int)dw, (int)dh);
+    return cudaGetLastError();
+}
+
+// =====================================================================================================
+// Bloom upsample + additive blend, destination extent == 2 x source extent
+// (bloom_upsample.frag:16-41, PIN-9), optionally fused with tonemapping.frag:29-48 + PIN-11.
+// CTA = 16x16 source texels = 32x32 destination pixels; thread = 2x2 destination block.
+//
+// Destination pixel x = 2i + p samples the source at i - 1/4 + p/2 + m/2 for tap offsets
+// m = -2..2 (in units of d = half a source texel): window column (origin i-2) c0 and weight g:
+//   c0 = floor((2p - 1 + 2m) / 4) + 2,   g = ((2p - 1 + 2m) mod 4) / 4  in {1/4, 3/4}.
+// =====================================================================================================
+__host__ __device__ constexpr int up_fd4(int q) { return q >= 0 ? q / 4 : -((-q + 3) / 4); }
+__host__ __device__ constexpr int up_c0(int p, int m) { return up_fd4(2 * p - 1 + 2 * m) + 2; }
+__host__ __device__ constexpr bool up_g75(int p, int m) { return (2 * p - 1 + 2 * m) - 4 * up_fd4(2 * p - 1 + 2 * m) == 3; }
+
+// 4 * lerp(a, b, g): g = 3/4 -> a + 3b ; g = 1/4 -> 3a + b   (3 * fp16 texel is exact)
+template <bool G75>
+__device__ __forceinline__ V3 hlerp4(V3 a, V3 b) {
+    if (G75) return {fma_exact(b.x, 3.0f, a.x), fma_exact(b.y, 3.0f, a.y), fma_exact(b.z, 3.0f, a.z)};
+    return {fma_exact(a.x, 3.0f, b.x), fma_exact(a.y, 3.0f, b.y), fma_exact(a.z, 3.0f, b.z)};
+}
+// 16 * lerp(H0, H1, g) from h = 4H: g = 3/4 -> h0 + RN(3 h1) ; g = 1/4 -> RN(3 h0) + h1
+template <bool G75>
+__device__ __forceinline__ V3 vlerp16(V3 h0, V3 h1) {
+    if (G75) return {fadd(h0.x, fmul(h1.x, 3.0f)), fadd(h0.y, fmul(h1.y, 3.0f)), fadd(h0.z, fmul(h1.z, 3.0f))};
+    return {fadd(fmul(h0.x, 3.0f), h1.x), fadd(fmul(h0.y, 3.0f), h1.y), fadd(fmul(h0.z, 3.0f), h1.z)};
+}
+
+struct UpH {            // horizontal lerps (x4) of one destination-column parity
+    V3 m2[3], m1[3], z[5], p1[3], p2[3];   // tap m = -2,-1: window rows 1..3 ; m = 0: rows 0..4 ; m = +1,+2: rows 1..3
+};
+
+template <int PX>
+__device__ __forceinline__ void up_hlerps(const uint2 (*s_t)[20], int tj, int ti, UpH& h) {
+#pragma unroll
+    for (int r = 0; r < 5; ++r) {
+        V3 t[5];
+#pragma unroll
+        for (int c = 0; c < 4; ++c) t[c + PX] = unpack_rgb(s_t[tj + r][ti + c + PX]);   // window cols PX..PX+3
+        h.z[r] = hlerp4<up_g75(PX, 0)>(t[up_c0(PX, 0)], t[up_c0(PX, 0) + 1]);
+        if (r >= 1 && r <= 3) {
+            h.m2[r - 1] = hlerp4<up_g75(PX, -2)>(t[up_c0(PX, -2)], t[up_c0(PX, -2) + 1]);
+            h.m1[r - 1] = hlerp4<up_g75(PX, -1)>(t[up_c0(PX, -1)], t[up_c0(PX, -1) + 1]);
+            h.p1[r - 1] = hlerp4<up_g75(PX, 1)>(t[up_c0(PX, 1)], t[up_c0(PX, 1) + 1]);
+            h.p2[r - 1] = hlerp4<up_g75(PX, 2)>(t[up_c0(PX, 2)], t[up_c0(PX, 2) + 1]);
+        }
+    }
+}
+
+// 256 * (tent sum / 16), i.e. R16 of the file header; rows via the same (c0, g) tables with p = PY
+template <int PY>
+__device__ __forceinline__ V3 up_combine(const UpH& h) {
+#define ASH_UPV(arr, base, n) vlerp16<up_g75(PY, n)>(arr[up_c0(PY, n) - (base)], arr[up_c0(PY, n) + 1 - (base)])
+    const V3 s0 = ASH_UPV(h.m2, 1, 0);      // (-2d, 0)      bloom_upsample.frag:21
+    const V3 s1 = ASH_UPV(h.m1, 1, -1);     // (-d, -d)
+    const V3 s2 = ASH_UPV(h.z, 0, -2);      // (0, -2d)
+    const V3 s3 = ASH_UPV(h.p1, 1, -1);     // (d, -d)
+    const V3 s4 = ASH_UPV(h.p2, 1, 0);      // (2d, 0)
+    const V3 s5 = ASH_UPV(h.p1, 1, 1);      // (d, d)
+    const V3 s6 = ASH_UPV(h.z, 0, 2);       // (0, 2d)
+    const V3 s7 = ASH_UPV(h.m1, 1, 1);      // (-d, d)
+    const V3 s8 = ASH_UPV(h.z, 0, 0);       // (0, 0)
+#undef ASH_UPV
+    const V3 q = add3(add3(add3(s1, s3), s5), s7);                           // :33
+    const V3 p = add3(add3(add3(s0, s2), s4), s6);                           // :34
+    const V3 r = {fadd(fadd(fmul(s8.x, 4.0f), fmul(q.x, 2.0f)), p.x), fadd(fadd(fmul(s8.y, 4.0f), fmul(q.y, 2.0f)), p.y),
+                  fadd(fadd(fmul(s8.z, 4.0f), fmul(q.z, 2.0f)), p.z)};       // :32-34
+    return r;
+}
+
+__device__ __forceinline__ float aces_fast(float x) {                        // tonemapping.frag:20-27, 8-bit output only
+    const float n = x * (2.51f * x + 0.03f), d = x * (2.43f * x + 0.59f) + 0.14f;
+    return __saturatef(__fdividef(n, d));
+}
+__device__ __forceinline__ uint32_t tonemap_pack8(V3 c, V3 bloom, const AshPostProcessPushConstants& pc, float inv_gamma) {
+    const float r = (c.x + bloom.x * pc.bloom_intensity) * pc.exposure;      // :38, :41
+    const float g = (c.y + bloom.y * pc.bloom_intensity) * pc.exposure;
+    const float b = (c.z + bloom.z * pc.bloom_intensity) * pc.exposure;
+    const uint32_t r8 = (uint32_t)__float2int_rd(__saturatef(__powf(aces_fast(r), inv_gamma)) * 255.0f + 0.5f);   // :44-47, PIN-11
+    const uint32_t g8 = (uint32_t)__float2int_rd(__saturatef(__powf(aces_fast(g), inv_gamma)) * 255.0f + 0.5f);
+    const uint32_t b8 = (uint32_t)__float2int_rd(__saturatef(__powf(aces_fast(b), inv_gamma)) * 255.0f + 0.5f);
+    return r8 | (g8 << 8) | (b8 << 16) | 0xFF000000u;
+}
+
+template <bool TONEMAP, bool STORE_U>
+__global__ void __launch_bounds__(256, 2)
+k_upsample_fast(const uint2* __restrict__ src, int sw, int sh, uint2* __restrict__ dst, float intensity,
+                const uint2* __restrict__ hdr, uint32_t* __restrict__ ldr8, AshPostProcessPushConstants pc) {
+    __shared__ uint2 s_t[20][20];
+    const int i0 = blockIdx.x * 16, j0 = blockIdx.y * 16;
+    for (int idx = threadIdx.x; idx < 400; idx += 256) {
+        const int r = idx / 20, c = idx - r * 20;
+        const int gx = min(max(i0 - 2 + c, 0), sw - 1), gy = min(max(j0 - 2 + r, 0), sh - 1);          // CLAMP_TO_EDGE
+        s_t[r][c] = __ldg(src + (size_t)gy * sw + gx);
+    }
+    __syncthreads();
+    const int ti = threadIdx.x & 15, tj = threadIdx.x >> 4;
+    const int i = i0 + ti, j = j0 + tj;
+    if (i >= sw || j >= sh) return;
+    const int dw = 2 * sw;
+    const float k = fmul(intensity, 0.00390625f);                 // (R16 / 256) * intensity == R16 * (intensity / 256)
+    const float inv_gamma = TONEMAP ? __fdividef(1.0f, pc.gamma) : 0.0f;
+
+    V3 up[2][2];     // [py][px] upsampled value, before the additive blend
+    {
+        UpH h;
+        up_hlerps<0>(s_t, tj, ti, h);
+        const V3 a = up_combine<0>(h), b = up_combine<1>(h);
+        up[0][0] = {fmul(a.x, k), fmul(a.y, k), fmul(a.z, k)};
+        up[1][0] = {fmul(b.x, k), fmul(b.y, k), fmul(b.z, k)};
+    }
+    {
+        UpH h;
+        up_hlerps<1>(s_t, tj, ti, h);
+        const V3 a = up_combine<0>(h), b = up_combine<1>(h);
+        up[0][1] = {fmul(a.x, k), fmul(a.y, k), fmul(a.z, k)};
+        up[1][1] = {fmul(b.x, k), fmul(b.y, k), fmul(b.z, k)};
+    }
+#pragma unroll
+    for (int py = 0; py < 2; ++py) {
+        const size_t o = (size_t)(2 * j + py) * dw + 2 * i;                   // 16-byte aligned pair of texels
+        const uint4 d = *reinterpret_cast<const uint4*>(dst + o);
+        const V3 d0 = unpack_rgb(make_uint2(d.x, d.y)), d1 = unpack_rgb(make_uint2(d.z, d.w));
+        const uint2 u0 = pack_rgba16f(fadd(up[py][0].x, d0.x), fadd(up[py][0].y, d0.y), fadd(up[py][0].z, d0.z), 1.0f);
+        const uint2 u1 = pack_rgba16f(fadd(up[py][1].x, d1.x), fadd(up[py][1].y, d1.y), fadd(up[py][1].z, d1.z), 1.0f);
+        if (STORE_U) *reinterpret_cast<uint4*>(dst + o) = make_uint4(u0.x, u0.y, u1.x, u1.y);
+        if (TONEMAP) {
+            const uint4 c = __ldg(reinterpret_cast<const uint4*>(hdr + o));
+            const uint32_t a8 = tonemap_pack8(unpack_rgb(make_uint2(c.x, c.y)), unpack_rgb(u0), pc, inv_gamma);
+            const uint32_t b8 = tonemap_pack8(unpack_rgb(make_uint2(c.z, c.w)), unpack_rgb(u1), pc, inv_gamma);
+            *reinterpret_cast<uint2*>(ldr8 + o) = make_uint2(a8, b8);
+        }
+    }
+}
+
+cudaError_t launch_bloom_upsample_fast(const void* src, uint32_t sw, uint32_t sh, void* dst, float intensity,
+                                       const Launch& L) {
+    const dim3 grid((sw + 15) / 16, (sh + 15) / 16);
+    Timed timed(L, ASH_KERNEL_BLOOM_UPSAMPLE);
+    k_upsample_fast<false, true><<<grid, 256, 0, L.s>>>(static_cast<const uint2*>(src), (int)sw, (int)sh,
+                                                        static_cast<uint2*>(dst), intensity, nullptr, nullptr,
+                                                        AshPostProcessPushConstants{});
+    return cudaGetLastError();
+}
+
+cudaError_t launch_upsample_tonemap_fast(const void* src, uint32_t sw, uint32_t sh, void* dst, float intensity,
+                                         const void* hdr, void* ldr8, const AshPostProcessPushConstants& pc,
+                                         bool store_u, const Launch& L) {
+    const dim3 grid((sw + 15) / 16, (sh + 15) / 16);
+    Timed timed(L, ASH_KERNEL_UPSAMPLE_TONEMAP);
+    if (store_u)
+        k_upsample_fast<true, true><<<grid, 256, 0, L.s>>>(static_cast<const uint2*>(src), (int)sw, (int)sh, static_cast<uint2*>(dst),
+                                                           intensity, static_cast<const uint2*>(hdr), static_cast<uint32_t*>(ldr8), pc);
+    else
+        k_upsample_fast<true, false><<<grid, 256, 0, L.s>>>(static_cast<const uint2*>(src), (int)sw, (int)sh, static_cast<uint2*>(dst),
+                                                            intensity, static_cast<const uint2*>(hdr), static_cast<uint32_t*>(ldr8), pc);
+    return cudaGetLastError();
+}
+
+// =====================================================================================================
+// Tonemap alone (tonemapping.frag:29-48), centre taps validated: one thread = 2 pixels (16 B in, 8 B out)
+// =====================================================================================================
+__global__ void __launch_bounds__(256)
+k_tonemap_fast(const uint4* __restrict__ hdr, const uint4* __restrict__ bloom, uint2* __restrict__ ldr8, size_t pairs,
+               AshPostProcessPushConstants pc) {
+    const float inv_gamma = __fdividef(1.0f, pc.gamma);
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < pairs; i += (size_t)gridDim.x * blockDim.x) {
+        const uint4 c = __ldg(hdr + i);
+        uint4 b = make_uint4(0, 0, 0, 0);
+        if (bloom) b = __ldg(bloom + i);
+        ldr8[i] = make_uint2(tonemap_pack8(unpack_rgb(make_uint2(c.x, c.y)), unpack_rgb(make_uint2(b.x, b.y)), pc, inv_gamma),
+                             tonemap_pack8(unpack_rgb(make_uint2(c.z, c.w)), unpack_rgb(make_uint2(b.z, b.w)), pc, inv_gamma));
+    }
+}
+
+cudaError_t launch_tonemap_fast(const void* hdr, const void* bloom_or_null, void* ldr8, uint32_t W, uint32_t H,
+                                const AshPostProcessPushConstants& pc, const Launch& L) {
+    const size_t pairs = (size_t)W * H / 2;
+    const unsigned grid = (unsigned)min((pairs + 255) / 256, (size_t)148 * 16);
+    Timed timed(L, ASH_KERNEL_TONEMAP);
+    k_tonemap_fast<<<grid, 256, 0, L.s>>>(static_cast<const uint4*>(hdr), static_cast<const uint4*>(bloom_or_null),
+                                          static_cast<uint2*>(ldr8), pairs, pc);
+    return cudaGetLastError();
+}
+
+}  // namespace ash

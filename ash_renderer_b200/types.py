@@ -48,6 +48,7 @@ TILE_STRIDE = 257
 
 STAGE_HIZ, STAGE_CULL, STAGE_LIGHTS, STAGE_TAA, STAGE_BLOOM, STAGE_TONEMAP = 1, 2, 4, 8, 16, 32
 STAGE_ALL = 0x3F
+STAGE_KEEP_BLOOM = 0x40
 
 BUF_VISIBILITY, BUF_DRAWS_OUT, BUF_VISIBLE_COUNT, BUF_TILE_DATA = 1, 2, 3, 4
 BUF_TAA_OUT, BUF_LDR8, BUF_STATS, BUF_TILE_MINMAX, BUF_VISIBILITY_BITS = 5, 6, 7, 8, 9

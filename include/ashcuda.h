@@ -169,6 +169,8 @@ typedef struct AshCudaViewParams {
 #define ASH_STAGE_BLOOM      0x10u
 #define ASH_STAGE_TONEMAP    0x20u
 #define ASH_STAGE_ALL        0x3Fu
+#define ASH_STAGE_KEEP_BLOOM 0x40u /* view_run: also store the bloom buffer U_0 (the fused last upsample +
+                                      tonemap otherwise never writes it; ASH_BUF_BLOOM_MIP(0) then holds D_0) */
 
 /* Buffer ids for ashcuda_get / ashcuda_readback. */
 #define ASH_BUF_HIZ_MIP(i)    (0x100 + (i)) /* fp32 W_i x H_i; mip 0 is the depth buffer      */
@@ -259,6 +261,11 @@ uint64_t ashcuda_kernel_launches(ashcuda_ctx*);                /* kernels launch
  * launch count accumulated for one class since the previous query of it, and resets them. */
 int ashcuda_profile_kernels(ashcuda_ctx*, uint32_t mask);
 int ashcuda_kernel_time_ms(ashcuda_ctx*, int kernel_class, float* ms, uint64_t* launches);
+/* Diagnostics (host only, no device needed): does the pinned LINEAR sampler land exactly on the
+ * texels/weights the fast kernels assume, for every coordinate of one axis?  kind 0: centre taps
+ * (n_dst texels, size_f = extent as float); 1: TAA 3x3 taps (size_f, inv = screenParams.z|w);
+ * 2: 2:1 downsample (n_src -> n_dst); 3: 1:2 upsample (n_src -> n_dst).  Returns 1 / 0. */
+int ashcuda_debug_exact_taps(int kind, int n_src, int n_dst, float size_f, float inv);
 const char* ashcuda_last_error(ashcuda_ctx*);                  /* NULL ctx: last create error */
 const char* ashcuda_version(void);
 

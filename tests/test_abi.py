@@ -107,3 +107,20 @@ def test_product_package_never_touches_the_oracle():
                 text = open(os.path.join(dirpath, f), errors="ignore").read()
                 assert "libashoracle" not in text and "ash_oracle_" not in text, f
                 assert not re.search(r"^\s*(from|import)\s+oracle", text, flags=re.M), f
+
+
+def test_exact_tap_validation_of_the_fast_kernels():
+    """exact_taps.cu: the sampler shortcuts hold for the benchmark extents and are refused otherwise."""
+    lib = backend.load_library()
+    f = np.float32
+    for n in (3840, 2160, 1920, 1080, 960, 540, 64, 33, 1):
+        assert lib.ashcuda_debug_exact_taps(0, 0, n, f(n), f(0)) == 1
+        assert lib.ashcuda_debug_exact_taps(1, 0, n, f(n), f(1) / f(n)) == 1
+    assert lib.ashcuda_debug_exact_taps(1, 0, 1920, f(1920), f(0.7) / f(1920)) == 0      # caller passed a wrong texel size
+    assert lib.ashcuda_debug_exact_taps(0, 0, 1920, f(1900), f(0)) == 0
+    for s, d in ((3840, 1920), (2160, 1080), (1920, 960), (1080, 540), (540, 270), (270, 135), (4096, 2048), (2, 1)):
+        assert lib.ashcuda_debug_exact_taps(2, s, d, f(0), f(0)) == 1
+        assert lib.ashcuda_debug_exact_taps(3, d, s, f(0), f(0)) == 1
+    for s, d in ((135, 67), (67, 33), (33, 16), (3, 1)):                                # odd: general kernels
+        assert lib.ashcuda_debug_exact_taps(2, s, d, f(0), f(0)) == 0
+        assert lib.ashcuda_debug_exact_taps(3, d, s, f(0), f(0)) == 0

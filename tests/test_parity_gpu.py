@@ -317,8 +317,9 @@ def _oracle_view(oracle, cam, objs, draws, lights, depth, frames, taa_pcs, hiz_l
     return vis, dout, cnt, td, true_counts, hist, U[0], ldr
 
 
-@pytest.mark.parametrize("W,H", [(320, 180), (1920, 1080)])
-def test_view_run_matches_oracle(backend, oracle, W, H):
+@pytest.mark.parametrize("W,H,keep", [(320, 180, True), (1920, 1080, True), (1920, 1080, False), (200, 120, False),
+                                      (67, 45, True)])
+def test_view_run_matches_oracle(backend, oracle, W, H, keep):
     from ash_renderer_b200.host import TemporalAA
     cam, objs, draws, depth = _cull_scene(W, H, (8, 8, 8), seed=5)
     lights = synth.make_lights(256, extent=10.0, seed=5, center=(0.0, 2.0, 22.0))
@@ -339,12 +340,14 @@ def test_view_run_matches_oracle(backend, oracle, W, H):
         c.set_depth(depth)
         for f, pc in zip(frames, pcs):
             c.set_color(f, None)
-            c.view_run(_view_params(cam, len(objs), len(lights), levels, W, H, pc))
+            c.view_run(_view_params(cam, len(objs), len(lights), levels, W, H, pc,
+                                    stages=T.STAGE_ALL | (T.STAGE_KEEP_BLOOM if keep else 0)))
         assert np.array_equal(c.visibility(), vis) and c.visible_count() == cnt
         assert np.array_equal(c.draws_out(cnt), dout)
         _compare_tile_lists(c.tile_data(), td)
         _assert_half_images_equal(c.taa_out(), taa_ref, "taa")
-        _assert_half_images_equal(c.bloom_mip(0), bloom_ref, "bloom U_0")
+        if keep:
+            _assert_half_images_equal(c.bloom_mip(0), bloom_ref, "bloom U_0")
         d = np.abs(c.ldr8().astype(np.int16) - ldr_ref.astype(np.int16))
         assert d.max() <= 1
         st = c.stats()
