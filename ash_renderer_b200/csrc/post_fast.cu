@@ -29,33 +29,73 @@ __device__ __forceinline__ V3 unpack_rgb(uint2 t) { V4 v = unpack_rgba16f(t); re
 // No velocity buffer (PIN-12: velocity == 0 -> jitter-delta branch, uniform over the frame).
 // CTA = 32x32 pixels, 256 threads, thread = 1x4 strip.
 // =====================================================================================================
+// Safe-domain helpers (operands bounded by construction: fdiv_safe, ash_math.cuh)
+__device__ __forceinline__ V3 taa_tonemap_safe(V3 c) {      // c in [0, 65504]: 1 + c in [1, 65505]
+    return {fdiv_safe(c.x, fadd(1.0f, c.x)), fdiv_safe(c.y, fadd(1.0f, c.y)), fdiv_safe(c.z, fadd(1.0f, c.z))};
+}
+__device__ __forceinline__ V3 soft_threshold_safe(V3 c, float threshold) {   // bloom_threshold.frag:18-27
+    const float knee = 0.5f;
+    const float br = gmax(c.x, gmax(c.y, c.z));
+    float soft = fadd(fsub(br, threshold), knee);
+    soft = gclamp(soft, 0.0f, fmul(2.0f, knee));
+    soft = fdiv_safe(fmul(soft, soft), fadd(fmul(4.0f, knee), 0.00001f));      // [0,1] / 2.00001
+    float contrib = gmax(soft, fsub(br, threshold));
+    contrib = fdiv_safe(contrib, gmax(br, 0.00001f));                            // divisor in [1e-5, 65504]
+    return scale3(c, contrib);
+}
+
 __device__ __forceinline__ V3 clip_aabb_fast(V3 mn, V3 mx, V3 hist) {       // :64-77
     const V3 center = scale3(add3(mx, mn), 0.5f);
     const V3 half = adds3(scale3(sub3(mx, mn), 0.5f), 0.001f);
     const V3 delta = sub3(hist, center);
     // RN(|d|/h) > 1  <=>  |d| > h  for h >= 0.001 (a float above h is at least h + ulp(h) > h(1 + 2^-24))
     if (fabsf(delta.x) > half.x || fabsf(delta.y) > half.y || fabsf(delta.z) > half.z) {
-        const V3 v = div3(delta, half);
+        // tonemapped YCoCg: |delta| <= 3, half in [0.001, 2], 1 < maxv <= 3000: safe domain
+        const V3 v = {fdiv_safe(delta.x, half.x), fdiv_safe(delta.y, half.y), fdiv_safe(delta.z, half.z)};
         const float maxv = fmaxf(fmaxf(fabsf(v.x), fabsf(v.y)), fabsf(v.z));
-        return add3(center, divs3(delta, maxv));
+        return add3(center, v3(fdiv_safe(delta.x, maxv), fdiv_safe(delta.y, maxv), fdiv_safe(delta.z, maxv)));
     }
     return hist;
 }
 
-template <bool THRESH>
-__global__ void __launch_bounds__(256, 2)
+constexpr int kTaaTile = 32, kTaaHalo = kTaaTile + 2, kTaaTexels = kTaaHalo * kTaaHalo;   // 34 x 34 = 1156
+constexpr int kTaaLoads = (kTaaTexels + 255) / 256;                                      // 5 per thread
+
+// HIST_SMEM: |jitter delta| <= 0.99 px, so every history tap of a tile lies inside its 1-texel halo.
+template <bool THRESH, bool HIST_SMEM>
+__global__ void __launch_bounds__(256, 3)
 k_taa_fast(Tex16 cur, Tex16 hist, uint2* __restrict__ out, uint2* __restrict__ thr,
            AshTaaPushConstants pc, float threshold) {
-    __shared__ float4 s_nb[34][34];
+    __shared__ float4 s_nb[kTaaHalo][kTaaHalo];      // tonemapped YCoCg of `current`, tile + halo
+    __shared__ uint2  s_c[kTaaTile][kTaaTile];       // raw `current`, tile
+    __shared__ uint2  s_h[HIST_SMEM ? kTaaHalo : 1][HIST_SMEM ? kTaaHalo : 1];   // raw history, tile + halo
     const int W = cur.W, H = cur.H;
-    const int x0 = blockIdx.x * 32, y0 = blockIdx.y * 32;
+    const int x0 = blockIdx.x * kTaaTile, y0 = blockIdx.y * kTaaTile;
     const bool clamp_on = pc.params[1] > 0.5f;
-    if (clamp_on) {
-        for (int idx = threadIdx.x; idx < 34 * 34; idx += 256) {
-            const int r = idx / 34, c = idx - r * 34;
-            const int gx = min(max(x0 - 1 + c, 0), W - 1), gy = min(max(y0 - 1 + r, 0), H - 1);
-            const V3 s = rgb_to_ycocg(taa_tonemap(unpack_rgb(__ldg(cur.p + (size_t)gy * W + gx))));   // :120
-            s_nb[r][c] = make_float4(s.x, s.y, s.z, 0.0f);
+    {   // stage: all global loads of the CTA are issued here, back to back
+        uint2 tc[kTaaLoads], th[kTaaLoads];
+#pragma unroll
+        for (int it = 0; it < kTaaLoads; ++it) {
+            const int idx = threadIdx.x + it * 256;
+            if (idx < kTaaTexels) {
+                const int r = idx / kTaaHalo, c = idx - r * kTaaHalo;
+                const size_t g = (size_t)min(max(y0 - 1 + r, 0), H - 1) * W + min(max(x0 - 1 + c, 0), W - 1);   // CLAMP_TO_EDGE
+                tc[it] = __ldg(cur.p + g);
+                if (HIST_SMEM) th[it] = __ldg(hist.p + g);
+            }
+        }
+#pragma unroll
+        for (int it = 0; it < kTaaLoads; ++it) {
+            const int idx = threadIdx.x + it * 256;
+            if (idx < kTaaTexels) {
+                const int r = idx / kTaaHalo, c = idx - r * kTaaHalo;
+                if (HIST_SMEM) s_h[r][c] = th[it];
+                if (r >= 1 && r <= kTaaTile && c >= 1 && c <= kTaaTile) s_c[r - 1][c - 1] = tc[it];
+                if (clamp_on) {
+                    const V3 s = rgb_to_ycocg(taa_tonemap_safe(unpack_rgb(tc[it])));                  // :120
+                    s_nb[r][c] = make_float4(s.x, s.y, s.z, 0.0f);
+                }
+            }
         }
     }
     __syncthreads();
@@ -64,9 +104,9 @@ k_taa_fast(Tex16 cur, Tex16 hist, uint2* __restrict__ out, uint2* __restrict__ t
     if (x >= W || yb >= H) return;
 
     const float sw = pc.screen_params[0], sh = pc.screen_params[1];
-    const float u = fdiv(fadd((float)x, 0.5f), sw);                                        // :92
-    const float vx = fdiv(fsub(pc.jitter[0], pc.prev_jitter[0]), sw);                      // :97-99
-    const float vy = fdiv(fsub(pc.jitter[1], pc.prev_jitter[1]), sh);
+    const float u = fdiv_safe(fadd((float)x, 0.5f), sw);                                   // :92 (extent in [1, 32768])
+    const float vx = fdiv_safe(fsub(pc.jitter[0], pc.prev_jitter[0]), sw);                 // :97-99
+    const float vy = fdiv_safe(fsub(pc.jitter[1], pc.prev_jitter[1]), sh);
     const float hu = gclamp(fsub(u, vx), 0.0f, 1.0f);                                      // :102
     int hx0, hx1; float fx;
     bilinear_setup(hu, W, hx0, hx1, fx);
@@ -92,15 +132,22 @@ k_taa_fast(Tex16 cur, Tex16 hist, uint2* __restrict__ out, uint2* __restrict__ t
     for (int k = 0; k < 4; ++k) {
         const int y = yb + k;
         if (y >= H) break;
-        const float v = fdiv(fadd((float)y, 0.5f), sh);
+        const float v = fdiv_safe(fadd((float)y, 0.5f), sh);
         const float hv = gclamp(fsub(v, vy), 0.0f, 1.0f);
         int hy0, hy1; float fy;
         bilinear_setup(hv, H, hy0, hy1, fy);
-        const V3 c = unpack_rgb(__ldg(cur.p + (size_t)y * W + x));                         // :105 (centre tap == texel)
+        const V3 c = unpack_rgb(s_c[4 * ty + k][tx]);                                      // :105 (centre tap == texel)
         V3 h;                                                                              // :108 bilinear history
         {
-            const V3 a = unpack_rgb(__ldg(hist.p + (size_t)hy0 * W + hx0)), b = unpack_rgb(__ldg(hist.p + (size_t)hy0 * W + hx1));
-            const V3 cc = unpack_rgb(__ldg(hist.p + (size_t)hy1 * W + hx0)), d = unpack_rgb(__ldg(hist.p + (size_t)hy1 * W + hx1));
+            V3 a, b, cc, d;
+            if (HIST_SMEM) {
+                const int cx0 = hx0 - (x0 - 1), cx1 = hx1 - (x0 - 1), ry0 = hy0 - (y0 - 1), ry1 = hy1 - (y0 - 1);
+                a = unpack_rgb(s_h[ry0][cx0]); b = unpack_rgb(s_h[ry0][cx1]);
+                cc = unpack_rgb(s_h[ry1][cx0]); d = unpack_rgb(s_h[ry1][cx1]);
+            } else {
+                a = unpack_rgb(__ldg(hist.p + (size_t)hy0 * W + hx0)); b = unpack_rgb(__ldg(hist.p + (size_t)hy0 * W + hx1));
+                cc = unpack_rgb(__ldg(hist.p + (size_t)hy1 * W + hx0)); d = unpack_rgb(__ldg(hist.p + (size_t)hy1 * W + hx1));
+            }
             const float ify = fsub(1.0f, fy);
             const V3 top = {fadd(fmul(a.x, ifx), fmul(b.x, fx)), fadd(fmul(a.y, ifx), fmul(b.y, fx)), fadd(fmul(a.z, ifx), fmul(b.z, fx))};
             const V3 bot = {fadd(fmul(cc.x, ifx), fmul(d.x, fx)), fadd(fmul(cc.y, ifx), fmul(d.y, fx)), fadd(fmul(cc.z, ifx), fmul(d.z, fx))};
@@ -114,14 +161,14 @@ k_taa_fast(Tex16 cur, Tex16 hist, uint2* __restrict__ out, uint2* __restrict__ t
             const V3 ctr = scale3(add3(mn, mx), 0.5f), ext = scale3(sub3(mx, mn), 0.5f);   // :132-135
             mn = sub3(ctr, scale3(ext, 1.25f));
             mx = add3(ctr, scale3(ext, 1.25f));
-            const V3 hy = rgb_to_ycocg(taa_tonemap(h));
-            h = taa_untonemap(ycocg_to_rgb(clip_aabb_fast(mn, mx, hy)));                   // :140-141
+            const V3 hy = rgb_to_ycocg(taa_tonemap_safe(h));
+            h = taa_untonemap(ycocg_to_rgb(clip_aabb_fast(mn, mx, hy)));                   // :140-141 (divisor may reach 0: guarded div)
         }
         const uint2 o = pack_rgba16f(fadd(fmul(c.x, ib), fmul(h.x, blend)), fadd(fmul(c.y, ib), fmul(h.y, blend)),
                                      fadd(fmul(c.z, ib), fmul(h.z, blend)), 1.0f);         // mix(), :159
         out[(size_t)y * W + x] = o;
         if (THRESH) {                      // bloom threshold of the resolved texel as stored (fp16)
-            const V3 b = soft_threshold(unpack_rgb(o), threshold);
+            const V3 b = soft_threshold_safe(unpack_rgb(o), threshold);
             thr[(size_t)y * W + x] = pack_rgba16f(b.x, b.y, b.z, 1.0f);
         }
     }
@@ -132,42 +179,41 @@ cudaError_t launch_taa_fast(const void* cur, const void* hist, void* out, void* 
     const int W = (int)pc.screen_params[0], H = (int)pc.screen_params[1];
     const Tex16 c{static_cast<const uint2*>(cur), W, H}, h{static_cast<const uint2*>(hist), W, H};
     const dim3 grid((W + 31) / 32, (H + 31) / 32);
-    if (thr_or_null) {
-        Timed timed(L, ASH_KERNEL_TAA_THRESHOLD);
-        k_taa_fast<true><<<grid, 256, 0, L.s>>>(c, h, static_cast<uint2*>(out), static_cast<uint2*>(thr_or_null), pc, threshold);
-    } else {
-        Timed timed(L, ASH_KERNEL_TAA);
-        k_taa_fast<false><<<grid, 256, 0, L.s>>>(c, h, static_cast<uint2*>(out), nullptr, pc, threshold);
-    }
+    const bool in_halo = fabsf(pc.jitter[0] - pc.prev_jitter[0]) <= 0.99f && fabsf(pc.jitter[1] - pc.prev_jitter[1]) <= 0.99f;
+    uint2* o = static_cast<uint2*>(out);
+    uint2* t = static_cast<uint2*>(thr_or_null);
+    Timed timed(L, thr_or_null ? ASH_KERNEL_TAA_THRESHOLD : ASH_KERNEL_TAA);
+    if (t) { if (in_halo) k_taa_fast<true, true><<<grid, 256, 0, L.s>>>(c, h, o, t, pc, threshold);
+             else         k_taa_fast<true, false><<<grid, 256, 0, L.s>>>(c, h, o, t, pc, threshold); }
+    else   { if (in_halo) k_taa_fast<false, true><<<grid, 256, 0, L.s>>>(c, h, o, t, pc, threshold);
+             else         k_taa_fast<false, false><<<grid, 256, 0, L.s>>>(c, h, o, t, pc, threshold); }
     return cudaGetLastError();
 }
 
 // =====================================================================================================
 // Bloom downsample, source extent == 2 x destination extent (bloom_downsample.frag:16-108)
-// CTA = 32x8 destination pixels; source tile 66x18 texels staged in shared memory as fp16.
+// One thread = one destination pixel = one 4x4 source window, fetched with 12 independent loads
+// (8 B, 16 B, 8 B per row) issued back to back; neighbouring threads share texels through L1.
 // =====================================================================================================
 __global__ void __launch_bounds__(256)
 k_downsample_fast(const uint2* __restrict__ src, int sw, int sh, uint2* __restrict__ dst, int dw, int dh) {
-    __shared__ __align__(16) uint2 s_t[18][66];
-    const int x0 = blockIdx.x * 32, y0 = blockIdx.y * 8;
-    for (int idx = threadIdx.x; idx < 18 * 66; idx += 256) {
-        const int r = idx / 66, c = idx - r * 66;
-        const int gx = min(max(2 * x0 - 1 + c, 0), sw - 1), gy = min(max(2 * y0 - 1 + r, 0), sh - 1);   // CLAMP_TO_EDGE
-        s_t[r][c] = __ldg(src + (size_t)gy * sw + gx);
-    }
-    __syncthreads();
-    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
-    const int x = x0 + tx, y = y0 + ty;
+    const int x = blockIdx.x * 32 + (threadIdx.x & 31), y = blockIdx.y * 8 + (threadIdx.x >> 5);
     if (x >= dw || y >= dh) return;
-
-    // 4x4 window: window (i,j) = source texel (2x-1+i, 2y-1+j)
+    // 4x4 window: window (i,j) = source texel (2x-1+i, 2y-1+j), CLAMP_TO_EDGE
+    const int xl = max(2 * x - 1, 0), xr = min(2 * x + 2, sw - 1);
+    uint2 e0[4], e3[4]; uint4 m[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        const uint2* row = src + (size_t)min(max(2 * y - 1 + j, 0), sh - 1) * sw;
+        e0[j] = __ldg(row + xl);
+        m[j] = __ldg(reinterpret_cast<const uint4*>(row + 2 * x));       // texels 2x, 2x+1 (16-byte aligned: sw is even)
+        e3[j] = __ldg(row + xr);
+    }
     V3 hs[4][3];     // hs[j][i] = t[j][i] + t[j][i+1]            (= 2 * horizontal lerp at 1/2)
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
-        const uint4 p0 = *reinterpret_cast<const uint4*>(&s_t[2 * ty + j][2 * tx]);
-        const uint4 p1 = *reinterpret_cast<const uint4*>(&s_t[2 * ty + j][2 * tx + 2]);
-        const V3 t0 = unpack_rgb(make_uint2(p0.x, p0.y)), t1 = unpack_rgb(make_uint2(p0.z, p0.w));
-        const V3 t2 = unpack_rgb(make_uint2(p1.x, p1.y)), t3 = unpack_rgb(make_uint2(p1.z, p1.w));
+        const V3 t0 = unpack_rgb(e0[j]), t1 = unpack_rgb(make_uint2(m[j].x, m[j].y));
+        const V3 t2 = unpack_rgb(make_uint2(m[j].z, m[j].w)), t3 = unpack_rgb(e3[j]);
         hs[j][0] = add3(t0, t1); hs[j][1] = add3(t1, t2); hs[j][2] = add3(t2, t3);
     }
     V3 res = {0.0f, 0.0f, 0.0f};
@@ -176,7 +222,7 @@ k_downsample_fast(const uint2* __restrict__ src, int sw, int sh, uint2* __restri
     auto tap = [&](int i, int j, float wt) {
         const V3 t4 = add3(hs[j][i], hs[j + 1][i]);
         const float luma4 = fadd(fadd(fmul(t4.x, 0.2126f), fmul(t4.y, 0.7152f)), fmul(t4.z, 0.0722f));
-        const float w = fdiv(1.0f, fma_exact(luma4, 0.25f, 1.0f));          // 1 / (1 + luma)        :87-101
+        const float w = fdiv_safe(1.0f, fma_exact(luma4, 0.25f, 1.0f));     // 1 / (1 + luma), luma in [0, 65504]   :87-101
         const float k = 0.25f * wt;                                          // power of two
         res = {fma_exact(fmul(t4.x, w), k, res.x), fma_exact(fmul(t4.y, w), k, res.y), fma_exact(fmul(t4.z, w), k, res.z)};
         sum = fma_exact(w, wt, sum);
@@ -184,7 +230,8 @@ k_downsample_fast(const uint2* __restrict__ src, int sw, int sh, uint2* __restri
     tap(1, 1, 0.25f);                                                        // centre
     tap(0, 0, 0.0625f); tap(2, 0, 0.0625f); tap(0, 2, 0.0625f); tap(2, 2, 0.0625f);   // a b c d   :25-28
     tap(0, 1, 0.125f);  tap(2, 1, 0.125f);  tap(1, 0, 0.125f);  tap(1, 2, 0.125f);    // e f g h   :31-34
-    dst[(size_t)y * dw + x] = pack_rgba16f(fdiv(res.x, sum), fdiv(res.y, sum), fdiv(res.z, sum), 1.0f);   // :107
+    // sum in [1.5e-5, 1], res in [0, 65504]: safe domain                                          :107
+    dst[(size_t)y * dw + x] = pack_rgba16f(fdiv_safe(res.x, sum), fdiv_safe(res.y, sum), fdiv_safe(res.z, sum), 1.0f);
 }
 
 cudaError_t launch_bloom_downsample_fast(const void* src, uint32_t sw, uint32_t sh, void* dst, uint32_t dw,
@@ -284,16 +331,36 @@ k_upsample_fast(const uint2* __restrict__ src, int sw, int sh, uint2* __restrict
                 const uint2* __restrict__ hdr, uint32_t* __restrict__ ldr8, AshPostProcessPushConstants pc) {
     __shared__ uint2 s_t[20][20];
     const int i0 = blockIdx.x * 16, j0 = blockIdx.y * 16;
-    for (int idx = threadIdx.x; idx < 400; idx += 256) {
-        const int r = idx / 20, c = idx - r * 20;
-        const int gx = min(max(i0 - 2 + c, 0), sw - 1), gy = min(max(j0 - 2 + r, 0), sh - 1);          // CLAMP_TO_EDGE
-        s_t[r][c] = __ldg(src + (size_t)gy * sw + gx);
-    }
-    __syncthreads();
     const int ti = threadIdx.x & 15, tj = threadIdx.x >> 4;
     const int i = i0 + ti, j = j0 + tj;
-    if (i >= sw || j >= sh) return;
+    const bool active = i < sw && j < sh;
     const int dw = 2 * sw;
+    // every global load of the thread is issued up front: the source tile and its own 2x2 destination block
+    uint2 st[2];
+#pragma unroll
+    for (int it = 0; it < 2; ++it) {
+        const int idx = threadIdx.x + it * 256;
+        if (idx < 400) {
+            const int r = idx / 20, c = idx - r * 20;
+            st[it] = __ldg(src + (size_t)min(max(j0 - 2 + r, 0), sh - 1) * sw + min(max(i0 - 2 + c, 0), sw - 1));   // CLAMP_TO_EDGE
+        }
+    }
+    uint4 dpre[2], cpre[2];
+    if (active) {
+#pragma unroll
+        for (int py = 0; py < 2; ++py) {
+            const size_t o = (size_t)(2 * j + py) * dw + 2 * i;               // 16-byte aligned pair of texels
+            dpre[py] = *reinterpret_cast<const uint4*>(dst + o);
+            if (TONEMAP) cpre[py] = __ldg(reinterpret_cast<const uint4*>(hdr + o));
+        }
+    }
+#pragma unroll
+    for (int it = 0; it < 2; ++it) {
+        const int idx = threadIdx.x + it * 256;
+        if (idx < 400) s_t[idx / 20][idx % 20] = st[it];
+    }
+    __syncthreads();
+    if (!active) return;
     const float k = fmul(intensity, 0.00390625f);                 // (R16 / 256) * intensity == R16 * (intensity / 256)
     const float inv_gamma = TONEMAP ? __fdividef(1.0f, pc.gamma) : 0.0f;
 
@@ -315,13 +382,13 @@ k_upsample_fast(const uint2* __restrict__ src, int sw, int sh, uint2* __restrict
 #pragma unroll
     for (int py = 0; py < 2; ++py) {
         const size_t o = (size_t)(2 * j + py) * dw + 2 * i;                   // 16-byte aligned pair of texels
-        const uint4 d = *reinterpret_cast<const uint4*>(dst + o);
+        const uint4 d = dpre[py];
         const V3 d0 = unpack_rgb(make_uint2(d.x, d.y)), d1 = unpack_rgb(make_uint2(d.z, d.w));
         const uint2 u0 = pack_rgba16f(fadd(up[py][0].x, d0.x), fadd(up[py][0].y, d0.y), fadd(up[py][0].z, d0.z), 1.0f);
         const uint2 u1 = pack_rgba16f(fadd(up[py][1].x, d1.x), fadd(up[py][1].y, d1.y), fadd(up[py][1].z, d1.z), 1.0f);
         if (STORE_U) *reinterpret_cast<uint4*>(dst + o) = make_uint4(u0.x, u0.y, u1.x, u1.y);
         if (TONEMAP) {
-            const uint4 c = __ldg(reinterpret_cast<const uint4*>(hdr + o));
+            const uint4 c = cpre[py];
             const uint32_t a8 = tonemap_pack8(unpack_rgb(make_uint2(c.x, c.y)), unpack_rgb(u0), pc, inv_gamma);
             const uint32_t b8 = tonemap_pack8(unpack_rgb(make_uint2(c.z, c.w)), unpack_rgb(u1), pc, inv_gamma);
             *reinterpret_cast<uint2*>(ldr8 + o) = make_uint2(a8, b8);
