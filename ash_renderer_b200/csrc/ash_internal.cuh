@@ -72,6 +72,8 @@ struct ashcuda_ctx {
     int          device = 0;
     cudaStream_t stream = nullptr;
     bool         own_stream = false;
+    cudaStream_t front_stream = nullptr;      // view_run: Hi-Z + cull + light cull run here (fork / join by events)
+    cudaEvent_t  ev_fork = nullptr, ev_join = nullptr;
     uint32_t     W = 0, H = 0, tiles_x = 0, tiles_y = 0;
     AshCudaConfig cfg{};
     std::string  err;

@@ -71,6 +71,7 @@ void ashcuda_default_config(AshCudaConfig* cfg) {
     cfg->bloom_mips = 5;                            // features/bloom.rs:29
     cfg->enable_post = 1;
     cfg->srgb_encode = 0;
+    cfg->concurrent_frontend = 1;
 }
 
 const char* ashcuda_last_error(ashcuda_ctx* ctx) {
@@ -89,6 +90,10 @@ void ashcuda_destroy(ashcuda_ctx* c) {
     for (void* p : owned) if (p) cudaFree(p);
     for (uint32_t k = 1; k <= ASH_MAX_BLOOM_MIPS; ++k) if (c->bloom.d[k]) cudaFree(c->bloom.d[k]);
     c->prof.release_all();
+    if (c->front_stream) cudaStreamSynchronize(c->front_stream);
+    if (c->ev_fork) cudaEventDestroy(c->ev_fork);
+    if (c->ev_join) cudaEventDestroy(c->ev_join);
+    if (c->front_stream) cudaStreamDestroy(c->front_stream);
     if (c->own_stream && c->stream) cudaStreamDestroy(c->stream);
     delete c;
 }
@@ -99,6 +104,9 @@ static int create_impl(ashcuda_ctx* c) {
     ASH_CUDA(c, cudaSetDevice(c->device));
     ASH_CUDA(c, cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
     c->own_stream = true;
+    ASH_CUDA(c, cudaStreamCreateWithFlags(&c->front_stream, cudaStreamNonBlocking));
+    ASH_CUDA(c, cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming));
+    ASH_CUDA(c, cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming));
     // ---- pyramid geometry (PIN-3/4)
     Pyramid& p = c->pyr;
     p.levels = hiz_level_count(W, H);
@@ -138,7 +146,7 @@ static int create_impl(ashcuda_ctx* c) {
     ASH_CUDA(c, dmalloc(&c->lights_owned, L * sizeof(AshGpuLight)));
     ASH_CUDA(c, dmalloc(&c->camera_dev, sizeof(AshCullingCameraData)));
     ASH_CUDA(c, dmalloc(&c->cand, L * sizeof(LightCand)));
-    ASH_CUDA(c, dmalloc(&c->cand_idx, L * 4));
+    ASH_CUDA(c, dmalloc(&c->cand_idx, L * 16));   // CandZ records (light_cull.cu), 16 B each
     ASH_CUDA(c, dmalloc(&c->cand_count, 4));
     ASH_CUDA(c, dmalloc(&c->tile_data, tiles * ASH_TILE_STRIDE * 4));    // light_culling_pipeline.rs:55-56
     ASH_CUDA(c, dmalloc(&c->stats, sizeof(AshViewStats)));
@@ -424,14 +432,9 @@ int ashcuda_tonemap(ashcuda_ctx* c, const AshPostProcessPushConstants* pc) {
     return ASH_OK;
 }
 
-int ashcuda_view_run(ashcuda_ctx* c, const AshCudaViewParams* vp) {
-    if (!c || !vp) return fail(c, ASH_ERR_INVALID, "view_run: null");
+static int view_post(ashcuda_ctx* c, const AshCudaViewParams* vp) {
     int rc = ASH_OK;
     const uint32_t st = vp->stages;
-    if (st & (ASH_STAGE_LIGHTS)) { rc = ashcuda_set_camera(c, &vp->camera); if (rc) return rc; }
-    if (st & ASH_STAGE_HIZ) { rc = ashcuda_hiz_build(c); if (rc) return rc; }
-    if (st & ASH_STAGE_CULL) { rc = ashcuda_occlusion_cull(c, &vp->cull); if (rc) return rc; }
-    if (st & ASH_STAGE_LIGHTS) { rc = ashcuda_light_cull(c, &vp->light); if (rc) return rc; }
     // ---- post chain: TAA+threshold fused, bloom chain, last upsample + tonemap fused (same results
     //      as the staged calls; falls back to them stage by stage when a fast kernel does not apply)
     const bool want_bloom = (st & ASH_STAGE_BLOOM) != 0;
@@ -462,6 +465,42 @@ int ashcuda_view_run(ashcuda_ctx* c, const AshCudaViewParams* vp) {
         }
     }
     if ((st & ASH_STAGE_TONEMAP) && !tonemap_done) { rc = ashcuda_tonemap(c, &vp->post); if (rc) return rc; }
+    return ASH_OK;
+}
+
+int ashcuda_view_run(ashcuda_ctx* c, const AshCudaViewParams* vp) {
+    if (!c || !vp) return fail(c, ASH_ERR_INVALID, "view_run: null");
+    int rc = ASH_OK;
+    const uint32_t st = vp->stages;
+    // ---- front end (Hi-Z -> cull, light cull): independent of the post chain of the same view, so it
+    //      is forked onto the context's second stream and joined before view_run returns control of
+    //      the main stream (inputs uploaded earlier on the main stream are ordered by the fork event)
+    const bool front = (st & (ASH_STAGE_HIZ | ASH_STAGE_CULL | ASH_STAGE_LIGHTS)) != 0;
+    const bool post = (st & (ASH_STAGE_TAA | ASH_STAGE_BLOOM | ASH_STAGE_TONEMAP)) != 0;
+    const bool fork = front && post && c->cfg.concurrent_frontend && c->front_stream;
+    cudaStream_t main_stream = c->stream;
+    if (fork) {
+        ASH_CUDA(c, cudaSetDevice(c->device));
+        ASH_CUDA(c, cudaEventRecord(c->ev_fork, main_stream));
+        ASH_CUDA(c, cudaStreamWaitEvent(c->front_stream, c->ev_fork, 0));
+        c->stream = c->front_stream;
+    }
+    if (st & (ASH_STAGE_LIGHTS)) rc = ashcuda_set_camera(c, &vp->camera);
+    if (!rc && (st & ASH_STAGE_HIZ)) rc = ashcuda_hiz_build(c);
+    if (!rc && (st & ASH_STAGE_CULL)) rc = ashcuda_occlusion_cull(c, &vp->cull);
+    if (!rc && (st & ASH_STAGE_LIGHTS)) rc = ashcuda_light_cull(c, &vp->light);
+    if (fork) {
+        cudaError_t e = cudaEventRecord(c->ev_join, c->front_stream);
+        c->stream = main_stream;
+        if (!rc && e != cudaSuccess) { c->err = std::string("view_run: ") + cudaGetErrorString(e); rc = ASH_ERR_DEVICE; }
+    }
+    if (rc) return rc;
+    rc = view_post(c, vp);
+    if (fork) {                                                              // join (also on the error path)
+        cudaError_t e = cudaStreamWaitEvent(c->stream, c->ev_join, 0);
+        if (!rc && e != cudaSuccess) { c->err = std::string("view_run: ") + cudaGetErrorString(e); rc = ASH_ERR_DEVICE; }
+    }
+    if (rc) return rc;
     ASH_CUDA(c, cudaMemcpyAsync(&c->stats->view_id, &vp->view_id, 4, cudaMemcpyHostToDevice, c->stream));
     return ASH_OK;
 }

@@ -39,7 +39,6 @@ k_depth_pyramid(Pyramid p, uint32_t* __restrict__ tile_minmax, uint32_t tiles_x,
                 uint32_t* __restrict__ depth_range, uint32_t* __restrict__ ticket) {
     __shared__ float    s4[4][4];
     __shared__ uint32_t s_mn[8], s_mx[8];
-    __shared__ bool     s_last;
 
     const uint32_t W = p.w[0], H = p.h[0];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -160,31 +159,42 @@ k_depth_pyramid(Pyramid p, uint32_t* __restrict__ tile_minmax, uint32_t tiles_x,
         }
     }
 
-    // ---- tail: the last CTA to finish builds the remaining levels out of L2
-    if (p.levels - 1 <= F) return;
-    __threadfence();
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        const uint32_t t = atomicAdd(ticket, 1u);
-        s_last = (t == gridDim.x * gridDim.y - 1u);
+}
+
+// Levels fast_levels+1 .. levels-1 (a few thousand texels in total): one CTA; the first of them is
+// gathered from L2 into shared memory and the rest never leave it, except for their stores.
+constexpr int kTailCap = 4096;     // texels of the first tail level that fit the shared-memory path
+__global__ void __launch_bounds__(1024)
+k_pyramid_tail(Pyramid p) {
+    __shared__ float s_a[kTailCap], s_b[kTailCap / 4 + 1];
+    const int F = p.fast_levels;
+    const float* src_g = (F == 0) ? p.mip0 : p.mips + p.off[F];
+    int sw = (int)p.w[F], sh = (int)p.h[F];
+    const bool in_smem = sw * sh <= kTailCap;
+    float* cur = s_a; float* nxt = s_b;
+    if (in_smem) {
+        for (int idx = threadIdx.x; idx < sw * sh; idx += blockDim.x) cur[idx] = __ldcg(src_g + idx);
+        __syncthreads();
     }
-    __syncthreads();
-    if (!s_last) return;
-    __threadfence();
     for (int L = F + 1; L < p.levels; ++L) {
-        const float* src = (L == 1) ? p.mip0 : p.mips + p.off[L - 1];
         float* dst = p.mips + p.off[L];
-        const int sw = (int)p.w[L - 1], sh = (int)p.h[L - 1], dw = (int)p.w[L], dh = (int)p.h[L];
+        const int dw = (int)p.w[L], dh = (int)p.h[L];
         for (int idx = threadIdx.x; idx < dw * dh; idx += blockDim.x) {
             const int x = idx % dw, y = idx / dw;
             const int i0 = min(2 * x, sw - 1), i1 = min(2 * x + 1, sw - 1);      // PIN-5 edge clamp
             const int j0 = min(2 * y, sh - 1), j1 = min(2 * y + 1, sh - 1);
-            dst[idx] = hiz_max4(__ldcg(src + (size_t)j0 * sw + i0), __ldcg(src + (size_t)j0 * sw + i1),
-                                __ldcg(src + (size_t)j1 * sw + i0), __ldcg(src + (size_t)j1 * sw + i1));
+            float v;
+            if (in_smem) v = hiz_max4(cur[j0 * sw + i0], cur[j0 * sw + i1], cur[j1 * sw + i0], cur[j1 * sw + i1]);
+            else v = hiz_max4(__ldcg(src_g + (size_t)j0 * sw + i0), __ldcg(src_g + (size_t)j0 * sw + i1),
+                              __ldcg(src_g + (size_t)j1 * sw + i0), __ldcg(src_g + (size_t)j1 * sw + i1));
+            dst[idx] = v;
+            if (in_smem) nxt[idx] = v;
         }
         __syncthreads();
+        if (in_smem) { float* t = cur; cur = nxt; nxt = t; }
+        else src_g = dst;
+        sw = dw; sh = dh;
     }
-    if (threadIdx.x == 0) *ticket = 0u;
 }
 
 cudaError_t launch_depth_pyramid(const Pyramid& p, uint32_t* tile_minmax, uint32_t tiles_x,
@@ -194,6 +204,10 @@ cudaError_t launch_depth_pyramid(const Pyramid& p, uint32_t* tile_minmax, uint32
     Timed timed(L, ASH_KERNEL_DEPTH_PYRAMID);
     if (vec) k_depth_pyramid<true><<<grid, 256, 0, L.s>>>(p, tile_minmax, tiles_x, depth_range, ticket);
     else     k_depth_pyramid<false><<<grid, 256, 0, L.s>>>(p, tile_minmax, tiles_x, depth_range, ticket);
+    if (p.levels - 1 > p.fast_levels) {
+        ++*L.launches;                       // accounted to the same class as the main pass
+        k_pyramid_tail<<<1, 1024, 0, L.s>>>(p);
+    }
     return cudaGetLastError();
 }
 

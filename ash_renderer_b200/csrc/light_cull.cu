@@ -23,6 +23,11 @@ namespace ash {
 constexpr int kPrepassThreads = 1024;
 constexpr int kTileWarps = 16;
 
+// One candidate = 32 bytes: {view x, y, z, radius} {dot((0,0,-1),c), dot((0,0,1),c), light index bits, 0}.
+// The two z dots are the tile-independent parts of planes 4/5 (:96-97, :104), evaluated exactly as the
+// shader does (so non-finite light positions behave identically) once per light instead of once per tile.
+struct CandZ { float zneg, zpos; uint32_t index, pad; };
+
 __global__ void __launch_bounds__(kPrepassThreads)
 k_light_prepass(const AshGpuLight* __restrict__ lights, uint32_t light_count,
                 const AshCullingCameraData* __restrict__ cam, uint32_t* __restrict__ depth_range,
@@ -36,38 +41,65 @@ k_light_prepass(const AshGpuLight* __restrict__ lights, uint32_t light_count,
     // uint order == float order only for non-negative, non-NaN depth (PIN-2); otherwise keep all
     const bool sane = gmx <= 0x7F800000u && gmn <= gmx;
     const float gmin_d = __uint_as_float(gmn), gmax_d = __uint_as_float(gmx);
+    CandZ* candz = reinterpret_cast<CandZ*>(cand_idx);
     if (threadIdx.x == 0) s_base = 0;
     __syncthreads();
-    for (uint32_t start = 0; start < light_count; start += kPrepassThreads) {
-        const uint32_t i = start + threadIdx.x;
-        bool keep = false;
-        LightCand c = {0.f, 0.f, 0.f, 0.f};
-        if (i < light_count) {
-            const float4 pos = __ldg(reinterpret_cast<const float4*>(lights[i].position));
-            const float enabled = __ldg(&lights[i].params[3]);
-            const V4 pv = mul4(view, pos.x, pos.y, pos.z, 1.0f);                 // :181
-            c = {pv.x, pv.y, pv.z, pos.w};
-            keep = !(enabled < 0.5f);                                            // :178
-            if (keep && sane) {
-                // planes 4/5 with the global slab: dist = dot((0,0,-+1), c) + w, reject if < -r
-                const float d4 = fadd(dot3(v3(0.0f, 0.0f, -1.0f), v3(c.x, c.y, c.z)), -gmin_d);
-                const float d5 = fadd(dot3(v3(0.0f, 0.0f, 1.0f), v3(c.x, c.y, c.z)), gmax_d);
-                if (d4 < -c.r || d5 < -c.r) keep = false;
+    // blocked assignment keeps ascending light order with ONE block scan per 32K lights:
+    // thread t owns lights [start + t*chunk, start + (t+1)*chunk), chunk <= 32 (keep bits in a register)
+    for (uint32_t start = 0; start < light_count; start += kPrepassThreads * 32u) {
+        const uint32_t span = min(light_count - start, kPrepassThreads * 32u);
+        const uint32_t chunk = (span + kPrepassThreads - 1) / kPrepassThreads;
+        const uint32_t first = start + threadIdx.x * chunk;
+        uint32_t keep_bits = 0;
+        for (uint32_t j = 0; j < chunk; ++j) {
+            const uint32_t i = first + j;
+            if (i < start + span) {
+                const float4 pos = __ldg(reinterpret_cast<const float4*>(lights[i].position));
+                const float enabled = __ldg(&lights[i].params[3]);
+                bool keep = !(enabled < 0.5f);                                           // :178
+                if (keep && sane) {
+                    const float z = mrow(view.c[0].z, view.c[1].z, view.c[2].z, view.c[3].z, pos.x, pos.y, pos.z, 1.0f);
+                    const float x = mrow(view.c[0].x, view.c[1].x, view.c[2].x, view.c[3].x, pos.x, pos.y, pos.z, 1.0f);
+                    const float y = mrow(view.c[0].y, view.c[1].y, view.c[2].y, view.c[3].y, pos.x, pos.y, pos.z, 1.0f);
+                    // planes 4/5 with the global slab: a light failing them here fails them in every tile
+                    const float d4 = fadd(dot3(v3(0.0f, 0.0f, -1.0f), v3(x, y, z)), -gmin_d);
+                    const float d5 = fadd(dot3(v3(0.0f, 0.0f, 1.0f), v3(x, y, z)), gmax_d);
+                    if (d4 < -pos.w || d5 < -pos.w) keep = false;
+                }
+                if (keep) keep_bits |= 1u << j;
             }
         }
-        const uint32_t ballot = __ballot_sync(0xFFFFFFFFu, keep);
-        if (lane == 0) s_warp[warp] = __popc(ballot);
+        // block-wide exclusive scan of the per-thread counts
+        const uint32_t mine = __popc(keep_bits);
+        uint32_t incl = mine;
+#pragma unroll
+        for (int s = 1; s < 32; s <<= 1) {
+            const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, incl, s);
+            if (lane >= s) incl += t;
+        }
+        if (lane == 31) s_warp[warp] = incl;
         __syncthreads();
         uint32_t off = s_base, total = 0;
+#pragma unroll
         for (int w = 0; w < kPrepassThreads / 32; ++w) {
             const uint32_t n = s_warp[w];
             if (w < warp) off += n;
             total += n;
         }
-        if (keep) {
-            const uint32_t slot = off + __popc(ballot & ((1u << lane) - 1u));
-            *reinterpret_cast<float4*>(cand + slot) = make_float4(c.x, c.y, c.z, c.r);
-            cand_idx[slot] = i;
+        uint32_t slot = off + incl - mine;
+        while (keep_bits) {
+            const uint32_t j = __ffs(keep_bits) - 1;
+            keep_bits &= keep_bits - 1;
+            const uint32_t i = first + j;
+            const float4 pos = __ldg(reinterpret_cast<const float4*>(lights[i].position));
+            const V4 pv = mul4(view, pos.x, pos.y, pos.z, 1.0f);                         // :181
+            *reinterpret_cast<float4*>(cand + slot) = make_float4(pv.x, pv.y, pv.z, pos.w);
+            CandZ cz;
+            cz.zneg = dot3(v3(0.0f, 0.0f, -1.0f), v3(pv.x, pv.y, pv.z));
+            cz.zpos = dot3(v3(0.0f, 0.0f, 1.0f), v3(pv.x, pv.y, pv.z));
+            cz.index = i; cz.pad = 0;
+            *reinterpret_cast<uint4*>(candz + slot) = *reinterpret_cast<const uint4*>(&cz);
+            ++slot;
         }
         __syncthreads();
         if (threadIdx.x == 0) s_base += total;
@@ -138,14 +170,14 @@ k_light_tiles(const AshCullingCameraData* __restrict__ cam, uint32_t W, uint32_t
         uint32_t li = 0;
         if (j < nc) {
             const float4 q = __ldg(reinterpret_cast<const float4*>(cand) + j);
-            li = __ldg(cand_idx + j);
+            const uint4 zq = __ldg(reinterpret_cast<const uint4*>(cand_idx) + j);      // CandZ
+            li = zq.z;
             const V3 c = {q.x, q.y, q.z};
             const float nr = -q.w;
-            // sphereInFrustum, :101-109: dist = dot(plane.xyz, c) + plane.w ; reject if dist < -radius
-            pass = !(fadd(dot3(n[0], c), 0.0f) < nr) && !(fadd(dot3(n[1], c), 0.0f) < nr) &&
-                   !(fadd(dot3(n[2], c), 0.0f) < nr) && !(fadd(dot3(n[3], c), 0.0f) < nr) &&
-                   !(fadd(dot3(v3(0.0f, 0.0f, -1.0f), c), w4) < nr) &&
-                   !(fadd(dot3(v3(0.0f, 0.0f, 1.0f), c), w5) < nr);
+            // sphereInFrustum, :101-109: dist = dot(plane.xyz, c) + plane.w ; reject if dist < -radius.
+            // Side planes have w = 0: (d + 0.0) < nr  <=>  d < nr.  Planes 4/5: the dot is precomputed per light.
+            pass = !(dot3(n[0], c) < nr) && !(dot3(n[1], c) < nr) && !(dot3(n[2], c) < nr) && !(dot3(n[3], c) < nr) &&
+                   !(fadd(__uint_as_float(zq.x), w4) < nr) && !(fadd(__uint_as_float(zq.y), w5) < nr);
         }
         const uint32_t ballot = __ballot_sync(0xFFFFFFFFu, pass);
         if (pass) {

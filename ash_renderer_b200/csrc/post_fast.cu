@@ -311,18 +311,22 @@ __device__ __forceinline__ V3 up_combine(const UpH& h) {
     return r;
 }
 
-__device__ __forceinline__ float aces_fast(float x) {                        // tonemapping.frag:20-27, 8-bit output only
-    const float n = x * (2.51f * x + 0.03f), d = x * (2.43f * x + 0.59f) + 0.14f;
-    return __saturatef(__fdividef(n, d));
+// ---- tonemapping.frag:20-48 for the 8-bit target only (PIN-11: within 1 LSB of the reference): FMA contraction,
+//      MUFU reciprocal / lg2 / ex2.  Not used for any fp16 / fp32 output.
+__device__ __forceinline__ float lg2_ftz(float x) { float r; asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+__device__ __forceinline__ float ex2_ftz(float x) { float r; asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+__device__ __forceinline__ float rcp_ftz(float x) { float r; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+__device__ __forceinline__ uint32_t tonemap8(float c, float bloom, const AshPostProcessPushConstants& pc, float inv_gamma) {
+    const float x = __fmaf_rn(bloom, pc.bloom_intensity, c) * pc.exposure;              // :38, :41
+    const float n = x * __fmaf_rn(2.51f, x, 0.03f);                                      // :20-27
+    const float d = __fmaf_rn(x, __fmaf_rn(2.43f, x, 0.59f), 0.14f);
+    const float a = __saturatef(n * rcp_ftz(d));
+    const float g = ex2_ftz(inv_gamma * lg2_ftz(a));                                     // pow(a, 1/gamma), a in [0,1]   :47
+    return (uint32_t)__float2int_rd(__fmaf_rn(__saturatef(g), 255.0f, 0.5f));            // PIN-11
 }
 __device__ __forceinline__ uint32_t tonemap_pack8(V3 c, V3 bloom, const AshPostProcessPushConstants& pc, float inv_gamma) {
-    const float r = (c.x + bloom.x * pc.bloom_intensity) * pc.exposure;      // :38, :41
-    const float g = (c.y + bloom.y * pc.bloom_intensity) * pc.exposure;
-    const float b = (c.z + bloom.z * pc.bloom_intensity) * pc.exposure;
-    const uint32_t r8 = (uint32_t)__float2int_rd(__saturatef(__powf(aces_fast(r), inv_gamma)) * 255.0f + 0.5f);   // :44-47, PIN-11
-    const uint32_t g8 = (uint32_t)__float2int_rd(__saturatef(__powf(aces_fast(g), inv_gamma)) * 255.0f + 0.5f);
-    const uint32_t b8 = (uint32_t)__float2int_rd(__saturatef(__powf(aces_fast(b), inv_gamma)) * 255.0f + 0.5f);
-    return r8 | (g8 << 8) | (b8 << 16) | 0xFF000000u;
+    return tonemap8(c.x, bloom.x, pc, inv_gamma) | (tonemap8(c.y, bloom.y, pc, inv_gamma) << 8) |
+           (tonemap8(c.z, bloom.z, pc, inv_gamma) << 16) | 0xFF000000u;
 }
 
 template <bool TONEMAP, bool STORE_U>

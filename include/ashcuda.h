@@ -132,8 +132,10 @@ typedef struct AshCudaConfig {
     uint32_t hiz_levels;      /* value pushed as hizLevels is min(levels_built, this)      */
     uint32_t bloom_mips;      /* bloom chain depth allocated (<= ASH_MAX_BLOOM_MIPS)       */
     uint32_t enable_post;     /* 0: allocate no colour/TAA/bloom/LDR targets               */
-    uint32_t srgb_encode;     /* 1: extra sRGB OETF on the 8-bit store (swapchain.rs:81-88) */
-    uint32_t _reserved[9];
+    uint32_t srgb_encode;     /* reserved (swapchain.rs:81-88 sRGB target): must be 0               */
+    uint32_t concurrent_frontend; /* 1 (default): view_run runs Hi-Z + cull + light cull on a second
+                                     stream, concurrently with the post chain of the same view     */
+    uint32_t _reserved[8];
 } AshCudaConfig;
 
 /* Per-view statistics (OcclusionStats, occlusion_culling.rs:152-185 + tile list stats).
