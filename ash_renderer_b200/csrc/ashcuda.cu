@@ -477,7 +477,8 @@ int ashcuda_view_run(ashcuda_ctx* c, const AshCudaViewParams* vp) {
     //      the main stream (inputs uploaded earlier on the main stream are ordered by the fork event)
     const bool front = (st & (ASH_STAGE_HIZ | ASH_STAGE_CULL | ASH_STAGE_LIGHTS)) != 0;
     const bool post = (st & (ASH_STAGE_TAA | ASH_STAGE_BLOOM | ASH_STAGE_TONEMAP)) != 0;
-    const bool fork = front && post && c->cfg.concurrent_frontend && c->front_stream;
+    // (per-kernel profiling serialises the view so that event pairs time one kernel each)
+    const bool fork = front && post && c->cfg.concurrent_frontend && c->front_stream && c->prof.mask == 0;
     cudaStream_t main_stream = c->stream;
     if (fork) {
         ASH_CUDA(c, cudaSetDevice(c->device));

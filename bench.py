@@ -338,14 +338,10 @@ def run_cuda(args):
             ms = float(t.item())
         return ms
 
-    # ---- device-resident throughput (the `value`)
+    # ---- device-resident throughput (the `value`): every stream busy, front end forked per view
     for s in slots:
         s["ctx"].profile_kernels(0)
     timed(step_resident, 1, max(args.warmup, 3) - 1)       # warm-up (also fills every TAA history)
-    for s in slots:
-        s["ctx"].profile_kernels((1 << T.KERNEL_COUNT) - 1)
-        for k in range(T.KERNEL_COUNT):
-            s["ctx"].kernel_time_ms(k)                     # reset accumulators
     launches0 = sum(s["ctx"].kernel_launches() for s in slots)
     sampler = ClockSampler(local)
     if rank == 0:
@@ -356,7 +352,14 @@ def run_cuda(args):
     launches_per_step = (sum(s["ctx"].kernel_launches() for s in slots) - launches0) / (args.steps + 1)
     value = total_views * args.steps / (ms * 1e-3)
 
-    # per-kernel-class device time over the timed region (events recorded by the library)
+    # ---- per-kernel device time: the same steps again in the same process, serialised (one stream,
+    #      no fork) so that each CUDA-event pair recorded by the library brackets exactly one kernel
+    for s in slots:
+        s["ctx"].set_stream(streams[0].cuda_stream)
+        s["ctx"].profile_kernels((1 << T.KERNEL_COUNT) - 1)
+        for k in range(T.KERNEL_COUNT):
+            s["ctx"].kernel_time_ms(k)                     # reset accumulators
+    prof_ms = timed(step_resident, args.steps, 1)
     ktime = np.zeros(T.KERNEL_COUNT)
     kcount = np.zeros(T.KERNEL_COUNT)
     for s in slots:
@@ -365,6 +368,8 @@ def run_cuda(args):
             ktime[k] += t
             kcount[k] += n
         s["ctx"].profile_kernels(0)
+    for v, s in enumerate(slots):
+        s["ctx"].set_stream(streams[v % args.streams].cuda_stream)
     stats = [s["ctx"].stats() for s in slots]
     st_mean = {f: float(np.mean([st[f] for st in stats])) for f in T.VIEW_STATS.names}
 
@@ -423,7 +428,9 @@ def run_cuda(args):
         "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic",
         "config": {"workload": workload_name(), "views_per_gpu_per_step": B, "distinct_view_inputs_per_gpu": distinct,
-                   "streams": args.streams, "l2": f"inputs larger than L2: {B} views x 99.5 MB of depth+HDR per step per GPU",
+                   "streams": args.streams, "concurrent_frontend": True,
+                   "kernel_timing": f"same {args.steps} steps repeated serialised (1 stream, no fork) with CUDA events around each launch: "
+                                    f"{prof_ms / args.steps:.3f} ms/step", "l2": f"inputs larger than L2: {B} views x 99.5 MB of depth+HDR per step per GPU",
                    "visible_fraction_mean": st_mean["visible_objects"] / n_objs,
                    "candidate_lights_mean": st_mean["candidate_lights"],
                    "lights_per_tile_mean": st_mean["sum_tile_lights"] / tiles, "lights_per_tile_max": int(st_all[:, 5].max())},

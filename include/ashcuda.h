@@ -260,7 +260,8 @@ int ashcuda_mip_extent(ashcuda_ctx*, int which, uint32_t* w, uint32_t* h);
 uint64_t ashcuda_kernel_launches(ashcuda_ctx*);                /* kernels launched so far by this ctx */
 /* Device-time accounting: launches of the classes in `mask` (bit ASH_KERNEL_*) are bracketed by
  * CUDA events on the ctx stream.  ashcuda_kernel_time_ms syncs the stream, returns the time and
- * launch count accumulated for one class since the previous query of it, and resets them. */
+ * launch count accumulated for one class since the previous query of it, and resets them.
+ * While any class is profiled, view_run does not fork its front end (one kernel at a time per ctx). */
 int ashcuda_profile_kernels(ashcuda_ctx*, uint32_t mask);
 int ashcuda_kernel_time_ms(ashcuda_ctx*, int kernel_class, float* ms, uint64_t* launches);
 /* Diagnostics (host only, no device needed): does the pinned LINEAR sampler land exactly on the
