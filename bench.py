@@ -384,14 +384,10 @@ def run_cuda(args):
     assert int(chk["o_cnt"][0]) == int(stats[0]["visible_objects"]), "e2e result differs from resident result"
 
     # ---- stats all_gather (the only inter-GPU exchange; 32 B per view)
-    st_arr = np.stack([np.frombuffer(st.tobytes(), np.uint32) for st in stats]).astype(np.int32)
-    if world > 1:
-        mine = torch.from_numpy(st_arr).cuda()
-        allst = torch.empty((world * B, 8), dtype=torch.int32, device="cuda")
-        dist.all_gather_into_tensor(allst, mine)
-        st_all = allst.cpu().numpy()
-    else:
-        st_all = st_arr
+    from ash_renderer_b200 import views as V
+    st_all = V.stats_to_words(V.all_gather_stats(np.array(stats, T.VIEW_STATS), total_views, world, rank,
+                                                 device="cuda" if world > 1 else None))
+    assert len(st_all) == total_views, "stats all_gather lost views"
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
