@@ -209,6 +209,8 @@ def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
+    # torchrun exports OMP_NUM_THREADS=1; the CPU arm is meant to use every host core it can
+    os.environ["OMP_NUM_THREADS"] = str(os.cpu_count() or 1)
     objs, draws, lights = make_scene()
     n_views = 2
     views = [make_view_inputs(v, 1024, objs) for v in range(n_views)]
@@ -417,7 +419,9 @@ def run_cuda(args):
     per_view_s = ms * 1e-3 / (B * args.steps)
 
     # ---- CPU baseline (bounded sample: up to 2 full 4K views, ~10-30 s)
-    cpu_v, cpu_cores, cpu_n = cpu_oracle_rate(objs, draws, lights, host_views, taa_pc, max_views=args.cpu_views, budget_s=20.0)
+    # (rank 0 at N=1 only: under torchrun the other ranks would wait at exit and OMP is pinned to 1 thread)
+    cpu_v, cpu_cores, cpu_n = cpu_oracle_rate(objs, draws, lights, host_views, taa_pc,
+                                              max_views=args.cpu_views if world == 1 else 0, budget_s=20.0)
 
     out = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
