@@ -1,0 +1,86 @@
+//! extern "C" declarations of include/ashcuda.h against the crate's own #[repr(C)] types
+//! (byte-identical layouts; sizes asserted below).  UNBUILT (no Rust toolchain in the image).
+#![allow(non_camel_case_types)]
+use crate::renderer::features::light_culling::{CullingCameraData, GpuLight, LightCullingPushConstants};
+use crate::renderer::occlusion_culling::{CullObjectData, CullingPushConstants, IndirectDrawCommand};
+use crate::renderer::temporal_aa::TaaPushConstants;
+use crate::renderer::fullscreen_pass::PostProcessPushConstants;
+use std::os::raw::{c_char, c_int, c_void};
+
+#[repr(C)] pub struct ashcuda_ctx { _private: [u8; 0] }
+
+#[repr(C)] #[derive(Clone, Copy, Default)]
+pub struct AshBloomParams { pub threshold: f32, pub upsample_intensity: f32, pub mip_count: u32, pub _padding: u32 }
+
+#[repr(C)] #[derive(Clone, Copy, Default)]
+pub struct AshCudaConfig {
+    pub max_objects: u32, pub max_lights: u32, pub max_draws: u32, pub hiz_levels: u32, pub bloom_mips: u32,
+    pub enable_post: u32, pub srgb_encode: u32, pub concurrent_frontend: u32, pub _reserved: [u32; 8],
+}
+
+#[repr(C)] #[derive(Clone, Copy)]
+pub struct AshCudaViewParams {
+    pub cull: CullingPushConstants, pub light: LightCullingPushConstants, pub camera: CullingCameraData,
+    pub taa: TaaPushConstants, pub bloom: AshBloomParams, pub post: PostProcessPushConstants,
+    pub view_id: u32, pub stages: u32, pub _padding: [u32; 2],
+}
+
+#[repr(C)] #[derive(Clone, Copy, Default, Debug)]
+pub struct AshViewStats {
+    pub view_id: u32, pub total_objects: u32, pub visible_objects: u32, pub tiles: u32,
+    pub sum_tile_lights: u32, pub max_tile_lights: u32, pub overflow_tiles: u32, pub candidate_lights: u32,
+}
+
+const _: () = assert!(std::mem::size_of::<CullObjectData>() == 112 && std::mem::size_of::<IndirectDrawCommand>() == 20);
+const _: () = assert!(std::mem::size_of::<CullingPushConstants>() == 96 && std::mem::size_of::<GpuLight>() == 64);
+const _: () = assert!(std::mem::size_of::<CullingCameraData>() == 208 && std::mem::size_of::<TaaPushConstants>() == 48);
+const _: () = assert!(std::mem::size_of::<AshCudaViewParams>() == 416 && std::mem::size_of::<AshCudaConfig>() == 64);
+
+pub const ASH_OK: c_int = 0;
+pub const ASH_ERR_DEVICE: c_int = -1;
+pub const ASH_ERR_NOT_INITIALIZED: c_int = -2;
+pub const ASH_ERR_NOT_FOUND: c_int = -3;
+pub const ASH_ERR_INVALID: c_int = -4;
+pub const ASH_ERR_OUT_OF_MEMORY: c_int = -5;
+pub const ASH_STAGE_ALL: u32 = 0x3F;
+pub const ASH_BUF_VISIBILITY: c_int = 1;
+pub const ASH_BUF_DRAWS_OUT: c_int = 2;
+pub const ASH_BUF_VISIBLE_COUNT: c_int = 3;
+pub const ASH_BUF_TILE_DATA: c_int = 4;
+pub const ASH_BUF_TAA_OUT: c_int = 5;
+pub const ASH_BUF_LDR8: c_int = 6;
+pub const ASH_BUF_STATS: c_int = 7;
+
+extern "C" {
+    pub fn ashcuda_default_config(cfg: *mut AshCudaConfig);
+    pub fn ashcuda_create(out: *mut *mut ashcuda_ctx, device: c_int, width: u32, height: u32, cfg: *const AshCudaConfig) -> c_int;
+    pub fn ashcuda_destroy(ctx: *mut ashcuda_ctx);
+    pub fn ashcuda_set_stream(ctx: *mut ashcuda_ctx, cuda_stream: *mut c_void) -> c_int;
+    pub fn ashcuda_set_depth(ctx: *mut ashcuda_ctx, depth: *const f32, on_device: c_int) -> c_int;
+    pub fn ashcuda_set_objects(ctx: *mut ashcuda_ctx, objs: *const CullObjectData, n: u32, draws_in: *const IndirectDrawCommand, n_draws: u32, on_device: c_int) -> c_int;
+    pub fn ashcuda_set_lights(ctx: *mut ashcuda_ctx, lights: *const GpuLight, n: u32, on_device: c_int) -> c_int;
+    pub fn ashcuda_set_camera(ctx: *mut ashcuda_ctx, cam: *const CullingCameraData) -> c_int;
+    pub fn ashcuda_set_color(ctx: *mut ashcuda_ctx, hdr_rgba16f: *const c_void, velocity_rg16f: *const c_void, on_device: c_int) -> c_int;
+    pub fn ashcuda_taa_reset_history(ctx: *mut ashcuda_ctx) -> c_int;
+    pub fn ashcuda_hiz_build(ctx: *mut ashcuda_ctx) -> c_int;
+    pub fn ashcuda_occlusion_cull(ctx: *mut ashcuda_ctx, pc: *const CullingPushConstants) -> c_int;
+    pub fn ashcuda_light_cull(ctx: *mut ashcuda_ctx, pc: *const LightCullingPushConstants) -> c_int;
+    pub fn ashcuda_taa_resolve(ctx: *mut ashcuda_ctx, pc: *const TaaPushConstants) -> c_int;
+    pub fn ashcuda_bloom(ctx: *mut ashcuda_ctx, bp: *const AshBloomParams) -> c_int;
+    pub fn ashcuda_tonemap(ctx: *mut ashcuda_ctx, pc: *const PostProcessPushConstants) -> c_int;
+    pub fn ashcuda_view_run(ctx: *mut ashcuda_ctx, vp: *const AshCudaViewParams) -> c_int;
+    pub fn ashcuda_upload_view(ctx: *mut ashcuda_ctx, depth: *const f32, hdr: *const c_void, velocity: *const c_void) -> c_int;
+    pub fn ashcuda_download_view(ctx: *mut ashcuda_ctx, visibility: *mut u32, tile_data: *mut u32, ldr8: *mut u8, stats: *mut AshViewStats, visible_count: *mut u32) -> c_int;
+    pub fn ashcuda_get(ctx: *mut ashcuda_ctx, which: c_int, dev_ptr: *mut *mut c_void, bytes: *mut usize) -> c_int;
+    pub fn ashcuda_readback(ctx: *mut ashcuda_ctx, which: c_int, host_dst: *mut c_void, bytes: usize) -> c_int;
+    pub fn ashcuda_readback_async(ctx: *mut ashcuda_ctx, which: c_int, host_dst: *mut c_void, bytes: usize) -> c_int;
+    pub fn ashcuda_sync(ctx: *mut ashcuda_ctx) -> c_int;
+    pub fn ashcuda_hiz_level_count(ctx: *mut ashcuda_ctx) -> c_int;
+    pub fn ashcuda_mip_extent(ctx: *mut ashcuda_ctx, which: c_int, w: *mut u32, h: *mut u32) -> c_int;
+    pub fn ashcuda_kernel_launches(ctx: *mut ashcuda_ctx) -> u64;
+    pub fn ashcuda_profile_kernels(ctx: *mut ashcuda_ctx, mask: u32) -> c_int;
+    pub fn ashcuda_kernel_time_ms(ctx: *mut ashcuda_ctx, kernel_class: c_int, ms: *mut f32, launches: *mut u64) -> c_int;
+    pub fn ashcuda_debug_exact_taps(kind: c_int, n_src: c_int, n_dst: c_int, size_f: f32, inv: f32) -> c_int;
+    pub fn ashcuda_last_error(ctx: *mut ashcuda_ctx) -> *const c_char;
+    pub fn ashcuda_version() -> *const c_char;
+}
