@@ -112,6 +112,7 @@ struct ashcuda_ctx {
     ash::LightCand* cand = nullptr;
     uint32_t* cand_idx = nullptr;
     uint32_t* cand_count = nullptr;
+    uint8_t*  light_scratch = nullptr;   // tile planes + per-cell candidate lists (light_cull.cu)
     uint32_t* tile_data = nullptr;
     AshViewStats* stats = nullptr;
 
@@ -145,8 +146,10 @@ cudaError_t launch_occlusion_cull(const AshCullObjectData* objs, const AshIndire
 cudaError_t launch_light_cull(const AshGpuLight* lights, const AshLightCullingPushConstants& pc,
                               const AshCullingCameraData* cam_dev, const uint32_t* tile_minmax,
                               uint32_t* depth_range, LightCand* cand, uint32_t* cand_idx,
-                              uint32_t* cand_count, uint32_t* tile_data, AshViewStats* stats,
-                              const Launch& L);
+                              uint32_t* cand_count, uint8_t* scratch, uint32_t max_lights,
+                              uint32_t* tile_data, AshViewStats* stats, const Launch& L);
+size_t light_cull_scratch_bytes(uint32_t W, uint32_t H, uint32_t max_lights, size_t* planes_off, size_t* list_off,
+                                size_t* count_off);
 // `center`: the exact-tap checks passed, so centre / +-1 texel taps may be fetched directly
 cudaError_t launch_taa(const void* cur, const void* hist, const void* vel, void* out,
                        const AshTaaPushConstants& pc, bool center, const Launch& L);

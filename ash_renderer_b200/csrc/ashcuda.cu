@@ -85,7 +85,7 @@ void ashcuda_destroy(ashcuda_ctx* c) {
     void* owned[] = {c->depth_owned, c->pyr.mips, c->tile_minmax, c->depth_range, c->counters,
                      c->objs_owned, c->draws_in_owned, c->visibility, c->vis_bits, c->cta_counts,
                      c->draws_out, c->visible_count, c->lights_owned, c->camera_dev, c->cand,
-                     c->cand_idx, c->cand_count, c->tile_data, c->stats, c->color_owned,
+                     c->cand_idx, c->cand_count, c->light_scratch, c->tile_data, c->stats, c->color_owned,
                      c->velocity_owned, c->taa[0], c->taa[1], c->bloom_t, c->ldr8};
     for (void* p : owned) if (p) cudaFree(p);
     for (uint32_t k = 1; k <= ASH_MAX_BLOOM_MIPS; ++k) if (c->bloom.d[k]) cudaFree(c->bloom.d[k]);
@@ -148,6 +148,10 @@ static int create_impl(ashcuda_ctx* c) {
     ASH_CUDA(c, dmalloc(&c->cand, L * sizeof(LightCand)));
     ASH_CUDA(c, dmalloc(&c->cand_idx, L * 16));   // CandZ records (light_cull.cu), 16 B each
     ASH_CUDA(c, dmalloc(&c->cand_count, 4));
+    {
+        size_t po, lo, co;
+        ASH_CUDA(c, dmalloc(&c->light_scratch, light_cull_scratch_bytes(c->W, c->H, c->cfg.max_lights, &po, &lo, &co)));
+    }
     ASH_CUDA(c, dmalloc(&c->tile_data, tiles * ASH_TILE_STRIDE * 4));    // light_culling_pipeline.rs:55-56
     ASH_CUDA(c, dmalloc(&c->stats, sizeof(AshViewStats)));
     ASH_CUDA(c, cudaMemsetAsync(c->stats, 0, sizeof(AshViewStats), c->stream));
@@ -335,7 +339,7 @@ int ashcuda_light_cull(ashcuda_ctx* c, const AshLightCullingPushConstants* pc) {
     ASH_CUDA(c, cudaSetDevice(c->device));
     if (!c->have_pyramid) { int rc = ashcuda_hiz_build(c); if (rc) return rc; }
     ASH_CUDA(c, launch_light_cull(c->lights, *pc, c->camera_dev, c->tile_minmax, c->depth_range, c->cand,
-                                  c->cand_idx, c->cand_count, c->tile_data, c->stats, c->L()));
+                                  c->cand_idx, c->cand_count, c->light_scratch, c->cfg.max_lights, c->tile_data, c->stats, c->L()));
     return ASH_OK;
 }
 

@@ -8,12 +8,15 @@
 //     evaluated with the frame's global [min,max] depth fails them in every tile (rounding is
 //     monotone and tile min >= global min, tile max <= global max), so only survivors
 //     ("candidates") are kept, in ascending light index.
+//   k_tile_planes (1 thread per tile): the four side planes of every tile frustum (:71-98), once.
+//   k_light_cells (1 warp per 8x8-tile cell): a conservative prefilter — candidates that provably
+//     fail the shader's test in every tile of the cell are dropped, the rest form the cell's list.
 //   k_light_tiles (1 warp per tile): tile min/max come from the depth pyramid kernel (depth is not
-//     read again); 4 lanes build the tile frustum (:71-98); lanes test 32 candidates at a time
-//     with the shader's exact predicate (:101-109) and append by ballot + popc prefix, which
-//     yields ascending order and first-256-on-overflow (PIN-7) without atomics.
+//     read again); lanes test 32 of the cell's survivors at a time with the shader's exact
+//     predicate (:101-109) and append by ballot + popc prefix, which yields ascending order and
+//     first-256-on-overflow (PIN-7) without atomics.
 //
-// Algorithmic bytes per launch pair: 64*L (lights) + 208 (camera) + 8*tiles (tile min/max)
+// Algorithmic bytes per launch group: 64*L (lights) + 208 (camera) + 8*tiles (tile min/max)
 // + 4*sum_tiles(1+count).
 #include "ash_internal.cuh"
 #include "ash_math.cuh"
@@ -123,11 +126,179 @@ __device__ __forceinline__ V3 screen_to_view0(const M4& ip, float u, float v) {
     return {fdiv(q.x, q.w), fdiv(q.y, q.w), fdiv(q.z, q.w)};
 }
 
-__global__ void __launch_bounds__(kTileWarps * 32)
-k_light_tiles(const AshCullingCameraData* __restrict__ cam, uint32_t W, uint32_t H, uint32_t tiles_x,
-              uint32_t tiles, uint32_t light_count, const uint32_t* __restrict__ tile_minmax,
+// getTileFrustum, :71-98: the four side planes of tile (tx,ty): normals n[0..3] (left, right, bottom, top;
+// zero vector when |cross| <= 1e-4, :92-95) and the cross-product lengths (for the cell prefilter).
+__device__ __forceinline__ void tile_side_planes(const M4& ip, uint32_t tx, uint32_t ty, float sw, float sh,
+                                                 V3 n[4], float len[4]) {
+    const float ts = 16.0f;
+    const float min_x = fsub(fmul(fdiv(fmul((float)tx, ts), sw), 2.0f), 1.0f);
+    const float min_y = fsub(fmul(fdiv(fmul((float)ty, ts), sh), 2.0f), 1.0f);
+    const float max_x = fsub(fmul(fdiv(fmul((float)(tx + 1u), ts), sw), 2.0f), 1.0f);
+    const float max_y = fsub(fmul(fdiv(fmul((float)(ty + 1u), ts), sh), 2.0f), 1.0f);
+    const float u0 = fadd(fmul(min_x, 0.5f), 0.5f), u1 = fadd(fmul(max_x, 0.5f), 0.5f);
+    const float v0 = fadd(fmul(min_y, 0.5f), 0.5f), v1 = fadd(fmul(max_y, 0.5f), 0.5f);
+    const V3 c0 = screen_to_view0(ip, u0, v0), c1 = screen_to_view0(ip, u1, v0);
+    const V3 c2 = screen_to_view0(ip, u1, v1), c3 = screen_to_view0(ip, u0, v1);
+    const V3 cr[4] = {cross3(c3, c0), cross3(c1, c2), cross3(c0, c1), cross3(c2, c3)};
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        len[k] = length3(cr[k]);
+        n[k] = (len[k] > 0.0001f) ? divs3(cr[k], len[k]) : v3(0.0f, 0.0f, 0.0f);   // normalize(v) = v / length(v)
+    }
+}
+
+// ---- pass 2: one thread per tile builds its side planes once (they depend on the camera only)
+struct TilePlanes { float4 a, b, c; };      // n0.xyz n1.x | n1.yz n2.xy | n2.z n3.xyz
+
+__global__ void __launch_bounds__(128)
+k_tile_planes(const AshCullingCameraData* __restrict__ cam, uint32_t W, uint32_t H, uint32_t tiles_x,
+              uint32_t tiles, TilePlanes* __restrict__ planes) {
+    const uint32_t tile = blockIdx.x * blockDim.x + threadIdx.x;
+    if (tile >= tiles) return;
+    const M4 ip = load_m4(cam->inv_projection);
+    V3 n[4]; float len[4];
+    tile_side_planes(ip, tile % tiles_x, tile / tiles_x, (float)W, (float)H, n, len);
+    TilePlanes p;
+    p.a = make_float4(n[0].x, n[0].y, n[0].z, n[1].x);
+    p.b = make_float4(n[1].y, n[1].z, n[2].x, n[2].y);
+    p.c = make_float4(n[2].z, n[3].x, n[3].y, n[3].z);
+    planes[tile] = p;
+}
+
+// ---- pass 3: conservative prefilter per cell of 8x8 tiles (128x128 px), one warp per cell.
+// A candidate is dropped from a cell only if it provably fails the shader's test in EVERY tile of it:
+//  * planes 4/5: fadd(zdot, w) is monotone in w and the cell's [min,max] depth contains every tile's,
+//    so failing with the cell's bounds implies failing with each tile's (exact, no margin);
+//  * side planes, per family f (left / right / bottom / top): with a, b the family's normals at the two
+//    ends of the cell, every tile's ACTUAL normal (read back from k_tile_planes' output, so the bound
+//    holds for any matrix) is decomposed as n_t = al*a + be*b + e with al, be >= 0.  Then
+//        n_t.c <= (al+be)*max(a.c, b.c) + |e||c|
+//    and with s_min = min_t(al+be), E = max_t|e|, a light with max(a.c,b.c) < 0 and
+//        s_min*max(a.c,b.c) + E|c| < -r
+//    has n_t.c < -r in every tile.  For a perspective camera the family's normals lie on one great
+//    circle, so E is only the rounding noise of the shader's cross products (~1e-4) and s_min ~ 1.
+//    A tile whose normal the shader zeroed (:92-95) gets al = be = 0, hence s_min = 0 and nothing is
+//    rejected by that family; non-finite normals disable the family.
+constexpr int kCellTiles = 8;
+constexpr int kCellWarps = 4;
+
+__device__ __forceinline__ V3 plane_n(const TilePlanes& p, int f) {
+    switch (f) {
+        case 0: return {p.a.x, p.a.y, p.a.z};
+        case 1: return {p.a.w, p.b.x, p.b.y};
+        case 2: return {p.b.z, p.b.w, p.c.x};
+        default: return {p.c.y, p.c.z, p.c.w};
+    }
+}
+__device__ __forceinline__ float pdot(V3 a, V3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
+
+__global__ void __launch_bounds__(kCellWarps * 32)
+k_light_cells(uint32_t tiles_x, uint32_t tiles_y, uint32_t cells_x, uint32_t cells,
+              const TilePlanes* __restrict__ planes, const uint32_t* __restrict__ tile_minmax,
               const LightCand* __restrict__ cand, const uint32_t* __restrict__ cand_idx,
-              const uint32_t* __restrict__ cand_count, uint32_t* __restrict__ tile_data,
+              const uint32_t* __restrict__ cand_count, uint32_t* __restrict__ cell_list, uint32_t cell_stride,
+              uint32_t* __restrict__ cell_count) {
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t cell = blockIdx.x * kCellWarps + warp;
+    if (cell >= cells) return;
+    const uint32_t cx = cell % cells_x, cy = cell / cells_x;
+    const uint32_t tx0 = cx * kCellTiles, ty0 = cy * kCellTiles;
+    const uint32_t tx1 = min(tx0 + kCellTiles - 1, tiles_x - 1), ty1 = min(ty0 + kCellTiles - 1, tiles_y - 1);
+    const TilePlanes p00 = planes[(size_t)ty0 * tiles_x + tx0];
+    const TilePlanes p10 = planes[(size_t)ty0 * tiles_x + tx1];
+    const TilePlanes p01 = planes[(size_t)ty1 * tiles_x + tx0];
+    V3 fa[4], fb[4];
+    float smin[4], emax[4];
+    bool bad[4];
+    uint32_t mn = 0xFFFFFFFFu, mx = 0u, worst = 0u;
+#pragma unroll
+    for (int f = 0; f < 4; ++f) {
+        fa[f] = plane_n(p00, f);
+        fb[f] = plane_n(f < 2 ? p10 : p01, f);
+        smin[f] = 3.0e38f; emax[f] = 0.0f; bad[f] = false;
+    }
+    for (uint32_t t = lane; t < (uint32_t)(kCellTiles * kCellTiles); t += 32) {
+        const uint32_t tx = tx0 + (t % kCellTiles), ty = ty0 + (t / kCellTiles);
+        if (tx > tx1 || ty > ty1) continue;
+        const size_t tile = (size_t)ty * tiles_x + tx;
+        const uint2 mm = __ldg(reinterpret_cast<const uint2*>(tile_minmax) + tile);
+        mn = min(mn, mm.x); mx = max(mx, mm.y); worst = max(worst, max(mm.x, mm.y));
+        const TilePlanes p = planes[tile];
+#pragma unroll
+        for (int f = 0; f < 4; ++f) {
+            const V3 n = plane_n(p, f), a = fa[f], b = fb[f];
+            const float aa = pdot(a, a), bb = pdot(b, b), ab = pdot(a, b), na = pdot(n, a), nb = pdot(n, b);
+            const float det = aa * bb - ab * ab;
+            float al, be;
+            if (det > 1e-6f) { al = (na * bb - nb * ab) / det; be = (nb * aa - na * ab) / det; }
+            else             { al = aa > 0.5f ? na / aa : 0.0f; be = 0.0f; }
+            al = al > 0.0f ? al : 0.0f;                              // NaN -> 0 (the residual then carries the NaN)
+            be = be > 0.0f ? be : 0.0f;
+            const V3 e = {n.x - al * a.x - be * b.x, n.y - al * a.y - be * b.y, n.z - al * a.z - be * b.z};
+            const float el = sqrtf(pdot(e, e));
+            if (!(el < 1.0f) || !(al + be < 4.0f)) bad[f] = true;    // NaN / inf / nonsense
+            smin[f] = fminf(smin[f], al + be);
+            emax[f] = fmaxf(emax[f], el);
+        }
+    }
+#pragma unroll
+    for (int s = 16; s > 0; s >>= 1) {
+        mn = min(mn, __shfl_xor_sync(0xFFFFFFFFu, mn, s));
+        mx = max(mx, __shfl_xor_sync(0xFFFFFFFFu, mx, s));
+        worst = max(worst, __shfl_xor_sync(0xFFFFFFFFu, worst, s));
+#pragma unroll
+        for (int f = 0; f < 4; ++f) {
+            smin[f] = fminf(smin[f], __shfl_xor_sync(0xFFFFFFFFu, smin[f], s));
+            emax[f] = fmaxf(emax[f], __shfl_xor_sync(0xFFFFFFFFu, emax[f], s));
+        }
+    }
+    bool fvalid[4];
+#pragma unroll
+    for (int f = 0; f < 4; ++f) {
+        fvalid[f] = !__any_sync(0xFFFFFFFFu, bad[f]) && smin[f] > 0.0f;
+        emax[f] += 4e-6f;      // rounding of e itself and of the shader's own dot product
+    }
+    // uint order == float order only when every tile bound is a non-negative non-NaN float
+    const bool zsane = worst <= 0x7F800000u && mn <= mx;
+    const float w4 = -__uint_as_float(mn), w5 = __uint_as_float(mx);
+
+    const uint32_t nc = *cand_count;
+    uint32_t* list = cell_list + (size_t)cell * cell_stride;
+    uint32_t count = 0;
+    for (uint32_t base = 0; base < nc; base += 32) {
+        const uint32_t j = base + lane;
+        bool keep = false;
+        if (j < nc) {
+            const float4 q = __ldg(reinterpret_cast<const float4*>(cand) + j);
+            const uint4 zq = __ldg(reinterpret_cast<const uint4*>(cand_idx) + j);      // CandZ
+            const V3 c = {q.x, q.y, q.z};
+            const float nr = -q.w;
+            bool reject = false;
+            if (zsane) reject = (fadd(__uint_as_float(zq.x), w4) < nr) || (fadd(__uint_as_float(zq.y), w5) < nr);
+            const float clen = sqrtf(pdot(c, c)) * 1.000001f;
+            const float slack = 1e-6f * (fabsf(q.w) + clen);
+#pragma unroll
+            for (int f = 0; f < 4; ++f) {
+                const float m = fmaxf(pdot(fa[f], c), pdot(fb[f], c));
+                // every comparison is false on NaN / inf operands, so those candidates are kept
+                if (fvalid[f] && m < 0.0f && smin[f] * m + emax[f] * clen + slack < nr) reject = true;
+            }
+            keep = !reject;
+        }
+        const uint32_t ballot = __ballot_sync(0xFFFFFFFFu, keep);
+        if (keep) list[count + __popc(ballot & ((1u << lane) - 1u))] = j;
+        count += __popc(ballot);
+    }
+    if (lane == 0) cell_count[cell] = count;
+}
+
+// ---- pass 4: the shader's exact test (:101-109), one warp per tile, over its cell's survivors only
+__global__ void __launch_bounds__(kTileWarps * 32)
+k_light_tiles(uint32_t tiles_x, uint32_t tiles, uint32_t cells_x, uint32_t light_count,
+              const TilePlanes* __restrict__ planes, const uint32_t* __restrict__ tile_minmax,
+              const LightCand* __restrict__ cand, const uint32_t* __restrict__ cand_idx,
+              const uint32_t* __restrict__ cell_list, uint32_t cell_stride,
+              const uint32_t* __restrict__ cell_count, uint32_t* __restrict__ tile_data,
               AshViewStats* __restrict__ stats) {
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     __shared__ uint32_t s_cnt[kTileWarps];
@@ -136,39 +307,20 @@ k_light_tiles(const AshCullingCameraData* __restrict__ cam, uint32_t W, uint32_t
     uint32_t* out = tile_data + (size_t)tile * ASH_TILE_STRIDE;                  // :119
     if (light_count == 0u) { if (lane == 0 && active) out[0] = 0u; return; }     // :160-165 (uniform)
     const uint32_t tx = tile % tiles_x, ty = tile / tiles_x;
-
-    // getTileFrustum, :71-98 — lane k (<4) computes corner k, then plane k
-    const M4 ip = load_m4(cam->inv_projection);
-    const float sw = (float)W, sh = (float)H, ts = 16.0f;
-    const float min_x = fsub(fmul(fdiv(fmul((float)tx, ts), sw), 2.0f), 1.0f);
-    const float min_y = fsub(fmul(fdiv(fmul((float)ty, ts), sh), 2.0f), 1.0f);
-    const float max_x = fsub(fmul(fdiv(fmul((float)(tx + 1u), ts), sw), 2.0f), 1.0f);
-    const float max_y = fsub(fmul(fdiv(fmul((float)(ty + 1u), ts), sh), 2.0f), 1.0f);
-    const int k = lane & 3;
-    const float cxn = (k == 1 || k == 2) ? max_x : min_x;       // corners 0..3: (min,min) (max,min) (max,max) (min,max)
-    const float cyn = (k >= 2) ? max_y : min_y;
-    const V3 corner = screen_to_view0(ip, fadd(fmul(cxn, 0.5f), 0.5f), fadd(fmul(cyn, 0.5f), 0.5f));
-    // plane k = cross(corners[a], corners[b]) with (a,b) = (3,0) (1,2) (0,1) (2,3)
-    const int ia = (k == 0) ? 3 : (k == 1) ? 1 : (k == 2) ? 0 : 2;
-    const int ib = (k == 0) ? 0 : (k == 1) ? 2 : (k == 2) ? 1 : 3;
-    const V3 a = {__shfl_sync(0xFFFFFFFFu, corner.x, ia), __shfl_sync(0xFFFFFFFFu, corner.y, ia), __shfl_sync(0xFFFFFFFFu, corner.z, ia)};
-    const V3 b = {__shfl_sync(0xFFFFFFFFu, corner.x, ib), __shfl_sync(0xFFFFFFFFu, corner.y, ib), __shfl_sync(0xFFFFFFFFu, corner.z, ib)};
-    const V3 cr = cross3(a, b);
-    const V3 nk = (length3(cr) > 0.0001f) ? normalize3(cr) : v3(0.0f, 0.0f, 0.0f);
-    V3 n[4];
-#pragma unroll
-    for (int p = 0; p < 4; ++p)
-        n[p] = {__shfl_sync(0xFFFFFFFFu, nk.x, p), __shfl_sync(0xFFFFFFFFu, nk.y, p), __shfl_sync(0xFFFFFFFFu, nk.z, p)};
+    const uint32_t cell = (ty / kCellTiles) * cells_x + tx / kCellTiles;
+    const TilePlanes p = planes[tile];
+    const V3 n0 = {p.a.x, p.a.y, p.a.z}, n1 = {p.a.w, p.b.x, p.b.y}, n2 = {p.b.z, p.b.w, p.c.x}, n3 = {p.c.y, p.c.z, p.c.w};
     const uint2 mm = __ldg(reinterpret_cast<const uint2*>(tile_minmax) + tile);
     const float w4 = -__uint_as_float(mm.x), w5 = __uint_as_float(mm.y);       // :96-97
-
-    const uint32_t nc = active ? *cand_count : 0u;
+    const uint32_t* list = cell_list + (size_t)cell * cell_stride;
+    const uint32_t nc = active ? cell_count[cell] : 0u;
     uint32_t count = 0;
     for (uint32_t base = 0; base < nc; base += 32) {
-        const uint32_t j = base + lane;
+        const uint32_t k = base + lane;
         bool pass = false;
         uint32_t li = 0;
-        if (j < nc) {
+        if (k < nc) {
+            const uint32_t j = list[k];
             const float4 q = __ldg(reinterpret_cast<const float4*>(cand) + j);
             const uint4 zq = __ldg(reinterpret_cast<const uint4*>(cand_idx) + j);      // CandZ
             li = zq.z;
@@ -176,7 +328,7 @@ k_light_tiles(const AshCullingCameraData* __restrict__ cam, uint32_t W, uint32_t
             const float nr = -q.w;
             // sphereInFrustum, :101-109: dist = dot(plane.xyz, c) + plane.w ; reject if dist < -radius.
             // Side planes have w = 0: (d + 0.0) < nr  <=>  d < nr.  Planes 4/5: the dot is precomputed per light.
-            pass = !(dot3(n[0], c) < nr) && !(dot3(n[1], c) < nr) && !(dot3(n[2], c) < nr) && !(dot3(n[3], c) < nr) &&
+            pass = !(dot3(n0, c) < nr) && !(dot3(n1, c) < nr) && !(dot3(n2, c) < nr) && !(dot3(n3, c) < nr) &&
                    !(fadd(__uint_as_float(zq.x), w4) < nr) && !(fadd(__uint_as_float(zq.y), w5) < nr);
         }
         const uint32_t ballot = __ballot_sync(0xFFFFFFFFu, pass);
@@ -208,24 +360,51 @@ k_light_tiles(const AshCullingCameraData* __restrict__ cam, uint32_t W, uint32_t
     }
 }
 
+size_t light_cull_scratch_bytes(uint32_t W, uint32_t H, uint32_t max_lights, size_t* planes_off, size_t* list_off,
+                                size_t* count_off) {
+    const uint32_t tiles_x = (W + 15u) / 16u, tiles_y = (H + 15u) / 16u;
+    const uint32_t cells = ((tiles_x + kCellTiles - 1) / kCellTiles) * ((tiles_y + kCellTiles - 1) / kCellTiles);
+    auto up = [](size_t v) { return (v + 255) & ~size_t(255); };
+    size_t off = 0;
+    *planes_off = off; off = up(off + (size_t)tiles_x * tiles_y * sizeof(TilePlanes));
+    *list_off = off;   off = up(off + (size_t)cells * max_lights * sizeof(uint32_t));
+    *count_off = off;  off = up(off + (size_t)cells * sizeof(uint32_t));
+    return off;
+}
+
 cudaError_t launch_light_cull(const AshGpuLight* lights, const AshLightCullingPushConstants& pc,
                               const AshCullingCameraData* cam_dev, const uint32_t* tile_minmax,
                               uint32_t* depth_range, LightCand* cand, uint32_t* cand_idx,
-                              uint32_t* cand_count, uint32_t* tile_data, AshViewStats* stats,
-                              const Launch& L) {
+                              uint32_t* cand_count, uint8_t* scratch, uint32_t max_lights,
+                              uint32_t* tile_data, AshViewStats* stats, const Launch& L) {
     const uint32_t W = pc.screen_size[0], H = pc.screen_size[1];
     const uint32_t tiles_x = (W + 15u) / 16u, tiles_y = (H + 15u) / 16u, tiles = tiles_x * tiles_y;
+    const uint32_t cells_x = (tiles_x + kCellTiles - 1) / kCellTiles, cells_y = (tiles_y + kCellTiles - 1) / kCellTiles;
+    const uint32_t cells = cells_x * cells_y;
+    size_t po, lo, co;
+    light_cull_scratch_bytes(W, H, max_lights, &po, &lo, &co);
+    TilePlanes* planes = reinterpret_cast<TilePlanes*>(scratch + po);
+    uint32_t* cell_list = reinterpret_cast<uint32_t*>(scratch + lo);
+    uint32_t* cell_count = reinterpret_cast<uint32_t*>(scratch + co);
+    cudaError_t e;
     {
         Timed timed(L, ASH_KERNEL_LIGHT_PREPASS);
         k_light_prepass<<<1, kPrepassThreads, 0, L.s>>>(lights, pc.light_count, cam_dev, depth_range, cand,
                                                       cand_idx, cand_count, stats, tiles);
+        if ((e = cudaGetLastError()) != cudaSuccess) return e;
+        if (pc.light_count != 0u) {
+            k_tile_planes<<<(tiles + 127) / 128, 128, 0, L.s>>>(cam_dev, W, H, tiles_x, tiles, planes);
+            if ((e = cudaGetLastError()) != cudaSuccess) return e;
+            k_light_cells<<<(cells + kCellWarps - 1) / kCellWarps, kCellWarps * 32, 0, L.s>>>(
+                tiles_x, tiles_y, cells_x, cells, planes, tile_minmax, cand, cand_idx, cand_count, cell_list,
+                max_lights, cell_count);
+            if ((e = cudaGetLastError()) != cudaSuccess) return e;
+        }
     }
-    cudaError_t e = cudaGetLastError();
-    if (e != cudaSuccess) return e;
     Timed timed(L, ASH_KERNEL_LIGHT_TILES);
     k_light_tiles<<<(tiles + kTileWarps - 1) / kTileWarps, kTileWarps * 32, 0, L.s>>>(
-        cam_dev, W, H, tiles_x, tiles, pc.light_count, tile_minmax, cand, cand_idx, cand_count,
-        tile_data, stats);
+        tiles_x, tiles, cells_x, pc.light_count, planes, tile_minmax, cand, cand_idx, cell_list, max_lights,
+        cell_count, tile_data, stats);
     return cudaGetLastError();
 }
 

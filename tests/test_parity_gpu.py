@@ -198,6 +198,56 @@ def test_light_cull_bit_exact(backend, oracle, W, H, n_lights, extent, eye):
     assert ref[:, 0].max() > 0
 
 
+@pytest.mark.parametrize("case", ["near_tiny", "ortho", "random_matrix", "offcentre", "weird_lights", "flat_depth"])
+def test_light_cull_prefilter_is_conservative(backend, oracle, case):
+    """The per-cell prefilter (light_cull.cu k_light_cells) must never drop a light the shader keeps:
+    cameras whose tile planes degenerate (shader zeroes the normal, :92-95), non-perspective and
+    arbitrary inverse projections, non-finite / negative-radius lights, constant depth."""
+    W, H = 1000, 600
+    rng = np.random.default_rng(11)
+    cam = synth.Camera((0.0, 2.0, 22.0), (0, 0, 0), W, H, near=0.002 if case == "near_tiny" else 0.5)
+    objs, _ = synth.make_objects((6, 6, 6), seed=3)
+    depth = synth.splat_depth(objs, cam)
+    n_lights = 1500
+    lights = synth.make_lights(n_lights, extent=12.0, seed=5, center=(0, 0, 0))
+    cd = cam.camera_data()
+    # raw depth in [0,1] bounds the z slab (SURVEY PIN-2), so lights that the SIDE planes can separate
+    # sit within ~1 unit of the eye in view z and are spread laterally
+    n = 1200
+    vp = np.stack([rng.uniform(-1.2, 1.2, n), rng.uniform(-0.8, 0.8, n), rng.uniform(-1.6, 0.3, n), np.ones(n)], 1)
+    wp = (np.linalg.inv(cd["view"][0].astype(np.float64).T) @ vp.T).T
+    lights["position"][:n, :3] = wp[:, :3].astype(np.float32)
+    lights["position"][:n, 3] = rng.uniform(0.01, 0.25, n).astype(np.float32)
+    if case == "ortho":
+        ip = np.diag([8.0, 4.5, -50.0, 1.0]).astype(np.float32)
+        ip[3, 2] = -0.5                                    # column-major rows: translation in z
+        cd["inv_projection"][0] = ip
+    elif case == "random_matrix":
+        cd["inv_projection"][0] = rng.normal(size=(4, 4)).astype(np.float32)
+    elif case == "offcentre":
+        ip = cd["inv_projection"][0].copy()
+        ip[3, 0] += np.float32(0.37); ip[3, 1] -= np.float32(0.21)     # sheared frustum
+        cd["inv_projection"][0] = ip
+    elif case == "weird_lights":
+        p = lights["position"]
+        p[0, 0] = np.nan; p[1, 3] = np.nan; p[2, 1] = np.inf; p[3, 3] = np.inf; p[4, 3] = -3.0
+        p[5, :3] = 1e30; p[6, 3] = 0.0; p[7, 3] = -np.inf; p[8, 2] = -np.inf
+    elif case == "flat_depth":
+        depth = np.full((H, W), 0.9995, np.float32)
+    pc = cam.light_pc(n_lights)
+    ref, true_counts, _ = oracle.light_cull(lights, pc, cd, depth)
+    with _ctx(backend, W, H, enable_post=0) as c:
+        c.set_depth(depth)
+        c.upload_lights(lights)
+        c.upload_camera(cd)
+        c.hiz_build()
+        c.light_cull(pc)
+        _compare_tile_lists(c.tile_data(), ref)
+        assert c.stats()["overflow_tiles"] == int((true_counts > 256).sum())
+    if case in ("offcentre", "weird_lights", "flat_depth"):
+        assert ref[:, 0].min() < ref[:, 0].max()        # the side planes do separate tiles here
+
+
 def test_light_cull_overflow_zero_lights_and_disabled(backend, oracle):
     W, H = 64, 48
     cam = synth.Camera((0, 0, 5), (0, 0, 0), W, H)
