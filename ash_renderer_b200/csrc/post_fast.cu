@@ -182,11 +182,11 @@ cudaError_t launch_taa_fast(const void* cur, const void* hist, void* out, void* 
     const bool in_halo = fabsf(pc.jitter[0] - pc.prev_jitter[0]) <= 0.99f && fabsf(pc.jitter[1] - pc.prev_jitter[1]) <= 0.99f;
     uint2* o = static_cast<uint2*>(out);
     uint2* t = static_cast<uint2*>(thr_or_null);
+    // the usual case (sub-pixel jitter delta): two pixels per thread on the packed fp32 pipe, post_pair.cu
+    if (in_halo) return launch_taa_pair(cur, hist, out, thr_or_null, pc, threshold, L);
     Timed timed(L, thr_or_null ? ASH_KERNEL_TAA_THRESHOLD : ASH_KERNEL_TAA);
-    if (t) { if (in_halo) k_taa_fast<true, true><<<grid, 256, 0, L.s>>>(c, h, o, t, pc, threshold);
-             else         k_taa_fast<true, false><<<grid, 256, 0, L.s>>>(c, h, o, t, pc, threshold); }
-    else   { if (in_halo) k_taa_fast<false, true><<<grid, 256, 0, L.s>>>(c, h, o, t, pc, threshold);
-             else         k_taa_fast<false, false><<<grid, 256, 0, L.s>>>(c, h, o, t, pc, threshold); }
+    if (t) k_taa_fast<true, false><<<grid, 256, 0, L.s>>>(c, h, o, t, pc, threshold);
+    else   k_taa_fast<false, false><<<grid, 256, 0, L.s>>>(c, h, o, t, pc, threshold);
     return cudaGetLastError();
 }
 
@@ -329,8 +329,11 @@ __device__ __forceinline__ uint32_t tonemap_pack8(V3 c, V3 bloom, const AshPostP
            (tonemap8(c.z, bloom.z, pc, inv_gamma) << 16) | 0xFF000000u;
 }
 
+#ifndef ASH_UPS_MINB
+#define ASH_UPS_MINB 3
+#endif
 template <bool TONEMAP, bool STORE_U>
-__global__ void __launch_bounds__(256, 2)
+__global__ void __launch_bounds__(256, ASH_UPS_MINB)
 k_upsample_fast(const uint2* __restrict__ src, int sw, int sh, uint2* __restrict__ dst, float intensity,
                 const uint2* __restrict__ hdr, uint32_t* __restrict__ ldr8, AshPostProcessPushConstants pc) {
     __shared__ uint2 s_t[20][20];

@@ -343,7 +343,7 @@ public:
         int rc = ashcuda_create(&ctx_, device_index_, width_, height_, &cfg_);
         if (rc != ASH_OK) { last_error_ = ashcuda_last_error(nullptr); last_code_ = rc; ctx_ = nullptr; log_error("on_added"); return; }
         lights.calculate_tiles(width_, height_);
-        scene_dirty_ = true;
+        scene_dirty_ = true; last_code_ = ASH_OK;
     }
     void on_removed(const Device&) override { ashcuda_destroy(ctx_); ctx_ = nullptr; }
     void set_frame_inputs(const FrameInputs& in) { inputs_ = in; have_inputs_ = true; }
@@ -403,7 +403,7 @@ public:
 
 private:
     bool check(int rc, const char* what) {
-        if (rc == ASH_OK) return true;
+        if (rc == ASH_OK) { last_code_ = ASH_OK; return true; }      // last_code() = status of the latest call
         last_code_ = rc; last_error_ = ashcuda_last_error(ctx_); log_error(what);
         return false;
     }
