@@ -170,6 +170,8 @@ cudaError_t launch_taa_pair(const void* cur, const void* hist, void* out, void* 
                             const AshTaaPushConstants& pc, float threshold, const Launch& L);
 cudaError_t launch_bloom_downsample_fast(const void* src, uint32_t sw, uint32_t sh, void* dst, uint32_t dw,
                                          uint32_t dh, const Launch& L);
+cudaError_t launch_bloom_downsample_pair(const void* src, uint32_t sw, uint32_t sh, void* dst, uint32_t dw,
+                                         uint32_t dh, const Launch& L);
 cudaError_t launch_bloom_upsample_fast(const void* src, uint32_t sw, uint32_t sh, void* dst, float intensity,
                                        const Launch& L);
 cudaError_t launch_upsample_tonemap_fast(const void* src, uint32_t sw, uint32_t sh, void* dst, float intensity,

@@ -236,6 +236,10 @@ k_downsample_fast(const uint2* __restrict__ src, int sw, int sh, uint2* __restri
 
 cudaError_t launch_bloom_downsample_fast(const void* src, uint32_t sw, uint32_t sh, void* dst, uint32_t dw,
                                          uint32_t dh, const Launch& L) {
+#ifndef ASH_DOWN_PAIR
+#define ASH_DOWN_PAIR 1
+#endif
+    if (ASH_DOWN_PAIR && (dw & 1u) == 0u) return launch_bloom_downsample_pair(src, sw, sh, dst, dw, dh, L);    // two pixels per thread, post_pair.cu
     const dim3 grid((dw + 31) / 32, (dh + 7) / 8);
     Timed timed(L, ASH_KERNEL_BLOOM_DOWNSAMPLE);
     k_downsample_fast<<<grid, 256, 0, L.s>>>(static_cast<const uint2*>(src), (int)sw, (int)sh,

@@ -14,8 +14,8 @@ __device__ __forceinline__ V3 unpack_rgb_(uint2 t) { V4 v = unpack_rgba16f(t); r
 // The history sampling coordinates are separable: 32 column entries and 32 row entries per tile are
 // computed once (by 64 threads, while the global loads are in flight) instead of once per pixel.
 // =====================================================================================================
-constexpr int kT = 32, kHalo = kT + 2, kTexels = kHalo * kHalo;      // 34 x 34 = 1156
-constexpr int kLoads = (kTexels + 255) / 256;                        // 5 per thread
+constexpr int kT = 32, kHalo = kT + 2;                                 // 34 x 34 = 1156 staged texels
+constexpr int kLoads = 5;                                            // 4 block rows + 1 fringe texel per thread
 
 struct AxisTap { int i0, i1; float f; float pad; };                  // halo-local texel indices + 8-bit weight
 
@@ -31,17 +31,25 @@ k_taa_pair(Tex16 cur, Tex16 hist, uint2* __restrict__ out, uint2* __restrict__ t
     const int W = cur.W, H = cur.H;
     const int x0 = blockIdx.x * kT, y0 = blockIdx.y * kT;
     const bool clamp_on = pc.params[1] > 0.5f;
+    // Staging map (no divisions): step it < 4: warp w stages row w + 8*it, lane = column (the 32x32 block at
+    // halo origin); step 4: threads 0..63 stage rows 32..33, threads 64..131 stage columns 32..33.
+    const int lane_ = threadIdx.x & 31, warp_ = threadIdx.x >> 5;
+    const int xr = threadIdx.x < 64 ? lane_ : 32 + (threadIdx.x & 1);                 // step-4 column
+    const int rr = threadIdx.x < 64 ? 32 + warp_ : (int)(threadIdx.x - 64) >> 1;      // step-4 row
+    const bool extra = threadIdx.x < 132;
     {   // stage: all global loads of the CTA are issued here, back to back
         uint2 tc[kLoads], th[kLoads];
+        const int gx = min(max(x0 - 1 + lane_, 0), W - 1);                                             // CLAMP_TO_EDGE
 #pragma unroll
-        for (int it = 0; it < kLoads; ++it) {
-            const int idx = threadIdx.x + it * 256;
-            if (idx < kTexels) {
-                const int r = idx / kHalo, c = idx - r * kHalo;
-                const size_t g = (size_t)min(max(y0 - 1 + r, 0), H - 1) * W + min(max(x0 - 1 + c, 0), W - 1);   // CLAMP_TO_EDGE
-                tc[it] = __ldg(cur.p + g);
-                th[it] = __ldg(hist.p + g);
-            }
+        for (int it = 0; it < 4; ++it) {
+            const size_t g = (size_t)min(max(y0 - 1 + warp_ + 8 * it, 0), H - 1) * W + gx;
+            tc[it] = __ldg(cur.p + g);
+            th[it] = __ldg(hist.p + g);
+        }
+        if (extra) {
+            const size_t g = (size_t)min(max(y0 - 1 + rr, 0), H - 1) * W + min(max(x0 - 1 + xr, 0), W - 1);
+            tc[4] = __ldg(cur.p + g);
+            th[4] = __ldg(hist.p + g);
         }
         if (threadIdx.x < 2 * kT) {     // coordinate tables, :92-102 + PIN-6, while the loads fly
             const bool is_row = threadIdx.x >= kT;
@@ -71,32 +79,28 @@ k_taa_pair(Tex16 cur, Tex16 hist, uint2* __restrict__ out, uint2* __restrict__ t
             }
         }
         // tonemapped YCoCg of the staged texels, two at a time
-        auto store_raw = [&](int it) {
-            const int idx = threadIdx.x + it * 256;
-            const int r = idx / kHalo, c = idx - r * kHalo;
+        auto store_raw = [&](int it, int r, int c) {
             s_h[r][c] = th[it];
-            if (r >= 1 && r <= kT && c >= 1 && c <= kT) s_c[r - 1][c - 1] = tc[it];
+            if (r >= 1 && r <= kT && c >= 1) s_c[r - 1][c - 1] = tc[it];       // c <= 31 here
         };
 #pragma unroll
-        for (int it = 0; it + 1 < kLoads; it += 2) {        // both indices < 1024 + 255 < kTexels?  (it+1)*256+255 = 1023 for it = 2: always in range
-            store_raw(it); store_raw(it + 1);
+        for (int it = 0; it < 4; it += 2) {
+            const int r0 = warp_ + 8 * it, r1 = r0 + 8;
+            store_raw(it, r0, lane_); store_raw(it + 1, r1, lane_);
             if (clamp_on) {
                 const V3P s = rgb_to_ycocg(taa_tonemap_safe(pk3(unpack_rgb_(tc[it]), unpack_rgb_(tc[it + 1]))));   // :120
-                const int i0 = threadIdx.x + it * 256, i1 = i0 + 256;
-                s_nb[i0 / kHalo][i0 % kHalo] = make_float4(lo(s.x), lo(s.y), lo(s.z), 0.0f);
-                s_nb[i1 / kHalo][i1 % kHalo] = make_float4(hi(s.x), hi(s.y), hi(s.z), 0.0f);
+                s_nb[r0][lane_] = make_float4(lo(s.x), lo(s.y), lo(s.z), 0.0f);
+                s_nb[r1][lane_] = make_float4(hi(s.x), hi(s.y), hi(s.z), 0.0f);
             }
         }
-        if (kLoads & 1) {
-            const int it = kLoads - 1, idx = threadIdx.x + it * 256;
-            if (idx < kTexels) {
-                store_raw(it);
-                if (clamp_on) {
-                    const V3 c3 = unpack_rgb_(tc[it]);
-                    const V3 tm = {fdiv_safe(c3.x, fadd(1.0f, c3.x)), fdiv_safe(c3.y, fadd(1.0f, c3.y)), fdiv_safe(c3.z, fadd(1.0f, c3.z))};
-                    const V3 s = rgb_to_ycocg(tm);
-                    s_nb[idx / kHalo][idx % kHalo] = make_float4(s.x, s.y, s.z, 0.0f);
-                }
+        if (extra) {
+            s_h[rr][xr] = th[4];
+            if (rr >= 1 && rr <= kT && xr >= 1 && xr <= kT) s_c[rr - 1][xr - 1] = tc[4];
+            if (clamp_on) {
+                const V3 c3 = unpack_rgb_(tc[4]);
+                const V3 tm = {fdiv_safe(c3.x, fadd(1.0f, c3.x)), fdiv_safe(c3.y, fadd(1.0f, c3.y)), fdiv_safe(c3.z, fadd(1.0f, c3.z))};
+                const V3 s = rgb_to_ycocg(tm);
+                s_nb[rr][xr] = make_float4(s.x, s.y, s.z, 0.0f);
             }
         }
     }
@@ -171,6 +175,68 @@ cudaError_t launch_taa_pair(const void* cur, const void* hist, void* out, void* 
     Timed timed(L, thr_or_null ? ASH_KERNEL_TAA_THRESHOLD : ASH_KERNEL_TAA);
     if (t) k_taa_pair<true><<<grid, 256, 0, L.s>>>(c, h, o, t, pc, threshold);
     else   k_taa_pair<false><<<grid, 256, 0, L.s>>>(c, h, o, t, pc, threshold);
+    return cudaGetLastError();
+}
+
+// =====================================================================================================
+// Bloom downsample, source extent == 2 x destination extent, destination width even
+// (bloom_downsample.frag:16-108; the tap algebra is k_downsample_fast's, post_fast.cu).
+// One thread = two horizontally adjacent destination pixels (lanes) = one 6x4 source window:
+// lane lo uses window columns 0..3, lane hi columns 2..5, fetched with 16 independent loads
+// (8 B, 16 B, 16 B, 8 B per row).
+// =====================================================================================================
+#ifndef ASH_DOWN_MINB
+#define ASH_DOWN_MINB 3
+#endif
+__global__ void __launch_bounds__(256, ASH_DOWN_MINB)
+k_downsample_pair(const uint2* __restrict__ src, int sw, int sh, uint2* __restrict__ dst, int dw, int dh) {
+    const int X = blockIdx.x * 32 + (threadIdx.x & 31), y = blockIdx.y * 8 + (threadIdx.x >> 5);
+    const int x = 2 * X;
+    if (x >= dw || y >= dh) return;
+    // window column i = source texel 4X - 1 + i, CLAMP_TO_EDGE (only columns 0 and 5 can leave the image)
+    const int xl = max(4 * X - 1, 0), xr = min(4 * X + 4, sw - 1);
+    uint2 e0[4], e5[4]; uint4 ma[4], mb[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        const uint2* row = src + (size_t)min(max(2 * y - 1 + j, 0), sh - 1) * sw;
+        e0[j] = __ldg(row + xl);
+        ma[j] = __ldg(reinterpret_cast<const uint4*>(row + 4 * X));          // texels 4X, 4X+1 (32-byte aligned)
+        mb[j] = __ldg(reinterpret_cast<const uint4*>(row + 4 * X + 2));      // texels 4X+2, 4X+3
+        e5[j] = __ldg(row + xr);
+    }
+    V3P hs[4][3];    // hs[j][i] = t[j][i] + t[j][i+1] of each lane's own window
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        const V3 t0 = unpack_rgb_(e0[j]), t1 = unpack_rgb_(make_uint2(ma[j].x, ma[j].y)), t2 = unpack_rgb_(make_uint2(ma[j].z, ma[j].w));
+        const V3 t3 = unpack_rgb_(make_uint2(mb[j].x, mb[j].y)), t4 = unpack_rgb_(make_uint2(mb[j].z, mb[j].w)), t5 = unpack_rgb_(e5[j]);
+        const V3P a0 = pk3(t0, t2), a1 = pk3(t1, t3), a2 = pk3(t2, t4), a3 = pk3(t3, t5);
+        hs[j][0] = add3(a0, a1); hs[j][1] = add3(a1, a2); hs[j][2] = add3(a2, a3);
+    }
+    V3P res = {splat(0.0f), splat(0.0f), splat(0.0f)};
+    P2 sum = splat(0.0f);
+    auto tap = [&](int i, int j, float wt) {
+        const V3P t4 = add3(hs[j][i], hs[j + 1][i]);
+        const P2 luma4 = fadd(fadd(fmul(t4.x, 0.2126f), fmul(t4.y, 0.7152f)), fmul(t4.z, 0.0722f));
+        const P2 w = fdiv_safe(1.0f, ffma(luma4, splat(0.25f), splat(1.0f)));   // 1 / (1 + luma), luma in [0, 65504]   :87-101
+        const P2 k = splat(0.25f * wt);                                          // power of two
+        res = {ffma(fmul(t4.x, w), k, res.x), ffma(fmul(t4.y, w), k, res.y), ffma(fmul(t4.z, w), k, res.z)};
+        sum = ffma(w, splat(wt), sum);
+    };
+    tap(1, 1, 0.25f);                                                        // centre
+    tap(0, 0, 0.0625f); tap(2, 0, 0.0625f); tap(0, 2, 0.0625f); tap(2, 2, 0.0625f);   // a b c d   :25-28
+    tap(0, 1, 0.125f);  tap(2, 1, 0.125f);  tap(1, 0, 0.125f);  tap(1, 2, 0.125f);    // e f g h   :31-34
+    // sum in [1.5e-5, 1], res in [0, 65504]: safe domain                                          :107
+    const V3P o = {fdiv_safe(res.x, sum), fdiv_safe(res.y, sum), fdiv_safe(res.z, sum)};
+    const uint2 oa = pack_rgba16f(lo(o.x), lo(o.y), lo(o.z), 1.0f), ob = pack_rgba16f(hi(o.x), hi(o.y), hi(o.z), 1.0f);
+    *reinterpret_cast<uint4*>(dst + (size_t)y * dw + x) = make_uint4(oa.x, oa.y, ob.x, ob.y);      // dw even: 16-byte aligned
+}
+
+cudaError_t launch_bloom_downsample_pair(const void* src, uint32_t sw, uint32_t sh, void* dst, uint32_t dw,
+                                         uint32_t dh, const Launch& L) {
+    const dim3 grid((dw / 2 + 31) / 32, (dh + 7) / 8);
+    Timed timed(L, ASH_KERNEL_BLOOM_DOWNSAMPLE);
+    k_downsample_pair<<<grid, 256, 0, L.s>>>(static_cast<const uint2*>(src), (int)sw, (int)sh,
+                                             static_cast<uint2*>(dst), (int)dw, (int)dh);
     return cudaGetLastError();
 }
 
