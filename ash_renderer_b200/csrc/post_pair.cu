@@ -10,107 +10,85 @@ __device__ __forceinline__ V3 unpack_rgb_(uint2 t) { V4 v = unpack_rgba16f(t); r
 // =====================================================================================================
 // TAA resolve (+ bloom threshold) — taa_resolve.comp:83-167 (+ bloom_threshold.frag:18-35), no velocity
 // buffer (PIN-12), |jitter delta| <= 0.99 px so that every history tap lies in the tile's 1-texel halo.
-// CTA = 32x32 pixels, 256 threads; thread = 1x4 strip = two (row k, row k+1) pairs.
+// Tile = 32x32 pixels, 256 threads; thread = 1x4 strip = two (row k, row k+1) pairs.
 // The history sampling coordinates are separable: 32 column entries and 32 row entries per tile are
-// computed once (by 64 threads, while the global loads are in flight) instead of once per pixel.
+// computed once (by 64 threads) instead of once per pixel.
+// Staging map (no divisions): step it < 4: warp w stages halo row w + 8*it, lane = halo column (the 32x32
+// block at the halo origin); step 4: threads 0..63 stage rows 32..33, threads 64..131 columns 32..33.
 // =====================================================================================================
 constexpr int kT = 32, kHalo = kT + 2;                                 // 34 x 34 = 1156 staged texels
-constexpr int kLoads = 5;                                            // 4 block rows + 1 fringe texel per thread
 
 struct AxisTap { int i0, i1; float f; float pad; };                  // halo-local texel indices + 8-bit weight
+struct TaaTables { AxisTap col[kT], row[kT]; float blend; };
+struct TaaRaw { uint2 cur[kHalo][kHalo], hist[kHalo][kHalo]; };       // RGBA16F texels, tile + halo
 
-template <bool THRESH>
-__global__ void __launch_bounds__(256, 3)
-k_taa_pair(Tex16 cur, Tex16 hist, uint2* __restrict__ out, uint2* __restrict__ thr,
-           AshTaaPushConstants pc, float threshold) {
-    __shared__ float4 s_nb[kHalo][kHalo];      // tonemapped YCoCg of `current`, tile + halo
-    __shared__ uint2  s_c[kT][kT];             // raw `current`, tile
-    __shared__ uint2  s_h[kHalo][kHalo];       // raw history, tile + halo
-    __shared__ AxisTap s_col[kT], s_row[kT];
-    __shared__ float  s_blend;
-    const int W = cur.W, H = cur.H;
-    const int x0 = blockIdx.x * kT, y0 = blockIdx.y * kT;
-    const bool clamp_on = pc.params[1] > 0.5f;
-    // Staging map (no divisions): step it < 4: warp w stages row w + 8*it, lane = column (the 32x32 block at
-    // halo origin); step 4: threads 0..63 stage rows 32..33, threads 64..131 stage columns 32..33.
-    const int lane_ = threadIdx.x & 31, warp_ = threadIdx.x >> 5;
-    const int xr = threadIdx.x < 64 ? lane_ : 32 + (threadIdx.x & 1);                 // step-4 column
-    const int rr = threadIdx.x < 64 ? 32 + warp_ : (int)(threadIdx.x - 64) >> 1;      // step-4 row
-    const bool extra = threadIdx.x < 132;
-    {   // stage: all global loads of the CTA are issued here, back to back
-        uint2 tc[kLoads], th[kLoads];
-        const int gx = min(max(x0 - 1 + lane_, 0), W - 1);                                             // CLAMP_TO_EDGE
-#pragma unroll
-        for (int it = 0; it < 4; ++it) {
-            const size_t g = (size_t)min(max(y0 - 1 + warp_ + 8 * it, 0), H - 1) * W + gx;
-            tc[it] = __ldg(cur.p + g);
-            th[it] = __ldg(hist.p + g);
-        }
-        if (extra) {
-            const size_t g = (size_t)min(max(y0 - 1 + rr, 0), H - 1) * W + min(max(x0 - 1 + xr, 0), W - 1);
-            tc[4] = __ldg(cur.p + g);
-            th[4] = __ldg(hist.p + g);
-        }
-        if (threadIdx.x < 2 * kT) {     // coordinate tables, :92-102 + PIN-6, while the loads fly
-            const bool is_row = threadIdx.x >= kT;
-            const int k = threadIdx.x & (kT - 1);
-            const float ext = is_row ? pc.screen_params[1] : pc.screen_params[0];
-            const int n = is_row ? H : W, p0 = is_row ? y0 : x0;
-            const float jd = is_row ? fsub(pc.jitter[1], pc.prev_jitter[1]) : fsub(pc.jitter[0], pc.prev_jitter[0]);
-            const float u = fdiv_safe(fadd((float)(p0 + k), 0.5f), ext);            // :92 (extent in [1, 32768])
-            const float vel = fdiv_safe(jd, ext);                                    // :97-99
-            const float hu = gclamp(fsub(u, vel), 0.0f, 1.0f);                       // :102
-            AxisTap t;
-            bilinear_setup(hu, n, t.i0, t.i1, t.f);
-            t.i0 = min(max(t.i0 - (p0 - 1), 0), kHalo - 1);                          // halo-local (clamp only guards rows/cols past the extent)
-            t.i1 = min(max(t.i1 - (p0 - 1), 0), kHalo - 1);
-            t.pad = 0.0f;
-            if (is_row) s_row[k] = t; else s_col[k] = t;
-            if (threadIdx.x == 0) {                                                  // :145-150
-                float blend = pc.params[0];
-                if (pc.params[2] > 0.5f) {
-                    const float sw = pc.screen_params[0], sh = pc.screen_params[1];
-                    const float vx = fdiv_safe(fsub(pc.jitter[0], pc.prev_jitter[0]), sw);
-                    const float vy = fdiv_safe(fsub(pc.jitter[1], pc.prev_jitter[1]), sh);
-                    const float vl = length2(fmul(vx, sw), fmul(vy, sh));
-                    blend = fmul(blend, gclamp(fsub(1.0f, fmul(vl, 0.1f)), 0.0f, 1.0f));
-                }
-                s_blend = blend;
-            }
-        }
-        // tonemapped YCoCg of the staged texels, two at a time
-        auto store_raw = [&](int it, int r, int c) {
-            s_h[r][c] = th[it];
-            if (r >= 1 && r <= kT && c >= 1) s_c[r - 1][c - 1] = tc[it];       // c <= 31 here
-        };
-#pragma unroll
-        for (int it = 0; it < 4; it += 2) {
-            const int r0 = warp_ + 8 * it, r1 = r0 + 8;
-            store_raw(it, r0, lane_); store_raw(it + 1, r1, lane_);
-            if (clamp_on) {
-                const V3P s = rgb_to_ycocg(taa_tonemap_safe(pk3(unpack_rgb_(tc[it]), unpack_rgb_(tc[it + 1]))));   // :120
-                s_nb[r0][lane_] = make_float4(lo(s.x), lo(s.y), lo(s.z), 0.0f);
-                s_nb[r1][lane_] = make_float4(hi(s.x), hi(s.y), hi(s.z), 0.0f);
-            }
-        }
-        if (extra) {
-            s_h[rr][xr] = th[4];
-            if (rr >= 1 && rr <= kT && xr >= 1 && xr <= kT) s_c[rr - 1][xr - 1] = tc[4];
-            if (clamp_on) {
-                const V3 c3 = unpack_rgb_(tc[4]);
-                const V3 tm = {fdiv_safe(c3.x, fadd(1.0f, c3.x)), fdiv_safe(c3.y, fadd(1.0f, c3.y)), fdiv_safe(c3.z, fadd(1.0f, c3.z))};
-                const V3 s = rgb_to_ycocg(tm);
-                s_nb[rr][xr] = make_float4(s.x, s.y, s.z, 0.0f);
-            }
-        }
+struct StageMap {
+    int lane, warp, xr, rr; bool extra;
+    __device__ __forceinline__ StageMap() {
+        lane = threadIdx.x & 31; warp = threadIdx.x >> 5;
+        xr = threadIdx.x < 64 ? lane : 32 + (threadIdx.x & 1);
+        rr = threadIdx.x < 64 ? 32 + warp : (int)(threadIdx.x - 64) >> 1;
+        extra = threadIdx.x < 132;
     }
-    __syncthreads();
+};
+
+// coordinate tables of one tile, :92-102 + PIN-6 (threads 0..63; thread 0 also the blend factor, :145-150)
+__device__ __forceinline__ void taa_tables(TaaTables& tb, const AshTaaPushConstants& pc, int W, int H, int x0, int y0) {
+    if (threadIdx.x >= 2 * kT) return;
+    const bool is_row = threadIdx.x >= kT;
+    const int k = threadIdx.x & (kT - 1);
+    const float ext = is_row ? pc.screen_params[1] : pc.screen_params[0];
+    const int n = is_row ? H : W, p0 = is_row ? y0 : x0;
+    const float jd = is_row ? fsub(pc.jitter[1], pc.prev_jitter[1]) : fsub(pc.jitter[0], pc.prev_jitter[0]);
+    const float u = fdiv_safe(fadd((float)(p0 + k), 0.5f), ext);            // :92 (extent in [1, 32768])
+    const float vel = fdiv_safe(jd, ext);                                    // :97-99
+    const float hu = gclamp(fsub(u, vel), 0.0f, 1.0f);                       // :102
+    AxisTap t;
+    bilinear_setup(hu, n, t.i0, t.i1, t.f);
+    t.i0 = min(max(t.i0 - (p0 - 1), 0), kHalo - 1);                          // halo-local (the clamp only guards rows / columns past the extent)
+    t.i1 = min(max(t.i1 - (p0 - 1), 0), kHalo - 1);
+    t.pad = 0.0f;
+    if (is_row) tb.row[k] = t; else tb.col[k] = t;
+    if (threadIdx.x == 0) {
+        float blend = pc.params[0];
+        if (pc.params[2] > 0.5f) {
+            const float sw = pc.screen_params[0], sh = pc.screen_params[1];
+            const float vx = fdiv_safe(fsub(pc.jitter[0], pc.prev_jitter[0]), sw);
+            const float vy = fdiv_safe(fsub(pc.jitter[1], pc.prev_jitter[1]), sh);
+            const float vl = length2(fmul(vx, sw), fmul(vy, sh));
+            blend = fmul(blend, gclamp(fsub(1.0f, fmul(vl, 0.1f)), 0.0f, 1.0f));
+        }
+        tb.blend = blend;
+    }
+}
+
+// tonemapped YCoCg (:120) of this thread's 5 staged `current` texels -> s_nb, two at a time
+__device__ __forceinline__ void taa_stage_nb(float4 (*s_nb)[kHalo], const uint2 (&tc)[5], const StageMap& m) {
+#pragma unroll
+    for (int it = 0; it < 4; it += 2) {
+        const int r0 = m.warp + 8 * it, r1 = r0 + 8;
+        const V3P s = rgb_to_ycocg(taa_tonemap_safe(pk3(unpack_rgb_(tc[it]), unpack_rgb_(tc[it + 1]))));
+        s_nb[r0][m.lane] = make_float4(lo(s.x), lo(s.y), lo(s.z), 0.0f);
+        s_nb[r1][m.lane] = make_float4(hi(s.x), hi(s.y), hi(s.z), 0.0f);
+    }
+    if (m.extra) {
+        const V3 c3 = unpack_rgb_(tc[4]);
+        const V3 tm = {fdiv_safe(c3.x, fadd(1.0f, c3.x)), fdiv_safe(c3.y, fadd(1.0f, c3.y)), fdiv_safe(c3.z, fadd(1.0f, c3.z))};
+        const V3 s = rgb_to_ycocg(tm);
+        s_nb[m.rr][m.xr] = make_float4(s.x, s.y, s.z, 0.0f);
+    }
+}
+
+// resolve this thread's 1x4 strip of the tile at (x0, y0)
+template <bool THRESH>
+__device__ __forceinline__ void taa_strip(const float4 (*s_nb)[kHalo], const TaaRaw& raw, const TaaTables& tb, bool clamp_on,
+                                          int W, int H, int x0, int y0, uint2* __restrict__ out, uint2* __restrict__ thr,
+                                          float threshold) {
     const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
     const int x = x0 + tx, yb = y0 + 4 * ty;
     if (x >= W || yb >= H) return;
-
-    const AxisTap col = s_col[tx];
-    const float blend = s_blend, ib = fsub(1.0f, blend);
+    const AxisTap col = tb.col[tx];
+    const float blend = tb.blend, ib = fsub(1.0f, blend);
     const float fx = col.f, ifx = fsub(1.0f, fx);
 
     // row-wise min / max of the 3 horizontal neighbours, for the 6 rows this strip touches
@@ -127,14 +105,14 @@ k_taa_pair(Tex16 cur, Tex16 hist, uint2* __restrict__ out, uint2* __restrict__ t
     for (int k = 0; k < 4; k += 2) {                 // lanes: lo = row yb + k, hi = row yb + k + 1
         const int y = yb + k;
         if (y >= H) break;
-        const AxisTap ra = s_row[4 * ty + k], rb = s_row[4 * ty + k + 1];
-        const V3P c = pk3(unpack_rgb_(s_c[4 * ty + k][tx]), unpack_rgb_(s_c[4 * ty + k + 1][tx]));     // :105 (centre tap == texel)
+        const AxisTap ra = tb.row[4 * ty + k], rb = tb.row[4 * ty + k + 1];
+        const V3P c = pk3(unpack_rgb_(raw.cur[4 * ty + k + 1][tx + 1]), unpack_rgb_(raw.cur[4 * ty + k + 2][tx + 1]));   // :105 (centre tap == texel)
         V3P h;                                                                                         // :108 bilinear history
         {
-            const V3P a  = pk3(unpack_rgb_(s_h[ra.i0][col.i0]), unpack_rgb_(s_h[rb.i0][col.i0]));
-            const V3P b  = pk3(unpack_rgb_(s_h[ra.i0][col.i1]), unpack_rgb_(s_h[rb.i0][col.i1]));
-            const V3P cc = pk3(unpack_rgb_(s_h[ra.i1][col.i0]), unpack_rgb_(s_h[rb.i1][col.i0]));
-            const V3P d  = pk3(unpack_rgb_(s_h[ra.i1][col.i1]), unpack_rgb_(s_h[rb.i1][col.i1]));
+            const V3P a  = pk3(unpack_rgb_(raw.hist[ra.i0][col.i0]), unpack_rgb_(raw.hist[rb.i0][col.i0]));
+            const V3P b  = pk3(unpack_rgb_(raw.hist[ra.i0][col.i1]), unpack_rgb_(raw.hist[rb.i0][col.i1]));
+            const V3P cc = pk3(unpack_rgb_(raw.hist[ra.i1][col.i0]), unpack_rgb_(raw.hist[rb.i1][col.i0]));
+            const V3P d  = pk3(unpack_rgb_(raw.hist[ra.i1][col.i1]), unpack_rgb_(raw.hist[rb.i1][col.i1]));
             const P2 fy = pk(ra.f, rb.f), ify = fsub(1.0f, fy);
             const V3P top = add3(scale3(a, ifx), scale3(b, fx));
             const V3P bot = add3(scale3(cc, ifx), scale3(d, fx));
@@ -163,6 +141,48 @@ k_taa_pair(Tex16 cur, Tex16 hist, uint2* __restrict__ out, uint2* __restrict__ t
             if (has_b) thr[(size_t)(y + 1) * W + x] = pack_rgba16f(hi(b.x), hi(b.y), hi(b.z), 1.0f);
         }
     }
+}
+
+// A persistent cp.async double-buffered variant of this kernel (as k_upsample_pipe, post_fast.cu) was
+// measured 20 % SLOWER (0.140 vs 0.116 ms at 4K): three barriers per tile and the extra shared-memory
+// pass outweigh the hidden load latency; the one-shot kernel below keeps its loads in registers.
+template <bool THRESH>
+__global__ void __launch_bounds__(256, 3)
+k_taa_pair(Tex16 cur, Tex16 hist, uint2* __restrict__ out, uint2* __restrict__ thr,
+           AshTaaPushConstants pc, float threshold) {
+    __shared__ float4 s_nb[kHalo][kHalo];      // tonemapped YCoCg of `current`, tile + halo
+    __shared__ TaaRaw s_raw;
+    __shared__ TaaTables s_tb;
+    const int W = cur.W, H = cur.H;
+    const int x0 = blockIdx.x * kT, y0 = blockIdx.y * kT;
+    const bool clamp_on = pc.params[1] > 0.5f;
+    const StageMap m;
+    {   // stage: all global loads of the CTA are issued here, back to back
+        uint2 tc[5], th[5];
+        const int gx = min(max(x0 - 1 + m.lane, 0), W - 1);                                            // CLAMP_TO_EDGE
+#pragma unroll
+        for (int it = 0; it < 4; ++it) {
+            const size_t g = (size_t)min(max(y0 - 1 + m.warp + 8 * it, 0), H - 1) * W + gx;
+            tc[it] = __ldg(cur.p + g);
+            th[it] = __ldg(hist.p + g);
+        }
+        tc[4] = th[4] = make_uint2(0u, 0u);
+        if (m.extra) {
+            const size_t g = (size_t)min(max(y0 - 1 + m.rr, 0), H - 1) * W + min(max(x0 - 1 + m.xr, 0), W - 1);
+            tc[4] = __ldg(cur.p + g);
+            th[4] = __ldg(hist.p + g);
+        }
+        taa_tables(s_tb, pc, W, H, x0, y0);      // while the loads fly
+#pragma unroll
+        for (int it = 0; it < 4; ++it) {
+            s_raw.cur[m.warp + 8 * it][m.lane] = tc[it];
+            s_raw.hist[m.warp + 8 * it][m.lane] = th[it];
+        }
+        if (m.extra) { s_raw.cur[m.rr][m.xr] = tc[4]; s_raw.hist[m.rr][m.xr] = th[4]; }
+        if (clamp_on) taa_stage_nb(s_nb, tc, m);
+    }
+    __syncthreads();
+    taa_strip<THRESH>(s_nb, s_raw, s_tb, clamp_on, W, H, x0, y0, out, thr, threshold);
 }
 
 cudaError_t launch_taa_pair(const void* cur, const void* hist, void* out, void* thr_or_null,
