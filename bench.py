@@ -34,6 +34,10 @@ N_OBJECTS_GRID = (50, 50, 40)      # 100 000 instances
 N_LIGHTS = 8192
 HIZ_LEVELS = 12                    # "full pyramid" (PIN-4)
 METRIC, UNIT = "4k_views_per_sec", "views/s"
+# dram__bytes_read.sum + dram__bytes_write.sum per launch, from the committed `ncu --set full` captures of this
+# very workload (one launch each; re-captured whenever the kernel changes)
+NCU_DRAM_SOURCE = "profiles/r01_d_full_k_taa_pair.md (132.74 MB read + 94.09 MB write)"
+NCU_DRAM_BYTES = {"taa_threshold_fused": 132.741376e6 + 94.085632e6}
 
 
 def workload_name():
@@ -413,6 +417,9 @@ def run_cuda(args):
                                     "share_of_kernel_time": ktime[k] / ktime.sum()}
     dom = max(range(T.KERNEL_COUNT), key=lambda k: ktime[k])
     dom_k = kernels[KERNEL_NAMES[dom]]
+    # DRAM bytes per launch of that kernel (dram__bytes_read.sum + dram__bytes_write.sum) from the committed
+    # `ncu --set full` capture of this workload; null for any other workload or kernel.
+    traffic = NCU_DRAM_BYTES.get(KERNEL_NAMES[dom])          # the workload (cfg5, 4K) is fixed in this file
     # whole-view roofline: compulsory bytes of the staged path / measured time per view
     view_bytes = sum(algorithmic_bytes(k, n_objs, n_lights, st_mean) * kcount[k] / (B * (args.steps + 1))
                      for k in range(T.KERNEL_COUNT) if kcount[k])
@@ -439,7 +446,8 @@ def run_cuda(args):
                 "ms_per_step": e2e_ms / args.steps},
         "gpu_launches": int(round(launches_per_step * args.steps)),
         "roofline": {"bound": "hbm", "kernel": KERNEL_NAMES[dom], "achieved": dom_k["gbs"], "peak": peak, "unit": "GB/s",
-                     "frac": dom_k["gbs"] / peak, "traffic": None, "peak_source": peak_src,
+                     "frac": dom_k["gbs"] / peak, "traffic": traffic, "traffic_source": NCU_DRAM_SOURCE if traffic else None,
+                     "peak_source": peak_src,
                      "whole_view": {"alg_bytes_per_view_staged": view_bytes, "gbs": view_bytes / per_view_s / 1e9,
                                     "frac": view_bytes / per_view_s / 1e9 / peak}},
         "kernels": kernels,
