@@ -8,8 +8,9 @@
 // pixel block loaded as four 128-bit streaming loads (full 128 B lines per warp row).  Mips 1-2
 // reduce in registers, 3-4 by warp shuffles, 5-6 through 64 B of shared memory.  The 16x16 light
 // tile coincides with the mip-4 footprint, so its min/max (on float bits, like the shader's
-// atomicMin/atomicMax on floatBitsToUint) falls out of the same shuffles.  The last CTA to finish
-// (ticket + __threadfence) reduces the remaining tiny levels from L2.
+// atomicMin/atomicMax on floatBitsToUint) falls out of the same shuffles.  The remaining tiny levels
+// (mip 7 and up, <= 60x33 texels at 4K) are reduced by k_pyramid_tail, one CTA ping-ponging through
+// shared memory, launched right behind on the same stream.
 //
 // Algorithmic bytes per launch: 4*W*H (depth) + 4*sum_{L>=1} W_L*H_L (mips) + 8*tiles.
 #include "ash_internal.cuh"
