@@ -31,6 +31,7 @@ EXPORTS = [
     "ashcuda_hiz_level_count", "ashcuda_mip_extent", "ashcuda_kernel_launches", "ashcuda_last_error",
     "ashcuda_version", "ashcuda_profile_kernels", "ashcuda_kernel_time_ms", "ashcuda_upload_view", "ashcuda_download_view",
     "ashcuda_debug_exact_taps",
+    "ashcuda_set_instances", "ashcuda_set_lod_meshes", "ashcuda_set_lod_config", "ashcuda_instancing_finalize",
 ]
 
 
@@ -87,6 +88,10 @@ def load_library():
         "ashcuda_debug_exact_taps": (i32, [i32, i32, i32, C.c_float, C.c_float]),
         "ashcuda_upload_view": (i32, [vp, vp, vp, vp]),
         "ashcuda_download_view": (i32, [vp, vp, vp, vp, vp, vp]),
+        "ashcuda_set_instances": (i32, [vp, vp, vp, vp, u32, i32]),
+        "ashcuda_set_lod_meshes": (i32, [vp, vp, u32, i32]),
+        "ashcuda_set_lod_config": (i32, [vp, vp]),
+        "ashcuda_instancing_finalize": (i32, [vp, vp]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(lib, name)
@@ -286,6 +291,45 @@ class Context:
 
     def stats(self):
         return self.readback(T.BUF_STATS, T.VIEW_STATS)[0]
+
+    # ---- row f-2: LOD selection + instance batching (lod_system.rs / instancing.rs on the device)
+    def set_instances(self, instances, batch_id, lod_mesh_id):
+        pi, d0 = _ptr(instances)
+        pb, d1 = _ptr(batch_id)
+        pm, d2 = _ptr(lod_mesh_id)
+        if not (d0 == d1 == d2):
+            raise AshError(ASH_ERR_INVALID, "set_instances: all three arrays must live on the same side")
+        n = batch_id.shape[0] if isinstance(batch_id, np.ndarray) else batch_id.numel()
+        self._keep["instances"] = (instances, batch_id, lod_mesh_id)
+        self._ck(self._lib.ashcuda_set_instances(self._h, pi, pb, pm, n, d0))
+
+    def set_lod_meshes(self, meshes):
+        p, dev = _ptr(meshes)
+        n = meshes.shape[0] if isinstance(meshes, np.ndarray) else meshes.numel() * meshes.element_size() // T.LOD_MESH.itemsize
+        self._keep["lod_meshes"] = meshes
+        self._ck(self._lib.ashcuda_set_lod_meshes(self._h, p, n, dev))
+
+    def set_lod_config(self, cfg=None):
+        self._ck(self._lib.ashcuda_set_lod_config(self._h, None if cfg is None else np.ascontiguousarray(cfg, T.LOD_CONFIG).ctypes.data))
+
+    def instancing_finalize(self, params):
+        ip = np.ascontiguousarray(params, T.INSTANCING_PARAMS)
+        self._ck(self._lib.ashcuda_instancing_finalize(self._h, ip.ctypes.data))
+
+    def lod_selection(self):
+        return self.readback(T.BUF_LOD_SELECTION, T.LOD_SELECTION)
+
+    def instancing_stats(self):
+        return self.readback(T.BUF_INSTANCING_STATS, T.INSTANCING_STATS)[0]
+
+    def bucket_offsets(self):
+        return self.readback(T.BUF_BUCKET_OFFSETS, np.uint32)
+
+    def instance_draws(self):
+        return self.readback(T.BUF_INSTANCE_DRAWS, T.DRAW_COMMAND)
+
+    def instances_out(self, count):
+        return self.readback(T.BUF_INSTANCES_OUT, T.INSTANCE_DATA, count)
 
     def kernel_launches(self):
         return int(self._lib.ashcuda_kernel_launches(self._h))

@@ -113,6 +113,24 @@ struct ashcuda_ctx {
     uint32_t* cand_idx = nullptr;
     uint32_t* cand_count = nullptr;
     uint8_t*  light_scratch = nullptr;   // tile planes + per-cell candidate lists (light_cull.cu)
+
+    // instancing / LOD (instancing.cu); allocated on the first ashcuda_set_instances
+    const AshInstanceData* inst = nullptr;      AshInstanceData* inst_owned = nullptr;
+    const uint32_t* inst_batch = nullptr;       uint32_t* inst_batch_owned = nullptr;
+    const uint32_t* inst_mesh = nullptr;        uint32_t* inst_mesh_owned = nullptr;
+    const AshLodMesh* lod_meshes = nullptr;     AshLodMesh* lod_meshes_owned = nullptr;
+    uint32_t  n_inst = 0, n_lod_meshes = 0, lod_meshes_cap = 0, n_buckets = 0;
+    AshLodConfig lod_cfg{};
+    uint32_t* batch_mesh = nullptr;             // mesh id of each batch
+    AshLodSelection* lod_sel = nullptr;
+    uint32_t* bucket_of = nullptr;
+    uint32_t* cta_hist = nullptr;
+    uint32_t* bucket_offsets = nullptr;
+    uint32_t* bucket_totals = nullptr;
+    AshInstanceData* inst_out = nullptr;
+    AshIndirectDrawCommand* inst_draws = nullptr;
+    AshInstancingStats* inst_stats = nullptr;
+    bool      have_instancing = false;
     uint32_t* tile_data = nullptr;
     AshViewStats* stats = nullptr;
 
@@ -148,6 +166,15 @@ cudaError_t launch_light_cull(const AshGpuLight* lights, const AshLightCullingPu
                               uint32_t* depth_range, LightCand* cand, uint32_t* cand_idx,
                               uint32_t* cand_count, uint8_t* scratch, uint32_t max_lights,
                               uint32_t* tile_data, AshViewStats* stats, const Launch& L);
+cudaError_t launch_batch_mesh(const uint32_t* batch_id, const uint32_t* mesh_id, uint32_t n, uint32_t n_batches,
+                              uint32_t* batch_mesh, cudaStream_t s);
+size_t instancing_hist_bytes(uint32_t max_objects, uint32_t n_buckets);
+cudaError_t launch_instancing(const AshInstanceData* inst, const uint32_t* batch_id, const uint32_t* mesh_id,
+                              const AshLodMesh* meshes, uint32_t n_meshes, const uint32_t* batch_mesh,
+                              const uint32_t* visibility, const AshInstancingParams& ip, const AshLodConfig& cfg,
+                              uint32_t n_buckets, AshLodSelection* sel, uint32_t* bucket_of, uint32_t* cta_hist,
+                              uint32_t* offsets, uint32_t* totals, AshInstanceData* out, AshIndirectDrawCommand* draws,
+                              AshInstancingStats* stats, const Launch& L);
 size_t light_cull_scratch_bytes(uint32_t W, uint32_t H, uint32_t max_lights, size_t* planes_off, size_t* list_off,
                                 size_t* count_off);
 // `center`: the exact-tap checks passed, so centre / +-1 texel taps may be fetched directly

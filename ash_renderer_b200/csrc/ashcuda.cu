@@ -72,6 +72,7 @@ void ashcuda_default_config(AshCudaConfig* cfg) {
     cfg->enable_post = 1;
     cfg->srgb_encode = 0;
     cfg->concurrent_frontend = 1;
+    cfg->max_batches = 64;
 }
 
 const char* ashcuda_last_error(ashcuda_ctx* ctx) {
@@ -86,7 +87,10 @@ void ashcuda_destroy(ashcuda_ctx* c) {
                      c->objs_owned, c->draws_in_owned, c->visibility, c->vis_bits, c->cta_counts,
                      c->draws_out, c->visible_count, c->lights_owned, c->camera_dev, c->cand,
                      c->cand_idx, c->cand_count, c->light_scratch, c->tile_data, c->stats, c->color_owned,
-                     c->velocity_owned, c->taa[0], c->taa[1], c->bloom_t, c->ldr8};
+                     c->velocity_owned, c->taa[0], c->taa[1], c->bloom_t, c->ldr8,
+                     c->inst_owned, c->inst_batch_owned, c->inst_mesh_owned, c->lod_meshes_owned, c->batch_mesh,
+                     c->lod_sel, c->bucket_of, c->cta_hist, c->bucket_offsets, c->bucket_totals, c->inst_out,
+                     c->inst_draws, c->inst_stats};
     for (void* p : owned) if (p) cudaFree(p);
     for (uint32_t k = 1; k <= ASH_MAX_BLOOM_MIPS; ++k) if (c->bloom.d[k]) cudaFree(c->bloom.d[k]);
     c->prof.release_all();
@@ -183,6 +187,8 @@ static int create_impl(ashcuda_ctx* c) {
     return ASH_OK;
 }
 
+static void lod_config_default(AshLodConfig* k);
+
 int ashcuda_create(ashcuda_ctx** out, int device, uint32_t width, uint32_t height,
                    const AshCudaConfig* cfg_or_null) {
     if (!out) { g_create_error = "ashcuda_create: out is NULL"; return ASH_ERR_INVALID; }
@@ -202,9 +208,11 @@ int ashcuda_create(ashcuda_ctx** out, int device, uint32_t width, uint32_t heigh
     if (!c) { g_create_error = "out of host memory"; return ASH_ERR_OUT_OF_MEMORY; }
     c->device = device; c->W = width; c->H = height;
     if (cfg_or_null) c->cfg = *cfg_or_null; else ashcuda_default_config(&c->cfg);
-    if (c->cfg.bloom_mips > ASH_MAX_BLOOM_MIPS || c->cfg.hiz_levels == 0) {
+    if (c->cfg.max_batches == 0) c->cfg.max_batches = 64;          // configs written before the field existed
+    if (c->cfg.bloom_mips > ASH_MAX_BLOOM_MIPS || c->cfg.hiz_levels == 0 || c->cfg.max_batches > 128) {
         g_create_error = "ashcuda_create: bad config"; delete c; return ASH_ERR_INVALID;
     }
+    lod_config_default(&c->lod_cfg);
     int rc = create_impl(c);
     if (rc != ASH_OK) { g_create_error = c->err; ashcuda_destroy(c); return rc; }
     *out = c;
@@ -479,7 +487,7 @@ int ashcuda_view_run(ashcuda_ctx* c, const AshCudaViewParams* vp) {
     // ---- front end (Hi-Z -> cull, light cull): independent of the post chain of the same view, so it
     //      is forked onto the context's second stream and joined before view_run returns control of
     //      the main stream (inputs uploaded earlier on the main stream are ordered by the fork event)
-    const bool front = (st & (ASH_STAGE_HIZ | ASH_STAGE_CULL | ASH_STAGE_LIGHTS)) != 0;
+    const bool front = (st & (ASH_STAGE_HIZ | ASH_STAGE_CULL | ASH_STAGE_LIGHTS | ASH_STAGE_INSTANCING)) != 0;
     const bool post = (st & (ASH_STAGE_TAA | ASH_STAGE_BLOOM | ASH_STAGE_TONEMAP)) != 0;
     // (per-kernel profiling serialises the view so that event pairs time one kernel each)
     const bool fork = front && post && c->cfg.concurrent_frontend && c->front_stream && c->prof.mask == 0;
@@ -493,6 +501,14 @@ int ashcuda_view_run(ashcuda_ctx* c, const AshCudaViewParams* vp) {
     if (st & (ASH_STAGE_LIGHTS)) rc = ashcuda_set_camera(c, &vp->camera);
     if (!rc && (st & ASH_STAGE_HIZ)) rc = ashcuda_hiz_build(c);
     if (!rc && (st & ASH_STAGE_CULL)) rc = ashcuda_occlusion_cull(c, &vp->cull);
+    if (!rc && (st & ASH_STAGE_INSTANCING)) {        // consumes visibility[] of the cull above
+        AshInstancingParams ip{};
+        std::memcpy(ip.view_proj, vp->cull.view_proj, sizeof(ip.view_proj));
+        std::memcpy(ip.camera_pos, vp->camera.camera_pos, sizeof(ip.camera_pos));
+        ip.screen_size[0] = vp->cull.screen_params[0]; ip.screen_size[1] = vp->cull.screen_params[1];
+        ip.object_count = vp->cull.object_count;
+        rc = ashcuda_instancing_finalize(c, &ip);
+    }
     if (!rc && (st & ASH_STAGE_LIGHTS)) rc = ashcuda_light_cull(c, &vp->light);
     if (fork) {
         cudaError_t e = cudaEventRecord(c->ev_join, c->front_stream);
@@ -507,6 +523,103 @@ int ashcuda_view_run(ashcuda_ctx* c, const AshCudaViewParams* vp) {
     }
     if (rc) return rc;
     ASH_CUDA(c, cudaMemcpyAsync(&c->stats->view_id, &vp->view_id, 4, cudaMemcpyHostToDevice, c->stream));
+    return ASH_OK;
+}
+
+// ------------------------------------------------------------------------------ (f-2) instancing / LOD
+static void lod_config_default(AshLodConfig* k) {          // LodConfig::default(), lod_system.rs:47-57
+    std::memset(k, 0, sizeof(*k));
+    k->mode = ASH_LOD_MODE_SCREEN_SIZE; k->smooth_transitions = 1u; k->transition_width = 0.1f;
+    k->global_bias = 0.0f; k->cull_threshold = 0.001f; k->use_visibility = 1u;
+}
+
+static int instancing_alloc(ashcuda_ctx* c) {
+    if (c->lod_sel) return ASH_OK;
+    const size_t N = c->cfg.max_objects;
+    c->n_buckets = c->cfg.max_batches * ASH_MAX_LOD_LEVELS;
+    ASH_CUDA(c, dmalloc(&c->inst_owned, N * sizeof(AshInstanceData)));
+    ASH_CUDA(c, dmalloc(&c->inst_batch_owned, N * 4));
+    ASH_CUDA(c, dmalloc(&c->inst_mesh_owned, N * 4));
+    ASH_CUDA(c, dmalloc(&c->batch_mesh, (size_t)c->cfg.max_batches * 4));
+    ASH_CUDA(c, dmalloc(&c->lod_sel, N * sizeof(AshLodSelection)));
+    ASH_CUDA(c, dmalloc(&c->bucket_of, N * 4));
+    ASH_CUDA(c, dmalloc(&c->cta_hist, instancing_hist_bytes(c->cfg.max_objects, c->n_buckets)));
+    ASH_CUDA(c, dmalloc(&c->bucket_offsets, ((size_t)c->n_buckets + 1) * 4));
+    ASH_CUDA(c, dmalloc(&c->bucket_totals, (size_t)c->n_buckets * 4));
+    ASH_CUDA(c, dmalloc(&c->inst_out, N * sizeof(AshInstanceData)));
+    ASH_CUDA(c, dmalloc(&c->inst_draws, (size_t)c->n_buckets * sizeof(AshIndirectDrawCommand)));
+    ASH_CUDA(c, dmalloc(&c->inst_stats, sizeof(AshInstancingStats)));
+    ASH_CUDA(c, cudaMemsetAsync(c->inst_stats, 0, sizeof(AshInstancingStats), c->stream));
+    return ASH_OK;
+}
+
+int ashcuda_set_instances(ashcuda_ctx* c, const AshInstanceData* instances, const uint32_t* batch_id,
+                          const uint32_t* lod_mesh_id, uint32_t n, int on_device) {
+    if (!c || (n && (!instances || !batch_id || !lod_mesh_id))) return fail(c, ASH_ERR_INVALID, "set_instances: null");
+    if (n > c->cfg.max_objects) return fail(c, ASH_ERR_INVALID, "set_instances: n > max_objects");
+    ASH_CUDA(c, cudaSetDevice(c->device));
+    int rc = instancing_alloc(c);
+    if (rc) return rc;
+    if (on_device) { c->inst = instances; c->inst_batch = batch_id; c->inst_mesh = lod_mesh_id; }
+    else {
+        for (uint32_t i = 0; i < n; ++i)
+            if (batch_id[i] >= c->cfg.max_batches) return fail(c, ASH_ERR_INVALID, "set_instances: batch id >= max_batches");
+        if (n) {
+            ASH_CUDA(c, cudaMemcpyAsync(c->inst_owned, instances, (size_t)n * sizeof(*instances), cudaMemcpyHostToDevice, c->stream));
+            ASH_CUDA(c, cudaMemcpyAsync(c->inst_batch_owned, batch_id, (size_t)n * 4, cudaMemcpyHostToDevice, c->stream));
+            ASH_CUDA(c, cudaMemcpyAsync(c->inst_mesh_owned, lod_mesh_id, (size_t)n * 4, cudaMemcpyHostToDevice, c->stream));
+        }
+        c->inst = c->inst_owned; c->inst_batch = c->inst_batch_owned; c->inst_mesh = c->inst_mesh_owned;
+    }
+    c->n_inst = n;
+    // a BatchKey names one mesh: take it from the batch's lowest-index object
+    ASH_CUDA(c, launch_batch_mesh(c->inst_batch, c->inst_mesh, n, c->cfg.max_batches, c->batch_mesh, c->stream));
+    c->launches += 2 + (n ? 1 : 0);
+    c->have_instancing = true;
+    return ASH_OK;
+}
+
+int ashcuda_set_lod_meshes(ashcuda_ctx* c, const AshLodMesh* meshes, uint32_t n, int on_device) {
+    if (!c || !meshes || !n) return fail(c, ASH_ERR_INVALID, "set_lod_meshes: null or empty");
+    ASH_CUDA(c, cudaSetDevice(c->device));
+    if (on_device) c->lod_meshes = meshes;
+    else {
+        for (uint32_t i = 0; i < n; ++i)
+            if (meshes[i].level_count > ASH_MAX_LOD_LEVELS) return fail(c, ASH_ERR_INVALID, "set_lod_meshes: level_count > MAX_LOD_LEVELS");
+        if (n > c->lod_meshes_cap) {
+            ASH_CUDA(c, cudaStreamSynchronize(c->stream));
+            if (c->lod_meshes_owned) cudaFree(c->lod_meshes_owned);
+            c->lod_meshes_owned = nullptr; c->lod_meshes_cap = 0;
+            ASH_CUDA(c, dmalloc(&c->lod_meshes_owned, (size_t)n * sizeof(AshLodMesh)));
+            c->lod_meshes_cap = n;
+        }
+        ASH_CUDA(c, cudaMemcpyAsync(c->lod_meshes_owned, meshes, (size_t)n * sizeof(*meshes), cudaMemcpyHostToDevice, c->stream));
+        c->lod_meshes = c->lod_meshes_owned;
+    }
+    c->n_lod_meshes = n;
+    return ASH_OK;
+}
+
+int ashcuda_set_lod_config(ashcuda_ctx* c, const AshLodConfig* k) {
+    if (!c) return fail(c, ASH_ERR_INVALID, "set_lod_config: null");
+    if (k) {
+        if (k->mode > ASH_LOD_MODE_FORCE) return fail(c, ASH_ERR_INVALID, "set_lod_config: unknown mode");
+        c->lod_cfg = *k;
+    } else lod_config_default(&c->lod_cfg);
+    return ASH_OK;
+}
+
+int ashcuda_instancing_finalize(ashcuda_ctx* c, const AshInstancingParams* ip) {
+    if (!c || !ip) return fail(c, ASH_ERR_INVALID, "instancing_finalize: null");
+    if (!c->have_instancing) return fail(c, ASH_ERR_NOT_INITIALIZED, "instancing_finalize: no instances set");
+    if (!c->lod_meshes) return fail(c, ASH_ERR_NOT_INITIALIZED, "instancing_finalize: no LOD meshes set");
+    if (ip->object_count > c->n_inst) return fail(c, ASH_ERR_INVALID, "instancing_finalize: object_count > instances set");
+    if (c->lod_cfg.use_visibility && ip->object_count > c->n_objs)
+        return fail(c, ASH_ERR_INVALID, "instancing_finalize: use_visibility needs a cull result for every object");
+    ASH_CUDA(c, cudaSetDevice(c->device));
+    ASH_CUDA(c, launch_instancing(c->inst, c->inst_batch, c->inst_mesh, c->lod_meshes, c->n_lod_meshes, c->batch_mesh,
+                                  c->visibility, *ip, c->lod_cfg, c->n_buckets, c->lod_sel, c->bucket_of, c->cta_hist,
+                                  c->bucket_offsets, c->bucket_totals, c->inst_out, c->inst_draws, c->inst_stats, c->L()));
     return ASH_OK;
 }
 
@@ -544,9 +657,14 @@ int ashcuda_get(ashcuda_ctx* c, int which, void** dev_ptr, size_t* bytes) {
         case ASH_BUF_TILE_MINMAX:     p = c->tile_minmax; n = tiles * 8; break;
         case ASH_BUF_VISIBILITY_BITS: p = c->vis_bits; n = (((size_t)c->n_objs + 31) / 32) * 4; break;
         case ASH_BUF_BLOOM_THRESHOLD: p = c->bloom_t; n = P * 8; break;
+        case ASH_BUF_LOD_SELECTION:   p = c->lod_sel; n = (size_t)c->n_inst * sizeof(AshLodSelection); break;
+        case ASH_BUF_INSTANCES_OUT:   p = c->inst_out; n = (size_t)c->n_inst * sizeof(AshInstanceData); break;
+        case ASH_BUF_BUCKET_OFFSETS:  p = c->bucket_offsets; n = ((size_t)c->n_buckets + 1) * 4; break;
+        case ASH_BUF_INSTANCE_DRAWS:  p = c->inst_draws; n = (size_t)c->n_buckets * sizeof(AshIndirectDrawCommand); break;
+        case ASH_BUF_INSTANCING_STATS: p = c->inst_stats; n = sizeof(AshInstancingStats); break;
         default: return fail(c, ASH_ERR_NOT_FOUND, "get: unknown buffer id");
     }
-    if (!p) return fail(c, ASH_ERR_NOT_FOUND, "get: buffer not allocated (post chain disabled?)");
+    if (!p) return fail(c, ASH_ERR_NOT_FOUND, "get: buffer not allocated (post chain disabled, or no instances set)");
     *dev_ptr = p; *bytes = n;
     return ASH_OK;
 }

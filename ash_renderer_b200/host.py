@@ -7,6 +7,8 @@ defaults), feeding the C ABI through `backend.Context`.
   HaltonSequence / TaaConfig / TemporalAA               src/renderer/temporal_aa.rs:14-207
   BloomConfig / TonemappingConfig                       features/bloom.rs:9-33, tonemapping.rs:22-44
   RenderFeature / FeatureManager                        features/feature_trait.rs:25-98
+  InstanceData / BatchKey / InstancingManager           src/renderer/instancing.rs:19-277   (row f-2)
+  LodLevel / LodMesh / LodConfig / LodManager           src/renderer/lod_system.rs:15-394    (row f-2)
   CudaComputeFeature                                    the plugin a maintainer registers
 
 The reference's host caps (MAX_LIGHTS 1024, MAX_CULLABLE_OBJECTS 65536, HIZ_LEVELS 10) are the
@@ -333,6 +335,285 @@ class TonemappingConfig:
         pc = np.zeros(1, T.POST_PC)
         pc["exposure"], pc["gamma"], pc["bloom_intensity"] = self.exposure, self.gamma, bloom_intensity
         return pc
+
+
+# ------------------------------------------------------------------ row f-2: instancing + LOD
+MAX_INSTANCES_PER_BATCH = 65536  # instancing.rs:16
+MAX_LOD_LEVELS = 8               # lod_system.rs:15
+
+
+def instance_data_from_matrix(model_cols, color=(1.0, 1.0, 1.0, 1.0), custom=(0.0, 0.0, 0.0, 0.0)):
+    """InstanceData::from_matrix / ::new / with_custom (instancing.rs:37-66): model_row* hold COLUMNS."""
+    d = np.zeros((), T.INSTANCE_DATA)
+    m = np.asarray(model_cols, np.float32).reshape(4, 4)
+    d["model_row0"], d["model_row1"], d["model_row2"], d["model_row3"] = m[0], m[1], m[2], m[3]
+    d["color"], d["custom"] = color, custom
+    return d
+
+
+def instance_position(instance):
+    """InstanceData::position (instancing.rs:68-70)."""
+    return tuple(float(v) for v in np.asarray(instance["model_row3"]).reshape(-1)[:3])
+
+
+class BatchKey:
+    """instancing.rs:74-90"""
+
+    def __init__(self, mesh_id, material_id):
+        self.mesh_id, self.material_id = int(mesh_id), int(material_id)
+
+    def __eq__(self, o):
+        return (self.mesh_id, self.material_id) == (o.mesh_id, o.material_id)
+
+    def __hash__(self):
+        return hash((self.mesh_id, self.material_id))
+
+
+class InstancingStats:
+    """instancing.rs:155-186"""
+
+    def __init__(self):
+        self.total_instances = 0
+        self.batch_count = 0
+        self.instances_culled = 0
+        self.avg_instances_per_batch = 0.0
+
+    def efficiency(self):
+        return 0.0 if self.batch_count == 0 else self.avg_instances_per_batch / MAX_INSTANCES_PER_BATCH
+
+    def format(self):
+        return (f"Instancing: {self.total_instances} instances in {self.batch_count} batches "
+                f"(avg {self.avg_instances_per_batch:.1f}), {self.instances_culled} culled")
+
+
+class InstancingManager:
+    """InstancingManager (instancing.rs:188-277).  Instances are kept in submission order together with
+    the dense id of their BatchKey (first-seen order), which is what the device stage consumes."""
+
+    def __init__(self):
+        self._keys = {}                # BatchKey -> dense batch id
+        self._counts = []              # instances per batch this frame
+        self._instances, self._batch_id = [], []
+        self._stats = InstancingStats()
+        self.frustum_cull = True
+
+    def begin_frame(self):
+        self._counts = [0] * len(self._counts)
+        self._instances, self._batch_id = [], []
+        self._stats = InstancingStats()
+
+    def add_instance(self, key, instance):
+        b = self._keys.setdefault(key, len(self._keys))
+        if b == len(self._counts):
+            self._counts.append(0)
+        if self._counts[b] < MAX_INSTANCES_PER_BATCH:          # :219-223
+            self._counts[b] += 1
+            self._instances.append(instance)
+            self._batch_id.append(b)
+            self._stats.total_instances += 1
+
+    def add_instances(self, key, instances):
+        for i in instances:
+            self.add_instance(key, i)
+
+    def finalize(self):
+        self._stats.batch_count = sum(1 for c in self._counts if c)          # empty batches are dropped, :255
+        if self._stats.batch_count:
+            self._stats.avg_instances_per_batch = float(np.float32(self._stats.total_instances) / np.float32(self._stats.batch_count))
+
+    def stats(self):
+        return self._stats
+
+    def set_frustum_cull(self, enabled):
+        self.frustum_cull = bool(enabled)
+
+    def batch_count_of(self, key):
+        return self._counts[self._keys[key]] if key in self._keys else 0
+
+    def batch_index(self, key):
+        return self._keys.get(key)
+
+    def instance_data(self):
+        return np.array(self._instances, T.INSTANCE_DATA).reshape(-1) if self._instances else np.zeros(0, T.INSTANCE_DATA)
+
+    def batch_ids(self):
+        return np.asarray(self._batch_id, np.uint32)
+
+
+class LodLevel:
+    """lod_system.rs:61-76"""
+
+    def __init__(self, screen_threshold=0.0, distance_threshold=0.0, triangle_count=0, vertex_count=0,
+                 index_offset=0, index_count=0):
+        self.screen_threshold, self.distance_threshold = screen_threshold, distance_threshold
+        self.triangle_count, self.vertex_count = triangle_count, vertex_count
+        self.index_offset, self.index_count = index_offset, index_count
+
+
+class LodMesh:
+    """lod_system.rs:78-124"""
+
+    def __init__(self, levels, bounding_radius):
+        self.levels, self.bounding_radius, self.lod_bias = list(levels), bounding_radius, 0.0
+
+    @staticmethod
+    def single(triangle_count, bounding_radius):
+        return LodMesh([LodLevel(0.0, F32_MAX, triangle_count, triangle_count, 0, triangle_count * 3)], bounding_radius)
+
+    def with_level(self, level):
+        self.levels.append(level)
+        return self
+
+    def level_count(self):
+        return len(self.levels)
+
+    def record(self):
+        """-> one AshLodMesh (levels flattened to MAX_LOD_LEVELS)."""
+        if len(self.levels) > MAX_LOD_LEVELS:
+            raise ValueError("more than MAX_LOD_LEVELS levels")
+        r = np.zeros((), T.LOD_MESH)
+        for i, l in enumerate(self.levels):
+            r["levels"][i] = (l.screen_threshold, l.distance_threshold, l.triangle_count, l.vertex_count,
+                              l.index_offset, l.index_count)
+        r["level_count"], r["bounding_radius"], r["lod_bias"] = len(self.levels), self.bounding_radius, self.lod_bias
+        return r
+
+
+class LodConfig:
+    """lod_system.rs:35-58; mode is "ScreenSize", "Distance" or ("Force", level) (:17-26)."""
+
+    def __init__(self, mode="ScreenSize", smooth_transitions=True, transition_width=0.1, global_bias=0.0,
+                 cull_threshold=0.001):
+        self.mode, self.smooth_transitions, self.transition_width = mode, smooth_transitions, transition_width
+        self.global_bias, self.cull_threshold = global_bias, cull_threshold
+
+    def record(self, use_visibility=True):
+        r = np.zeros(1, T.LOD_CONFIG)
+        if isinstance(self.mode, tuple):
+            r["mode"], r["force_level"] = T.LOD_MODE_FORCE, self.mode[1]
+        else:
+            r["mode"] = {"ScreenSize": T.LOD_MODE_SCREEN_SIZE, "Distance": T.LOD_MODE_DISTANCE}[self.mode]
+        r["smooth_transitions"], r["transition_width"] = int(self.smooth_transitions), self.transition_width
+        r["global_bias"], r["cull_threshold"], r["use_visibility"] = self.global_bias, self.cull_threshold, int(use_visibility)
+        return r
+
+
+class LodSelection:
+    """lod_system.rs:126-137"""
+
+    def __init__(self, level, blend, culled, screen_coverage):
+        self.level, self.blend, self.culled, self.screen_coverage = level, blend, culled, screen_coverage
+
+
+class LodStats:
+    """lod_system.rs:146-183"""
+
+    def __init__(self):
+        self.objects_per_lod = [0] * MAX_LOD_LEVELS
+        self.objects_culled = 0
+        self.triangles_before = 0
+        self.triangles_after = 0
+
+    def reduction_rate(self):
+        return 0.0 if self.triangles_before == 0 else 1.0 - self.triangles_after / self.triangles_before
+
+    def format(self):
+        return (f"LOD: {self.reduction_rate() * 100.0:.1f}% reduction ({self.triangles_before / 1e6:.1f}M → "
+                f"{self.triangles_after / 1e6:.1f}M tris), {self.objects_culled} culled")
+
+    def reset(self):
+        self.__init__()
+
+
+def _rust_as_usize(x):
+    x = np.float32(x)
+    if np.isnan(x) or x <= 0:
+        return 0
+    return int(min(float(x), 4294967295.0))
+
+
+class LodManager:
+    """LodManager (lod_system.rs:139-394): the scalar host version, one object per call, in fp32 with the
+    reference's evaluation order.  The device stage (ashcuda_instancing_finalize) does the same per frame
+    for every visible object; tests compare the two through the oracle."""
+
+    def __init__(self, config=None):
+        self.config = config or LodConfig()
+        self._stats = LodStats()
+
+    def begin_frame(self):
+        self._stats.reset()
+
+    @staticmethod
+    def calculate_screen_coverage(position, radius, view_proj_cols, screen_width, screen_height):   # :207-235
+        f = np.float32
+        m = np.asarray(view_proj_cols, np.float32).reshape(4, 4)
+        p = [f(v) for v in position]
+        with np.errstate(all="ignore"):
+            clip_w = f(f(f(m[0][3] * p[0]) + f(m[1][3] * p[1])) + f(m[2][3] * p[2])) + f(m[3][3] * f(1.0))
+            if clip_w <= 0:
+                return f(0.0)
+            proj_radius = f(radius) / clip_w
+            sw, sh = f(screen_width), f(screen_height)
+            mx = sh if (np.isnan(sw) or sw < sh) and not np.isnan(sh) else sw
+            pixel_radius = f(f(proj_radius * mx) * f(0.5))
+            area = f(f(f(np.pi) * pixel_radius) * pixel_radius)
+            cov = f(area / f(sw * sh))
+            return f(1.0) if np.isnan(cov) or cov > 1 else cov
+
+    def select_lod(self, mesh, world_position, view_proj_cols, camera_position, screen_width, screen_height):   # :238-345
+        f = np.float32
+        st, cfg, n = self._stats, self.config, len(mesh.levels)
+        last = max(n - 1, 0)
+        if n:
+            st.triangles_before += mesh.levels[0].triangle_count
+        if isinstance(cfg.mode, tuple):
+            level = min(cfg.mode[1], last)
+            if n:
+                st.triangles_after += mesh.levels[level].triangle_count
+                st.objects_per_lod[level] += 1
+            return LodSelection(level, 0.0, False, 1.0)
+        cov = self.calculate_screen_coverage(world_position, mesh.bounding_radius, view_proj_cols, screen_width, screen_height)
+        if cov < f(cfg.cull_threshold):
+            st.objects_culled += 1
+            return LodSelection(last, 0.0, True, float(cov))
+        level, blend = last, f(0.0)
+        with np.errstate(all="ignore"):
+            if cfg.mode == "ScreenSize":
+                for i, l in enumerate(mesh.levels):
+                    th = f(l.screen_threshold)
+                    if cov >= th:
+                        if cfg.smooth_transitions and i + 1 < n:
+                            rng = f(th - f(mesh.levels[i + 1].screen_threshold))
+                            if rng > 0:
+                                b = f(f(f(th - cov) / rng) / f(cfg.transition_width))
+                                blend = b if np.isnan(b) else min(max(b, f(0.0)), f(1.0))
+                        level = i
+                        break
+            else:
+                d = [f(f(a) - f(b)) for a, b in zip(world_position, camera_position)]
+                dist = np.sqrt(f(f(f(d[0] * d[0]) + f(d[1] * d[1])) + f(d[2] * d[2])))
+                for i, l in enumerate(mesh.levels):
+                    if dist <= f(l.distance_threshold):
+                        level = i
+                        break
+            x = f(f(f(level) + f(cfg.global_bias)) + f(mesh.lod_bias))
+            if x < 0:
+                x = f(0.0)
+            if x > f(last):
+                x = f(last)
+        biased = _rust_as_usize(x)
+        if biased < n:
+            st.triangles_after += mesh.levels[biased].triangle_count
+            if biased < MAX_LOD_LEVELS:
+                st.objects_per_lod[biased] += 1
+        return LodSelection(biased, float(blend), False, float(cov))
+
+    def stats(self):
+        return self._stats
+
+    def config_mut(self):
+        return self.config
 
 
 # ------------------------------------------------------------------ plugin API

@@ -228,3 +228,46 @@ def random_velocity(W, H, seed=0, still_frac=0.5, max_px=3.0):
     v = rng.uniform(-max_px, max_px, (H, W, 2)) / np.array([W, H])
     v[rng.random((H, W)) < still_frac] = 0.0
     return v.astype(np.float16)
+
+
+# ------------------------------------------------------------------ row f-2: instances + LOD meshes
+def make_lod_meshes(n_meshes=6, seed=7):
+    """LodMesh records with 1..8 levels, descending screen thresholds / ascending distance thresholds."""
+    rng = np.random.default_rng(seed)
+    meshes = np.zeros(n_meshes, T.LOD_MESH)
+    for m in range(n_meshes):
+        n = 1 + (m * 3) % T.MAX_LOD_LEVELS if m else 1
+        th = np.sort(rng.uniform(0.0005, 0.2, n))[::-1].copy()
+        th[-1] = 0.0 if m % 2 == 0 else th[-1]
+        dist = np.sort(rng.uniform(5.0, 120.0, n))
+        tri = (20000 // (2 ** np.arange(n))).astype(np.uint32)
+        for l in range(n):
+            meshes[m]["levels"][l] = (th[l], dist[l], tri[l], tri[l] // 2 + 3, 100000 * m + 3 * int(tri[:l].sum()), 3 * tri[l])
+        meshes[m]["level_count"] = n
+        meshes[m]["bounding_radius"] = rng.uniform(0.3, 2.5)
+        meshes[m]["lod_bias"] = [0.0, 0.0, 1.0, -1.0, 0.4, 2.6][m % 6]
+    return meshes
+
+
+def make_instances(objs, n_batches=5, n_meshes=6, seed=8):
+    """One InstanceData per cull object (same model columns); a batch id and a LodMesh id per object
+    (every object of a batch draws the same mesh, as a BatchKey names one mesh)."""
+    rng = np.random.default_rng(seed)
+    n = len(objs)
+    inst = np.zeros(n, T.INSTANCE_DATA)
+    m = objs["model"]
+    inst["model_row0"], inst["model_row1"], inst["model_row2"], inst["model_row3"] = m[:, 0], m[:, 1], m[:, 2], m[:, 3]
+    inst["color"] = rng.uniform(0, 1, (n, 4)).astype(np.float32)
+    inst["custom"][:, 0] = np.arange(n)
+    batch = rng.integers(0, n_batches, n).astype(np.uint32)
+    mesh_of_batch = (np.arange(n_batches) * 7 + 1) % n_meshes
+    return inst, batch, mesh_of_batch[batch].astype(np.uint32)
+
+
+def instancing_params(cam, n):
+    ip = np.zeros(1, T.INSTANCING_PARAMS)
+    ip["view_proj"][0] = cam.view_proj.astype(np.float32)
+    ip["camera_pos"][0] = [*cam.eye.astype(np.float32), 1.0]
+    ip["screen_size"][0] = [cam.W, cam.H]
+    ip["object_count"] = n
+    return ip

@@ -4,7 +4,8 @@ Sizes are the reference's: CullObjectData 112 B (occlusion_culling.rs:72-91, tes
 IndirectDrawCommand 20 B (:114-120), CullingPushConstants 96 B (:125-136), GpuLight 64 B
 (features/light_culling.rs:28-37), LightCullingPushConstants 16 B (:69-76), CullingCameraData
 208 B (:81-86), TaaPushConstants 48 B (temporal_aa.rs:86-97), PostProcessPushConstants 16 B
-(fullscreen_pass.rs:152-163).  include/ashcuda.h declares the same layouts for C.
+(fullscreen_pass.rs:152-163); row f-2: InstanceData 96 B (instancing.rs:19-34), LodLevel 24 B
+(lod_system.rs:61-76).  include/ashcuda.h declares the same layouts for C.
 """
 import numpy as np
 
@@ -28,13 +29,37 @@ BLOOM_PARAMS = np.dtype([("threshold", "<f4"), ("upsample_intensity", "<f4"), ("
                          ("_padding", "<u4")])
 CONFIG = np.dtype([("max_objects", "<u4"), ("max_lights", "<u4"), ("max_draws", "<u4"),
                    ("hiz_levels", "<u4"), ("bloom_mips", "<u4"), ("enable_post", "<u4"),
-                   ("srgb_encode", "<u4"), ("concurrent_frontend", "<u4"), ("_reserved", "<u4", 8)])
+                   ("srgb_encode", "<u4"), ("concurrent_frontend", "<u4"), ("max_batches", "<u4"),
+                   ("_reserved", "<u4", 7)])
 VIEW_STATS = np.dtype([("view_id", "<u4"), ("total_objects", "<u4"), ("visible_objects", "<u4"),
                        ("tiles", "<u4"), ("sum_tile_lights", "<u4"), ("max_tile_lights", "<u4"),
                        ("overflow_tiles", "<u4"), ("candidate_lights", "<u4")])
 VIEW_PARAMS = np.dtype([("cull", CULLING_PC), ("light", LIGHT_PC), ("camera", CAMERA_DATA),
                         ("taa", TAA_PC), ("bloom", BLOOM_PARAMS), ("post", POST_PC),
                         ("view_id", "<u4"), ("stages", "<u4"), ("_padding", "<u4", 2)])
+
+# ---- row f-2: LOD selection + instance batching
+MAX_LOD_LEVELS, MAX_INSTANCES_PER_BATCH, LOD_NOT_VISIBLE = 8, 65536, 0xFFFFFFFF
+LOD_MODE_SCREEN_SIZE, LOD_MODE_DISTANCE, LOD_MODE_FORCE = 0, 1, 2
+INSTANCE_DATA = np.dtype([("model_row0", "<f4", 4), ("model_row1", "<f4", 4), ("model_row2", "<f4", 4),
+                          ("model_row3", "<f4", 4), ("color", "<f4", 4), ("custom", "<f4", 4)])
+LOD_LEVEL = np.dtype([("screen_threshold", "<f4"), ("distance_threshold", "<f4"), ("triangle_count", "<u4"),
+                      ("vertex_count", "<u4"), ("index_offset", "<u4"), ("index_count", "<u4")])
+LOD_MESH = np.dtype([("levels", LOD_LEVEL, MAX_LOD_LEVELS), ("level_count", "<u4"), ("bounding_radius", "<f4"),
+                     ("lod_bias", "<f4"), ("_padding", "<u4")])
+LOD_CONFIG = np.dtype([("mode", "<u4"), ("force_level", "<u4"), ("smooth_transitions", "<u4"),
+                       ("transition_width", "<f4"), ("global_bias", "<f4"), ("cull_threshold", "<f4"),
+                       ("use_visibility", "<u4"), ("_padding", "<u4")])
+LOD_SELECTION = np.dtype([("level", "<u4"), ("blend", "<f4"), ("culled", "<u4"), ("screen_coverage", "<f4")])
+INSTANCING_STATS = np.dtype([("objects_per_lod", "<u4", MAX_LOD_LEVELS), ("objects_culled", "<u4"),
+                             ("total_instances", "<u4"), ("batch_count", "<u4"), ("avg_instances_per_batch", "<f4"),
+                             ("triangles_before", "<u8"), ("triangles_after", "<u8"), ("instances_dropped", "<u4"),
+                             ("_padding", "<u4")])
+INSTANCING_PARAMS = np.dtype([("view_proj", "<f4", (4, 4)), ("camera_pos", "<f4", 4), ("screen_size", "<f4", 2),
+                              ("object_count", "<u4"), ("_padding", "<u4")])
+assert INSTANCE_DATA.itemsize == 96 and LOD_LEVEL.itemsize == 24 and LOD_MESH.itemsize == 208
+assert LOD_CONFIG.itemsize == 32 and LOD_SELECTION.itemsize == 16 and INSTANCING_STATS.itemsize == 72
+assert INSTANCING_PARAMS.itemsize == 96
 
 assert CULL_OBJECT.itemsize == 112 and DRAW_COMMAND.itemsize == 20 and CULLING_PC.itemsize == 96
 assert GPU_LIGHT.itemsize == 64 and LIGHT_PC.itemsize == 16 and CAMERA_DATA.itemsize == 208
@@ -49,10 +74,12 @@ TILE_STRIDE = 257
 STAGE_HIZ, STAGE_CULL, STAGE_LIGHTS, STAGE_TAA, STAGE_BLOOM, STAGE_TONEMAP = 1, 2, 4, 8, 16, 32
 STAGE_ALL = 0x3F
 STAGE_KEEP_BLOOM = 0x40
+STAGE_INSTANCING = 0x80
 
 BUF_VISIBILITY, BUF_DRAWS_OUT, BUF_VISIBLE_COUNT, BUF_TILE_DATA = 1, 2, 3, 4
 BUF_TAA_OUT, BUF_LDR8, BUF_STATS, BUF_TILE_MINMAX, BUF_VISIBILITY_BITS = 5, 6, 7, 8, 9
 BUF_BLOOM_THRESHOLD = 10
+BUF_LOD_SELECTION, BUF_INSTANCES_OUT, BUF_BUCKET_OFFSETS, BUF_INSTANCE_DRAWS, BUF_INSTANCING_STATS = 11, 12, 13, 14, 15
 
 
 def BUF_HIZ_MIP(i):
@@ -65,5 +92,5 @@ def BUF_BLOOM_MIP(i):
 # kernel classes (ashcuda_profile_kernels / ashcuda_kernel_time_ms)
 (KERNEL_DEPTH_PYRAMID, KERNEL_OCCLUSION_CULL, KERNEL_CULL_COMPACT, KERNEL_LIGHT_PREPASS, KERNEL_LIGHT_TILES,
  KERNEL_TAA, KERNEL_BLOOM_THRESHOLD, KERNEL_BLOOM_DOWNSAMPLE, KERNEL_BLOOM_UPSAMPLE, KERNEL_TONEMAP,
- KERNEL_TAA_THRESHOLD, KERNEL_UPSAMPLE_TONEMAP) = range(12)
-KERNEL_COUNT = 12
+ KERNEL_TAA_THRESHOLD, KERNEL_UPSAMPLE_TONEMAP, KERNEL_INSTANCING) = range(13)
+KERNEL_COUNT = 13

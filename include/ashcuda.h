@@ -124,6 +124,84 @@ typedef struct AshBloomParams {
     uint32_t _padding;
 } AshBloomParams;
 
+/* ---- (f-2) consumers of the cull result: LOD selection + instance batching ------------------------
+ * InstanceData (96 B), src/renderer/instancing.rs:19-34; the fields named model_row* hold COLUMNS
+ * (to_cols_array_2d, :38-46); position() = model_row3.xyz (:68-70). */
+typedef struct AshInstanceData {
+    float model_row0[4], model_row1[4], model_row2[4], model_row3[4];
+    float color[4];
+    float custom[4];
+} AshInstanceData;
+
+#define ASH_MAX_LOD_LEVELS          8u      /* lod_system.rs:15  MAX_LOD_LEVELS          */
+#define ASH_MAX_INSTANCES_PER_BATCH 65536u  /* instancing.rs:16  MAX_INSTANCES_PER_BATCH */
+#define ASH_LOD_NOT_VISIBLE         0xFFFFFFFFu
+
+/* LodLevel (24 B), lod_system.rs:61-76 */
+typedef struct AshLodLevel {
+    float    screen_threshold;
+    float    distance_threshold;
+    uint32_t triangle_count;
+    uint32_t vertex_count;
+    uint32_t index_offset;
+    uint32_t index_count;
+} AshLodLevel;
+
+/* LodMesh (lod_system.rs:78-87) with `levels: Vec<LodLevel>` flattened to MAX_LOD_LEVELS (208 B) */
+typedef struct AshLodMesh {
+    AshLodLevel levels[ASH_MAX_LOD_LEVELS];
+    uint32_t    level_count;
+    float       bounding_radius;
+    float       lod_bias;
+    uint32_t    _padding;
+} AshLodMesh;
+
+/* LodConfig + LodSelectionMode (lod_system.rs:17-58), 32 B */
+#define ASH_LOD_MODE_SCREEN_SIZE 0u
+#define ASH_LOD_MODE_DISTANCE    1u
+#define ASH_LOD_MODE_FORCE       2u
+typedef struct AshLodConfig {
+    uint32_t mode;               /* ASH_LOD_MODE_*                         */
+    uint32_t force_level;        /* LodSelectionMode::Force(level)          */
+    uint32_t smooth_transitions; /* default 1                               */
+    float    transition_width;   /* default 0.1                             */
+    float    global_bias;        /* default 0.0                             */
+    float    cull_threshold;     /* default 0.001                           */
+    uint32_t use_visibility;     /* 1: only objects with visibility[i] == 1 (the occlusion cull's output) are
+                                    selected and batched; 0: every object, as the CPU managers do alone   */
+    uint32_t _padding;
+} AshLodConfig;
+
+/* LodSelection (16 B), lod_system.rs:126-137; level == ASH_LOD_NOT_VISIBLE for objects the cull rejected */
+typedef struct AshLodSelection {
+    uint32_t level;
+    float    blend;
+    uint32_t culled;
+    float    screen_coverage;
+} AshLodSelection;
+
+/* LodStats (lod_system.rs:146-157) + InstancingStats (instancing.rs:155-166), 72 B */
+typedef struct AshInstancingStats {
+    uint32_t objects_per_lod[ASH_MAX_LOD_LEVELS];
+    uint32_t objects_culled;           /* LodStats: too small on screen                            */
+    uint32_t total_instances;          /* InstancingStats: instances accepted into batches          */
+    uint32_t batch_count;              /* non-empty (batch, LOD) buckets = draw calls               */
+    float    avg_instances_per_batch;  /* total_instances / batch_count (0 when there is no batch)  */
+    uint64_t triangles_before;
+    uint64_t triangles_after;
+    uint32_t instances_dropped;        /* beyond MAX_INSTANCES_PER_BATCH in their bucket (:223-226) */
+    uint32_t _padding;
+} AshInstancingStats;
+
+/* Per-view parameters of the standalone call (view_run takes them from its cull / camera blocks) */
+typedef struct AshInstancingParams {
+    float    view_proj[4][4];    /* columns; LodManager::select_lod's view_proj (lod_system.rs:241) */
+    float    camera_pos[4];      /* xyz                                                      */
+    float    screen_size[2];     /* width, height                                            */
+    uint32_t object_count;
+    uint32_t _padding;
+} AshInstancingParams;
+
 /* Library configuration; zero-initialise then call ashcuda_default_config(). */
 typedef struct AshCudaConfig {
     uint32_t max_objects;     /* capacity of the object/visibility/draw buffers            */
@@ -135,7 +213,8 @@ typedef struct AshCudaConfig {
     uint32_t srgb_encode;     /* reserved (swapchain.rs:81-88 sRGB target): must be 0               */
     uint32_t concurrent_frontend; /* 1 (default): view_run runs Hi-Z + cull + light cull on a second
                                      stream, concurrently with the post chain of the same view     */
-    uint32_t _reserved[8];
+    uint32_t max_batches;     /* instancing: distinct batch ids (BatchKey values), default 64, <= 128 */
+    uint32_t _reserved[7];
 } AshCudaConfig;
 
 /* Per-view statistics (OcclusionStats, occlusion_culling.rs:152-185 + tile list stats).
@@ -171,6 +250,7 @@ typedef struct AshCudaViewParams {
 #define ASH_STAGE_BLOOM      0x10u
 #define ASH_STAGE_TONEMAP    0x20u
 #define ASH_STAGE_ALL        0x3Fu
+#define ASH_STAGE_INSTANCING 0x80u /* after the cull: LOD selection + instance batching (not part of ASH_STAGE_ALL) */
 #define ASH_STAGE_KEEP_BLOOM 0x40u /* view_run: also store the bloom buffer U_0 (the fused last upsample +
                                       tonemap otherwise never writes it; ASH_BUF_BLOOM_MIP(0) then holds D_0) */
 
@@ -187,6 +267,11 @@ typedef struct AshCudaViewParams {
 #define ASH_BUF_TILE_MINMAX    8  /* u32[tiles*2]: float bits of tile min/max depth            */
 #define ASH_BUF_VISIBILITY_BITS 9 /* u32[ceil(n/32)] 1 bit per object                          */
 #define ASH_BUF_BLOOM_THRESHOLD 10/* RGBA16F W x H: T = D_0 (staged path only)                 */
+#define ASH_BUF_LOD_SELECTION  11 /* AshLodSelection[object_count]                              */
+#define ASH_BUF_INSTANCES_OUT  12 /* AshInstanceData[total_instances], grouped by bucket, ascending object index inside */
+#define ASH_BUF_BUCKET_OFFSETS 13 /* u32[max_batches*8 + 1]: bucket b = batch*8 + level starts at offsets[b]  */
+#define ASH_BUF_INSTANCE_DRAWS 14 /* AshIndirectDrawCommand[max_batches*8]: one per bucket      */
+#define ASH_BUF_INSTANCING_STATS 15 /* AshInstancingStats                                        */
 
 /* Kernel classes for ashcuda_profile_kernels / ashcuda_kernel_time_ms (device-time accounting;
  * the Vulkan-timestamp TimingScopes of diagnostics/gpu_profiler.rs:25-44 play this role upstream). */
@@ -202,7 +287,8 @@ typedef struct AshCudaViewParams {
 #define ASH_KERNEL_TONEMAP          9
 #define ASH_KERNEL_TAA_THRESHOLD   10  /* fused: TAA resolve + bloom threshold                   */
 #define ASH_KERNEL_UPSAMPLE_TONEMAP 11 /* fused: last bloom upsample + tonemap + 8-bit pack      */
-#define ASH_KERNEL_COUNT           12
+#define ASH_KERNEL_INSTANCING       12 /* LOD select + bucket scan + instance scatter (3 launches)  */
+#define ASH_KERNEL_COUNT           13
 
 typedef struct ashcuda_ctx ashcuda_ctx;
 
@@ -238,6 +324,20 @@ int ashcuda_bloom         (ashcuda_ctx*, const AshBloomParams*);                
 int ashcuda_tonemap       (ashcuda_ctx*, const AshPostProcessPushConstants*);    /* tonemapping.frag           */
 /* the whole view-frame in one call, fused kernels, same results as the staged calls */
 int ashcuda_view_run      (ashcuda_ctx*, const AshCudaViewParams*);
+
+/* ---- (f-2) LOD selection + instance batching on the device ------------------------------------------
+ * One record per cull object (same index): its InstanceData, a dense batch id (the host's BatchKey ->
+ * id map, instancing.rs:74-90) and the LodMesh it draws.  ashcuda_instancing_finalize does, for every
+ * (visible) object in ascending index, what the CPU managers do per frame:
+ *   sel = LodManager::select_lod(mesh, instance.position(), view_proj, camera_pos, w, h)   lod_system.rs:238-345
+ *   if !sel.culled: InstancingManager::add_instance(key(batch, sel.level), instance)        instancing.rs:212-224
+ * then InstancingManager::finalize (:253-263): stats, plus one indirect draw per (batch, level) bucket
+ * {index_count, instance_count, first_index = level.index_offset, 0, first_instance = bucket offset}. */
+int ashcuda_set_instances (ashcuda_ctx*, const AshInstanceData* instances, const uint32_t* batch_id,
+                           const uint32_t* lod_mesh_id, uint32_t n, int on_device);
+int ashcuda_set_lod_meshes(ashcuda_ctx*, const AshLodMesh* meshes, uint32_t n, int on_device);
+int ashcuda_set_lod_config(ashcuda_ctx*, const AshLodConfig*);      /* NULL: LodConfig::default(), :47-57 */
+int ashcuda_instancing_finalize(ashcuda_ctx*, const AshInstancingParams*);
 
 /* --- whole-view host I/O for callers whose frame data lives in host memory (the e2e path):
  *     upload = set_depth + set_color from host pointers (pinned memory makes the copies async);

@@ -34,9 +34,9 @@ POST_PC_DTYPE = np.dtype([("exposure", "<f4"), ("gamma", "<f4"), ("bloom_intensi
 
 def build(force=False):
     """Compile libashoracle.so with the committed Makefile (g++ -O2 -fopenmp -ffp-contract=off)."""
-    src = os.path.join(_HERE, "ash_oracle.cpp")
+    srcs = [os.path.join(_HERE, f) for f in ("ash_oracle.cpp", "ash_oracle_instancing.cpp")]
     if (not force and os.path.exists(_LIB_PATH)
-            and os.path.getmtime(_LIB_PATH) >= os.path.getmtime(src)):
+            and os.path.getmtime(_LIB_PATH) >= max(os.path.getmtime(f) for f in srcs)):
         return _LIB_PATH
     env = dict(os.environ)
     env.pop("CXX", None)
@@ -200,3 +200,52 @@ def tonemap(hdr, bloom, pc):
     out = np.empty((H, W, 4), np.uint8)
     lib().ash_oracle_tonemap(_p(hdr), _p(bloom), W, H, _p(pc), _p(out))
     return out
+
+
+# ---- row f-2 (oracle/ash_oracle_instancing.cpp): lod_system.rs + instancing.rs, serially
+INSTANCE_DTYPE = np.dtype([("model_row0", "<f4", 4), ("model_row1", "<f4", 4), ("model_row2", "<f4", 4),
+                           ("model_row3", "<f4", 4), ("color", "<f4", 4), ("custom", "<f4", 4)])
+LOD_LEVEL_DTYPE = np.dtype([("screen_threshold", "<f4"), ("distance_threshold", "<f4"), ("triangle_count", "<u4"),
+                            ("vertex_count", "<u4"), ("index_offset", "<u4"), ("index_count", "<u4")])
+LOD_MESH_DTYPE = np.dtype([("levels", LOD_LEVEL_DTYPE, 8), ("level_count", "<u4"), ("bounding_radius", "<f4"),
+                           ("lod_bias", "<f4"), ("_padding", "<u4")])
+LOD_CONFIG_DTYPE = np.dtype([("mode", "<u4"), ("force_level", "<u4"), ("smooth_transitions", "<u4"),
+                             ("transition_width", "<f4"), ("global_bias", "<f4"), ("cull_threshold", "<f4"),
+                             ("use_visibility", "<u4"), ("_padding", "<u4")])
+LOD_SELECTION_DTYPE = np.dtype([("level", "<u4"), ("blend", "<f4"), ("culled", "<u4"), ("screen_coverage", "<f4")])
+INSTANCING_STATS_DTYPE = np.dtype([("objects_per_lod", "<u4", 8), ("objects_culled", "<u4"), ("total_instances", "<u4"),
+                                   ("batch_count", "<u4"), ("avg_instances_per_batch", "<f4"),
+                                   ("triangles_before", "<u8"), ("triangles_after", "<u8"),
+                                   ("instances_dropped", "<u4"), ("_padding", "<u4")])
+INSTANCING_PARAMS_DTYPE = np.dtype([("view_proj", "<f4", (4, 4)), ("camera_pos", "<f4", 4), ("screen_size", "<f4", 2),
+                                    ("object_count", "<u4"), ("_padding", "<u4")])
+
+
+def screen_coverage(view_proj_cols, position, radius, width, height):
+    """LodManager::calculate_screen_coverage (lod_system.rs:207-235); view_proj as 4 columns."""
+    f = lib().ash_oracle_screen_coverage
+    f.restype = C.c_float
+    f.argtypes = [C.c_void_p, C.c_void_p, C.c_float, C.c_float, C.c_float]
+    vp = _c(view_proj_cols, np.float32)
+    pos = _c(position, np.float32)
+    return float(f(_p(vp), _p(pos), radius, width, height))
+
+
+def instancing(instances, batch_id, mesh_id, meshes, params, cfg, n_batches, visibility=None):
+    """Whole frame of select_lod + add_instance + finalize; returns (sel, out, offsets, draws, stats)."""
+    inst, bid, mid = _c(instances, INSTANCE_DTYPE), _c(batch_id, np.uint32), _c(mesh_id, np.uint32)
+    ms, ip, k = _c(meshes, LOD_MESH_DTYPE), _c(params, INSTANCING_PARAMS_DTYPE), _c(cfg, LOD_CONFIG_DTYPE)
+    n = int(ip.reshape(-1)[0]["object_count"])
+    nb = int(n_batches) * 8
+    vis = None if visibility is None else _c(visibility, np.uint32)
+    sel = np.zeros(n, LOD_SELECTION_DTYPE)
+    out = np.zeros(max(n, 1), INSTANCE_DTYPE)
+    offsets = np.zeros(nb + 1, np.uint32)
+    draws = np.zeros(nb, DRAW_DTYPE)
+    stats = np.zeros(1, INSTANCING_STATS_DTYPE)
+    f = lib().ash_oracle_instancing
+    f.restype = None
+    f.argtypes = [C.c_void_p] * 4 + [C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32] + [C.c_void_p] * 5
+    f(_p(inst), _p(bid), _p(mid), _p(ms), len(ms.reshape(-1)), None if vis is None else _p(vis), _p(ip), _p(k), int(n_batches),
+      _p(sel), _p(out), _p(offsets), _p(draws), _p(stats))
+    return sel, out[:int(offsets[-1])], offsets, draws, stats[0]

@@ -65,6 +65,13 @@ def test_header_struct_sizes_compile(tmp_path):
                    "_Static_assert(sizeof(AshBloomParams)==16,\"\");\n"
                    "_Static_assert(sizeof(AshCudaConfig)==64,\"\");\n"
                    "_Static_assert(sizeof(AshViewStats)==32,\"\");\n"
+                   "_Static_assert(sizeof(AshInstanceData)==96,\"\");\n"          # instancing.rs:19-34
+                   "_Static_assert(sizeof(AshLodLevel)==24,\"\");\n"
+                   "_Static_assert(sizeof(AshLodMesh)==208,\"\");\n"
+                   "_Static_assert(sizeof(AshLodConfig)==32,\"\");\n"
+                   "_Static_assert(sizeof(AshLodSelection)==16,\"\");\n"
+                   "_Static_assert(sizeof(AshInstancingStats)==72,\"\");\n"
+                   "_Static_assert(sizeof(AshInstancingParams)==96,\"\");\n"
                    f"_Static_assert(sizeof(AshCudaViewParams)=={T.VIEW_PARAMS.itemsize},\"\");\n"
                    "int main(void){return 0;}\n")
     subprocess.run(["/usr/bin/gcc", "-std=c11", "-I", os.path.join(ROOT, "include"), "-c", str(src),
@@ -77,6 +84,7 @@ def test_default_config_mirrors_reference_constants():
     assert cfg["max_lights"][0] == 1024        # features/light_culling.rs:17
     assert cfg["hiz_levels"][0] == 10          # occlusion_culling.rs:21
     assert cfg["bloom_mips"][0] == 5           # features/bloom.rs:29
+    assert cfg["max_batches"][0] == 64
 
 
 def test_null_and_bad_arguments_do_not_crash():

@@ -160,6 +160,112 @@ def test_occlusion_cull_edge_cases(backend, oracle):
             assert c.visible_count() == 0
 
 
+# ------------------------------------------------------------------ row f-2: LOD selection + instance batching
+def _instancing_scene(W, H, grid, seed, n_batches):
+    cam, objs, draws, depth = _cull_scene(W, H, grid, seed=seed)
+    meshes = synth.make_lod_meshes(6, seed=seed + 1)
+    inst, batch, mesh = synth.make_instances(objs, n_batches, 6, seed=seed + 2)
+    return cam, objs, draws, depth, meshes, inst, batch, mesh
+
+
+def _compare_instancing(c, ref, n, n_batches):
+    sel, out, offsets, draws, stats = ref
+    got_sel = c.lod_selection()[:n]
+    assert np.array_equal(got_sel.view(np.uint32), sel.view(np.uint32)), "LodSelection (level, blend bits, culled, coverage bits)"
+    nb = n_batches * 8
+    got_off = c.bucket_offsets()
+    assert np.array_equal(got_off[:nb + 1], offsets)
+    assert np.array_equal(c.instance_draws()[:nb], draws)
+    got_out = c.instances_out(int(offsets[-1]))
+    assert got_out.tobytes() == out.tobytes(), "instance streams (bucket order, ascending object index inside)"
+    gs = c.instancing_stats()
+    for k in ("objects_per_lod", "objects_culled", "total_instances", "batch_count", "triangles_before",
+              "triangles_after", "instances_dropped"):
+        assert np.array_equal(gs[k], stats[k]), k
+    assert np.float32(gs["avg_instances_per_batch"]).view(np.uint32) == np.float32(stats["avg_instances_per_batch"]).view(np.uint32)
+
+
+@pytest.mark.parametrize("mode,use_vis,grid", [
+    ("ScreenSize", True, (12, 10, 9)), ("ScreenSize", False, (40, 50, 50)), ("Distance", True, (25, 20, 20)),
+    (("Force", 1), True, (12, 10, 9)), (("Force", 7), False, (7, 5, 3)), ("ScreenSize", True, (1, 1, 1))])
+def test_instancing_bit_exact(backend, oracle, mode, use_vis, grid):
+    from ash_renderer_b200 import host
+    W, H, n_batches = 1920, 1080, 9
+    cam, objs, draws, depth, meshes, inst, batch, mesh = _instancing_scene(W, H, grid, seed=sum(grid), n_batches=n_batches)
+    n = len(objs)
+    cfg = host.LodConfig(mode=mode, global_bias=0.3 if mode == "Distance" else 0.0).record(use_visibility=use_vis)
+    pc = cam.cull_pc(n, 10)
+    vis, _, _ = oracle.occlusion_cull(objs, draws, pc, depth)
+    ip = synth.instancing_params(cam, n)
+    ref = oracle.instancing(inst, batch, mesh, meshes, ip, cfg, n_batches, vis if use_vis else None)
+    with _ctx(backend, W, H, enable_post=0, max_batches=n_batches) as c:
+        c.set_depth(depth)
+        c.set_objects(objs, draws)
+        c.set_instances(inst, batch, mesh)
+        c.set_lod_meshes(meshes)
+        c.set_lod_config(cfg)
+        c.hiz_build()
+        c.occlusion_cull(pc)
+        c.instancing_finalize(ip)
+        _compare_instancing(c, ref, n, n_batches)
+        c.instancing_finalize(ip)                        # idempotent: stats and streams are rebuilt, not accumulated
+        _compare_instancing(c, ref, n, n_batches)
+    if n > 100:
+        assert ref[4]["batch_count"] > 1 and 0 < ref[4]["total_instances"] <= n
+
+
+def test_instancing_batch_cap_and_errors(backend, oracle):
+    from ash_renderer_b200 import host
+    cam = synth.Camera((0.0, 2.0, 22.0), (0, 0, 0), 640, 360)
+    n = 70000
+    inst = np.zeros(n, T.INSTANCE_DATA)
+    inst["model_row3"][:, 3] = 1.0
+    inst["custom"][:, 0] = np.arange(n)
+    zero = np.zeros(n, np.uint32)
+    meshes = synth.make_lod_meshes(1, seed=1)
+    cfg = host.LodConfig(cull_threshold=0.0).record(use_visibility=False)
+    ip = synth.instancing_params(cam, n)
+    ref = oracle.instancing(inst, zero, zero, meshes, ip, cfg, 2)
+    assert ref[4]["total_instances"] == 65536 and ref[4]["instances_dropped"] == n - 65536      # instancing.rs:219-223
+    with _ctx(backend, 640, 360, enable_post=0, max_batches=2) as c:
+        with pytest.raises(backend.AshError) as e:
+            c.instancing_finalize(ip)
+        assert e.value.code == backend.ASH_ERR_NOT_INITIALIZED            # FeatureNotInitialized: nothing set yet
+        c.set_instances(inst, zero, zero)
+        with pytest.raises(backend.AshError):
+            c.instancing_finalize(ip)                                     # no LOD meshes
+        c.set_lod_meshes(meshes)
+        c.set_lod_config(cfg)
+        c.instancing_finalize(ip)
+        _compare_instancing(c, ref, n, 2)
+        with pytest.raises(backend.AshError):
+            c.set_instances(inst, zero + 2, zero)                         # batch id >= max_batches
+
+
+def test_view_run_with_instancing_stage(backend, oracle):
+    from ash_renderer_b200 import host
+    W, H, n_batches = 1280, 720, 4
+    cam, objs, draws, depth, meshes, inst, batch, mesh = _instancing_scene(W, H, (14, 12, 10), seed=21, n_batches=n_batches)
+    n = len(objs)
+    pc = cam.cull_pc(n, 10)
+    vis, _, cnt = oracle.occlusion_cull(objs, draws, pc, depth)
+    cfg = host.LodConfig().record(use_visibility=True)
+    ref = oracle.instancing(inst, batch, mesh, meshes, synth.instancing_params(cam, n), cfg, n_batches, vis)
+    vp = np.zeros(1, T.VIEW_PARAMS)
+    vp["cull"], vp["camera"], vp["light"] = pc, cam.camera_data(), cam.light_pc(0)
+    vp["stages"] = T.STAGE_HIZ | T.STAGE_CULL | T.STAGE_INSTANCING
+    with _ctx(backend, W, H, enable_post=0, max_batches=n_batches) as c:
+        c.set_depth(depth)
+        c.set_objects(objs, draws)
+        c.set_instances(inst, batch, mesh)
+        c.set_lod_meshes(meshes)
+        c.set_lod_config(cfg)
+        c.view_run(vp)
+        assert c.visible_count() == cnt
+        _compare_instancing(c, ref, n, n_batches)
+        assert c.instancing_stats()["objects_culled"] + int(c.instancing_stats()["objects_per_lod"].sum()) == cnt
+
+
 # ------------------------------------------------------------------ light cull
 def _compare_tile_lists(got, ref):
     assert got.shape == ref.shape
