@@ -117,13 +117,16 @@ def algorithmic_bytes(kclass, n_objs, n_lights, st):
         9: 2 * c * P + 4 * P,
         10: 4 * c * P,                                                       # fused TAA + threshold: cur, hist in; out, T out
         11: c * (bl[1] + 2 * P) + 4 * P,                                     # fused last upsample + tonemap
+        # row f-2 (--instancing): visibility + batch id + mesh id, position of visible objects, selection out,
+        # kept instances in + out, one draw per bucket
+        12: 12 * n_objs + 16 * V + 16 * n_objs + 192 * int(st.get("kept_instances", 0)) + 20 * int(st.get("buckets", 0)),
     }
     return float(table[kclass])
 
 
 KERNEL_NAMES = ["depth_pyramid", "occlusion_cull", "cull_compact", "light_prepass", "light_tiles", "taa_resolve",
                 "bloom_threshold", "bloom_downsample", "bloom_upsample", "tonemap", "taa_threshold_fused",
-                "upsample_tonemap_fused"]
+                "upsample_tonemap_fused", "instancing"]
 
 
 # ------------------------------------------------------------------ clocks sampling (B200_PROFILING.md)
@@ -248,7 +251,7 @@ def run_reference(args):
 def run_cuda(args):
     import torch
     import torch.distributed as dist
-    from ash_renderer_b200 import backend, types as T
+    from ash_renderer_b200 import backend, synth, types as T
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -269,6 +272,15 @@ def run_cuda(args):
     d_draws = torch.from_numpy(draws.view(np.uint8)).cuda()
     d_lights = torch.from_numpy(lights.view(np.uint8)).cuda()
 
+    inst_scene = None
+    if args.instancing:
+        from ash_renderer_b200 import host as H_
+        meshes = synth.make_lod_meshes(6, seed=7)
+        inst, batch, mesh = synth.make_instances(objs, 16, 6, seed=8)
+        inst_scene = {"meshes": meshes, "inst": inst, "batch": batch, "mesh": mesh, "cfg": H_.LodConfig().record(use_visibility=True),
+                      "d_inst": torch.from_numpy(inst.view(np.uint8)).cuda(), "d_batch": torch.from_numpy(batch.view(np.int32)).cuda(),
+                      "d_mesh": torch.from_numpy(mesh.view(np.int32)).cuda(), "d_meshes": torch.from_numpy(meshes.view(np.uint8)).cuda()}
+
     host_views = [make_view_inputs(rank * B + v, max(total_views, 1024), objs) for v in range(distinct)]
     streams = [torch.cuda.Stream() for _ in range(args.streams)]
     slots = []
@@ -278,7 +290,13 @@ def run_cuda(args):
         c.set_stream(streams[v % args.streams].cuda_stream)
         c.set_objects(d_objs, d_draws)
         c.upload_lights(d_lights)
-        slot = {"ctx": c, "vp": view_params(cam, n_objs, n_lights, taa_pc, rank * B + v),
+        vparams = view_params(cam, n_objs, n_lights, taa_pc, rank * B + v)
+        if inst_scene:
+            c.set_instances(inst_scene["d_inst"], inst_scene["d_batch"], inst_scene["d_mesh"])
+            c.set_lod_meshes(inst_scene["d_meshes"])
+            c.set_lod_config(inst_scene["cfg"])
+            vparams["stages"] |= T.STAGE_INSTANCING
+        slot = {"ctx": c, "vp": vparams,
                 "d_depth": torch.from_numpy(depth).cuda(), "d_hdr": torch.from_numpy(hdr.view(np.uint16)).cuda(),
                 "h_depth": torch.from_numpy(depth).pin_memory(), "h_hdr": torch.from_numpy(hdr.view(np.uint16)).pin_memory()}
         tiles = ((W + 15) // 16) * ((H + 15) // 16)
@@ -378,6 +396,25 @@ def run_cuda(args):
         s["ctx"].set_stream(streams[v % args.streams].cuda_stream)
     stats = [s["ctx"].stats() for s in slots]
     st_mean = {f: float(np.mean([st[f] for st in stats])) for f in T.VIEW_STATS.names}
+    widened = None
+    if inst_scene:
+        ist = [s["ctx"].instancing_stats() for s in slots]
+        st_mean["kept_instances"] = float(np.mean([x["total_instances"] for x in ist]))
+        st_mean["buckets"] = 16 * 8
+        widened = {"row": "f-2: LodManager::select_lod + InstancingManager::add_instance/finalize on the device",
+                   "instances": n_objs, "batches": 16, "lod_meshes": 6,
+                   "kept_instances_mean": st_mean["kept_instances"],
+                   "objects_culled_by_lod_mean": float(np.mean([x["objects_culled"] for x in ist])),
+                   "draw_calls_mean": float(np.mean([x["batch_count"] for x in ist])),
+                   "triangle_reduction_mean": float(np.mean([1.0 - x["triangles_after"] / max(int(x["triangles_before"]), 1) for x in ist]))}
+        if world == 1 and args.cpu_views > 0:     # the serial CPU managers on the same scene (oracle restatement)
+            from oracle import oracle as O
+            cam0 = host_views[0][0]
+            vis0 = slots[0]["ctx"].visibility()
+            t0 = time.perf_counter()
+            O.instancing(inst_scene["inst"], inst_scene["batch"], inst_scene["mesh"], inst_scene["meshes"],
+                         synth.instancing_params(cam0, n_objs), inst_scene["cfg"], 16, vis0)
+            widened["cpu_ms_per_view"] = (time.perf_counter() - t0) * 1e3
 
     # ---- end-to-end through host buffers
     e2e_ms = timed(step_e2e, args.steps, 2)
@@ -434,7 +471,8 @@ def run_cuda(args):
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
         "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic",
-        "config": {"workload": workload_name(), "views_per_gpu_per_step": B, "distinct_view_inputs_per_gpu": distinct,
+        "config": {"workload": workload_name() + (" + LOD selection / instance batching (--instancing)" if inst_scene else ""),
+                   "views_per_gpu_per_step": B, "distinct_view_inputs_per_gpu": distinct,
                    "streams": args.streams, "concurrent_frontend": True,
                    "kernel_timing": f"same {args.steps} steps repeated serialised (1 stream, no fork) with CUDA events around each launch: "
                                     f"{prof_ms / args.steps:.3f} ms/step", "l2": f"inputs larger than L2: {B} views x 99.5 MB of depth+HDR per step per GPU",
@@ -451,6 +489,7 @@ def run_cuda(args):
                      "whole_view": {"alg_bytes_per_view_staged": view_bytes, "gbs": view_bytes / per_view_s / 1e9,
                                     "frac": view_bytes / per_view_s / 1e9 / peak}},
         "kernels": kernels,
+        "widened": widened,
         "cpu_baseline": {"value": cpu_v, "unit": UNIT, "cores": cpu_cores, "kind": "port",
                          "sample": f"{cpu_n} full 4K view(s) of the same workload through the OpenMP CPU oracle"},
     }
@@ -469,6 +508,9 @@ def main():
     ap.add_argument("--distinct", type=int, default=4, help="distinct synthetic depth/HDR inputs generated per GPU (host setup cost)")
     ap.add_argument("--streams", type=int, default=4)
     ap.add_argument("--cpu-views", type=int, default=2)
+    ap.add_argument("--instancing", action="store_true",
+                    help="widened path (SURVEY 8.6 row f-2): also run LOD selection + instance batching after the cull; "
+                         "not part of the headline workload, reported under \"widened\"")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)
