@@ -11,7 +11,8 @@
 // (Mat4 * Vec4 = ((x_axis*v.x + y_axis*v.y) + z_axis*v.z) + w_axis*v.w, no FMA), PIN-1.
 //
 //   k_lod_select       1 thread / object: selection, stats, bucket id, per-CTA bucket histogram
-//   k_bucket_scan      1 CTA: per-bucket exclusive scan over CTAs (in place), bucket offsets, draws, stats
+//   k_bucket_scan_ctas 1 warp / bucket: exclusive scan of the per-CTA counts
+//   k_bucket_offsets   1 CTA: bucket offsets, one indirect draw per bucket, finalize() statistics
 //   k_instance_scatter 1 thread / object: ordered slot = CTA base + earlier warps + rank in warp; 96 B copy
 //
 // Algorithmic bytes per call: N*(4 + 4 + 4) (visibility, batch id, mesh id) + 12 B position per visible
@@ -143,23 +144,41 @@ k_lod_select(const AshInstanceData* __restrict__ inst, const uint32_t* __restric
     if (threadIdx.x == 1 && s_tri[1]) atomicAdd(reinterpret_cast<unsigned long long*>(&stats->triangles_after), s_tri[1]);
 }
 
-// One CTA of 1024 threads, thread b = bucket b (n_buckets <= 1024): column scan over the CTAs (coalesced
-// across threads), then a block scan of the kept counts.
+// Per-bucket exclusive scan over the CTAs: one warp per bucket, lanes stride over CTAs (n_ctas x n_buckets is
+// small: 391 x 128 at 100 k objects / 16 batches).  cta_base[c][b] = slots taken by CTAs < c in bucket b.
+__global__ void __launch_bounds__(256)
+k_bucket_scan_ctas(const uint32_t* __restrict__ cta_hist, uint32_t n_ctas, uint32_t n_buckets,
+                   uint32_t* __restrict__ cta_base, uint32_t* __restrict__ totals) {
+    const uint32_t b = blockIdx.x * 8u + (threadIdx.x >> 5), lane = threadIdx.x & 31u;
+    if (b >= n_buckets) return;
+    uint32_t running = 0;
+    for (uint32_t c0 = 0; c0 < n_ctas; c0 += 32u) {
+        const uint32_t c = c0 + lane;
+        const uint32_t v = c < n_ctas ? cta_hist[(size_t)c * n_buckets + b] : 0u;
+        uint32_t incl = v;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, incl, d);
+            if ((int)lane >= d) incl += t;
+        }
+        if (c < n_ctas) cta_base[(size_t)c * n_buckets + b] = running + incl - v;
+        running += __shfl_sync(0xFFFFFFFFu, incl, 31);
+    }
+    if (lane == 0) totals[b] = running;
+}
+
+// One CTA, thread b = bucket b (n_buckets <= 1024): bucket offsets (kept = min(total, MAX_INSTANCES_PER_BATCH)),
+// one indirect draw per bucket {index_count, instance_count, first_index, vertex_offset = 0, first_instance},
+// and InstancingManager::finalize's statistics.
 __global__ void __launch_bounds__(1024)
-k_bucket_scan(uint32_t* __restrict__ cta_hist, uint32_t n_ctas, uint32_t n_buckets, uint32_t* __restrict__ offsets, uint32_t* __restrict__ totals, AshInstancingStats* __restrict__ stats) {
+k_bucket_offsets(const uint32_t* __restrict__ totals, uint32_t n_buckets, const uint32_t* __restrict__ batch_mesh,
+                 const AshLodMesh* __restrict__ meshes, uint32_t n_meshes, uint32_t* __restrict__ offsets,
+                 AshIndirectDrawCommand* __restrict__ draws, AshInstancingStats* __restrict__ stats) {
     __shared__ uint32_t s_scan[1024];
     __shared__ uint32_t s_nonempty, s_dropped;
     const uint32_t b = threadIdx.x;
     if (b == 0) { s_nonempty = 0u; s_dropped = 0u; }
-    uint32_t total = 0;
-    if (b < n_buckets) {
-        for (uint32_t c = 0; c < n_ctas; ++c) {
-            const size_t k = (size_t)c * n_buckets + b;
-            const uint32_t v = cta_hist[k];
-            cta_hist[k] = total;               // exclusive prefix: slots of this CTA start here
-            total += v;
-        }
-    }
+    const uint32_t total = b < n_buckets ? totals[b] : 0u;
     const uint32_t kept = total < ASH_MAX_INSTANCES_PER_BATCH ? total : ASH_MAX_INSTANCES_PER_BATCH;
     s_scan[b] = kept;
     __syncthreads();
@@ -170,10 +189,18 @@ k_bucket_scan(uint32_t* __restrict__ cta_hist, uint32_t n_ctas, uint32_t n_bucke
         __syncthreads();
     }
     if (b < n_buckets) {
-        offsets[b] = s_scan[b] - kept;
-        totals[b] = total;
+        const uint32_t off = s_scan[b] - kept;
+        offsets[b] = off;
         if (kept) atomicAdd(&s_nonempty, 1u);
         if (total > kept) atomicAdd(&s_dropped, total - kept);
+        const uint32_t batch = b / ASH_MAX_LOD_LEVELS, level = b % ASH_MAX_LOD_LEVELS;
+        AshIndirectDrawCommand d = {0u, kept, 0u, 0, off};
+        const uint32_t mid = batch_mesh[batch];
+        if (mid < n_meshes && level < meshes[mid].level_count) {
+            d.index_count = meshes[mid].levels[level].index_count;
+            d.first_index = meshes[mid].levels[level].index_offset;
+        }
+        draws[b] = d;
     }
     if (b == n_buckets - 1u) offsets[n_buckets] = s_scan[b];
     __syncthreads();
@@ -188,7 +215,7 @@ k_bucket_scan(uint32_t* __restrict__ cta_hist, uint32_t n_ctas, uint32_t n_bucke
 
 __global__ void __launch_bounds__(kInstThreads)
 k_instance_scatter(const AshInstanceData* __restrict__ inst, const uint32_t* __restrict__ bucket_of, uint32_t n,
-                   const uint32_t* __restrict__ cta_hist, uint32_t n_buckets, const uint32_t* __restrict__ offsets,
+                   const uint32_t* __restrict__ cta_base, uint32_t n_buckets, const uint32_t* __restrict__ offsets,
                    AshInstanceData* __restrict__ out) {
     extern __shared__ uint32_t s_warp[];                 // [8 warps][n_buckets]
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -201,7 +228,7 @@ k_instance_scatter(const AshInstanceData* __restrict__ inst, const uint32_t* __r
     if (bucket != kNoBucket && rank == 0u) s_warp[warp * n_buckets + bucket] = __popc(peers);
     __syncthreads();
     if (bucket == kNoBucket) return;
-    uint32_t slot = cta_hist[(size_t)blockIdx.x * n_buckets + bucket] + rank;
+    uint32_t slot = cta_base[(size_t)blockIdx.x * n_buckets + bucket] + rank;
     for (int w = 0; w < warp; ++w) slot += s_warp[w * n_buckets + bucket];
     if (slot >= ASH_MAX_INSTANCES_PER_BATCH) return;     // instancing.rs:219-223: the batch is full
     const uint4* src = reinterpret_cast<const uint4*>(inst + i);
@@ -211,23 +238,6 @@ k_instance_scatter(const AshInstanceData* __restrict__ inst, const uint32_t* __r
     for (int k = 0; k < 6; ++k) v[k] = __ldg(src + k);
 #pragma unroll
     for (int k = 0; k < 6; ++k) dst[k] = v[k];
-}
-
-// one indirect draw per bucket: {index_count, instance_count, first_index, vertex_offset = 0, first_instance}
-__global__ void k_bucket_draws(const uint32_t* __restrict__ offsets, uint32_t n_buckets, const uint32_t* __restrict__ batch_mesh,
-                               const AshLodMesh* __restrict__ meshes, uint32_t n_meshes, AshIndirectDrawCommand* __restrict__ draws) {
-    const uint32_t b = blockIdx.x * blockDim.x + threadIdx.x;
-    if (b >= n_buckets) return;
-    const uint32_t batch = b / ASH_MAX_LOD_LEVELS, level = b % ASH_MAX_LOD_LEVELS;
-    AshIndirectDrawCommand d = {0u, 0u, 0u, 0, 0u};
-    const uint32_t mid = batch_mesh[batch];
-    d.instance_count = offsets[b + 1] - offsets[b];
-    d.first_instance = offsets[b];
-    if (mid < n_meshes && level < meshes[mid].level_count) {
-        d.index_count = meshes[mid].levels[level].index_count;
-        d.first_index = meshes[mid].levels[level].index_offset;
-    }
-    draws[b] = d;
 }
 
 // batch -> mesh map: the mesh of the lowest-index object of each batch (a BatchKey names one mesh)
@@ -255,7 +265,7 @@ cudaError_t launch_batch_mesh(const uint32_t* batch_id, const uint32_t* mesh_id,
 }
 
 size_t instancing_hist_bytes(uint32_t max_objects, uint32_t n_buckets) {
-    return (size_t)((max_objects + kInstThreads - 1) / kInstThreads) * n_buckets * sizeof(uint32_t);
+    return (size_t)((max_objects + kInstThreads - 1) / kInstThreads) * n_buckets * sizeof(uint32_t) * 2;   // counts + bases
 }
 
 cudaError_t launch_instancing(const AshInstanceData* inst, const uint32_t* batch_id, const uint32_t* mesh_id,
@@ -279,13 +289,13 @@ cudaError_t launch_instancing(const AshInstanceData* inst, const uint32_t* batch
                                                                                    n, P, n_buckets, sel, bucket_of, cta_hist, stats);
         if ((e = cudaGetLastError()) != cudaSuccess) return e;
     }
-    k_bucket_scan<<<1, 1024, 0, L.s>>>(cta_hist, n_ctas, n_buckets, offsets, totals, stats);
+    uint32_t* cta_base = cta_hist + (size_t)n_ctas * n_buckets;      // second half of the histogram allocation
+    k_bucket_scan_ctas<<<(n_buckets + 7) / 8, 256, 0, L.s>>>(cta_hist, n_ctas, n_buckets, cta_base, totals);
     if ((e = cudaGetLastError()) != cudaSuccess) return e;
-    if (n_ctas) {
-        k_instance_scatter<<<n_ctas, kInstThreads, 8u * n_buckets * sizeof(uint32_t), L.s>>>(inst, bucket_of, n, cta_hist, n_buckets, offsets, out);
-        if ((e = cudaGetLastError()) != cudaSuccess) return e;
-    }
-    k_bucket_draws<<<(n_buckets + 127) / 128, 128, 0, L.s>>>(offsets, n_buckets, batch_mesh, meshes, n_meshes, draws);
+    k_bucket_offsets<<<1, 1024, 0, L.s>>>(totals, n_buckets, batch_mesh, meshes, n_meshes, offsets, draws, stats);
+    if ((e = cudaGetLastError()) != cudaSuccess) return e;
+    if (n_ctas) k_instance_scatter<<<n_ctas, kInstThreads, 8u * n_buckets * sizeof(uint32_t), L.s>>>(inst, bucket_of, n, cta_base, n_buckets, offsets, out);
+    *L.launches += n_ctas ? 3u : 1u;                 // the Timed guard counted one of the (up to) four kernels
     return cudaGetLastError();
 }
 

@@ -399,6 +399,7 @@ cudaError_t launch_light_cull(const AshGpuLight* lights, const AshLightCullingPu
                 tiles_x, tiles_y, cells_x, cells, planes, tile_minmax, cand, cand_idx, cand_count, cell_list,
                 max_lights, cell_count);
             if ((e = cudaGetLastError()) != cudaSuccess) return e;
+            *L.launches += 2;                        // tile planes + cells ride in the prepass class
         }
     }
     Timed timed(L, ASH_KERNEL_LIGHT_TILES);
