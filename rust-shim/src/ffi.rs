@@ -5,6 +5,7 @@ use crate::renderer::features::light_culling::{CullingCameraData, GpuLight, Ligh
 use crate::renderer::occlusion_culling::{CullObjectData, CullingPushConstants, IndirectDrawCommand};
 use crate::renderer::temporal_aa::TaaPushConstants;
 use crate::renderer::fullscreen_pass::PostProcessPushConstants;
+use crate::renderer::instancing::InstanceData;                 // 96 B, instancing.rs:19-34 (passed by pointer unchanged)
 use std::os::raw::{c_char, c_int, c_void};
 
 #[repr(C)] pub struct ashcuda_ctx { _private: [u8; 0] }
@@ -15,7 +16,7 @@ pub struct AshBloomParams { pub threshold: f32, pub upsample_intensity: f32, pub
 #[repr(C)] #[derive(Clone, Copy, Default)]
 pub struct AshCudaConfig {
     pub max_objects: u32, pub max_lights: u32, pub max_draws: u32, pub hiz_levels: u32, pub bloom_mips: u32,
-    pub enable_post: u32, pub srgb_encode: u32, pub concurrent_frontend: u32, pub _reserved: [u32; 8],
+    pub enable_post: u32, pub srgb_encode: u32, pub concurrent_frontend: u32, pub max_batches: u32, pub _reserved: [u32; 7],
 }
 
 #[repr(C)] #[derive(Clone, Copy)]
@@ -30,6 +31,34 @@ pub struct AshViewStats {
     pub view_id: u32, pub total_objects: u32, pub visible_objects: u32, pub tiles: u32,
     pub sum_tile_lights: u32, pub max_tile_lights: u32, pub overflow_tiles: u32, pub candidate_lights: u32,
 }
+
+// ---- row f-2: LodManager / InstancingManager on the device.  LodMesh holds a Vec<LodLevel>, so the host
+// flattens it: `AshLodMesh::from(&LodMesh)` copies up to MAX_LOD_LEVELS levels.
+#[repr(C)] #[derive(Clone, Copy, Default)]
+pub struct AshLodLevel { pub screen_threshold: f32, pub distance_threshold: f32, pub triangle_count: u32,
+                         pub vertex_count: u32, pub index_offset: u32, pub index_count: u32 }
+#[repr(C)] #[derive(Clone, Copy, Default)]
+pub struct AshLodMesh { pub levels: [AshLodLevel; 8], pub level_count: u32, pub bounding_radius: f32, pub lod_bias: f32, pub _padding: u32 }
+#[repr(C)] #[derive(Clone, Copy, Default)]
+pub struct AshLodConfig { pub mode: u32, pub force_level: u32, pub smooth_transitions: u32, pub transition_width: f32,
+                          pub global_bias: f32, pub cull_threshold: f32, pub use_visibility: u32, pub _padding: u32 }
+#[repr(C)] #[derive(Clone, Copy, Default)]
+pub struct AshLodSelection { pub level: u32, pub blend: f32, pub culled: u32, pub screen_coverage: f32 }
+#[repr(C)] #[derive(Clone, Copy, Default)]
+pub struct AshInstancingStats { pub objects_per_lod: [u32; 8], pub objects_culled: u32, pub total_instances: u32, pub batch_count: u32,
+                                pub avg_instances_per_batch: f32, pub triangles_before: u64, pub triangles_after: u64,
+                                pub instances_dropped: u32, pub _padding: u32 }
+#[repr(C)] #[derive(Clone, Copy, Default)]
+pub struct AshInstancingParams { pub view_proj: [[f32; 4]; 4], pub camera_pos: [f32; 4], pub screen_size: [f32; 2],
+                                 pub object_count: u32, pub _padding: u32 }
+const _: () = assert!(std::mem::size_of::<InstanceData>() == 96 && std::mem::size_of::<AshLodMesh>() == 208);
+const _: () = assert!(std::mem::size_of::<AshInstancingStats>() == 72 && std::mem::size_of::<AshInstancingParams>() == 96);
+pub const ASH_STAGE_INSTANCING: u32 = 0x80;
+pub const ASH_BUF_LOD_SELECTION: c_int = 11;
+pub const ASH_BUF_INSTANCES_OUT: c_int = 12;
+pub const ASH_BUF_BUCKET_OFFSETS: c_int = 13;
+pub const ASH_BUF_INSTANCE_DRAWS: c_int = 14;
+pub const ASH_BUF_INSTANCING_STATS: c_int = 15;
 
 const _: () = assert!(std::mem::size_of::<CullObjectData>() == 112 && std::mem::size_of::<IndirectDrawCommand>() == 20);
 const _: () = assert!(std::mem::size_of::<CullingPushConstants>() == 96 && std::mem::size_of::<GpuLight>() == 64);
@@ -69,6 +98,10 @@ extern "C" {
     pub fn ashcuda_bloom(ctx: *mut ashcuda_ctx, bp: *const AshBloomParams) -> c_int;
     pub fn ashcuda_tonemap(ctx: *mut ashcuda_ctx, pc: *const PostProcessPushConstants) -> c_int;
     pub fn ashcuda_view_run(ctx: *mut ashcuda_ctx, vp: *const AshCudaViewParams) -> c_int;
+    pub fn ashcuda_set_instances(ctx: *mut ashcuda_ctx, instances: *const InstanceData, batch_id: *const u32, lod_mesh_id: *const u32, n: u32, on_device: c_int) -> c_int;
+    pub fn ashcuda_set_lod_meshes(ctx: *mut ashcuda_ctx, meshes: *const AshLodMesh, n: u32, on_device: c_int) -> c_int;
+    pub fn ashcuda_set_lod_config(ctx: *mut ashcuda_ctx, cfg: *const AshLodConfig) -> c_int;
+    pub fn ashcuda_instancing_finalize(ctx: *mut ashcuda_ctx, ip: *const AshInstancingParams) -> c_int;
     pub fn ashcuda_upload_view(ctx: *mut ashcuda_ctx, depth: *const f32, hdr: *const c_void, velocity: *const c_void) -> c_int;
     pub fn ashcuda_download_view(ctx: *mut ashcuda_ctx, visibility: *mut u32, tile_data: *mut u32, ldr8: *mut u8, stats: *mut AshViewStats, visible_count: *mut u32) -> c_int;
     pub fn ashcuda_get(ctx: *mut ashcuda_ctx, which: c_int, dev_ptr: *mut *mut c_void, bytes: *mut usize) -> c_int;
