@@ -191,9 +191,9 @@ cudaError_t launch_tonemap(const void* hdr, const void* bloom_or_null, void* ldr
 
 // ---- fast post kernels (post_fast.cu): bit-identical to the general ones, valid when the exact-tap
 //      checks below hold for the extents involved
-cudaError_t launch_taa_fast(const void* cur, const void* hist, void* out, void* thr_or_null,
+cudaError_t launch_taa_fast(const void* cur, const void* hist, const void* vel_or_null, void* out, void* thr_or_null,
                             const AshTaaPushConstants& pc, float threshold, const Launch& L);
-cudaError_t launch_taa_pair(const void* cur, const void* hist, void* out, void* thr_or_null,
+cudaError_t launch_taa_pair(const void* cur, const void* hist, const void* vel_or_null, void* out, void* thr_or_null,
                             const AshTaaPushConstants& pc, float threshold, const Launch& L);
 cudaError_t launch_bloom_downsample_fast(const void* src, uint32_t sw, uint32_t sh, void* dst, uint32_t dw,
                                          uint32_t dh, const Launch& L);

@@ -375,8 +375,8 @@ static int taa_resolve_impl(ashcuda_ctx* c, const AshTaaPushConstants* pc, void*
     void* out = c->taa[c->taa_cur ^ 1];
     const bool exact = taa_taps_exact(c, pc);
     *fused = false;
-    if (exact && !c->velocity) {
-        ASH_CUDA(c, launch_taa_fast(c->color, hist, out, thr_or_null, *pc, threshold, c->L()));
+    if (exact) {
+        ASH_CUDA(c, launch_taa_fast(c->color, hist, c->velocity, out, thr_or_null, *pc, threshold, c->L()));
         *fused = thr_or_null != nullptr;
     } else {
         ASH_CUDA(c, launch_taa(c->color, hist, c->velocity, out, *pc, exact, c->L()));

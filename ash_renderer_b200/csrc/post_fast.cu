@@ -174,7 +174,7 @@ k_taa_fast(Tex16 cur, Tex16 hist, uint2* __restrict__ out, uint2* __restrict__ t
     }
 }
 
-cudaError_t launch_taa_fast(const void* cur, const void* hist, void* out, void* thr_or_null,
+cudaError_t launch_taa_fast(const void* cur, const void* hist, const void* vel_or_null, void* out, void* thr_or_null,
                             const AshTaaPushConstants& pc, float threshold, const Launch& L) {
     const int W = (int)pc.screen_params[0], H = (int)pc.screen_params[1];
     const Tex16 c{static_cast<const uint2*>(cur), W, H}, h{static_cast<const uint2*>(hist), W, H};
@@ -183,7 +183,8 @@ cudaError_t launch_taa_fast(const void* cur, const void* hist, void* out, void* 
     uint2* o = static_cast<uint2*>(out);
     uint2* t = static_cast<uint2*>(thr_or_null);
     // the usual case (sub-pixel jitter delta): two pixels per thread on the packed fp32 pipe, post_pair.cu
-    if (in_halo) return launch_taa_pair(cur, hist, out, thr_or_null, pc, threshold, L);
+    // (with a velocity buffer the history taps are gathered per pixel, so the halo condition does not apply)
+    if (vel_or_null || in_halo) return launch_taa_pair(cur, hist, vel_or_null, out, thr_or_null, pc, threshold, L);
     Timed timed(L, thr_or_null ? ASH_KERNEL_TAA_THRESHOLD : ASH_KERNEL_TAA);
     if (t) k_taa_fast<true, false><<<grid, 256, 0, L.s>>>(c, h, o, t, pc, threshold);
     else   k_taa_fast<false, false><<<grid, 256, 0, L.s>>>(c, h, o, t, pc, threshold);

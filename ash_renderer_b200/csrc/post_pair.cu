@@ -79,17 +79,27 @@ __device__ __forceinline__ void taa_stage_nb(float4 (*s_nb)[kHalo], const uint2 
     }
 }
 
-// resolve this thread's 1x4 strip of the tile at (x0, y0)
-template <bool THRESH>
+// resolve this thread's 1x4 strip of the tile at (x0, y0).
+// VEL = false: no velocity buffer, the history taps come from the staged halo through the per-tile tables.
+// VEL = true : per-pixel velocity (RG16F, centre tap == texel): velocity test (:97-99), history UV (:102), 8-bit
+//              bilinear setup and velocity-weighted blend (:145-150) per lane; the four history texels of each
+//              lane are gathered from global memory (L2), the rest of the resolve is the same packed code.
+template <bool THRESH, bool VEL>
 __device__ __forceinline__ void taa_strip(const float4 (*s_nb)[kHalo], const TaaRaw& raw, const TaaTables& tb, bool clamp_on,
                                           int W, int H, int x0, int y0, uint2* __restrict__ out, uint2* __restrict__ thr,
-                                          float threshold) {
+                                          float threshold, const Tex16& hist, const __half2* __restrict__ vel,
+                                          const AshTaaPushConstants& pc) {
     const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
     const int x = x0 + tx, yb = y0 + 4 * ty;
     if (x >= W || yb >= H) return;
-    const AxisTap col = tb.col[tx];
-    const float blend = tb.blend, ib = fsub(1.0f, blend);
+    const AxisTap col = VEL ? AxisTap{0, 0, 0.0f, 0.0f} : tb.col[tx];
+    const float blend = VEL ? 0.0f : tb.blend, ib = fsub(1.0f, blend);
     const float fx = col.f, ifx = fsub(1.0f, fx);
+    // VEL: per-thread constants of the per-pixel coordinate math
+    const float sw = pc.screen_params[0], sh = pc.screen_params[1];
+    const float u = VEL ? fdiv_safe(fadd((float)x, 0.5f), sw) : 0.0f;                                 // :92 (extent in [1, 32768])
+    const float jvx = VEL ? fdiv(fsub(pc.jitter[0], pc.prev_jitter[0]), sw) : 0.0f;                   // :97-99
+    const float jvy = VEL ? fdiv(fsub(pc.jitter[1], pc.prev_jitter[1]), sh) : 0.0f;
 
     // row-wise min / max of the 3 horizontal neighbours, for the 6 rows this strip touches
     V3 rmn[6], rmx[6];
@@ -105,10 +115,11 @@ __device__ __forceinline__ void taa_strip(const float4 (*s_nb)[kHalo], const Taa
     for (int k = 0; k < 4; k += 2) {                 // lanes: lo = row yb + k, hi = row yb + k + 1
         const int y = yb + k;
         if (y >= H) break;
-        const AxisTap ra = tb.row[4 * ty + k], rb = tb.row[4 * ty + k + 1];
+        const AxisTap ra = VEL ? AxisTap{0, 0, 0.0f, 0.0f} : tb.row[4 * ty + k], rb = VEL ? ra : tb.row[4 * ty + k + 1];
         const V3P c = pk3(unpack_rgb_(raw.cur[4 * ty + k + 1][tx + 1]), unpack_rgb_(raw.cur[4 * ty + k + 2][tx + 1]));   // :105 (centre tap == texel)
         V3P h;                                                                                         // :108 bilinear history
-        {
+        P2 blend2 = splat(blend), ib2 = splat(ib);
+        if (!VEL) {
             const V3P a  = pk3(unpack_rgb_(raw.hist[ra.i0][col.i0]), unpack_rgb_(raw.hist[rb.i0][col.i0]));
             const V3P b  = pk3(unpack_rgb_(raw.hist[ra.i0][col.i1]), unpack_rgb_(raw.hist[rb.i0][col.i1]));
             const V3P cc = pk3(unpack_rgb_(raw.hist[ra.i1][col.i0]), unpack_rgb_(raw.hist[rb.i1][col.i0]));
@@ -117,6 +128,37 @@ __device__ __forceinline__ void taa_strip(const float4 (*s_nb)[kHalo], const Taa
             const V3P top = add3(scale3(a, ifx), scale3(b, fx));
             const V3P bot = add3(scale3(cc, ifx), scale3(d, fx));
             h = add3(scale3(top, ify), scale3(bot, fy));
+        } else {
+            const int yl[2] = {y, min(y + 1, H - 1)};            // lane hi of a last odd row recomputes lane lo's row (not stored)
+            int hx0[2], hx1[2], hy0[2], hy1[2]; float hfx[2], hfy[2], bl[2];
+#pragma unroll
+            for (int l = 0; l < 2; ++l) {
+                const float2 q = __half22float2(__ldg(vel + (size_t)yl[l] * W + x));
+                float vx = q.x, vy = q.y;
+                if (length2(vx, vy) < 0.0001f) { vx = jvx; vy = jvy; }                                 // :97-99
+                const float v = fdiv_safe(fadd((float)yl[l], 0.5f), sh);                               // :92
+                const float hu = gclamp(fsub(u, vx), 0.0f, 1.0f), hv = gclamp(fsub(v, vy), 0.0f, 1.0f);   // :102
+                bilinear_setup(hu, W, hx0[l], hx1[l], hfx[l]);
+                bilinear_setup(hv, H, hy0[l], hy1[l], hfy[l]);
+                float b = pc.params[0];                                                                // :145-150
+                if (pc.params[2] > 0.5f) {
+                    const float vl = length2(fmul(vx, sw), fmul(vy, sh));
+                    b = fmul(b, gclamp(fsub(1.0f, fmul(vl, 0.1f)), 0.0f, 1.0f));
+                }
+                if (hu < 0.0f || hu > 1.0f || hv < 0.0f || hv > 1.0f) b = 0.0f;                        // :153-156 (dead after the clamp)
+                bl[l] = b;
+            }
+            auto tap = [&](int l, int yy, int xx) { return unpack_rgb_(__ldg(hist.p + (size_t)yy * W + xx)); };
+            const V3P a  = pk3(tap(0, hy0[0], hx0[0]), tap(1, hy0[1], hx0[1]));
+            const V3P b  = pk3(tap(0, hy0[0], hx1[0]), tap(1, hy0[1], hx1[1]));
+            const V3P cc = pk3(tap(0, hy1[0], hx0[0]), tap(1, hy1[1], hx0[1]));
+            const V3P d  = pk3(tap(0, hy1[0], hx1[0]), tap(1, hy1[1], hx1[1]));
+            const P2 fx2 = pk(hfx[0], hfx[1]), ifx2 = fsub(1.0f, fx2), fy = pk(hfy[0], hfy[1]), ify = fsub(1.0f, fy);
+            const V3P top = add3(scale3(a, ifx2), scale3(b, fx2));
+            const V3P bot = add3(scale3(cc, ifx2), scale3(d, fx2));
+            h = add3(scale3(top, ify), scale3(bot, fy));
+            blend2 = pk(bl[0], bl[1]);
+            ib2 = fsub(1.0f, blend2);
         }
         if (clamp_on) {                                                                                // :112-142
             auto mn3 = [&](int r) { return V3{fminf(fminf(rmn[r].x, rmn[r + 1].x), rmn[r + 2].x), fminf(fminf(rmn[r].y, rmn[r + 1].y), rmn[r + 2].y),
@@ -130,7 +172,7 @@ __device__ __forceinline__ void taa_strip(const float4 (*s_nb)[kHalo], const Taa
             const V3P hy = rgb_to_ycocg(taa_tonemap_safe(h));
             h = taa_untonemap_pair(ycocg_to_rgb(clip_aabb_pair(mn, mx, hy)));                          // :140-141
         }
-        const V3P o = add3(scale3(c, ib), scale3(h, blend));                                           // mix(), :159
+        const V3P o = add3(scale3(c, ib2), scale3(h, blend2));                                         // mix(), :159
         const uint2 oa = pack_rgba16f(lo(o.x), lo(o.y), lo(o.z), 1.0f), ob = pack_rgba16f(hi(o.x), hi(o.y), hi(o.z), 1.0f);
         const bool has_b = y + 1 < H;
         out[(size_t)y * W + x] = oa;
@@ -146,9 +188,9 @@ __device__ __forceinline__ void taa_strip(const float4 (*s_nb)[kHalo], const Taa
 // A persistent cp.async double-buffered variant of this kernel (as k_upsample_pipe, post_fast.cu) was
 // measured 20 % SLOWER (0.140 vs 0.116 ms at 4K): three barriers per tile and the extra shared-memory
 // pass outweigh the hidden load latency; the one-shot kernel below keeps its loads in registers.
-template <bool THRESH>
+template <bool THRESH, bool VEL>
 __global__ void __launch_bounds__(256, 3)
-k_taa_pair(Tex16 cur, Tex16 hist, uint2* __restrict__ out, uint2* __restrict__ thr,
+k_taa_pair(Tex16 cur, Tex16 hist, const __half2* __restrict__ vel, uint2* __restrict__ out, uint2* __restrict__ thr,
            AshTaaPushConstants pc, float threshold) {
     __shared__ float4 s_nb[kHalo][kHalo];      // tonemapped YCoCg of `current`, tile + halo
     __shared__ TaaRaw s_raw;
@@ -164,28 +206,28 @@ k_taa_pair(Tex16 cur, Tex16 hist, uint2* __restrict__ out, uint2* __restrict__ t
         for (int it = 0; it < 4; ++it) {
             const size_t g = (size_t)min(max(y0 - 1 + m.warp + 8 * it, 0), H - 1) * W + gx;
             tc[it] = __ldg(cur.p + g);
-            th[it] = __ldg(hist.p + g);
+            if (!VEL) th[it] = __ldg(hist.p + g);
         }
         tc[4] = th[4] = make_uint2(0u, 0u);
         if (m.extra) {
             const size_t g = (size_t)min(max(y0 - 1 + m.rr, 0), H - 1) * W + min(max(x0 - 1 + m.xr, 0), W - 1);
             tc[4] = __ldg(cur.p + g);
-            th[4] = __ldg(hist.p + g);
+            if (!VEL) th[4] = __ldg(hist.p + g);
         }
-        taa_tables(s_tb, pc, W, H, x0, y0);      // while the loads fly
+        if (!VEL) taa_tables(s_tb, pc, W, H, x0, y0);      // while the loads fly
 #pragma unroll
         for (int it = 0; it < 4; ++it) {
             s_raw.cur[m.warp + 8 * it][m.lane] = tc[it];
-            s_raw.hist[m.warp + 8 * it][m.lane] = th[it];
+            if (!VEL) s_raw.hist[m.warp + 8 * it][m.lane] = th[it];
         }
-        if (m.extra) { s_raw.cur[m.rr][m.xr] = tc[4]; s_raw.hist[m.rr][m.xr] = th[4]; }
+        if (m.extra) { s_raw.cur[m.rr][m.xr] = tc[4]; if (!VEL) s_raw.hist[m.rr][m.xr] = th[4]; }
         if (clamp_on) taa_stage_nb(s_nb, tc, m);
     }
     __syncthreads();
-    taa_strip<THRESH>(s_nb, s_raw, s_tb, clamp_on, W, H, x0, y0, out, thr, threshold);
+    taa_strip<THRESH, VEL>(s_nb, s_raw, s_tb, clamp_on, W, H, x0, y0, out, thr, threshold, hist, vel, pc);
 }
 
-cudaError_t launch_taa_pair(const void* cur, const void* hist, void* out, void* thr_or_null,
+cudaError_t launch_taa_pair(const void* cur, const void* hist, const void* vel_or_null, void* out, void* thr_or_null,
                             const AshTaaPushConstants& pc, float threshold, const Launch& L) {
     const int W = (int)pc.screen_params[0], H = (int)pc.screen_params[1];
     const Tex16 c{static_cast<const uint2*>(cur), W, H}, h{static_cast<const uint2*>(hist), W, H};
@@ -193,8 +235,11 @@ cudaError_t launch_taa_pair(const void* cur, const void* hist, void* out, void* 
     uint2* o = static_cast<uint2*>(out);
     uint2* t = static_cast<uint2*>(thr_or_null);
     Timed timed(L, thr_or_null ? ASH_KERNEL_TAA_THRESHOLD : ASH_KERNEL_TAA);
-    if (t) k_taa_pair<true><<<grid, 256, 0, L.s>>>(c, h, o, t, pc, threshold);
-    else   k_taa_pair<false><<<grid, 256, 0, L.s>>>(c, h, o, t, pc, threshold);
+    const __half2* v = static_cast<const __half2*>(vel_or_null);
+    if (v) { if (t) k_taa_pair<true, true><<<grid, 256, 0, L.s>>>(c, h, v, o, t, pc, threshold);
+             else   k_taa_pair<false, true><<<grid, 256, 0, L.s>>>(c, h, v, o, t, pc, threshold); }
+    else   { if (t) k_taa_pair<true, false><<<grid, 256, 0, L.s>>>(c, h, v, o, t, pc, threshold);
+             else   k_taa_pair<false, false><<<grid, 256, 0, L.s>>>(c, h, v, o, t, pc, threshold); }
     return cudaGetLastError();
 }
 

@@ -380,7 +380,7 @@ def test_light_cull_overflow_zero_lights_and_disabled(backend, oracle):
 
 # ------------------------------------------------------------------ TAA
 @pytest.mark.parametrize("W,H,with_vel", [(200, 120, True), (200, 120, False), (67, 45, True),
-                                          (1920, 1080, False), (33, 9, False)])
+                                          (1920, 1080, False), (33, 9, False), (1920, 1080, True), (33, 9, True)])
 def test_taa_bit_exact(backend, oracle, W, H, with_vel):
     cur, hist = synth.random_hdr(W, H, seed=1), synth.random_hdr(W, H, seed=2)
     vel = synth.random_velocity(W, H, seed=3) if with_vel else None
@@ -509,6 +509,30 @@ def test_view_run_matches_oracle(backend, oracle, W, H, keep):
         st = c.stats()
         assert st["view_id"] == 7 and st["visible_objects"] == cnt and st["sum_tile_lights"] == int(td[:, 0].sum())
         assert c.kernel_launches() > 0
+
+
+def test_view_run_post_chain_with_velocity_buffer(backend, oracle):
+    """Fused TAA + threshold with a per-pixel velocity buffer (fast kernel, history gathered per pixel)."""
+    from ash_renderer_b200.host import TemporalAA
+    W, H = 640, 360
+    seq = synth.HdrSequence(W, H, seed=9, n_discs=30)
+    vel = synth.random_velocity(W, H, seed=10, still_frac=0.3, max_px=6.0)
+    taa = TemporalAA()
+    cam = synth.Camera((0.0, 2.0, 22.0), (0, 0, 0), W, H)
+    hist, ref_bloom = None, None
+    with _ctx(backend, W, H) as c:
+        for t in range(3):
+            taa.begin_frame()
+            j = taa.current_jitter()
+            f = seq.frame(float(j[0]), float(j[1]))
+            pc = taa.push_constants(W, H)
+            ref = oracle.taa_resolve(f, f if hist is None else hist, vel, pc)
+            U, _ = oracle.bloom_chain(ref, 0.8, 5)
+            c.set_color(f, vel)
+            c.view_run(_view_params(cam, 0, 0, 1, W, H, pc, stages=T.STAGE_TAA | T.STAGE_BLOOM | T.STAGE_TONEMAP | T.STAGE_KEEP_BLOOM))
+            _assert_half_images_equal(c.taa_out(), ref, f"taa+velocity frame {t}")
+            _assert_half_images_equal(c.bloom_mip(0), U[0], f"bloom frame {t}")
+            hist = ref
 
 
 def test_view_io_host_path(backend, oracle):
