@@ -326,11 +326,15 @@ def run_cuda(args):
         ev.record(main)
         return ev
 
+    d_vel = None
+    if args.velocity:
+        d_vel = torch.from_numpy(synth.random_velocity(W, H, seed=11, still_frac=0.3, max_px=4.0).view(np.uint16)).cuda()
+
     def step_resident():
         for s in slots:
             c = s["ctx"]
             c.set_depth(s["d_depth"])
-            c.set_color(s["d_hdr"], None)
+            c.set_color(s["d_hdr"], d_vel)
             c.view_run(s["vp"])
 
     def step_e2e():
@@ -471,7 +475,8 @@ def run_cuda(args):
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
         "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic",
-        "config": {"workload": workload_name() + (" + LOD selection / instance batching (--instancing)" if inst_scene else ""),
+        "config": {"workload": workload_name() + (" + LOD selection / instance batching (--instancing)" if inst_scene else "")
+                   + (" + per-pixel velocity buffer in the TAA (--velocity; resident passes only)" if args.velocity else ""),
                    "views_per_gpu_per_step": B, "distinct_view_inputs_per_gpu": distinct,
                    "streams": args.streams, "concurrent_frontend": True,
                    "kernel_timing": f"same {args.steps} steps repeated serialised (1 stream, no fork) with CUDA events around each launch: "
@@ -508,6 +513,8 @@ def main():
     ap.add_argument("--distinct", type=int, default=4, help="distinct synthetic depth/HDR inputs generated per GPU (host setup cost)")
     ap.add_argument("--streams", type=int, default=4)
     ap.add_argument("--cpu-views", type=int, default=2)
+    ap.add_argument("--velocity", action="store_true",
+                    help="supply a per-pixel RG16F velocity buffer to the TAA (the headline workload has none, PIN-12)")
     ap.add_argument("--instancing", action="store_true",
                     help="widened path (SURVEY 8.6 row f-2): also run LOD selection + instance batching after the cull; "
                          "not part of the headline workload, reported under \"widened\"")
