@@ -236,7 +236,7 @@ def run_reference(args):
     dt = time.perf_counter() - t0
     v = args.steps / dt
     sample = f"{args.steps} steps x 1 full 4K view each (bounded sample of the {args.views}-view step)"
-    print(json.dumps({
+    emit_json({
         "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": min(args.warmup, 1), "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
@@ -244,7 +244,7 @@ def run_reference(args):
                    "the reference has no CPU implementation and its Vulkan path is unavailable on this box"},
         "cpu_baseline": {"value": v, "unit": UNIT, "cores": oracle.num_threads(), "kind": "port", "sample": sample},
         "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-    }))
+    })
 
 
 # ------------------------------------------------------------------ CUDA arm
@@ -498,12 +498,30 @@ def run_cuda(args):
         "cpu_baseline": {"value": cpu_v, "unit": UNIT, "cores": cpu_cores, "kind": "port",
                          "sample": f"{cpu_n} full 4K view(s) of the same workload through the OpenMP CPU oracle"},
     }
-    print(json.dumps(out))
+    emit_json(out)
     if world > 1:
         dist.destroy_process_group()
 
 
+_JSON_FD = None
+
+
+def emit_json(obj):
+    """The one JSON line of the contract goes to the process's ORIGINAL stdout; everything else any library
+    prints (NCCL's version banner, torchrun chatter) was redirected to stderr at start-up."""
+    line = (json.dumps(obj) + "\n").encode()
+    if _JSON_FD is None:
+        sys.stdout.write(line.decode())
+        sys.stdout.flush()
+    else:
+        os.write(_JSON_FD, line)
+
+
 def main():
+    global _JSON_FD
+    sys.stdout.flush()
+    _JSON_FD = os.dup(1)
+    os.dup2(2, 1)                      # fd 1 -> stderr for the rest of the run
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=10)

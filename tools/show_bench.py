@@ -1,6 +1,6 @@
 import json, sys
 for f in sys.argv[1:]:
-    d = json.load(open(f))
+    d = json.loads([l for l in open(f) if l.startswith('{')][-1])
     print(f, f"value={d['value']:.0f} ms/step={d['ms_per_step']:.3f} e2e={d['e2e']['value']:.0f} dom={d['roofline']['kernel']} frac={d['roofline']['frac']:.3f} whole_view_frac={d['roofline']['whole_view']['frac']:.3f}")
     for k, v in d['kernels'].items():
         print(f"  {k:24s} n/view={v['launches_per_view']:.0f} avg_ms={v['avg_ms']:.4f} GB/s={v['gbs']:.0f} share={v['share_of_kernel_time']:.3f}")
