@@ -8,6 +8,8 @@
 //   HaltonSequence / TaaConfig / TemporalAA                                 src/renderer/temporal_aa.rs:14-207
 //   BloomConfig / TonemappingConfig                                         features/bloom.rs:9-33, tonemapping.rs:22-44
 //   RenderFeature / FeatureManager                                          features/feature_trait.rs:25-98
+//   InstanceData helpers / BatchKey / InstancingStats / InstancingManager   src/renderer/instancing.rs:19-277  (row f-2)
+//   LodLevel / LodMesh / LodConfig / LodSelection / LodStats / LodManager   src/renderer/lod_system.rs:15-394   (row f-2)
 //   CudaComputeFeature — the plugin a maintainer registers; the Rust twin is rust-shim/src/feature.rs
 //
 // Matrices are `float[4][4]` with m[c] = column c (glam `to_cols_array_2d`).  The Rust toolchain is
@@ -22,7 +24,9 @@
 #include <memory>
 #include <stdexcept>
 #include <string>
+#include <map>
 #include <typeindex>
+#include <utility>
 #include <vector>
 
 #include "ashcuda.h"
@@ -304,6 +308,190 @@ private:
     const Device* device_ = nullptr;
 };
 
+// ---------------------------------------------------------------- row f-2: instancing + LOD
+constexpr size_t MAX_INSTANCES_PER_BATCH = ASH_MAX_INSTANCES_PER_BATCH;   // instancing.rs:16
+constexpr size_t MAX_LOD_LEVELS = ASH_MAX_LOD_LEVELS;                     // lod_system.rs:15
+
+inline AshInstanceData instance_data_from_matrix(const Mat4 model) {      // InstanceData::from_matrix, :37-48
+    AshInstanceData d{};
+    std::memcpy(d.model_row0, model[0], 16); std::memcpy(d.model_row1, model[1], 16);
+    std::memcpy(d.model_row2, model[2], 16); std::memcpy(d.model_row3, model[3], 16);
+    d.color[0] = d.color[1] = d.color[2] = d.color[3] = 1.0f;
+    return d;
+}
+inline AshInstanceData instance_data_new(const Mat4 model, const float color[4]) {   // InstanceData::new, :50-61
+    AshInstanceData d = instance_data_from_matrix(model);
+    std::memcpy(d.color, color, 16);
+    return d;
+}
+inline void instance_position(const AshInstanceData& d, float out[3]) { std::memcpy(out, d.model_row3, 12); }   // :68-70
+
+struct BatchKey {                                    // :74-90
+    uint32_t mesh_id = 0, material_id = 0;
+    bool operator<(const BatchKey& o) const { return std::make_pair(mesh_id, material_id) < std::make_pair(o.mesh_id, o.material_id); }
+    bool operator==(const BatchKey& o) const { return mesh_id == o.mesh_id && material_id == o.material_id; }
+};
+
+struct InstancingStats {                             // :155-186
+    uint32_t total_instances = 0, batch_count = 0, instances_culled = 0;
+    float avg_instances_per_batch = 0.0f;
+    float efficiency() const { return batch_count == 0 ? 0.0f : avg_instances_per_batch / (float)MAX_INSTANCES_PER_BATCH; }
+    std::string format() const {
+        char b[160];
+        std::snprintf(b, sizeof b, "Instancing: %u instances in %u batches (avg %.1f), %u culled", total_instances, batch_count,
+                      avg_instances_per_batch, instances_culled);
+        return b;
+    }
+};
+
+// InstancingManager (:188-277).  Instances are kept in submission order with the dense id of their BatchKey
+// (first-seen order) — the arrays ashcuda_set_instances consumes.
+class InstancingManager {
+public:
+    void begin_frame() { for (auto& c : counts_) c = 0; instances_.clear(); batch_ids_.clear(); stats_ = InstancingStats{}; }   // :203-209
+    void add_instance(const BatchKey& key, const AshInstanceData& instance) {                   // :212-224
+        auto it = keys_.find(key);
+        if (it == keys_.end()) { it = keys_.emplace(key, (uint32_t)keys_.size()).first; counts_.push_back(0); }
+        const uint32_t b = it->second;
+        if (counts_[b] < MAX_INSTANCES_PER_BATCH) {
+            counts_[b] += 1; instances_.push_back(instance); batch_ids_.push_back(b); stats_.total_instances += 1;
+        }
+    }
+    template <class It> void add_instances(const BatchKey& key, It first, It last) { for (; first != last; ++first) add_instance(key, *first); }   // :227-243
+    void finalize() {                                                                           // :253-263
+        stats_.batch_count = 0;
+        for (size_t c : counts_) if (c) stats_.batch_count += 1;
+        if (stats_.batch_count > 0) stats_.avg_instances_per_batch = (float)stats_.total_instances / (float)stats_.batch_count;
+    }
+    const InstancingStats& stats() const { return stats_; }
+    void set_frustum_cull(bool e) { frustum_cull_ = e; }
+    size_t batch_len(const BatchKey& key) const { auto it = keys_.find(key); return it == keys_.end() ? 0 : counts_[it->second]; }
+    size_t key_count() const { return keys_.size(); }
+    const std::vector<AshInstanceData>& instance_data() const { return instances_; }
+    const std::vector<uint32_t>& batch_ids() const { return batch_ids_; }
+private:
+    std::map<BatchKey, uint32_t> keys_;
+    std::vector<size_t> counts_;
+    std::vector<AshInstanceData> instances_;
+    std::vector<uint32_t> batch_ids_;
+    InstancingStats stats_;
+    bool frustum_cull_ = true;
+};
+
+using LodLevel = AshLodLevel;                        // lod_system.rs:61-76
+using LodSelection = AshLodSelection;                // :126-137
+
+struct LodMesh {                                     // :78-124
+    std::vector<LodLevel> levels;
+    float bounding_radius = 0.0f, lod_bias = 0.0f;
+    static LodMesh single(uint32_t triangle_count, float bounding_radius) {                     // :91-104
+        LodMesh m; m.bounding_radius = bounding_radius;
+        m.levels.push_back(LodLevel{0.0f, std::numeric_limits<float>::max(), triangle_count, triangle_count, 0u, triangle_count * 3u});
+        return m;
+    }
+    LodMesh& with_level(const LodLevel& l) { levels.push_back(l); return *this; }
+    size_t level_count() const { return levels.size(); }
+    AshLodMesh record() const {                      // levels flattened to MAX_LOD_LEVELS for the device
+        if (levels.size() > MAX_LOD_LEVELS) throw AshError(ASH_ERR_INVALID, "LodMesh: more than MAX_LOD_LEVELS levels");
+        AshLodMesh r{};
+        for (size_t i = 0; i < levels.size(); ++i) r.levels[i] = levels[i];
+        r.level_count = (uint32_t)levels.size(); r.bounding_radius = bounding_radius; r.lod_bias = lod_bias;
+        return r;
+    }
+};
+
+struct LodConfig {                                   // :35-58 (+ LodSelectionMode :17-33)
+    uint32_t mode = ASH_LOD_MODE_SCREEN_SIZE, force_level = 0;
+    bool smooth_transitions = true;
+    float transition_width = 0.1f, global_bias = 0.0f, cull_threshold = 0.001f;
+    AshLodConfig record(bool use_visibility = true) const {
+        AshLodConfig r{};
+        r.mode = mode; r.force_level = force_level; r.smooth_transitions = smooth_transitions ? 1u : 0u;
+        r.transition_width = transition_width; r.global_bias = global_bias; r.cull_threshold = cull_threshold;
+        r.use_visibility = use_visibility ? 1u : 0u;
+        return r;
+    }
+};
+
+struct LodStats {                                    // :146-183
+    uint32_t objects_per_lod[ASH_MAX_LOD_LEVELS] = {};
+    uint32_t objects_culled = 0;
+    uint64_t triangles_before = 0, triangles_after = 0;
+    double reduction_rate() const { return triangles_before == 0 ? 0.0 : 1.0 - (double)triangles_after / (double)triangles_before; }
+    void reset() { *this = LodStats{}; }
+};
+
+// LodManager (:139-394): the per-object scalar version, fp32 in the reference's evaluation order (the translation
+// unit must be built without FMA contraction, as tests/cpp does).  The device stage does the same in bulk.
+class LodManager {
+public:
+    LodManager() = default;
+    explicit LodManager(const LodConfig& c) : config_(c) {}
+    void begin_frame() { stats_.reset(); }
+    static float calculate_screen_coverage(const float position[3], float radius, const Mat4 view_proj, float screen_width,
+                                           float screen_height) {                               // :207-235
+        volatile float t0 = view_proj[0][3] * position[0], t1 = view_proj[1][3] * position[1], t2 = view_proj[2][3] * position[2];
+        volatile float a = t0 + t1; volatile float b = a + t2; volatile float clip_w = b + view_proj[3][3] * 1.0f;
+        if (clip_w <= 0.0f) return 0.0f;
+        volatile float proj_radius = radius / clip_w;
+        const float mx = rmax(screen_width, screen_height);
+        volatile float pr = proj_radius * mx; volatile float pixel_radius = pr * 0.5f;
+        volatile float ar = 3.14159274101257324f * pixel_radius; volatile float area = ar * pixel_radius;
+        volatile float screen_area = screen_width * screen_height;
+        volatile float cov = area / screen_area;
+        return rmin(cov, 1.0f);
+    }
+    LodSelection select_lod(const LodMesh& mesh, const float world_position[3], const Mat4 view_proj, const float camera_position[3],
+                            float screen_width, float screen_height) {                         // :238-345
+        const size_t n = mesh.levels.size(), last = n ? n - 1 : 0;
+        if (n) stats_.triangles_before += mesh.levels[0].triangle_count;
+        if (config_.mode == ASH_LOD_MODE_FORCE) {
+            const size_t level = config_.force_level < last ? config_.force_level : last;
+            if (n) { stats_.triangles_after += mesh.levels[level].triangle_count; stats_.objects_per_lod[level] += 1; }
+            return LodSelection{(uint32_t)level, 0.0f, 0u, 1.0f};
+        }
+        const float cov = calculate_screen_coverage(world_position, mesh.bounding_radius, view_proj, screen_width, screen_height);
+        if (cov < config_.cull_threshold) { stats_.objects_culled += 1; return LodSelection{(uint32_t)last, 0.0f, 1u, cov}; }
+        size_t level = last; float blend = 0.0f;
+        if (config_.mode == ASH_LOD_MODE_SCREEN_SIZE) {
+            for (size_t i = 0; i < n; ++i) {
+                const float th = mesh.levels[i].screen_threshold;
+                if (cov >= th) {
+                    if (config_.smooth_transitions && i + 1 < n) {
+                        volatile float range = th - mesh.levels[i + 1].screen_threshold;
+                        if (range > 0.0f) {
+                            volatile float d = th - cov; volatile float pos = d / range; volatile float q = pos / config_.transition_width;
+                            float bl = q; if (bl < 0.0f) bl = 0.0f; if (bl > 1.0f) bl = 1.0f;
+                            blend = bl;
+                        }
+                    }
+                    level = i; break;
+                }
+            }
+        } else {
+            volatile float dx = world_position[0] - camera_position[0], dy = world_position[1] - camera_position[1], dz = world_position[2] - camera_position[2];
+            volatile float xx = dx * dx, yy = dy * dy, zz = dz * dz; volatile float s1 = xx + yy; volatile float s2 = s1 + zz;
+            const float dist = std::sqrt((float)s2);
+            for (size_t i = 0; i < n; ++i) if (dist <= mesh.levels[i].distance_threshold) { level = i; break; }
+        }
+        volatile float x0 = (float)level + config_.global_bias; volatile float x1 = x0 + mesh.lod_bias;
+        float x = x1; if (x < 0.0f) x = 0.0f; if (x > (float)last) x = (float)last;
+        const size_t biased = (x == x && x > 0.0f) ? (size_t)x : 0;
+        if (biased < n) {
+            stats_.triangles_after += mesh.levels[biased].triangle_count;
+            if (biased < MAX_LOD_LEVELS) stats_.objects_per_lod[biased] += 1;
+        }
+        return LodSelection{(uint32_t)biased, blend, 0u, cov};
+    }
+    const LodStats& stats() const { return stats_; }
+    LodConfig& config_mut() { return config_; }
+private:
+    static float rmax(float a, float b) { return (a != a) ? b : ((b != b) ? a : (a < b ? b : a)); }   // f32::max
+    static float rmin(float a, float b) { return (a != a) ? b : ((b != b) ? a : (b < a ? b : a)); }   // f32::min
+    LodConfig config_;
+    LodStats stats_;
+};
+
 // ---------------------------------------------------------------- the drop-in feature
 // Per-frame inputs the reference's contexts do not carry (feature_trait.rs:10-23 has no camera,
 // depth or colour): handed over through an additive setter before render_frame.
@@ -336,6 +524,11 @@ public:
     BloomConfig       bloom;
     TonemappingConfig tonemapping;
     std::vector<AshIndirectDrawCommand> draw_templates{AshIndirectDrawCommand{}};
+    // row f-2 (optional): one instance + LodMesh id per cull object, in the same order as culling.add_object
+    InstancingManager instancing;
+    LodManager        lod;
+    std::vector<LodMesh>  lod_meshes;
+    std::vector<uint32_t> lod_mesh_ids;
 
     const char* name() const override { return "CudaCompute"; }
     void on_added(const Device&) override {               // LightCullingPipeline::new, :41-243
@@ -357,6 +550,18 @@ public:
             if (!check(ashcuda_set_objects(ctx_, o.data(), (uint32_t)o.size(), draw_templates.data(), (uint32_t)draw_templates.size(), 0), "set_objects")) return;
             const auto& l = lights.get_light_buffer_data();
             if (!check(ashcuda_set_lights(ctx_, l.data(), (uint32_t)l.size(), 0), "set_lights")) return;
+            instancing_on_ = false;
+            if (!lod_meshes.empty() && !instancing.instance_data().empty() &&
+                instancing.instance_data().size() == lod_mesh_ids.size() && lod_mesh_ids.size() == o.size()) {
+                std::vector<AshLodMesh> recs;
+                for (const LodMesh& m : lod_meshes) recs.push_back(m.record());
+                const AshLodConfig k = lod.config_mut().record(true);
+                if (!check(ashcuda_set_instances(ctx_, instancing.instance_data().data(), instancing.batch_ids().data(), lod_mesh_ids.data(),
+                                                 (uint32_t)lod_mesh_ids.size(), 0), "set_instances")) return;
+                if (!check(ashcuda_set_lod_meshes(ctx_, recs.data(), (uint32_t)recs.size(), 0), "set_lod_meshes")) return;
+                if (!check(ashcuda_set_lod_config(ctx_, &k), "set_lod_config")) return;
+                instancing_on_ = true;
+            }
             scene_dirty_ = false;
         }
     }
@@ -383,6 +588,7 @@ public:
         uint32_t st = ASH_STAGE_HIZ;
         if (culling.is_enabled()) st |= ASH_STAGE_CULL;
         if (lights.is_enabled()) st |= ASH_STAGE_LIGHTS;
+        if (instancing_on_ && culling.is_enabled()) st |= ASH_STAGE_INSTANCING;
         if (inputs_.hdr) {
             if (taa.is_enabled()) st |= ASH_STAGE_TAA;
             if (bloom.enabled) st |= ASH_STAGE_BLOOM;
@@ -397,6 +603,8 @@ public:
         if (ctx_ && check(ashcuda_readback(ctx_, ASH_BUF_VISIBLE_COUNT, &n, 4), "readback")) culling.update_stats(n);
         return n;
     }
+    // LodStats + InstancingStats of the last frame (syncs the stream)
+    bool read_instancing_stats(AshInstancingStats* out) { return ctx_ && check(ashcuda_readback(ctx_, ASH_BUF_INSTANCING_STATS, out, sizeof(*out)), "readback"); }
     ashcuda_ctx* context() const { return ctx_; }
     int last_code() const { return last_code_; }
     const std::string& last_error() const { return last_error_; }
@@ -415,7 +623,7 @@ private:
     AshCudaConfig cfg_{};
     ashcuda_ctx* ctx_ = nullptr;
     FrameInputs inputs_{};
-    bool have_inputs_ = false, scene_dirty_ = true;
+    bool have_inputs_ = false, scene_dirty_ = true, instancing_on_ = false;
     int last_code_ = ASH_OK;
     std::string last_error_;
 };

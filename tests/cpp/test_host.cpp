@@ -1,6 +1,7 @@
 // C++ host-layer tests (include/ashcuda_host.hpp).  Cases follow the reference's in-file unit tests:
 // occlusion_culling.rs:290-314, features/light_culling.rs:257-276, light_culling_integration.rs:216-231,
-// temporal_aa.rs:220-238, plus FeatureManager ordering (feature_trait.rs:57-97).
+// temporal_aa.rs:220-238, instancing.rs:279-334, lod_system.rs:396-428, plus FeatureManager ordering
+// (feature_trait.rs:57-97).
 // Usage: test_host          -> host logic + "no CPU fallback" check (exit 0 on success)
 //        test_host --gpu    -> additionally runs one small view through CudaComputeFeature on cuda:0
 #include <cassert>
@@ -84,6 +85,50 @@ int main(int argc, char** argv) {
         const char* want[] = {"B.added", "A.before", "B.before", "A.render", "B.render", "A.removed", "B.removed"};
         CHECK(g_log.size() == 7); for (int i = 0; i < 7; ++i) CHECK(std::strcmp(g_log[i], want[i]) == 0);
     }
+    {   // instancing.rs:283-320 test_instance_data / test_batching / test_multiple_batches
+        Mat4 m; identity(m); m[3][0] = 1.0f; m[3][1] = 2.0f; m[3][2] = 3.0f;                    // Mat4::from_translation
+        float p[3]; instance_position(instance_data_from_matrix(m), p);
+        CHECK(p[0] == 1.0f && p[1] == 2.0f && p[2] == 3.0f && sizeof(AshInstanceData) == 96);
+        InstancingManager mgr; mgr.begin_frame();
+        const BatchKey key{1, 1};
+        for (int i = 0; i < 100; ++i) { Mat4 t; identity(t); t[3][0] = (float)i; mgr.add_instance(key, instance_data_from_matrix(t)); }
+        mgr.finalize();
+        CHECK(mgr.stats().total_instances == 100 && mgr.stats().batch_count == 1 && mgr.stats().avg_instances_per_batch == 100.0f);
+        InstancingManager m2; m2.begin_frame();
+        for (uint32_t mesh = 0; mesh < 5; ++mesh) m2.add_instance(BatchKey{mesh, 0}, AshInstanceData{});
+        m2.finalize();
+        CHECK(m2.stats().batch_count == 5 && m2.batch_ids().size() == 5 && m2.batch_ids()[4] == 4);
+        m2.begin_frame(); m2.add_instance(BatchKey{3, 0}, AshInstanceData{}); m2.finalize();
+        CHECK(m2.stats().batch_count == 1 && m2.batch_ids()[0] == 3);                            // keys keep their dense ids
+    }
+    {   // lod_system.rs:400-425 test_single_lod / test_screen_coverage / test_reduction_rate
+        const LodMesh mesh = LodMesh::single(1000, 1.0f);
+        CHECK(mesh.level_count() == 1 && mesh.levels[0].index_count == 3000 && mesh.record().level_count == 1);
+        Mat4 proj, view, vp; perspective_rh(0.7853982f, 16.0f / 9.0f, 0.1f, 100.0f, proj); proj[1][1] = -proj[1][1];   // no Y flip here
+        identity(view); view[3][2] = -10.0f;                                                      // look_at_rh((0,0,10), 0, Y)
+        mat4_mul(proj, view, vp);
+        const float origin[3] = {0, 0, 0};
+        const float cov = LodManager::calculate_screen_coverage(origin, 1.0f, vp, 1920.0f, 1080.0f);
+        CHECK(cov > 0.0f && cov < 1.0f && std::fabs(cov - 3.14159265f * 96.0f * 96.0f / (1920.0f * 1080.0f)) < 1e-6f);
+        const float behind[3] = {0, 0, 20};
+        CHECK(LodManager::calculate_screen_coverage(behind, 1.0f, vp, 1920.0f, 1080.0f) == 0.0f);
+        LodStats st; st.triangles_before = 1000; st.triangles_after = 250;
+        CHECK(std::fabs(st.reduction_rate() - 0.75) < 0.001);
+        // select_lod: three levels, coverage 0.01396 -> level 1; Force; cull threshold
+        LodMesh m3; m3.bounding_radius = 1.0f;
+        m3.with_level(LodLevel{0.05f, 10.0f, 4000, 2000, 0, 12000}).with_level(LodLevel{0.01f, 50.0f, 1000, 500, 12000, 3000})
+          .with_level(LodLevel{0.0f, 1e9f, 100, 50, 15000, 300});
+        LodManager lm; lm.begin_frame();
+        const float cam[3] = {0, 0, 10};
+        LodSelection s = lm.select_lod(m3, origin, vp, cam, 1920.0f, 1080.0f);
+        CHECK(s.level == 1 && s.culled == 0 && s.blend == 0.0f && s.screen_coverage == cov);       // (0.01 - cov) / 0.01 < 0 -> clamped to 0
+        LodConfig force; force.mode = ASH_LOD_MODE_FORCE; force.force_level = 9;
+        LodManager lf(force); s = lf.select_lod(m3, origin, vp, cam, 1920.0f, 1080.0f);
+        CHECK(s.level == 2 && s.screen_coverage == 1.0f && lf.stats().objects_per_lod[2] == 1 && lf.stats().triangles_after == 100);
+        LodConfig strict; strict.cull_threshold = 0.5f;
+        LodManager lc(strict); s = lc.select_lod(m3, origin, vp, cam, 1920.0f, 1080.0f);
+        CHECK(s.culled == 1 && s.level == 2 && lc.stats().objects_culled == 1 && lc.stats().triangles_before == 4000);
+    }
     const uint32_t W = 320, H = 180;
     CudaComputeFeature f(W, H, 4096, 256, 9);
     FeatureFrameContext fc; FeatureRenderContext rc; Device dev;
@@ -95,7 +140,15 @@ int main(int argc, char** argv) {
     CHECK(f.context() != nullptr);
     Mat4 I; identity(I);
     const float c[3] = {0, 0, 0}, e[3] = {0.5f, 0.5f, 0.5f};
-    for (int i = 0; i < 64; ++i) { Mat4 M; identity(M); M[3][0] = (float)(i % 8) * 2.0f - 7.0f; M[3][1] = (float)(i / 8) * 2.0f - 7.0f; f.culling.add_object(bounding_box_from_center_extents(c, e), M, 0); }
+    f.lod_meshes.push_back(LodMesh::single(1000, 1.0f));
+    f.instancing.begin_frame();
+    for (int i = 0; i < 64; ++i) {
+        Mat4 M; identity(M); M[3][0] = (float)(i % 8) * 2.0f - 7.0f; M[3][1] = (float)(i / 8) * 2.0f - 7.0f;
+        f.culling.add_object(bounding_box_from_center_extents(c, e), M, 0);
+        f.instancing.add_instance(BatchKey{(uint32_t)(i % 2), 0}, instance_data_from_matrix(M));
+        f.lod_mesh_ids.push_back(0);
+    }
+    f.instancing.finalize();
     std::vector<PointLight> pl(32); for (int i = 0; i < 32; ++i) { pl[i].position[0] = (float)i - 16.0f; pl[i].position[2] = 20.0f; pl[i].radius = 4.0f; }
     f.lights.update_lights(pl, {});
     FrameInputs in; identity(in.view); in.view[3][2] = -22.0f; in.camera_pos[2] = 22.0f;
@@ -106,6 +159,8 @@ int main(int argc, char** argv) {
     CHECK(f.last_code() == ASH_OK);
     const uint32_t vis = f.read_visible_count();
     CHECK(vis > 0 && vis <= 64 && f.culling.stats().total_objects == 64);
+    AshInstancingStats ist{};
+    CHECK(f.read_instancing_stats(&ist) && ist.total_instances + ist.objects_culled == vis && ist.batch_count <= 2 && ist.triangles_before == 1000ull * vis);
     std::vector<uint8_t> ldr((size_t)W * H * 4);
     CHECK(ashcuda_readback(f.context(), ASH_BUF_LDR8, ldr.data(), ldr.size()) == ASH_OK && ldr[3] == 255 && ldr[0] > 0);
     f.on_removed(dev);
