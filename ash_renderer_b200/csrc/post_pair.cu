@@ -188,8 +188,11 @@ __device__ __forceinline__ void taa_strip(const float4 (*s_nb)[kHalo], const Taa
 // A persistent cp.async double-buffered variant of this kernel (as k_upsample_pipe, post_fast.cu) was
 // measured 20 % SLOWER (0.140 vs 0.116 ms at 4K): three barriers per tile and the extra shared-memory
 // pass outweigh the hidden load latency; the one-shot kernel below keeps its loads in registers.
+#ifndef ASH_TAA_MINB
+#define ASH_TAA_MINB 3
+#endif
 template <bool THRESH, bool VEL>
-__global__ void __launch_bounds__(256, 3)
+__global__ void __launch_bounds__(256, ASH_TAA_MINB)
 k_taa_pair(Tex16 cur, Tex16 hist, const __half2* __restrict__ vel, uint2* __restrict__ out, uint2* __restrict__ thr,
            AshTaaPushConstants pc, float threshold) {
     __shared__ float4 s_nb[kHalo][kHalo];      // tonemapped YCoCg of `current`, tile + halo
