@@ -28,7 +28,7 @@ EXPORTS = [
     "ashcuda_set_color", "ashcuda_taa_reset_history", "ashcuda_hiz_build", "ashcuda_occlusion_cull",
     "ashcuda_light_cull", "ashcuda_taa_resolve", "ashcuda_bloom", "ashcuda_tonemap",
     "ashcuda_view_run", "ashcuda_get", "ashcuda_readback", "ashcuda_readback_async", "ashcuda_sync",
-    "ashcuda_hiz_level_count", "ashcuda_mip_extent", "ashcuda_kernel_launches", "ashcuda_last_error",
+    "ashcuda_hiz_level_count", "ashcuda_mip_extent", "ashcuda_kernel_launches", "ashcuda_graph_stats", "ashcuda_last_error",
     "ashcuda_version", "ashcuda_profile_kernels", "ashcuda_kernel_time_ms", "ashcuda_upload_view", "ashcuda_download_view",
     "ashcuda_debug_exact_taps",
     "ashcuda_set_instances", "ashcuda_set_lod_meshes", "ashcuda_set_lod_config", "ashcuda_instancing_finalize",
@@ -81,6 +81,7 @@ def load_library():
         "ashcuda_hiz_level_count": (i32, [vp]),
         "ashcuda_mip_extent": (i32, [vp, i32, C.POINTER(u32), C.POINTER(u32)]),
         "ashcuda_kernel_launches": (C.c_uint64, [vp]),
+        "ashcuda_graph_stats": (C.c_int, [vp, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]),
         "ashcuda_last_error": (C.c_char_p, [vp]),
         "ashcuda_version": (C.c_char_p, []),
         "ashcuda_profile_kernels": (i32, [vp, u32]),
@@ -333,6 +334,12 @@ class Context:
 
     def kernel_launches(self):
         return int(self._lib.ashcuda_kernel_launches(self._h))
+
+    def graph_stats(self):
+        """(views captured into a CUDA graph, views replayed from one) by view_run."""
+        cap, rep = C.c_uint64(0), C.c_uint64(0)
+        self._ck(self._lib.ashcuda_graph_stats(self._h, C.byref(cap), C.byref(rep)))
+        return int(cap.value), int(rep.value)
 
     def profile_kernels(self, mask):
         self._ck(self._lib.ashcuda_profile_kernels(self._h, int(mask)))

@@ -66,6 +66,35 @@ struct Timed {
     ~Timed() { if (b) cudaEventRecord(b, L.s); }
 };
 
+// One by-value kernel argument that changes from view to view: which kernel, which argument, its new value.
+// CUDA-graph replay (view_graph.cu) patches exactly these nodes before each launch.
+struct PatchArg {
+    const void* func = nullptr;
+    int         arg_index = 0, n_args = 0;
+    alignas(16) unsigned char value[256];
+};
+void cull_patch(const AshCullingPushConstants& pc, PatchArg* out);                                   // occlusion_cull.cu
+void taa_pair_patch(bool thresh, bool vel, const AshTaaPushConstants& pc, PatchArg* out);           // post_pair.cu
+bool taa_in_halo(const AshTaaPushConstants& pc);                                                     // post_fast.cu
+void lod_patch(const AshInstancingParams& ip, const AshLodConfig& cfg, PatchArg* out);               // instancing.cu
+
+// What a captured view depends on besides the per-view values patched at replay (memcmp'd, zero-initialised).
+struct GraphKey {
+    cudaStream_t stream; const void *depth, *color, *velocity, *objs, *draws_in, *lights, *inst, *inst_batch, *inst_mesh, *lod_meshes;
+    uint32_t stages, n_objs, n_draws, n_lights, n_inst, n_lod_meshes, object_count, hiz_levels, lod_use_visibility;
+    AshLightCullingPushConstants light;
+    float    taa_screen[4];
+    AshBloomParams bloom; AshPostProcessPushConstants post;
+    uint32_t in_halo, taa_cur, history_valid, taa_ran, have_color, have_depth, have_instancing, concurrent;
+};
+struct ViewGraph {
+    cudaGraph_t graph = nullptr; cudaGraphExec_t exec = nullptr;
+    cudaGraphNode_t n_store = nullptr, n_cull = nullptr, n_taa = nullptr, n_lod = nullptr;
+    GraphKey key{}; bool valid = false;
+    uint64_t launches = 0;                                  // kernels per replay
+    bool taa_flip = false, history_valid = false, taa_ran = false, bloom_valid = false, have_pyramid = false, have_camera = false;
+};
+
 }  // namespace ash
 
 struct ashcuda_ctx {
@@ -131,6 +160,11 @@ struct ashcuda_ctx {
     AshIndirectDrawCommand* inst_draws = nullptr;
     AshInstancingStats* inst_stats = nullptr;
     bool      have_instancing = false;
+
+    // CUDA-graph replay of view_run (view_graph.cu): one captured graph per TAA ping-pong parity
+    ash::ViewGraph vgraph[2];
+    bool      graphs_broken = false;             // a capture failed once: stay on the eager path
+    uint64_t  graph_replays = 0, graph_captures = 0;
     uint32_t* tile_data = nullptr;
     AshViewStats* stats = nullptr;
 
@@ -166,6 +200,8 @@ cudaError_t launch_light_cull(const AshGpuLight* lights, const AshLightCullingPu
                               uint32_t* depth_range, LightCand* cand, uint32_t* cand_idx,
                               uint32_t* cand_count, uint8_t* scratch, uint32_t max_lights,
                               uint32_t* tile_data, AshViewStats* stats, const Launch& L);
+cudaError_t launch_store_view(const AshCullingCameraData& cam, bool with_camera, uint32_t view_id, AshCullingCameraData* camera_dev,
+                              AshViewStats* stats, const Launch& L);                                  // view_graph.cu
 cudaError_t launch_batch_mesh(const uint32_t* batch_id, const uint32_t* mesh_id, uint32_t n, uint32_t n_batches,
                               uint32_t* batch_mesh, cudaStream_t s);
 size_t instancing_hist_bytes(uint32_t max_objects, uint32_t n_buckets);
@@ -213,3 +249,17 @@ bool axis_down_taps_exact(int sn, int dn);
 bool axis_up_taps_exact(int sn, int dn);
 
 }  // namespace ash
+
+#define ASH_CUDA(ctx, call)                                                              \
+    do {                                                                                 \
+        cudaError_t e__ = (call);                                                        \
+        if (e__ != cudaSuccess) {                                                        \
+            (ctx)->err = std::string(#call) + ": " + cudaGetErrorString(e__);            \
+            return e__ == cudaErrorMemoryAllocation ? ASH_ERR_OUT_OF_MEMORY : ASH_ERR_DEVICE; \
+        }                                                                                \
+    } while (0)
+
+// view_graph.cu / ashcuda.cu
+int  ash_view_run_eager(ashcuda_ctx* c, const AshCudaViewParams* vp);
+int  ash_view_run_graph(ashcuda_ctx* c, const AshCudaViewParams* vp, bool* handled);
+void ash_view_graphs_destroy(ashcuda_ctx* c);

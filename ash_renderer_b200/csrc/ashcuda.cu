@@ -31,15 +31,6 @@ void ash::Profiler::release_all() {
     open.clear(); pool.clear();
 }
 
-#define ASH_CUDA(ctx, call)                                                              \
-    do {                                                                                 \
-        cudaError_t e__ = (call);                                                        \
-        if (e__ != cudaSuccess) {                                                        \
-            (ctx)->err = std::string(#call) + ": " + cudaGetErrorString(e__);            \
-            return e__ == cudaErrorMemoryAllocation ? ASH_ERR_OUT_OF_MEMORY : ASH_ERR_DEVICE; \
-        }                                                                                \
-    } while (0)
-
 static int fail(ashcuda_ctx* c, int code, const char* msg) {
     if (c) c->err = msg;
     return code;
@@ -73,6 +64,7 @@ void ashcuda_default_config(AshCudaConfig* cfg) {
     cfg->srgb_encode = 0;
     cfg->concurrent_frontend = 1;
     cfg->max_batches = 64;
+    cfg->graph_replay = 1;
 }
 
 const char* ashcuda_last_error(ashcuda_ctx* ctx) {
@@ -83,6 +75,7 @@ void ashcuda_destroy(ashcuda_ctx* c) {
     if (!c) return;
     cudaSetDevice(c->device);
     if (c->stream) cudaStreamSynchronize(c->stream);
+    ash_view_graphs_destroy(c);
     void* owned[] = {c->depth_owned, c->pyr.mips, c->tile_minmax, c->depth_range, c->counters,
                      c->objs_owned, c->draws_in_owned, c->visibility, c->vis_bits, c->cta_counts,
                      c->draws_out, c->visible_count, c->lights_owned, c->camera_dev, c->cand,
@@ -223,6 +216,7 @@ int ashcuda_set_stream(ashcuda_ctx* c, void* cuda_stream) {
     if (!c) return ASH_ERR_INVALID;
     ASH_CUDA(c, cudaSetDevice(c->device));
     ASH_CUDA(c, cudaStreamSynchronize(c->stream));
+    ash_view_graphs_destroy(c);                // captured views name the old stream
     if (c->own_stream) { cudaStreamDestroy(c->stream); c->own_stream = false; }
     if (cuda_stream) { c->stream = static_cast<cudaStream_t>(cuda_stream); }
     else { ASH_CUDA(c, cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking)); c->own_stream = true; }
@@ -482,6 +476,15 @@ static int view_post(ashcuda_ctx* c, const AshCudaViewParams* vp) {
 
 int ashcuda_view_run(ashcuda_ctx* c, const AshCudaViewParams* vp) {
     if (!c || !vp) return fail(c, ASH_ERR_INVALID, "view_run: null");
+    bool handled = false;                      // view_graph.cu: replay of a captured view, else the eager body
+    int rc = ash_view_run_graph(c, vp, &handled);
+    if (rc || handled) return rc;
+    return ash_view_run_eager(c, vp);
+}
+
+}  // extern "C"
+
+int ash_view_run_eager(ashcuda_ctx* c, const AshCudaViewParams* vp) {
     int rc = ASH_OK;
     const uint32_t st = vp->stages;
     // ---- front end (Hi-Z -> cull, light cull): independent of the post chain of the same view, so it
@@ -498,7 +501,13 @@ int ashcuda_view_run(ashcuda_ctx* c, const AshCudaViewParams* vp) {
         ASH_CUDA(c, cudaStreamWaitEvent(c->front_stream, c->ev_fork, 0));
         c->stream = c->front_stream;
     }
-    if (st & (ASH_STAGE_LIGHTS)) rc = ashcuda_set_camera(c, &vp->camera);
+    {   // camera block (light cull) and view id, by value: no host memory is read after this call returns
+        const bool with_camera = (st & ASH_STAGE_LIGHTS) != 0;
+        cudaError_t e = cudaSetDevice(c->device);
+        if (e == cudaSuccess) e = launch_store_view(vp->camera, with_camera, vp->view_id, c->camera_dev, c->stats, c->L());
+        if (e != cudaSuccess) { c->err = std::string("view_run: ") + cudaGetErrorString(e); rc = ASH_ERR_DEVICE; }
+        else if (with_camera) { c->camera_host = vp->camera; c->have_camera = true; }
+    }
     if (!rc && (st & ASH_STAGE_HIZ)) rc = ashcuda_hiz_build(c);
     if (!rc && (st & ASH_STAGE_CULL)) rc = ashcuda_occlusion_cull(c, &vp->cull);
     if (!rc && (st & ASH_STAGE_INSTANCING)) {        // consumes visibility[] of the cull above
@@ -521,10 +530,10 @@ int ashcuda_view_run(ashcuda_ctx* c, const AshCudaViewParams* vp) {
         cudaError_t e = cudaStreamWaitEvent(c->stream, c->ev_join, 0);
         if (!rc && e != cudaSuccess) { c->err = std::string("view_run: ") + cudaGetErrorString(e); rc = ASH_ERR_DEVICE; }
     }
-    if (rc) return rc;
-    ASH_CUDA(c, cudaMemcpyAsync(&c->stats->view_id, &vp->view_id, 4, cudaMemcpyHostToDevice, c->stream));
-    return ASH_OK;
+    return rc;
 }
+
+extern "C" {
 
 // ------------------------------------------------------------------------------ (f-2) instancing / LOD
 static void lod_config_default(AshLodConfig* k) {          // LodConfig::default(), lod_system.rs:47-57
@@ -704,6 +713,12 @@ int ashcuda_debug_exact_taps(int kind, int n_src, int n_dst, float size_f, float
 }
 
 uint64_t ashcuda_kernel_launches(ashcuda_ctx* c) { return c ? c->launches : 0; }
+
+int ashcuda_graph_stats(ashcuda_ctx* c, uint64_t* captures, uint64_t* replays) {
+    if (!c || !captures || !replays) return fail(c, ASH_ERR_INVALID, "graph_stats: null");
+    *captures = c->graph_captures; *replays = c->graph_replays;
+    return ASH_OK;
+}
 
 int ashcuda_profile_kernels(ashcuda_ctx* c, uint32_t mask) {
     if (!c) return ASH_ERR_INVALID;

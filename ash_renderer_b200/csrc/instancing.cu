@@ -17,6 +17,7 @@
 //
 // Algorithmic bytes per call: N*(4 + 4 + 4) (visibility, batch id, mesh id) + 12 B position per visible
 // object + 16 B selection per object + 2*96 B per kept instance + 20 B per bucket.
+#include <cstring>
 #include "ash_internal.cuh"
 #include "ash_math.cuh"
 
@@ -268,6 +269,24 @@ size_t instancing_hist_bytes(uint32_t max_objects, uint32_t n_buckets) {
     return (size_t)((max_objects + kInstThreads - 1) / kInstThreads) * n_buckets * sizeof(uint32_t) * 2;   // counts + bases
 }
 
+static LodParams make_lod_params(const AshInstancingParams& ip, const AshLodConfig& cfg) {
+    LodParams P;
+    for (int c = 0; c < 4; ++c) for (int r = 0; r < 4; ++r) P.vp[c * 4 + r] = ip.view_proj[c][r];
+    P.cam[0] = ip.camera_pos[0]; P.cam[1] = ip.camera_pos[1]; P.cam[2] = ip.camera_pos[2];
+    P.sw = ip.screen_size[0]; P.sh = ip.screen_size[1];
+    P.cfg = cfg;
+    return P;
+}
+
+// graph replay: argument 7 of k_lod_select is the per-view LodParams
+void lod_patch(const AshInstancingParams& ip, const AshLodConfig& cfg, PatchArg* out) {
+    static_assert(sizeof(LodParams) <= sizeof(out->value), "PatchArg too small");
+    const LodParams P = make_lod_params(ip, cfg);
+    out->func = reinterpret_cast<const void*>(&k_lod_select);
+    out->arg_index = 7; out->n_args = 13;
+    std::memcpy(out->value, &P, sizeof(P));
+}
+
 cudaError_t launch_instancing(const AshInstanceData* inst, const uint32_t* batch_id, const uint32_t* mesh_id,
                               const AshLodMesh* meshes, uint32_t n_meshes, const uint32_t* batch_mesh,
                               const uint32_t* visibility, const AshInstancingParams& ip, const AshLodConfig& cfg,
@@ -276,11 +295,7 @@ cudaError_t launch_instancing(const AshInstanceData* inst, const uint32_t* batch
                               AshInstancingStats* stats, const Launch& L) {
     const uint32_t n = ip.object_count;
     const uint32_t n_ctas = (n + kInstThreads - 1) / kInstThreads;
-    LodParams P;
-    for (int c = 0; c < 4; ++c) for (int r = 0; r < 4; ++r) P.vp[c * 4 + r] = ip.view_proj[c][r];
-    P.cam[0] = ip.camera_pos[0]; P.cam[1] = ip.camera_pos[1]; P.cam[2] = ip.camera_pos[2];
-    P.sw = ip.screen_size[0]; P.sh = ip.screen_size[1];
-    P.cfg = cfg;
+    const LodParams P = make_lod_params(ip, cfg);
     Timed timed(L, ASH_KERNEL_INSTANCING);
     cudaError_t e = cudaMemsetAsync(stats, 0, sizeof(AshInstancingStats), L.s);
     if (e != cudaSuccess) return e;

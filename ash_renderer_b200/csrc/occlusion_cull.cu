@@ -8,6 +8,7 @@
 //
 // Algorithmic bytes per launch: 112*N (objects) + 4*N (visibility) + 4*N (one Hi-Z texel)
 // + 40*V (draw command in + out) + 4.
+#include <cstring>
 #include "ash_internal.cuh"
 #include "ash_math.cuh"
 
@@ -167,11 +168,7 @@ k_cull_compact(const AshCullObjectData* __restrict__ objs, const AshIndirectDraw
     }
 }
 
-cudaError_t launch_occlusion_cull(const AshCullObjectData* objs, const AshIndirectDrawCommand* draws_in,
-                                  const AshCullingPushConstants& pc, const Pyramid& p,
-                                  uint32_t* visibility, uint32_t* vis_bits, uint32_t* cta_counts,
-                                  AshIndirectDrawCommand* draws_out, uint32_t* visible_count,
-                                  AshViewStats* stats, const Launch& L) {
+static CullParams make_cull_params(const AshCullingPushConstants& pc) {
     CullParams cp;
     for (int c = 0; c < 4; ++c)
         cp.vp.c[c] = {pc.view_proj[c][0], pc.view_proj[c][1], pc.view_proj[c][2], pc.view_proj[c][3]};
@@ -179,6 +176,24 @@ cudaError_t launch_occlusion_cull(const AshCullObjectData* objs, const AshIndire
     cp.screen_h = pc.screen_params[1];
     cp.object_count = pc.object_count;
     cp.hiz_levels = pc.hiz_levels;
+    return cp;
+}
+
+// graph replay: argument 1 of k_occlusion_cull is the per-view CullParams
+void cull_patch(const AshCullingPushConstants& pc, PatchArg* out) {
+    static_assert(sizeof(CullParams) <= sizeof(out->value), "PatchArg too small");
+    const CullParams cp = make_cull_params(pc);
+    out->func = reinterpret_cast<const void*>(&k_occlusion_cull);
+    out->arg_index = 1; out->n_args = 6;
+    std::memcpy(out->value, &cp, sizeof(cp));
+}
+
+cudaError_t launch_occlusion_cull(const AshCullObjectData* objs, const AshIndirectDrawCommand* draws_in,
+                                  const AshCullingPushConstants& pc, const Pyramid& p,
+                                  uint32_t* visibility, uint32_t* vis_bits, uint32_t* cta_counts,
+                                  AshIndirectDrawCommand* draws_out, uint32_t* visible_count,
+                                  AshViewStats* stats, const Launch& L) {
+    const CullParams cp = make_cull_params(pc);
     const uint32_t grid = (pc.object_count + kCullThreads - 1) / kCullThreads;
     {
         Timed timed(L, ASH_KERNEL_OCCLUSION_CULL);

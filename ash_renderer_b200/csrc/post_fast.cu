@@ -174,12 +174,16 @@ k_taa_fast(Tex16 cur, Tex16 hist, uint2* __restrict__ out, uint2* __restrict__ t
     }
 }
 
+bool taa_in_halo(const AshTaaPushConstants& pc) {
+    return fabsf(pc.jitter[0] - pc.prev_jitter[0]) <= 0.99f && fabsf(pc.jitter[1] - pc.prev_jitter[1]) <= 0.99f;
+}
+
 cudaError_t launch_taa_fast(const void* cur, const void* hist, const void* vel_or_null, void* out, void* thr_or_null,
                             const AshTaaPushConstants& pc, float threshold, const Launch& L) {
     const int W = (int)pc.screen_params[0], H = (int)pc.screen_params[1];
     const Tex16 c{static_cast<const uint2*>(cur), W, H}, h{static_cast<const uint2*>(hist), W, H};
     const dim3 grid((W + 31) / 32, (H + 31) / 32);
-    const bool in_halo = fabsf(pc.jitter[0] - pc.prev_jitter[0]) <= 0.99f && fabsf(pc.jitter[1] - pc.prev_jitter[1]) <= 0.99f;
+    const bool in_halo = taa_in_halo(pc);
     uint2* o = static_cast<uint2*>(out);
     uint2* t = static_cast<uint2*>(thr_or_null);
     // the usual case (sub-pixel jitter delta): two pixels per thread on the packed fp32 pipe, post_pair.cu

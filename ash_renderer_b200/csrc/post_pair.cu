@@ -1,6 +1,7 @@
 // post_pair.cu — post kernels that evaluate two pixels per thread in lock-step on the packed fp32 pipe
 // (FADD2 / FMUL2 / FFMA2, ash_f32x2.cuh).  Bit-identical to post_fast.cu / post.cu: the same pinned
 // IEEE operation sequence per lane; only the instruction count changes.
+#include <cstring>
 #include "post_pair.cuh"
 
 namespace ash {
@@ -228,6 +229,14 @@ k_taa_pair(Tex16 cur, Tex16 hist, const __half2* __restrict__ vel, uint2* __rest
     }
     __syncthreads();
     taa_strip<THRESH, VEL>(s_nb, s_raw, s_tb, clamp_on, W, H, x0, y0, out, thr, threshold, hist, vel, pc);
+}
+
+// graph replay: argument 5 of k_taa_pair is the per-view AshTaaPushConstants
+void taa_pair_patch(bool thresh, bool vel, const AshTaaPushConstants& pc, PatchArg* out) {
+    out->func = thresh ? (vel ? reinterpret_cast<const void*>(&k_taa_pair<true, true>) : reinterpret_cast<const void*>(&k_taa_pair<true, false>))
+                       : (vel ? reinterpret_cast<const void*>(&k_taa_pair<false, true>) : reinterpret_cast<const void*>(&k_taa_pair<false, false>));
+    out->arg_index = 5; out->n_args = 7;
+    std::memcpy(out->value, &pc, sizeof(pc));
 }
 
 cudaError_t launch_taa_pair(const void* cur, const void* hist, const void* vel_or_null, void* out, void* thr_or_null,

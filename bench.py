@@ -306,7 +306,8 @@ def run_cuda(args):
     slots = []
     for v in range(B):
         cam, depth, hdr = host_views[v % distinct]
-        c = backend.Context(W, H, device=local, max_objects=n_objs, max_lights=n_lights, hiz_levels=HIZ_LEVELS)
+        c = backend.Context(W, H, device=local, max_objects=n_objs, max_lights=n_lights, hiz_levels=HIZ_LEVELS,
+                            graph_replay=args.graph_replay)
         c.set_stream(streams[v % args.streams].cuda_stream)
         c.set_objects(d_objs, d_draws)
         c.upload_lights(d_lights)
@@ -499,6 +500,7 @@ def run_cuda(args):
                    + (" + per-pixel velocity buffer in the TAA (--velocity; resident passes only)" if args.velocity else ""),
                    "views_per_gpu_per_step": B, "distinct_view_inputs_per_gpu": distinct,
                    "streams": args.streams, "concurrent_frontend": True,
+                   "graph_replay": bool(args.graph_replay),
                    "kernel_timing": f"same {args.steps} steps repeated serialised (1 stream, no fork) with CUDA events around each launch: "
                                     f"{prof_ms / args.steps:.3f} ms/step", "l2": f"inputs larger than L2: {B} views x 99.5 MB of depth+HDR per step per GPU",
                    "visible_fraction_mean": st_mean["visible_objects"] / n_objs,
@@ -551,6 +553,8 @@ def main():
     ap.add_argument("--distinct", type=int, default=4, help="distinct synthetic depth/HDR inputs generated per GPU (host setup cost)")
     ap.add_argument("--streams", type=int, default=4)
     ap.add_argument("--cpu-views", type=int, default=2)
+    ap.add_argument("--graph-replay", type=int, default=1, choices=[0, 1],
+                    help="1: view_run replays a captured CUDA graph per view (library default); 0: launches every kernel")
     ap.add_argument("--velocity", action="store_true",
                     help="supply a per-pixel RG16F velocity buffer to the TAA (the headline workload has none, PIN-12)")
     ap.add_argument("--instancing", action="store_true",

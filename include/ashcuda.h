@@ -214,7 +214,10 @@ typedef struct AshCudaConfig {
     uint32_t concurrent_frontend; /* 1 (default): view_run runs Hi-Z + cull + light cull on a second
                                      stream, concurrently with the post chain of the same view     */
     uint32_t max_batches;     /* instancing: distinct batch ids (BatchKey values), default 64, <= 128 */
-    uint32_t _reserved[7];
+    uint32_t graph_replay;    /* 1 (default): view_run captures the view into a CUDA graph once and replays it,
+                                 patching the per-view kernel arguments; 0: launch every kernel each view.
+                                 Same kernels, same results either way (csrc/view_graph.cu)                 */
+    uint32_t _reserved[6];
 } AshCudaConfig;
 
 /* Per-view statistics (OcclusionStats, occlusion_culling.rs:152-185 + tile list stats).
@@ -358,6 +361,8 @@ int ashcuda_sync    (ashcuda_ctx*);
 int ashcuda_hiz_level_count(ashcuda_ctx*);                     /* levels_built (PIN-4) */
 int ashcuda_mip_extent(ashcuda_ctx*, int which, uint32_t* w, uint32_t* h);
 uint64_t ashcuda_kernel_launches(ashcuda_ctx*);                /* kernels launched so far by this ctx */
+/* view_run graph replay (AshCudaConfig.graph_replay): views captured into a CUDA graph / views replayed from one */
+int ashcuda_graph_stats(ashcuda_ctx*, uint64_t* captures, uint64_t* replays);
 /* Device-time accounting: launches of the classes in `mask` (bit ASH_KERNEL_*) are bracketed by
  * CUDA events on the ctx stream.  ashcuda_kernel_time_ms syncs the stream, returns the time and
  * launch count accumulated for one class since the previous query of it, and resets them.

@@ -16,7 +16,7 @@ pub struct AshBloomParams { pub threshold: f32, pub upsample_intensity: f32, pub
 #[repr(C)] #[derive(Clone, Copy, Default)]
 pub struct AshCudaConfig {
     pub max_objects: u32, pub max_lights: u32, pub max_draws: u32, pub hiz_levels: u32, pub bloom_mips: u32,
-    pub enable_post: u32, pub srgb_encode: u32, pub concurrent_frontend: u32, pub max_batches: u32, pub _reserved: [u32; 7],
+    pub enable_post: u32, pub srgb_encode: u32, pub concurrent_frontend: u32, pub max_batches: u32, pub graph_replay: u32, pub _reserved: [u32; 6],
 }
 
 #[repr(C)] #[derive(Clone, Copy)]
@@ -111,6 +111,7 @@ extern "C" {
     pub fn ashcuda_hiz_level_count(ctx: *mut ashcuda_ctx) -> c_int;
     pub fn ashcuda_mip_extent(ctx: *mut ashcuda_ctx, which: c_int, w: *mut u32, h: *mut u32) -> c_int;
     pub fn ashcuda_kernel_launches(ctx: *mut ashcuda_ctx) -> u64;
+    pub fn ashcuda_graph_stats(ctx: *mut ashcuda_ctx, captures: *mut u64, replays: *mut u64) -> c_int;
     pub fn ashcuda_profile_kernels(ctx: *mut ashcuda_ctx, mask: u32) -> c_int;
     pub fn ashcuda_kernel_time_ms(ctx: *mut ashcuda_ctx, kernel_class: c_int, ms: *mut f32, launches: *mut u64) -> c_int;
     pub fn ashcuda_debug_exact_taps(kind: c_int, n_src: c_int, n_dst: c_int, size_f: f32, inv: f32) -> c_int;

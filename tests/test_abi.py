@@ -85,6 +85,7 @@ def test_default_config_mirrors_reference_constants():
     assert cfg["hiz_levels"][0] == 10          # occlusion_culling.rs:21
     assert cfg["bloom_mips"][0] == 5           # features/bloom.rs:29
     assert cfg["max_batches"][0] == 64
+    assert cfg["graph_replay"][0] == 1
 
 
 def test_null_and_bad_arguments_do_not_crash():

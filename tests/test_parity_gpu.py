@@ -535,6 +535,65 @@ def test_view_run_post_chain_with_velocity_buffer(backend, oracle):
             hist = ref
 
 
+@pytest.mark.parametrize("velocity", [False, True])
+def test_view_run_graph_replay_equals_eager(backend, velocity):
+    """view_run through CUDA-graph replay (per-view kernel arguments patched) against the eager launches:
+    a moving camera, TAA jitter sequence, instancing stage; every output of every view bit-identical."""
+    from ash_renderer_b200 import host
+    from ash_renderer_b200.host import TemporalAA
+    W, H, n_batches, n_views = 640, 360, 4, 8
+    cam0, objs, draws, depth, meshes, inst, batch, mesh = _instancing_scene(W, H, (10, 8, 8), seed=31, n_batches=n_batches)
+    lights = synth.make_lights(300, extent=10.0, seed=31, center=(0.0, 2.0, 22.0))
+    seq = synth.HdrSequence(W, H, seed=32, n_discs=20)
+    vel = synth.random_velocity(W, H, seed=33, still_frac=0.3, max_px=4.0) if velocity else None
+    taa = TemporalAA()
+    views = []
+    for t in range(n_views):
+        taa.begin_frame()
+        j = taa.current_jitter()
+        cam = synth.Camera((0.6 * t - 2.0, 2.0 + 0.1 * t, 22.0 - 0.5 * t), (0.1 * t, 0, 0), W, H)
+        vp = _view_params(cam, len(objs), len(lights), 9, W, H, taa.push_constants(W, H),
+                          stages=T.STAGE_ALL | T.STAGE_KEEP_BLOOM | T.STAGE_INSTANCING, view_id=100 + t)
+        views.append((seq.frame(float(j[0]), float(j[1])), vp))
+    outs = {}
+    for mode in (0, 1):
+        with _ctx(backend, W, H, max_batches=n_batches, graph_replay=mode) as c:
+            c.set_objects(objs, draws)
+            c.upload_lights(lights)
+            c.set_depth(depth)
+            c.set_instances(inst, batch, mesh)
+            c.set_lod_meshes(meshes)
+            c.set_lod_config(host.LodConfig().record(use_visibility=True))
+            per_view = []
+            for f, vp in views:
+                c.set_color(f, vel)
+                c.view_run(vp)
+                cnt = c.visible_count()
+                st = c.instancing_stats()
+                per_view.append(dict(vis=c.visibility(), cnt=cnt, draws=c.draws_out(cnt), tiles=c.tile_data(), stats=c.stats().tobytes(),
+                                     taa=c.taa_out(), bloom=c.bloom_mip(0), ldr=c.ldr8(), sel=c.lod_selection().tobytes(),
+                                     off=c.bucket_offsets(), idraws=c.instance_draws(), istats=st.tobytes(),
+                                     iout=c.instances_out(int(st["total_instances"])).tobytes()))
+            outs[mode] = per_view
+            cap, rep = c.graph_stats()
+            if mode == 0:
+                assert (cap, rep) == (0, 0)
+            else:      # parity 0 first frame (no history), parity 1, parity 0 with history, then replays
+                assert cap == 3 and rep == n_views - 3, (cap, rep)
+            launches = c.kernel_launches()
+        outs[("launches", mode)] = launches
+    assert outs[("launches", 0)] == outs[("launches", 1)]
+    for t, (a, b) in enumerate(zip(outs[0], outs[1])):
+        assert a["cnt"] == b["cnt"] and a["stats"] == b["stats"], f"view {t}: stats"
+        for k in ("vis", "draws", "tiles", "off", "idraws"):
+            assert np.array_equal(a[k], b[k]), f"view {t}: {k}"
+        for k in ("sel", "istats", "iout"):
+            assert a[k] == b[k], f"view {t}: {k}"
+        for k in ("taa", "bloom", "ldr"):
+            assert np.array_equal(np.asarray(a[k]).view(np.uint8), np.asarray(b[k]).view(np.uint8)), f"view {t}: {k}"
+    assert len({v["stats"] for v in outs[1]}) == n_views      # the views really differ (view id, counts)
+
+
 def test_view_io_host_path(backend, oracle):
     """upload_view / download_view (the e2e path): host buffers in, host buffers out."""
     W, H = 320, 180
