@@ -32,6 +32,7 @@ EXPORTS = [
     "ashcuda_version", "ashcuda_profile_kernels", "ashcuda_kernel_time_ms", "ashcuda_upload_view", "ashcuda_download_view",
     "ashcuda_debug_exact_taps",
     "ashcuda_set_instances", "ashcuda_set_lod_meshes", "ashcuda_set_lod_config", "ashcuda_instancing_finalize",
+    "ashcuda_set_forward_params", "ashcuda_forward_depth", "ashcuda_forward_shade",
 ]
 
 
@@ -93,6 +94,9 @@ def load_library():
         "ashcuda_set_lod_meshes": (i32, [vp, vp, u32, i32]),
         "ashcuda_set_lod_config": (i32, [vp, vp]),
         "ashcuda_instancing_finalize": (i32, [vp, vp]),
+        "ashcuda_set_forward_params": (i32, [vp, vp]),
+        "ashcuda_forward_depth": (i32, [vp, vp, u32]),
+        "ashcuda_forward_shade": (i32, [vp]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(lib, name)
@@ -331,6 +335,27 @@ class Context:
 
     def instances_out(self, count):
         return self.readback(T.BUF_INSTANCES_OUT, T.INSTANCE_DATA, count)
+
+    # ---- row f-1: depth / HDR producers (compute forward pass)
+    def set_forward_params(self, params=None):
+        self._ck(self._lib.ashcuda_set_forward_params(
+            self._h, None if params is None else np.ascontiguousarray(params, T.FORWARD_PARAMS).ctypes.data))
+
+    def forward_depth(self, camera, object_count):
+        cam = np.ascontiguousarray(camera, T.CAMERA_DATA)
+        self._ck(self._lib.ashcuda_forward_depth(self._h, cam.ctypes.data, int(object_count)))
+
+    def forward_shade(self):
+        self._ck(self._lib.ashcuda_forward_shade(self._h))
+
+    def forward_keys(self):
+        return self.readback(T.BUF_FORWARD_KEYS, np.uint64).reshape(self.H, self.W)
+
+    def depth(self):
+        return self.readback(T.BUF_HIZ_MIP(0), np.float32).reshape(self.H, self.W)
+
+    def color(self):
+        return self.readback(T.BUF_COLOR, np.float16).reshape(self.H, self.W, 4)
 
     def kernel_launches(self):
         return int(self._lib.ashcuda_kernel_launches(self._h))

@@ -77,6 +77,7 @@ void cull_patch(const AshCullingPushConstants& pc, PatchArg* out);              
 void taa_pair_patch(bool thresh, bool vel, const AshTaaPushConstants& pc, PatchArg* out);           // post_pair.cu
 bool taa_in_halo(const AshTaaPushConstants& pc);                                                     // post_fast.cu
 void lod_patch(const AshInstancingParams& ip, const AshLodConfig& cfg, PatchArg* out);               // instancing.cu
+void forward_setup_patch(const AshCullingCameraData& cam, PatchArg* out);                            // forward.cu
 
 // What a captured view depends on besides the per-view values patched at replay (memcmp'd, zero-initialised).
 struct GraphKey {
@@ -86,13 +87,16 @@ struct GraphKey {
     float    taa_screen[4];
     AshBloomParams bloom; AshPostProcessPushConstants post;
     uint32_t in_halo, taa_cur, history_valid, taa_ran, have_color, have_depth, have_instancing, concurrent;
+    AshForwardParams fwd;
 };
 struct ViewGraph {
     cudaGraph_t graph = nullptr; cudaGraphExec_t exec = nullptr;
-    cudaGraphNode_t n_store = nullptr, n_cull = nullptr, n_taa = nullptr, n_lod = nullptr;
+    cudaGraphNode_t n_store = nullptr, n_cull = nullptr, n_taa = nullptr, n_lod = nullptr, n_fwd = nullptr;
     GraphKey key{}; bool valid = false;
     uint64_t launches = 0;                                  // kernels per replay
     bool taa_flip = false, history_valid = false, taa_ran = false, bloom_valid = false, have_pyramid = false, have_camera = false;
+    bool have_depth = false, have_color = false, have_forward = false;
+    const float* depth = nullptr; const void* color = nullptr; const void* velocity = nullptr;
 };
 
 }  // namespace ash
@@ -161,6 +165,17 @@ struct ashcuda_ctx {
     AshInstancingStats* inst_stats = nullptr;
     bool      have_instancing = false;
 
+    // (f-1) compute forward pass (forward.cu); allocated on the first ashcuda_forward_depth
+    AshForwardParams fwd_params{};
+    unsigned long long* fwd_keys = nullptr;      // W*H: depth bits << 32 | object index
+    float4*   fwd_spheres = nullptr;             // per object: view-space centre, radius
+    int4*     fwd_rects = nullptr;               // per object: pixel rectangle [x0,y0,x1,y1)
+    uint32_t* fwd_big = nullptr;                 // [0] count, [1..] object indices with a big rectangle
+    float4*   fwd_lights_view = nullptr;
+    float*    fwd_rays = nullptr;                // W + H ray-table entries
+    void*     fwd_consts = nullptr;
+    bool      have_forward = false;              // keys / spheres of the current view are valid
+
     // CUDA-graph replay of view_run (view_graph.cu): one captured graph per TAA ping-pong parity
     ash::ViewGraph vgraph[2];
     bool      graphs_broken = false;             // a capture failed once: stay on the eager path
@@ -202,6 +217,15 @@ cudaError_t launch_light_cull(const AshGpuLight* lights, const AshLightCullingPu
                               uint32_t* tile_data, AshViewStats* stats, const Launch& L);
 cudaError_t launch_store_view(const AshCullingCameraData& cam, bool with_camera, uint32_t view_id, AshCullingCameraData* camera_dev,
                               AshViewStats* stats, const Launch& L);                                  // view_graph.cu
+size_t forward_consts_bytes();                                                                       // forward.cu
+cudaError_t launch_forward_depth(const AshCullingCameraData& cam, const AshForwardParams& fp, const AshCullObjectData* objs, uint32_t n,
+                                 const AshGpuLight* lights, uint32_t n_lights, uint32_t W, uint32_t H, float4* spheres, int4* rects,
+                                 uint32_t* big_list, uint32_t* big_count, float4* lights_view, float* ray_x, float* ray_y,
+                                 void* consts, unsigned long long* keys, float* depth, const Launch& L);
+cudaError_t launch_forward_shade(const AshForwardParams& fp, const unsigned long long* keys, const float4* spheres,
+                                 const AshGpuLight* lights, uint32_t n_lights, const float4* lights_view, const uint32_t* tile_data,
+                                 const AshInstanceData* inst, uint32_t n_inst, const void* consts, const float* ray_x,
+                                 const float* ray_y, uint32_t W, uint32_t H, void* hdr, const Launch& L);
 cudaError_t launch_batch_mesh(const uint32_t* batch_id, const uint32_t* mesh_id, uint32_t n, uint32_t n_batches,
                               uint32_t* batch_mesh, cudaStream_t s);
 size_t instancing_hist_bytes(uint32_t max_objects, uint32_t n_buckets);

@@ -83,7 +83,8 @@ void ashcuda_destroy(ashcuda_ctx* c) {
                      c->velocity_owned, c->taa[0], c->taa[1], c->bloom_t, c->ldr8,
                      c->inst_owned, c->inst_batch_owned, c->inst_mesh_owned, c->lod_meshes_owned, c->batch_mesh,
                      c->lod_sel, c->bucket_of, c->cta_hist, c->bucket_offsets, c->bucket_totals, c->inst_out,
-                     c->inst_draws, c->inst_stats};
+                     c->inst_draws, c->inst_stats, c->fwd_keys, c->fwd_spheres, c->fwd_rects, c->fwd_big,
+                     c->fwd_lights_view, c->fwd_rays, c->fwd_consts};
     for (void* p : owned) if (p) cudaFree(p);
     for (uint32_t k = 1; k <= ASH_MAX_BLOOM_MIPS; ++k) if (c->bloom.d[k]) cudaFree(c->bloom.d[k]);
     c->prof.release_all();
@@ -181,6 +182,7 @@ static int create_impl(ashcuda_ctx* c) {
 }
 
 static void lod_config_default(AshLodConfig* k);
+static void forward_params_default(AshForwardParams* p);
 
 int ashcuda_create(ashcuda_ctx** out, int device, uint32_t width, uint32_t height,
                    const AshCudaConfig* cfg_or_null) {
@@ -206,6 +208,7 @@ int ashcuda_create(ashcuda_ctx** out, int device, uint32_t width, uint32_t heigh
         g_create_error = "ashcuda_create: bad config"; delete c; return ASH_ERR_INVALID;
     }
     lod_config_default(&c->lod_cfg);
+    forward_params_default(&c->fwd_params);
     int rc = create_impl(c);
     if (rc != ASH_OK) { g_create_error = c->err; ashcuda_destroy(c); return rc; }
     *out = c;
@@ -235,6 +238,7 @@ int ashcuda_set_depth(ashcuda_ctx* c, const float* depth, int on_device) {
     c->pyr.mip0 = c->depth;
     c->have_depth = true;
     c->have_pyramid = false;
+    c->have_forward = false;            // the object keys of a forward_depth no longer describe this depth buffer
     return ASH_OK;
 }
 
@@ -490,10 +494,12 @@ int ash_view_run_eager(ashcuda_ctx* c, const AshCudaViewParams* vp) {
     // ---- front end (Hi-Z -> cull, light cull): independent of the post chain of the same view, so it
     //      is forked onto the context's second stream and joined before view_run returns control of
     //      the main stream (inputs uploaded earlier on the main stream are ordered by the fork event)
-    const bool front = (st & (ASH_STAGE_HIZ | ASH_STAGE_CULL | ASH_STAGE_LIGHTS | ASH_STAGE_INSTANCING)) != 0;
+    const bool front = (st & (ASH_STAGE_HIZ | ASH_STAGE_CULL | ASH_STAGE_LIGHTS | ASH_STAGE_INSTANCING | ASH_STAGE_FORWARD_DEPTH)) != 0;
     const bool post = (st & (ASH_STAGE_TAA | ASH_STAGE_BLOOM | ASH_STAGE_TONEMAP)) != 0;
-    // (per-kernel profiling serialises the view so that event pairs time one kernel each)
-    const bool fork = front && post && c->cfg.concurrent_frontend && c->front_stream && c->prof.mask == 0;
+    // (per-kernel profiling serialises the view so that event pairs time one kernel each; a view whose colour
+    //  buffer is shaded from this view's tile lists has nothing to overlap: the post chain waits for it)
+    const bool fork = front && post && c->cfg.concurrent_frontend && c->front_stream && c->prof.mask == 0 &&
+                      !(st & ASH_STAGE_FORWARD_SHADE);
     cudaStream_t main_stream = c->stream;
     if (fork) {
         ASH_CUDA(c, cudaSetDevice(c->device));
@@ -508,6 +514,7 @@ int ash_view_run_eager(ashcuda_ctx* c, const AshCudaViewParams* vp) {
         if (e != cudaSuccess) { c->err = std::string("view_run: ") + cudaGetErrorString(e); rc = ASH_ERR_DEVICE; }
         else if (with_camera) { c->camera_host = vp->camera; c->have_camera = true; }
     }
+    if (!rc && (st & ASH_STAGE_FORWARD_DEPTH)) rc = ashcuda_forward_depth(c, &vp->camera, vp->cull.object_count);
     if (!rc && (st & ASH_STAGE_HIZ)) rc = ashcuda_hiz_build(c);
     if (!rc && (st & ASH_STAGE_CULL)) rc = ashcuda_occlusion_cull(c, &vp->cull);
     if (!rc && (st & ASH_STAGE_INSTANCING)) {        // consumes visibility[] of the cull above
@@ -519,6 +526,7 @@ int ash_view_run_eager(ashcuda_ctx* c, const AshCudaViewParams* vp) {
         rc = ashcuda_instancing_finalize(c, &ip);
     }
     if (!rc && (st & ASH_STAGE_LIGHTS)) rc = ashcuda_light_cull(c, &vp->light);
+    if (!rc && (st & ASH_STAGE_FORWARD_SHADE)) rc = ashcuda_forward_shade(c);
     if (fork) {
         cudaError_t e = cudaEventRecord(c->ev_join, c->front_stream);
         c->stream = main_stream;
@@ -536,6 +544,15 @@ int ash_view_run_eager(ashcuda_ctx* c, const AshCudaViewParams* vp) {
 extern "C" {
 
 // ------------------------------------------------------------------------------ (f-2) instancing / LOD
+static void forward_params_default(AshForwardParams* p) {
+    std::memset(p, 0, sizeof(*p));
+    const float dir[4] = {-0.3f, -1.0f, -0.2f, 0.0f}, white[4] = {1.0f, 1.0f, 1.0f, 1.0f}, amb[4] = {0.03f, 0.03f, 0.03f, 1.0f};
+    const float mr[4] = {0.0f, 0.5f, 1.0f, 1.0f}, bg[4] = {0.02f, 0.02f, 0.03f, 1.0f};
+    std::memcpy(p->light_direction, dir, 16); std::memcpy(p->light_color, white, 16); std::memcpy(p->ambient_color, amb, 16);
+    std::memcpy(p->base_color_factor, white, 16); std::memcpy(p->parameters, mr, 16); std::memcpy(p->background, bg, 16);
+    p->near_plane = 0.1f; p->radius_scale = 1.0f; p->flags = ASH_FWD_TILE_LIGHTS;
+}
+
 static void lod_config_default(AshLodConfig* k) {          // LodConfig::default(), lod_system.rs:47-57
     std::memset(k, 0, sizeof(*k));
     k->mode = ASH_LOD_MODE_SCREEN_SIZE; k->smooth_transitions = 1u; k->transition_width = 0.1f;
@@ -632,6 +649,60 @@ int ashcuda_instancing_finalize(ashcuda_ctx* c, const AshInstancingParams* ip) {
     return ASH_OK;
 }
 
+// ------------------------------------------------------------------------------ (f-1) forward producers
+static int forward_alloc(ashcuda_ctx* c) {
+    if (c->fwd_keys) return ASH_OK;
+    const size_t P = (size_t)c->W * c->H, N = c->cfg.max_objects;
+    ASH_CUDA(c, dmalloc(&c->fwd_keys, P * 8));
+    ASH_CUDA(c, dmalloc(&c->fwd_spheres, N * sizeof(float4)));
+    ASH_CUDA(c, dmalloc(&c->fwd_rects, N * sizeof(int4)));
+    ASH_CUDA(c, dmalloc(&c->fwd_big, (N + 1) * 4));
+    ASH_CUDA(c, dmalloc(&c->fwd_lights_view, (size_t)c->cfg.max_lights * sizeof(float4)));
+    ASH_CUDA(c, dmalloc(&c->fwd_rays, ((size_t)c->W + c->H) * 4));
+    ASH_CUDA(c, dmalloc(&c->fwd_consts, forward_consts_bytes()));
+    return ASH_OK;
+}
+
+int ashcuda_set_forward_params(ashcuda_ctx* c, const AshForwardParams* p) {
+    if (!c) return fail(c, ASH_ERR_INVALID, "set_forward_params: null");
+    if (p) {
+        if (!(p->near_plane > 0.0f) || !(p->radius_scale >= 0.0f)) return fail(c, ASH_ERR_INVALID, "set_forward_params: near_plane <= 0 or radius_scale < 0");
+        c->fwd_params = *p;
+    } else forward_params_default(&c->fwd_params);
+    return ASH_OK;
+}
+
+int ashcuda_forward_depth(ashcuda_ctx* c, const AshCullingCameraData* cam, uint32_t object_count) {
+    if (!c || !cam) return fail(c, ASH_ERR_INVALID, "forward_depth: null");
+    if (object_count > c->n_objs) return fail(c, ASH_ERR_INVALID, "forward_depth: object_count > uploaded objects");
+    if (cam->projection[2][3] != -1.0f || cam->projection[3][3] != 0.0f)
+        return fail(c, ASH_ERR_INVALID, "forward_depth: projection is not a right-handed perspective (w_clip = -z_view)");
+    ASH_CUDA(c, cudaSetDevice(c->device));
+    int rc = forward_alloc(c);
+    if (rc) return rc;
+    ASH_CUDA(c, launch_forward_depth(*cam, c->fwd_params, c->objs, object_count, c->lights, c->n_lights, c->W, c->H, c->fwd_spheres,
+                                     c->fwd_rects, c->fwd_big + 1, c->fwd_big, c->fwd_lights_view, c->fwd_rays, c->fwd_rays + c->W,
+                                     c->fwd_consts, c->fwd_keys, c->depth_owned, c->L()));
+    c->depth = c->depth_owned; c->pyr.mip0 = c->depth;
+    c->have_depth = true; c->have_pyramid = false; c->have_forward = true;
+    return ASH_OK;
+}
+
+int ashcuda_forward_shade(ashcuda_ctx* c) {
+    if (!c) return fail(c, ASH_ERR_INVALID, "forward_shade: null");
+    if (!c->cfg.enable_post) return fail(c, ASH_ERR_NOT_INITIALIZED, "forward_shade: post chain disabled in config (no colour target)");
+    if (!c->have_forward) return fail(c, ASH_ERR_NOT_INITIALIZED, "forward_shade: no forward_depth for this view");
+    const bool inst_color = (c->fwd_params.flags & ASH_FWD_INSTANCE_COLOR) != 0;
+    if (inst_color && !c->have_instancing) return fail(c, ASH_ERR_NOT_INITIALIZED, "forward_shade: ASH_FWD_INSTANCE_COLOR without set_instances");
+    ASH_CUDA(c, cudaSetDevice(c->device));
+    ASH_CUDA(c, launch_forward_shade(c->fwd_params, c->fwd_keys, c->fwd_spheres, c->lights, c->n_lights, c->fwd_lights_view, c->tile_data,
+                                     inst_color ? c->inst : nullptr, inst_color ? c->n_inst : 0u, c->fwd_consts, c->fwd_rays,
+                                     c->fwd_rays + c->W, c->W, c->H, c->color_owned, c->L()));
+    c->color = c->color_owned; c->velocity = nullptr;
+    c->have_color = true; c->taa_ran = false; c->bloom_valid = false;
+    return ASH_OK;
+}
+
 // ------------------------------------------------------------------------------ outputs
 int ashcuda_hiz_level_count(ashcuda_ctx* c) { return c ? c->pyr.levels : ASH_ERR_INVALID; }
 
@@ -671,6 +742,8 @@ int ashcuda_get(ashcuda_ctx* c, int which, void** dev_ptr, size_t* bytes) {
         case ASH_BUF_BUCKET_OFFSETS:  p = c->bucket_offsets; n = ((size_t)c->n_buckets + 1) * 4; break;
         case ASH_BUF_INSTANCE_DRAWS:  p = c->inst_draws; n = (size_t)c->n_buckets * sizeof(AshIndirectDrawCommand); break;
         case ASH_BUF_INSTANCING_STATS: p = c->inst_stats; n = sizeof(AshInstancingStats); break;
+        case ASH_BUF_FORWARD_KEYS:    p = c->fwd_keys; n = P * 8; break;
+        case ASH_BUF_COLOR:           p = const_cast<void*>(c->color); n = P * 8; break;
         default: return fail(c, ASH_ERR_NOT_FOUND, "get: unknown buffer id");
     }
     if (!p) return fail(c, ASH_ERR_NOT_FOUND, "get: buffer not allocated (post chain disabled, or no instances set)");

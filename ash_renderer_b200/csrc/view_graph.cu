@@ -58,11 +58,12 @@ GraphKey make_key(const ashcuda_ctx* c, const AshCudaViewParams* vp) {
     k.taa_cur = (uint32_t)c->taa_cur; k.history_valid = c->history_valid; k.taa_ran = c->taa_ran;
     k.have_color = c->have_color; k.have_depth = c->have_depth; k.have_instancing = c->have_instancing;
     k.concurrent = c->cfg.concurrent_frontend;
+    k.fwd = c->fwd_params;
     return k;
 }
 
 // the per-view arguments of this view, in the order ViewGraph keeps the nodes
-struct Patches { PatchArg store, cull, taa, lod; bool has_cull, has_taa, has_lod; };
+struct Patches { PatchArg store, cull, taa, lod, fwd; bool has_cull, has_taa, has_lod, has_fwd; };
 
 void make_patches(const ashcuda_ctx* c, const AshCudaViewParams* vp, Patches* P) {
     const uint32_t st = vp->stages;
@@ -70,7 +71,7 @@ void make_patches(const ashcuda_ctx* c, const AshCudaViewParams* vp, Patches* P)
     P->has_taa = (st & ASH_STAGE_TAA) != 0;
     P->has_lod = (st & ASH_STAGE_INSTANCING) && vp->cull.object_count > 0;
     if (P->has_cull) cull_patch(vp->cull, &P->cull);
-    if (P->has_taa) taa_pair_patch((st & ASH_STAGE_BLOOM) != 0, c->velocity != nullptr, vp->taa, &P->taa);
+    if (P->has_taa) taa_pair_patch((st & ASH_STAGE_BLOOM) != 0, c->velocity != nullptr && !(st & ASH_STAGE_FORWARD_SHADE), vp->taa, &P->taa);
     if (P->has_lod) {
         AshInstancingParams ip{};
         std::memcpy(ip.view_proj, vp->cull.view_proj, sizeof(ip.view_proj));
@@ -79,6 +80,8 @@ void make_patches(const ashcuda_ctx* c, const AshCudaViewParams* vp, Patches* P)
         ip.object_count = vp->cull.object_count;
         lod_patch(ip, c->lod_cfg, &P->lod);
     }
+    P->has_fwd = (st & ASH_STAGE_FORWARD_DEPTH) != 0;
+    if (P->has_fwd) forward_setup_patch(vp->camera, &P->fwd);
     P->store.func = reinterpret_cast<const void*>(&k_store_view);
     P->store.n_args = 5;
 }
@@ -128,16 +131,23 @@ void drop(ViewGraph& g) {
 struct StateSnap {
     int taa_cur; bool history_valid, taa_ran, bloom_valid, have_pyramid, have_camera; uint64_t launches; AshCullingCameraData camera_host;
     float taa_chk[4]; bool taa_exact;
+    bool have_depth, have_color, have_forward; const float* depth; const void* color; const void* velocity;
 };
 StateSnap snap(const ashcuda_ctx* c) {
-    StateSnap s{c->taa_cur, c->history_valid, c->taa_ran, c->bloom_valid, c->have_pyramid, c->have_camera, c->launches, c->camera_host, {}, c->taa_exact};
+    StateSnap s{};
+    s.taa_cur = c->taa_cur; s.history_valid = c->history_valid; s.taa_ran = c->taa_ran; s.bloom_valid = c->bloom_valid;
+    s.have_pyramid = c->have_pyramid; s.have_camera = c->have_camera; s.launches = c->launches; s.camera_host = c->camera_host; s.taa_exact = c->taa_exact;
     std::memcpy(s.taa_chk, c->taa_chk, sizeof(s.taa_chk));
+    s.have_depth = c->have_depth; s.have_color = c->have_color; s.have_forward = c->have_forward;
+    s.depth = c->depth; s.color = c->color; s.velocity = c->velocity;
     return s;
 }
 void restore(ashcuda_ctx* c, const StateSnap& s) {
     c->taa_cur = s.taa_cur; c->history_valid = s.history_valid; c->taa_ran = s.taa_ran; c->bloom_valid = s.bloom_valid;
     c->have_pyramid = s.have_pyramid; c->have_camera = s.have_camera; c->launches = s.launches; c->camera_host = s.camera_host;
     std::memcpy(c->taa_chk, s.taa_chk, sizeof(s.taa_chk)); c->taa_exact = s.taa_exact;
+    c->have_depth = s.have_depth; c->have_color = s.have_color; c->have_forward = s.have_forward;
+    c->depth = s.depth; c->pyr.mip0 = c->depth; c->color = s.color; c->velocity = s.velocity;
 }
 
 }  // namespace
@@ -158,9 +168,10 @@ int ash_view_run_graph(ashcuda_ctx* c, const AshCudaViewParams* vp, bool* handle
     const uint32_t st = vp->stages;
     if (!c->cfg.graph_replay || c->graphs_broken || c->prof.mask != 0) return ASH_OK;
     // the TAA node must be the pair kernel (post_fast.cu dispatch: exact taps and (velocity || jitter delta inside the halo))
+    const bool shaded = (st & ASH_STAGE_FORWARD_SHADE) != 0;                     // colour made inside the view, no velocity
     if (st & ASH_STAGE_TAA) {
-        if (!c->have_color || !c->cfg.enable_post) return ASH_OK;                // eager path reports the error
-        if (!(c->velocity || taa_in_halo(vp->taa))) return ASH_OK;
+        if (!(c->have_color || shaded) || !c->cfg.enable_post) return ASH_OK;    // eager path reports the error
+        if (!((c->velocity && !shaded) || taa_in_halo(vp->taa))) return ASH_OK;
     }
     ViewGraph& g = c->vgraph[c->taa_cur & 1];
     const GraphKey key = make_key(c, vp);
@@ -184,6 +195,7 @@ int ash_view_run_graph(ashcuda_ctx* c, const AshCudaViewParams* vp, bool* handle
             if (ok && P.has_cull) ok = find_node(g.graph, P.cull.func, &g.n_cull) == cudaSuccess;
             if (ok && P.has_taa) ok = find_node(g.graph, P.taa.func, &g.n_taa) == cudaSuccess;     // absent: TAA taps not exact
             if (ok && P.has_lod) ok = find_node(g.graph, P.lod.func, &g.n_lod) == cudaSuccess;
+            if (ok && P.has_fwd) ok = find_node(g.graph, P.fwd.func, &g.n_fwd) == cudaSuccess;
         } else if (graph) cudaGraphDestroy(graph);
         if (!ok) {
             // an invalid view (rc != 0) is the caller's error, reported by the eager path below; a failed capture of a
@@ -199,6 +211,8 @@ int ash_view_run_graph(ashcuda_ctx* c, const AshCudaViewParams* vp, bool* handle
         g.taa_flip = c->taa_cur != s0.taa_cur;
         g.history_valid = c->history_valid; g.taa_ran = c->taa_ran; g.bloom_valid = c->bloom_valid;
         g.have_pyramid = c->have_pyramid; g.have_camera = c->have_camera;
+        g.have_depth = c->have_depth; g.have_color = c->have_color; g.have_forward = c->have_forward;
+        g.depth = c->depth; g.color = c->color; g.velocity = c->velocity;
         c->graph_captures += 1;
         // the capture left the context in its post-view state and the argument values of this very view in the
         // nodes: launch as captured
@@ -219,10 +233,13 @@ int ash_view_run_graph(ashcuda_ctx* c, const AshCudaViewParams* vp, bool* handle
     if (P.has_cull) ASH_CUDA(c, patch_node(g, g.n_cull, P.cull.n_args, P.cull.arg_index, P.cull.value));
     if (P.has_taa) ASH_CUDA(c, patch_node(g, g.n_taa, P.taa.n_args, P.taa.arg_index, P.taa.value));
     if (P.has_lod) ASH_CUDA(c, patch_node(g, g.n_lod, P.lod.n_args, P.lod.arg_index, P.lod.value));
+    if (P.has_fwd) ASH_CUDA(c, patch_node(g, g.n_fwd, P.fwd.n_args, P.fwd.arg_index, P.fwd.value));
     ASH_CUDA(c, cudaGraphLaunch(g.exec, c->stream));
     if (g.taa_flip) c->taa_cur ^= 1;
     c->history_valid = g.history_valid; c->taa_ran = g.taa_ran; c->bloom_valid = g.bloom_valid;
     c->have_pyramid = g.have_pyramid; c->have_camera = g.have_camera;
+    c->have_depth = g.have_depth; c->have_color = g.have_color; c->have_forward = g.have_forward;
+    c->depth = g.depth; c->pyr.mip0 = c->depth; c->color = g.color; c->velocity = g.velocity;
     if (st & ASH_STAGE_LIGHTS) c->camera_host = vp->camera;
     c->launches += g.launches;
     c->graph_replays += 1;

@@ -271,3 +271,20 @@ def instancing_params(cam, n):
     ip["screen_size"][0] = [cam.W, cam.H]
     ip["object_count"] = n
     return ip
+
+
+def forward_params(light_direction=(-0.3, -1.0, -0.2), light_color=(1.0, 0.95, 0.9), ambient=(0.03, 0.03, 0.04),
+                   base_color=(0.8, 0.8, 0.8), emissive=(0.0, 0.0, 0.0), metallic=0.1, roughness=0.5,
+                   background=(0.02, 0.02, 0.03), near=0.5, radius_scale=1.0, flags=T.FWD_TILE_LIGHTS):
+    """AshForwardParams: the frag.frag MVP / Material uniform fields the compute forward pass (row f-1) uses."""
+    p = np.zeros(1, T.FORWARD_PARAMS)
+    p["light_direction"][0, :3] = light_direction
+    p["light_color"][0] = [*light_color, 1.0]
+    p["ambient_color"][0] = [*ambient, 1.0]
+    p["base_color_factor"][0] = [*base_color, 1.0]
+    p["emissive_factor"][0] = [*emissive, 1.0]
+    p["parameters"][0] = [metallic, roughness, 1.0, 1.0]
+    p["background"][0] = [*background, 1.0]
+    p["near_plane"], p["radius_scale"], p["flags"] = near, radius_scale, flags
+    return p
+

@@ -60,6 +60,14 @@ INSTANCING_PARAMS = np.dtype([("view_proj", "<f4", (4, 4)), ("camera_pos", "<f4"
 assert INSTANCE_DATA.itemsize == 96 and LOD_LEVEL.itemsize == 24 and LOD_MESH.itemsize == 208
 assert LOD_CONFIG.itemsize == 32 and LOD_SELECTION.itemsize == 16 and INSTANCING_STATS.itemsize == 72
 assert INSTANCING_PARAMS.itemsize == 96
+# (f-1) compute forward pass: the frag.frag uniform fields it uses (AshForwardParams)
+FORWARD_PARAMS = np.dtype([("light_direction", "<f4", 4), ("light_color", "<f4", 4), ("ambient_color", "<f4", 4),
+                           ("base_color_factor", "<f4", 4), ("emissive_factor", "<f4", 4), ("parameters", "<f4", 4),
+                           ("background", "<f4", 4), ("near_plane", "<f4"), ("radius_scale", "<f4"), ("flags", "<u4"),
+                           ("_padding", "<u4")])
+assert FORWARD_PARAMS.itemsize == 128
+FWD_TILE_LIGHTS, FWD_REINHARD, FWD_INSTANCE_COLOR = 1, 2, 4
+FWD_NO_OBJECT = 0xFFFFFFFF
 
 assert CULL_OBJECT.itemsize == 112 and DRAW_COMMAND.itemsize == 20 and CULLING_PC.itemsize == 96
 assert GPU_LIGHT.itemsize == 64 and LIGHT_PC.itemsize == 16 and CAMERA_DATA.itemsize == 208
@@ -75,11 +83,13 @@ STAGE_HIZ, STAGE_CULL, STAGE_LIGHTS, STAGE_TAA, STAGE_BLOOM, STAGE_TONEMAP = 1, 
 STAGE_ALL = 0x3F
 STAGE_KEEP_BLOOM = 0x40
 STAGE_INSTANCING = 0x80
+STAGE_FORWARD_DEPTH, STAGE_FORWARD_SHADE = 0x100, 0x200
 
 BUF_VISIBILITY, BUF_DRAWS_OUT, BUF_VISIBLE_COUNT, BUF_TILE_DATA = 1, 2, 3, 4
 BUF_TAA_OUT, BUF_LDR8, BUF_STATS, BUF_TILE_MINMAX, BUF_VISIBILITY_BITS = 5, 6, 7, 8, 9
 BUF_BLOOM_THRESHOLD = 10
 BUF_LOD_SELECTION, BUF_INSTANCES_OUT, BUF_BUCKET_OFFSETS, BUF_INSTANCE_DRAWS, BUF_INSTANCING_STATS = 11, 12, 13, 14, 15
+BUF_FORWARD_KEYS, BUF_COLOR = 16, 17
 
 
 def BUF_HIZ_MIP(i):
@@ -92,5 +102,5 @@ def BUF_BLOOM_MIP(i):
 # kernel classes (ashcuda_profile_kernels / ashcuda_kernel_time_ms)
 (KERNEL_DEPTH_PYRAMID, KERNEL_OCCLUSION_CULL, KERNEL_CULL_COMPACT, KERNEL_LIGHT_PREPASS, KERNEL_LIGHT_TILES,
  KERNEL_TAA, KERNEL_BLOOM_THRESHOLD, KERNEL_BLOOM_DOWNSAMPLE, KERNEL_BLOOM_UPSAMPLE, KERNEL_TONEMAP,
- KERNEL_TAA_THRESHOLD, KERNEL_UPSAMPLE_TONEMAP, KERNEL_INSTANCING) = range(13)
-KERNEL_COUNT = 13
+ KERNEL_TAA_THRESHOLD, KERNEL_UPSAMPLE_TONEMAP, KERNEL_INSTANCING, KERNEL_FORWARD_DEPTH, KERNEL_FORWARD_SHADE) = range(15)
+KERNEL_COUNT = 15

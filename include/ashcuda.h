@@ -133,6 +133,28 @@ typedef struct AshInstanceData {
     float custom[4];
 } AshInstanceData;
 
+/* ---- (f-1) producers: a compute forward pass that makes the depth and HDR colour buffers on the device --
+ * The uniform fields of shaders/frag.frag the compute forward pass uses (MVP :12-23, Material :25-37);
+ * view and projection come from AshCullingCameraData.  Textures (bindless indices -1), the shadow map
+ * (shadow = 0) and normal maps are not part of it. */
+typedef struct AshForwardParams {
+    float light_direction[4];   /* MVP.light_direction: world-space direction the light travels            */
+    float light_color[4];       /* MVP.light_color rgb                                                     */
+    float ambient_color[4];     /* MVP.ambient_color rgb                                                   */
+    float base_color_factor[4]; /* Material.base_color_factor                                              */
+    float emissive_factor[4];   /* Material.emissive_factor                                                */
+    float parameters[4];        /* Material.parameters: x metallic, y roughness (z, w unused: no textures) */
+    float background[4];        /* HDR clear colour of pixels no occluder covers                           */
+    float near_plane;           /* hits nearer than this along the view axis are clipped                   */
+    float radius_scale;         /* occluder sphere radius = scale * min world half-extent of the AABB      */
+    uint32_t flags;             /* ASH_FWD_*                                                               */
+    uint32_t _padding;
+} AshForwardParams;
+#define ASH_FWD_TILE_LIGHTS    1u /* add the lights of the pixel's tile list (tileData of this view's light cull) */
+#define ASH_FWD_REINHARD       2u /* frag.frag:226: color / (color + 1) on shaded pixels                            */
+#define ASH_FWD_INSTANCE_COLOR 4u /* base colour *= AshInstanceData.color of the same index (needs set_instances)   */
+#define ASH_FWD_NO_OBJECT      0xFFFFFFFFu
+
 #define ASH_MAX_LOD_LEVELS          8u      /* lod_system.rs:15  MAX_LOD_LEVELS          */
 #define ASH_MAX_INSTANCES_PER_BATCH 65536u  /* instancing.rs:16  MAX_INSTANCES_PER_BATCH */
 #define ASH_LOD_NOT_VISIBLE         0xFFFFFFFFu
@@ -254,6 +276,8 @@ typedef struct AshCudaViewParams {
 #define ASH_STAGE_TONEMAP    0x20u
 #define ASH_STAGE_ALL        0x3Fu
 #define ASH_STAGE_INSTANCING 0x80u /* after the cull: LOD selection + instance batching (not part of ASH_STAGE_ALL) */
+#define ASH_STAGE_FORWARD_DEPTH 0x100u /* before Hi-Z: depth buffer from the cull objects' occluder spheres (f-1)       */
+#define ASH_STAGE_FORWARD_SHADE 0x200u /* after the light cull: HDR colour from the tile light lists (f-1, f-2)         */
 #define ASH_STAGE_KEEP_BLOOM 0x40u /* view_run: also store the bloom buffer U_0 (the fused last upsample +
                                       tonemap otherwise never writes it; ASH_BUF_BLOOM_MIP(0) then holds D_0) */
 
@@ -275,6 +299,8 @@ typedef struct AshCudaViewParams {
 #define ASH_BUF_BUCKET_OFFSETS 13 /* u32[max_batches*8 + 1]: bucket b = batch*8 + level starts at offsets[b]  */
 #define ASH_BUF_INSTANCE_DRAWS 14 /* AshIndirectDrawCommand[max_batches*8]: one per bucket      */
 #define ASH_BUF_INSTANCING_STATS 15 /* AshInstancingStats                                        */
+#define ASH_BUF_FORWARD_KEYS   16 /* u64 W x H: (depth bits << 32) | object index, ASH_FWD_NO_OBJECT where none */
+#define ASH_BUF_COLOR          17 /* RGBA16F W x H: the current HDR colour input (set_color / forward_shade)    */
 
 /* Kernel classes for ashcuda_profile_kernels / ashcuda_kernel_time_ms (device-time accounting;
  * the Vulkan-timestamp TimingScopes of diagnostics/gpu_profiler.rs:25-44 play this role upstream). */
@@ -291,7 +317,9 @@ typedef struct AshCudaViewParams {
 #define ASH_KERNEL_TAA_THRESHOLD   10  /* fused: TAA resolve + bloom threshold                   */
 #define ASH_KERNEL_UPSAMPLE_TONEMAP 11 /* fused: last bloom upsample + tonemap + 8-bit pack      */
 #define ASH_KERNEL_INSTANCING       12 /* LOD select + bucket scan + instance scatter (3 launches)  */
-#define ASH_KERNEL_COUNT           13
+#define ASH_KERNEL_FORWARD_DEPTH    13 /* setup + clear + sphere splat (small, big) + depth resolve     */
+#define ASH_KERNEL_FORWARD_SHADE    14 /* tiled-forward shading from the tile light lists              */
+#define ASH_KERNEL_COUNT           15
 
 typedef struct ashcuda_ctx ashcuda_ctx;
 
@@ -341,6 +369,18 @@ int ashcuda_set_instances (ashcuda_ctx*, const AshInstanceData* instances, const
 int ashcuda_set_lod_meshes(ashcuda_ctx*, const AshLodMesh* meshes, uint32_t n, int on_device);
 int ashcuda_set_lod_config(ashcuda_ctx*, const AshLodConfig*);      /* NULL: LodConfig::default(), :47-57 */
 int ashcuda_instancing_finalize(ashcuda_ctx*, const AshInstancingParams*);
+
+/* ---- (f-1) depth / HDR producers (csrc/forward.cu) --------------------------------------------------
+ * forward_depth ray-casts one occluder sphere per enabled cull object (centre = model * bounds.center,
+ * radius = radius_scale * min_k(extents_k * |model column k|), inside the object's world AABB) through
+ * the pixel centres, keeps per pixel the nearest hit as (ndc depth, object index) and writes the depth
+ * buffer the rest of the path consumes (as set_depth would).  forward_shade evaluates frag.frag's
+ * Cook-Torrance BRDF (:89-114, :167-213) at the hit for the MVP light and, with ASH_FWD_TILE_LIGHTS,
+ * for every light of the pixel's 16x16 tile list (the consumer light_culling.comp was written for and
+ * frag.frag never got), and writes the HDR colour buffer (as set_color would). */
+int ashcuda_set_forward_params(ashcuda_ctx*, const AshForwardParams*);   /* NULL: defaults */
+int ashcuda_forward_depth(ashcuda_ctx*, const AshCullingCameraData* cam, uint32_t object_count);
+int ashcuda_forward_shade(ashcuda_ctx*);   /* after forward_depth (and light_cull with ASH_FWD_TILE_LIGHTS) of the same view */
 
 /* --- whole-view host I/O for callers whose frame data lives in host memory (the e2e path):
  *     upload = set_depth + set_color from host pointers (pinned memory makes the copies async);

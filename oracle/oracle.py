@@ -34,7 +34,7 @@ POST_PC_DTYPE = np.dtype([("exposure", "<f4"), ("gamma", "<f4"), ("bloom_intensi
 
 def build(force=False):
     """Compile libashoracle.so with the committed Makefile (g++ -O2 -fopenmp -ffp-contract=off)."""
-    srcs = [os.path.join(_HERE, f) for f in ("ash_oracle.cpp", "ash_oracle_instancing.cpp")]
+    srcs = [os.path.join(_HERE, f) for f in ("ash_oracle.cpp", "ash_oracle_instancing.cpp", "ash_oracle_forward.cpp")]
     if (not force and os.path.exists(_LIB_PATH)
             and os.path.getmtime(_LIB_PATH) >= max(os.path.getmtime(f) for f in srcs)):
         return _LIB_PATH
@@ -249,3 +249,41 @@ def instancing(instances, batch_id, mesh_id, meshes, params, cfg, n_batches, vis
     f(_p(inst), _p(bid), _p(mid), _p(ms), len(ms.reshape(-1)), None if vis is None else _p(vis), _p(ip), _p(k), int(n_batches),
       _p(sel), _p(out), _p(offsets), _p(draws), _p(stats))
     return sel, out[:int(offsets[-1])], offsets, draws, stats[0]
+
+
+# ---- row f-1: compute forward pass (oracle/ash_oracle_forward.cpp)
+FORWARD_PARAMS_DTYPE = np.dtype([("light_direction", "<f4", 4), ("light_color", "<f4", 4), ("ambient_color", "<f4", 4),
+                                 ("base_color_factor", "<f4", 4), ("emissive_factor", "<f4", 4), ("parameters", "<f4", 4),
+                                 ("background", "<f4", 4), ("near_plane", "<f4"), ("radius_scale", "<f4"), ("flags", "<u4"),
+                                 ("_padding", "<u4")])
+
+
+def forward_depth(objs, cam, fp, W, H, brute=False):
+    """Nearest occluder-sphere hit per pixel: (keys u64 HxW, depth f32 HxW).  brute=True tests every pixel
+    against every sphere (no silhouette rectangle): the check that the rectangle is conservative."""
+    o, c, p = _c(objs, OBJECT_DTYPE), _c(cam, CAMERA_DTYPE), _c(fp, FORWARD_PARAMS_DTYPE)
+    keys = np.zeros((H, W), np.uint64)
+    depth = np.zeros((H, W), np.float32)
+    f = lib().ash_oracle_forward_depth
+    f.restype = None
+    f.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_int, C.c_void_p, C.c_void_p]
+    f(_p(o), len(o.reshape(-1)), _p(c), _p(p), W, H, int(bool(brute)), _p(keys), _p(depth))
+    return keys, depth
+
+
+def forward_shade(keys, objs, lights, tile_data, cam, fp, instances=None):
+    """frag.frag's BRDF at every hit for the MVP light + the tile light lists: RGBA16F HxWx4."""
+    H, W = keys.shape
+    k, o, l = _c(keys, np.uint64), _c(objs, OBJECT_DTYPE), _c(lights, LIGHT_DTYPE)
+    td = _c(tile_data, np.uint32)
+    c, p = _c(cam, CAMERA_DTYPE), _c(fp, FORWARD_PARAMS_DTYPE)
+    inst = None if instances is None else _c(instances, INSTANCE_DTYPE)
+    hdr = np.zeros((H, W, 4), np.float16)
+    f = lib().ash_oracle_forward_shade
+    f.restype = None
+    f.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_uint32,
+                  C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_void_p]
+    f(_p(k), _p(o), len(o.reshape(-1)), _p(l), len(l.reshape(-1)), _p(td), None if inst is None else _p(inst),
+      0 if inst is None else len(inst.reshape(-1)), _p(c), _p(p), W, H, _p(hdr))
+    return hdr
+

@@ -535,6 +535,111 @@ def test_view_run_post_chain_with_velocity_buffer(backend, oracle):
             hist = ref
 
 
+# ------------------------------------------------------------------ row f-1: depth / HDR producers
+def _forward_scene(W, H, eye, target, grid, seed, n_lights=200, **fpkw):
+    cam = synth.Camera(eye, target, W, H, near=0.5)
+    objs, draws = synth.make_objects(grid, spacing=2.0, seed=seed, jitter=0.3, disabled_frac=0.1)
+    lights = synth.make_lights(n_lights, extent=10.0, seed=seed + 1, center=(0.0, 2.0, 4.0))
+    return cam, objs, draws, lights, synth.forward_params(near=0.5, **fpkw)
+
+
+@pytest.mark.parametrize("W,H,eye,target,grid", [
+    (640, 360, (0.0, 2.0, 22.0), (0, 0, 0), (10, 8, 8)),
+    (333, 187, (3.0, 1.0, 9.0), (0, 0, 0), (8, 6, 6)),            # odd extent, close: big rectangles
+    (320, 180, (0.3, 0.2, 0.1), (5, 1, 4), (8, 6, 6)),            # eye inside the grid: near-plane crossings, full-screen rectangles
+    (1920, 1080, (-14.0, 9.0, 30.0), (0, 0, 0), (24, 16, 16)),
+])
+def test_forward_depth_bit_exact(backend, oracle, W, H, eye, target, grid):
+    cam, objs, draws, lights, fp = _forward_scene(W, H, eye, target, grid, seed=41)
+    keys, depth = oracle.forward_depth(objs, cam.camera_data(), fp, W, H)
+    with _ctx(backend, W, H) as c:
+        c.set_objects(objs, draws)
+        c.upload_lights(lights)
+        c.set_forward_params(fp)
+        c.forward_depth(cam.camera_data(), len(objs))
+        assert np.array_equal(c.forward_keys(), keys), "(depth bits, object index) keys"
+        assert np.array_equal(c.depth().view(np.uint32), depth.view(np.uint32)), "depth buffer"
+        # and the depth buffer is live for the rest of the path
+        levels = min(9, len(oracle.mip_extents(W, H)))
+        vis, dout, cnt = oracle.occlusion_cull(objs, draws, cam.cull_pc(len(objs), levels), depth)
+        c.hiz_build()
+        c.occlusion_cull(cam.cull_pc(len(objs), levels))
+        assert np.array_equal(c.visibility(), vis) and c.visible_count() == cnt
+
+
+@pytest.mark.parametrize("flags", [T.FWD_TILE_LIGHTS, T.FWD_TILE_LIGHTS | T.FWD_REINHARD | T.FWD_INSTANCE_COLOR, 0])
+def test_forward_shade_bit_exact(backend, oracle, flags):
+    W, H = 640, 360
+    cam, objs, draws, lights, fp = _forward_scene(W, H, (0.0, 2.0, 22.0), (0, 0, 0), (10, 8, 8), seed=43, n_lights=400,
+                                                  metallic=0.3, roughness=0.35, flags=flags)
+    meshes = synth.make_lod_meshes(6, seed=3)
+    inst, batch, mesh = synth.make_instances(objs, 4, 6, seed=4)
+    rng = np.random.default_rng(5)
+    inst["color"][:, :3] = rng.uniform(0.1, 1.0, (len(inst), 3)).astype(np.float32)
+    keys, depth = oracle.forward_depth(objs, cam.camera_data(), fp, W, H)
+    td, _, _ = oracle.light_cull(lights, cam.light_pc(len(lights)), cam.camera_data(), depth)
+    ref = oracle.forward_shade(keys, objs, lights, td, cam.camera_data(), fp, instances=inst)
+    with _ctx(backend, W, H, max_batches=4) as c:
+        c.set_objects(objs, draws)
+        c.upload_lights(lights)
+        c.set_instances(inst, batch, mesh)
+        c.set_forward_params(fp)
+        with pytest.raises(backend.AshError):
+            c.forward_shade()                                      # no forward_depth yet
+        c.forward_depth(cam.camera_data(), len(objs))
+        c.upload_camera(cam.camera_data())
+        c.light_cull(cam.light_pc(len(lights)))
+        _compare_tile_lists(c.tile_data(), td)
+        c.forward_shade()
+        _assert_half_images_equal(c.color(), ref, "forward HDR colour")
+        lit = c.color()[..., :3].astype(np.float32)
+        assert np.isfinite(lit).all() and lit.max() > 0.2
+
+
+@pytest.mark.parametrize("graph", [0, 1])
+def test_view_run_from_scene_to_ldr_with_forward_stages(backend, oracle, graph):
+    """The whole widened view: objects + lights + camera in, depth and HDR colour made on the device, then Hi-Z,
+    cull, light cull, TAA, bloom, tonemap — nothing but the scene crosses the host boundary; eager and graph replay."""
+    from ash_renderer_b200.host import TemporalAA
+    W, H = 640, 360
+    objs, draws = synth.make_objects((10, 8, 8), spacing=2.0, seed=51, jitter=0.3)
+    lights = synth.make_lights(300, extent=10.0, seed=52, center=(0.0, 2.0, 4.0))
+    fp = synth.forward_params(near=0.5, flags=T.FWD_TILE_LIGHTS)
+    taa = TemporalAA()
+    hist = None
+    stages = T.STAGE_ALL | T.STAGE_KEEP_BLOOM | T.STAGE_FORWARD_DEPTH | T.STAGE_FORWARD_SHADE
+    with _ctx(backend, W, H, graph_replay=graph) as c:
+        c.set_objects(objs, draws)
+        c.upload_lights(lights)
+        c.set_forward_params(fp)
+        for t in range(5):
+            taa.begin_frame()
+            pc = taa.push_constants(W, H)
+            cam = synth.Camera((0.4 * t - 1.0, 2.0, 22.0 - 0.7 * t), (0, 0, 0), W, H, near=0.5)
+            c.view_run(_view_params(cam, len(objs), len(lights), 9, W, H, pc, stages=stages, view_id=t))
+            if t in (0, 4):                                        # first view (captured) and a replayed one
+                keys, depth = oracle.forward_depth(objs, cam.camera_data(), fp, W, H)
+                vis, dout, cnt = oracle.occlusion_cull(objs, draws, cam.cull_pc(len(objs), 9), depth)
+                td, _, _ = oracle.light_cull(lights, cam.light_pc(len(lights)), cam.camera_data(), depth)
+                hdr = oracle.forward_shade(keys, objs, lights, td, cam.camera_data(), fp)
+                assert np.array_equal(c.forward_keys(), keys)
+                assert np.array_equal(c.visibility(), vis) and c.visible_count() == cnt
+                _compare_tile_lists(c.tile_data(), td)
+                _assert_half_images_equal(c.color(), hdr, f"HDR view {t}")
+                assert int(c.stats()["view_id"]) == t
+            else:
+                hdr = c.color()
+            ref = oracle.taa_resolve(hdr, hdr if hist is None else hist, None, pc)
+            _assert_half_images_equal(c.taa_out(), ref, f"taa view {t}")
+            hist = ref
+        U, _ = oracle.bloom_chain(hist, 0.8, 5)
+        _assert_half_images_equal(c.bloom_mip(0), U[0], "bloom")
+        d = np.abs(c.ldr8().astype(np.int16) - oracle.tonemap(hist, U[0], _post_pc()).astype(np.int16))
+        assert d.max() <= 1
+        cap, rep = c.graph_stats()
+        assert (cap > 0 and rep > 0) if graph else (cap == 0 and rep == 0)
+
+
 @pytest.mark.parametrize("velocity", [False, True])
 def test_view_run_graph_replay_equals_eager(backend, velocity):
     """view_run through CUDA-graph replay (per-view kernel arguments patched) against the eager launches:
