@@ -677,6 +677,7 @@ int ashcuda_forward_depth(ashcuda_ctx* c, const AshCullingCameraData* cam, uint3
     if (object_count > c->n_objs) return fail(c, ASH_ERR_INVALID, "forward_depth: object_count > uploaded objects");
     if (cam->projection[2][3] != -1.0f || cam->projection[3][3] != 0.0f)
         return fail(c, ASH_ERR_INVALID, "forward_depth: projection is not a right-handed perspective (w_clip = -z_view)");
+    if (c->W > 65535u || c->H > 65535u) return fail(c, ASH_ERR_INVALID, "forward_depth: extent above 65535 (rectangles are packed in 16 bits)");
     ASH_CUDA(c, cudaSetDevice(c->device));
     int rc = forward_alloc(c);
     if (rc) return rc;

@@ -10,11 +10,14 @@
 //                     silhouette (tangent rays), classed small / big; light i -> view space;
 //                     column i / row i -> ray table; thread 0 -> per-view constants
 //   k_forward_clear   keys = (bits(1.0) << 32) | NO_OBJECT
-//   k_splat_small     one warp per sphere, lanes 8x4 over the rectangle; per pixel a ray / sphere
-//                     test and a 64-bit atomicMin of (depth bits << 32 | object index): nearest hit,
-//                     lowest index on ties, whatever the order — bit-exact against the serial oracle
-//   k_splat_big       rectangles above kBigArea pixels: every CTA walks the big list and takes the
-//                     32x32-pixel chunks congruent to its index (a near sphere can cover the screen)
+//   k_splat_big       rectangles above kBigArea pixels, launched FIRST (big = near): every CTA walks the
+//                     big list (staged through shared memory) and takes the 32x32-pixel chunks congruent
+//                     to its index (a near sphere can cover a third of the screen)
+//   k_splat_small     one warp per sphere, lanes 8x4 over the rectangle, two launches (mid, then small
+//                     areas); per pixel: skip if the key already there is nearer than this sphere can
+//                     be, else a ray / sphere test and a 64-bit atomicMin of (depth bits << 32 | object
+//                     index): nearest hit, lowest index on ties, whatever the order — bit-exact against
+//                     the serial oracle
 //   k_forward_depth   depth buffer = high halves of the keys (what set_depth would have uploaded)
 //   k_forward_shade   one CTA per 16x16 light tile: tile list -> shared memory, then per pixel
 //                     frag.frag's Cook-Torrance BRDF (:89-114, :167-213) for the MVP light and every
@@ -31,7 +34,8 @@
 
 namespace ash {
 
-constexpr int kBigArea = 1024;          // pixels: above this a rectangle goes to the CTA-cooperative kernel
+constexpr int kBigArea = 16384;         // pixels: above this a rectangle goes to the CTA-cooperative kernel
+constexpr int kMidArea = 2048;          // warp-per-sphere launches: (kMidArea, kBigArea] first, then the rest (near before far)
 constexpr int kChunk = 32;              // k_splat_big works in 32x32-pixel chunks
 
 struct FwdConsts {                      // written by k_forward_setup thread 0, read by the other kernels
@@ -43,11 +47,23 @@ __device__ __forceinline__ float ray_coord(int i, int S, float P) {
     return fdiv(fsub(fmul(fdiv(fadd((float)i, 0.5f), (float)S), 2.0f), 1.0f), P);
 }
 
-__device__ __forceinline__ void axis_bound(float c, float cz, float r, float den, float P, int S, int* i0, int* i1) {
-    const float D = fsub(fadd(fmul(c, c), fmul(cz, cz)), fmul(r, r));
-    const float sq = fsqrt(gmax(D, 0.0f));
-    const float m = fmul(c, cz), k = fmul(r, sq);
-    const float n0 = fmul(P, fdiv(fsub(m, k), den)), n1 = fmul(P, fdiv(fadd(m, k), den));
+// per-axis pixel bound of the part of the sphere in front of the near plane, padded by a pixel.
+// tangent: the eye plane does not cut the sphere (cz > r): slopes x/z of the two tangent rays.
+// otherwise the box bound of { x in [c-r, c+r], z in [near, cz+r] }.
+__device__ __forceinline__ void axis_bound(float c, float cz, float r, bool tangent, float near_plane, float P, int S, int* i0, int* i1) {
+    float s0, s1;
+    if (tangent) {
+        const float den = fmul(fsub(cz, r), fadd(cz, r));
+        const float D = fsub(fadd(fmul(c, c), fmul(cz, cz)), fmul(r, r));
+        const float sq = fsqrt(gmax(D, 0.0f));
+        const float m = fmul(c, cz), k = fmul(r, sq);
+        s0 = fdiv(fsub(m, k), den); s1 = fdiv(fadd(m, k), den);
+    } else {
+        const float zmax = fadd(cz, r), lo_c = fsub(c, r), hi_c = fadd(c, r);
+        s0 = lo_c < 0.0f ? fdiv(lo_c, near_plane) : fdiv(lo_c, zmax);
+        s1 = hi_c > 0.0f ? fdiv(hi_c, near_plane) : fdiv(hi_c, zmax);
+    }
+    const float n0 = fmul(P, s0), n1 = fmul(P, s1);
     const float p0 = fmul(fadd(fmul(n0, 0.5f), 0.5f), (float)S), p1 = fmul(fadd(fmul(n1, 0.5f), 0.5f), (float)S);
     const float lo = gmin(p0, p1), hi = gmax(p0, p1);
     if (!(lo <= hi)) { *i0 = 0; *i1 = S; return; }
@@ -88,19 +104,23 @@ k_forward_setup(AshCullingCameraData cam, AshForwardParams fp, const AshCullObje
             const V4 cv = mul4(view, wc.x, wc.y, wc.z, 1.0f);
             s = make_float4(cv.x, cv.y, cv.z, r);
             const float cz = -cv.z;
-            if (!(r > 0.0f) || fadd(cz, r) < fp.near_plane) {
-                // empty
-            } else if (!(fsub(cz, r) > fp.near_plane)) {
-                q = make_int4(0, 0, (int)W, (int)H);
-            } else {
-                const float den = fmul(fsub(cz, r), fadd(cz, r));
-                axis_bound(cv.x, cz, r, den, cam.projection[0][0], (int)W, &q.x, &q.z);
-                axis_bound(cv.y, cz, r, den, cam.projection[1][1], (int)H, &q.y, &q.w);
+            if (r > 0.0f && !(fadd(cz, r) < fp.near_plane)) {
+                const bool tangent = cz > r;
+                int x0, x1, y0, y1;
+                axis_bound(cv.x, cz, r, tangent, fp.near_plane, cam.projection[0][0], (int)W, &x0, &x1);
+                axis_bound(cv.y, cz, r, tangent, fp.near_plane, cam.projection[1][1], (int)H, &y0, &y1);
+                // a lower bound of every depth this sphere can produce (hits are at view distance >= cz - r; 0.2 % and
+                // 1e-6 cover the rounding of the quadratic and of the depth formula): pixels already nearer skip the test
+                float lb = 0.0f;
+                const float t_lb = fmul(fsub(cz, r), 0.998f);
+                if (t_lb > fp.near_plane && cam.projection[3][2] < 0.0f)
+                    lb = gmax(fsub(fdiv(fsub(cam.projection[3][2], fmul(cam.projection[2][2], t_lb)), t_lb), 1e-6f), 0.0f);
+                q = make_int4((int)((uint32_t)x0 | ((uint32_t)x1 << 16)), (int)((uint32_t)y0 | ((uint32_t)y1 << 16)), (int)__float_as_uint(lb), max(x1 - x0, 0) * max(y1 - y0, 0));
             }
         }
         spheres[i] = s;
-        rects[i] = q;
-        if ((q.z - q.x) * (q.w - q.y) > kBigArea) big_list[atomicAdd(big_count, 1u)] = i;   // order is irrelevant (atomicMin)
+        rects[i] = q;                        // {x0 | x1 << 16, y0 | y1 << 16, depth lower bound bits, area}
+        if (q.w > kBigArea) big_list[atomicAdd(big_count, 1u)] = i;   // order is irrelevant (atomicMin)
     }
     if (i < n_lights) {
         const AshGpuLight& l = lights[i];
@@ -133,56 +153,73 @@ __global__ void __launch_bounds__(256) k_forward_clear(ulonglong2* __restrict__ 
     if (blockIdx.x == 0 && threadIdx.x == 0 && (n & 1)) keys[n - 1] = clear;
 }
 
-__device__ __forceinline__ void splat_pixel(float4 s, float cc, uint32_t id, int x, int y, const FwdConsts& k,
+__device__ __forceinline__ void splat_pixel(float4 s, float cc, uint32_t lb_bits, uint32_t id, int x, int y, const FwdConsts& k,
                                             const float* __restrict__ ray_x, const float* __restrict__ ray_y,
                                             unsigned long long* __restrict__ keys) {
+    unsigned long long* p = keys + (size_t)y * k.W + x;
+    const unsigned long long cur = *p;                  // plain read: keys only decrease, a stale value only costs work
+    if ((uint32_t)(cur >> 32) < lb_bits) return;        // something nearer than this sphere can be is already there
     const float t = hit_t(s, cc, __ldg(ray_x + x), __ldg(ray_y + y), k.near_plane);
     if (t < 0.0f) return;
     const float d = fadd(fdiv(fsub(k.P32, fmul(k.P22, t)), t), 0.0f);              // ndc z of view z = -t; -0 -> +0
     if (!(d >= 0.0f && d <= 1.0f)) return;
     const unsigned long long key = ((unsigned long long)__float_as_uint(d) << 32) | id;
-    unsigned long long* p = keys + (size_t)y * k.W + x;
-    if (key < *p) atomicMin(p, key);        // the plain read only skips atomics that cannot win (keys only decrease)
+    if (key < cur) atomicMin(p, key);
 }
 
+// one warp per sphere whose rectangle area is in (area_lo, area_hi]
 __global__ void __launch_bounds__(256)
 k_splat_small(const float4* __restrict__ spheres, const int4* __restrict__ rects, const FwdConsts* __restrict__ consts,
-              const float* __restrict__ ray_x, const float* __restrict__ ray_y, unsigned long long* __restrict__ keys) {
+              const float* __restrict__ ray_x, const float* __restrict__ ray_y, unsigned long long* __restrict__ keys,
+              int area_lo, int area_hi) {
     const FwdConsts k = *consts;
     const uint32_t id = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     if (id >= k.object_count) return;
     const int4 q = __ldg(rects + id);
-    const int area = (q.z - q.x) * (q.w - q.y);
-    if (area <= 0 || area > kBigArea) return;
+    if (q.w <= area_lo || q.w > area_hi) return;
+    const int x0 = q.x & 0xFFFF, x1 = (int)((uint32_t)q.x >> 16), y0 = q.y & 0xFFFF, y1 = (int)((uint32_t)q.y >> 16);
     const float4 s = __ldg(spheres + id);
     const float cc = sphere_cc(s);
     const int lane = threadIdx.x & 31, lx = lane & 7, ly = lane >> 3;
-    for (int y = q.y + ly; y < q.w; y += 4)
-        for (int x = q.x + lx; x < q.z; x += 8) splat_pixel(s, cc, id, x, y, k, ray_x, ray_y, keys);
+    for (int y = y0 + ly; y < y1; y += 4)
+        for (int x = x0 + lx; x < x1; x += 8) splat_pixel(s, cc, (uint32_t)q.z, id, x, y, k, ray_x, ray_y, keys);
 }
 
+// rectangles above kBigArea: the list is staged through shared memory 256 entries at a time; chunk c of
+// entry b belongs to CTA (c + 7 b) mod grid, so that spheres of a few chunks spread over the whole grid
 __global__ void __launch_bounds__(256)
 k_splat_big(const float4* __restrict__ spheres, const int4* __restrict__ rects, const uint32_t* __restrict__ big_list,
             const uint32_t* __restrict__ big_count, const FwdConsts* __restrict__ consts,
             const float* __restrict__ ray_x, const float* __restrict__ ray_y, unsigned long long* __restrict__ keys) {
+    __shared__ int4 s_q[256];
+    __shared__ float4 s_s[256];
+    __shared__ uint32_t s_id[256];
     const FwdConsts k = *consts;
     const uint32_t nb = *big_count;
     const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
-    for (uint32_t b = 0; b < nb; ++b) {
-        const uint32_t id = big_list[b];
-        const int4 q = __ldg(rects + id);
-        const int ncx = (q.z - q.x + kChunk - 1) / kChunk, ncy = (q.w - q.y + kChunk - 1) / kChunk;
-        // chunk c goes to CTA (c + 7 b) mod grid: spheres of a few chunks spread over the whole grid
-        const uint32_t first = (blockIdx.x + gridDim.x - (7u * b) % gridDim.x) % gridDim.x;
-        if (first >= (uint32_t)(ncx * ncy)) continue;
-        const float4 s = __ldg(spheres + id);
-        const float cc = sphere_cc(s);
-        for (uint32_t c = first; c < (uint32_t)(ncx * ncy); c += gridDim.x) {
-            const int x = q.x + (int)(c % ncx) * kChunk + tx, y0 = q.y + (int)(c / ncx) * kChunk + ty;
-            if (x >= q.z) continue;
+    for (uint32_t b0 = 0; b0 < nb; b0 += 256) {
+        __syncthreads();
+        if (b0 + threadIdx.x < nb) {
+            const uint32_t id = big_list[b0 + threadIdx.x];
+            s_id[threadIdx.x] = id; s_q[threadIdx.x] = __ldg(rects + id); s_s[threadIdx.x] = __ldg(spheres + id);
+        }
+        __syncthreads();
+        const uint32_t nloc = min(256u, nb - b0);
+        for (uint32_t j = 0; j < nloc; ++j) {
+            const int4 q = s_q[j];
+            const int x0 = q.x & 0xFFFF, x1 = (int)((uint32_t)q.x >> 16), y0 = q.y & 0xFFFF, y1 = (int)((uint32_t)q.y >> 16);
+            const int ncx = (x1 - x0 + kChunk - 1) / kChunk, ncy = (y1 - y0 + kChunk - 1) / kChunk;
+            const uint32_t first = (blockIdx.x + gridDim.x - (7u * (b0 + j)) % gridDim.x) % gridDim.x;
+            if (first >= (uint32_t)(ncx * ncy)) continue;
+            const float4 s = s_s[j];
+            const float cc = sphere_cc(s);
+            for (uint32_t c = first; c < (uint32_t)(ncx * ncy); c += gridDim.x) {
+                const int x = x0 + (int)(c % ncx) * kChunk + tx, yy = y0 + (int)(c / ncx) * kChunk + ty;
+                if (x >= x1) continue;
 #pragma unroll
-            for (int r = 0; r < kChunk; r += 8)
-                if (y0 + r < q.w) splat_pixel(s, cc, id, x, y0 + r, k, ray_x, ray_y, keys);
+                for (int r = 0; r < kChunk; r += 8)
+                    if (yy + r < y1) splat_pixel(s, cc, (uint32_t)q.z, s_id[j], x, yy + r, k, ray_x, ray_y, keys);
+            }
         }
     }
 }
@@ -321,10 +358,12 @@ cudaError_t launch_forward_depth(const AshCullingCameraData& cam, const AshForwa
     k_forward_setup<<<(span + 255) / 256, 256, 0, L.s>>>(cam, fp, objs, n, lights, n_lights, W, H, spheres, rects, big_list, big_count,
                                                          lights_view, ray_x, ray_y, static_cast<FwdConsts*>(consts));
     k_forward_clear<<<148 * 8, 256, 0, L.s>>>(reinterpret_cast<ulonglong2*>(keys), P / 2, keys, P);
-    if (n) {
-        k_splat_small<<<(n + 7) / 8, 256, 0, L.s>>>(spheres, rects, static_cast<const FwdConsts*>(consts), ray_x, ray_y, keys);
-        k_splat_big<<<148 * 4, 256, 0, L.s>>>(spheres, rects, big_list, big_count, static_cast<const FwdConsts*>(consts), ray_x, ray_y, keys);
-        *L.launches += 2;
+    if (n) {   // big (near) spheres first: what they cover lets the far ones skip their tests (same result in any order)
+        const FwdConsts* kc = static_cast<const FwdConsts*>(consts);
+        k_splat_big<<<148 * 4, 256, 0, L.s>>>(spheres, rects, big_list, big_count, kc, ray_x, ray_y, keys);
+        k_splat_small<<<(n + 7) / 8, 256, 0, L.s>>>(spheres, rects, kc, ray_x, ray_y, keys, kMidArea, kBigArea);
+        k_splat_small<<<(n + 7) / 8, 256, 0, L.s>>>(spheres, rects, kc, ray_x, ray_y, keys, 0, kMidArea);
+        *L.launches += 3;
     }
     k_forward_depth<<<148 * 8, 256, 0, L.s>>>(reinterpret_cast<const uint2*>(keys), depth, P);
     *L.launches += 2;

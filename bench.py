@@ -120,13 +120,17 @@ def algorithmic_bytes(kclass, n_objs, n_lights, st):
         # row f-2 (--instancing): visibility + batch id + mesh id, position of visible objects, selection out,
         # kept instances in + out, one draw per bucket
         12: 12 * n_objs + 16 * V + 16 * n_objs + 192 * int(st.get("kept_instances", 0)) + 20 * int(st.get("buckets", 0)),
+        # row f-1 (--forward): objects in, sphere + rectangle out, key clear, key resolve (8 B in, 4 B depth out);
+        # the splat's atomics hit L2.  Shade: key in, RGBA16F out, the tile lists.
+        13: 144 * n_objs + 8 * P + 12 * P,
+        14: 8 * P + c * P + 4 * (tiles + sum_l),
     }
     return float(table[kclass])
 
 
 KERNEL_NAMES = ["depth_pyramid", "occlusion_cull", "cull_compact", "light_prepass", "light_tiles", "taa_resolve",
                 "bloom_threshold", "bloom_downsample", "bloom_upsample", "tonemap", "taa_threshold_fused",
-                "upsample_tonemap_fused", "instancing"]
+                "upsample_tonemap_fused", "instancing", "forward_depth", "forward_shade"]
 
 
 # ------------------------------------------------------------------ clocks sampling (B200_PROFILING.md)
@@ -301,6 +305,7 @@ def run_cuda(args):
                       "d_inst": torch.from_numpy(inst.view(np.uint8)).cuda(), "d_batch": torch.from_numpy(batch.view(np.int32)).cuda(),
                       "d_mesh": torch.from_numpy(mesh.view(np.int32)).cuda(), "d_meshes": torch.from_numpy(meshes.view(np.uint8)).cuda()}
 
+    fwd_params = synth.forward_params(near=0.5, flags=T.FWD_TILE_LIGHTS) if args.forward else None
     host_views = [make_view_inputs(rank * B + v, max(total_views, 1024), objs) for v in range(distinct)]
     streams = [torch.cuda.Stream() for _ in range(args.streams)]
     slots = []
@@ -317,6 +322,9 @@ def run_cuda(args):
             c.set_lod_meshes(inst_scene["d_meshes"])
             c.set_lod_config(inst_scene["cfg"])
             vparams["stages"] |= T.STAGE_INSTANCING
+        if args.forward:
+            c.set_forward_params(fwd_params)
+            vparams["stages"] |= T.STAGE_FORWARD_DEPTH | T.STAGE_FORWARD_SHADE
         slot = {"ctx": c, "vp": vparams,
                 "d_depth": torch.from_numpy(depth).cuda(), "d_hdr": torch.from_numpy(hdr.view(np.uint16)).cuda(),
                 "h_depth": torch.from_numpy(depth).pin_memory(), "h_hdr": torch.from_numpy(hdr.view(np.uint16)).pin_memory()}
@@ -354,14 +362,16 @@ def run_cuda(args):
     def step_resident():
         for s in slots:
             c = s["ctx"]
-            c.set_depth(s["d_depth"])
-            c.set_color(s["d_hdr"], d_vel)
+            if not args.forward:                       # --forward: depth and HDR colour are made inside view_run
+                c.set_depth(s["d_depth"])
+                c.set_color(s["d_hdr"], d_vel)
             c.view_run(s["vp"])
 
     def step_e2e():
         for s in slots:
             c = s["ctx"]
-            c.upload_view(s["h_depth"], s["h_hdr"])
+            if not args.forward:                       # --forward: only the parameter block crosses the host boundary
+                c.upload_view(s["h_depth"], s["h_hdr"])
             c.view_run(s["vp"])
             c.download_view(s["o_vis"], s["o_td"], s["o_ldr"], s["o_st"], s["o_cnt"])
 
@@ -441,11 +451,30 @@ def run_cuda(args):
                          synth.instancing_params(cam0, n_objs), inst_scene["cfg"], 16, vis0)
             widened["cpu_ms_per_view"] = (time.perf_counter() - t0) * 1e3
 
+    if args.forward:
+        keys0 = slots[0]["ctx"].forward_keys()
+        widened = dict(widened or {})
+        widened.update({"row_f1": "depth + HDR colour produced on the device: occluder-sphere ray cast + tiled-forward Cook-Torrance shading "
+                                  "(frag.frag BRDF) over the tile light lists; no per-view host upload",
+                        "occluders": n_objs, "covered_fraction": float(((keys0 & np.uint64(0xFFFFFFFF)) != np.uint64(0xFFFFFFFF)).mean())})
+        if world == 1 and args.cpu_views > 0:     # the CPU oracle of the same two stages on view 0 (serial splat, OpenMP shade)
+            from oracle import oracle as O
+            cam0 = host_views[0][0]
+            t0 = time.perf_counter()
+            k0, d0 = O.forward_depth(objs, cam0.camera_data(), fwd_params, W, H)
+            t1 = time.perf_counter()
+            O.forward_shade(k0, objs, lights, slots[0]["ctx"].tile_data(), cam0.camera_data(), fwd_params)
+            widened["cpu_forward_depth_ms"] = (t1 - t0) * 1e3
+            widened["cpu_forward_shade_ms"] = (time.perf_counter() - t1) * 1e3
+            widened["forward_depth_keys_equal_oracle"] = bool(np.array_equal(k0, keys0))
+
     # ---- end-to-end through host buffers
     e2e_ms = timed(step_e2e, args.steps, 2)
     e2e_value = total_views * args.steps / (e2e_ms * 1e-3)
     tiles = ((W + 15) // 16) * ((H + 15) // 16)
     h2d = B * (W * H * 4 + W * H * 8 + T.VIEW_PARAMS.itemsize)   # depth + HDR + the per-view parameter block
+    if args.forward:
+        h2d = B * T.VIEW_PARAMS.itemsize
     d2h = B * (n_objs * 4 + tiles * 257 * 4 + W * H * 4 + 32 + 4)
     # sanity: the e2e outputs equal the resident path's
     chk = slots[0]
@@ -497,6 +526,7 @@ def run_cuda(args):
         "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic",
         "config": {"workload": workload_name() + (" + LOD selection / instance batching (--instancing)" if inst_scene else "")
+                   + (" with depth + HDR colour produced on the device by the compute forward pass (--forward, row f-1)" if args.forward else "")
                    + (" + per-pixel velocity buffer in the TAA (--velocity; resident passes only)" if args.velocity else ""),
                    "views_per_gpu_per_step": B, "distinct_view_inputs_per_gpu": distinct,
                    "streams": args.streams, "concurrent_frontend": True,
@@ -555,6 +585,9 @@ def main():
     ap.add_argument("--cpu-views", type=int, default=2)
     ap.add_argument("--graph-replay", type=int, default=1, choices=[0, 1],
                     help="1: view_run replays a captured CUDA graph per view (library default); 0: launches every kernel")
+    ap.add_argument("--forward", action="store_true",
+                    help="widened path (SURVEY 8.6 row f-1): depth and HDR colour are produced on the device from the cull objects "
+                         "and the tile light lists instead of being uploaded; not the headline workload")
     ap.add_argument("--velocity", action="store_true",
                     help="supply a per-pixel RG16F velocity buffer to the TAA (the headline workload has none, PIN-12)")
     ap.add_argument("--instancing", action="store_true",

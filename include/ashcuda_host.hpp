@@ -529,6 +529,20 @@ public:
     LodManager        lod;
     std::vector<LodMesh>  lod_meshes;
     std::vector<uint32_t> lod_mesh_ids;
+    // row f-1 (optional): make the depth and HDR colour buffers on the device from the cull objects and the tile
+    // light lists (shaders/frag.frag's BRDF) instead of taking them from FrameInputs
+    bool             produce_inputs = false;
+    AshForwardParams forward_params = default_forward_params();
+
+    static AshForwardParams default_forward_params() {     // the library's defaults (ashcuda_set_forward_params(ctx, NULL))
+        AshForwardParams p{};
+        const float dir[4] = {-0.3f, -1.0f, -0.2f, 0.0f}, white[4] = {1, 1, 1, 1}, amb[4] = {0.03f, 0.03f, 0.03f, 1.0f};
+        const float mr[4] = {0.0f, 0.5f, 1.0f, 1.0f}, bg[4] = {0.02f, 0.02f, 0.03f, 1.0f};
+        std::memcpy(p.light_direction, dir, 16); std::memcpy(p.light_color, white, 16); std::memcpy(p.ambient_color, amb, 16);
+        std::memcpy(p.base_color_factor, white, 16); std::memcpy(p.parameters, mr, 16); std::memcpy(p.background, bg, 16);
+        p.near_plane = 0.1f; p.radius_scale = 1.0f; p.flags = ASH_FWD_TILE_LIGHTS;
+        return p;
+    }
 
     const char* name() const override { return "CudaCompute"; }
     void on_added(const Device&) override {               // LightCullingPipeline::new, :41-243
@@ -567,8 +581,12 @@ public:
     }
     void render(const FeatureRenderContext&) override {
         if (!ctx_ || !have_inputs_) { fail(ASH_ERR_NOT_INITIALIZED, "render without context or frame inputs"); return; }
-        if (!check(ashcuda_set_depth(ctx_, inputs_.depth, inputs_.on_device), "set_depth")) return;
-        if (inputs_.hdr && !check(ashcuda_set_color(ctx_, inputs_.hdr, inputs_.velocity, inputs_.on_device), "set_color")) return;
+        if (produce_inputs) {
+            if (!check(ashcuda_set_forward_params(ctx_, &forward_params), "set_forward_params")) return;
+        } else {
+            if (!check(ashcuda_set_depth(ctx_, inputs_.depth, inputs_.on_device), "set_depth")) return;
+            if (inputs_.hdr && !check(ashcuda_set_color(ctx_, inputs_.hdr, inputs_.velocity, inputs_.on_device), "set_color")) return;
+        }
         const AshCudaViewParams vp = view_params();
         check(ashcuda_view_run(ctx_, &vp), "view_run");
     }
@@ -589,7 +607,8 @@ public:
         if (culling.is_enabled()) st |= ASH_STAGE_CULL;
         if (lights.is_enabled()) st |= ASH_STAGE_LIGHTS;
         if (instancing_on_ && culling.is_enabled()) st |= ASH_STAGE_INSTANCING;
-        if (inputs_.hdr) {
+        if (produce_inputs) st |= ASH_STAGE_FORWARD_DEPTH | ASH_STAGE_FORWARD_SHADE | ASH_STAGE_LIGHTS;
+        if (inputs_.hdr || produce_inputs) {
             if (taa.is_enabled()) st |= ASH_STAGE_TAA;
             if (bloom.enabled) st |= ASH_STAGE_BLOOM;
             st |= ASH_STAGE_TONEMAP;

@@ -73,12 +73,23 @@ Sphere sphere_of(const AshCullObjectData& o, const AshCullingCameraData& cam, fl
     return {{cv.x, cv.y, cv.z}, r};
 }
 
-// per-axis pixel bound of the sphere's silhouette (tangent rays through the eye), padded by a pixel
-void axis_bound(float c, float cz, float r, float den, float P, int S, int* i0, int* i1) {
-    const float D = (c * c + cz * cz) - r * r;
-    const float sq = sqrtf(gmax(D, 0.0f));
-    const float m = c * cz, k = r * sq;
-    const float n0 = P * ((m - k) / den), n1 = P * ((m + k) / den);
+// per-axis pixel bound of the part of the sphere in front of the near plane, padded by a pixel:
+// tangent rays through the eye when the eye plane does not cut the sphere (cz > r), else the box bound
+// of { x in [c-r, c+r], z in [near, cz+r] }
+void axis_bound(float c, float cz, float r, bool tangent, float near_plane, float P, int S, int* i0, int* i1) {
+    float s0, s1;
+    if (tangent) {
+        const float den = (cz - r) * (cz + r);
+        const float D = (c * c + cz * cz) - r * r;
+        const float sq = sqrtf(gmax(D, 0.0f));
+        const float m = c * cz, k = r * sq;
+        s0 = (m - k) / den; s1 = (m + k) / den;
+    } else {
+        const float zmax = cz + r, lo_c = c - r, hi_c = c + r;
+        s0 = lo_c < 0.0f ? lo_c / near_plane : lo_c / zmax;
+        s1 = hi_c > 0.0f ? hi_c / near_plane : hi_c / zmax;
+    }
+    const float n0 = P * s0, n1 = P * s1;
     const float p0 = (n0 * 0.5f + 0.5f) * (float)S, p1 = (n1 * 0.5f + 0.5f) * (float)S;
     const float lo = gmin(p0, p1), hi = gmax(p0, p1);
     if (!(lo <= hi)) { *i0 = 0; *i1 = S; return; }
@@ -89,11 +100,10 @@ struct Rect { int x0, y0, x1, y1; };
 Rect rect_of(const Sphere& s, const AshCullingCameraData& cam, float near_plane, int W, int H) {
     const float cz = -s.c.z;
     if (!(s.r > 0.0f) || cz + s.r < near_plane) return {0, 0, 0, 0};
-    if (!(cz - s.r > near_plane)) return {0, 0, W, H};
-    const float den = (cz - s.r) * (cz + s.r);
+    const bool tangent = cz > s.r;
     Rect q;
-    axis_bound(s.c.x, cz, s.r, den, cam.projection[0][0], W, &q.x0, &q.x1);
-    axis_bound(s.c.y, cz, s.r, den, cam.projection[1][1], H, &q.y0, &q.y1);
+    axis_bound(s.c.x, cz, s.r, tangent, near_plane, cam.projection[0][0], W, &q.x0, &q.x1);
+    axis_bound(s.c.y, cz, s.r, tangent, near_plane, cam.projection[1][1], H, &q.y0, &q.y1);
     return q;
 }
 

@@ -53,6 +53,19 @@ pub struct AshInstancingParams { pub view_proj: [[f32; 4]; 4], pub camera_pos: [
                                  pub object_count: u32, pub _padding: u32 }
 const _: () = assert!(std::mem::size_of::<InstanceData>() == 96 && std::mem::size_of::<AshLodMesh>() == 208);
 const _: () = assert!(std::mem::size_of::<AshInstancingStats>() == 72 && std::mem::size_of::<AshInstancingParams>() == 96);
+/// frag.frag MVP / Material uniform fields used by the compute forward pass (row f-1)
+#[repr(C)] #[derive(Clone, Copy, Default)]
+pub struct AshForwardParams { pub light_direction: [f32; 4], pub light_color: [f32; 4], pub ambient_color: [f32; 4],
+                              pub base_color_factor: [f32; 4], pub emissive_factor: [f32; 4], pub parameters: [f32; 4],
+                              pub background: [f32; 4], pub near_plane: f32, pub radius_scale: f32, pub flags: u32, pub _padding: u32 }
+const _: () = assert!(std::mem::size_of::<AshForwardParams>() == 128);
+pub const ASH_FWD_TILE_LIGHTS: u32 = 1;
+pub const ASH_FWD_REINHARD: u32 = 2;
+pub const ASH_FWD_INSTANCE_COLOR: u32 = 4;
+pub const ASH_STAGE_FORWARD_DEPTH: u32 = 0x100;
+pub const ASH_STAGE_FORWARD_SHADE: u32 = 0x200;
+pub const ASH_BUF_FORWARD_KEYS: c_int = 16;
+pub const ASH_BUF_COLOR: c_int = 17;
 pub const ASH_STAGE_INSTANCING: u32 = 0x80;
 pub const ASH_BUF_LOD_SELECTION: c_int = 11;
 pub const ASH_BUF_INSTANCES_OUT: c_int = 12;
@@ -102,6 +115,9 @@ extern "C" {
     pub fn ashcuda_set_lod_meshes(ctx: *mut ashcuda_ctx, meshes: *const AshLodMesh, n: u32, on_device: c_int) -> c_int;
     pub fn ashcuda_set_lod_config(ctx: *mut ashcuda_ctx, cfg: *const AshLodConfig) -> c_int;
     pub fn ashcuda_instancing_finalize(ctx: *mut ashcuda_ctx, ip: *const AshInstancingParams) -> c_int;
+    pub fn ashcuda_set_forward_params(ctx: *mut ashcuda_ctx, params: *const AshForwardParams) -> c_int;
+    pub fn ashcuda_forward_depth(ctx: *mut ashcuda_ctx, cam: *const CullingCameraData, object_count: u32) -> c_int;
+    pub fn ashcuda_forward_shade(ctx: *mut ashcuda_ctx) -> c_int;
     pub fn ashcuda_upload_view(ctx: *mut ashcuda_ctx, depth: *const f32, hdr: *const c_void, velocity: *const c_void) -> c_int;
     pub fn ashcuda_download_view(ctx: *mut ashcuda_ctx, visibility: *mut u32, tile_data: *mut u32, ldr8: *mut u8, stats: *mut AshViewStats, visible_count: *mut u32) -> c_int;
     pub fn ashcuda_get(ctx: *mut ashcuda_ctx, which: c_int, dev_ptr: *mut *mut c_void, bytes: *mut usize) -> c_int;

@@ -163,6 +163,18 @@ int main(int argc, char** argv) {
     CHECK(f.read_instancing_stats(&ist) && ist.total_instances + ist.objects_culled == vis && ist.batch_count <= 2 && ist.triangles_before == 1000ull * vis);
     std::vector<uint8_t> ldr((size_t)W * H * 4);
     CHECK(ashcuda_readback(f.context(), ASH_BUF_LDR8, ldr.data(), ldr.size()) == ASH_OK && ldr[3] == 255 && ldr[0] > 0);
+    // row f-1: the same frame with depth and HDR colour produced on the device (no FrameInputs buffers)
+    f.produce_inputs = true;
+    f.forward_params.near_plane = 0.5f;
+    FrameInputs in2 = in; in2.depth = nullptr; in2.hdr = nullptr; in2.view_id = 9;
+    f.set_frame_inputs(in2); f.before_frame(fc); f.render(rc);
+    CHECK(f.last_code() == ASH_OK);
+    CHECK((f.view_params().stages & (ASH_STAGE_FORWARD_DEPTH | ASH_STAGE_FORWARD_SHADE | ASH_STAGE_TONEMAP)) ==
+          (ASH_STAGE_FORWARD_DEPTH | ASH_STAGE_FORWARD_SHADE | ASH_STAGE_TONEMAP));
+    std::vector<uint64_t> keys((size_t)W * H);
+    CHECK(ashcuda_readback(f.context(), ASH_BUF_FORWARD_KEYS, keys.data(), keys.size() * 8) == ASH_OK);
+    size_t covered = 0; for (uint64_t k : keys) covered += (uint32_t)k != ASH_FWD_NO_OBJECT;
+    CHECK(covered > 0 && covered < keys.size() && f.read_visible_count() > 0);
     f.on_removed(dev);
     std::printf("host tests ok (gpu: %u/64 visible, ldr[0]=%u)\n", vis, ldr[0]);
     return 0;

@@ -19,7 +19,9 @@ def _scene(W, H, eye=(0.0, 2.0, 22.0), target=(0, 0, 0), grid=(8, 6, 6), seed=3,
 
 @pytest.mark.parametrize("eye,target", [((0.0, 2.0, 22.0), (0, 0, 0)), ((3.0, 1.0, 9.0), (0, 0, 0)),
                                         ((0.3, 0.2, 0.1), (5, 1, 4)),            # inside the grid: spheres cross the near plane
-                                        ((-14.0, 9.0, 3.0), (0, 0, 0))])
+                                        ((-14.0, 9.0, 3.0), (0, 0, 0)),
+                                        ((1.1, -0.9, 2.7), (-6, 2, -3)), ((-2.9, 3.1, -1.2), (4, -3, 5)),       # more eyes inside the grid
+                                        ((6.9, 0.1, 0.4), (-7, 0.5, 0.2)), ((0.0, 4.95, 0.0), (0.2, -5, 0.1))])
 def test_silhouette_rectangle_is_conservative(eye, target):
     W, H = 160, 90
     cam, objs, _, fp = _scene(W, H, eye, target)
