@@ -32,7 +32,7 @@ EXPORTS = [
     "ashcuda_version", "ashcuda_profile_kernels", "ashcuda_kernel_time_ms", "ashcuda_upload_view", "ashcuda_download_view",
     "ashcuda_debug_exact_taps",
     "ashcuda_set_instances", "ashcuda_set_lod_meshes", "ashcuda_set_lod_config", "ashcuda_instancing_finalize",
-    "ashcuda_set_forward_params", "ashcuda_forward_depth", "ashcuda_forward_shade",
+    "ashcuda_set_forward_params", "ashcuda_forward_depth", "ashcuda_forward_shade", "ashcuda_debug_compute_utils",
 ]
 
 
@@ -97,6 +97,7 @@ def load_library():
         "ashcuda_set_forward_params": (i32, [vp, vp]),
         "ashcuda_forward_depth": (i32, [vp, vp, u32]),
         "ashcuda_forward_shade": (i32, [vp]),
+        "ashcuda_debug_compute_utils": (i32, [i32, i32, vp, u32, vp, vp]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(lib, name)
@@ -378,3 +379,28 @@ class Context:
 
 def version():
     return load_library().ashcuda_version().decode()
+
+
+CU_MIN, CU_MAX, CU_SUM, CU_SCAN, CU_SPHERE_IN_FRUSTUM, CU_AABB_IN_FRUSTUM, CU_DEPTH, CU_PLANES = range(8)
+
+
+def compute_utils(op, data=None, params=None, device=0):
+    """shaders/compute_utils.glsl on the device (csrc/ash_compute_utils.cuh), one function per call; see ashcuda.h."""
+    lib = load_library()
+    p = np.zeros(18, np.float32)
+    if params is not None:
+        q = np.asarray(params, np.float32).reshape(-1)
+        p[:len(q)] = q
+    if op == CU_PLANES:
+        out = np.zeros((6, 4), np.float32)
+        rc = lib.ashcuda_debug_compute_utils(device, op, None, 0, p.ctypes.data, out.ctypes.data)
+    else:
+        a = np.ascontiguousarray(data, np.uint32 if op == CU_SCAN else np.float32)
+        n = a.shape[0]
+        out = (np.zeros(n // 256, np.float32) if op <= CU_SUM else np.zeros(n, np.uint32) if op in (CU_SCAN, CU_SPHERE_IN_FRUSTUM, CU_AABB_IN_FRUSTUM)
+               else np.zeros((n, 4), np.float32))
+        rc = lib.ashcuda_debug_compute_utils(device, op, a.ctypes.data, n, p.ctypes.data, out.ctypes.data)
+    if rc != ASH_OK:
+        raise AshError(rc, "ashcuda_debug_compute_utils")
+    return out
+

@@ -414,6 +414,24 @@ int ashcuda_kernel_time_ms(ashcuda_ctx*, int kernel_class, float* ms, uint64_t* 
  * (n_dst texels, size_f = extent as float); 1: TAA 3x3 taps (size_f, inv = screenParams.z|w);
  * 2: 2:1 downsample (n_src -> n_dst); 3: 1:2 upsample (n_src -> n_dst).  Returns 1 / 0. */
 int ashcuda_debug_exact_taps(int kind, int n_src, int n_dst, float size_f, float inv);
+/* shaders/compute_utils.glsl as a CUDA header (csrc/ash_compute_utils.cuh; row f-4): runs one function of
+ * the library on host data on `device` (no context), for parity tests.  op:
+ *   ASH_CU_MIN / MAX / SUM   in: float[n], n % 256 == 0  -> out: float[n/256]   parallelMin/Max/Sum, :22-65
+ *   ASH_CU_SCAN              in: u32[n],   n % 256 == 0  -> out: u32[n]         exclusivePrefixSum per 256, :80-111
+ *   ASH_CU_SPHERE_IN_FRUSTUM in: float[n][4] (centre, radius), params[0..15] = view_proj columns -> out: u32[n], :171-178
+ *   ASH_CU_AABB_IN_FRUSTUM   in: float[n][6] (min, max), same params -> out: u32[n], :188-195
+ *   ASH_CU_DEPTH             in: float[n][3] (u, v, depth), params = inv_proj columns, near, far
+ *                            -> out: float[n][4] = linearizeDepth, uvDepthToView xyz, :205-219
+ *   ASH_CU_PLANES            params = view_proj columns -> out: float[6][4] extractPlane(face 0..5), :126-160 */
+#define ASH_CU_MIN 0
+#define ASH_CU_MAX 1
+#define ASH_CU_SUM 2
+#define ASH_CU_SCAN 3
+#define ASH_CU_SPHERE_IN_FRUSTUM 4
+#define ASH_CU_AABB_IN_FRUSTUM 5
+#define ASH_CU_DEPTH 6
+#define ASH_CU_PLANES 7
+int ashcuda_debug_compute_utils(int device, int op, const void* in, uint32_t n, const float* params18, void* out);
 const char* ashcuda_last_error(ashcuda_ctx*);                  /* NULL ctx: last create error */
 const char* ashcuda_version(void);
 

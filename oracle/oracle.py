@@ -34,7 +34,7 @@ POST_PC_DTYPE = np.dtype([("exposure", "<f4"), ("gamma", "<f4"), ("bloom_intensi
 
 def build(force=False):
     """Compile libashoracle.so with the committed Makefile (g++ -O2 -fopenmp -ffp-contract=off)."""
-    srcs = [os.path.join(_HERE, f) for f in ("ash_oracle.cpp", "ash_oracle_instancing.cpp", "ash_oracle_forward.cpp")]
+    srcs = [os.path.join(_HERE, f) for f in ("ash_oracle.cpp", "ash_oracle_instancing.cpp", "ash_oracle_forward.cpp", "ash_oracle_utils.cpp")]
     if (not force and os.path.exists(_LIB_PATH)
             and os.path.getmtime(_LIB_PATH) >= max(os.path.getmtime(f) for f in srcs)):
         return _LIB_PATH
@@ -286,4 +286,28 @@ def forward_shade(keys, objs, lights, tile_data, cam, fp, instances=None):
     f(_p(k), _p(o), len(o.reshape(-1)), _p(l), len(l.reshape(-1)), _p(td), None if inst is None else _p(inst),
       0 if inst is None else len(inst.reshape(-1)), _p(c), _p(p), W, H, _p(hdr))
     return hdr
+
+
+# ---- row f-4: shaders/compute_utils.glsl (oracle/ash_oracle_utils.cpp); op numbering = ASH_CU_* of ashcuda.h
+CU_MIN, CU_MAX, CU_SUM, CU_SCAN, CU_SPHERE_IN_FRUSTUM, CU_AABB_IN_FRUSTUM, CU_DEPTH, CU_PLANES = range(8)
+
+
+def compute_utils(op, data=None, params=None):
+    p = np.zeros(18, np.float32)
+    if params is not None:
+        q = np.asarray(params, np.float32).reshape(-1)
+        p[:len(q)] = q
+    f = lib().ash_oracle_compute_utils
+    f.restype = C.c_int
+    f.argtypes = [C.c_int, C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p]
+    if op == CU_PLANES:
+        out = np.zeros((6, 4), np.float32)
+        assert f(op, None, 0, _p(p), _p(out)) == 0
+        return out
+    a = np.ascontiguousarray(data, np.uint32 if op == CU_SCAN else np.float32)
+    n = a.shape[0]
+    out = (np.zeros(n // 256, np.float32) if op <= CU_SUM else np.zeros(n, np.uint32) if op in (CU_SCAN, CU_SPHERE_IN_FRUSTUM, CU_AABB_IN_FRUSTUM)
+           else np.zeros((n, 4), np.float32))
+    assert f(op, _p(a), n, _p(p), _p(out)) == 0
+    return out
 
