@@ -349,6 +349,10 @@ class Context:
     def forward_shade(self):
         self._ck(self._lib.ashcuda_forward_shade(self._h))
 
+    def culling_stats(self):
+        """CullingStats of the last cull (render_stats.rs:54-65) + early / late counts of two-phase culling."""
+        return self.readback(T.BUF_CULLING_STATS, T.CULLING_STATS)[0]
+
     def forward_keys(self):
         return self.readback(T.BUF_FORWARD_KEYS, np.uint64).reshape(self.H, self.W)
 

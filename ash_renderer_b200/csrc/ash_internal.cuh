@@ -73,7 +73,7 @@ struct PatchArg {
     int         arg_index = 0, n_args = 0;
     alignas(16) unsigned char value[256];
 };
-void cull_patch(const AshCullingPushConstants& pc, PatchArg* out);                                   // occlusion_cull.cu
+void cull_patch(const AshCullingPushConstants& pc, int mode, PatchArg* out);                                   // occlusion_cull.cu
 void taa_pair_patch(bool thresh, bool vel, const AshTaaPushConstants& pc, PatchArg* out);           // post_pair.cu
 bool taa_in_halo(const AshTaaPushConstants& pc);                                                     // post_fast.cu
 void lod_patch(const AshInstancingParams& ip, const AshLodConfig& cfg, PatchArg* out);               // instancing.cu
@@ -86,12 +86,12 @@ struct GraphKey {
     AshLightCullingPushConstants light;
     float    taa_screen[4];
     AshBloomParams bloom; AshPostProcessPushConstants post;
-    uint32_t in_halo, taa_cur, history_valid, taa_ran, have_color, have_depth, have_instancing, concurrent;
+    uint32_t in_halo, taa_cur, history_valid, taa_ran, have_color, have_depth, have_instancing, concurrent, have_pyramid;
     AshForwardParams fwd;
 };
 struct ViewGraph {
     cudaGraph_t graph = nullptr; cudaGraphExec_t exec = nullptr;
-    cudaGraphNode_t n_store = nullptr, n_cull = nullptr, n_taa = nullptr, n_lod = nullptr, n_fwd = nullptr;
+    cudaGraphNode_t n_store = nullptr, n_cull = nullptr, n_cull2 = nullptr, n_taa = nullptr, n_lod = nullptr, n_fwd = nullptr;
     GraphKey key{}; bool valid = false;
     uint64_t launches = 0;                                  // kernels per replay
     bool taa_flip = false, history_valid = false, taa_ran = false, bloom_valid = false, have_pyramid = false, have_camera = false;
@@ -134,6 +134,7 @@ struct ashcuda_ctx {
     uint32_t* cta_counts = nullptr;
     AshIndirectDrawCommand* draws_out = nullptr;
     uint32_t* visible_count = nullptr;
+    AshCullingStats* culling_stats = nullptr;
 
     // light cull
     const AshGpuLight* lights = nullptr;
@@ -174,6 +175,7 @@ struct ashcuda_ctx {
     float4*   fwd_lights_view = nullptr;
     float*    fwd_rays = nullptr;                // W + H ray-table entries
     void*     fwd_consts = nullptr;
+    uint32_t* fwd_late = nullptr;                // two-phase culling: objects newly visible in phase 2
     bool      have_forward = false;              // keys / spheres of the current view are valid
 
     // CUDA-graph replay of view_run (view_graph.cu): one captured graph per TAA ping-pong parity
@@ -209,7 +211,10 @@ cudaError_t launch_occlusion_cull(const AshCullObjectData* objs, const AshIndire
                                   const AshCullingPushConstants& pc, const Pyramid& p,
                                   uint32_t* visibility, uint32_t* vis_bits, uint32_t* cta_counts,
                                   AshIndirectDrawCommand* draws_out, uint32_t* visible_count,
-                                  AshViewStats* stats, const Launch& L);
+                                  AshViewStats* stats, AshCullingStats* cstats, int phase, bool no_occlusion,
+                                  uint32_t* late, const Launch& L);
+cudaError_t launch_culling_stats_finish(const AshViewStats* stats, const AshInstancingStats* inst_stats, uint32_t light_count,
+                                        bool with_lights, AshCullingStats* cstats, const Launch& L);
 cudaError_t launch_light_cull(const AshGpuLight* lights, const AshLightCullingPushConstants& pc,
                               const AshCullingCameraData* cam_dev, const uint32_t* tile_minmax,
                               uint32_t* depth_range, LightCand* cand, uint32_t* cand_idx,
@@ -218,10 +223,14 @@ cudaError_t launch_light_cull(const AshGpuLight* lights, const AshLightCullingPu
 cudaError_t launch_store_view(const AshCullingCameraData& cam, bool with_camera, uint32_t view_id, AshCullingCameraData* camera_dev,
                               AshViewStats* stats, const Launch& L);                                  // view_graph.cu
 size_t forward_consts_bytes();                                                                       // forward.cu
-cudaError_t launch_forward_depth(const AshCullingCameraData& cam, const AshForwardParams& fp, const AshCullObjectData* objs, uint32_t n,
-                                 const AshGpuLight* lights, uint32_t n_lights, uint32_t W, uint32_t H, float4* spheres, int4* rects,
-                                 uint32_t* big_list, uint32_t* big_count, float4* lights_view, float* ray_x, float* ray_y,
-                                 void* consts, unsigned long long* keys, float* depth, const Launch& L);
+struct ForwardBuffers {                       // forward.cu: everything the depth producer touches
+    float4* spheres; int4* rects; uint32_t* big_list; uint32_t* big_count; float4* lights_view; float* ray_x; float* ray_y;
+    void* consts; unsigned long long* keys; float* depth;
+};
+cudaError_t launch_forward_setup(const AshCullingCameraData& cam, const AshForwardParams& fp, const AshCullObjectData* objs, uint32_t n,
+                                 const AshGpuLight* lights, uint32_t n_lights, uint32_t W, uint32_t H, const ForwardBuffers& B, const Launch& L);
+cudaError_t launch_forward_splat(uint32_t n, uint32_t W, uint32_t H, const ForwardBuffers& B, const uint32_t* mask_or_null, const Launch& L);
+cudaError_t launch_forward_resolve(uint32_t W, uint32_t H, const ForwardBuffers& B, const Launch& L);
 cudaError_t launch_forward_shade(const AshForwardParams& fp, const unsigned long long* keys, const float4* spheres,
                                  const AshGpuLight* lights, uint32_t n_lights, const float4* lights_view, const uint32_t* tile_data,
                                  const AshInstanceData* inst, uint32_t n_inst, const void* consts, const float* ray_x,
@@ -287,3 +296,4 @@ bool axis_up_taps_exact(int sn, int dn);
 int  ash_view_run_eager(ashcuda_ctx* c, const AshCudaViewParams* vp);
 int  ash_view_run_graph(ashcuda_ctx* c, const AshCudaViewParams* vp, bool* handled);
 void ash_view_graphs_destroy(ashcuda_ctx* c);
+int  ash_forward_alloc(ashcuda_ctx* c);

@@ -84,7 +84,7 @@ void ashcuda_destroy(ashcuda_ctx* c) {
                      c->inst_owned, c->inst_batch_owned, c->inst_mesh_owned, c->lod_meshes_owned, c->batch_mesh,
                      c->lod_sel, c->bucket_of, c->cta_hist, c->bucket_offsets, c->bucket_totals, c->inst_out,
                      c->inst_draws, c->inst_stats, c->fwd_keys, c->fwd_spheres, c->fwd_rects, c->fwd_big,
-                     c->fwd_lights_view, c->fwd_rays, c->fwd_consts};
+                     c->fwd_lights_view, c->fwd_rays, c->fwd_consts, c->fwd_late, c->culling_stats};
     for (void* p : owned) if (p) cudaFree(p);
     for (uint32_t k = 1; k <= ASH_MAX_BLOOM_MIPS; ++k) if (c->bloom.d[k]) cudaFree(c->bloom.d[k]);
     c->prof.release_all();
@@ -133,6 +133,8 @@ static int create_impl(ashcuda_ctx* c) {
     const size_t N = c->cfg.max_objects;
     ASH_CUDA(c, dmalloc(&c->objs_owned, N * sizeof(AshCullObjectData)));
     ASH_CUDA(c, dmalloc(&c->draws_in_owned, (size_t)c->cfg.max_draws * sizeof(AshIndirectDrawCommand)));
+    ASH_CUDA(c, dmalloc(&c->culling_stats, sizeof(AshCullingStats)));
+    ASH_CUDA(c, cudaMemsetAsync(c->culling_stats, 0, sizeof(AshCullingStats), c->stream));
     ASH_CUDA(c, dmalloc(&c->visibility, N * 4));
     ASH_CUDA(c, dmalloc(&c->vis_bits, ((N + 31) / 32) * 4));
     ASH_CUDA(c, dmalloc(&c->cta_counts, ((N + 255) / 256) * 4));
@@ -330,8 +332,8 @@ int ashcuda_occlusion_cull(ashcuda_ctx* c, const AshCullingPushConstants* pc) {
         return ASH_OK;
     }
     ASH_CUDA(c, launch_occlusion_cull(c->objs, c->draws_in, *pc, c->pyr, c->visibility, c->vis_bits,
-                                      c->cta_counts, c->draws_out, c->visible_count, c->stats,
-                                      c->L()));
+                                      c->cta_counts, c->draws_out, c->visible_count, c->stats, c->culling_stats,
+                                      0, false, nullptr, c->L()));
     return ASH_OK;
 }
 
@@ -486,7 +488,12 @@ int ashcuda_view_run(ashcuda_ctx* c, const AshCudaViewParams* vp) {
     return ash_view_run_eager(c, vp);
 }
 
+static int two_phase_cull(ashcuda_ctx* c, const AshCudaViewParams* vp);
+static int forward_alloc(ashcuda_ctx* c);
+
 }  // extern "C"
+
+int ash_forward_alloc(ashcuda_ctx* c) { return forward_alloc(c); }     // view_graph.cu: allocations cannot be captured
 
 int ash_view_run_eager(ashcuda_ctx* c, const AshCudaViewParams* vp) {
     int rc = ASH_OK;
@@ -514,9 +521,14 @@ int ash_view_run_eager(ashcuda_ctx* c, const AshCudaViewParams* vp) {
         if (e != cudaSuccess) { c->err = std::string("view_run: ") + cudaGetErrorString(e); rc = ASH_ERR_DEVICE; }
         else if (with_camera) { c->camera_host = vp->camera; c->have_camera = true; }
     }
-    if (!rc && (st & ASH_STAGE_FORWARD_DEPTH)) rc = ashcuda_forward_depth(c, &vp->camera, vp->cull.object_count);
+    const bool two_phase = (st & ASH_STAGE_TWO_PHASE) != 0;
+    if (!rc && two_phase) {
+        const uint32_t need = ASH_STAGE_FORWARD_DEPTH | ASH_STAGE_HIZ | ASH_STAGE_CULL;
+        if ((st & need) != need) rc = fail(c, ASH_ERR_INVALID, "view_run: ASH_STAGE_TWO_PHASE needs FORWARD_DEPTH | HIZ | CULL");
+        else rc = two_phase_cull(c, vp);
+    } else if (!rc && (st & ASH_STAGE_FORWARD_DEPTH)) rc = ashcuda_forward_depth(c, &vp->camera, vp->cull.object_count);
     if (!rc && (st & ASH_STAGE_HIZ)) rc = ashcuda_hiz_build(c);
-    if (!rc && (st & ASH_STAGE_CULL)) rc = ashcuda_occlusion_cull(c, &vp->cull);
+    if (!rc && (st & ASH_STAGE_CULL) && !two_phase) rc = ashcuda_occlusion_cull(c, &vp->cull);
     if (!rc && (st & ASH_STAGE_INSTANCING)) {        // consumes visibility[] of the cull above
         AshInstancingParams ip{};
         std::memcpy(ip.view_proj, vp->cull.view_proj, sizeof(ip.view_proj));
@@ -527,6 +539,11 @@ int ash_view_run_eager(ashcuda_ctx* c, const AshCudaViewParams* vp) {
     }
     if (!rc && (st & ASH_STAGE_LIGHTS)) rc = ashcuda_light_cull(c, &vp->light);
     if (!rc && (st & ASH_STAGE_FORWARD_SHADE)) rc = ashcuda_forward_shade(c);
+    if (!rc && (st & ASH_STAGE_CULL) && vp->cull.object_count) {      // CullingStats: the fields other stages own
+        cudaError_t e = launch_culling_stats_finish(c->stats, (st & ASH_STAGE_INSTANCING) ? c->inst_stats : nullptr, vp->light.light_count,
+                                                    (st & ASH_STAGE_LIGHTS) != 0, c->culling_stats, c->L());
+        if (e != cudaSuccess) { c->err = std::string("view_run: ") + cudaGetErrorString(e); rc = ASH_ERR_DEVICE; }
+    }
     if (fork) {
         cudaError_t e = cudaEventRecord(c->ev_join, c->front_stream);
         c->stream = main_stream;
@@ -660,7 +677,13 @@ static int forward_alloc(ashcuda_ctx* c) {
     ASH_CUDA(c, dmalloc(&c->fwd_lights_view, (size_t)c->cfg.max_lights * sizeof(float4)));
     ASH_CUDA(c, dmalloc(&c->fwd_rays, ((size_t)c->W + c->H) * 4));
     ASH_CUDA(c, dmalloc(&c->fwd_consts, forward_consts_bytes()));
+    ASH_CUDA(c, dmalloc(&c->fwd_late, N * 4));
     return ASH_OK;
+}
+
+static ForwardBuffers forward_buffers(ashcuda_ctx* c) {
+    return ForwardBuffers{c->fwd_spheres, c->fwd_rects, c->fwd_big + 1, c->fwd_big, c->fwd_lights_view, c->fwd_rays, c->fwd_rays + c->W,
+                          c->fwd_consts, c->fwd_keys, c->depth_owned};
 }
 
 int ashcuda_set_forward_params(ashcuda_ctx* c, const AshForwardParams* p) {
@@ -681,11 +704,48 @@ int ashcuda_forward_depth(ashcuda_ctx* c, const AshCullingCameraData* cam, uint3
     ASH_CUDA(c, cudaSetDevice(c->device));
     int rc = forward_alloc(c);
     if (rc) return rc;
-    ASH_CUDA(c, launch_forward_depth(*cam, c->fwd_params, c->objs, object_count, c->lights, c->n_lights, c->W, c->H, c->fwd_spheres,
-                                     c->fwd_rects, c->fwd_big + 1, c->fwd_big, c->fwd_lights_view, c->fwd_rays, c->fwd_rays + c->W,
-                                     c->fwd_consts, c->fwd_keys, c->depth_owned, c->L()));
+    const ForwardBuffers B = forward_buffers(c);
+    ASH_CUDA(c, launch_forward_setup(*cam, c->fwd_params, c->objs, object_count, c->lights, c->n_lights, c->W, c->H, B, c->L()));
+    ASH_CUDA(c, launch_forward_splat(object_count, c->W, c->H, B, nullptr, c->L()));
+    ASH_CUDA(c, launch_forward_resolve(c->W, c->H, B, c->L()));
     c->depth = c->depth_owned; c->pyr.mip0 = c->depth;
     c->have_depth = true; c->have_pyramid = false; c->have_forward = true;
+    return ASH_OK;
+}
+
+// Row f-3: two-phase occlusion culling around the device rasteriser (forward_depth's splat).  The pyramid the
+// previous view of this context left (mip 0 = the owned depth buffer, untouched until the resolve below)
+// is phase 1's occluder set; on a first view phase 1 is the frustum test alone.
+static int two_phase_cull(ashcuda_ctx* c, const AshCudaViewParams* vp) {
+    const AshCullingPushConstants* pc = &vp->cull;
+    if (pc->object_count > c->n_objs) return fail(c, ASH_ERR_INVALID, "two_phase: objectCount > uploaded objects");
+    if (pc->object_count == 0) return fail(c, ASH_ERR_INVALID, "two_phase: no objects");
+    if (pc->hiz_levels == 0 || (int)pc->hiz_levels > c->pyr.levels) return fail(c, ASH_ERR_INVALID, "two_phase: hizLevels outside [1, levels_built]");
+    if (vp->camera.projection[2][3] != -1.0f || vp->camera.projection[3][3] != 0.0f)
+        return fail(c, ASH_ERR_INVALID, "two_phase: projection is not a right-handed perspective (w_clip = -z_view)");
+    if (c->W > 65535u || c->H > 65535u) return fail(c, ASH_ERR_INVALID, "two_phase: extent above 65535");
+    ASH_CUDA(c, cudaSetDevice(c->device));
+    int rc = forward_alloc(c);
+    if (rc) return rc;
+    const ForwardBuffers B = forward_buffers(c);
+    const uint32_t n = pc->object_count;
+    const bool have_prev = c->have_pyramid && c->depth == c->depth_owned;
+    ASH_CUDA(c, launch_forward_setup(vp->camera, c->fwd_params, c->objs, n, c->lights, c->n_lights, c->W, c->H, B, c->L()));
+    c->depth = c->depth_owned; c->pyr.mip0 = c->depth;
+    // phase 1: against the previous pyramid; draw the survivors; Hi-Z of what was drawn
+    ASH_CUDA(c, launch_occlusion_cull(c->objs, c->draws_in, *pc, c->pyr, c->visibility, c->vis_bits, c->cta_counts, c->draws_out,
+                                      c->visible_count, c->stats, c->culling_stats, 1, !have_prev, nullptr, c->L()));
+    ASH_CUDA(c, launch_forward_splat(n, c->W, c->H, B, c->visibility, c->L()));
+    ASH_CUDA(c, launch_forward_resolve(c->W, c->H, B, c->L()));
+    c->have_depth = true; c->have_forward = true;
+    rc = ashcuda_hiz_build(c);
+    if (rc) return rc;
+    // phase 2: everything phase 1 rejected, against the new pyramid; draw the late objects; final depth
+    ASH_CUDA(c, launch_occlusion_cull(c->objs, c->draws_in, *pc, c->pyr, c->visibility, c->vis_bits, c->cta_counts, c->draws_out,
+                                      c->visible_count, c->stats, c->culling_stats, 2, false, c->fwd_late, c->L()));
+    ASH_CUDA(c, launch_forward_splat(n, c->W, c->H, B, c->fwd_late, c->L()));
+    ASH_CUDA(c, launch_forward_resolve(c->W, c->H, B, c->L()));
+    c->have_pyramid = false;                      // the caller rebuilds it from the final depth (ASH_STAGE_HIZ follows)
     return ASH_OK;
 }
 
@@ -745,6 +805,7 @@ int ashcuda_get(ashcuda_ctx* c, int which, void** dev_ptr, size_t* bytes) {
         case ASH_BUF_INSTANCING_STATS: p = c->inst_stats; n = sizeof(AshInstancingStats); break;
         case ASH_BUF_FORWARD_KEYS:    p = c->fwd_keys; n = P * 8; break;
         case ASH_BUF_COLOR:           p = const_cast<void*>(c->color); n = P * 8; break;
+        case ASH_BUF_CULLING_STATS:   p = c->culling_stats; n = sizeof(AshCullingStats); break;
         default: return fail(c, ASH_ERR_NOT_FOUND, "get: unknown buffer id");
     }
     if (!p) return fail(c, ASH_ERR_NOT_FOUND, "get: buffer not allocated (post chain disabled, or no instances set)");

@@ -171,10 +171,11 @@ __device__ __forceinline__ void splat_pixel(float4 s, float cc, uint32_t lb_bits
 __global__ void __launch_bounds__(256)
 k_splat_small(const float4* __restrict__ spheres, const int4* __restrict__ rects, const FwdConsts* __restrict__ consts,
               const float* __restrict__ ray_x, const float* __restrict__ ray_y, unsigned long long* __restrict__ keys,
-              int area_lo, int area_hi) {
+              int area_lo, int area_hi, const uint32_t* __restrict__ mask) {
     const FwdConsts k = *consts;
     const uint32_t id = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     if (id >= k.object_count) return;
+    if (mask && !__ldg(mask + id)) return;                 // two-phase culling: only the objects of this phase
     const int4 q = __ldg(rects + id);
     if (q.w <= area_lo || q.w > area_hi) return;
     const int x0 = q.x & 0xFFFF, x1 = (int)((uint32_t)q.x >> 16), y0 = q.y & 0xFFFF, y1 = (int)((uint32_t)q.y >> 16);
@@ -190,7 +191,8 @@ k_splat_small(const float4* __restrict__ spheres, const int4* __restrict__ rects
 __global__ void __launch_bounds__(256)
 k_splat_big(const float4* __restrict__ spheres, const int4* __restrict__ rects, const uint32_t* __restrict__ big_list,
             const uint32_t* __restrict__ big_count, const FwdConsts* __restrict__ consts,
-            const float* __restrict__ ray_x, const float* __restrict__ ray_y, unsigned long long* __restrict__ keys) {
+            const float* __restrict__ ray_x, const float* __restrict__ ray_y, unsigned long long* __restrict__ keys,
+            const uint32_t* __restrict__ mask) {
     __shared__ int4 s_q[256];
     __shared__ float4 s_s[256];
     __shared__ uint32_t s_id[256];
@@ -201,7 +203,9 @@ k_splat_big(const float4* __restrict__ spheres, const int4* __restrict__ rects, 
         __syncthreads();
         if (b0 + threadIdx.x < nb) {
             const uint32_t id = big_list[b0 + threadIdx.x];
-            s_id[threadIdx.x] = id; s_q[threadIdx.x] = __ldg(rects + id); s_s[threadIdx.x] = __ldg(spheres + id);
+            int4 q = __ldg(rects + id);
+            if (mask && !__ldg(mask + id)) q = make_int4(0, 0, 0, 0);          // not in this phase: no chunks
+            s_id[threadIdx.x] = id; s_q[threadIdx.x] = q; s_s[threadIdx.x] = __ldg(spheres + id);
         }
         __syncthreads();
         const uint32_t nloc = min(256u, nb - b0);
@@ -346,27 +350,38 @@ void forward_setup_patch(const AshCullingCameraData& cam, PatchArg* out) {      
     std::memcpy(out->value, &cam, sizeof(cam));
 }
 
-cudaError_t launch_forward_depth(const AshCullingCameraData& cam, const AshForwardParams& fp, const AshCullObjectData* objs, uint32_t n,
-                                 const AshGpuLight* lights, uint32_t n_lights, uint32_t W, uint32_t H, float4* spheres, int4* rects,
-                                 uint32_t* big_list, uint32_t* big_count, float4* lights_view, float* ray_x, float* ray_y,
-                                 void* consts, unsigned long long* keys, float* depth, const Launch& L) {
+// setup + key clear | splat (optionally only the objects whose mask is set; may be called again to add
+// objects to the same keys) | resolve keys -> depth.  One ASH_KERNEL_FORWARD_DEPTH span each.
+cudaError_t launch_forward_setup(const AshCullingCameraData& cam, const AshForwardParams& fp, const AshCullObjectData* objs, uint32_t n,
+                                 const AshGpuLight* lights, uint32_t n_lights, uint32_t W, uint32_t H, const ForwardBuffers& B, const Launch& L) {
     Timed timed(L, ASH_KERNEL_FORWARD_DEPTH);
-    cudaError_t e = cudaMemsetAsync(big_count, 0, 4, L.s);
+    cudaError_t e = cudaMemsetAsync(B.big_count, 0, 4, L.s);
     if (e != cudaSuccess) return e;
     const uint32_t span = max(max(n, n_lights), max(W, H));
     const size_t P = (size_t)W * H;
-    k_forward_setup<<<(span + 255) / 256, 256, 0, L.s>>>(cam, fp, objs, n, lights, n_lights, W, H, spheres, rects, big_list, big_count,
-                                                         lights_view, ray_x, ray_y, static_cast<FwdConsts*>(consts));
-    k_forward_clear<<<148 * 8, 256, 0, L.s>>>(reinterpret_cast<ulonglong2*>(keys), P / 2, keys, P);
-    if (n) {   // big (near) spheres first: what they cover lets the far ones skip their tests (same result in any order)
-        const FwdConsts* kc = static_cast<const FwdConsts*>(consts);
-        k_splat_big<<<148 * 4, 256, 0, L.s>>>(spheres, rects, big_list, big_count, kc, ray_x, ray_y, keys);
-        k_splat_small<<<(n + 7) / 8, 256, 0, L.s>>>(spheres, rects, kc, ray_x, ray_y, keys, kMidArea, kBigArea);
-        k_splat_small<<<(n + 7) / 8, 256, 0, L.s>>>(spheres, rects, kc, ray_x, ray_y, keys, 0, kMidArea);
-        *L.launches += 3;
-    }
-    k_forward_depth<<<148 * 8, 256, 0, L.s>>>(reinterpret_cast<const uint2*>(keys), depth, P);
+    k_forward_setup<<<(span + 255) / 256, 256, 0, L.s>>>(cam, fp, objs, n, lights, n_lights, W, H, B.spheres, B.rects, B.big_list, B.big_count,
+                                                         B.lights_view, B.ray_x, B.ray_y, static_cast<FwdConsts*>(B.consts));
+    k_forward_clear<<<148 * 8, 256, 0, L.s>>>(reinterpret_cast<ulonglong2*>(B.keys), P / 2, B.keys, P);
+    *L.launches += 1;
+    return cudaGetLastError();
+}
+
+cudaError_t launch_forward_splat(uint32_t n, uint32_t W, uint32_t H, const ForwardBuffers& B, const uint32_t* mask, const Launch& L) {
+    if (!n) return cudaSuccess;
+    Timed timed(L, ASH_KERNEL_FORWARD_DEPTH);
+    // big (near) spheres first: what they cover lets the far ones skip their tests (same result in any order)
+    const FwdConsts* kc = static_cast<const FwdConsts*>(B.consts);
+    k_splat_big<<<148 * 4, 256, 0, L.s>>>(B.spheres, B.rects, B.big_list, B.big_count, kc, B.ray_x, B.ray_y, B.keys, mask);
+    k_splat_small<<<(n + 7) / 8, 256, 0, L.s>>>(B.spheres, B.rects, kc, B.ray_x, B.ray_y, B.keys, kMidArea, kBigArea, mask);
+    k_splat_small<<<(n + 7) / 8, 256, 0, L.s>>>(B.spheres, B.rects, kc, B.ray_x, B.ray_y, B.keys, 0, kMidArea, mask);
     *L.launches += 2;
+    (void)W; (void)H;
+    return cudaGetLastError();
+}
+
+cudaError_t launch_forward_resolve(uint32_t W, uint32_t H, const ForwardBuffers& B, const Launch& L) {
+    Timed timed(L, ASH_KERNEL_FORWARD_DEPTH);
+    k_forward_depth<<<148 * 8, 256, 0, L.s>>>(reinterpret_cast<const uint2*>(B.keys), B.depth, (size_t)W * H);
     return cudaGetLastError();
 }
 

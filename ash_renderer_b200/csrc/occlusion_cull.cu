@@ -34,12 +34,20 @@ __device__ __forceinline__ int mip_from_size(float s, int hi) {
 
 __device__ __forceinline__ float4 ldg4(const void* p) { return __ldg(reinterpret_cast<const float4*>(p)); }
 
+// MODE 0: the reference dispatch.  Two-phase culling (row f-3, ashcuda_view_run with ASH_STAGE_TWO_PHASE):
+// MODE 1 = phase 1 against the PREVIOUS frame's pyramid (no_occlusion != 0 on a first frame: frustum only);
+// MODE 2 = phase 2 against the pyramid of what phase 1 drew: objects already visible stay visible untested,
+// the others are tested and the newly visible ones flagged in late[] (they are drawn, then the final
+// pyramid is built).  visibility / vis_bits / cta_counts always describe every object.
+template <int MODE>
 __global__ void __launch_bounds__(kCullThreads)
 k_occlusion_cull(const AshCullObjectData* __restrict__ objs, CullParams cp, Pyramid pyr,
                  uint32_t* __restrict__ visibility, uint32_t* __restrict__ vis_bits,
-                 uint32_t* __restrict__ cta_counts) {
+                 uint32_t* __restrict__ cta_counts, uint32_t no_occlusion, uint32_t* __restrict__ late,
+                 AshCullingStats* __restrict__ cstats) {
     __shared__ float4   s_planes[6];
     __shared__ uint32_t s_warp_cnt[kCullThreads / 32];
+    __shared__ uint32_t s_warp_aux[kCullThreads / 32];
 
     // extractFrustumPlanes, :82-100 — built from COLUMNS of viewProj, as the shader does
     if (threadIdx.x < 6) {
@@ -55,7 +63,10 @@ k_occlusion_cull(const AshCullObjectData* __restrict__ objs, CullParams cp, Pyra
 
     const uint32_t idx = blockIdx.x * kCullThreads + threadIdx.x;
     bool visible = false;
-    if (idx < cp.object_count) {
+    bool aux = false;                 // MODE 0/1: passed the frustum test; MODE 2: newly visible (late)
+    const bool early = MODE == 2 && idx < cp.object_count && visibility[idx] != 0u;
+    if (early) visible = true;
+    if (idx < cp.object_count && !early) {
         const char* o = reinterpret_cast<const char*>(objs + idx);
         const float4 tail = ldg4(o + 96);                        // drawIndex, lodBias, flags, pad
         if (__float_as_uint(tail.z) & 1u) {                      // :195-198
@@ -76,8 +87,10 @@ k_occlusion_cull(const AshCullObjectData* __restrict__ objs, CullParams cp, Pyra
                 const V3 pv = add3(wc, mul3(we, v3(gsign(n.x), gsign(n.y), gsign(n.z))));
                 if (fadd(dot3(n, pv), pl.w) < 0.0f) { culled = true; break; }
             }
+            if (MODE != 2) aux = !culled;
             // occlusionCull, :123-178
-            if (!culled) {
+            if (!culled && MODE == 1 && no_occlusion) visible = true;
+            else if (!culled) {
                 float minx = 1.0f, miny = 1.0f, maxx = 0.0f, maxy = 0.0f, minz = 1.0f;
                 bool behind = false;
 #pragma unroll
@@ -110,20 +123,28 @@ k_occlusion_cull(const AshCullObjectData* __restrict__ objs, CullParams cp, Pyra
                 }
             }
         }
+        if (MODE == 2) aux = visible;
         visibility[idx] = visible ? 1u : 0u;
     }
+    if (MODE == 2 && idx < cp.object_count) late[idx] = aux ? 1u : 0u;
     const uint32_t ballot = __ballot_sync(0xFFFFFFFFu, visible);
+    const uint32_t ballot_aux = __ballot_sync(0xFFFFFFFFu, aux);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     if (lane == 0) {
         if (blockIdx.x * kCullThreads + warp * 32 < cp.object_count) vis_bits[idx >> 5] = ballot;
         s_warp_cnt[warp] = __popc(ballot);
+        s_warp_aux[warp] = __popc(ballot_aux);
     }
     __syncthreads();
     if (threadIdx.x == 0) {
-        uint32_t c = 0;
+        uint32_t c = 0, a = 0;
 #pragma unroll
-        for (int w = 0; w < kCullThreads / 32; ++w) c += s_warp_cnt[w];
+        for (int w = 0; w < kCullThreads / 32; ++w) { c += s_warp_cnt[w]; a += s_warp_aux[w]; }
         cta_counts[blockIdx.x] = c;
+        // CullingStats (render_stats.rs:54-65): integer atomics, order independent
+        if (MODE != 2) { if (a) atomicAdd(&cstats->after_frustum, a); }
+        else if (a) atomicAdd(&cstats->late_visible, a);
+        if (MODE == 1 && c) atomicAdd(&cstats->early_visible, c);
     }
 }
 
@@ -132,7 +153,8 @@ __global__ void __launch_bounds__(kCullThreads)
 k_cull_compact(const AshCullObjectData* __restrict__ objs, const AshIndirectDrawCommand* __restrict__ draws_in,
                uint32_t object_count, const uint32_t* __restrict__ vis_bits,
                const uint32_t* __restrict__ cta_counts, AshIndirectDrawCommand* __restrict__ draws_out,
-               uint32_t* __restrict__ visible_count, AshViewStats* __restrict__ stats) {
+               uint32_t* __restrict__ visible_count, AshViewStats* __restrict__ stats,
+               AshCullingStats* __restrict__ cstats) {
     __shared__ uint32_t s_red[kCullThreads / 32];
     __shared__ uint32_t s_warp_off[kCullThreads / 32];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -165,6 +187,8 @@ k_cull_compact(const AshCullObjectData* __restrict__ objs, const AshIndirectDraw
         *visible_count = total;
         stats->total_objects = object_count;
         stats->visible_objects = total;
+        cstats->objects_submitted = object_count;         // StatsCollector::record_culling, render_stats.rs:213-217
+        cstats->after_occlusion = total;
     }
 }
 
@@ -179,31 +203,53 @@ static CullParams make_cull_params(const AshCullingPushConstants& pc) {
     return cp;
 }
 
-// graph replay: argument 1 of k_occlusion_cull is the per-view CullParams
-void cull_patch(const AshCullingPushConstants& pc, PatchArg* out) {
+// graph replay: argument 1 of k_occlusion_cull is the per-view CullParams (every mode of a captured view gets it)
+void cull_patch(const AshCullingPushConstants& pc, int mode, PatchArg* out) {
     static_assert(sizeof(CullParams) <= sizeof(out->value), "PatchArg too small");
     const CullParams cp = make_cull_params(pc);
-    out->func = reinterpret_cast<const void*>(&k_occlusion_cull);
-    out->arg_index = 1; out->n_args = 6;
+    out->func = mode == 0 ? reinterpret_cast<const void*>(&k_occlusion_cull<0>)
+              : mode == 1 ? reinterpret_cast<const void*>(&k_occlusion_cull<1>) : reinterpret_cast<const void*>(&k_occlusion_cull<2>);
+    out->arg_index = 1; out->n_args = 9;
     std::memcpy(out->value, &cp, sizeof(cp));
 }
 
+// phase: 0 = the reference dispatch + compaction; 1 = phase 1 (no compaction); 2 = phase 2 + compaction
 cudaError_t launch_occlusion_cull(const AshCullObjectData* objs, const AshIndirectDrawCommand* draws_in,
                                   const AshCullingPushConstants& pc, const Pyramid& p,
                                   uint32_t* visibility, uint32_t* vis_bits, uint32_t* cta_counts,
                                   AshIndirectDrawCommand* draws_out, uint32_t* visible_count,
-                                  AshViewStats* stats, const Launch& L) {
+                                  AshViewStats* stats, AshCullingStats* cstats, int phase, bool no_occlusion,
+                                  uint32_t* late, const Launch& L) {
     const CullParams cp = make_cull_params(pc);
     const uint32_t grid = (pc.object_count + kCullThreads - 1) / kCullThreads;
+    if (phase != 2) {
+        cudaError_t e = cudaMemsetAsync(cstats, 0, sizeof(AshCullingStats), L.s);
+        if (e != cudaSuccess) return e;
+    }
     {
         Timed timed(L, ASH_KERNEL_OCCLUSION_CULL);
-        k_occlusion_cull<<<grid, kCullThreads, 0, L.s>>>(objs, cp, p, visibility, vis_bits, cta_counts);
+        if (phase == 0) k_occlusion_cull<0><<<grid, kCullThreads, 0, L.s>>>(objs, cp, p, visibility, vis_bits, cta_counts, 0u, nullptr, cstats);
+        else if (phase == 1) k_occlusion_cull<1><<<grid, kCullThreads, 0, L.s>>>(objs, cp, p, visibility, vis_bits, cta_counts, no_occlusion ? 1u : 0u, nullptr, cstats);
+        else k_occlusion_cull<2><<<grid, kCullThreads, 0, L.s>>>(objs, cp, p, visibility, vis_bits, cta_counts, 0u, late, cstats);
     }
     cudaError_t e = cudaGetLastError();
-    if (e != cudaSuccess) return e;
+    if (e != cudaSuccess || phase == 1) return e;
     Timed timed(L, ASH_KERNEL_CULL_COMPACT);
     k_cull_compact<<<grid, kCullThreads, 0, L.s>>>(objs, draws_in, pc.object_count, vis_bits, cta_counts,
-                                                 draws_out, visible_count, stats);
+                                                 draws_out, visible_count, stats, cstats);
+    return cudaGetLastError();
+}
+
+// lights_culled and lod_triangles_saved of CullingStats from the view's other statistics (end of view_run)
+__global__ void k_culling_stats_finish(const AshViewStats* __restrict__ stats, const AshInstancingStats* __restrict__ inst_stats,
+                                       uint32_t light_count, uint32_t with_lights, AshCullingStats* __restrict__ cstats) {
+    if (with_lights) cstats->lights_culled = light_count - min(light_count, stats->candidate_lights);
+    if (inst_stats) cstats->lod_triangles_saved = inst_stats->triangles_before - inst_stats->triangles_after;   // record_lod_savings, :232-234
+}
+cudaError_t launch_culling_stats_finish(const AshViewStats* stats, const AshInstancingStats* inst_stats, uint32_t light_count,
+                                        bool with_lights, AshCullingStats* cstats, const Launch& L) {
+    k_culling_stats_finish<<<1, 1, 0, L.s>>>(stats, inst_stats, light_count, with_lights ? 1u : 0u, cstats);
+    *L.launches += 1;
     return cudaGetLastError();
 }
 

@@ -57,20 +57,22 @@ GraphKey make_key(const ashcuda_ctx* c, const AshCudaViewParams* vp) {
     k.in_halo = taa_in_halo(vp->taa) ? 1u : 0u;
     k.taa_cur = (uint32_t)c->taa_cur; k.history_valid = c->history_valid; k.taa_ran = c->taa_ran;
     k.have_color = c->have_color; k.have_depth = c->have_depth; k.have_instancing = c->have_instancing;
-    k.concurrent = c->cfg.concurrent_frontend;
+    k.concurrent = c->cfg.concurrent_frontend; k.have_pyramid = c->have_pyramid;
     k.fwd = c->fwd_params;
     return k;
 }
 
 // the per-view arguments of this view, in the order ViewGraph keeps the nodes
-struct Patches { PatchArg store, cull, taa, lod, fwd; bool has_cull, has_taa, has_lod, has_fwd; };
+struct Patches { PatchArg store, cull, cull2, taa, lod, fwd; bool has_cull, has_cull2, has_taa, has_lod, has_fwd; };
 
 void make_patches(const ashcuda_ctx* c, const AshCudaViewParams* vp, Patches* P) {
     const uint32_t st = vp->stages;
     P->has_cull = (st & ASH_STAGE_CULL) && vp->cull.object_count > 0;
     P->has_taa = (st & ASH_STAGE_TAA) != 0;
     P->has_lod = (st & ASH_STAGE_INSTANCING) && vp->cull.object_count > 0;
-    if (P->has_cull) cull_patch(vp->cull, &P->cull);
+    P->has_cull2 = P->has_cull && (st & ASH_STAGE_TWO_PHASE);
+    if (P->has_cull) cull_patch(vp->cull, P->has_cull2 ? 1 : 0, &P->cull);
+    if (P->has_cull2) cull_patch(vp->cull, 2, &P->cull2);
     if (P->has_taa) taa_pair_patch((st & ASH_STAGE_BLOOM) != 0, c->velocity != nullptr && !(st & ASH_STAGE_FORWARD_SHADE), vp->taa, &P->taa);
     if (P->has_lod) {
         AshInstancingParams ip{};
@@ -182,6 +184,7 @@ int ash_view_run_graph(ashcuda_ctx* c, const AshCudaViewParams* vp, bool* handle
         // ---- capture: run the eager body once into a graph (nothing executes yet)
         drop(g);
         if (cudaSetDevice(c->device) != cudaSuccess) return ASH_OK;
+        if ((st & ASH_STAGE_FORWARD_DEPTH) && ash_forward_alloc(c) != ASH_OK) return ASH_OK;   // lazy buffers: not inside a capture
         const StateSnap s0 = snap(c);
         if (cudaStreamBeginCapture(c->stream, cudaStreamCaptureModeThreadLocal) != cudaSuccess) { cudaGetLastError(); c->graphs_broken = true; return ASH_OK; }
         const int rc = ash_view_run_eager(c, vp);
@@ -193,6 +196,7 @@ int ash_view_run_graph(ashcuda_ctx* c, const AshCudaViewParams* vp, bool* handle
             ok = cudaGraphInstantiate(&g.exec, g.graph, 0) == cudaSuccess;
             ok = ok && find_node(g.graph, P.store.func, &g.n_store) == cudaSuccess;
             if (ok && P.has_cull) ok = find_node(g.graph, P.cull.func, &g.n_cull) == cudaSuccess;
+            if (ok && P.has_cull2) ok = find_node(g.graph, P.cull2.func, &g.n_cull2) == cudaSuccess;
             if (ok && P.has_taa) ok = find_node(g.graph, P.taa.func, &g.n_taa) == cudaSuccess;     // absent: TAA taps not exact
             if (ok && P.has_lod) ok = find_node(g.graph, P.lod.func, &g.n_lod) == cudaSuccess;
             if (ok && P.has_fwd) ok = find_node(g.graph, P.fwd.func, &g.n_fwd) == cudaSuccess;
@@ -231,6 +235,7 @@ int ash_view_run_graph(ashcuda_ctx* c, const AshCudaViewParams* vp, bool* handle
     uint32_t with_camera = (st & ASH_STAGE_LIGHTS) ? 1u : 0u, view_id = vp->view_id;
     ASH_CUDA(c, patch_node(g, g.n_store, P.store.n_args, 0, &cam, 1, &with_camera, 2, &view_id));
     if (P.has_cull) ASH_CUDA(c, patch_node(g, g.n_cull, P.cull.n_args, P.cull.arg_index, P.cull.value));
+    if (P.has_cull2) ASH_CUDA(c, patch_node(g, g.n_cull2, P.cull2.n_args, P.cull2.arg_index, P.cull2.value));
     if (P.has_taa) ASH_CUDA(c, patch_node(g, g.n_taa, P.taa.n_args, P.taa.arg_index, P.taa.value));
     if (P.has_lod) ASH_CUDA(c, patch_node(g, g.n_lod, P.lod.n_args, P.lod.arg_index, P.lod.value));
     if (P.has_fwd) ASH_CUDA(c, patch_node(g, g.n_fwd, P.fwd.n_args, P.fwd.arg_index, P.fwd.value));

@@ -68,6 +68,11 @@ FORWARD_PARAMS = np.dtype([("light_direction", "<f4", 4), ("light_color", "<f4",
 assert FORWARD_PARAMS.itemsize == 128
 FWD_TILE_LIGHTS, FWD_REINHARD, FWD_INSTANCE_COLOR = 1, 2, 4
 FWD_NO_OBJECT = 0xFFFFFFFF
+# CullingStats (render_stats.rs:54-65) + the early / late split of two-phase culling (AshCullingStats)
+CULLING_STATS = np.dtype([("objects_submitted", "<u4"), ("after_frustum", "<u4"), ("after_occlusion", "<u4"),
+                          ("lights_culled", "<u4"), ("lod_triangles_saved", "<u8"), ("early_visible", "<u4"),
+                          ("late_visible", "<u4")])
+assert CULLING_STATS.itemsize == 32
 
 assert CULL_OBJECT.itemsize == 112 and DRAW_COMMAND.itemsize == 20 and CULLING_PC.itemsize == 96
 assert GPU_LIGHT.itemsize == 64 and LIGHT_PC.itemsize == 16 and CAMERA_DATA.itemsize == 208
@@ -84,12 +89,13 @@ STAGE_ALL = 0x3F
 STAGE_KEEP_BLOOM = 0x40
 STAGE_INSTANCING = 0x80
 STAGE_FORWARD_DEPTH, STAGE_FORWARD_SHADE = 0x100, 0x200
+STAGE_TWO_PHASE = 0x400
 
 BUF_VISIBILITY, BUF_DRAWS_OUT, BUF_VISIBLE_COUNT, BUF_TILE_DATA = 1, 2, 3, 4
 BUF_TAA_OUT, BUF_LDR8, BUF_STATS, BUF_TILE_MINMAX, BUF_VISIBILITY_BITS = 5, 6, 7, 8, 9
 BUF_BLOOM_THRESHOLD = 10
 BUF_LOD_SELECTION, BUF_INSTANCES_OUT, BUF_BUCKET_OFFSETS, BUF_INSTANCE_DRAWS, BUF_INSTANCING_STATS = 11, 12, 13, 14, 15
-BUF_FORWARD_KEYS, BUF_COLOR = 16, 17
+BUF_FORWARD_KEYS, BUF_COLOR, BUF_CULLING_STATS = 16, 17, 18
 
 
 def BUF_HIZ_MIP(i):

@@ -325,6 +325,8 @@ def run_cuda(args):
         if args.forward:
             c.set_forward_params(fwd_params)
             vparams["stages"] |= T.STAGE_FORWARD_DEPTH | T.STAGE_FORWARD_SHADE
+            if args.two_phase:
+                vparams["stages"] |= T.STAGE_TWO_PHASE
         slot = {"ctx": c, "vp": vparams,
                 "d_depth": torch.from_numpy(depth).cuda(), "d_hdr": torch.from_numpy(hdr.view(np.uint16)).cuda(),
                 "h_depth": torch.from_numpy(depth).pin_memory(), "h_hdr": torch.from_numpy(hdr.view(np.uint16)).pin_memory()}
@@ -456,6 +458,8 @@ def run_cuda(args):
         widened = dict(widened or {})
         widened.update({"row_f1": "depth + HDR colour produced on the device: occluder-sphere ray cast + tiled-forward Cook-Torrance shading "
                                   "(frag.frag BRDF) over the tile light lists; no per-view host upload",
+                        "two_phase_culling": bool(args.two_phase),
+                        "culling_stats": {k: int(slots[0]["ctx"].culling_stats()[k]) for k in T.CULLING_STATS.names},
                         "occluders": n_objs, "covered_fraction": float(((keys0 & np.uint64(0xFFFFFFFF)) != np.uint64(0xFFFFFFFF)).mean())})
         if world == 1 and args.cpu_views > 0:     # the CPU oracle of the same two stages on view 0 (serial splat, OpenMP shade)
             from oracle import oracle as O
@@ -466,7 +470,8 @@ def run_cuda(args):
             O.forward_shade(k0, objs, lights, slots[0]["ctx"].tile_data(), cam0.camera_data(), fwd_params)
             widened["cpu_forward_depth_ms"] = (t1 - t0) * 1e3
             widened["cpu_forward_shade_ms"] = (time.perf_counter() - t1) * 1e3
-            widened["forward_depth_keys_equal_oracle"] = bool(np.array_equal(k0, keys0))
+            if not args.two_phase:            # (two-phase draws only the visible objects: a different, history-dependent image)
+                widened["forward_depth_keys_equal_oracle"] = bool(np.array_equal(k0, keys0))
 
     # ---- end-to-end through host buffers
     e2e_ms = timed(step_e2e, args.steps, 2)
@@ -527,6 +532,7 @@ def run_cuda(args):
         "dtype": "f32", "data": "synthetic",
         "config": {"workload": workload_name() + (" + LOD selection / instance batching (--instancing)" if inst_scene else "")
                    + (" with depth + HDR colour produced on the device by the compute forward pass (--forward, row f-1)" if args.forward else "")
+                   + (" + two-phase occlusion culling (--two-phase, row f-3)" if args.two_phase else "")
                    + (" + per-pixel velocity buffer in the TAA (--velocity; resident passes only)" if args.velocity else ""),
                    "views_per_gpu_per_step": B, "distinct_view_inputs_per_gpu": distinct,
                    "streams": args.streams, "concurrent_frontend": True,
@@ -588,12 +594,17 @@ def main():
     ap.add_argument("--forward", action="store_true",
                     help="widened path (SURVEY 8.6 row f-1): depth and HDR colour are produced on the device from the cull objects "
                          "and the tile light lists instead of being uploaded; not the headline workload")
+    ap.add_argument("--two-phase", action="store_true",
+                    help="with --forward (row f-3): two-phase occlusion culling around the device rasteriser, phase 1 against the "
+                         "previous step's Hi-Z pyramid of the same view slot")
     ap.add_argument("--velocity", action="store_true",
                     help="supply a per-pixel RG16F velocity buffer to the TAA (the headline workload has none, PIN-12)")
     ap.add_argument("--instancing", action="store_true",
                     help="widened path (SURVEY 8.6 row f-2): also run LOD selection + instance batching after the cull; "
                          "not part of the headline workload, reported under \"widened\"")
     args = ap.parse_args()
+    if args.two_phase and not args.forward:
+        ap.error("--two-phase needs --forward")
     if args.impl == "reference":
         run_reference(args)
     else:

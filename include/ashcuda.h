@@ -255,6 +255,18 @@ typedef struct AshViewStats {
     uint32_t candidate_lights; /* lights surviving the per-view depth-slab prefilter */
 } AshViewStats;
 
+/* CullingStats (render_stats.rs:54-65) as StatsCollector::record_culling / record_lod_savings (:213-234) would
+ * fill it, plus the early / late split of two-phase culling.  ASH_BUF_CULLING_STATS. */
+typedef struct AshCullingStats {
+    uint32_t objects_submitted;
+    uint32_t after_frustum;
+    uint32_t after_occlusion;
+    uint32_t lights_culled;        /* lights no tile of this view can see (light_count - candidates); view_run only */
+    uint64_t lod_triangles_saved;  /* LodStats triangles_before - triangles_after; view_run with ASH_STAGE_INSTANCING */
+    uint32_t early_visible;        /* two-phase: visible against the previous frame's pyramid */
+    uint32_t late_visible;         /* two-phase: newly visible against the pyramid of what phase 1 drew */
+} AshCullingStats;
+
 /* Everything that changes per view-frame, for ashcuda_view_run. */
 typedef struct AshCudaViewParams {
     AshCullingPushConstants      cull;
@@ -278,6 +290,9 @@ typedef struct AshCudaViewParams {
 #define ASH_STAGE_INSTANCING 0x80u /* after the cull: LOD selection + instance batching (not part of ASH_STAGE_ALL) */
 #define ASH_STAGE_FORWARD_DEPTH 0x100u /* before Hi-Z: depth buffer from the cull objects' occluder spheres (f-1)       */
 #define ASH_STAGE_FORWARD_SHADE 0x200u /* after the light cull: HDR colour from the tile light lists (f-1, f-2)         */
+#define ASH_STAGE_TWO_PHASE 0x400u /* with FORWARD_DEPTH | HIZ | CULL (row f-3): phase 1 culls against the pyramid the previous
+                                      view left, its survivors are drawn, Hi-Z is rebuilt, phase 2 tests the rest and draws the
+                                      newly visible ("late") objects; visibility = early | late, final pyramid from both       */
 #define ASH_STAGE_KEEP_BLOOM 0x40u /* view_run: also store the bloom buffer U_0 (the fused last upsample +
                                       tonemap otherwise never writes it; ASH_BUF_BLOOM_MIP(0) then holds D_0) */
 
@@ -300,6 +315,7 @@ typedef struct AshCudaViewParams {
 #define ASH_BUF_INSTANCE_DRAWS 14 /* AshIndirectDrawCommand[max_batches*8]: one per bucket      */
 #define ASH_BUF_INSTANCING_STATS 15 /* AshInstancingStats                                        */
 #define ASH_BUF_FORWARD_KEYS   16 /* u64 W x H: (depth bits << 32) | object index, ASH_FWD_NO_OBJECT where none */
+#define ASH_BUF_CULLING_STATS  18 /* AshCullingStats                                                              */
 #define ASH_BUF_COLOR          17 /* RGBA16F W x H: the current HDR colour input (set_color / forward_shade)    */
 
 /* Kernel classes for ashcuda_profile_kernels / ashcuda_kernel_time_ms (device-time accounting;

@@ -160,16 +160,19 @@ extern "C" {
 // keys[y*W + x] = (depth bits << 32) | object index of the nearest hit (lowest index on equal depth),
 // (bits(1.0f) << 32) | ASH_FWD_NO_OBJECT where nothing is hit; depth[] = the high halves as floats.
 // brute != 0 tests every pixel against every sphere instead of the silhouette rectangle (tests only).
+// mask (or NULL): only objects with mask[i] != 0 are drawn; accumulate != 0: keys[] already holds earlier
+// draws of the same view (two-phase culling draws the late objects on top of the early ones).
 void ash_oracle_forward_depth(const AshCullObjectData* objs, uint32_t n, const AshCullingCameraData* cam,
                               const AshForwardParams* fp, uint32_t W, uint32_t H, int brute,
-                              uint64_t* keys, float* depth) {
+                              const uint32_t* mask, int accumulate, uint64_t* keys, float* depth) {
     const size_t P = (size_t)W * H;
     const uint64_t clear = ((uint64_t)fbits(1.0f) << 32) | ASH_FWD_NO_OBJECT;
-    for (size_t i = 0; i < P; ++i) keys[i] = clear;
+    if (!accumulate) for (size_t i = 0; i < P; ++i) keys[i] = clear;
     std::vector<float> rx(W), ry(H);
     for (uint32_t x = 0; x < W; ++x) rx[x] = ray_coord((int)x, (int)W, cam->projection[0][0]);
     for (uint32_t y = 0; y < H; ++y) ry[y] = ray_coord((int)y, (int)H, cam->projection[1][1]);
     for (uint32_t i = 0; i < n; ++i) {
+        if (mask && !mask[i]) continue;
         const Sphere s = sphere_of(objs[i], *cam, fp->radius_scale);
         Rect q = rect_of(s, *cam, fp->near_plane, (int)W, (int)H);
         if (brute && s.r > 0.0f) q = {0, 0, (int)W, (int)H};

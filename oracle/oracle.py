@@ -258,17 +258,40 @@ FORWARD_PARAMS_DTYPE = np.dtype([("light_direction", "<f4", 4), ("light_color", 
                                  ("_padding", "<u4")])
 
 
-def forward_depth(objs, cam, fp, W, H, brute=False):
+def forward_depth(objs, cam, fp, W, H, brute=False, mask=None, keys_in=None):
     """Nearest occluder-sphere hit per pixel: (keys u64 HxW, depth f32 HxW).  brute=True tests every pixel
-    against every sphere (no silhouette rectangle): the check that the rectangle is conservative."""
+    against every sphere (no silhouette rectangle): the check that the rectangle is conservative.
+    mask: draw only these objects; keys_in: draw on top of an earlier pass of the same view (two-phase culling)."""
     o, c, p = _c(objs, OBJECT_DTYPE), _c(cam, CAMERA_DTYPE), _c(fp, FORWARD_PARAMS_DTYPE)
-    keys = np.zeros((H, W), np.uint64)
+    keys = np.zeros((H, W), np.uint64) if keys_in is None else np.ascontiguousarray(keys_in, np.uint64).copy()
     depth = np.zeros((H, W), np.float32)
+    m = None if mask is None else _c(mask, np.uint32)
     f = lib().ash_oracle_forward_depth
     f.restype = None
-    f.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_int, C.c_void_p, C.c_void_p]
-    f(_p(o), len(o.reshape(-1)), _p(c), _p(p), W, H, int(bool(brute)), _p(keys), _p(depth))
+    f.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_int, C.c_void_p, C.c_int,
+                  C.c_void_p, C.c_void_p]
+    f(_p(o), len(o.reshape(-1)), _p(c), _p(p), W, H, int(bool(brute)), None if m is None else _p(m), int(keys_in is not None),
+      _p(keys), _p(depth))
     return keys, depth
+
+
+def two_phase_cull(objs, draws, cull_pc, cam, fp, W, H, prev_depth=None):
+    """Row f-3, the procedure of ashcuda_view_run with ASH_STAGE_TWO_PHASE, from the single-phase oracle pieces:
+    phase 1 = occlusion_cull against the previous frame's depth pyramid (a first frame has none: a far-plane
+    depth buffer occludes nothing, leaving the frustum test); draw its survivors; phase 2 = occlusion_cull of
+    the rest against the pyramid of that depth; draw the late objects.  Returns a dict."""
+    n = int(np.asarray(cull_pc).reshape(-1)[0]["object_count"])
+    d0 = np.ones((H, W), np.float32) if prev_depth is None else prev_depth
+    vis1, _, early = occlusion_cull(objs, draws, cull_pc, d0)
+    keys, depth1 = forward_depth(objs[:n], cam, fp, W, H, mask=vis1)
+    vis_a, _, _ = occlusion_cull(objs, draws, cull_pc, depth1)
+    late = (vis_a != 0) & (vis1 == 0)
+    vis = ((vis1 != 0) | late).astype(np.uint32)
+    keys, depth = forward_depth(objs[:n], cam, fp, W, H, mask=late.astype(np.uint32), keys_in=keys)
+    o = _c(objs, OBJECT_DTYPE).reshape(-1)[:n]
+    draws_out = _c(draws, DRAW_DTYPE).reshape(-1)[o["draw_index"][vis != 0]]
+    return dict(visibility=vis, late=late.astype(np.uint32), early_count=int(early), late_count=int(late.sum()),
+                count=int(vis.sum()), draws_out=draws_out, keys=keys, depth=depth, depth_phase1=depth1)
 
 
 def forward_shade(keys, objs, lights, tile_data, cam, fp, instances=None):

@@ -62,6 +62,13 @@ const _: () = assert!(std::mem::size_of::<AshForwardParams>() == 128);
 pub const ASH_FWD_TILE_LIGHTS: u32 = 1;
 pub const ASH_FWD_REINHARD: u32 = 2;
 pub const ASH_FWD_INSTANCE_COLOR: u32 = 4;
+/// CullingStats (render_stats.rs:54-65) + early / late counts of two-phase culling
+#[repr(C)] #[derive(Clone, Copy, Default)]
+pub struct AshCullingStats { pub objects_submitted: u32, pub after_frustum: u32, pub after_occlusion: u32, pub lights_culled: u32,
+                             pub lod_triangles_saved: u64, pub early_visible: u32, pub late_visible: u32 }
+const _: () = assert!(std::mem::size_of::<AshCullingStats>() == 32);
+pub const ASH_STAGE_TWO_PHASE: u32 = 0x400;
+pub const ASH_BUF_CULLING_STATS: c_int = 18;
 pub const ASH_STAGE_FORWARD_DEPTH: u32 = 0x100;
 pub const ASH_STAGE_FORWARD_SHADE: u32 = 0x200;
 pub const ASH_BUF_FORWARD_KEYS: c_int = 16;

@@ -73,6 +73,7 @@ def test_header_struct_sizes_compile(tmp_path):
                    "_Static_assert(sizeof(AshInstancingStats)==72,\"\");\n"
                    "_Static_assert(sizeof(AshInstancingParams)==96,\"\");\n"
                    "_Static_assert(sizeof(AshForwardParams)==128,\"\");\n"
+                   "_Static_assert(sizeof(AshCullingStats)==32,\"\");\n"
                    f"_Static_assert(sizeof(AshCudaViewParams)=={T.VIEW_PARAMS.itemsize},\"\");\n"
                    "int main(void){return 0;}\n")
     subprocess.run(["/usr/bin/gcc", "-std=c11", "-I", os.path.join(ROOT, "include"), "-c", str(src),

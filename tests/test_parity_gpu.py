@@ -535,6 +535,82 @@ def test_view_run_post_chain_with_velocity_buffer(backend, oracle):
             hist = ref
 
 
+# ------------------------------------------------------------------ row f-3: two-phase culling + CullingStats
+@pytest.mark.parametrize("graph", [0, 1])
+def test_two_phase_culling_matches_oracle_procedure(backend, oracle, graph):
+    """Phase 1 against the previous view's pyramid, draw, Hi-Z, phase 2 for the rest, draw the late objects:
+    visibility, ordered draws, keys, final depth and CullingStats against the same procedure built from the
+    single-phase oracle pieces, over a camera path (first view: no previous pyramid)."""
+    W, H, levels = 512, 256, 8
+    objs, draws = synth.make_objects((12, 8, 10), spacing=2.0, seed=61, jitter=0.3, disabled_frac=0.05)
+    objs["model"][:, 0, 0] *= 1.5; objs["model"][:, 1, 1] *= 1.5; objs["model"][:, 2, 2] *= 1.5      # bigger spheres: real occlusion
+    lights = synth.make_lights(64, extent=10.0, seed=62, center=(0.0, 2.0, 4.0))
+    fp = synth.forward_params(near=0.5, flags=0)
+    stages = T.STAGE_HIZ | T.STAGE_CULL | T.STAGE_LIGHTS | T.STAGE_FORWARD_DEPTH | T.STAGE_TWO_PHASE
+    prev_depth = None
+    late_total = 0
+    with _ctx(backend, W, H, enable_post=0, graph_replay=graph) as c:
+        c.set_objects(objs, draws)
+        c.upload_lights(lights)
+        c.set_forward_params(fp)
+        for t in range(6):
+            cam = synth.Camera((2.5 * t - 6.0, 1.0 + 0.5 * t, 26.0 - 1.5 * t), (0.5 * t, 0, 0), W, H, near=0.5)
+            pc = cam.cull_pc(len(objs), levels)
+            ref = oracle.two_phase_cull(objs, draws, pc, cam.camera_data(), fp, W, H, prev_depth)
+            vp = _view_params(cam, len(objs), len(lights), levels, W, H, _taa_pc(W, H), stages=stages, view_id=t)
+            c.view_run(vp)
+            assert np.array_equal(c.visibility(), ref["visibility"]), f"view {t}: visibility"
+            assert c.visible_count() == ref["count"]
+            assert np.array_equal(c.draws_out(ref["count"]), ref["draws_out"]), f"view {t}: draws"
+            assert np.array_equal(c.forward_keys(), ref["keys"]), f"view {t}: keys"
+            assert np.array_equal(c.depth().view(np.uint32), ref["depth"].view(np.uint32)), f"view {t}: depth"
+            cs = c.culling_stats()
+            _, _, after_frustum = oracle.occlusion_cull(objs, draws, pc, np.ones((H, W), np.float32))
+            assert int(cs["objects_submitted"]) == len(objs) and int(cs["after_frustum"]) == after_frustum
+            assert int(cs["early_visible"]) == ref["early_count"] and int(cs["late_visible"]) == ref["late_count"]
+            assert int(cs["after_occlusion"]) == ref["count"] == ref["early_count"] + ref["late_count"]
+            assert int(cs["lights_culled"]) == len(lights) - int(c.stats()["candidate_lights"])
+            if t == 0:
+                assert ref["early_count"] == after_frustum and ref["late_count"] == 0      # first view: frustum only
+            late_total += ref["late_count"]
+            # the light cull of the same view saw the final depth
+            td, _, _ = oracle.light_cull(lights, cam.light_pc(len(lights)), cam.camera_data(), ref["depth"])
+            _compare_tile_lists(c.tile_data(), td)
+            prev_depth = ref["depth"]
+        assert late_total > 0, "the camera path never produced a late object: the test scene is too easy"
+        cap, rep = c.graph_stats()
+        assert ((cap == 2 and rep == 4) if graph else (cap == 0 and rep == 0)), (cap, rep)
+
+
+def test_culling_stats_single_phase_with_instancing(backend, oracle):
+    from ash_renderer_b200 import host
+    W, H, n_batches = 640, 360, 4
+    cam, objs, draws, depth, meshes, inst, batch, mesh = _instancing_scene(W, H, (12, 10, 8), seed=71, n_batches=n_batches)
+    lights = synth.make_lights(200, extent=10.0, seed=72, center=(0.0, 2.0, 22.0))
+    n = len(objs)
+    pc = cam.cull_pc(n, 9)
+    _, _, after_frustum = oracle.occlusion_cull(objs, draws, pc, np.ones((H, W), np.float32))
+    _, _, cnt = oracle.occlusion_cull(objs, draws, pc, depth)
+    vp = _view_params(cam, n, len(lights), 9, W, H, _taa_pc(W, H), stages=T.STAGE_HIZ | T.STAGE_CULL | T.STAGE_LIGHTS | T.STAGE_INSTANCING)
+    with _ctx(backend, W, H, enable_post=0, max_batches=n_batches) as c:
+        c.set_depth(depth)
+        c.set_objects(objs, draws)
+        c.upload_lights(lights)
+        c.set_instances(inst, batch, mesh)
+        c.set_lod_meshes(meshes)
+        c.set_lod_config(host.LodConfig().record(use_visibility=True))
+        c.view_run(vp)
+        cs, ist = c.culling_stats(), c.instancing_stats()
+        assert (int(cs["objects_submitted"]), int(cs["after_frustum"]), int(cs["after_occlusion"])) == (n, after_frustum, cnt)
+        assert int(cs["lights_culled"]) == len(lights) - int(c.stats()["candidate_lights"])
+        assert int(cs["lod_triangles_saved"]) == int(ist["triangles_before"]) - int(ist["triangles_after"]) > 0
+        assert int(cs["early_visible"]) == 0 and int(cs["late_visible"]) == 0
+        # the staged call fills the cull's own fields too
+        c.occlusion_cull(pc)
+        cs = c.culling_stats()
+        assert (int(cs["objects_submitted"]), int(cs["after_frustum"]), int(cs["after_occlusion"])) == (n, after_frustum, cnt)
+
+
 # ------------------------------------------------------------------ row f-1: depth / HDR producers
 def _forward_scene(W, H, eye, target, grid, seed, n_lights=200, **fpkw):
     cam = synth.Camera(eye, target, W, H, near=0.5)
