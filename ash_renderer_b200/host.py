@@ -67,6 +67,39 @@ class OcclusionStats:
                 f"({self.cull_rate() * 100.0:.1f}% culled), {self.draws_culled} draws saved")
 
 
+class CullingStats:
+    """render_stats.rs:54-65"""
+
+    def __init__(self):
+        self.objects_submitted = 0
+        self.after_frustum = 0
+        self.after_occlusion = 0
+        self.lights_culled = 0
+        self.lod_triangles_saved = 0
+
+
+class StatsCollector:
+    """The culling part of render_stats.rs:132-240 (record_culling :213-217, record_lod_savings :232-234)."""
+
+    def __init__(self):
+        self.culling = CullingStats()
+
+    def record_culling(self, submitted, after_frustum, after_occlusion):
+        self.culling.objects_submitted = int(submitted)
+        self.culling.after_frustum = int(after_frustum)
+        self.culling.after_occlusion = int(after_occlusion)
+
+    def record_lod_savings(self, triangles_saved):
+        self.culling.lod_triangles_saved = int(triangles_saved)
+
+    def record_device(self, cs):
+        """Feed one AshCullingStats record (Context.culling_stats()) through the reference's recorders."""
+        self.record_culling(cs["objects_submitted"], cs["after_frustum"], cs["after_occlusion"])
+        self.record_lod_savings(cs["lod_triangles_saved"])
+        self.culling.lights_culled = int(cs["lights_culled"])
+        return self.culling
+
+
 class OcclusionCulling:
     """CPU-side state of the cull pass (occlusion_culling.rs:188-272)."""
 

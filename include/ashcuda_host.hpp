@@ -505,6 +505,15 @@ struct FrameInputs {
     uint32_t     view_id = 0;
 };
 
+struct CullingStats { uint32_t objects_submitted = 0, after_frustum = 0, after_occlusion = 0, lights_culled = 0; uint64_t lod_triangles_saved = 0; };   // render_stats.rs:54-65
+struct StatsCollector {                              // the culling part of render_stats.rs:132-240
+    CullingStats culling;
+    void record_culling(uint32_t submitted, uint32_t after_frustum, uint32_t after_occlusion) {      // :213-217
+        culling.objects_submitted = submitted; culling.after_frustum = after_frustum; culling.after_occlusion = after_occlusion;
+    }
+    void record_lod_savings(uint64_t triangles_saved) { culling.lod_triangles_saved = triangles_saved; }   // :232-234
+};
+
 class CudaComputeFeature : public RenderFeature {
 public:
     CudaComputeFeature(uint32_t width, uint32_t height, size_t max_objects = MAX_CULLABLE_OBJECTS,
@@ -621,6 +630,15 @@ public:
         uint32_t n = 0;
         if (ctx_ && check(ashcuda_readback(ctx_, ASH_BUF_VISIBLE_COUNT, &n, 4), "readback")) culling.update_stats(n);
         return n;
+    }
+    // CullingStats through the reference's recorders (render_stats.rs:213-234); syncs the stream
+    bool read_culling_stats(StatsCollector* sc) {
+        AshCullingStats cs{};
+        if (!ctx_ || !check(ashcuda_readback(ctx_, ASH_BUF_CULLING_STATS, &cs, sizeof(cs)), "readback")) return false;
+        sc->record_culling(cs.objects_submitted, cs.after_frustum, cs.after_occlusion);
+        sc->record_lod_savings(cs.lod_triangles_saved);
+        sc->culling.lights_culled = cs.lights_culled;
+        return true;
     }
     // LodStats + InstancingStats of the last frame (syncs the stream)
     bool read_instancing_stats(AshInstancingStats* out) { return ctx_ && check(ashcuda_readback(ctx_, ASH_BUF_INSTANCING_STATS, out, sizeof(*out)), "readback"); }

@@ -161,6 +161,8 @@ int main(int argc, char** argv) {
     CHECK(vis > 0 && vis <= 64 && f.culling.stats().total_objects == 64);
     AshInstancingStats ist{};
     CHECK(f.read_instancing_stats(&ist) && ist.total_instances + ist.objects_culled == vis && ist.batch_count <= 2 && ist.triangles_before == 1000ull * vis);
+    StatsCollector sc;
+    CHECK(f.read_culling_stats(&sc) && sc.culling.objects_submitted == 64 && sc.culling.after_occlusion == vis && sc.culling.after_frustum >= vis);
     std::vector<uint8_t> ldr((size_t)W * H * 4);
     CHECK(ashcuda_readback(f.context(), ASH_BUF_LDR8, ldr.data(), ldr.size()) == ASH_OK && ldr[3] == 255 && ldr[0] > 0);
     // row f-1: the same frame with depth and HDR colour produced on the device (no FrameInputs buffers)

@@ -605,6 +605,8 @@ def test_culling_stats_single_phase_with_instancing(backend, oracle):
         assert int(cs["lights_culled"]) == len(lights) - int(c.stats()["candidate_lights"])
         assert int(cs["lod_triangles_saved"]) == int(ist["triangles_before"]) - int(ist["triangles_after"]) > 0
         assert int(cs["early_visible"]) == 0 and int(cs["late_visible"]) == 0
+        rec = host.StatsCollector().record_device(cs)            # StatsCollector::record_culling / record_lod_savings
+        assert (rec.objects_submitted, rec.after_frustum, rec.after_occlusion) == (n, after_frustum, cnt) and rec.lod_triangles_saved > 0
         # the staged call fills the cull's own fields too
         c.occlusion_cull(pc)
         cs = c.culling_stats()
