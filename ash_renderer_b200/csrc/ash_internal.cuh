@@ -273,6 +273,11 @@ cudaError_t launch_bloom_upsample_fast(const void* src, uint32_t sw, uint32_t sh
 cudaError_t launch_upsample_tonemap_fast(const void* src, uint32_t sw, uint32_t sh, void* dst, float intensity,
                                          const void* hdr, void* ldr8, const AshPostProcessPushConstants& pc,
                                          bool store_u, const Launch& L);
+// post_up_pair.cu: the same two kernels with two source texels per thread on the packed fp32 pipe
+bool upsample_pair_applies(uint32_t sw, uint32_t sh);
+cudaError_t launch_upsample_pair(const void* src, uint32_t sw, uint32_t sh, void* dst, float intensity, cudaStream_t s);
+cudaError_t launch_upsample_tonemap_pair(const void* src, uint32_t sw, uint32_t sh, void* dst, float intensity, const void* hdr,
+                                         void* ldr8, const AshPostProcessPushConstants& pc, bool store_u, cudaStream_t s);
 cudaError_t launch_tonemap_fast(const void* hdr, const void* bloom_or_null, void* ldr8, uint32_t W, uint32_t H,
                                 const AshPostProcessPushConstants& pc, const Launch& L);
 // ---- exact-tap validation (exact_taps.cu), host side, O(n) per axis

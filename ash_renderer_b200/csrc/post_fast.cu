@@ -261,9 +261,7 @@ cudaError_t launch_bloom_downsample_fast(const void* src, uint32_t sw, uint32_t 
 // m = -2..2 (in units of d = half a source texel): window column (origin i-2) c0 and weight g:
 //   c0 = floor((2p - 1 + 2m) / 4) + 2,   g = ((2p - 1 + 2m) mod 4) / 4  in {1/4, 3/4}.
 // =====================================================================================================
-__host__ __device__ constexpr int up_fd4(int q) { return q >= 0 ? q / 4 : -((-q + 3) / 4); }
-__host__ __device__ constexpr int up_c0(int p, int m) { return up_fd4(2 * p - 1 + 2 * m) + 2; }
-__host__ __device__ constexpr bool up_g75(int p, int m) { return (2 * p - 1 + 2 * m) - 4 * up_fd4(2 * p - 1 + 2 * m) == 3; }
+// (up_fd4 / up_c0 / up_g75: post_math.cuh)
 
 // 4 * lerp(a, b, g): g = 3/4 -> a + 3b ; g = 1/4 -> 3a + b   (3 * fp16 texel is exact)
 template <bool G75>
@@ -416,14 +414,7 @@ k_upsample_fast(const uint2* __restrict__ src, int sw, int sh, uint2* __restrict
 // destination / HDR blocks of tile n+1 are fetched with cp.async into the other shared-memory buffer
 // while tile n is computed, so the load latency that the one-shot kernel exposes at the top of every
 // CTA (ncu: 52 % issue-active, long-scoreboard bound) is hidden behind arithmetic.
-__device__ __forceinline__ void cp_async8(void* smem, const void* gmem) {
-    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" :: "r"((uint32_t)__cvta_generic_to_shared(smem)), "l"(gmem));
-}
-__device__ __forceinline__ void cp_async16(void* smem, const void* gmem) {
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" :: "r"((uint32_t)__cvta_generic_to_shared(smem)), "l"(gmem));
-}
-__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
-template <int N> __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" :: "n"(N) : "memory"); }
+// (cp_async8 / cp_async16 / cp_async_commit / cp_async_wait: post_math.cuh)
 
 template <bool TONEMAP>
 struct UpTile {
@@ -529,10 +520,14 @@ static cudaError_t launch_upsample_pipe(const void* src, uint32_t sw, uint32_t s
 #ifndef ASH_UPS_PIPE
 #define ASH_UPS_PIPE 1
 #endif
+#ifndef ASH_UPS_PAIR          // two source texels per thread on the packed fp32 pipe (post_up_pair.cu)
+#define ASH_UPS_PAIR 1
+#endif
 cudaError_t launch_bloom_upsample_fast(const void* src, uint32_t sw, uint32_t sh, void* dst, float intensity,
                                        const Launch& L) {
     const dim3 grid((sw + 15) / 16, (sh + 15) / 16);
     Timed timed(L, ASH_KERNEL_BLOOM_UPSAMPLE);
+    if (ASH_UPS_PAIR && upsample_pair_applies(sw, sh)) return launch_upsample_pair(src, sw, sh, dst, intensity, L.s);
     if (ASH_UPS_PIPE && grid.x * grid.y >= 148u * ASH_UPS_PIPE_MINB * 2u)
         return launch_upsample_pipe<false, true>(src, sw, sh, dst, intensity, nullptr, nullptr, AshPostProcessPushConstants{}, L.s);
     k_upsample_fast<false, true><<<grid, 256, 0, L.s>>>(static_cast<const uint2*>(src), (int)sw, (int)sh,
@@ -546,6 +541,8 @@ cudaError_t launch_upsample_tonemap_fast(const void* src, uint32_t sw, uint32_t 
                                          bool store_u, const Launch& L) {
     const dim3 grid((sw + 15) / 16, (sh + 15) / 16);
     Timed timed(L, ASH_KERNEL_UPSAMPLE_TONEMAP);
+    if (ASH_UPS_PAIR && upsample_pair_applies(sw, sh))
+        return launch_upsample_tonemap_pair(src, sw, sh, dst, intensity, hdr, ldr8, pc, store_u, L.s);
     if (ASH_UPS_PIPE && grid.x * grid.y >= 148u * ASH_UPS_PIPE_MINB * 2u)
         return store_u ? launch_upsample_pipe<true, true>(src, sw, sh, dst, intensity, hdr, ldr8, pc, L.s)
                        : launch_upsample_pipe<true, false>(src, sw, sh, dst, intensity, hdr, ldr8, pc, L.s);

@@ -68,5 +68,21 @@ __device__ __forceinline__ uint32_t to_unorm8(float l) {
     return (uint32_t)floorf(fadd(fmul(gclamp(l, 0.0f, 1.0f), 255.0f), 0.5f));
 }
 
+// ---------------------------------------------------------------- 1:2 tent upsample tap tables (bloom_upsample.frag:16-41, PIN-9)
+// Destination pixel x = 2i + p samples the source at i - 1/4 + p/2 + m/2 for tap offsets m = -2..2 (in units of
+// half a source texel): window column (origin i-2) c0 and weight g in {1/4, 3/4}; see post_fast.cu.
+__host__ __device__ constexpr int up_fd4(int q) { return q >= 0 ? q / 4 : -((-q + 3) / 4); }
+__host__ __device__ constexpr int up_c0(int p, int m) { return up_fd4(2 * p - 1 + 2 * m) + 2; }
+__host__ __device__ constexpr bool up_g75(int p, int m) { return (2 * p - 1 + 2 * m) - 4 * up_fd4(2 * p - 1 + 2 * m) == 3; }
+
+// ---------------------------------------------------------------- cp.async staging (LDGSTS)
+__device__ __forceinline__ void cp_async8(void* smem, const void* gmem) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" :: "r"((uint32_t)__cvta_generic_to_shared(smem)), "l"(gmem));
+}
+__device__ __forceinline__ void cp_async16(void* smem, const void* gmem) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" :: "r"((uint32_t)__cvta_generic_to_shared(smem)), "l"(gmem));
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N> __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" :: "n"(N) : "memory"); }
 
 }  // namespace ash
