@@ -62,6 +62,18 @@ __device__ __forceinline__ P2 fdiv_safe(P2 a, P2 b) {
     const P2 e = ffma(nb, q, a);
     return ffma(r, e, q);
 }
+// fdiv_safe(1, b): the quotient step q = fma(1, r, 0) is r itself (r > 0 or r < 0, never -0), so it is dropped
+__device__ __forceinline__ P2 frcp_safe(P2 b) {
+    float r0, r1;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r0) : "f"(lo(b)));
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r1) : "f"(hi(b)));
+    P2 r = pk(r0, r1);
+    const P2 nb = neg(b);
+    const P2 t = ffma(nb, r, splat(1.0f));
+    r = ffma(r, t, r);
+    const P2 e = ffma(nb, r, splat(1.0f));
+    return ffma(r, e, r);
+}
 __device__ __forceinline__ P2 fdiv_safe(float a, P2 b) { return fdiv_safe(splat(a), b); }
 __device__ __forceinline__ P2 fdiv_safe(P2 a, float b) { return fdiv_safe(a, splat(b)); }
 

@@ -126,8 +126,12 @@ __device__ __forceinline__ void taa_strip(const float4 (*s_nb)[kHalo], const Taa
             const V3P cc = pk3(unpack_rgb_(raw.hist[ra.i1][col.i0]), unpack_rgb_(raw.hist[rb.i1][col.i0]));
             const V3P d  = pk3(unpack_rgb_(raw.hist[ra.i1][col.i1]), unpack_rgb_(raw.hist[rb.i1][col.i1]));
             const P2 fy = pk(ra.f, rb.f), ify = fsub(1.0f, fy);
-            const V3P top = add3(scale3(a, ifx), scale3(b, fx));
-            const V3P bot = add3(scale3(cc, ifx), scale3(d, fx));
+            // texel (11 significant bits) x weight k/256 (<= 9 bits) is exact in fp32 (no subnormals: >= 2^-32), so
+            // the horizontal lerps round once with or without the FMA; the vertical ones keep both roundings
+            const P2 fx2 = splat(fx);
+            const V3P pa = scale3(a, ifx), pc2 = scale3(cc, ifx);
+            const V3P top = {ffma(b.x, fx2, pa.x), ffma(b.y, fx2, pa.y), ffma(b.z, fx2, pa.z)};
+            const V3P bot = {ffma(d.x, fx2, pc2.x), ffma(d.y, fx2, pc2.y), ffma(d.z, fx2, pc2.z)};
             h = add3(scale3(top, ify), scale3(bot, fy));
         } else {
             const int yl[2] = {y, min(y + 1, H - 1)};            // lane hi of a last odd row recomputes lane lo's row (not stored)
@@ -155,8 +159,9 @@ __device__ __forceinline__ void taa_strip(const float4 (*s_nb)[kHalo], const Taa
             const V3P cc = pk3(tap(0, hy1[0], hx0[0]), tap(1, hy1[1], hx0[1]));
             const V3P d  = pk3(tap(0, hy1[0], hx1[0]), tap(1, hy1[1], hx1[1]));
             const P2 fx2 = pk(hfx[0], hfx[1]), ifx2 = fsub(1.0f, fx2), fy = pk(hfy[0], hfy[1]), ify = fsub(1.0f, fy);
-            const V3P top = add3(scale3(a, ifx2), scale3(b, fx2));
-            const V3P bot = add3(scale3(cc, ifx2), scale3(d, fx2));
+            const V3P pa = scale3(a, ifx2), pc2 = scale3(cc, ifx2);                                   // exact products, as above
+            const V3P top = {ffma(b.x, fx2, pa.x), ffma(b.y, fx2, pa.y), ffma(b.z, fx2, pa.z)};
+            const V3P bot = {ffma(d.x, fx2, pc2.x), ffma(d.y, fx2, pc2.y), ffma(d.z, fx2, pc2.z)};
             h = add3(scale3(top, ify), scale3(bot, fy));
             blend2 = pk(bl[0], bl[1]);
             ib2 = fsub(1.0f, blend2);
@@ -294,7 +299,7 @@ k_downsample_pair(const uint2* __restrict__ src, int sw, int sh, uint2* __restri
     auto tap = [&](int i, int j, float wt) {
         const V3P t4 = add3(hs[j][i], hs[j + 1][i]);
         const P2 luma4 = fadd(fadd(fmul(t4.x, 0.2126f), fmul(t4.y, 0.7152f)), fmul(t4.z, 0.0722f));
-        const P2 w = fdiv_safe(1.0f, ffma(luma4, splat(0.25f), splat(1.0f)));   // 1 / (1 + luma), luma in [0, 65504]   :87-101
+        const P2 w = frcp_safe(ffma(luma4, splat(0.25f), splat(1.0f)));         // 1 / (1 + luma), luma in [0, 65504]   :87-101
         const P2 k = splat(0.25f * wt);                                          // power of two
         res = {ffma(fmul(t4.x, w), k, res.x), ffma(fmul(t4.y, w), k, res.y), ffma(fmul(t4.z, w), k, res.z)};
         sum = ffma(w, splat(wt), sum);

@@ -1,4 +1,4 @@
 cd $GRAFT_REPO_ROOT
-B="python bench.py --steps 2 --warmup 3 --streams 1 --views 2 --distinct 2 --cpu-views 0"
-ncu --set full --clock-control none --import-source on -k regex:k_upsample_pair -s 5 -c 1 -f -o gpurun_out/full_g_k_upsample_pair_tm $B > gpurun_out/ncu_full_g_up.log 2>&1
-tail -2 gpurun_out/ncu_full_g_up.log
+python -m pytest tests -m gpu -x -q 2>&1 | tail -4
+python bench.py --steps 5 --warmup 3 --cpu-views 0 > gpurun_out/ab_head.json 2> gpurun_out/ab_head.err || tail -3 gpurun_out/ab_head.err
+echo "== head"; python tools/show_bench.py gpurun_out/ab_head.json
