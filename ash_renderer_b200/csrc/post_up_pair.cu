@@ -11,6 +11,7 @@
 //
 // CTA = 128 threads = one 16x16 source tile = 32x32 destination pixels; persistent loop over tiles with the
 // next tile's source / destination / HDR blocks in flight (cp.async) while the current one is computed.
+// The source tile is converted to fp32 once per tile into the lane-paired layout the window reads use (UpSrcP).
 #include "post_pair.cuh"
 
 namespace ash {
@@ -38,14 +39,26 @@ struct UpHP {           // horizontal lerps (x4) of one destination-column parit
     V3P m2[3], m1[3], z[5], p1[3], p2[3];   // tap m = -2,-1: window rows 1..3 ; m = 0: rows 0..4 ; m = +1,+2: rows 1..3
 };
 
+// The source tile as the lanes consume it: entry (p, c), p = 0..11, holds texel (p, c) of the staged 20x20 tile
+// in the lo halves and texel (p + 8, c) in the hi halves, already converted to fp32 — one conversion per texel
+// per tile instead of one per thread that has the texel in its 5x5 window (HADD2.F32 costs two FMA-pipe
+// cycles, as much as an FFMA2), and the 64-bit lanes arrive in aligned register pairs straight from LDS.
+struct UpSrcP {
+    ulonglong2 xy[12][20];                   // {(x_p, x_{p+8}), (y_p, y_{p+8})}
+    unsigned long long z[12][20];            // (z_p, z_{p+8})
+};
+__device__ __forceinline__ V3P up_window_(const UpSrcP& S, int p, int c) {
+    const ulonglong2 a = S.xy[p][c];
+    return {P2{a.x}, P2{a.y}, P2{S.z[p][c]}};
+}
+
 template <int PX>
-__device__ __forceinline__ void up_hlerps_p(const uint2 (*s_t)[20], int tj, int ti, UpHP& h) {
+__device__ __forceinline__ void up_hlerps_p(const UpSrcP& S, int tj, int ti, UpHP& h) {
 #pragma unroll
     for (int r = 0; r < 5; ++r) {
         V3P t[5];
 #pragma unroll
-        for (int c = 0; c < 4; ++c)                                                      // window cols PX..PX+3
-            t[c + PX] = up_unpack2_(s_t[tj + r][ti + c + PX], s_t[tj + kUpLane + r][ti + c + PX]);
+        for (int c = 0; c < 4; ++c) t[c + PX] = up_window_(S, tj + r, ti + c + PX);      // window cols PX..PX+3
         h.z[r] = hlerp4p<up_g75(PX, 0)>(t[up_c0(PX, 0)], t[up_c0(PX, 0) + 1]);
         if (r >= 1 && r <= 3) {
             h.m2[r - 1] = hlerp4p<up_g75(PX, -2)>(t[up_c0(PX, -2)], t[up_c0(PX, -2) + 1]);
@@ -123,6 +136,7 @@ k_upsample_pair(const uint2* __restrict__ src, int sw, int sh, uint2* __restrict
                 const uint2* __restrict__ hdr, uint32_t* __restrict__ ldr8, AshPostProcessPushConstants pc,
                 int tiles_x, int ntiles) {
     __shared__ __align__(16) UpTileP<TONEMAP> T[2];
+    __shared__ __align__(16) UpSrcP S;
     const int ti = threadIdx.x & 15, tj = threadIdx.x >> 4;          // tj in 0..7: lanes = source rows tj, tj + 8
     const int dw = 2 * sw, dh = 2 * sh;
 
@@ -160,20 +174,30 @@ k_upsample_pair(const uint2* __restrict__ src, int sw, int sh, uint2* __restrict
         cp_async_commit();
         cp_async_wait<1>();                                       // this thread's copies of `tile` have landed
         __syncthreads();                                          // ... and everybody else's
+#pragma unroll
+        for (int k = 0; k < 2; ++k) {                             // fp16 -> paired fp32, 240 entries
+            const int e = (int)threadIdx.x + 128 * k;
+            if (k == 0 || e < 240) {
+                const int p = e / 20, c = e - p * 20;
+                const V3P t = up_unpack2_(T[b].src[p][c], T[b].src[p + kUpLane][c]);
+                S.xy[p][c] = make_ulonglong2(t.x.v, t.y.v);
+                S.z[p][c] = t.z.v;
+            }
+        }
+        __syncthreads();
         const int i = (tile % tiles_x) * 16 + ti, j = (tile / tiles_x) * 16 + tj;
         if (i < sw && j < sh) {
             const bool hi_ok = j + kUpLane < sh;                  // lane hi past the last row: computed on the clamped tile, not stored
-            const uint2 (*s_t)[20] = T[b].src;
             V3P up[2][2];    // [py][px] upsampled value of both lanes, before the additive blend
             {
                 UpHP h;
-                up_hlerps_p<0>(s_t, tj, ti, h);
+                up_hlerps_p<0>(S, tj, ti, h);
                 up[0][0] = scale3(up_combine_p<0>(h), k2);
                 up[1][0] = scale3(up_combine_p<1>(h), k2);
             }
             {
                 UpHP h;
-                up_hlerps_p<1>(s_t, tj, ti, h);
+                up_hlerps_p<1>(S, tj, ti, h);
                 up[0][1] = scale3(up_combine_p<0>(h), k2);
                 up[1][1] = scale3(up_combine_p<1>(h), k2);
             }
@@ -201,7 +225,7 @@ k_upsample_pair(const uint2* __restrict__ src, int sw, int sh, uint2* __restrict
                 }
             }
         }
-        __syncthreads();                                          // buffer b is refilled by the next iteration's issue
+        __syncthreads();                                          // buffer b is refilled by the next iteration's issue, S by its conversion
     }
     cp_async_wait<0>();
 }
