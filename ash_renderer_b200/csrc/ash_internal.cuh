@@ -268,6 +268,8 @@ cudaError_t launch_bloom_downsample_fast(const void* src, uint32_t sw, uint32_t 
                                          uint32_t dh, const Launch& L);
 cudaError_t launch_bloom_downsample_pair(const void* src, uint32_t sw, uint32_t sh, void* dst, uint32_t dw,
                                          uint32_t dh, const Launch& L);
+cudaError_t launch_bloom_downsample_box(const void* src, uint32_t sw, uint32_t sh, void* dst, uint32_t dw,
+                                        uint32_t dh, const Launch& L);                                     // post_down_box.cu
 cudaError_t launch_bloom_upsample_fast(const void* src, uint32_t sw, uint32_t sh, void* dst, float intensity,
                                        const Launch& L);
 cudaError_t launch_upsample_tonemap_fast(const void* src, uint32_t sw, uint32_t sh, void* dst, float intensity,

@@ -244,6 +244,10 @@ cudaError_t launch_bloom_downsample_fast(const void* src, uint32_t sw, uint32_t 
 #ifndef ASH_DOWN_PAIR
 #define ASH_DOWN_PAIR 1
 #endif
+#ifndef ASH_DOWN_BOX
+#define ASH_DOWN_BOX 1
+#endif
+    if (ASH_DOWN_BOX && dw >= 64u && dw % 32u == 0u) return launch_bloom_downsample_box(src, sw, sh, dst, dw, dh, L);           // every box once, post_down_box.cu
     if (ASH_DOWN_PAIR && (dw & 1u) == 0u) return launch_bloom_downsample_pair(src, sw, sh, dst, dw, dh, L);    // two pixels per thread, post_pair.cu
     const dim3 grid((dw + 31) / 32, (dh + 7) / 8);
     Timed timed(L, ASH_KERNEL_BLOOM_DOWNSAMPLE);
