@@ -125,6 +125,11 @@ k_downsample_box(const uint2* __restrict__ src, int sw, int sh, uint2* __restric
     if (XB < dw) dst[(size_t)Y * dw + XB] = pack_rgba16f(hi(o.x), hi(o.y), hi(o.z), 1.0f);
 }
 
+// A persistent cp.async double-buffered variant of this kernel (130 x 18 source texels of the next tile pair
+// staged while the current one is computed, as k_upsample_pair does) was measured SLOWER: 35.2 vs 28.4 us at
+// 4K -> 1080p under ncu.  Its long-scoreboard stalls vanish (3.5 -> 0.3) but two CTA barriers per tile pair
+// (2.0 stalled warps per issue), the copy address arithmetic (+17 % instructions), 2-way bank conflicts of the
+// 8-byte window reads and 3 instead of 4 CTAs per SM (73 KB of shared memory) cost more than the latency hidden.
 cudaError_t launch_bloom_downsample_box(const void* src, uint32_t sw, uint32_t sh, void* dst, uint32_t dw,
                                         uint32_t dh, const Launch& L) {
     const dim3 grid((dw + 63) / 64, (dh + 7) / 8);

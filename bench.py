@@ -36,8 +36,8 @@ HIZ_LEVELS = 12                    # "full pyramid" (PIN-4)
 METRIC, UNIT = "4k_views_per_sec", "views/s"
 # dram__bytes_read.sum + dram__bytes_write.sum per launch, from the committed `ncu --set full` captures of this
 # very workload (one launch each; re-captured whenever the kernel changes)
-NCU_DRAM_SOURCE = "profiles/r01_d_full_k_taa_pair.md (132.74 MB read + 94.09 MB write)"
-NCU_DRAM_BYTES = {"taa_threshold_fused": 132.741376e6 + 94.085632e6}
+NCU_DRAM_SOURCE = "profiles/r01_h_full_k_taa_pair.md (132.74 MB read + 93.84 MB write)"
+NCU_DRAM_BYTES = {"taa_threshold_fused": 132.739328e6 + 93.842432e6}
 
 
 def workload_name():
@@ -587,7 +587,7 @@ def main():
     ap.add_argument("--impl", default="cuda", choices=["cuda", "reference"])
     ap.add_argument("--views", type=int, default=16, help="views per GPU per step")
     ap.add_argument("--distinct", type=int, default=4, help="distinct synthetic depth/HDR inputs generated per GPU (host setup cost)")
-    ap.add_argument("--streams", type=int, default=4)
+    ap.add_argument("--streams", type=int, default=8)
     ap.add_argument("--cpu-views", type=int, default=2)
     ap.add_argument("--graph-replay", type=int, default=1, choices=[0, 1],
                     help="1: view_run replays a captured CUDA graph per view (library default); 0: launches every kernel")
