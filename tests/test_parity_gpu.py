@@ -419,7 +419,9 @@ def test_taa_sequence_halton_16_frames(backend, oracle):
 
 
 # ------------------------------------------------------------------ bloom + tonemap
-@pytest.mark.parametrize("W,H,mips", [(200, 120, 5), (67, 45, 5), (1920, 1080, 5), (64, 64, 3), (33, 9, 2), (256, 256, 8)])
+# (1984, 1096): level 1 = 992 x 548 — box downsample with its right lane past the edge (992 % 64 == 32) and a partial last
+# row of tiles (548 % 8 == 4); pair upsample whose second lane runs out of rows in the last row of tiles (548 % 16 == 4)
+@pytest.mark.parametrize("W,H,mips", [(200, 120, 5), (67, 45, 5), (1920, 1080, 5), (64, 64, 3), (33, 9, 2), (256, 256, 8), (1984, 1096, 3)])
 def test_bloom_chain_bit_exact(backend, oracle, W, H, mips):
     hdr = synth.random_hdr(W, H, seed=W)
     U, D = oracle.bloom_chain(hdr, 0.8, mips)

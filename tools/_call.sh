@@ -1,4 +1,4 @@
 cd $GRAFT_REPO_ROOT
-B="python bench.py --steps 2 --warmup 3 --streams 1 --views 2 --distinct 2 --cpu-views 0"
-ncu --set full --clock-control none --import-source on -k regex:k_downsample_box_pipe -s 4 -c 1 -f -o gpurun_out/full_i_box_pipe $B > gpurun_out/ncu_full_i.log 2>&1
-tail -1 gpurun_out/ncu_full_i.log
+python -m pytest tests -m gpu -x -q 2>&1 | tail -3
+python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29511 bench.py --gpus 2 --steps 10 --warmup 3 > gpurun_out/bench_h_2gpu.json 2> gpurun_out/bench_h_2gpu.err; tail -c 300 gpurun_out/bench_h_2gpu.err; python tools/show_bench.py gpurun_out/bench_h_2gpu.json | head -1
+python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29512 bench.py --impl reference --gpus 2 --steps 1 --warmup 0 > gpurun_out/bench_ref_h_2gpu.json 2> gpurun_out/bench_ref_h_2gpu.err; head -c 300 gpurun_out/bench_ref_h_2gpu.json
