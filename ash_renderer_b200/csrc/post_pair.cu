@@ -17,27 +17,31 @@ __device__ __forceinline__ V3 unpack_rgb_(uint2 t) { V4 v = unpack_rgba16f(t); r
 // Staging map (no divisions): step it < 4: warp w stages halo row w + 8*it, lane = halo column (the 32x32
 // block at the halo origin); step 4: threads 0..63 stage rows 32..33, threads 64..131 columns 32..33.
 // =====================================================================================================
-constexpr int kT = 32, kHalo = kT + 2;                                 // 34 x 34 = 1156 staged texels
+#ifndef ASH_TAA_TH
+#define ASH_TAA_TH 16                                                  // tile height: 32 (256 threads) or 16 (128 threads)
+#endif
+constexpr int kT = 32, kHalo = kT + 2;                                 // tile width; 34 staged columns
+constexpr int kTH = ASH_TAA_TH, kHaloH = kTH + 2, kTaaThreads = 8 * kTH, kTaaWarps = kTaaThreads / 32;
 
 struct AxisTap { int i0, i1; float f; float pad; };                  // halo-local texel indices + 8-bit weight
-struct TaaTables { AxisTap col[kT], row[kT]; float blend; };
-struct TaaRaw { uint2 cur[kHalo][kHalo], hist[kHalo][kHalo]; };       // RGBA16F texels, tile + halo
+struct TaaTables { AxisTap col[kT], row[kTH]; float blend; };
+struct TaaRaw { uint2 cur[kHaloH][kHalo], hist[kHaloH][kHalo]; };       // RGBA16F texels, tile + halo
 
 struct StageMap {
     int lane, warp, xr, rr; bool extra;
     __device__ __forceinline__ StageMap() {
         lane = threadIdx.x & 31; warp = threadIdx.x >> 5;
         xr = threadIdx.x < 64 ? lane : 32 + (threadIdx.x & 1);
-        rr = threadIdx.x < 64 ? 32 + warp : (int)(threadIdx.x - 64) >> 1;
-        extra = threadIdx.x < 132;
+        rr = threadIdx.x < 64 ? kTH + warp : (int)(threadIdx.x - 64) >> 1;
+        extra = threadIdx.x < 64 + 2 * kHaloH;
     }
 };
 
 // coordinate tables of one tile, :92-102 + PIN-6 (threads 0..63; thread 0 also the blend factor, :145-150)
 __device__ __forceinline__ void taa_tables(TaaTables& tb, const AshTaaPushConstants& pc, int W, int H, int x0, int y0) {
-    if (threadIdx.x >= 2 * kT) return;
+    if (threadIdx.x >= kT + kTH) return;
     const bool is_row = threadIdx.x >= kT;
-    const int k = threadIdx.x & (kT - 1);
+    const int k = is_row ? (int)threadIdx.x - kT : (int)threadIdx.x;
     const float ext = is_row ? pc.screen_params[1] : pc.screen_params[0];
     const int n = is_row ? H : W, p0 = is_row ? y0 : x0;
     const float jd = is_row ? fsub(pc.jitter[1], pc.prev_jitter[1]) : fsub(pc.jitter[0], pc.prev_jitter[0]);
@@ -46,8 +50,8 @@ __device__ __forceinline__ void taa_tables(TaaTables& tb, const AshTaaPushConsta
     const float hu = gclamp(fsub(u, vel), 0.0f, 1.0f);                       // :102
     AxisTap t;
     bilinear_setup(hu, n, t.i0, t.i1, t.f);
-    t.i0 = min(max(t.i0 - (p0 - 1), 0), kHalo - 1);                          // halo-local (the clamp only guards rows / columns past the extent)
-    t.i1 = min(max(t.i1 - (p0 - 1), 0), kHalo - 1);
+    t.i0 = min(max(t.i0 - (p0 - 1), 0), (is_row ? kHaloH : kHalo) - 1);                          // halo-local (the clamp only guards rows / columns past the extent)
+    t.i1 = min(max(t.i1 - (p0 - 1), 0), (is_row ? kHaloH : kHalo) - 1);
     t.pad = 0.0f;
     if (is_row) tb.row[k] = t; else tb.col[k] = t;
     if (threadIdx.x == 0) {
@@ -67,7 +71,7 @@ __device__ __forceinline__ void taa_tables(TaaTables& tb, const AshTaaPushConsta
 __device__ __forceinline__ void taa_stage_nb(float4 (*s_nb)[kHalo], const uint2 (&tc)[5], const StageMap& m) {
 #pragma unroll
     for (int it = 0; it < 4; it += 2) {
-        const int r0 = m.warp + 8 * it, r1 = r0 + 8;
+        const int r0 = m.warp + kTaaWarps * it, r1 = r0 + kTaaWarps;
         const V3P s = rgb_to_ycocg(taa_tonemap_safe(pk3(unpack_rgb_(tc[it]), unpack_rgb_(tc[it + 1]))));
         s_nb[r0][m.lane] = make_float4(lo(s.x), lo(s.y), lo(s.z), 0.0f);
         s_nb[r1][m.lane] = make_float4(hi(s.x), hi(s.y), hi(s.z), 0.0f);
@@ -198,14 +202,17 @@ __device__ __forceinline__ void taa_strip(const float4 (*s_nb)[kHalo], const Taa
 #define ASH_TAA_MINB 3
 #endif
 template <bool THRESH, bool VEL>
-__global__ void __launch_bounds__(256, ASH_TAA_MINB)
+#ifndef ASH_TAA_CTAS
+#define ASH_TAA_CTAS (ASH_TAA_MINB * 256 / (8 * ASH_TAA_TH))
+#endif
+__global__ void __launch_bounds__(kTaaThreads, ASH_TAA_CTAS)
 k_taa_pair(Tex16 cur, Tex16 hist, const __half2* __restrict__ vel, uint2* __restrict__ out, uint2* __restrict__ thr,
            AshTaaPushConstants pc, float threshold) {
-    __shared__ float4 s_nb[kHalo][kHalo];      // tonemapped YCoCg of `current`, tile + halo
+    __shared__ float4 s_nb[kHaloH][kHalo];     // tonemapped YCoCg of `current`, tile + halo
     __shared__ TaaRaw s_raw;
     __shared__ TaaTables s_tb;
     const int W = cur.W, H = cur.H;
-    const int x0 = blockIdx.x * kT, y0 = blockIdx.y * kT;
+    const int x0 = blockIdx.x * kT, y0 = blockIdx.y * kTH;
     const bool clamp_on = pc.params[1] > 0.5f;
     const StageMap m;
     {   // stage: all global loads of the CTA are issued here, back to back
@@ -213,7 +220,7 @@ k_taa_pair(Tex16 cur, Tex16 hist, const __half2* __restrict__ vel, uint2* __rest
         const int gx = min(max(x0 - 1 + m.lane, 0), W - 1);                                            // CLAMP_TO_EDGE
 #pragma unroll
         for (int it = 0; it < 4; ++it) {
-            const size_t g = (size_t)min(max(y0 - 1 + m.warp + 8 * it, 0), H - 1) * W + gx;
+            const size_t g = (size_t)min(max(y0 - 1 + m.warp + kTaaWarps * it, 0), H - 1) * W + gx;
             tc[it] = __ldg(cur.p + g);
             if (!VEL) th[it] = __ldg(hist.p + g);
         }
@@ -226,8 +233,8 @@ k_taa_pair(Tex16 cur, Tex16 hist, const __half2* __restrict__ vel, uint2* __rest
         if (!VEL) taa_tables(s_tb, pc, W, H, x0, y0);      // while the loads fly
 #pragma unroll
         for (int it = 0; it < 4; ++it) {
-            s_raw.cur[m.warp + 8 * it][m.lane] = tc[it];
-            if (!VEL) s_raw.hist[m.warp + 8 * it][m.lane] = th[it];
+            s_raw.cur[m.warp + kTaaWarps * it][m.lane] = tc[it];
+            if (!VEL) s_raw.hist[m.warp + kTaaWarps * it][m.lane] = th[it];
         }
         if (m.extra) { s_raw.cur[m.rr][m.xr] = tc[4]; if (!VEL) s_raw.hist[m.rr][m.xr] = th[4]; }
         if (clamp_on) taa_stage_nb(s_nb, tc, m);
@@ -248,15 +255,15 @@ cudaError_t launch_taa_pair(const void* cur, const void* hist, const void* vel_o
                             const AshTaaPushConstants& pc, float threshold, const Launch& L) {
     const int W = (int)pc.screen_params[0], H = (int)pc.screen_params[1];
     const Tex16 c{static_cast<const uint2*>(cur), W, H}, h{static_cast<const uint2*>(hist), W, H};
-    const dim3 grid((W + kT - 1) / kT, (H + kT - 1) / kT);
+    const dim3 grid((W + kT - 1) / kT, (H + kTH - 1) / kTH);
     uint2* o = static_cast<uint2*>(out);
     uint2* t = static_cast<uint2*>(thr_or_null);
     Timed timed(L, thr_or_null ? ASH_KERNEL_TAA_THRESHOLD : ASH_KERNEL_TAA);
     const __half2* v = static_cast<const __half2*>(vel_or_null);
-    if (v) { if (t) k_taa_pair<true, true><<<grid, 256, 0, L.s>>>(c, h, v, o, t, pc, threshold);
-             else   k_taa_pair<false, true><<<grid, 256, 0, L.s>>>(c, h, v, o, t, pc, threshold); }
-    else   { if (t) k_taa_pair<true, false><<<grid, 256, 0, L.s>>>(c, h, v, o, t, pc, threshold);
-             else   k_taa_pair<false, false><<<grid, 256, 0, L.s>>>(c, h, v, o, t, pc, threshold); }
+    if (v) { if (t) k_taa_pair<true, true><<<grid, kTaaThreads, 0, L.s>>>(c, h, v, o, t, pc, threshold);
+             else   k_taa_pair<false, true><<<grid, kTaaThreads, 0, L.s>>>(c, h, v, o, t, pc, threshold); }
+    else   { if (t) k_taa_pair<true, false><<<grid, kTaaThreads, 0, L.s>>>(c, h, v, o, t, pc, threshold);
+             else   k_taa_pair<false, false><<<grid, kTaaThreads, 0, L.s>>>(c, h, v, o, t, pc, threshold); }
     return cudaGetLastError();
 }
 
