@@ -18,7 +18,7 @@ __device__ __forceinline__ V3 unpack_rgb_(uint2 t) { V4 v = unpack_rgba16f(t); r
 // block at the halo origin); step 4: threads 0..63 stage rows 32..33, threads 64..131 columns 32..33.
 // =====================================================================================================
 #ifndef ASH_TAA_TH
-#define ASH_TAA_TH 16                                                  // tile height: 32 (256 threads) or 16 (128 threads)
+#define ASH_TAA_TH 16                                                  // tile height: 32 (256 threads, 114.8 us at 4K), 16 (128 threads, 109.4 us) or 8 (64 threads, 114.0 us)
 #endif
 constexpr int kT = 32, kHalo = kT + 2;                                 // tile width; 34 staged columns
 constexpr int kTH = ASH_TAA_TH, kHaloH = kTH + 2, kTaaThreads = 8 * kTH, kTaaWarps = kTaaThreads / 32;
@@ -27,13 +27,19 @@ struct AxisTap { int i0, i1; float f; float pad; };                  // halo-loc
 struct TaaTables { AxisTap col[kT], row[kTH]; float blend; };
 struct TaaRaw { uint2 cur[kHaloH][kHalo], hist[kHaloH][kHalo]; };       // RGBA16F texels, tile + halo
 
+// halo entries beyond the 32-column x kTH-row block: 64 of rows kTH, kTH+1 and 2 * kHaloH of columns 32, 33
+constexpr int kExtraEntries = 64 + 2 * kHaloH, kExtraSlots = (kExtraEntries + kTaaThreads - 1) / kTaaThreads;
 struct StageMap {
-    int lane, warp, xr, rr; bool extra;
+    int lane, warp, xr[kExtraSlots], rr[kExtraSlots]; bool extra[kExtraSlots];
     __device__ __forceinline__ StageMap() {
         lane = threadIdx.x & 31; warp = threadIdx.x >> 5;
-        xr = threadIdx.x < 64 ? lane : 32 + (threadIdx.x & 1);
-        rr = threadIdx.x < 64 ? kTH + warp : (int)(threadIdx.x - 64) >> 1;
-        extra = threadIdx.x < 64 + 2 * kHaloH;
+#pragma unroll
+        for (int n = 0; n < kExtraSlots; ++n) {
+            const int e = (int)threadIdx.x + n * kTaaThreads;
+            xr[n] = e < 64 ? (e & 31) : 32 + (e & 1);
+            rr[n] = e < 64 ? kTH + (e >> 5) : (e - 64) >> 1;
+            extra[n] = e < kExtraEntries;
+        }
     }
 };
 
@@ -67,8 +73,8 @@ __device__ __forceinline__ void taa_tables(TaaTables& tb, const AshTaaPushConsta
     }
 }
 
-// tonemapped YCoCg (:120) of this thread's 5 staged `current` texels -> s_nb, two at a time
-__device__ __forceinline__ void taa_stage_nb(float4 (*s_nb)[kHalo], const uint2 (&tc)[5], const StageMap& m) {
+// tonemapped YCoCg (:120) of this thread's staged `current` texels -> s_nb, two at a time
+__device__ __forceinline__ void taa_stage_nb(float4 (*s_nb)[kHalo], const uint2 (&tc)[4 + kExtraSlots], const StageMap& m) {
 #pragma unroll
     for (int it = 0; it < 4; it += 2) {
         const int r0 = m.warp + kTaaWarps * it, r1 = r0 + kTaaWarps;
@@ -76,12 +82,14 @@ __device__ __forceinline__ void taa_stage_nb(float4 (*s_nb)[kHalo], const uint2 
         s_nb[r0][m.lane] = make_float4(lo(s.x), lo(s.y), lo(s.z), 0.0f);
         s_nb[r1][m.lane] = make_float4(hi(s.x), hi(s.y), hi(s.z), 0.0f);
     }
-    if (m.extra) {
-        const V3 c3 = unpack_rgb_(tc[4]);
-        const V3 tm = {fdiv_safe(c3.x, fadd(1.0f, c3.x)), fdiv_safe(c3.y, fadd(1.0f, c3.y)), fdiv_safe(c3.z, fadd(1.0f, c3.z))};
-        const V3 s = rgb_to_ycocg(tm);
-        s_nb[m.rr][m.xr] = make_float4(s.x, s.y, s.z, 0.0f);
-    }
+#pragma unroll
+    for (int n = 0; n < kExtraSlots; ++n)
+        if (m.extra[n]) {
+            const V3 c3 = unpack_rgb_(tc[4 + n]);
+            const V3 tm = {fdiv_safe(c3.x, fadd(1.0f, c3.x)), fdiv_safe(c3.y, fadd(1.0f, c3.y)), fdiv_safe(c3.z, fadd(1.0f, c3.z))};
+            const V3 s = rgb_to_ycocg(tm);
+            s_nb[m.rr[n]][m.xr[n]] = make_float4(s.x, s.y, s.z, 0.0f);
+        }
 }
 
 // resolve this thread's 1x4 strip of the tile at (x0, y0).
@@ -216,7 +224,7 @@ k_taa_pair(Tex16 cur, Tex16 hist, const __half2* __restrict__ vel, uint2* __rest
     const bool clamp_on = pc.params[1] > 0.5f;
     const StageMap m;
     {   // stage: all global loads of the CTA are issued here, back to back
-        uint2 tc[5], th[5];
+        uint2 tc[4 + kExtraSlots], th[4 + kExtraSlots];
         const int gx = min(max(x0 - 1 + m.lane, 0), W - 1);                                            // CLAMP_TO_EDGE
 #pragma unroll
         for (int it = 0; it < 4; ++it) {
@@ -224,11 +232,14 @@ k_taa_pair(Tex16 cur, Tex16 hist, const __half2* __restrict__ vel, uint2* __rest
             tc[it] = __ldg(cur.p + g);
             if (!VEL) th[it] = __ldg(hist.p + g);
         }
-        tc[4] = th[4] = make_uint2(0u, 0u);
-        if (m.extra) {
-            const size_t g = (size_t)min(max(y0 - 1 + m.rr, 0), H - 1) * W + min(max(x0 - 1 + m.xr, 0), W - 1);
-            tc[4] = __ldg(cur.p + g);
-            if (!VEL) th[4] = __ldg(hist.p + g);
+#pragma unroll
+        for (int n = 0; n < kExtraSlots; ++n) {
+            tc[4 + n] = th[4 + n] = make_uint2(0u, 0u);
+            if (m.extra[n]) {
+                const size_t g = (size_t)min(max(y0 - 1 + m.rr[n], 0), H - 1) * W + min(max(x0 - 1 + m.xr[n], 0), W - 1);
+                tc[4 + n] = __ldg(cur.p + g);
+                if (!VEL) th[4 + n] = __ldg(hist.p + g);
+            }
         }
         if (!VEL) taa_tables(s_tb, pc, W, H, x0, y0);      // while the loads fly
 #pragma unroll
@@ -236,7 +247,9 @@ k_taa_pair(Tex16 cur, Tex16 hist, const __half2* __restrict__ vel, uint2* __rest
             s_raw.cur[m.warp + kTaaWarps * it][m.lane] = tc[it];
             if (!VEL) s_raw.hist[m.warp + kTaaWarps * it][m.lane] = th[it];
         }
-        if (m.extra) { s_raw.cur[m.rr][m.xr] = tc[4]; if (!VEL) s_raw.hist[m.rr][m.xr] = th[4]; }
+#pragma unroll
+        for (int n = 0; n < kExtraSlots; ++n)
+            if (m.extra[n]) { s_raw.cur[m.rr[n]][m.xr[n]] = tc[4 + n]; if (!VEL) s_raw.hist[m.rr[n]][m.xr[n]] = th[4 + n]; }
         if (clamp_on) taa_stage_nb(s_nb, tc, m);
     }
     __syncthreads();
