@@ -414,116 +414,10 @@ k_upsample_fast(const uint2* __restrict__ src, int sw, int sh, uint2* __restrict
     }
 }
 
-// ---- the same kernel as a persistent, software-pipelined loop over tiles: the source tile and the
-// destination / HDR blocks of tile n+1 are fetched with cp.async into the other shared-memory buffer
-// while tile n is computed, so the load latency that the one-shot kernel exposes at the top of every
-// CTA (ncu: 52 % issue-active, long-scoreboard bound) is hidden behind arithmetic.
-// (cp_async8 / cp_async16 / cp_async_commit / cp_async_wait: post_math.cuh)
+// (The persistent, cp.async double-buffered form of this kernel — k_upsample_pipe, 90 -> 68 us for the fused last level
+//  at 4K — was superseded by k_upsample_pair, post_up_pair.cu: the same pipeline with two source texels per thread on
+//  the packed fp32 pipe, 60 us.  Levels too small to fill the persistent grid twice run the one-shot kernel above.)
 
-template <bool TONEMAP>
-struct UpTile {
-    uint2 src[20][20];                       // 16x16 source texels + 2-texel halo
-    uint4 dst[32][16];                       // 32x32 destination texels (the additive-blend operand)
-    uint4 hdr[TONEMAP ? 32 : 1][16];         // 32x32 HDR texels (tonemap input)
-};
-
-#ifndef ASH_UPS_PIPE_MINB
-#define ASH_UPS_PIPE_MINB 3
-#endif
-template <bool TONEMAP, bool STORE_U>
-__global__ void __launch_bounds__(256, ASH_UPS_PIPE_MINB)
-k_upsample_pipe(const uint2* __restrict__ src, int sw, int sh, uint2* __restrict__ dst, float intensity,
-                const uint2* __restrict__ hdr, uint32_t* __restrict__ ldr8, AshPostProcessPushConstants pc,
-                int tiles_x, int ntiles) {
-    __shared__ __align__(16) UpTile<TONEMAP> T[2];
-    const int ti = threadIdx.x & 15, tj = threadIdx.x >> 4;
-    const int dw = 2 * sw, dh = 2 * sh;
-    // per-thread staging slots, fixed for the whole loop
-    const int sr0 = threadIdx.x / 20, sc0 = threadIdx.x - sr0 * 20;                 // source texel slot 1
-    const int s1 = threadIdx.x + 256, sr1 = s1 / 20, sc1 = s1 - sr1 * 20;           // slot 2 (threads 0..143)
-    const int br0 = threadIdx.x >> 4, br1 = br0 + 16, bc = threadIdx.x & 15;        // 16-byte block slots: rows br0, br1, column bc
-
-    auto issue = [&](int tile, int b) {
-        const int i0 = (tile % tiles_x) * 16, j0 = (tile / tiles_x) * 16;
-        cp_async8(&T[b].src[sr0][sc0], src + (size_t)min(max(j0 - 2 + sr0, 0), sh - 1) * sw + min(max(i0 - 2 + sc0, 0), sw - 1));   // CLAMP_TO_EDGE
-        if (s1 < 400) cp_async8(&T[b].src[sr1][sc1], src + (size_t)min(max(j0 - 2 + sr1, 0), sh - 1) * sw + min(max(i0 - 2 + sc1, 0), sw - 1));
-        if (i0 + bc < sw) {
-            const size_t col = (size_t)2 * (i0 + bc);
-            if (2 * j0 + br0 < dh) {
-                cp_async16(&T[b].dst[br0][bc], dst + (size_t)(2 * j0 + br0) * dw + col);
-                if (TONEMAP) cp_async16(&T[b].hdr[br0][bc], hdr + (size_t)(2 * j0 + br0) * dw + col);
-            }
-            if (2 * j0 + br1 < dh) {
-                cp_async16(&T[b].dst[br1][bc], dst + (size_t)(2 * j0 + br1) * dw + col);
-                if (TONEMAP) cp_async16(&T[b].hdr[br1][bc], hdr + (size_t)(2 * j0 + br1) * dw + col);
-            }
-        }
-    };
-
-    const float k = fmul(intensity, 0.00390625f);                 // (R16 / 256) * intensity == R16 * (intensity / 256)
-    const float inv_gamma = TONEMAP ? __fdividef(1.0f, pc.gamma) : 0.0f;
-    int tile = blockIdx.x, b = 0;
-    if (tile < ntiles) issue(tile, 0);
-    cp_async_commit();
-    for (; tile < ntiles; tile += gridDim.x, b ^= 1) {
-        const int next = tile + gridDim.x;
-        if (next < ntiles) issue(next, b ^ 1);
-        cp_async_commit();
-        cp_async_wait<1>();                                       // this thread's copies of `tile` have landed
-        __syncthreads();                                          // ... and everybody else's
-        const int i = (tile % tiles_x) * 16 + ti, j = (tile / tiles_x) * 16 + tj;
-        if (i < sw && j < sh) {
-            const uint2 (*s_t)[20] = T[b].src;
-            V3 up[2][2];     // [py][px] upsampled value, before the additive blend
-            {
-                UpH h;
-                up_hlerps<0>(s_t, tj, ti, h);
-                const V3 a = up_combine<0>(h), c = up_combine<1>(h);
-                up[0][0] = {fmul(a.x, k), fmul(a.y, k), fmul(a.z, k)};
-                up[1][0] = {fmul(c.x, k), fmul(c.y, k), fmul(c.z, k)};
-            }
-            {
-                UpH h;
-                up_hlerps<1>(s_t, tj, ti, h);
-                const V3 a = up_combine<0>(h), c = up_combine<1>(h);
-                up[0][1] = {fmul(a.x, k), fmul(a.y, k), fmul(a.z, k)};
-                up[1][1] = {fmul(c.x, k), fmul(c.y, k), fmul(c.z, k)};
-            }
-#pragma unroll
-            for (int py = 0; py < 2; ++py) {
-                const size_t o = (size_t)(2 * j + py) * dw + 2 * i;                   // 16-byte aligned pair of texels
-                const uint4 d = T[b].dst[2 * tj + py][ti];
-                const V3 d0 = unpack_rgb(make_uint2(d.x, d.y)), d1 = unpack_rgb(make_uint2(d.z, d.w));
-                const uint2 u0 = pack_rgba16f(fadd(up[py][0].x, d0.x), fadd(up[py][0].y, d0.y), fadd(up[py][0].z, d0.z), 1.0f);
-                const uint2 u1 = pack_rgba16f(fadd(up[py][1].x, d1.x), fadd(up[py][1].y, d1.y), fadd(up[py][1].z, d1.z), 1.0f);
-                if (STORE_U) *reinterpret_cast<uint4*>(dst + o) = make_uint4(u0.x, u0.y, u1.x, u1.y);
-                if (TONEMAP) {
-                    const uint4 c = T[b].hdr[2 * tj + py][ti];
-                    const uint32_t a8 = tonemap_pack8(unpack_rgb(make_uint2(c.x, c.y)), unpack_rgb(u0), pc, inv_gamma);
-                    const uint32_t b8 = tonemap_pack8(unpack_rgb(make_uint2(c.z, c.w)), unpack_rgb(u1), pc, inv_gamma);
-                    *reinterpret_cast<uint2*>(ldr8 + o) = make_uint2(a8, b8);
-                }
-            }
-        }
-        __syncthreads();                                          // buffer b is refilled by the next iteration's issue
-    }
-    cp_async_wait<0>();
-}
-
-template <bool TONEMAP, bool STORE_U>
-static cudaError_t launch_upsample_pipe(const void* src, uint32_t sw, uint32_t sh, void* dst, float intensity,
-                                        const void* hdr, void* ldr8, const AshPostProcessPushConstants& pc, cudaStream_t s) {
-    const int tiles_x = (int)((sw + 15) / 16), ntiles = tiles_x * (int)((sh + 15) / 16);
-    const int grid = min(ntiles, 148 * ASH_UPS_PIPE_MINB);
-    k_upsample_pipe<TONEMAP, STORE_U><<<grid, 256, 0, s>>>(static_cast<const uint2*>(src), (int)sw, (int)sh, static_cast<uint2*>(dst),
-                                                            intensity, static_cast<const uint2*>(hdr), static_cast<uint32_t*>(ldr8),
-                                                            pc, tiles_x, ntiles);
-    return cudaGetLastError();
-}
-
-#ifndef ASH_UPS_PIPE
-#define ASH_UPS_PIPE 1
-#endif
 #ifndef ASH_UPS_PAIR          // two source texels per thread on the packed fp32 pipe (post_up_pair.cu)
 #define ASH_UPS_PAIR 1
 #endif
@@ -532,8 +426,6 @@ cudaError_t launch_bloom_upsample_fast(const void* src, uint32_t sw, uint32_t sh
     const dim3 grid((sw + 15) / 16, (sh + 15) / 16);
     Timed timed(L, ASH_KERNEL_BLOOM_UPSAMPLE);
     if (ASH_UPS_PAIR && upsample_pair_applies(sw, sh)) return launch_upsample_pair(src, sw, sh, dst, intensity, L.s);
-    if (ASH_UPS_PIPE && grid.x * grid.y >= 148u * ASH_UPS_PIPE_MINB * 2u)
-        return launch_upsample_pipe<false, true>(src, sw, sh, dst, intensity, nullptr, nullptr, AshPostProcessPushConstants{}, L.s);
     k_upsample_fast<false, true><<<grid, 256, 0, L.s>>>(static_cast<const uint2*>(src), (int)sw, (int)sh,
                                                         static_cast<uint2*>(dst), intensity, nullptr, nullptr,
                                                         AshPostProcessPushConstants{});
@@ -547,9 +439,6 @@ cudaError_t launch_upsample_tonemap_fast(const void* src, uint32_t sw, uint32_t 
     Timed timed(L, ASH_KERNEL_UPSAMPLE_TONEMAP);
     if (ASH_UPS_PAIR && upsample_pair_applies(sw, sh))
         return launch_upsample_tonemap_pair(src, sw, sh, dst, intensity, hdr, ldr8, pc, store_u, L.s);
-    if (ASH_UPS_PIPE && grid.x * grid.y >= 148u * ASH_UPS_PIPE_MINB * 2u)
-        return store_u ? launch_upsample_pipe<true, true>(src, sw, sh, dst, intensity, hdr, ldr8, pc, L.s)
-                       : launch_upsample_pipe<true, false>(src, sw, sh, dst, intensity, hdr, ldr8, pc, L.s);
     if (store_u)
         k_upsample_fast<true, true><<<grid, 256, 0, L.s>>>(static_cast<const uint2*>(src), (int)sw, (int)sh, static_cast<uint2*>(dst),
                                                            intensity, static_cast<const uint2*>(hdr), static_cast<uint32_t*>(ldr8), pc);

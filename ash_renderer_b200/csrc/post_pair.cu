@@ -203,7 +203,7 @@ __device__ __forceinline__ void taa_strip(const float4 (*s_nb)[kHalo], const Taa
     }
 }
 
-// A persistent cp.async double-buffered variant of this kernel (as k_upsample_pipe, post_fast.cu) was
+// A persistent cp.async double-buffered variant of this kernel (as k_upsample_pair, post_up_pair.cu) was
 // measured 20 % SLOWER (0.140 vs 0.116 ms at 4K): three barriers per tile and the extra shared-memory
 // pass outweigh the hidden load latency; the one-shot kernel below keeps its loads in registers.
 #ifndef ASH_TAA_MINB

@@ -1,12 +1,12 @@
 // post_up_pair.cu — the 1:2 tent upsample + additive blend (+ ACES tonemap / 8-bit pack) of post_fast.cu
 // evaluated for TWO source texels per thread in lock-step on the packed fp32 pipe (ash_f32x2.cuh).
 //
-// k_upsample_pipe (post_fast.cu) issues ~150 (upsample) / ~200 (with tonemap) instructions per destination
-// pixel, 55 % of them scalar FADD / FMUL / FFMA, and is bound by instruction issue (ncu: 75 % issue-active).
+// The scalar form of this pipeline (k_upsample_pipe, removed) issued ~150 (upsample) / ~200 (with tonemap) instructions per destination
+// pixel, 55 % of them scalar FADD / FMUL / FFMA, and was bound by instruction issue (ncu: 75 % issue-active).
 // Here a thread owns source texels (i, j) and (i, j + 8) of a 16x16 tile: both lanes run exactly the scalar
 // kernel's operation sequence (same taps, same order, same roundings), every add / mul / fma is one FADD2 /
 // FFMA2 for the pair, and the shared-memory addresses of the second lane are immediate offsets of the first.
-// Bit-identical to k_upsample_fast / k_upsample_pipe (bloom_upsample.frag:16-41, PIN-9; tonemapping.frag:20-48,
+// Bit-identical to k_upsample_fast (post_fast.cu; bloom_upsample.frag:16-41, PIN-9; tonemapping.frag:20-48,
 // PIN-11 for the 8-bit target).
 //
 // CTA = 128 threads = one 16x16 source tile = 32x32 destination pixels; persistent loop over tiles with the

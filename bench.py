@@ -582,7 +582,7 @@ def main():
     os.dup2(2, 1)                      # fd 1 -> stderr for the rest of the run
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--steps", type=int, default=16)      # 16 steps x 16 views = 256 views per GPU
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="cuda", choices=["cuda", "reference"])
     ap.add_argument("--views", type=int, default=16, help="views per GPU per step")
