@@ -97,27 +97,28 @@ __device__ __forceinline__ V3P up_combine_p(const UpHP& h) {
 __device__ __forceinline__ float up_lg2_(float x) { float r; asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
 __device__ __forceinline__ float up_ex2_(float x) { float r; asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
 __device__ __forceinline__ float up_rcp_(float x) { float r; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
-__device__ __forceinline__ uint32_t up_gamma8_(float n, float d, float inv_gamma) {
-    const float a = __saturatef(n * up_rcp_(d));
-    const float g = up_ex2_(inv_gamma * up_lg2_(a));                                     // pow(a, 1/gamma), a in [0,1]   :47
-    return (uint32_t)__float2int_rd(__fmaf_rn(__saturatef(g), 255.0f, 0.5f));            // PIN-11
-}
-__device__ __forceinline__ void tonemap8_pair(P2 c, P2 bloom, const AshPostProcessPushConstants& pc, float inv_gamma,
-                                              uint32_t& o_lo, uint32_t& o_hi) {
+// Per channel, both lanes: x, ACES numerator / denominator, n * rcp(d), inv_gamma * lg2, 255 g + 2^23 are packed; the
+// three MUFUs and the final clamp are per lane.  Relative to tonemap8 (post_fast.cu): the clamp of the ACES quotient is
+// dropped (a > 1 gives g > 1, a < 0 or NaN gives NaN, and the clamp of g maps those to 1 and 0 exactly as clamping a
+// first would, for gamma > 0), and the 8-bit value is read from the low mantissa byte of RN(255 g + 2^23), i.e. round
+// to nearest even instead of floor(255 g + 0.5): they differ only on exact ties, inside the 1-LSB tolerance of PIN-11.
+__device__ __forceinline__ P2 tonemap8_pair(P2 c, P2 bloom, const AshPostProcessPushConstants& pc, float inv_gamma, float magic) {
     const P2 x = fmul(ffma(bloom, splat(pc.bloom_intensity), c), pc.exposure);           // :38, :41
     const P2 n = fmul(x, ffma(splat(2.51f), x, splat(0.03f)));                           // :20-27
     const P2 d = ffma(x, ffma(splat(2.43f), x, splat(0.59f)), splat(0.14f));
-    o_lo = up_gamma8_(lo(n), lo(d), inv_gamma);
-    o_hi = up_gamma8_(hi(n), hi(d), inv_gamma);
+    const P2 a = fmul(n, pk(up_rcp_(lo(d)), up_rcp_(hi(d))));
+    const P2 e = fmul(pk(up_lg2_(lo(a)), up_lg2_(hi(a))), inv_gamma);                    // pow(a, 1/gamma)   :47
+    const P2 g = pk(__saturatef(up_ex2_(lo(e))), __saturatef(up_ex2_(hi(e))));
+    return ffma(g, splat(255.0f), splat(magic));                                         // low byte = 8-bit value (PIN-11)
 }
 __device__ __forceinline__ void tonemap_pack8_pair(V3P c, V3P bloom, const AshPostProcessPushConstants& pc, float inv_gamma,
                                                    uint32_t& o_lo, uint32_t& o_hi) {
-    uint32_t rl, rh, gl, gh, bl, bh;
-    tonemap8_pair(c.x, bloom.x, pc, inv_gamma, rl, rh);
-    tonemap8_pair(c.y, bloom.y, pc, inv_gamma, gl, gh);
-    tonemap8_pair(c.z, bloom.z, pc, inv_gamma, bl, bh);
-    o_lo = rl | (gl << 8) | (bl << 16) | 0xFF000000u;
-    o_hi = rh | (gh << 8) | (bh << 16) | 0xFF000000u;
+    // 2^23 + 255 g has the 8-bit value in byte 0 and zeros in byte 1; for blue 2^23 + 0xFF00 + 255 g puts alpha = 0xFF there
+    const P2 r = tonemap8_pair(c.x, bloom.x, pc, inv_gamma, 8388608.0f), g = tonemap8_pair(c.y, bloom.y, pc, inv_gamma, 8388608.0f),
+             b = tonemap8_pair(c.z, bloom.z, pc, inv_gamma, 8388608.0f + 65280.0f);
+    // bytes: r0, g0 <- byte 0 of r and g; b0, 0xFF <- bytes 0, 1 of b
+    o_lo = __byte_perm(__byte_perm(__float_as_uint(lo(r)), __float_as_uint(lo(g)), 0x0040), __float_as_uint(lo(b)), 0x5410);
+    o_hi = __byte_perm(__byte_perm(__float_as_uint(hi(r)), __float_as_uint(hi(g)), 0x0040), __float_as_uint(hi(b)), 0x5410);
 }
 
 template <bool TONEMAP>
