@@ -399,14 +399,16 @@ def test_taa_bit_exact(backend, oracle, W, H, with_vel):
             _assert_half_images_equal(c.taa_out(), ref, f"taa {kw}")
 
 
-def test_taa_sequence_halton_16_frames(backend, oracle):
+# BASELINE config 4 at a size the oracle follows in seconds: a 64-frame jittered sequence (four periods of the 16-entry
+# Halton table of temporal_aa.rs:42-58), every resolve compared, the history recurrence fed by the oracle's own output.
+@pytest.mark.parametrize("W,H,frames", [(160, 96, 18), (416, 240, 64)])
+def test_taa_sequence_halton_16_frames(backend, oracle, W, H, frames):
     from ash_renderer_b200.host import TemporalAA
-    W, H = 160, 96
     seq = synth.HdrSequence(W, H, seed=4, n_discs=20)
     taa = TemporalAA()
     hist = None
     with _ctx(backend, W, H) as c:
-        for t in range(18):
+        for t in range(frames):
             taa.begin_frame()
             j = taa.current_jitter()
             frame = seq.frame(float(j[0]), float(j[1]))

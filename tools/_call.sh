@@ -1,5 +1,5 @@
 cd $GRAFT_REPO_ROOT
-python -m pytest tests -m gpu -x -q 2>&1 | tail -3
-python bench.py --steps 5 --warmup 3 --cpu-views 0 > gpurun_out/ab_head.json 2> gpurun_out/ab_head.err || tail -3 gpurun_out/ab_head.err
-echo "== head"; python tools/show_bench.py gpurun_out/ab_head.json | grep -E "value|tonemap"
-bash tools/ab.sh prev 2>&1 | grep -E "==|value|tonemap"
+(time python -m pytest tests -m gpu -x -q 2>&1 | tail -3) 2>&1 | grep -E "passed|failed|real"
+python -c "import __graft_entry__ as g; g.smoke()" 2>&1 | tail -2
+(time python bench.py > gpurun_out/bench_j.json 2> gpurun_out/bench_j.err) 2>&1 | grep real; python tools/show_bench.py gpurun_out/bench_j.json | head -1
+(time python bench.py --impl reference --steps 2 --warmup 0 > gpurun_out/bench_ref_j.json 2> gpurun_out/bench_ref_j.err) 2>&1 | grep real; head -c 150 gpurun_out/bench_ref_j.json
