@@ -7,7 +7,9 @@ fn main() {
     let out = PathBuf::from(env::var("OUT_DIR").unwrap());
     let csrc = PathBuf::from(env::var("ASHCUDA_CSRC").unwrap_or_else(|_| "../ash_renderer_b200/csrc".into()));
     let nvcc = env::var("NVCC").unwrap_or_else(|_| "/usr/local/cuda/bin/nvcc".into());
-    let sources = ["ashcuda.cu", "depth_pyramid.cu", "occlusion_cull.cu", "light_cull.cu", "post.cu", "post_fast.cu", "exact_taps.cu"];
+    // the SRCS list of ash_renderer_b200/csrc/Makefile
+    let sources = ["ashcuda.cu", "depth_pyramid.cu", "occlusion_cull.cu", "light_cull.cu", "post.cu", "post_fast.cu", "post_pair.cu",
+                   "post_up_pair.cu", "post_down_box.cu", "instancing.cu", "forward.cu", "compute_utils.cu", "view_graph.cu", "exact_taps.cu"];
     let mut objects = Vec::new();
     for s in sources {
         let obj = out.join(s).with_extension("o");
