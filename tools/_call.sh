@@ -1,5 +1,6 @@
 cd $GRAFT_REPO_ROOT
-(time python -m pytest tests -m gpu -x -q 2>&1 | tail -3) 2>&1 | grep -E "passed|failed|real"
-python -c "import __graft_entry__ as g; g.smoke()" 2>&1 | tail -2
-(time python bench.py > gpurun_out/bench_j.json 2> gpurun_out/bench_j.err) 2>&1 | grep real; python tools/show_bench.py gpurun_out/bench_j.json | head -1
-(time python bench.py --impl reference --steps 2 --warmup 0 > gpurun_out/bench_ref_j.json 2> gpurun_out/bench_ref_j.err) 2>&1 | grep real; head -c 150 gpurun_out/bench_ref_j.json
+B="python bench.py --steps 2 --warmup 3 --streams 1 --views 2 --distinct 2 --cpu-views 0"
+for K in k_occlusion_cull k_cull_compact k_light_prepass k_light_cells k_light_tiles; do
+  ncu --set full --clock-control none --import-source on -k regex:$K -s 5 -c 1 -f -o gpurun_out/full_i_$K $B > gpurun_out/ncu_full_i_$K.log 2>&1
+  tail -1 gpurun_out/ncu_full_i_$K.log
+done
