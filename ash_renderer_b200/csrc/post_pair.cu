@@ -23,7 +23,7 @@ __device__ __forceinline__ V3 unpack_rgb_(uint2 t) { V4 v = unpack_rgba16f(t); r
 constexpr int kT = 32, kHalo = kT + 2;                                 // tile width; 34 staged columns
 constexpr int kTH = ASH_TAA_TH, kHaloH = kTH + 2, kTaaThreads = 8 * kTH, kTaaWarps = kTaaThreads / 32;
 
-struct AxisTap { int i0, i1; float f; float pad; };                  // halo-local texel indices + 8-bit weight
+struct AxisTap { int i0, i1; float f; float pad; };                  // halo-local texel BYTE offsets (column: 8 i, row: 8 kHalo i) + 8-bit weight
 struct TaaTables { AxisTap col[kT], row[kTH]; float blend; };
 struct TaaRaw { uint2 cur[kHaloH][kHalo], hist[kHaloH][kHalo]; };       // RGBA16F texels, tile + halo
 
@@ -56,8 +56,9 @@ __device__ __forceinline__ void taa_tables(TaaTables& tb, const AshTaaPushConsta
     const float hu = gclamp(fsub(u, vel), 0.0f, 1.0f);                       // :102
     AxisTap t;
     bilinear_setup(hu, n, t.i0, t.i1, t.f);
-    t.i0 = min(max(t.i0 - (p0 - 1), 0), (is_row ? kHaloH : kHalo) - 1);                          // halo-local (the clamp only guards rows / columns past the extent)
-    t.i1 = min(max(t.i1 - (p0 - 1), 0), (is_row ? kHaloH : kHalo) - 1);
+    const int pitch = is_row ? 8 * kHalo : 8;                                // byte offsets: one add per tap address in the strip
+    t.i0 = min(max(t.i0 - (p0 - 1), 0), (is_row ? kHaloH : kHalo) - 1) * pitch;                  // halo-local (the clamp only guards rows / columns past the extent)
+    t.i1 = min(max(t.i1 - (p0 - 1), 0), (is_row ? kHaloH : kHalo) - 1) * pitch;
     t.pad = 0.0f;
     if (is_row) tb.row[k] = t; else tb.col[k] = t;
     if (threadIdx.x == 0) {
@@ -133,10 +134,12 @@ __device__ __forceinline__ void taa_strip(const float4 (*s_nb)[kHalo], const Taa
         V3P h;                                                                                         // :108 bilinear history
         P2 blend2 = splat(blend), ib2 = splat(ib);
         if (!VEL) {
-            const V3P a  = pk3(unpack_rgb_(raw.hist[ra.i0][col.i0]), unpack_rgb_(raw.hist[rb.i0][col.i0]));
-            const V3P b  = pk3(unpack_rgb_(raw.hist[ra.i0][col.i1]), unpack_rgb_(raw.hist[rb.i0][col.i1]));
-            const V3P cc = pk3(unpack_rgb_(raw.hist[ra.i1][col.i0]), unpack_rgb_(raw.hist[rb.i1][col.i0]));
-            const V3P d  = pk3(unpack_rgb_(raw.hist[ra.i1][col.i1]), unpack_rgb_(raw.hist[rb.i1][col.i1]));
+            const char* hb = reinterpret_cast<const char*>(&raw.hist[0][0]);
+            auto tap = [&](int ro, int co) { return unpack_rgb_(*reinterpret_cast<const uint2*>(hb + ro + co)); };
+            const V3P a  = pk3(tap(ra.i0, col.i0), tap(rb.i0, col.i0));
+            const V3P b  = pk3(tap(ra.i0, col.i1), tap(rb.i0, col.i1));
+            const V3P cc = pk3(tap(ra.i1, col.i0), tap(rb.i1, col.i0));
+            const V3P d  = pk3(tap(ra.i1, col.i1), tap(rb.i1, col.i1));
             const P2 fy = pk(ra.f, rb.f), ify = fsub(1.0f, fy);
             // texel (11 significant bits) x weight k/256 (<= 9 bits) is exact in fp32 (no subnormals: >= 2^-32), so
             // the horizontal lerps round once with or without the FMA; the vertical ones keep both roundings
@@ -193,12 +196,13 @@ __device__ __forceinline__ void taa_strip(const float4 (*s_nb)[kHalo], const Taa
         const V3P o = add3(scale3(c, ib2), scale3(h, blend2));                                         // mix(), :159
         const uint2 oa = pack_rgba16f(lo(o.x), lo(o.y), lo(o.z), 1.0f), ob = pack_rgba16f(hi(o.x), hi(o.y), hi(o.z), 1.0f);
         const bool has_b = y + 1 < H;
-        out[(size_t)y * W + x] = oa;
-        if (has_b) out[(size_t)(y + 1) * W + x] = ob;
+        const uint32_t o0 = (uint32_t)y * (uint32_t)W + (uint32_t)x, o1 = o0 + (uint32_t)W;        // < 2^32 texels: 32-bit offsets
+        out[o0] = oa;
+        if (has_b) out[o1] = ob;
         if (THRESH) {                      // bloom threshold of the resolved texel as stored (fp16)
             const V3P b = soft_threshold_pair(pk3(unpack_rgb_(oa), unpack_rgb_(ob)), threshold);
-            thr[(size_t)y * W + x] = pack_rgba16f(lo(b.x), lo(b.y), lo(b.z), 1.0f);
-            if (has_b) thr[(size_t)(y + 1) * W + x] = pack_rgba16f(hi(b.x), hi(b.y), hi(b.z), 1.0f);
+            thr[o0] = pack_rgba16f(lo(b.x), lo(b.y), lo(b.z), 1.0f);
+            if (has_b) thr[o1] = pack_rgba16f(hi(b.x), hi(b.y), hi(b.z), 1.0f);
         }
     }
 }
@@ -228,7 +232,7 @@ k_taa_pair(Tex16 cur, Tex16 hist, const __half2* __restrict__ vel, uint2* __rest
         const int gx = min(max(x0 - 1 + m.lane, 0), W - 1);                                            // CLAMP_TO_EDGE
 #pragma unroll
         for (int it = 0; it < 4; ++it) {
-            const size_t g = (size_t)min(max(y0 - 1 + m.warp + kTaaWarps * it, 0), H - 1) * W + gx;
+            const uint32_t g = (uint32_t)min(max(y0 - 1 + m.warp + kTaaWarps * it, 0), H - 1) * (uint32_t)W + (uint32_t)gx;
             tc[it] = __ldg(cur.p + g);
             if (!VEL) th[it] = __ldg(hist.p + g);
         }
@@ -236,7 +240,7 @@ k_taa_pair(Tex16 cur, Tex16 hist, const __half2* __restrict__ vel, uint2* __rest
         for (int n = 0; n < kExtraSlots; ++n) {
             tc[4 + n] = th[4 + n] = make_uint2(0u, 0u);
             if (m.extra[n]) {
-                const size_t g = (size_t)min(max(y0 - 1 + m.rr[n], 0), H - 1) * W + min(max(x0 - 1 + m.xr[n], 0), W - 1);
+                const uint32_t g = (uint32_t)min(max(y0 - 1 + m.rr[n], 0), H - 1) * (uint32_t)W + (uint32_t)min(max(x0 - 1 + m.xr[n], 0), W - 1);
                 tc[4 + n] = __ldg(cur.p + g);
                 if (!VEL) th[4 + n] = __ldg(hist.p + g);
             }
