@@ -141,24 +141,24 @@ k_upsample_pair(const uint2* __restrict__ src, int sw, int sh, uint2* __restrict
     const int ti = threadIdx.x & 15, tj = threadIdx.x >> 4;          // tj in 0..7: lanes = source rows tj, tj + 8
     const int dw = 2 * sw, dh = 2 * sh;
 
-    auto issue = [&](int tile, int b) {
-        const int i0 = (tile % tiles_x) * 16, j0 = (tile / tiles_x) * 16;
+    auto issue = [&](int tcx, int tcy, int b) {                      // tile column / row
+        const int i0 = tcx * 16, j0 = tcy * 16;
 #pragma unroll
         for (int k = 0; k < 4; ++k) {                                // 400 source texels, CLAMP_TO_EDGE
             const int idx = (int)threadIdx.x + 128 * k;
             if (k < 3 || idx < 400) {
                 const int r = idx / 20, c = idx - r * 20;
-                cp_async8(&T[b].src[r][c], src + (size_t)min(max(j0 - 2 + r, 0), sh - 1) * sw + min(max(i0 - 2 + c, 0), sw - 1));
+                cp_async8(&T[b].src[r][c], src + ((uint32_t)min(max(j0 - 2 + r, 0), sh - 1) * (uint32_t)sw + (uint32_t)min(max(i0 - 2 + c, 0), sw - 1)));   // < 2^32 texels: 32-bit offsets
             }
         }
         if (i0 + ti < sw) {                                          // 32 rows x 16 blocks of 16 bytes (two texels)
-            const size_t col = (size_t)2 * (i0 + ti);
+            const uint32_t col = 2u * (uint32_t)(i0 + ti);
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
                 const int br = tj + 8 * k;
                 if (2 * j0 + br < dh) {
-                    cp_async16(&T[b].dst[br][ti], dst + (size_t)(2 * j0 + br) * dw + col);
-                    if (TONEMAP) cp_async16(&T[b].hdr[br][ti], hdr + (size_t)(2 * j0 + br) * dw + col);
+                    cp_async16(&T[b].dst[br][ti], dst + ((uint32_t)(2 * j0 + br) * (uint32_t)dw + col));
+                    if (TONEMAP) cp_async16(&T[b].hdr[br][ti], hdr + ((uint32_t)(2 * j0 + br) * (uint32_t)dw + col));
                 }
             }
         }
@@ -166,12 +166,17 @@ k_upsample_pair(const uint2* __restrict__ src, int sw, int sh, uint2* __restrict
 
     const P2 k2 = splat(fmul(intensity, 0.00390625f));            // (R16 / 256) * intensity == R16 * (intensity / 256)
     const float inv_gamma = TONEMAP ? __fdividef(1.0f, pc.gamma) : 0.0f;
+    // tile coordinates advance by gridDim.x tiles per round without a division in the loop
+    const int step_y = (int)gridDim.x / tiles_x, step_x = (int)gridDim.x - step_y * tiles_x;
     int tile = blockIdx.x, b = 0;
-    if (tile < ntiles) issue(tile, 0);
+    int cy = tile / tiles_x, cx = tile - cy * tiles_x;
+    if (tile < ntiles) issue(cx, cy, 0);
     cp_async_commit();
     for (; tile < ntiles; tile += gridDim.x, b ^= 1) {
         const int next = tile + gridDim.x;
-        if (next < ntiles) issue(next, b ^ 1);
+        int nx = cx + step_x, ny = cy + step_y;
+        if (nx >= tiles_x) { nx -= tiles_x; ++ny; }
+        if (next < ntiles) issue(nx, ny, b ^ 1);
         cp_async_commit();
         cp_async_wait<1>();                                       // this thread's copies of `tile` have landed
         __syncthreads();                                          // ... and everybody else's
@@ -186,7 +191,8 @@ k_upsample_pair(const uint2* __restrict__ src, int sw, int sh, uint2* __restrict
             }
         }
         __syncthreads();
-        const int i = (tile % tiles_x) * 16 + ti, j = (tile / tiles_x) * 16 + tj;
+        const int i = cx * 16 + ti, j = cy * 16 + tj;
+        cx = nx; cy = ny;
         if (i < sw && j < sh) {
             const bool hi_ok = j + kUpLane < sh;                  // lane hi past the last row: computed on the clamped tile, not stored
             V3P up[2][2];    // [py][px] upsampled value of both lanes, before the additive blend
@@ -205,8 +211,8 @@ k_upsample_pair(const uint2* __restrict__ src, int sw, int sh, uint2* __restrict
 #pragma unroll
             for (int py = 0; py < 2; ++py) {
                 const int rl = 2 * tj + py, rh = rl + 2 * kUpLane;                     // tile-local destination rows of the lanes
-                const size_t ol = (size_t)(2 * j + py) * dw + 2 * i;                   // 16-byte aligned pair of texels
-                const size_t oh = ol + (size_t)(2 * kUpLane) * dw;
+                const uint32_t ol = (uint32_t)(2 * j + py) * (uint32_t)dw + 2u * (uint32_t)i;   // 16-byte aligned pair of texels
+                const uint32_t oh = ol + (uint32_t)(2 * kUpLane) * (uint32_t)dw;
                 const uint4 dl = T[b].dst[rl][ti], dhh = T[b].dst[rh][ti];
                 const V3P u0 = add3(up[py][0], up_unpack2_(make_uint2(dl.x, dl.y), make_uint2(dhh.x, dhh.y)));
                 const V3P u1 = add3(up[py][1], up_unpack2_(make_uint2(dl.z, dl.w), make_uint2(dhh.z, dhh.w)));
