@@ -36,8 +36,8 @@ HIZ_LEVELS = 12                    # "full pyramid" (PIN-4)
 METRIC, UNIT = "4k_views_per_sec", "views/s"
 # dram__bytes_read.sum + dram__bytes_write.sum per launch, from the committed `ncu --set full` captures of this
 # very workload (one launch each; re-captured whenever the kernel changes)
-NCU_DRAM_SOURCE = "profiles/r01_i_full_k_taa_pair.md (132.74 MB read + 94.53 MB write)"
-NCU_DRAM_BYTES = {"taa_threshold_fused": 132.741120e6 + 94.525184e6}
+NCU_DRAM_SOURCE = "profiles/r01_j_full_k_taa_pair.md (132.79 MB read + 93.82 MB write)"
+NCU_DRAM_BYTES = {"taa_threshold_fused": 132.792064e6 + 93.815296e6}
 
 
 def workload_name():
