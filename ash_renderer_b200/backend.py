@@ -29,7 +29,7 @@ EXPORTS = [
     "ashcuda_light_cull", "ashcuda_taa_resolve", "ashcuda_bloom", "ashcuda_tonemap",
     "ashcuda_view_run", "ashcuda_get", "ashcuda_readback", "ashcuda_readback_async", "ashcuda_sync",
     "ashcuda_hiz_level_count", "ashcuda_mip_extent", "ashcuda_kernel_launches", "ashcuda_graph_stats", "ashcuda_last_error",
-    "ashcuda_version", "ashcuda_profile_kernels", "ashcuda_kernel_time_ms", "ashcuda_upload_view", "ashcuda_download_view",
+    "ashcuda_version", "ashcuda_profile_kernels", "ashcuda_kernel_time_ms", "ashcuda_upload_view", "ashcuda_download_view", "ashcuda_download_view_packed",
     "ashcuda_debug_exact_taps",
     "ashcuda_set_instances", "ashcuda_set_lod_meshes", "ashcuda_set_lod_config", "ashcuda_instancing_finalize",
     "ashcuda_set_forward_params", "ashcuda_forward_depth", "ashcuda_forward_shade", "ashcuda_debug_compute_utils",
@@ -90,6 +90,7 @@ def load_library():
         "ashcuda_debug_exact_taps": (i32, [i32, i32, i32, C.c_float, C.c_float]),
         "ashcuda_upload_view": (i32, [vp, vp, vp, vp]),
         "ashcuda_download_view": (i32, [vp, vp, vp, vp, vp, vp]),
+        "ashcuda_download_view_packed": (i32, [vp, vp, vp, vp, u32, vp, vp, vp]),
         "ashcuda_set_instances": (i32, [vp, vp, vp, vp, u32, i32]),
         "ashcuda_set_lod_meshes": (i32, [vp, vp, u32, i32]),
         "ashcuda_set_lod_config": (i32, [vp, vp]),
@@ -239,6 +240,15 @@ class Context:
         """Device -> host copies of one view's results (async on the ctx stream; call sync())."""
         ptrs = [_ptr(a)[0] for a in (visibility, tile_data, ldr8, stats, visible_count)]
         self._ck(self._lib.ashcuda_download_view(self._h, *ptrs))
+
+    def download_view_packed(self, visibility=None, tile_offsets=None, tile_lights=None, ldr8=None, stats=None,
+                             visible_count=None):
+        """download_view with the tile light lists in CSR form: tile_offsets (tiles + 1 words) and tile_lights
+        (its length is the capacity).  After sync(), tile_offsets[-1] > len(tile_lights) means truncated."""
+        cap = 0 if tile_lights is None else int(tile_lights.numel() if hasattr(tile_lights, "numel") else tile_lights.size)
+        ptrs = [_ptr(a)[0] for a in (visibility, tile_offsets, tile_lights)]
+        tail = [_ptr(a)[0] for a in (ldr8, stats, visible_count)]
+        self._ck(self._lib.ashcuda_download_view_packed(self._h, *ptrs, cap, *tail))
 
     def sync(self):
         self._ck(self._lib.ashcuda_sync(self._h))

@@ -183,6 +183,9 @@ struct ashcuda_ctx {
     bool      graphs_broken = false;             // a capture failed once: stay on the eager path
     uint64_t  graph_replays = 0, graph_captures = 0;
     uint32_t* tile_data = nullptr;
+    uint32_t* tile_offsets = nullptr;          // packed (CSR) tile lists: tiles + 1 offsets, allocated on first use
+    uint32_t* tile_packed = nullptr;           // ... and tile_packed_cap light indices
+    uint32_t  tile_packed_cap = 0;
     AshViewStats* stats = nullptr;
 
     // post chain (RGBA16F = 8 B / texel)
@@ -215,6 +218,8 @@ cudaError_t launch_occlusion_cull(const AshCullObjectData* objs, const AshIndire
                                   uint32_t* late, const Launch& L);
 cudaError_t launch_culling_stats_finish(const AshViewStats* stats, const AshInstancingStats* inst_stats, uint32_t light_count,
                                         bool with_lights, AshCullingStats* cstats, const Launch& L);
+cudaError_t launch_tile_pack(const uint32_t* tile_data, uint32_t tiles, uint32_t* offsets, uint32_t* lights,
+                             uint32_t capacity, const Launch& L);                                            // light_cull.cu
 cudaError_t launch_light_cull(const AshGpuLight* lights, const AshLightCullingPushConstants& pc,
                               const AshCullingCameraData* cam_dev, const uint32_t* tile_minmax,
                               uint32_t* depth_range, LightCand* cand, uint32_t* cand_idx,

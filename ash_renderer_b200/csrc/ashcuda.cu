@@ -79,7 +79,7 @@ void ashcuda_destroy(ashcuda_ctx* c) {
     void* owned[] = {c->depth_owned, c->pyr.mips, c->tile_minmax, c->depth_range, c->counters,
                      c->objs_owned, c->draws_in_owned, c->visibility, c->vis_bits, c->cta_counts,
                      c->draws_out, c->visible_count, c->lights_owned, c->camera_dev, c->cand,
-                     c->cand_idx, c->cand_count, c->light_scratch, c->tile_data, c->stats, c->color_owned,
+                     c->cand_idx, c->cand_count, c->light_scratch, c->tile_data, c->tile_offsets, c->tile_packed, c->stats, c->color_owned,
                      c->velocity_owned, c->taa[0], c->taa[1], c->bloom_t, c->ldr8,
                      c->inst_owned, c->inst_batch_owned, c->inst_mesh_owned, c->lod_meshes_owned, c->batch_mesh,
                      c->lod_sel, c->bucket_of, c->cta_hist, c->bucket_offsets, c->bucket_totals, c->inst_out,
@@ -895,6 +895,29 @@ int ashcuda_download_view(ashcuda_ctx* c, uint32_t* visibility, uint32_t* tile_d
     if (stats) ASH_CUDA(c, cudaMemcpyAsync(stats, c->stats, sizeof(AshViewStats), cudaMemcpyDeviceToHost, c->stream));
     if (visible_count) ASH_CUDA(c, cudaMemcpyAsync(visible_count, c->visible_count, 4, cudaMemcpyDeviceToHost, c->stream));
     return ASH_OK;
+}
+
+int ashcuda_download_view_packed(ashcuda_ctx* c, uint32_t* visibility, uint32_t* tile_offsets, uint32_t* tile_lights,
+                                 uint32_t tile_lights_capacity, uint8_t* ldr8, AshViewStats* stats, uint32_t* visible_count) {
+    if (!c) return ASH_ERR_INVALID;
+    ASH_CUDA(c, cudaSetDevice(c->device));
+    if (tile_offsets || tile_lights) {
+        if (!tile_offsets || !tile_lights || tile_lights_capacity == 0)
+            return fail(c, ASH_ERR_INVALID, "download_view_packed: offsets, lights and a capacity go together");
+        const uint32_t tiles = c->tiles_x * c->tiles_y;
+        if (!c->tile_offsets) ASH_CUDA(c, dmalloc(&c->tile_offsets, ((size_t)tiles + 1) * 4));
+        if (c->tile_packed_cap < tile_lights_capacity) {          // (stream-ordered free: earlier packs on this stream are done first)
+            ASH_CUDA(c, cudaStreamSynchronize(c->stream));
+            if (c->tile_packed) ASH_CUDA(c, cudaFree(c->tile_packed));
+            c->tile_packed = nullptr; c->tile_packed_cap = 0;
+            ASH_CUDA(c, dmalloc(&c->tile_packed, (size_t)tile_lights_capacity * 4));
+            c->tile_packed_cap = tile_lights_capacity;
+        }
+        ASH_CUDA(c, launch_tile_pack(c->tile_data, tiles, c->tile_offsets, c->tile_packed, tile_lights_capacity, c->L()));
+        ASH_CUDA(c, cudaMemcpyAsync(tile_offsets, c->tile_offsets, ((size_t)tiles + 1) * 4, cudaMemcpyDeviceToHost, c->stream));
+        ASH_CUDA(c, cudaMemcpyAsync(tile_lights, c->tile_packed, (size_t)tile_lights_capacity * 4, cudaMemcpyDeviceToHost, c->stream));
+    }
+    return ashcuda_download_view(c, visibility, nullptr, ldr8, stats, visible_count);
 }
 
 }  // extern "C"

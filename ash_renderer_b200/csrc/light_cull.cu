@@ -409,4 +409,58 @@ cudaError_t launch_light_cull(const AshGpuLight* lights, const AshLightCullingPu
     return cudaGetLastError();
 }
 
+// =====================================================================================================
+// Tile light lists in CSR form for host consumers: the reference's table is tileData[tile * 257] = {count,
+// 256 slots} (light_culling.comp:43-45, 33 MB at 4K, almost all of it unused slots); the packed form is
+// offsets[tiles + 1] (exclusive scan of the counts) + the concatenated light indices in tile order — the same
+// information in about 1 MB.  offsets[tiles] is the total; entries beyond `capacity` are not written, so the
+// host detects a too-small destination from the total and falls back to the full table.
+// =====================================================================================================
+constexpr int kPackThreads = 1024;
+__global__ void __launch_bounds__(kPackThreads)
+k_tile_pack_offsets(const uint32_t* __restrict__ tile_data, uint32_t tiles, uint32_t* __restrict__ offsets) {
+    __shared__ uint32_t s_warp[kPackThreads / 32];
+    const uint32_t per = (tiles + kPackThreads - 1) / kPackThreads;          // consecutive tiles per thread
+    const uint32_t t0 = min(threadIdx.x * per, tiles), t1 = min(t0 + per, tiles);
+    uint32_t sum = 0;
+    for (uint32_t t = t0; t < t1; ++t) sum += __ldg(tile_data + (size_t)t * ASH_TILE_STRIDE);
+    uint32_t incl = sum;                                                     // warp inclusive scan
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) { const uint32_t v = __shfl_up_sync(0xFFFFFFFFu, incl, d); if ((threadIdx.x & 31) >= d) incl += v; }
+    if ((threadIdx.x & 31) == 31) s_warp[threadIdx.x >> 5] = incl;
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        const uint32_t w = s_warp[threadIdx.x];
+        uint32_t wi = w;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) { const uint32_t v = __shfl_up_sync(0xFFFFFFFFu, wi, d); if (threadIdx.x >= d) wi += v; }
+        s_warp[threadIdx.x] = wi - w;                                        // exclusive warp bases
+    }
+    __syncthreads();
+    uint32_t run = s_warp[threadIdx.x >> 5] + incl - sum;
+    for (uint32_t t = t0; t < t1; ++t) { offsets[t] = run; run += __ldg(tile_data + (size_t)t * ASH_TILE_STRIDE); }
+    if (threadIdx.x == kPackThreads - 1) offsets[tiles] = run;              // the last thread's chunk ends the table
+}
+
+__global__ void __launch_bounds__(256)
+k_tile_pack_lists(const uint32_t* __restrict__ tile_data, uint32_t tiles, const uint32_t* __restrict__ offsets,
+                  uint32_t* __restrict__ lights, uint32_t capacity) {
+    const uint32_t t = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (t >= tiles) return;
+    const uint32_t* src = tile_data + (size_t)t * ASH_TILE_STRIDE;
+    const uint32_t n = __ldg(src), o = __ldg(offsets + t);
+    for (uint32_t i = lane; i < n; i += 32) if (o + i < capacity) lights[o + i] = __ldg(src + 1 + i);
+}
+
+cudaError_t launch_tile_pack(const uint32_t* tile_data, uint32_t tiles, uint32_t* offsets, uint32_t* lights,
+                             uint32_t capacity, const Launch& L) {
+    Timed timed(L, ASH_KERNEL_LIGHT_TILES);
+    k_tile_pack_offsets<<<1, kPackThreads, 0, L.s>>>(tile_data, tiles, offsets);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return e;
+    k_tile_pack_lists<<<(tiles + 7) / 8, 256, 0, L.s>>>(tile_data, tiles, offsets, lights, capacity);
+    ++*L.launches;
+    return cudaGetLastError();
+}
+
 }  // namespace ash

@@ -332,7 +332,8 @@ def run_cuda(args):
                 "h_depth": torch.from_numpy(depth).pin_memory(), "h_hdr": torch.from_numpy(hdr.view(np.uint16)).pin_memory()}
         tiles = ((W + 15) // 16) * ((H + 15) // 16)
         slot["o_vis"] = torch.empty(n_objs, dtype=torch.int32).pin_memory()
-        slot["o_td"] = torch.empty(tiles * 257, dtype=torch.int32).pin_memory()
+        slot["o_off"] = torch.empty(tiles + 1, dtype=torch.int32).pin_memory()      # tile light lists in CSR form:
+        slot["o_tl"] = torch.empty(tiles * 16, dtype=torch.int32).pin_memory()      # offsets + up to 16 lights per tile on average
         slot["o_ldr"] = torch.empty(W * H * 4, dtype=torch.uint8).pin_memory()
         slot["o_st"] = torch.empty(8, dtype=torch.int32).pin_memory()
         slot["o_cnt"] = torch.empty(1, dtype=torch.int32).pin_memory()
@@ -375,7 +376,7 @@ def run_cuda(args):
             if not args.forward:                       # --forward: only the parameter block crosses the host boundary
                 c.upload_view(s["h_depth"], s["h_hdr"])
             c.view_run(s["vp"])
-            c.download_view(s["o_vis"], s["o_td"], s["o_ldr"], s["o_st"], s["o_cnt"])
+            c.download_view_packed(s["o_vis"], s["o_off"], s["o_tl"], s["o_ldr"], s["o_st"], s["o_cnt"])
 
     def barrier():
         torch.cuda.synchronize()
@@ -480,10 +481,15 @@ def run_cuda(args):
     h2d = B * (W * H * 4 + W * H * 8 + T.VIEW_PARAMS.itemsize)   # depth + HDR + the per-view parameter block
     if args.forward:
         h2d = B * T.VIEW_PARAMS.itemsize
-    d2h = B * (n_objs * 4 + tiles * 257 * 4 + W * H * 4 + 32 + 4)
+    d2h = B * (n_objs * 4 + (tiles + 1) * 4 + tiles * 16 * 4 + W * H * 4 + 32 + 4)   # visibility, packed tile lists, LDR8, stats, count
     # sanity: the e2e outputs equal the resident path's
     chk = slots[0]
     assert int(chk["o_cnt"][0]) == int(stats[0]["visible_objects"]), "e2e result differs from resident result"
+    off = chk["o_off"].numpy().view(np.uint32)
+    table = chk["ctx"].tile_data()
+    assert int(off[-1]) == int(table[:, 0].sum()) <= tiles * 16, "packed tile lists truncated or inconsistent"
+    t_probe = int(np.argmax(table[:, 0]))
+    assert np.array_equal(chk["o_tl"].numpy().view(np.uint32)[off[t_probe]:off[t_probe + 1]], table[t_probe, 1:1 + table[t_probe, 0]])
 
     # ---- stats all_gather (the only inter-GPU exchange; 32 B per view)
     from ash_renderer_b200 import views as V

@@ -407,6 +407,16 @@ int ashcuda_upload_view  (ashcuda_ctx*, const float* depth_wh, const void* hdr_r
                           const void* velocity_rg16f_or_null);
 int ashcuda_download_view(ashcuda_ctx*, uint32_t* visibility, uint32_t* tile_data, uint8_t* ldr8,
                           AshViewStats* stats, uint32_t* visible_count);
+/* The same with the tile light lists in CSR form instead of the reference's 257-word-per-tile table
+ * (light_culling.comp:43-45 / light_culling_pipeline.rs:55-56: 33 MB at 4K, nearly all unused slots):
+ * tile_offsets[tiles + 1] = exclusive scan of the per-tile counts (tile_offsets[tiles] = total), tile_lights =
+ * the light indices of tile 0, tile 1, ... back to back.  Exactly tile_lights_capacity words are copied into
+ * tile_lights; if tile_offsets[tiles] > tile_lights_capacity the lists are truncated there and the caller
+ * fetches the full table (ashcuda_download_view / ASH_BUF_TILE_DATA) instead.  tile_offsets and tile_lights
+ * may both be NULL to skip the lists.  Two small kernels on the ctx stream build the packed form. */
+int ashcuda_download_view_packed(ashcuda_ctx*, uint32_t* visibility, uint32_t* tile_offsets, uint32_t* tile_lights,
+                                 uint32_t tile_lights_capacity, uint8_t* ldr8, AshViewStats* stats,
+                                 uint32_t* visible_count);
 
 /* --- outputs: device pointers owned by ctx, valid until the next call that rewrites them.
  *     Replaces LightCullingPipeline::tile_buffer / tile_buffer_size (:322-330). */

@@ -128,6 +128,7 @@ extern "C" {
     pub fn ashcuda_debug_compute_utils(device: c_int, op: c_int, input: *const c_void, n: u32, params18: *const f32, out: *mut c_void) -> c_int;
     pub fn ashcuda_upload_view(ctx: *mut ashcuda_ctx, depth: *const f32, hdr: *const c_void, velocity: *const c_void) -> c_int;
     pub fn ashcuda_download_view(ctx: *mut ashcuda_ctx, visibility: *mut u32, tile_data: *mut u32, ldr8: *mut u8, stats: *mut AshViewStats, visible_count: *mut u32) -> c_int;
+    pub fn ashcuda_download_view_packed(ctx: *mut ashcuda_ctx, visibility: *mut u32, tile_offsets: *mut u32, tile_lights: *mut u32, tile_lights_capacity: u32, ldr8: *mut u8, stats: *mut AshViewStats, visible_count: *mut u32) -> c_int;
     pub fn ashcuda_get(ctx: *mut ashcuda_ctx, which: c_int, dev_ptr: *mut *mut c_void, bytes: *mut usize) -> c_int;
     pub fn ashcuda_readback(ctx: *mut ashcuda_ctx, which: c_int, host_dst: *mut c_void, bytes: usize) -> c_int;
     pub fn ashcuda_readback_async(ctx: *mut ashcuda_ctx, which: c_int, host_dst: *mut c_void, bytes: usize) -> c_int;

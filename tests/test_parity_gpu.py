@@ -799,7 +799,23 @@ def test_view_io_host_path(backend, oracle):
         c.view_run(_view_params(cam, len(objs), len(lights), 9, W, H, pc, view_id=3))
         c.download_view(o_vis, o_td, o_ldr, o_st, o_cnt)
         c.sync()
+        # the packed (CSR) form of the tile lists; then a destination that is too small, then a malformed call
+        p_vis, p_off, p_lights = np.zeros(len(objs), np.uint32), np.zeros(tiles + 1, np.uint32), np.full(tiles * 8, 0xFFFFFFFF, np.uint32)
+        p_ldr, p_cnt = np.zeros((H, W, 4), np.uint8), np.zeros(1, np.uint32)
+        c.download_view_packed(p_vis, p_off, p_lights, p_ldr, None, p_cnt)
+        c.sync()
+        s_off, small = np.zeros(tiles + 1, np.uint32), np.zeros(4, np.uint32)
+        c.download_view_packed(None, s_off, small)
+        c.sync()
+        with pytest.raises(backend.AshError):
+            c.download_view_packed(None, p_off, None)
     assert np.array_equal(o_vis, vis) and o_cnt[0] == cnt and o_st["view_id"][0] == 3
+    counts = td[:, 0].astype(np.int64)
+    expect = np.concatenate([td[t, 1:1 + counts[t]] for t in range(tiles)]).astype(np.uint32)
+    assert np.array_equal(p_off, np.concatenate([[0], np.cumsum(counts)]).astype(np.uint32)) and int(p_off[-1]) <= len(p_lights)
+    assert np.array_equal(p_lights[:int(p_off[-1])], expect)        # same lists as the 257-stride table, back to back
+    assert np.array_equal(p_vis, vis) and p_cnt[0] == cnt and np.array_equal(p_ldr, o_ldr)
+    assert int(s_off[-1]) == counts.sum() > 4 and np.array_equal(small, expect[:4])   # truncated, total still reported
     _compare_tile_lists(o_td, td)
     assert np.abs(o_ldr.astype(np.int16) - ldr_ref.astype(np.int16)).max() <= 1
 
