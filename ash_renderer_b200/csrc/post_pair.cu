@@ -27,7 +27,9 @@ struct AxisTap { int i0, i1; float f; float pad; };                  // halo-loc
 struct TaaTables { AxisTap col[kT], row[kTH]; float blend; };
 struct TaaRaw { uint2 cur[kHaloH][kHalo], hist[kHaloH][kHalo]; };       // RGBA16F texels, tile + halo
 
-// halo entries beyond the 32-column x kTH-row block: 64 of rows kTH, kTH+1 and 2 * kHaloH of columns 32, 33
+// halo entries beyond the 32-column x kTH-row block: 64 of rows kTH, kTH+1 and 2 * kHaloH of columns 32, 33, one per
+// thread (staging them as packed pairs on half the threads was measured slower: 106.8 vs 105.0 us, it lengthens the
+// two warps that also build the coordinate tables)
 constexpr int kExtraEntries = 64 + 2 * kHaloH, kExtraSlots = (kExtraEntries + kTaaThreads - 1) / kTaaThreads;
 struct StageMap {
     int lane, warp, xr[kExtraSlots], rr[kExtraSlots]; bool extra[kExtraSlots];
