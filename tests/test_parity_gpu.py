@@ -892,6 +892,16 @@ def test_full_size_properties_4k(backend):
         assert not c.bloom_mip(0)[..., :3].any()
 
 
+def test_post_chain_edge_sizes_bit_exact():
+    """tools/sweep_post_sizes.py: bloom chain and TAA at eleven extents chosen for the edges of the tiled kernels (partial
+    tiles, second packed lane out of range, halo clamps, 4K itself), every image bit-exact against the oracle."""
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("sweep_post_sizes", os.path.join(os.path.dirname(__file__), "..", "tools", "sweep_post_sizes.py"))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    assert mod.run(verbose=False) == 0
+
+
 # ------------------------------------------------------------------ error behaviour (AshError mirror)
 def test_error_codes(backend):
     W, H = 64, 64
