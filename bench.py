@@ -474,6 +474,26 @@ def run_cuda(args):
             if not args.two_phase:            # (two-phase draws only the visible objects: a different, history-dependent image)
                 widened["forward_depth_keys_equal_oracle"] = bool(np.array_equal(k0, keys0))
 
+    # ---- latency of ONE view with nothing else in flight (what a single-camera frame loop sees): 20 views, one at a
+    #      time on one slot, device time per view (informational: `value` is throughput with views overlapped)
+    def one_view():
+        c = slots[0]["ctx"]
+        if not args.forward:
+            c.set_depth(slots[0]["d_depth"])
+            c.set_color(slots[0]["d_hdr"], d_vel)
+        c.view_run(slots[0]["vp"])
+    for _ in range(3):
+        one_view()
+    torch.cuda.synchronize()
+    lat = []
+    for _ in range(20):
+        a, b = fence_start(), None
+        one_view()
+        b = fence_stop()
+        torch.cuda.synchronize()
+        lat.append(a.elapsed_time(b))
+    single_view_ms = float(np.median(lat))
+
     # ---- end-to-end through host buffers
     e2e_ms = timed(step_e2e, args.steps, 2)
     e2e_value = total_views * args.steps / (e2e_ms * 1e-3)
@@ -542,7 +562,7 @@ def run_cuda(args):
                    + (" + per-pixel velocity buffer in the TAA (--velocity; resident passes only)" if args.velocity else ""),
                    "views_per_gpu_per_step": B, "distinct_view_inputs_per_gpu": distinct,
                    "streams": args.streams, "concurrent_frontend": True,
-                   "graph_replay": bool(args.graph_replay),
+                   "graph_replay": bool(args.graph_replay), "single_view_latency_ms": single_view_ms,
                    "kernel_timing": f"same {args.steps} steps repeated serialised (1 stream, no fork) with CUDA events around each launch: "
                                     f"{prof_ms / args.steps:.3f} ms/step", "l2": f"inputs larger than L2: {B} views x 99.5 MB of depth+HDR per step per GPU",
                    "visible_fraction_mean": st_mean["visible_objects"] / n_objs,
