@@ -1,4 +1,5 @@
-import json, sys
+import json, sys, signal
+signal.signal(signal.SIGPIPE, signal.SIG_DFL)
 for f in sys.argv[1:]:
     d = json.loads([l for l in open(f) if l.startswith('{')][-1])
     print(f, f"value={d['value']:.0f} ms/step={d['ms_per_step']:.3f} e2e={d['e2e']['value']:.0f} dom={d['roofline']['kernel']} frac={d['roofline']['frac']:.3f} whole_view_frac={d['roofline']['whole_view']['frac']:.3f}")
