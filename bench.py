@@ -574,9 +574,10 @@ def run_cuda(args):
         "gpu_launches": int(round(launches_per_step * args.steps)),
         "roofline": {"bound": "hbm", "kernel": KERNEL_NAMES[dom], "achieved": dom_k["gbs"], "peak": peak, "unit": "GB/s",
                      "frac": dom_k["gbs"] / peak, "traffic": traffic, "traffic_source": NCU_DRAM_SOURCE if traffic else None,
-                     "peak_source": peak_src,
+                     "peak_source": peak_src, "frac_of_nominal_8000_gbs": dom_k["gbs"] / 8000.0,
                      "whole_view": {"alg_bytes_per_view_staged": view_bytes, "gbs": view_bytes / per_view_s / 1e9,
-                                    "frac": view_bytes / per_view_s / 1e9 / peak}},
+                                    "frac": view_bytes / per_view_s / 1e9 / peak,
+                                    "frac_of_nominal_8000_gbs": view_bytes / per_view_s / 1e9 / 8000.0}},
         "kernels": kernels,
         "widened": widened,
         "cpu_baseline": {"value": cpu_v, "unit": UNIT, "cores": cpu_cores, "kind": "port",
