@@ -4,12 +4,13 @@
 // tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs as the
 // checker and the timed CPU baseline.  Nothing under ash_renderer_b200/ may call into this file.
 //
-// PARITY UNPINNED: the reference (saptak7777/Ash-Renderer 0.3.8) holds no golden vectors, tests or
-// CPU implementation for these shaders and cannot be executed here (no Vulkan, no cargo), so this
-// restatement is pinned only by the reference's struct-size / tile-count / Halton unit tests and by
-// its own property tests (tests/test_oracle_*.py).  Conventions the GLSL leaves open are fixed in
-// DESIGN.md "PIN" table; each function cites the shader lines it follows (paths relative to the
-// reference repo).
+// PARITY PINNED TO THE REFERENCE'S SHADER TEXT: the reference (saptak7777/Ash-Renderer 0.3.8) holds no golden
+// vectors or CPU implementation for these shaders and cannot run under Vulkan here, but its GLSL sources compile
+// as C++ behind oracle/ref/glsl_compat.hpp (oracle/_ref/libashref.so, built from /root/reference/shaders where
+// they lie).  tests/test_oracle_ref.py requires this restatement to equal that library bit for bit on all eight
+// shaders, and tests/golden/ref_small.npz holds its outputs.  What the GLSL leaves to the implementation
+// (sampler filtering, evaluation order, image stores) is fixed by the PIN table of SURVEY.md §8.0 / DESIGN.md §2 and
+// is the same in both; each function cites the shader lines it follows (paths relative to the reference repo).
 //
 // Build: g++ -O2 -std=c++17 -fopenmp -ffp-contract=off -fno-fast-math -shared -fPIC  (oracle/Makefile)
 #include <cmath>
@@ -121,6 +122,7 @@ inline vec4 fetch16(const Img16& im, int x, int y) {
     const uint16_t* t = im.p + ((size_t)y * im.W + x) * 4;
     return {h2f(t[0]), h2f(t[1]), h2f(t[2]), h2f(t[3])};
 }
+int g_exact_weights = 0;   // ash_oracle_set_weight_mode: 1 = SURVEY PIN-6 exact fp32 weights, 0 = 8-bit
 inline void bilinear_setup(float u, int W, int& i0, int& i1, float& f) {
     float x = u * (float)W - 0.5f;
     float fl = floorf(x);
@@ -129,7 +131,7 @@ inline void bilinear_setup(float u, int W, int& i0, int& i1, float& f) {
     int i = (int)fl;
     i0 = clampi(i, 0, W - 1);
     i1 = clampi(i + 1, 0, W - 1);
-    f = fq;
+    f = g_exact_weights ? fr : fq;
 }
 inline float lerp1(float a, float b, float f) { return a * (1.0f - f) + b * f; }
 inline vec4 texture16(const Img16& im, float u, float v) {
@@ -559,6 +561,10 @@ void ash_oracle_tonemap(const uint16_t* hdrp, const uint16_t* bloomp, int W, int
             o[3] = 255;
         }
 }
+
+// PIN-6 weight model of the LINEAR sampler: 0 = 8-bit sub-texel weights (what the library implements),
+// 1 = exact fp32 weights (SURVEY.md PIN-6 as first written); tests/test_oracle_ref.py bounds the difference.
+void ash_oracle_set_weight_mode(int exact) { g_exact_weights = exact ? 1 : 0; }
 
 // fp16 helpers exported for the tests (checked against numpy.float16)
 uint16_t ash_oracle_f2h(float f) { return f2h(f); }

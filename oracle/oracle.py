@@ -2,7 +2,7 @@
 
 TEST INFRASTRUCTURE ONLY: imported by tests/, __graft_entry__.smoke() and bench.py's
 cpu_baseline / --impl reference legs.  The product package (ash_renderer_b200/) never imports it.
-Parity is unpinned by the reference (see the header of ash_oracle.cpp).
+Checked bit for bit against the reference's own GLSL compiled as C++ (oracle/ref.py, tests/test_oracle_ref.py).
 """
 import ctypes as C
 import os
@@ -74,6 +74,15 @@ def _c(a, dtype):
 
 def num_threads():
     return int(lib().ash_oracle_num_threads())
+
+
+WEIGHTS_Q8, WEIGHTS_EXACT = 0, 1
+
+
+def set_weight_mode(mode):
+    """PIN-6 LINEAR-sampler weights: WEIGHTS_Q8 (8 fractional bits, the library's model, default) or
+    WEIGHTS_EXACT (fp32 fraction, SURVEY.md PIN-6 as first written)."""
+    lib().ash_oracle_set_weight_mode(int(mode))
 
 
 # ---------------------------------------------------------------- Hi-Z

@@ -1,10 +1,12 @@
-"""Regenerates tests/golden/oracle_small.npz:  python -m tests.golden.make_golden
+"""Regenerates tests/golden/ref_small.npz:  python -m tests.golden.make_golden   (needs /root/reference)
 
-The reference ships no golden vectors for this path and cannot be executed here (GLSL under
-Vulkan; no graphics stack, no cargo), so these are REGRESSION vectors of the CPU oracle on small
-seeded inputs: they pin the oracle against drift, not against the reference ("parity unpinned").
-The GPU parity tests also replay them through the CUDA path (tests/test_parity_gpu.py).
+The vectors are outputs of the REFERENCE'S OWN SHADER SOURCES on small seeded inputs: oracle/_ref/libashref.so is
+/root/reference/shaders/*.comp|*.frag compiled as C++ behind oracle/ref/glsl_compat.hpp (oracle/ref/Makefile).  The
+file records the sha256 of every shader it was generated from.  tests/test_oracle.py checks the CPU oracle against
+them, tests/test_parity_gpu.py replays them through the CUDA path; both run where /root/reference is absent.
+(`tile_minmax` is the shader's shared-memory min/max, not an output: it comes from the oracle.)
 """
+import hashlib
 import os
 
 import numpy as np
@@ -34,13 +36,17 @@ def inputs():
                 taa_pc=taa_pc, post_pc=post_pc)
 
 
-def compute(oracle):
+def compute(oracle, minmax_from=None):
+    """`oracle`: oracle.oracle or oracle.ref (same call signatures)."""
     i = inputs()
     cam = i["cam"]
     mips, flat = oracle.hiz_build(i["depth"])
     pc = cam.cull_pc(len(i["objs"]), min(10, len(mips) + 1))
     vis, dout, cnt = oracle.occlusion_cull(i["objs"], i["draws"], pc, i["depth"], flat)
-    td, true_counts, minmax = oracle.light_cull(i["lights"], cam.light_pc(len(i["lights"])), cam.camera_data(), i["depth"])
+    res = oracle.light_cull(i["lights"], cam.light_pc(len(i["lights"])), cam.camera_data(), i["depth"])
+    td = res[0]
+    minmax = res[2] if len(res) > 2 else minmax_from.light_cull(i["lights"], cam.light_pc(len(i["lights"])),
+                                                                 cam.camera_data(), i["depth"])[2]
     counts = td[:, 0].copy()
     lists = np.concatenate([td[t, 1:1 + counts[t]] for t in range(len(td))])
     taa = oracle.taa_resolve(i["hdr"], i["hist"], i["vel"], i["taa_pc"])
@@ -55,7 +61,16 @@ def compute(oracle):
     return out
 
 
+SHADERS = ["hiz_generate.comp", "occlusion_cull.comp", "light_culling.comp", "taa_resolve.comp",
+           "bloom_threshold.frag", "bloom_downsample.frag", "bloom_upsample.frag", "tonemapping.frag"]
+META = ("shader_names", "shader_sha256", "generator")
+
 if __name__ == "__main__":
-    from oracle import oracle
-    np.savez_compressed(os.path.join(HERE, "oracle_small.npz"), **compute(oracle))
-    print("wrote", os.path.join(HERE, "oracle_small.npz"))
+    from oracle import oracle, ref
+    out = compute(ref, minmax_from=oracle)
+    out["shader_names"] = np.array(SHADERS)
+    out["shader_sha256"] = np.array([hashlib.sha256(open(os.path.join(ref.REFERENCE_SHADERS, s), "rb").read()).hexdigest()
+                                     for s in SHADERS])
+    out["generator"] = np.array("oracle/_ref/libashref.so (reference GLSL compiled as C++, oracle/ref/)")
+    np.savez_compressed(os.path.join(HERE, "ref_small.npz"), **out)
+    print("wrote", os.path.join(HERE, "ref_small.npz"))

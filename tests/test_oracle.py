@@ -10,7 +10,7 @@ import pytest
 
 from ash_renderer_b200 import synth, types as T
 
-GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "oracle_small.npz")
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "ref_small.npz")
 
 
 # ------------------------------------------------------------------ fp16 helpers
@@ -451,9 +451,11 @@ def test_tonemap_known_values(oracle):
 
 # ------------------------------------------------------------------ committed regression vectors
 def test_golden_vectors(oracle):
-    from tests.golden.make_golden import compute
+    """The committed vectors are outputs of the reference's own GLSL (oracle/_ref, tests/golden/make_golden.py)."""
+    from tests.golden.make_golden import compute, META
     g = np.load(GOLDEN)
+    assert "reference GLSL" in str(g["generator"])
     now = compute(oracle)
-    assert sorted(g.files) == sorted(now.keys())
-    for k in g.files:
+    assert sorted(k for k in g.files if k not in META) == sorted(now.keys())
+    for k in now:
         assert np.array_equal(g[k], now[k]), k

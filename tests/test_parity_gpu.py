@@ -14,7 +14,7 @@ from ash_renderer_b200 import synth, types as T
 
 pytestmark = pytest.mark.gpu
 
-GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "oracle_small.npz")
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "ref_small.npz")
 
 
 def _ctx(backend, W, H, **cfg):
