@@ -75,6 +75,7 @@ struct PatchArg {
 };
 void cull_patch(const AshCullingPushConstants& pc, int mode, PatchArg* out);                                   // occlusion_cull.cu
 void taa_pair_patch(bool thresh, bool vel, const AshTaaPushConstants& pc, PatchArg* out);           // post_pair.cu
+void taa_tol_patch(bool thresh, const AshTaaPushConstants& pc, PatchArg* out);                      // post_taa_tol.cu
 bool taa_in_halo(const AshTaaPushConstants& pc);                                                     // post_fast.cu
 void lod_patch(const AshInstancingParams& ip, const AshLodConfig& cfg, PatchArg* out);               // instancing.cu
 void forward_setup_patch(const AshCullingCameraData& cam, PatchArg* out);                            // forward.cu
@@ -269,6 +270,8 @@ cudaError_t launch_taa_fast(const void* cur, const void* hist, const void* vel_o
                             const AshTaaPushConstants& pc, float threshold, const Launch& L);
 cudaError_t launch_taa_pair(const void* cur, const void* hist, const void* vel_or_null, void* out, void* thr_or_null,
                             const AshTaaPushConstants& pc, float threshold, const Launch& L);
+cudaError_t launch_taa_tol(const void* cur, const void* hist, void* out, void* thr_or_null,
+                           const AshTaaPushConstants& pc, float threshold, const Launch& L);                // post_taa_tol.cu (precision = FAST)
 cudaError_t launch_bloom_downsample_fast(const void* src, uint32_t sw, uint32_t sh, void* dst, uint32_t dw,
                                          uint32_t dh, const Launch& L);
 cudaError_t launch_bloom_downsample_pair(const void* src, uint32_t sw, uint32_t sh, void* dst, uint32_t dw,

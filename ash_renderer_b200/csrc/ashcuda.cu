@@ -65,6 +65,7 @@ void ashcuda_default_config(AshCudaConfig* cfg) {
     cfg->concurrent_frontend = 1;
     cfg->max_batches = 64;
     cfg->graph_replay = 1;
+    cfg->precision = ASH_PRECISION_EXACT;
 }
 
 const char* ashcuda_last_error(ashcuda_ctx* ctx) {
@@ -206,7 +207,8 @@ int ashcuda_create(ashcuda_ctx** out, int device, uint32_t width, uint32_t heigh
     c->device = device; c->W = width; c->H = height;
     if (cfg_or_null) c->cfg = *cfg_or_null; else ashcuda_default_config(&c->cfg);
     if (c->cfg.max_batches == 0) c->cfg.max_batches = 64;          // configs written before the field existed
-    if (c->cfg.bloom_mips > ASH_MAX_BLOOM_MIPS || c->cfg.hiz_levels == 0 || c->cfg.max_batches > 128) {
+    if (c->cfg.bloom_mips > ASH_MAX_BLOOM_MIPS || c->cfg.hiz_levels == 0 || c->cfg.max_batches > 128 ||
+        c->cfg.precision > ASH_PRECISION_FAST) {
         g_create_error = "ashcuda_create: bad config"; delete c; return ASH_ERR_INVALID;
     }
     lod_config_default(&c->lod_cfg);
@@ -375,7 +377,10 @@ static int taa_resolve_impl(ashcuda_ctx* c, const AshTaaPushConstants* pc, void*
     void* out = c->taa[c->taa_cur ^ 1];
     const bool exact = taa_taps_exact(c, pc);
     *fused = false;
-    if (exact) {
+    if (exact && c->cfg.precision == ASH_PRECISION_FAST && !c->velocity && taa_in_halo(*pc)) {
+        ASH_CUDA(c, launch_taa_tol(c->color, hist, out, thr_or_null, *pc, threshold, c->L()));   // post_taa_tol.cu
+        *fused = thr_or_null != nullptr;
+    } else if (exact) {
         ASH_CUDA(c, launch_taa_fast(c->color, hist, c->velocity, out, thr_or_null, *pc, threshold, c->L()));
         *fused = thr_or_null != nullptr;
     } else {

@@ -1,0 +1,255 @@
+// post_taa_tol.cu — TAA resolve (+ bloom threshold) in the TOLERANCE precision mode (AshCudaConfig.precision = 1).
+//
+// Same semantics as k_taa_pair (post_pair.cu) and taa_resolve.comp:83-167 / bloom_threshold.frag:18-35, but the
+// colour arithmetic spends the tolerance BASELINE.json's north_star grants the post-processed images instead of
+// reproducing the oracle's IEEE sequence bit for bit (the exact mode, precision = 0, stays the default of the
+// library and the tests): results are within 1 fp16 ulp of the oracle on every texel (tests/test_parity_gpu.py,
+// tolerance-mode cases).  What is relaxed:
+//   * a / b        -> a * MUFU.RCP(b)                 (rcp.approx: 1 ulp of fp32, 2 instructions instead of 7)
+//   * x*k + y      -> one FMA, everywhere             (the exact mode contracts only provably exact products)
+//   * the clip box  center = ctr, half = 1.25 ext + 0.001  (taa_resolve.comp:132-135 then :65-66, algebraically equal)
+//   * clipAABB      center + delta * min(1, min_i(half_i / |delta_i|)), branch-free  (= :68-76)
+//   * 1/(4 knee + 1e-5) of the soft threshold is a compile-time constant.
+// What is NOT relaxed: which texels are sampled and with which weights.  The history coordinates (:92-102, PIN-6 8-bit
+// sub-texel weights) are evaluated per tile column / row exactly as in the exact kernels, the bloom threshold reads
+// the resolved texel as stored (fp16), and a thread only ever combines the texels the shader would.
+//
+// Work split (one CTA = 32 x 16 pixels, 128 threads, thread = 1 x 4 strip of its own column):
+//   * a thread loads ITS OWN four `current` / history texels (+ one halo texel for 100 of the 128 threads); the
+//     `current` texels stay in registers as fp32 and serve both the neighbourhood staging and the resolve's centre
+//     tap, so `current` is never written to shared memory in raw form and is converted from fp16 once;
+//   * tonemapped YCoCg of every texel of tile + halo: once per texel into shared memory (float4);
+//   * history: raw fp16 tile + halo in shared memory, four taps per pixel through the per-tile coordinate tables.
+#include <cstring>
+#include "ash_f32x2.cuh"
+#include "post_math.cuh"
+
+namespace ash {
+
+namespace tol {
+__device__ __forceinline__ P2 add(P2 a, P2 b) { P2 r; asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r.v) : "l"(a.v), "l"(b.v)); return r; }
+__device__ __forceinline__ P2 sub(P2 a, P2 b) { P2 r; asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(r.v) : "l"(a.v), "l"(b.v)); return r; }
+__device__ __forceinline__ P2 mul(P2 a, P2 b) { P2 r; asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r.v) : "l"(a.v), "l"(b.v)); return r; }   // ptxas may contract: welcome here
+__device__ __forceinline__ P2 fma(P2 a, P2 b, P2 c) { P2 r; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r.v) : "l"(a.v), "l"(b.v), "l"(c.v)); return r; }
+__device__ __forceinline__ float rcp(float x) { float r; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+__device__ __forceinline__ P2 rcp(P2 x) { return pk(rcp(lo(x)), rcp(hi(x))); }
+__device__ __forceinline__ P2 rcp_abs(P2 x) { return pk(rcp(fabsf(lo(x))), rcp(fabsf(hi(x)))); }
+struct V3P { P2 x, y, z; };
+__device__ __forceinline__ V3P pk3(V3 a, V3 b) { return {pk(a.x, b.x), pk(a.y, b.y), pk(a.z, b.z)}; }
+
+// c / (1 + c)                                                               taa_resolve.comp:55-57
+__device__ __forceinline__ V3P tonemap(V3P c) {
+    const P2 one = splat(1.0f);
+    return {mul(c.x, rcp(add(c.x, one))), mul(c.y, rcp(add(c.y, one))), mul(c.z, rcp(add(c.z, one)))};
+}
+// (0.25 r + 0.5 g + 0.25 b, 0.5 r - 0.5 b, -0.25 r + 0.5 g - 0.25 b)        :34-40
+__device__ __forceinline__ V3P rgb_to_ycocg(V3P c) {
+    const P2 rb = add(c.x, c.z), hg = mul(c.y, splat(0.5f));
+    return {fma(rb, splat(0.25f), hg), mul(sub(c.x, c.z), splat(0.5f)), fma(rb, splat(-0.25f), hg)};
+}
+// (y + co - cg, y + cg, y - co - cg)                                        :43-52
+__device__ __forceinline__ V3P ycocg_to_rgb(V3P c) {
+    const P2 a = sub(c.x, c.z);
+    return {add(a, c.y), add(c.x, c.z), sub(a, c.y)};
+}
+}  // namespace tol
+
+constexpr int kTolW = 32, kTolH = 16, kTolThreads = 128;          // tile; thread = column tx, rows 4 ty .. 4 ty + 3
+constexpr int kTolHaloW = kTolW + 2, kTolHaloH = kTolH + 2;
+constexpr int kTolExtras = 2 * kTolHaloW + 2 * kTolH;             // halo ring: 100 texels, one per thread 0..99
+static_assert(kTolExtras <= kTolThreads, "one halo texel per thread");
+
+struct TolTap { int i0, i1; float f, pad; };                     // halo-local BYTE offsets (column: 8 i, row: 8 * 34 i), 8-bit weight
+struct TolTables { TolTap col[kTolW], row[kTolH]; float blend, pad[3]; };
+
+// coordinate tables of one tile: taa_resolve.comp:92-102 + PIN-6, the very expressions of the exact kernels
+// (post_pair.cu: taa_tables) — sampling positions are not subject to the tolerance
+__device__ __forceinline__ void tol_tables(TolTables& tb, const AshTaaPushConstants& pc, int W, int H, int x0, int y0) {
+    if (threadIdx.x >= kTolW + kTolH) return;
+    const bool is_row = threadIdx.x >= kTolW;
+    const int k = is_row ? (int)threadIdx.x - kTolW : (int)threadIdx.x;
+    const float ext = is_row ? pc.screen_params[1] : pc.screen_params[0];
+    const int n = is_row ? H : W, p0 = is_row ? y0 : x0;
+    const float jd = is_row ? fsub(pc.jitter[1], pc.prev_jitter[1]) : fsub(pc.jitter[0], pc.prev_jitter[0]);
+    const float u = fdiv_safe(fadd((float)(p0 + k), 0.5f), ext);            // :92
+    const float vel = fdiv_safe(jd, ext);                                    // :97-99
+    const float hu = gclamp(fsub(u, vel), 0.0f, 1.0f);                       // :102
+    TolTap t;
+    bilinear_setup(hu, n, t.i0, t.i1, t.f);
+    const int pitch = is_row ? 8 * kTolHaloW : 8, last = (is_row ? kTolHaloH : kTolHaloW) - 1;
+    t.i0 = min(max(t.i0 - (p0 - 1), 0), last) * pitch;
+    t.i1 = min(max(t.i1 - (p0 - 1), 0), last) * pitch;
+    t.pad = 0.0f;
+    if (is_row) tb.row[k] = t; else tb.col[k] = t;
+    if (threadIdx.x == 0) {                                                  // :145-150
+        float blend = pc.params[0];
+        if (pc.params[2] > 0.5f) {
+            const float sw = pc.screen_params[0], sh = pc.screen_params[1];
+            const float vx = fdiv_safe(fsub(pc.jitter[0], pc.prev_jitter[0]), sw);
+            const float vy = fdiv_safe(fsub(pc.jitter[1], pc.prev_jitter[1]), sh);
+            const float vl = length2(fmul(vx, sw), fmul(vy, sh));
+            blend = fmul(blend, gclamp(fsub(1.0f, fmul(vl, 0.1f)), 0.0f, 1.0f));
+        }
+        tb.blend = blend;
+    }
+}
+
+__device__ __forceinline__ V3 tol_unpack(uint2 t) { V4 v = unpack_rgba16f(t); return {v.x, v.y, v.z}; }
+
+#ifndef ASH_TOL_CTAS
+#define ASH_TOL_CTAS 6
+#endif
+template <bool THRESH>
+__global__ void __launch_bounds__(kTolThreads, ASH_TOL_CTAS)
+k_taa_tol(Tex16 cur, Tex16 hist, uint2* __restrict__ out, uint2* __restrict__ thr, AshTaaPushConstants pc, float threshold) {
+    using namespace tol;
+    __shared__ float4 s_nb[kTolHaloH][kTolHaloW];        // tonemapped YCoCg of `current`, tile + halo
+    __shared__ uint2  s_h[kTolHaloH][kTolHaloW];         // raw history, tile + halo
+    __shared__ TolTables s_tb;
+    const int W = cur.W, H = cur.H;
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    const int x0 = blockIdx.x * kTolW, y0 = blockIdx.y * kTolH;
+    const int x = x0 + tx, yb = y0 + 4 * ty;
+    const bool clamp_on = pc.params[1] > 0.5f;
+
+    V3 c[4];                                             // this thread's own `current` texels, fp32, kept for the resolve
+    {
+        uint2 tc[4], th[4], ec = make_uint2(0u, 0u), eh = make_uint2(0u, 0u);
+        const uint32_t gx = (uint32_t)min(x, W - 1);                                                   // CLAMP_TO_EDGE
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const uint32_t g = (uint32_t)min(yb + k, H - 1) * (uint32_t)W + gx;
+            tc[k] = __ldg(cur.p + g);
+            th[k] = __ldg(hist.p + g);
+        }
+        // halo ring: top row (34), bottom row (34), left column (16), right column (16)
+        const int e = threadIdx.x;
+        const int ex = e < 2 * kTolHaloW ? (e < kTolHaloW ? e : e - kTolHaloW) : (e < 2 * kTolHaloW + kTolH ? 0 : kTolHaloW - 1);
+        const int ey = e < 2 * kTolHaloW ? (e < kTolHaloW ? 0 : kTolHaloH - 1) : 1 + ((e - 2 * kTolHaloW) & (kTolH - 1));
+        const bool extra = e < kTolExtras;
+        if (extra) {
+            const uint32_t g = (uint32_t)min(max(y0 - 1 + ey, 0), H - 1) * (uint32_t)W + (uint32_t)min(max(x0 - 1 + ex, 0), W - 1);
+            ec = __ldg(cur.p + g);
+            eh = __ldg(hist.p + g);
+        }
+        tol_tables(s_tb, pc, W, H, x0, y0);              // while the loads fly
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            s_h[4 * ty + 1 + k][tx + 1] = th[k];
+            c[k] = tol_unpack(tc[k]);
+        }
+        if (extra) s_h[ey][ex] = eh;
+        if (clamp_on) {                                  // :116-121, once per texel
+#pragma unroll
+            for (int k = 0; k < 4; k += 2) {
+                const V3P s = rgb_to_ycocg(tonemap(pk3(c[k], c[k + 1])));
+                s_nb[4 * ty + 1 + k][tx + 1] = make_float4(lo(s.x), lo(s.y), lo(s.z), 0.0f);
+                s_nb[4 * ty + 2 + k][tx + 1] = make_float4(hi(s.x), hi(s.y), hi(s.z), 0.0f);
+            }
+            if (extra) {
+                const V3 q = tol_unpack(ec);
+                const V3 t = {q.x * rcp(1.0f + q.x), q.y * rcp(1.0f + q.y), q.z * rcp(1.0f + q.z)};
+                const float rb = t.x + t.z, hg = 0.5f * t.y;
+                s_nb[ey][ex] = make_float4(fmaf(rb, 0.25f, hg), 0.5f * (t.x - t.z), fmaf(rb, -0.25f, hg), 0.0f);
+            }
+        }
+    }
+    __syncthreads();
+    if (x >= W || yb >= H) return;
+
+    const TolTap col = s_tb.col[tx];
+    const float blend = s_tb.blend;
+    const P2 b2 = splat(blend), ib2 = splat(1.0f - blend);
+    const P2 fx2 = splat(col.f), ifx2 = splat(1.0f - col.f);
+
+    // row-wise min / max of the 3 horizontal neighbours, for the 6 halo rows this strip touches
+    V3 rmn[6], rmx[6];
+    if (clamp_on) {
+#pragma unroll
+        for (int r = 0; r < 6; ++r) {
+            const float4 a = s_nb[4 * ty + r][tx], b = s_nb[4 * ty + r][tx + 1], d = s_nb[4 * ty + r][tx + 2];
+            rmn[r] = {fminf(fminf(a.x, b.x), d.x), fminf(fminf(a.y, b.y), d.y), fminf(fminf(a.z, b.z), d.z)};
+            rmx[r] = {fmaxf(fmaxf(a.x, b.x), d.x), fmaxf(fmaxf(a.y, b.y), d.y), fmaxf(fmaxf(a.z, b.z), d.z)};
+        }
+    }
+    const char* hb = reinterpret_cast<const char*>(&s_h[0][0]);
+#pragma unroll
+    for (int k = 0; k < 4; k += 2) {                     // lanes: lo = row yb + k, hi = row yb + k + 1
+        const int y = yb + k;
+        if (y >= H) break;
+        const TolTap ra = s_tb.row[4 * ty + k], rb = s_tb.row[4 * ty + k + 1];
+        auto tap = [&](int ro, int co) { return tol_unpack(*reinterpret_cast<const uint2*>(hb + ro + co)); };
+        V3P h;                                                                                       // :108 bilinear history
+        {
+            const V3P a  = pk3(tap(ra.i0, col.i0), tap(rb.i0, col.i0));
+            const V3P b  = pk3(tap(ra.i0, col.i1), tap(rb.i0, col.i1));
+            const V3P cc = pk3(tap(ra.i1, col.i0), tap(rb.i1, col.i0));
+            const V3P d  = pk3(tap(ra.i1, col.i1), tap(rb.i1, col.i1));
+            const P2 fy = pk(ra.f, rb.f), ify = sub(splat(1.0f), fy);
+            const V3P top = {fma(b.x, fx2, mul(a.x, ifx2)), fma(b.y, fx2, mul(a.y, ifx2)), fma(b.z, fx2, mul(a.z, ifx2))};
+            const V3P bot = {fma(d.x, fx2, mul(cc.x, ifx2)), fma(d.y, fx2, mul(cc.y, ifx2)), fma(d.z, fx2, mul(cc.z, ifx2))};
+            h = {fma(bot.x, fy, mul(top.x, ify)), fma(bot.y, fy, mul(top.y, ify)), fma(bot.z, fy, mul(top.z, ify))};
+        }
+        if (clamp_on) {                                                                              // :112-142
+            auto mn3 = [&](int r) { return V3{fminf(fminf(rmn[r].x, rmn[r + 1].x), rmn[r + 2].x), fminf(fminf(rmn[r].y, rmn[r + 1].y), rmn[r + 2].y),
+                                              fminf(fminf(rmn[r].z, rmn[r + 1].z), rmn[r + 2].z)}; };
+            auto mx3 = [&](int r) { return V3{fmaxf(fmaxf(rmx[r].x, rmx[r + 1].x), rmx[r + 2].x), fmaxf(fmaxf(rmx[r].y, rmx[r + 1].y), rmx[r + 2].y),
+                                              fmaxf(fmaxf(rmx[r].z, rmx[r + 1].z), rmx[r + 2].z)}; };
+            const V3P mn = pk3(mn3(k), mn3(k + 1)), mx = pk3(mx3(k), mx3(k + 1));
+            const P2 hf = splat(0.5f), e125 = splat(0.625f), eps = splat(0.001f);
+            const V3P ctr = {mul(add(mn.x, mx.x), hf), mul(add(mn.y, mx.y), hf), mul(add(mn.z, mx.z), hf)};
+            const V3P half = {fma(sub(mx.x, mn.x), e125, eps), fma(sub(mx.y, mn.y), e125, eps), fma(sub(mx.z, mn.z), e125, eps)};
+            const V3P hy = rgb_to_ycocg(tonemap(h));
+            const V3P dl = {sub(hy.x, ctr.x), sub(hy.y, ctr.y), sub(hy.z, ctr.z)};
+            // s = min(1, min_i half_i / |delta_i|): 1 inside the box (history kept), 1 / maxV outside (:68-76)
+            const P2 sx = mul(half.x, rcp_abs(dl.x)), sy = mul(half.y, rcp_abs(dl.y)), sz = mul(half.z, rcp_abs(dl.z));
+            const P2 s = pk(fminf(fminf(fminf(lo(sx), lo(sy)), lo(sz)), 1.0f), fminf(fminf(fminf(hi(sx), hi(sy)), hi(sz)), 1.0f));
+            const V3P q = ycocg_to_rgb(V3P{fma(dl.x, s, ctr.x), fma(dl.y, s, ctr.y), fma(dl.z, s, ctr.z)});
+            const P2 k1 = splat(1.0001f);                                                            // (1 - c) + 1e-4, :59-61
+            h = {mul(q.x, rcp(sub(k1, q.x))), mul(q.y, rcp(sub(k1, q.y))), mul(q.z, rcp(sub(k1, q.z)))};
+        }
+        const V3P cp = pk3(c[k], c[k + 1]);
+        const V3P o = {fma(h.x, b2, mul(cp.x, ib2)), fma(h.y, b2, mul(cp.y, ib2)), fma(h.z, b2, mul(cp.z, ib2))};   // mix(), :159
+        const uint2 oa = pack_rgba16f(lo(o.x), lo(o.y), lo(o.z), 1.0f), ob = pack_rgba16f(hi(o.x), hi(o.y), hi(o.z), 1.0f);
+        const bool has_b = y + 1 < H;
+        const uint32_t o0 = (uint32_t)y * (uint32_t)W + (uint32_t)x, o1 = o0 + (uint32_t)W;
+        out[o0] = oa;
+        if (has_b) out[o1] = ob;
+        if (THRESH) {                                    // bloom_threshold.frag:18-27 of the resolved texel AS STORED (fp16)
+            const V3 ta = tol_unpack(oa), tb = tol_unpack(ob);
+            const P2 br = pk(fmaxf(fmaxf(ta.x, ta.y), ta.z), fmaxf(fmaxf(tb.x, tb.y), tb.z));
+            const P2 over = sub(br, splat(threshold));                               // brightness - threshold
+            const P2 sf = add(over, splat(0.5f));                                    // + knee
+            const P2 sc = pk(fminf(fmaxf(lo(sf), 0.0f), 1.0f), fminf(fmaxf(hi(sf), 0.0f), 1.0f));
+            const P2 soft = mul(mul(sc, sc), splat(1.0f / 2.00001f));                // soft^2 / (4 knee + 1e-5)
+            const P2 ct = pk(fmaxf(lo(soft), lo(over)), fmaxf(hi(soft), hi(over)));
+            const P2 w = mul(ct, pk(rcp(fmaxf(lo(br), 0.00001f)), rcp(fmaxf(hi(br), 0.00001f))));
+            const V3P t3 = pk3(ta, tb);
+            const P2 bx = mul(t3.x, w), by = mul(t3.y, w), bz = mul(t3.z, w);
+            thr[o0] = pack_rgba16f(lo(bx), lo(by), lo(bz), 1.0f);
+            if (has_b) thr[o1] = pack_rgba16f(hi(bx), hi(by), hi(bz), 1.0f);
+        }
+    }
+}
+
+// graph replay: argument 4 of k_taa_tol is the per-view AshTaaPushConstants
+void taa_tol_patch(bool thresh, const AshTaaPushConstants& pc, PatchArg* out) {
+    out->func = thresh ? reinterpret_cast<const void*>(&k_taa_tol<true>) : reinterpret_cast<const void*>(&k_taa_tol<false>);
+    out->arg_index = 4; out->n_args = 6;
+    std::memcpy(out->value, &pc, sizeof(pc));
+}
+
+cudaError_t launch_taa_tol(const void* cur, const void* hist, void* out, void* thr_or_null,
+                           const AshTaaPushConstants& pc, float threshold, const Launch& L) {
+    const int W = (int)pc.screen_params[0], H = (int)pc.screen_params[1];
+    const Tex16 c{static_cast<const uint2*>(cur), W, H}, h{static_cast<const uint2*>(hist), W, H};
+    const dim3 grid((W + kTolW - 1) / kTolW, (H + kTolH - 1) / kTolH);
+    uint2* o = static_cast<uint2*>(out);
+    uint2* t = static_cast<uint2*>(thr_or_null);
+    Timed timed(L, thr_or_null ? ASH_KERNEL_TAA_THRESHOLD : ASH_KERNEL_TAA);
+    if (t) k_taa_tol<true><<<grid, kTolThreads, 0, L.s>>>(c, h, o, t, pc, threshold);
+    else   k_taa_tol<false><<<grid, kTolThreads, 0, L.s>>>(c, h, o, t, pc, threshold);
+    return cudaGetLastError();
+}
+
+}  // namespace ash

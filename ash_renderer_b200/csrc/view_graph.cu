@@ -73,7 +73,11 @@ void make_patches(const ashcuda_ctx* c, const AshCudaViewParams* vp, Patches* P)
     P->has_cull2 = P->has_cull && (st & ASH_STAGE_TWO_PHASE);
     if (P->has_cull) cull_patch(vp->cull, P->has_cull2 ? 1 : 0, &P->cull);
     if (P->has_cull2) cull_patch(vp->cull, 2, &P->cull2);
-    if (P->has_taa) taa_pair_patch((st & ASH_STAGE_BLOOM) != 0, c->velocity != nullptr && !(st & ASH_STAGE_FORWARD_SHADE), vp->taa, &P->taa);
+    if (P->has_taa) {
+        const bool vel = c->velocity != nullptr && !(st & ASH_STAGE_FORWARD_SHADE);
+        if (c->cfg.precision == ASH_PRECISION_FAST && !vel && taa_in_halo(vp->taa)) taa_tol_patch((st & ASH_STAGE_BLOOM) != 0, vp->taa, &P->taa);
+        else taa_pair_patch((st & ASH_STAGE_BLOOM) != 0, vel, vp->taa, &P->taa);
+    }
     if (P->has_lod) {
         AshInstancingParams ip{};
         std::memcpy(ip.view_proj, vp->cull.view_proj, sizeof(ip.view_proj));

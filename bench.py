@@ -312,7 +312,7 @@ def run_cuda(args):
     for v in range(B):
         cam, depth, hdr = host_views[v % distinct]
         c = backend.Context(W, H, device=local, max_objects=n_objs, max_lights=n_lights, hiz_levels=HIZ_LEVELS,
-                            graph_replay=args.graph_replay)
+                            graph_replay=args.graph_replay, precision=T.PRECISION_FAST if args.precision == "fast" else T.PRECISION_EXACT)
         c.set_stream(streams[v % args.streams].cuda_stream)
         c.set_objects(d_objs, d_draws)
         c.upload_lights(d_lights)
@@ -562,7 +562,7 @@ def run_cuda(args):
                    + (" + per-pixel velocity buffer in the TAA (--velocity; resident passes only)" if args.velocity else ""),
                    "views_per_gpu_per_step": B, "distinct_view_inputs_per_gpu": distinct,
                    "streams": args.streams, "concurrent_frontend": True,
-                   "graph_replay": bool(args.graph_replay), "single_view_latency_ms": single_view_ms,
+                   "graph_replay": bool(args.graph_replay), "precision": args.precision, "single_view_latency_ms": single_view_ms,
                    "kernel_timing": f"same {args.steps} steps repeated serialised (1 stream, no fork) with CUDA events around each launch: "
                                     f"{prof_ms / args.steps:.3f} ms/step", "l2": f"inputs larger than L2: {B} views x 99.5 MB of depth+HDR per step per GPU",
                    "visible_fraction_mean": st_mean["visible_objects"] / n_objs,
@@ -618,6 +618,9 @@ def main():
     ap.add_argument("--cpu-views", type=int, default=2)
     ap.add_argument("--graph-replay", type=int, default=1, choices=[0, 1],
                     help="1: view_run replays a captured CUDA graph per view (library default); 0: launches every kernel")
+    ap.add_argument("--precision", default="exact", choices=["exact", "fast"],
+                    help="exact: every image bit-identical to the CPU oracle; fast: the tolerance north_star grants the images "
+                         "(<= 1 fp16 ulp, <= 1 LSB), licensed by tests/test_precision_fast_gpu.py")
     ap.add_argument("--forward", action="store_true",
                     help="widened path (SURVEY 8.6 row f-1): depth and HDR colour are produced on the device from the cull objects "
                          "and the tile light lists instead of being uploaded; not the headline workload")

@@ -239,8 +239,15 @@ typedef struct AshCudaConfig {
     uint32_t graph_replay;    /* 1 (default): view_run captures the view into a CUDA graph once and replays it,
                                  patching the per-view kernel arguments; 0: launch every kernel each view.
                                  Same kernels, same results either way (csrc/view_graph.cu)                 */
-    uint32_t _reserved[6];
+    uint32_t precision;       /* ASH_PRECISION_EXACT (0, default): every image bit-identical to the reference semantics
+                                 as the CPU oracle states them; ASH_PRECISION_FAST (1): the post-chain colour
+                                 arithmetic spends the tolerance BASELINE.json's north_star grants (images within
+                                 1 fp16 ulp, 8-bit output within 1 LSB): approximate reciprocals, FMA contraction.
+                                 Sampling positions / weights, visibility and light lists are exact in both modes. */
+    uint32_t _reserved[5];
 } AshCudaConfig;
+#define ASH_PRECISION_EXACT 0u
+#define ASH_PRECISION_FAST  1u
 
 /* Per-view statistics (OcclusionStats, occlusion_culling.rs:152-185 + tile list stats).
  * This 32-byte record is the only thing exchanged between GPUs (allgather). */
