@@ -75,7 +75,10 @@ struct PatchArg {
 };
 void cull_patch(const AshCullingPushConstants& pc, int mode, PatchArg* out);                                   // occlusion_cull.cu
 void taa_pair_patch(bool thresh, bool vel, const AshTaaPushConstants& pc, PatchArg* out);           // post_pair.cu
-void taa_tol_patch(bool thresh, const AshTaaPushConstants& pc, PatchArg* out);                      // post_taa_tol.cu
+// per-view argument block of k_taa_tol (post_taa_tol.cu, precision = FAST).  regular: the host verified that the history
+// taps of every column / row are texels clamp(p + d), clamp(p + d + 1) with one weight per axis (exact_taps.cu)
+struct TaaTolArgs { AshTaaPushConstants pc; int dx, dy; float fx, fy, blend, threshold; uint32_t regular; };
+void taa_tol_patch(bool thresh, const TaaTolArgs& a, PatchArg* out);                                // post_taa_tol.cu
 bool taa_in_halo(const AshTaaPushConstants& pc);                                                     // post_fast.cu
 void lod_patch(const AshInstancingParams& ip, const AshLodConfig& cfg, PatchArg* out);               // instancing.cu
 void forward_setup_patch(const AshCullingCameraData& cam, PatchArg* out);                            // forward.cu
@@ -87,7 +90,7 @@ struct GraphKey {
     AshLightCullingPushConstants light;
     float    taa_screen[4];
     AshBloomParams bloom; AshPostProcessPushConstants post;
-    uint32_t in_halo, taa_cur, history_valid, taa_ran, have_color, have_depth, have_instancing, concurrent, have_pyramid;
+    uint32_t in_halo, tol_variant, taa_cur, history_valid, taa_ran, have_color, have_depth, have_instancing, concurrent, have_pyramid;
     AshForwardParams fwd;
 };
 struct ViewGraph {
@@ -204,6 +207,7 @@ struct ashcuda_ctx {
     bool        center_exact = false;          // (x+0.5)/W taps hit texel x exactly (exact_taps.cu)
     float       taa_chk[4] = {0, 0, 0, 0};     // screen_params the TAA tap check was last run for
     bool        taa_exact = false;
+    std::vector<ash::TaaTolArgs> tol_plans;    // precision = FAST: history-tap plans by push constants (a Halton period has 16)
 };
 
 namespace ash {
@@ -270,8 +274,8 @@ cudaError_t launch_taa_fast(const void* cur, const void* hist, const void* vel_o
                             const AshTaaPushConstants& pc, float threshold, const Launch& L);
 cudaError_t launch_taa_pair(const void* cur, const void* hist, const void* vel_or_null, void* out, void* thr_or_null,
                             const AshTaaPushConstants& pc, float threshold, const Launch& L);
-cudaError_t launch_taa_tol(const void* cur, const void* hist, void* out, void* thr_or_null,
-                           const AshTaaPushConstants& pc, float threshold, const Launch& L);                // post_taa_tol.cu (precision = FAST)
+cudaError_t launch_taa_tol(const void* cur, const void* hist, void* out, void* thr_or_null, const TaaTolArgs& a,
+                           const Launch& L);                                                                 // post_taa_tol.cu (precision = FAST)
 cudaError_t launch_bloom_downsample_fast(const void* src, uint32_t sw, uint32_t sh, void* dst, uint32_t dw,
                                          uint32_t dh, const Launch& L);
 cudaError_t launch_bloom_downsample_pair(const void* src, uint32_t sw, uint32_t sh, void* dst, uint32_t dw,
@@ -295,6 +299,8 @@ bool axis_center_exact(int n, float size_f);
 bool axis_taa_taps_exact(int n, float size_f, float inv);
 bool axis_down_taps_exact(int sn, int dn);
 bool axis_up_taps_exact(int sn, int dn);
+bool axis_taa_history_regular(int n, float size_f, float jitter_delta, int* d_out, float* f_out);
+float taa_uniform_blend(const AshTaaPushConstants& pc);
 
 }  // namespace ash
 
@@ -312,3 +318,4 @@ int  ash_view_run_eager(ashcuda_ctx* c, const AshCudaViewParams* vp);
 int  ash_view_run_graph(ashcuda_ctx* c, const AshCudaViewParams* vp, bool* handled);
 void ash_view_graphs_destroy(ashcuda_ctx* c);
 int  ash_forward_alloc(ashcuda_ctx* c);
+const ash::TaaTolArgs& ash_taa_tol_plan(ashcuda_ctx* c, const AshTaaPushConstants& pc, float threshold, ash::TaaTolArgs* scratch);

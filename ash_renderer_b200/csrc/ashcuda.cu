@@ -378,7 +378,8 @@ static int taa_resolve_impl(ashcuda_ctx* c, const AshTaaPushConstants* pc, void*
     const bool exact = taa_taps_exact(c, pc);
     *fused = false;
     if (exact && c->cfg.precision == ASH_PRECISION_FAST && !c->velocity && taa_in_halo(*pc)) {
-        ASH_CUDA(c, launch_taa_tol(c->color, hist, out, thr_or_null, *pc, threshold, c->L()));   // post_taa_tol.cu
+        TaaTolArgs ta;
+        ASH_CUDA(c, launch_taa_tol(c->color, hist, out, thr_or_null, ash_taa_tol_plan(c, *pc, threshold, &ta), c->L()));   // post_taa_tol.cu
         *fused = thr_or_null != nullptr;
     } else if (exact) {
         ASH_CUDA(c, launch_taa_fast(c->color, hist, c->velocity, out, thr_or_null, *pc, threshold, c->L()));
@@ -848,6 +849,7 @@ int ashcuda_debug_exact_taps(int kind, int n_src, int n_dst, float size_f, float
         case 1: return axis_taa_taps_exact(n_dst, size_f, inv) ? 1 : 0;
         case 2: return axis_down_taps_exact(n_src, n_dst) ? 1 : 0;
         case 3: return axis_up_taps_exact(n_src, n_dst) ? 1 : 0;
+        case 4: { int d; float f; return axis_taa_history_regular(n_dst, size_f, inv, &d, &f) ? 1 : 0; }
         default: return 0;
     }
 }

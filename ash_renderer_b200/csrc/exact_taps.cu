@@ -8,6 +8,7 @@
 // every row/column of an extent once, and only then lets a fast kernel replace the general one.
 // O(W + H) per check; results are cached in the context.
 #include "ash_internal.cuh"
+#include <cstring>
 #include "ash_math.cuh"
 
 namespace ash {
@@ -73,4 +74,63 @@ bool axis_up_taps_exact(int sn, int dn) {
     return true;
 }
 
+// taa_resolve.comp:92-108 without a velocity buffer: historyUV = clamp(uv - jitterDelta / size, 0, 1) on one axis.
+// "Regular": every p samples texels clamp(p + d), clamp(p + d + 1) with ONE weight f (where both taps are the same texel
+// the weight does not matter).  True for almost every jitter delta; false when the delta sits so close to a multiple of
+// 1/256 texel (or to 0) that the fp32 noise of (p + 0.5) / n * n moves single columns to the neighbouring weight / texel.
+bool axis_taa_history_regular(int n, float size_f, float jitter_delta, int* d_out, float* f_out) {
+    if (jitter_delta == 0.0f && axis_center_exact(n, size_f)) {     // historyUV == uv and that tap IS texel p: weight 0 on p + 1
+        *d_out = 0; *f_out = 0.0f;
+        return true;
+    }
+    const float vel = fdiv(jitter_delta, size_f);
+    int d = 0; float f0 = 0.0f; bool have = false;
+    for (int pass = 0; pass < 2; ++pass)
+        for (int p = 0; p < n; ++p) {
+            const float u = fdiv(fadd((float)p, 0.5f), size_f);
+            const float hu = gclamp(fsub(u, vel), 0.0f, 1.0f);
+            int i0, i1; float f;
+            bilinear_setup(hu, n, i0, i1, f);
+            if (pass == 0) { if (i0 != i1) { d = i0 - p; f0 = f; have = true; break; } }
+            else if (i0 != clampi(p + d, n) || i1 != clampi(p + d + 1, n) || (i0 != i1 && f != f0)) return false;
+        }
+    if (!have && n > 1) return false;
+    if (d < -1 || d > 0) return false;                     // taps must stay inside the 1-texel halo of a tile
+    *d_out = d; *f_out = f0;
+    return true;
+}
+
+// the blend factor of a frame without velocity buffer (:145-150): velocity = jitter delta / size, uniform
+float taa_uniform_blend(const AshTaaPushConstants& pc) {
+    float blend = pc.params[0];
+    if (pc.params[2] > 0.5f) {
+        const float sw = pc.screen_params[0], sh = pc.screen_params[1];
+        const float vx = fdiv(fsub(pc.jitter[0], pc.prev_jitter[0]), sw);
+        const float vy = fdiv(fsub(pc.jitter[1], pc.prev_jitter[1]), sh);
+        const float vl = fsqrt(fadd(fmul(fmul(vx, sw), fmul(vx, sw)), fmul(fmul(vy, sh), fmul(vy, sh))));
+        blend = fmul(blend, gclamp(fsub(1.0f, fmul(vl, 0.1f)), 0.0f, 1.0f));
+    }
+    return blend;
+}
+
 }  // namespace ash
+
+using namespace ash;
+
+// precision = FAST: the argument block of k_taa_tol for these push constants; the O(W + H) regularity check of the history
+// taps runs once per distinct (screenParams, jitter, prevJitter) and is cached (a Halton period has 16 of them)
+const TaaTolArgs& ash_taa_tol_plan(ashcuda_ctx* c, const AshTaaPushConstants& pc, float threshold, TaaTolArgs* scratch) {
+    for (TaaTolArgs& p : c->tol_plans)
+        if (memcmp(&p.pc, &pc, sizeof(pc)) == 0) { *scratch = p; scratch->threshold = threshold; return *scratch; }
+    TaaTolArgs a{};
+    a.pc = pc;
+    a.blend = taa_uniform_blend(pc);
+    const bool rx = axis_taa_history_regular((int)c->W, pc.screen_params[0], fsub(pc.jitter[0], pc.prev_jitter[0]), &a.dx, &a.fx);
+    const bool ry = axis_taa_history_regular((int)c->H, pc.screen_params[1], fsub(pc.jitter[1], pc.prev_jitter[1]), &a.dy, &a.fy);
+    a.regular = (rx && ry) ? 1u : 0u;
+    if (c->tol_plans.size() >= 64) c->tol_plans.erase(c->tol_plans.begin());
+    c->tol_plans.push_back(a);
+    *scratch = a; scratch->threshold = threshold;
+    return *scratch;
+}
+

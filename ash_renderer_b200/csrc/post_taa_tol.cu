@@ -96,12 +96,122 @@ __device__ __forceinline__ void tol_tables(TolTables& tb, const AshTaaPushConsta
 
 __device__ __forceinline__ V3 tol_unpack(uint2 t) { V4 v = unpack_rgba16f(t); return {v.x, v.y, v.z}; }
 
+// ---- stage: own texels + halo ring -> s_h (raw history), s_nb (tonemapped YCoCg of `current`); returns the thread's own
+// `current` texels as fp32
+__device__ __forceinline__ void tol_stage(const Tex16& cur, const Tex16& hist, float4 (*s_nb)[kTolHaloW], uint2 (*s_h)[kTolHaloW],
+                                          int x0, int y0, int tx, int ty, bool clamp_on, V3 (&c)[4]) {
+    using namespace tol;
+    const int W = cur.W, H = cur.H;
+    uint2 tc[4], th[4], ec = make_uint2(0u, 0u), eh = make_uint2(0u, 0u);
+    const uint32_t gx = (uint32_t)min(x0 + tx, W - 1);                                                 // CLAMP_TO_EDGE
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const uint32_t g = (uint32_t)min(y0 + 4 * ty + k, H - 1) * (uint32_t)W + gx;
+        tc[k] = __ldg(cur.p + g);
+        th[k] = __ldg(hist.p + g);
+    }
+    // halo ring: top row (34), bottom row (34), left column (16), right column (16)
+    const int e = threadIdx.x;
+    const int ex = e < 2 * kTolHaloW ? (e < kTolHaloW ? e : e - kTolHaloW) : (e < 2 * kTolHaloW + kTolH ? 0 : kTolHaloW - 1);
+    const int ey = e < 2 * kTolHaloW ? (e < kTolHaloW ? 0 : kTolHaloH - 1) : 1 + ((e - 2 * kTolHaloW) & (kTolH - 1));
+    const bool extra = e < kTolExtras;
+    if (extra) {
+        const uint32_t g = (uint32_t)min(max(y0 - 1 + ey, 0), H - 1) * (uint32_t)W + (uint32_t)min(max(x0 - 1 + ex, 0), W - 1);
+        ec = __ldg(cur.p + g);
+        eh = __ldg(hist.p + g);
+    }
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        s_h[4 * ty + 1 + k][tx + 1] = th[k];
+        c[k] = tol_unpack(tc[k]);
+    }
+    if (extra) s_h[ey][ex] = eh;
+    if (clamp_on) {                                      // :116-121, once per texel
+#pragma unroll
+        for (int k = 0; k < 2; ++k) {                    // lanes: rows k and k + 2 (the pairing of the resolve)
+            const V3P s = rgb_to_ycocg(tonemap(pk3(c[k], c[k + 2])));
+            s_nb[4 * ty + 1 + k][tx + 1] = make_float4(lo(s.x), lo(s.y), lo(s.z), 0.0f);
+            s_nb[4 * ty + 3 + k][tx + 1] = make_float4(hi(s.x), hi(s.y), hi(s.z), 0.0f);
+        }
+        if (extra) {
+            const V3 q = tol_unpack(ec);
+            const V3 t = {q.x * rcp(1.0f + q.x), q.y * rcp(1.0f + q.y), q.z * rcp(1.0f + q.z)};
+            const float rb = t.x + t.z, hg = 0.5f * t.y;
+            s_nb[ey][ex] = make_float4(fmaf(rb, 0.25f, hg), 0.5f * (t.x - t.z), fmaf(rb, -0.25f, hg), 0.0f);
+        }
+    }
+}
+
+// ---- min / max of the 3x3 neighbourhood of the strip's four pixels (:124-129): row-wise over the three horizontal
+// neighbours for the six halo rows the strip touches, then column-wise
+__device__ __forceinline__ void tol_neighbourhood(const float4 (*s_nb)[kTolHaloW], int tx, int ty, V3 (&mn)[4], V3 (&mx)[4]) {
+    V3 rmn[6], rmx[6];
+#pragma unroll
+    for (int r = 0; r < 6; ++r) {
+        const float4 a = s_nb[4 * ty + r][tx], b = s_nb[4 * ty + r][tx + 1], d = s_nb[4 * ty + r][tx + 2];
+        rmn[r] = {fminf(fminf(a.x, b.x), d.x), fminf(fminf(a.y, b.y), d.y), fminf(fminf(a.z, b.z), d.z)};
+        rmx[r] = {fmaxf(fmaxf(a.x, b.x), d.x), fmaxf(fmaxf(a.y, b.y), d.y), fmaxf(fmaxf(a.z, b.z), d.z)};
+    }
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        mn[k] = {fminf(fminf(rmn[k].x, rmn[k + 1].x), rmn[k + 2].x), fminf(fminf(rmn[k].y, rmn[k + 1].y), rmn[k + 2].y),
+                 fminf(fminf(rmn[k].z, rmn[k + 1].z), rmn[k + 2].z)};
+        mx[k] = {fmaxf(fmaxf(rmx[k].x, rmx[k + 1].x), rmx[k + 2].x), fmaxf(fmaxf(rmx[k].y, rmx[k + 1].y), rmx[k + 2].y),
+                 fmaxf(fmaxf(rmx[k].z, rmx[k + 1].z), rmx[k + 2].z)};
+    }
+}
+
+// ---- clip the history of two pixels to their neighbourhood boxes, blend, store, threshold (:112-162 + bloom_threshold.frag)
+template <bool THRESH>
+__device__ __forceinline__ void tol_finish_pair(tol::V3P h, tol::V3P cp, bool clamp_on, tol::V3P mn, tol::V3P mx, P2 b2, P2 ib2,
+                                                uint32_t o0, uint32_t o1, bool has1, uint2* __restrict__ out,
+                                                uint2* __restrict__ thr, float threshold) {
+    using namespace tol;
+    if (clamp_on) {
+        const P2 hf = splat(0.5f), e125 = splat(0.625f), eps = splat(0.001f);
+        const V3P ctr = {mul(add(mn.x, mx.x), hf), mul(add(mn.y, mx.y), hf), mul(add(mn.z, mx.z), hf)};
+        const V3P half = {fma(sub(mx.x, mn.x), e125, eps), fma(sub(mx.y, mn.y), e125, eps), fma(sub(mx.z, mn.z), e125, eps)};
+        const V3P hy = rgb_to_ycocg(tonemap(h));
+        const V3P dl = {sub(hy.x, ctr.x), sub(hy.y, ctr.y), sub(hy.z, ctr.z)};
+        // s = min(1, min_i half_i / |delta_i|): 1 inside the box (history kept), 1 / maxV outside (:68-76)
+        const P2 sx = mul(half.x, rcp_abs(dl.x)), sy = mul(half.y, rcp_abs(dl.y)), sz = mul(half.z, rcp_abs(dl.z));
+        const P2 s = pk(fminf(fminf(fminf(lo(sx), lo(sy)), lo(sz)), 1.0f), fminf(fminf(fminf(hi(sx), hi(sy)), hi(sz)), 1.0f));
+        const V3P q = ycocg_to_rgb(V3P{fma(dl.x, s, ctr.x), fma(dl.y, s, ctr.y), fma(dl.z, s, ctr.z)});
+        const P2 k1 = splat(1.0001f);                                                                // (1 - c) + 1e-4, :59-61
+        h = {mul(q.x, rcp(sub(k1, q.x))), mul(q.y, rcp(sub(k1, q.y))), mul(q.z, rcp(sub(k1, q.z)))};
+    }
+    const V3P o = {fma(h.x, b2, mul(cp.x, ib2)), fma(h.y, b2, mul(cp.y, ib2)), fma(h.z, b2, mul(cp.z, ib2))};       // mix(), :159
+    const uint2 oa = pack_rgba16f(lo(o.x), lo(o.y), lo(o.z), 1.0f), ob = pack_rgba16f(hi(o.x), hi(o.y), hi(o.z), 1.0f);
+    out[o0] = oa;
+    if (has1) out[o1] = ob;
+    if (THRESH) {                                        // bloom_threshold.frag:18-27 of the resolved texel AS STORED (fp16)
+        const V3 ta = tol_unpack(oa), tb = tol_unpack(ob);
+        const P2 br = pk(fmaxf(fmaxf(ta.x, ta.y), ta.z), fmaxf(fmaxf(tb.x, tb.y), tb.z));
+        const P2 over = sub(br, splat(threshold));                               // brightness - threshold
+        const P2 sf = add(over, splat(0.5f));                                    // + knee
+        const P2 sc = pk(fminf(fmaxf(lo(sf), 0.0f), 1.0f), fminf(fmaxf(hi(sf), 0.0f), 1.0f));
+        const P2 soft = mul(mul(sc, sc), splat(1.0f / 2.00001f));                // soft^2 / (4 knee + 1e-5)
+        const P2 ct = pk(fmaxf(lo(soft), lo(over)), fmaxf(hi(soft), hi(over)));
+        const P2 w = mul(ct, pk(rcp(fmaxf(lo(br), 0.00001f)), rcp(fmaxf(hi(br), 0.00001f))));
+        const V3P t3 = pk3(ta, tb);
+        const P2 bx = mul(t3.x, w), by = mul(t3.y, w), bz = mul(t3.z, w);
+        thr[o0] = pack_rgba16f(lo(bx), lo(by), lo(bz), 1.0f);
+        if (has1) thr[o1] = pack_rgba16f(hi(bx), hi(by), hi(bz), 1.0f);
+    }
+}
+
 #ifndef ASH_TOL_CTAS
 #define ASH_TOL_CTAS 6
 #endif
-template <bool THRESH>
+// REGULAR = false: history taps through per-tile coordinate tables (any jitter delta inside the halo).
+// REGULAR = true : the host has verified (exact_taps.cu: axis_taa_history_regular, the same fp32 expressions) that every
+//   column samples texels clamp(x + dx), clamp(x + dx + 1) with ONE weight fx and every row clamp(y + dy), clamp(y + dy + 1)
+//   with ONE weight fy — the usual case, the jitter delta being uniform over the frame.  Then the five history rows a
+//   strip touches are lerped horizontally once and shared by vertically adjacent pixels, no table is built, and every
+//   shared-memory address is a compile-time offset from one base.
+template <bool THRESH, bool REGULAR>
 __global__ void __launch_bounds__(kTolThreads, ASH_TOL_CTAS)
-k_taa_tol(Tex16 cur, Tex16 hist, uint2* __restrict__ out, uint2* __restrict__ thr, AshTaaPushConstants pc, float threshold) {
+k_taa_tol(Tex16 cur, Tex16 hist, uint2* __restrict__ out, uint2* __restrict__ thr, TaaTolArgs a) {
     using namespace tol;
     __shared__ float4 s_nb[kTolHaloH][kTolHaloW];        // tonemapped YCoCg of `current`, tile + halo
     __shared__ uint2  s_h[kTolHaloH][kTolHaloW];         // raw history, tile + halo
@@ -110,146 +220,85 @@ k_taa_tol(Tex16 cur, Tex16 hist, uint2* __restrict__ out, uint2* __restrict__ th
     const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
     const int x0 = blockIdx.x * kTolW, y0 = blockIdx.y * kTolH;
     const int x = x0 + tx, yb = y0 + 4 * ty;
-    const bool clamp_on = pc.params[1] > 0.5f;
+    const bool clamp_on = a.pc.params[1] > 0.5f;
 
     V3 c[4];                                             // this thread's own `current` texels, fp32, kept for the resolve
-    {
-        uint2 tc[4], th[4], ec = make_uint2(0u, 0u), eh = make_uint2(0u, 0u);
-        const uint32_t gx = (uint32_t)min(x, W - 1);                                                   // CLAMP_TO_EDGE
-#pragma unroll
-        for (int k = 0; k < 4; ++k) {
-            const uint32_t g = (uint32_t)min(yb + k, H - 1) * (uint32_t)W + gx;
-            tc[k] = __ldg(cur.p + g);
-            th[k] = __ldg(hist.p + g);
-        }
-        // halo ring: top row (34), bottom row (34), left column (16), right column (16)
-        const int e = threadIdx.x;
-        const int ex = e < 2 * kTolHaloW ? (e < kTolHaloW ? e : e - kTolHaloW) : (e < 2 * kTolHaloW + kTolH ? 0 : kTolHaloW - 1);
-        const int ey = e < 2 * kTolHaloW ? (e < kTolHaloW ? 0 : kTolHaloH - 1) : 1 + ((e - 2 * kTolHaloW) & (kTolH - 1));
-        const bool extra = e < kTolExtras;
-        if (extra) {
-            const uint32_t g = (uint32_t)min(max(y0 - 1 + ey, 0), H - 1) * (uint32_t)W + (uint32_t)min(max(x0 - 1 + ex, 0), W - 1);
-            ec = __ldg(cur.p + g);
-            eh = __ldg(hist.p + g);
-        }
-        tol_tables(s_tb, pc, W, H, x0, y0);              // while the loads fly
-#pragma unroll
-        for (int k = 0; k < 4; ++k) {
-            s_h[4 * ty + 1 + k][tx + 1] = th[k];
-            c[k] = tol_unpack(tc[k]);
-        }
-        if (extra) s_h[ey][ex] = eh;
-        if (clamp_on) {                                  // :116-121, once per texel
-#pragma unroll
-            for (int k = 0; k < 4; k += 2) {
-                const V3P s = rgb_to_ycocg(tonemap(pk3(c[k], c[k + 1])));
-                s_nb[4 * ty + 1 + k][tx + 1] = make_float4(lo(s.x), lo(s.y), lo(s.z), 0.0f);
-                s_nb[4 * ty + 2 + k][tx + 1] = make_float4(hi(s.x), hi(s.y), hi(s.z), 0.0f);
-            }
-            if (extra) {
-                const V3 q = tol_unpack(ec);
-                const V3 t = {q.x * rcp(1.0f + q.x), q.y * rcp(1.0f + q.y), q.z * rcp(1.0f + q.z)};
-                const float rb = t.x + t.z, hg = 0.5f * t.y;
-                s_nb[ey][ex] = make_float4(fmaf(rb, 0.25f, hg), 0.5f * (t.x - t.z), fmaf(rb, -0.25f, hg), 0.0f);
-            }
-        }
-    }
+    if (!REGULAR) tol_tables(s_tb, a.pc, W, H, x0, y0);
+    tol_stage(cur, hist, s_nb, s_h, x0, y0, tx, ty, clamp_on, c);
     __syncthreads();
     if (x >= W || yb >= H) return;
 
-    const TolTap col = s_tb.col[tx];
-    const float blend = s_tb.blend;
+    V3 mn[4], mx[4];
+    if (clamp_on) tol_neighbourhood(s_nb, tx, ty, mn, mx);
+    const float blend = REGULAR ? a.blend : s_tb.blend;
     const P2 b2 = splat(blend), ib2 = splat(1.0f - blend);
-    const P2 fx2 = splat(col.f), ifx2 = splat(1.0f - col.f);
+    const uint32_t o00 = (uint32_t)yb * (uint32_t)W + (uint32_t)x;
 
-    // row-wise min / max of the 3 horizontal neighbours, for the 6 halo rows this strip touches
-    V3 rmn[6], rmx[6];
-    if (clamp_on) {
+    if (REGULAR) {
+        // rows j = 0..4 of the history window, lerped horizontally as (hl0,hl2), (hl1,hl3), (hl2,hl4)
+        const uint2* hb = &s_h[4 * ty + 1 + a.dy][tx + 1 + a.dx];
+        V3 ta[5], tb[5];
 #pragma unroll
-        for (int r = 0; r < 6; ++r) {
-            const float4 a = s_nb[4 * ty + r][tx], b = s_nb[4 * ty + r][tx + 1], d = s_nb[4 * ty + r][tx + 2];
-            rmn[r] = {fminf(fminf(a.x, b.x), d.x), fminf(fminf(a.y, b.y), d.y), fminf(fminf(a.z, b.z), d.z)};
-            rmx[r] = {fmaxf(fmaxf(a.x, b.x), d.x), fmaxf(fmaxf(a.y, b.y), d.y), fmaxf(fmaxf(a.z, b.z), d.z)};
+        for (int j = 0; j < 5; ++j) { ta[j] = tol_unpack(hb[j * kTolHaloW]); tb[j] = tol_unpack(hb[j * kTolHaloW + 1]); }
+        const P2 fx2 = splat(a.fx), ifx2 = splat(1.0f - a.fx), fy2 = splat(a.fy), ify2 = splat(1.0f - a.fy);
+        V3P hl[3];
+#pragma unroll
+        for (int j = 0; j < 3; ++j) {
+            const V3P ta2 = pk3(ta[j], ta[j + 2]), tb2 = pk3(tb[j], tb[j + 2]);
+            hl[j] = {fma(tb2.x, fx2, mul(ta2.x, ifx2)), fma(tb2.y, fx2, mul(ta2.y, ifx2)), fma(tb2.z, fx2, mul(ta2.z, ifx2))};
         }
-    }
-    const char* hb = reinterpret_cast<const char*>(&s_h[0][0]);
 #pragma unroll
-    for (int k = 0; k < 4; k += 2) {                     // lanes: lo = row yb + k, hi = row yb + k + 1
-        const int y = yb + k;
-        if (y >= H) break;
-        const TolTap ra = s_tb.row[4 * ty + k], rb = s_tb.row[4 * ty + k + 1];
-        auto tap = [&](int ro, int co) { return tol_unpack(*reinterpret_cast<const uint2*>(hb + ro + co)); };
-        V3P h;                                                                                       // :108 bilinear history
-        {
-            const V3P a  = pk3(tap(ra.i0, col.i0), tap(rb.i0, col.i0));
-            const V3P b  = pk3(tap(ra.i0, col.i1), tap(rb.i0, col.i1));
-            const V3P cc = pk3(tap(ra.i1, col.i0), tap(rb.i1, col.i0));
-            const V3P d  = pk3(tap(ra.i1, col.i1), tap(rb.i1, col.i1));
+        for (int k = 0; k < 2; ++k) {                    // lanes: lo = row yb + k, hi = row yb + k + 2
+            if (yb + k >= H) break;
+            const V3P h = {fma(hl[k + 1].x, fy2, mul(hl[k].x, ify2)), fma(hl[k + 1].y, fy2, mul(hl[k].y, ify2)),
+                           fma(hl[k + 1].z, fy2, mul(hl[k].z, ify2))};
+            tol_finish_pair<THRESH>(h, pk3(c[k], c[k + 2]), clamp_on, pk3(mn[k], mn[k + 2]), pk3(mx[k], mx[k + 2]), b2, ib2,
+                                    o00 + (uint32_t)k * (uint32_t)W, o00 + (uint32_t)(k + 2) * (uint32_t)W, yb + k + 2 < H, out, thr, a.threshold);
+        }
+    } else {
+        const TolTap col = s_tb.col[tx];
+        const P2 fx2 = splat(col.f), ifx2 = splat(1.0f - col.f);
+        const char* hb = reinterpret_cast<const char*>(&s_h[0][0]);
+#pragma unroll
+        for (int k = 0; k < 2; ++k) {
+            if (yb + k >= H) break;
+            const TolTap ra = s_tb.row[4 * ty + k], rb = s_tb.row[4 * ty + k + 2];
+            auto tap = [&](int ro, int co) { return tol_unpack(*reinterpret_cast<const uint2*>(hb + ro + co)); };
+            const V3P t00 = pk3(tap(ra.i0, col.i0), tap(rb.i0, col.i0)), t01 = pk3(tap(ra.i0, col.i1), tap(rb.i0, col.i1));
+            const V3P t10 = pk3(tap(ra.i1, col.i0), tap(rb.i1, col.i0)), t11 = pk3(tap(ra.i1, col.i1), tap(rb.i1, col.i1));
             const P2 fy = pk(ra.f, rb.f), ify = sub(splat(1.0f), fy);
-            const V3P top = {fma(b.x, fx2, mul(a.x, ifx2)), fma(b.y, fx2, mul(a.y, ifx2)), fma(b.z, fx2, mul(a.z, ifx2))};
-            const V3P bot = {fma(d.x, fx2, mul(cc.x, ifx2)), fma(d.y, fx2, mul(cc.y, ifx2)), fma(d.z, fx2, mul(cc.z, ifx2))};
-            h = {fma(bot.x, fy, mul(top.x, ify)), fma(bot.y, fy, mul(top.y, ify)), fma(bot.z, fy, mul(top.z, ify))};
-        }
-        if (clamp_on) {                                                                              // :112-142
-            auto mn3 = [&](int r) { return V3{fminf(fminf(rmn[r].x, rmn[r + 1].x), rmn[r + 2].x), fminf(fminf(rmn[r].y, rmn[r + 1].y), rmn[r + 2].y),
-                                              fminf(fminf(rmn[r].z, rmn[r + 1].z), rmn[r + 2].z)}; };
-            auto mx3 = [&](int r) { return V3{fmaxf(fmaxf(rmx[r].x, rmx[r + 1].x), rmx[r + 2].x), fmaxf(fmaxf(rmx[r].y, rmx[r + 1].y), rmx[r + 2].y),
-                                              fmaxf(fmaxf(rmx[r].z, rmx[r + 1].z), rmx[r + 2].z)}; };
-            const V3P mn = pk3(mn3(k), mn3(k + 1)), mx = pk3(mx3(k), mx3(k + 1));
-            const P2 hf = splat(0.5f), e125 = splat(0.625f), eps = splat(0.001f);
-            const V3P ctr = {mul(add(mn.x, mx.x), hf), mul(add(mn.y, mx.y), hf), mul(add(mn.z, mx.z), hf)};
-            const V3P half = {fma(sub(mx.x, mn.x), e125, eps), fma(sub(mx.y, mn.y), e125, eps), fma(sub(mx.z, mn.z), e125, eps)};
-            const V3P hy = rgb_to_ycocg(tonemap(h));
-            const V3P dl = {sub(hy.x, ctr.x), sub(hy.y, ctr.y), sub(hy.z, ctr.z)};
-            // s = min(1, min_i half_i / |delta_i|): 1 inside the box (history kept), 1 / maxV outside (:68-76)
-            const P2 sx = mul(half.x, rcp_abs(dl.x)), sy = mul(half.y, rcp_abs(dl.y)), sz = mul(half.z, rcp_abs(dl.z));
-            const P2 s = pk(fminf(fminf(fminf(lo(sx), lo(sy)), lo(sz)), 1.0f), fminf(fminf(fminf(hi(sx), hi(sy)), hi(sz)), 1.0f));
-            const V3P q = ycocg_to_rgb(V3P{fma(dl.x, s, ctr.x), fma(dl.y, s, ctr.y), fma(dl.z, s, ctr.z)});
-            const P2 k1 = splat(1.0001f);                                                            // (1 - c) + 1e-4, :59-61
-            h = {mul(q.x, rcp(sub(k1, q.x))), mul(q.y, rcp(sub(k1, q.y))), mul(q.z, rcp(sub(k1, q.z)))};
-        }
-        const V3P cp = pk3(c[k], c[k + 1]);
-        const V3P o = {fma(h.x, b2, mul(cp.x, ib2)), fma(h.y, b2, mul(cp.y, ib2)), fma(h.z, b2, mul(cp.z, ib2))};   // mix(), :159
-        const uint2 oa = pack_rgba16f(lo(o.x), lo(o.y), lo(o.z), 1.0f), ob = pack_rgba16f(hi(o.x), hi(o.y), hi(o.z), 1.0f);
-        const bool has_b = y + 1 < H;
-        const uint32_t o0 = (uint32_t)y * (uint32_t)W + (uint32_t)x, o1 = o0 + (uint32_t)W;
-        out[o0] = oa;
-        if (has_b) out[o1] = ob;
-        if (THRESH) {                                    // bloom_threshold.frag:18-27 of the resolved texel AS STORED (fp16)
-            const V3 ta = tol_unpack(oa), tb = tol_unpack(ob);
-            const P2 br = pk(fmaxf(fmaxf(ta.x, ta.y), ta.z), fmaxf(fmaxf(tb.x, tb.y), tb.z));
-            const P2 over = sub(br, splat(threshold));                               // brightness - threshold
-            const P2 sf = add(over, splat(0.5f));                                    // + knee
-            const P2 sc = pk(fminf(fmaxf(lo(sf), 0.0f), 1.0f), fminf(fmaxf(hi(sf), 0.0f), 1.0f));
-            const P2 soft = mul(mul(sc, sc), splat(1.0f / 2.00001f));                // soft^2 / (4 knee + 1e-5)
-            const P2 ct = pk(fmaxf(lo(soft), lo(over)), fmaxf(hi(soft), hi(over)));
-            const P2 w = mul(ct, pk(rcp(fmaxf(lo(br), 0.00001f)), rcp(fmaxf(hi(br), 0.00001f))));
-            const V3P t3 = pk3(ta, tb);
-            const P2 bx = mul(t3.x, w), by = mul(t3.y, w), bz = mul(t3.z, w);
-            thr[o0] = pack_rgba16f(lo(bx), lo(by), lo(bz), 1.0f);
-            if (has_b) thr[o1] = pack_rgba16f(hi(bx), hi(by), hi(bz), 1.0f);
+            const V3P top = {fma(t01.x, fx2, mul(t00.x, ifx2)), fma(t01.y, fx2, mul(t00.y, ifx2)), fma(t01.z, fx2, mul(t00.z, ifx2))};
+            const V3P bot = {fma(t11.x, fx2, mul(t10.x, ifx2)), fma(t11.y, fx2, mul(t10.y, ifx2)), fma(t11.z, fx2, mul(t10.z, ifx2))};
+            const V3P h = {fma(bot.x, fy, mul(top.x, ify)), fma(bot.y, fy, mul(top.y, ify)), fma(bot.z, fy, mul(top.z, ify))};
+            tol_finish_pair<THRESH>(h, pk3(c[k], c[k + 2]), clamp_on, pk3(mn[k], mn[k + 2]), pk3(mx[k], mx[k + 2]), b2, ib2,
+                                    o00 + (uint32_t)k * (uint32_t)W, o00 + (uint32_t)(k + 2) * (uint32_t)W, yb + k + 2 < H, out, thr, a.threshold);
         }
     }
 }
 
-// graph replay: argument 4 of k_taa_tol is the per-view AshTaaPushConstants
-void taa_tol_patch(bool thresh, const AshTaaPushConstants& pc, PatchArg* out) {
-    out->func = thresh ? reinterpret_cast<const void*>(&k_taa_tol<true>) : reinterpret_cast<const void*>(&k_taa_tol<false>);
-    out->arg_index = 4; out->n_args = 6;
-    std::memcpy(out->value, &pc, sizeof(pc));
+static const void* tol_kernel(bool thresh, bool regular) {
+    return thresh ? (regular ? reinterpret_cast<const void*>(&k_taa_tol<true, true>) : reinterpret_cast<const void*>(&k_taa_tol<true, false>))
+                  : (regular ? reinterpret_cast<const void*>(&k_taa_tol<false, true>) : reinterpret_cast<const void*>(&k_taa_tol<false, false>));
 }
 
-cudaError_t launch_taa_tol(const void* cur, const void* hist, void* out, void* thr_or_null,
-                           const AshTaaPushConstants& pc, float threshold, const Launch& L) {
-    const int W = (int)pc.screen_params[0], H = (int)pc.screen_params[1];
-    const Tex16 c{static_cast<const uint2*>(cur), W, H}, h{static_cast<const uint2*>(hist), W, H};
+// graph replay: argument 4 of k_taa_tol is the per-view TaaTolArgs
+void taa_tol_patch(bool thresh, const TaaTolArgs& a, PatchArg* out) {
+    out->func = tol_kernel(thresh, a.regular != 0);
+    out->arg_index = 4; out->n_args = 5;
+    static_assert(sizeof(TaaTolArgs) <= sizeof(out->value), "PatchArg too small");
+    std::memcpy(out->value, &a, sizeof(a));
+}
+
+cudaError_t launch_taa_tol(const void* cur, const void* hist, void* out, void* thr_or_null, const TaaTolArgs& a, const Launch& L) {
+    const int W = (int)a.pc.screen_params[0], H = (int)a.pc.screen_params[1];
+    Tex16 c{static_cast<const uint2*>(cur), W, H}, h{static_cast<const uint2*>(hist), W, H};
     const dim3 grid((W + kTolW - 1) / kTolW, (H + kTolH - 1) / kTolH);
     uint2* o = static_cast<uint2*>(out);
     uint2* t = static_cast<uint2*>(thr_or_null);
+    TaaTolArgs args = a;
+    void* params[5] = {&c, &h, &o, &t, &args};
     Timed timed(L, thr_or_null ? ASH_KERNEL_TAA_THRESHOLD : ASH_KERNEL_TAA);
-    if (t) k_taa_tol<true><<<grid, kTolThreads, 0, L.s>>>(c, h, o, t, pc, threshold);
-    else   k_taa_tol<false><<<grid, kTolThreads, 0, L.s>>>(c, h, o, t, pc, threshold);
-    return cudaGetLastError();
+    return cudaLaunchKernel(tol_kernel(t != nullptr, a.regular != 0), grid, dim3(kTolThreads), params, 0, L.s);
 }
 
 }  // namespace ash

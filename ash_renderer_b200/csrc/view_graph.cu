@@ -55,6 +55,10 @@ GraphKey make_key(const ashcuda_ctx* c, const AshCudaViewParams* vp) {
     std::memcpy(k.taa_screen, vp->taa.screen_params, sizeof(k.taa_screen));
     k.bloom = vp->bloom; k.post = vp->post;
     k.in_halo = taa_in_halo(vp->taa) ? 1u : 0u;
+    if (c->cfg.precision == ASH_PRECISION_FAST && (vp->stages & ASH_STAGE_TAA) && k.in_halo) {   // which k_taa_tol instance the graph holds
+        TaaTolArgs ta;
+        k.tol_variant = 1u + ash_taa_tol_plan(const_cast<ashcuda_ctx*>(c), vp->taa, vp->bloom.threshold, &ta).regular;
+    }
     k.taa_cur = (uint32_t)c->taa_cur; k.history_valid = c->history_valid; k.taa_ran = c->taa_ran;
     k.have_color = c->have_color; k.have_depth = c->have_depth; k.have_instancing = c->have_instancing;
     k.concurrent = c->cfg.concurrent_frontend; k.have_pyramid = c->have_pyramid;
@@ -75,7 +79,10 @@ void make_patches(const ashcuda_ctx* c, const AshCudaViewParams* vp, Patches* P)
     if (P->has_cull2) cull_patch(vp->cull, 2, &P->cull2);
     if (P->has_taa) {
         const bool vel = c->velocity != nullptr && !(st & ASH_STAGE_FORWARD_SHADE);
-        if (c->cfg.precision == ASH_PRECISION_FAST && !vel && taa_in_halo(vp->taa)) taa_tol_patch((st & ASH_STAGE_BLOOM) != 0, vp->taa, &P->taa);
+        if (c->cfg.precision == ASH_PRECISION_FAST && !vel && taa_in_halo(vp->taa)) {
+            TaaTolArgs ta;
+            taa_tol_patch((st & ASH_STAGE_BLOOM) != 0, ash_taa_tol_plan(const_cast<ashcuda_ctx*>(c), vp->taa, vp->bloom.threshold, &ta), &P->taa);
+        }
         else taa_pair_patch((st & ASH_STAGE_BLOOM) != 0, vel, vp->taa, &P->taa);
     }
     if (P->has_lod) {

@@ -445,7 +445,9 @@ int ashcuda_kernel_time_ms(ashcuda_ctx*, int kernel_class, float* ms, uint64_t* 
 /* Diagnostics (host only, no device needed): does the pinned LINEAR sampler land exactly on the
  * texels/weights the fast kernels assume, for every coordinate of one axis?  kind 0: centre taps
  * (n_dst texels, size_f = extent as float); 1: TAA 3x3 taps (size_f, inv = screenParams.z|w);
- * 2: 2:1 downsample (n_src -> n_dst); 3: 1:2 upsample (n_src -> n_dst).  Returns 1 / 0. */
+ * 2: 2:1 downsample (n_src -> n_dst); 3: 1:2 upsample (n_src -> n_dst); 4: are the TAA history taps of a frame
+ * without velocity buffer "regular" on this axis (one texel offset and one weight for every coordinate; inv = the
+ * jitter delta in pixels) — the precondition of the shared-row history path of the FAST precision mode.  Returns 1 / 0. */
 int ashcuda_debug_exact_taps(int kind, int n_src, int n_dst, float size_f, float inv);
 /* shaders/compute_utils.glsl as a CUDA header (csrc/ash_compute_utils.cuh; row f-4): runs one function of
  * the library on host data on `device` (no context), for parity tests.  op:

@@ -31,13 +31,25 @@ def assert_within_ulps(got, ref, ulps, what, max_frac=None):
     return float((d > 0).mean())
 
 
+def test_history_regularity_check_separates_the_two_variants(backend):
+    """Host-side plan (exact_taps.cu): Halton deltas are regular, a delta on an 8-bit weight boundary is not."""
+    lib = backend.load_library()
+    reg = lambda n, d: lib.ashcuda_debug_exact_taps(4, 0, n, np.float32(n), np.float32(d))
+    for n in (200, 120, 1920, 1080, 3840, 2160):
+        assert reg(n, 0.25) and reg(n, -0.16666667) and reg(n, 0.0) and reg(n, -0.85)
+        assert not reg(n, 0.001953125) and not reg(n, 0.998046875)
+
+
 @pytest.mark.parametrize("W,H", [(200, 120), (67, 45), (33, 9), (1920, 1080), (1000, 3)])
 def test_taa_fast_within_one_ulp_white_noise(backend, oracle, W, H):
     """White-noise HDR with hot texels (the worst case for the neighbourhood clip), four parameter sets."""
     cur, hist = synth.random_hdr(W, H, seed=1), synth.random_hdr(W, H, seed=2)
     with _ctx(backend, W, H, **FAST) as c:
         for kw in (dict(), dict(clamp=0.0), dict(vel=0.0, jitter=(-0.4, 0.3), prev=(0.45, -0.45)), dict(blend=0.0),
-                   dict(jitter=(0.0, 0.0), prev=(0.0, 0.0))):
+                   dict(jitter=(0.0, 0.0), prev=(0.0, 0.0)),
+                   # a delta of 1/512 px sits on a rounding boundary of the 8-bit weight: single columns flip to the
+                   # neighbouring weight, the frame is NOT regular and the per-tile table variant runs
+                   dict(jitter=(0.001953125, 0.3), prev=(0.0, 0.0)), dict(jitter=(0.1, 0.998046875), prev=(0.0, 0.0))):
             pc = _taa_pc(W, H, **kw)
             c.taa_reset_history()
             c.set_color(hist, None)
