@@ -20,6 +20,7 @@
 //     tap, so `current` is never written to shared memory in raw form and is converted from fp16 once;
 //   * tonemapped YCoCg of every texel of tile + halo: once per texel into shared memory (float4);
 //   * history: raw fp16 tile + halo in shared memory, four taps per pixel through the per-tile coordinate tables.
+#include <algorithm>
 #include <cstring>
 #include "ash_f32x2.cuh"
 #include "post_math.cuh"
@@ -276,15 +277,163 @@ k_taa_tol(Tex16 cur, Tex16 hist, uint2* __restrict__ out, uint2* __restrict__ th
     }
 }
 
-static const void* tol_kernel(bool thresh, bool regular) {
-    return thresh ? (regular ? reinterpret_cast<const void*>(&k_taa_tol<true, true>) : reinterpret_cast<const void*>(&k_taa_tol<true, false>))
-                  : (regular ? reinterpret_cast<const void*>(&k_taa_tol<false, true>) : reinterpret_cast<const void*>(&k_taa_tol<false, false>));
+// =====================================================================================================
+// The same resolve as a PERSISTENT, double-buffered kernel: one CTA walks tiles t = blockIdx.x, + gridDim.x, ... and
+// the raw texels of tile t + 1 (current + history, tile + halo: 9.8 KB) travel into the second shared-memory stage
+// with cp.async while tile t is resolved.  The one-shot kernel above leaves the SM waiting for DRAM at the head of
+// every CTA (ncu: long_scoreboard 3.5 stalled warps per issue, issue-active 54 %); here a tile's loads are a whole tile
+// time (about 4 us) ahead of their use.  Two barriers per tile: data landed / neighbourhood staged.
+// =====================================================================================================
+struct TolRing { int ex, ey; bool extra; };
+__device__ __forceinline__ TolRing tol_ring() {          // halo ring: top row (34), bottom row (34), left column (16), right column (16)
+    const int e = threadIdx.x;
+    TolRing r;
+    r.ex = e < 2 * kTolHaloW ? (e < kTolHaloW ? e : e - kTolHaloW) : (e < 2 * kTolHaloW + kTolH ? 0 : kTolHaloW - 1);
+    r.ey = e < 2 * kTolHaloW ? (e < kTolHaloW ? 0 : kTolHaloH - 1) : 1 + ((e - 2 * kTolHaloW) & (kTolH - 1));
+    r.extra = e < kTolExtras;
+    return r;
 }
 
-// graph replay: argument 4 of k_taa_tol is the per-view TaaTolArgs
+__device__ __forceinline__ float4 tol_nb_record(float rb, float hg, float df) {   // (y, co, cg, -) from r + b, g / 2, r - b
+    float4 v;
+    v.x = fmaf(rb, 0.25f, hg); v.y = 0.5f * df; v.z = fmaf(rb, -0.25f, hg); v.w = v.x;
+    return v;
+}
+
+template <bool THRESH, bool REGULAR>
+__global__ void __launch_bounds__(kTolThreads, ASH_TOL_CTAS)
+k_taa_tol_pipe(Tex16 cur, Tex16 hist, uint2* __restrict__ out, uint2* __restrict__ thr, TaaTolArgs a, int tiles_x, int n_tiles) {
+    using namespace tol;
+    __shared__ uint2  s_c[2][kTolHaloH][kTolHaloW];      // raw `current`, tile + halo, two stages
+    __shared__ uint2  s_h[2][kTolHaloH][kTolHaloW];      // raw history
+    __shared__ float4 s_nb[kTolHaloH][kTolHaloW];        // tonemapped YCoCg of `current`
+    __shared__ TolTables s_tb;
+    const int W = cur.W, H = cur.H;
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    const bool clamp_on = a.pc.params[1] > 0.5f;
+    const TolRing ring = tol_ring();
+    const float blend_reg = a.blend;
+
+    auto issue = [&](int bx, int by, int st) {           // this thread's share of a tile's raw texels -> stage st
+        const int x0 = bx * kTolW, y0 = by * kTolH;
+        const uint32_t gx = (uint32_t)min(x0 + tx, W - 1);                                             // CLAMP_TO_EDGE
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const uint32_t g = (uint32_t)min(y0 + 4 * ty + k, H - 1) * (uint32_t)W + gx;
+            cp_async8(&s_c[st][4 * ty + 1 + k][tx + 1], cur.p + g);
+            cp_async8(&s_h[st][4 * ty + 1 + k][tx + 1], hist.p + g);
+        }
+        if (ring.extra) {
+            const uint32_t g = (uint32_t)min(max(y0 - 1 + ring.ey, 0), H - 1) * (uint32_t)W + (uint32_t)min(max(x0 - 1 + ring.ex, 0), W - 1);
+            cp_async8(&s_c[st][ring.ey][ring.ex], cur.p + g);
+            cp_async8(&s_h[st][ring.ey][ring.ex], hist.p + g);
+        }
+        cp_async_commit();
+    };
+
+    int tile = blockIdx.x;
+    if (tile >= n_tiles) return;
+    // tile coordinates advance without divisions: + gridDim.x tiles = + (dbx, dby) with a carry
+    const int dby = (int)gridDim.x / tiles_x, dbx = (int)gridDim.x - dby * tiles_x;
+    int by = tile / tiles_x, bx = tile - by * tiles_x;
+    issue(bx, by, 0);
+    for (int it = 0;; ++it) {
+        const int st = it & 1, next = tile + (int)gridDim.x;
+        int nbx = bx + dbx, nby = by + dby;
+        if (nbx >= tiles_x) { nbx -= tiles_x; ++nby; }
+        const int x0 = bx * kTolW, y0 = by * kTolH;
+        const int x = x0 + tx, yb = y0 + 4 * ty;
+        cp_async_wait<0>();
+        __syncthreads();                                 // tile landed; everybody is done with the previous tile's stage and s_nb
+        if (next < n_tiles) issue(nbx, nby, st ^ 1);
+        if (!REGULAR) tol_tables(s_tb, a.pc, W, H, x0, y0);
+
+        V3 c[4];                                         // own `current` texels, fp32: neighbourhood staging AND centre tap
+#pragma unroll
+        for (int k = 0; k < 4; ++k) c[k] = tol_unpack(s_c[st][4 * ty + 1 + k][tx + 1]);
+        if (clamp_on) {                                  // :116-121, once per texel
+#pragma unroll
+            for (int k = 0; k < 2; ++k) {                // lanes: rows k and k + 2 (the pairing of the resolve)
+                const V3P t = tonemap(pk3(c[k], c[k + 2]));
+                const P2 rb = add(t.x, t.z), hg = mul(t.y, splat(0.5f)), df = sub(t.x, t.z);
+                s_nb[4 * ty + 1 + k][tx + 1] = tol_nb_record(lo(rb), lo(hg), lo(df));
+                s_nb[4 * ty + 3 + k][tx + 1] = tol_nb_record(hi(rb), hi(hg), hi(df));
+            }
+            if (ring.extra) {
+                const V3 q = tol_unpack(s_c[st][ring.ey][ring.ex]);
+                const V3 t = {q.x * rcp(1.0f + q.x), q.y * rcp(1.0f + q.y), q.z * rcp(1.0f + q.z)};
+                s_nb[ring.ey][ring.ex] = tol_nb_record(t.x + t.z, 0.5f * t.y, t.x - t.z);
+            }
+        }
+        __syncthreads();
+        if (x < W && yb < H) {
+            V3 mn[4], mx[4];
+            if (clamp_on) tol_neighbourhood(s_nb, tx, ty, mn, mx);
+            const float blend = REGULAR ? blend_reg : s_tb.blend;
+            const P2 b2 = splat(blend), ib2 = splat(1.0f - blend);
+            const uint32_t o00 = (uint32_t)yb * (uint32_t)W + (uint32_t)x;
+            if (REGULAR) {
+                const uint2* hb = &s_h[st][4 * ty + 1 + a.dy][tx + 1 + a.dx];
+                V3 ta[5], tb[5];
+#pragma unroll
+                for (int j = 0; j < 5; ++j) { ta[j] = tol_unpack(hb[j * kTolHaloW]); tb[j] = tol_unpack(hb[j * kTolHaloW + 1]); }
+                const P2 fx2 = splat(a.fx), ifx2 = splat(1.0f - a.fx), fy2 = splat(a.fy), ify2 = splat(1.0f - a.fy);
+                V3P hl[3];
+#pragma unroll
+                for (int j = 0; j < 3; ++j) {
+                    const V3P ta2 = pk3(ta[j], ta[j + 2]), tb2 = pk3(tb[j], tb[j + 2]);
+                    hl[j] = {fma(tb2.x, fx2, mul(ta2.x, ifx2)), fma(tb2.y, fx2, mul(ta2.y, ifx2)), fma(tb2.z, fx2, mul(ta2.z, ifx2))};
+                }
+#pragma unroll
+                for (int k = 0; k < 2; ++k) {            // lanes: lo = row yb + k, hi = row yb + k + 2
+                    if (yb + k >= H) break;
+                    const V3P h = {fma(hl[k + 1].x, fy2, mul(hl[k].x, ify2)), fma(hl[k + 1].y, fy2, mul(hl[k].y, ify2)),
+                                   fma(hl[k + 1].z, fy2, mul(hl[k].z, ify2))};
+                    tol_finish_pair<THRESH>(h, pk3(c[k], c[k + 2]), clamp_on, pk3(mn[k], mn[k + 2]), pk3(mx[k], mx[k + 2]), b2, ib2,
+                                            o00 + (uint32_t)k * (uint32_t)W, o00 + (uint32_t)(k + 2) * (uint32_t)W, yb + k + 2 < H, out, thr, a.threshold);
+                }
+            } else {
+                const TolTap col = s_tb.col[tx];
+                const P2 fx2 = splat(col.f), ifx2 = splat(1.0f - col.f);
+                const char* hb = reinterpret_cast<const char*>(&s_h[st][0][0]);
+#pragma unroll
+                for (int k = 0; k < 2; ++k) {
+                    if (yb + k >= H) break;
+                    const TolTap ra = s_tb.row[4 * ty + k], rb = s_tb.row[4 * ty + k + 2];
+                    auto tap = [&](int ro, int co) { return tol_unpack(*reinterpret_cast<const uint2*>(hb + ro + co)); };
+                    const V3P t00 = pk3(tap(ra.i0, col.i0), tap(rb.i0, col.i0)), t01 = pk3(tap(ra.i0, col.i1), tap(rb.i0, col.i1));
+                    const V3P t10 = pk3(tap(ra.i1, col.i0), tap(rb.i1, col.i0)), t11 = pk3(tap(ra.i1, col.i1), tap(rb.i1, col.i1));
+                    const P2 fy = pk(ra.f, rb.f), ify = sub(splat(1.0f), fy);
+                    const V3P top = {fma(t01.x, fx2, mul(t00.x, ifx2)), fma(t01.y, fx2, mul(t00.y, ifx2)), fma(t01.z, fx2, mul(t00.z, ifx2))};
+                    const V3P bot = {fma(t11.x, fx2, mul(t10.x, ifx2)), fma(t11.y, fx2, mul(t10.y, ifx2)), fma(t11.z, fx2, mul(t10.z, ifx2))};
+                    const V3P h = {fma(bot.x, fy, mul(top.x, ify)), fma(bot.y, fy, mul(top.y, ify)), fma(bot.z, fy, mul(top.z, ify))};
+                    tol_finish_pair<THRESH>(h, pk3(c[k], c[k + 2]), clamp_on, pk3(mn[k], mn[k + 2]), pk3(mx[k], mx[k + 2]), b2, ib2,
+                                            o00 + (uint32_t)k * (uint32_t)W, o00 + (uint32_t)(k + 2) * (uint32_t)W, yb + k + 2 < H, out, thr, a.threshold);
+                }
+            }
+        }
+        if (next >= n_tiles) break;
+        tile = next; bx = nbx; by = nby;
+    }
+}
+
+#ifndef ASH_TOL_PIPE
+#define ASH_TOL_PIPE 1                                   // 1: persistent double-buffered kernel; 0: one CTA per tile
+#endif
+static const void* tol_kernel(bool thresh, bool regular) {
+#if ASH_TOL_PIPE
+    return thresh ? (regular ? reinterpret_cast<const void*>(&k_taa_tol_pipe<true, true>) : reinterpret_cast<const void*>(&k_taa_tol_pipe<true, false>))
+                  : (regular ? reinterpret_cast<const void*>(&k_taa_tol_pipe<false, true>) : reinterpret_cast<const void*>(&k_taa_tol_pipe<false, false>));
+#else
+    return thresh ? (regular ? reinterpret_cast<const void*>(&k_taa_tol<true, true>) : reinterpret_cast<const void*>(&k_taa_tol<true, false>))
+                  : (regular ? reinterpret_cast<const void*>(&k_taa_tol<false, true>) : reinterpret_cast<const void*>(&k_taa_tol<false, false>));
+#endif
+}
+
+// graph replay: argument 4 of k_taa_tol[_pipe] is the per-view TaaTolArgs
 void taa_tol_patch(bool thresh, const TaaTolArgs& a, PatchArg* out) {
     out->func = tol_kernel(thresh, a.regular != 0);
-    out->arg_index = 4; out->n_args = 5;
+    out->arg_index = 4; out->n_args = ASH_TOL_PIPE ? 7 : 5;
     static_assert(sizeof(TaaTolArgs) <= sizeof(out->value), "PatchArg too small");
     std::memcpy(out->value, &a, sizeof(a));
 }
@@ -292,12 +441,19 @@ void taa_tol_patch(bool thresh, const TaaTolArgs& a, PatchArg* out) {
 cudaError_t launch_taa_tol(const void* cur, const void* hist, void* out, void* thr_or_null, const TaaTolArgs& a, const Launch& L) {
     const int W = (int)a.pc.screen_params[0], H = (int)a.pc.screen_params[1];
     Tex16 c{static_cast<const uint2*>(cur), W, H}, h{static_cast<const uint2*>(hist), W, H};
-    const dim3 grid((W + kTolW - 1) / kTolW, (H + kTolH - 1) / kTolH);
+    int tiles_x = (W + kTolW - 1) / kTolW, n_tiles = tiles_x * ((H + kTolH - 1) / kTolH);
     uint2* o = static_cast<uint2*>(out);
     uint2* t = static_cast<uint2*>(thr_or_null);
     TaaTolArgs args = a;
-    void* params[5] = {&c, &h, &o, &t, &args};
+    void* params[7] = {&c, &h, &o, &t, &args, &tiles_x, &n_tiles};
     Timed timed(L, thr_or_null ? ASH_KERNEL_TAA_THRESHOLD : ASH_KERNEL_TAA);
+#if ASH_TOL_PIPE
+    static int n_sm = 0;
+    if (!n_sm) { int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev); }
+    const dim3 grid((unsigned)std::min(n_tiles, n_sm * ASH_TOL_CTAS));
+#else
+    const dim3 grid(tiles_x, (H + kTolH - 1) / kTolH);
+#endif
     return cudaLaunchKernel(tol_kernel(t != nullptr, a.regular != 0), grid, dim3(kTolThreads), params, 0, L.s);
 }
 
