@@ -55,9 +55,13 @@ __device__ __forceinline__ V3P ycocg_to_rgb(V3P c) {
 }
 }  // namespace tol
 
-constexpr int kTolW = 32, kTolH = 16, kTolThreads = 128;          // tile; thread = column tx, rows 4 ty .. 4 ty + 3
+#ifndef ASH_TOL_S
+#define ASH_TOL_S 4                                                // rows per thread (strip height): 4 or 2
+#endif
+constexpr int kTolS = ASH_TOL_S, kTolP = kTolS / 2;               // P = lane distance of a pixel pair: lanes are rows k and k + P
+constexpr int kTolW = 32, kTolThreads = 128, kTolH = (kTolThreads / 32) * kTolS;   // tile; thread = column tx, rows S ty .. S ty + S - 1
 constexpr int kTolHaloW = kTolW + 2, kTolHaloH = kTolH + 2;
-constexpr int kTolExtras = 2 * kTolHaloW + 2 * kTolH;             // halo ring: 100 texels, one per thread 0..99
+constexpr int kTolExtras = 2 * kTolHaloW + 2 * kTolH;             // halo ring (100 texels at S = 4), one per thread
 static_assert(kTolExtras <= kTolThreads, "one halo texel per thread");
 
 struct TolTap { int i0, i1; float f, pad; };                     // halo-local BYTE offsets (column: 8 i, row: 8 * 34 i), 8-bit weight
@@ -97,64 +101,83 @@ __device__ __forceinline__ void tol_tables(TolTables& tb, const AshTaaPushConsta
 
 __device__ __forceinline__ V3 tol_unpack(uint2 t) { V4 v = unpack_rgba16f(t); return {v.x, v.y, v.z}; }
 
+struct TolRingTable { unsigned short v[kTolThreads]; };
+constexpr TolRingTable tol_make_ring() {
+    TolRingTable t{};
+    for (int e = 0; e < kTolThreads; ++e) {
+        const int ex = e < 2 * kTolHaloW ? (e < kTolHaloW ? e : e - kTolHaloW) : (e < 2 * kTolHaloW + kTolH ? 0 : kTolHaloW - 1);
+        const int ey = e < 2 * kTolHaloW ? (e < kTolHaloW ? 0 : kTolHaloH - 1) : 1 + ((e - 2 * kTolHaloW) & (kTolH - 1));
+        t.v[e] = (unsigned short)(ex | (ey << 8));
+    }
+    return t;
+}
+__constant__ TolRingTable c_tol_ring = tol_make_ring();
+
+// (y, co, cg) of taa_resolve.comp:34-40 from r + b, g / 2, r - b, written straight into the four registers of one
+// 128-bit shared-memory store (the .w lane is never read)
+__device__ __forceinline__ float4 tol_nb_record(float rb, float hg, float df) {
+    float4 v;
+    v.x = fmaf(rb, 0.25f, hg); v.y = 0.5f * df; v.z = fmaf(rb, -0.25f, hg); v.w = v.x;
+    return v;
+}
+
 // ---- stage: own texels + halo ring -> s_h (raw history), s_nb (tonemapped YCoCg of `current`); returns the thread's own
 // `current` texels as fp32
 __device__ __forceinline__ void tol_stage(const Tex16& cur, const Tex16& hist, float4 (*s_nb)[kTolHaloW], uint2 (*s_h)[kTolHaloW],
-                                          int x0, int y0, int tx, int ty, bool clamp_on, V3 (&c)[4]) {
+                                          int x0, int y0, int tx, int ty, bool clamp_on, V3 (&c)[kTolS]) {
     using namespace tol;
     const int W = cur.W, H = cur.H;
-    uint2 tc[4], th[4], ec = make_uint2(0u, 0u), eh = make_uint2(0u, 0u);
+    uint2 tc[kTolS], th[kTolS], ec = make_uint2(0u, 0u), eh = make_uint2(0u, 0u);
     const uint32_t gx = (uint32_t)min(x0 + tx, W - 1);                                                 // CLAMP_TO_EDGE
 #pragma unroll
-    for (int k = 0; k < 4; ++k) {
-        const uint32_t g = (uint32_t)min(y0 + 4 * ty + k, H - 1) * (uint32_t)W + gx;
+    for (int k = 0; k < kTolS; ++k) {
+        const uint32_t g = (uint32_t)min(y0 + kTolS * ty + k, H - 1) * (uint32_t)W + gx;
         tc[k] = __ldg(cur.p + g);
         th[k] = __ldg(hist.p + g);
     }
-    // halo ring: top row (34), bottom row (34), left column (16), right column (16)
-    const int e = threadIdx.x;
-    const int ex = e < 2 * kTolHaloW ? (e < kTolHaloW ? e : e - kTolHaloW) : (e < 2 * kTolHaloW + kTolH ? 0 : kTolHaloW - 1);
-    const int ey = e < 2 * kTolHaloW ? (e < kTolHaloW ? 0 : kTolHaloH - 1) : 1 + ((e - 2 * kTolHaloW) & (kTolH - 1));
-    const bool extra = e < kTolExtras;
+    // halo ring: top row (34), bottom row (34), left column (16), right column (16): thread e takes ring texel e
+    const uint32_t ring = c_tol_ring.v[threadIdx.x];
+    const int ex = (int)(ring & 0xFFu), ey = (int)(ring >> 8);
+    const bool extra = threadIdx.x < kTolExtras;
     if (extra) {
         const uint32_t g = (uint32_t)min(max(y0 - 1 + ey, 0), H - 1) * (uint32_t)W + (uint32_t)min(max(x0 - 1 + ex, 0), W - 1);
         ec = __ldg(cur.p + g);
         eh = __ldg(hist.p + g);
     }
 #pragma unroll
-    for (int k = 0; k < 4; ++k) {
-        s_h[4 * ty + 1 + k][tx + 1] = th[k];
+    for (int k = 0; k < kTolS; ++k) {
+        s_h[kTolS * ty + 1 + k][tx + 1] = th[k];
         c[k] = tol_unpack(tc[k]);
     }
     if (extra) s_h[ey][ex] = eh;
     if (clamp_on) {                                      // :116-121, once per texel
 #pragma unroll
-        for (int k = 0; k < 2; ++k) {                    // lanes: rows k and k + 2 (the pairing of the resolve)
-            const V3P s = rgb_to_ycocg(tonemap(pk3(c[k], c[k + 2])));
-            s_nb[4 * ty + 1 + k][tx + 1] = make_float4(lo(s.x), lo(s.y), lo(s.z), 0.0f);
-            s_nb[4 * ty + 3 + k][tx + 1] = make_float4(hi(s.x), hi(s.y), hi(s.z), 0.0f);
+        for (int k = 0; k < kTolP; ++k) {                // lanes: rows k and k + P (the pairing of the resolve)
+            const V3P t = tonemap(pk3(c[k], c[k + kTolP]));
+            const P2 rb = add(t.x, t.z), hg = mul(t.y, splat(0.5f)), df = sub(t.x, t.z);
+            s_nb[kTolS * ty + 1 + k][tx + 1] = tol_nb_record(lo(rb), lo(hg), lo(df));
+            s_nb[kTolS * ty + 1 + kTolP + k][tx + 1] = tol_nb_record(hi(rb), hi(hg), hi(df));
         }
         if (extra) {
             const V3 q = tol_unpack(ec);
             const V3 t = {q.x * rcp(1.0f + q.x), q.y * rcp(1.0f + q.y), q.z * rcp(1.0f + q.z)};
-            const float rb = t.x + t.z, hg = 0.5f * t.y;
-            s_nb[ey][ex] = make_float4(fmaf(rb, 0.25f, hg), 0.5f * (t.x - t.z), fmaf(rb, -0.25f, hg), 0.0f);
+            s_nb[ey][ex] = tol_nb_record(t.x + t.z, 0.5f * t.y, t.x - t.z);
         }
     }
 }
 
 // ---- min / max of the 3x3 neighbourhood of the strip's four pixels (:124-129): row-wise over the three horizontal
 // neighbours for the six halo rows the strip touches, then column-wise
-__device__ __forceinline__ void tol_neighbourhood(const float4 (*s_nb)[kTolHaloW], int tx, int ty, V3 (&mn)[4], V3 (&mx)[4]) {
-    V3 rmn[6], rmx[6];
+__device__ __forceinline__ void tol_neighbourhood(const float4 (*s_nb)[kTolHaloW], int tx, int ty, V3 (&mn)[kTolS], V3 (&mx)[kTolS]) {
+    V3 rmn[kTolS + 2], rmx[kTolS + 2];
 #pragma unroll
-    for (int r = 0; r < 6; ++r) {
-        const float4 a = s_nb[4 * ty + r][tx], b = s_nb[4 * ty + r][tx + 1], d = s_nb[4 * ty + r][tx + 2];
+    for (int r = 0; r < kTolS + 2; ++r) {
+        const float4 a = s_nb[kTolS * ty + r][tx], b = s_nb[kTolS * ty + r][tx + 1], d = s_nb[kTolS * ty + r][tx + 2];
         rmn[r] = {fminf(fminf(a.x, b.x), d.x), fminf(fminf(a.y, b.y), d.y), fminf(fminf(a.z, b.z), d.z)};
         rmx[r] = {fmaxf(fmaxf(a.x, b.x), d.x), fmaxf(fmaxf(a.y, b.y), d.y), fmaxf(fmaxf(a.z, b.z), d.z)};
     }
 #pragma unroll
-    for (int k = 0; k < 4; ++k) {
+    for (int k = 0; k < kTolS; ++k) {
         mn[k] = {fminf(fminf(rmn[k].x, rmn[k + 1].x), rmn[k + 2].x), fminf(fminf(rmn[k].y, rmn[k + 1].y), rmn[k + 2].y),
                  fminf(fminf(rmn[k].z, rmn[k + 1].z), rmn[k + 2].z)};
         mx[k] = {fmaxf(fmaxf(rmx[k].x, rmx[k + 1].x), rmx[k + 2].x), fmaxf(fmaxf(rmx[k].y, rmx[k + 1].y), rmx[k + 2].y),
@@ -166,7 +189,7 @@ __device__ __forceinline__ void tol_neighbourhood(const float4 (*s_nb)[kTolHaloW
 template <bool THRESH>
 __device__ __forceinline__ void tol_finish_pair(tol::V3P h, tol::V3P cp, bool clamp_on, tol::V3P mn, tol::V3P mx, P2 b2, P2 ib2,
                                                 uint32_t o0, uint32_t o1, bool has1, uint2* __restrict__ out,
-                                                uint2* __restrict__ thr, float threshold) {
+                                                uint2* __restrict__ thr, float threshold, float one) {
     using namespace tol;
     if (clamp_on) {
         const P2 hf = splat(0.5f), e125 = splat(0.625f), eps = splat(0.001f);
@@ -182,7 +205,7 @@ __device__ __forceinline__ void tol_finish_pair(tol::V3P h, tol::V3P cp, bool cl
         h = {mul(q.x, rcp(sub(k1, q.x))), mul(q.y, rcp(sub(k1, q.y))), mul(q.z, rcp(sub(k1, q.z)))};
     }
     const V3P o = {fma(h.x, b2, mul(cp.x, ib2)), fma(h.y, b2, mul(cp.y, ib2)), fma(h.z, b2, mul(cp.z, ib2))};       // mix(), :159
-    const uint2 oa = pack_rgba16f(lo(o.x), lo(o.y), lo(o.z), 1.0f), ob = pack_rgba16f(hi(o.x), hi(o.y), hi(o.z), 1.0f);
+    const uint2 oa = pack_rgba16f(lo(o.x), lo(o.y), lo(o.z), one), ob = pack_rgba16f(hi(o.x), hi(o.y), hi(o.z), one);
     out[o0] = oa;
     if (has1) out[o1] = ob;
     if (THRESH) {                                        // bloom_threshold.frag:18-27 of the resolved texel AS STORED (fp16)
@@ -196,13 +219,13 @@ __device__ __forceinline__ void tol_finish_pair(tol::V3P h, tol::V3P cp, bool cl
         const P2 w = mul(ct, pk(rcp(fmaxf(lo(br), 0.00001f)), rcp(fmaxf(hi(br), 0.00001f))));
         const V3P t3 = pk3(ta, tb);
         const P2 bx = mul(t3.x, w), by = mul(t3.y, w), bz = mul(t3.z, w);
-        thr[o0] = pack_rgba16f(lo(bx), lo(by), lo(bz), 1.0f);
-        if (has1) thr[o1] = pack_rgba16f(hi(bx), hi(by), hi(bz), 1.0f);
+        thr[o0] = pack_rgba16f(lo(bx), lo(by), lo(bz), one);
+        if (has1) thr[o1] = pack_rgba16f(hi(bx), hi(by), hi(bz), one);
     }
 }
 
 #ifndef ASH_TOL_CTAS
-#define ASH_TOL_CTAS 6
+#define ASH_TOL_CTAS 7                                   // measured at 4K: 5: 80.6 us, 6: 75.5, 7: 67.8, 8: 67.7, 9: 73.5, 10: 77.9 (S = 4)
 #endif
 // REGULAR = false: history taps through per-tile coordinate tables (any jitter delta inside the halo).
 // REGULAR = true : the host has verified (exact_taps.cu: axis_taa_history_regular, the same fp32 expressions) that every
@@ -220,50 +243,52 @@ k_taa_tol(Tex16 cur, Tex16 hist, uint2* __restrict__ out, uint2* __restrict__ th
     const int W = cur.W, H = cur.H;
     const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
     const int x0 = blockIdx.x * kTolW, y0 = blockIdx.y * kTolH;
-    const int x = x0 + tx, yb = y0 + 4 * ty;
+    const int x = x0 + tx, yb = y0 + kTolS * ty;
     const bool clamp_on = a.pc.params[1] > 0.5f;
 
-    V3 c[4];                                             // this thread's own `current` texels, fp32, kept for the resolve
+    V3 c[kTolS];                                           // this thread's own `current` texels, fp32, kept for the resolve
     if (!REGULAR) tol_tables(s_tb, a.pc, W, H, x0, y0);
     tol_stage(cur, hist, s_nb, s_h, x0, y0, tx, ty, clamp_on, c);
     __syncthreads();
     if (x >= W || yb >= H) return;
 
-    V3 mn[4], mx[4];
+    V3 mn[kTolS], mx[kTolS];
     if (clamp_on) tol_neighbourhood(s_nb, tx, ty, mn, mx);
+    float one;                                           // alpha 1.0 kept in ONE register for the eight F2FP packs (an immediate would be re-materialised per use)
+    asm volatile("mov.f32 %0, 0f3F800000;" : "=f"(one));
     const float blend = REGULAR ? a.blend : s_tb.blend;
     const P2 b2 = splat(blend), ib2 = splat(1.0f - blend);
     const uint32_t o00 = (uint32_t)yb * (uint32_t)W + (uint32_t)x;
 
     if (REGULAR) {
         // rows j = 0..4 of the history window, lerped horizontally as (hl0,hl2), (hl1,hl3), (hl2,hl4)
-        const uint2* hb = &s_h[4 * ty + 1 + a.dy][tx + 1 + a.dx];
-        V3 ta[5], tb[5];
+        const uint2* hb = &s_h[kTolS * ty + 1 + a.dy][tx + 1 + a.dx];
+        V3 ta[kTolS + 1], tb[kTolS + 1];
 #pragma unroll
-        for (int j = 0; j < 5; ++j) { ta[j] = tol_unpack(hb[j * kTolHaloW]); tb[j] = tol_unpack(hb[j * kTolHaloW + 1]); }
+        for (int j = 0; j < kTolS + 1; ++j) { ta[j] = tol_unpack(hb[j * kTolHaloW]); tb[j] = tol_unpack(hb[j * kTolHaloW + 1]); }
         const P2 fx2 = splat(a.fx), ifx2 = splat(1.0f - a.fx), fy2 = splat(a.fy), ify2 = splat(1.0f - a.fy);
-        V3P hl[3];
+        V3P hl[kTolP + 1];
 #pragma unroll
-        for (int j = 0; j < 3; ++j) {
-            const V3P ta2 = pk3(ta[j], ta[j + 2]), tb2 = pk3(tb[j], tb[j + 2]);
+        for (int j = 0; j < kTolP + 1; ++j) {
+            const V3P ta2 = pk3(ta[j], ta[j + kTolP]), tb2 = pk3(tb[j], tb[j + kTolP]);
             hl[j] = {fma(tb2.x, fx2, mul(ta2.x, ifx2)), fma(tb2.y, fx2, mul(ta2.y, ifx2)), fma(tb2.z, fx2, mul(ta2.z, ifx2))};
         }
 #pragma unroll
-        for (int k = 0; k < 2; ++k) {                    // lanes: lo = row yb + k, hi = row yb + k + 2
+        for (int k = 0; k < kTolP; ++k) {                // lanes: lo = row yb + k, hi = row yb + k + P
             if (yb + k >= H) break;
             const V3P h = {fma(hl[k + 1].x, fy2, mul(hl[k].x, ify2)), fma(hl[k + 1].y, fy2, mul(hl[k].y, ify2)),
                            fma(hl[k + 1].z, fy2, mul(hl[k].z, ify2))};
-            tol_finish_pair<THRESH>(h, pk3(c[k], c[k + 2]), clamp_on, pk3(mn[k], mn[k + 2]), pk3(mx[k], mx[k + 2]), b2, ib2,
-                                    o00 + (uint32_t)k * (uint32_t)W, o00 + (uint32_t)(k + 2) * (uint32_t)W, yb + k + 2 < H, out, thr, a.threshold);
+            tol_finish_pair<THRESH>(h, pk3(c[k], c[k + kTolP]), clamp_on, pk3(mn[k], mn[k + kTolP]), pk3(mx[k], mx[k + kTolP]), b2, ib2,
+                                    o00 + (uint32_t)k * (uint32_t)W, o00 + (uint32_t)(k + kTolP) * (uint32_t)W, yb + k + kTolP < H, out, thr, a.threshold, one);
         }
     } else {
         const TolTap col = s_tb.col[tx];
         const P2 fx2 = splat(col.f), ifx2 = splat(1.0f - col.f);
         const char* hb = reinterpret_cast<const char*>(&s_h[0][0]);
 #pragma unroll
-        for (int k = 0; k < 2; ++k) {
+        for (int k = 0; k < kTolP; ++k) {
             if (yb + k >= H) break;
-            const TolTap ra = s_tb.row[4 * ty + k], rb = s_tb.row[4 * ty + k + 2];
+            const TolTap ra = s_tb.row[kTolS * ty + k], rb = s_tb.row[kTolS * ty + k + kTolP];
             auto tap = [&](int ro, int co) { return tol_unpack(*reinterpret_cast<const uint2*>(hb + ro + co)); };
             const V3P t00 = pk3(tap(ra.i0, col.i0), tap(rb.i0, col.i0)), t01 = pk3(tap(ra.i0, col.i1), tap(rb.i0, col.i1));
             const V3P t10 = pk3(tap(ra.i1, col.i0), tap(rb.i1, col.i0)), t11 = pk3(tap(ra.i1, col.i1), tap(rb.i1, col.i1));
@@ -271,169 +296,25 @@ k_taa_tol(Tex16 cur, Tex16 hist, uint2* __restrict__ out, uint2* __restrict__ th
             const V3P top = {fma(t01.x, fx2, mul(t00.x, ifx2)), fma(t01.y, fx2, mul(t00.y, ifx2)), fma(t01.z, fx2, mul(t00.z, ifx2))};
             const V3P bot = {fma(t11.x, fx2, mul(t10.x, ifx2)), fma(t11.y, fx2, mul(t10.y, ifx2)), fma(t11.z, fx2, mul(t10.z, ifx2))};
             const V3P h = {fma(bot.x, fy, mul(top.x, ify)), fma(bot.y, fy, mul(top.y, ify)), fma(bot.z, fy, mul(top.z, ify))};
-            tol_finish_pair<THRESH>(h, pk3(c[k], c[k + 2]), clamp_on, pk3(mn[k], mn[k + 2]), pk3(mx[k], mx[k + 2]), b2, ib2,
-                                    o00 + (uint32_t)k * (uint32_t)W, o00 + (uint32_t)(k + 2) * (uint32_t)W, yb + k + 2 < H, out, thr, a.threshold);
+            tol_finish_pair<THRESH>(h, pk3(c[k], c[k + kTolP]), clamp_on, pk3(mn[k], mn[k + kTolP]), pk3(mx[k], mx[k + kTolP]), b2, ib2,
+                                    o00 + (uint32_t)k * (uint32_t)W, o00 + (uint32_t)(k + kTolP) * (uint32_t)W, yb + k + kTolP < H, out, thr, a.threshold, one);
         }
     }
 }
 
-// =====================================================================================================
-// The same resolve as a PERSISTENT, double-buffered kernel: one CTA walks tiles t = blockIdx.x, + gridDim.x, ... and
-// the raw texels of tile t + 1 (current + history, tile + halo: 9.8 KB) travel into the second shared-memory stage
-// with cp.async while tile t is resolved.  The one-shot kernel above leaves the SM waiting for DRAM at the head of
-// every CTA (ncu: long_scoreboard 3.5 stalled warps per issue, issue-active 54 %); here a tile's loads are a whole tile
-// time (about 4 us) ahead of their use.  Two barriers per tile: data landed / neighbourhood staged.
-// =====================================================================================================
-struct TolRing { int ex, ey; bool extra; };
-__device__ __forceinline__ TolRing tol_ring() {          // halo ring: top row (34), bottom row (34), left column (16), right column (16)
-    const int e = threadIdx.x;
-    TolRing r;
-    r.ex = e < 2 * kTolHaloW ? (e < kTolHaloW ? e : e - kTolHaloW) : (e < 2 * kTolHaloW + kTolH ? 0 : kTolHaloW - 1);
-    r.ey = e < 2 * kTolHaloW ? (e < kTolHaloW ? 0 : kTolHaloH - 1) : 1 + ((e - 2 * kTolHaloW) & (kTolH - 1));
-    r.extra = e < kTolExtras;
-    return r;
-}
-
-__device__ __forceinline__ float4 tol_nb_record(float rb, float hg, float df) {   // (y, co, cg, -) from r + b, g / 2, r - b
-    float4 v;
-    v.x = fmaf(rb, 0.25f, hg); v.y = 0.5f * df; v.z = fmaf(rb, -0.25f, hg); v.w = v.x;
-    return v;
-}
-
-template <bool THRESH, bool REGULAR>
-__global__ void __launch_bounds__(kTolThreads, ASH_TOL_CTAS)
-k_taa_tol_pipe(Tex16 cur, Tex16 hist, uint2* __restrict__ out, uint2* __restrict__ thr, TaaTolArgs a, int tiles_x, int n_tiles) {
-    using namespace tol;
-    __shared__ uint2  s_c[2][kTolHaloH][kTolHaloW];      // raw `current`, tile + halo, two stages
-    __shared__ uint2  s_h[2][kTolHaloH][kTolHaloW];      // raw history
-    __shared__ float4 s_nb[kTolHaloH][kTolHaloW];        // tonemapped YCoCg of `current`
-    __shared__ TolTables s_tb;
-    const int W = cur.W, H = cur.H;
-    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
-    const bool clamp_on = a.pc.params[1] > 0.5f;
-    const TolRing ring = tol_ring();
-    const float blend_reg = a.blend;
-
-    auto issue = [&](int bx, int by, int st) {           // this thread's share of a tile's raw texels -> stage st
-        const int x0 = bx * kTolW, y0 = by * kTolH;
-        const uint32_t gx = (uint32_t)min(x0 + tx, W - 1);                                             // CLAMP_TO_EDGE
-#pragma unroll
-        for (int k = 0; k < 4; ++k) {
-            const uint32_t g = (uint32_t)min(y0 + 4 * ty + k, H - 1) * (uint32_t)W + gx;
-            cp_async8(&s_c[st][4 * ty + 1 + k][tx + 1], cur.p + g);
-            cp_async8(&s_h[st][4 * ty + 1 + k][tx + 1], hist.p + g);
-        }
-        if (ring.extra) {
-            const uint32_t g = (uint32_t)min(max(y0 - 1 + ring.ey, 0), H - 1) * (uint32_t)W + (uint32_t)min(max(x0 - 1 + ring.ex, 0), W - 1);
-            cp_async8(&s_c[st][ring.ey][ring.ex], cur.p + g);
-            cp_async8(&s_h[st][ring.ey][ring.ex], hist.p + g);
-        }
-        cp_async_commit();
-    };
-
-    int tile = blockIdx.x;
-    if (tile >= n_tiles) return;
-    // tile coordinates advance without divisions: + gridDim.x tiles = + (dbx, dby) with a carry
-    const int dby = (int)gridDim.x / tiles_x, dbx = (int)gridDim.x - dby * tiles_x;
-    int by = tile / tiles_x, bx = tile - by * tiles_x;
-    issue(bx, by, 0);
-    for (int it = 0;; ++it) {
-        const int st = it & 1, next = tile + (int)gridDim.x;
-        int nbx = bx + dbx, nby = by + dby;
-        if (nbx >= tiles_x) { nbx -= tiles_x; ++nby; }
-        const int x0 = bx * kTolW, y0 = by * kTolH;
-        const int x = x0 + tx, yb = y0 + 4 * ty;
-        cp_async_wait<0>();
-        __syncthreads();                                 // tile landed; everybody is done with the previous tile's stage and s_nb
-        if (next < n_tiles) issue(nbx, nby, st ^ 1);
-        if (!REGULAR) tol_tables(s_tb, a.pc, W, H, x0, y0);
-
-        V3 c[4];                                         // own `current` texels, fp32: neighbourhood staging AND centre tap
-#pragma unroll
-        for (int k = 0; k < 4; ++k) c[k] = tol_unpack(s_c[st][4 * ty + 1 + k][tx + 1]);
-        if (clamp_on) {                                  // :116-121, once per texel
-#pragma unroll
-            for (int k = 0; k < 2; ++k) {                // lanes: rows k and k + 2 (the pairing of the resolve)
-                const V3P t = tonemap(pk3(c[k], c[k + 2]));
-                const P2 rb = add(t.x, t.z), hg = mul(t.y, splat(0.5f)), df = sub(t.x, t.z);
-                s_nb[4 * ty + 1 + k][tx + 1] = tol_nb_record(lo(rb), lo(hg), lo(df));
-                s_nb[4 * ty + 3 + k][tx + 1] = tol_nb_record(hi(rb), hi(hg), hi(df));
-            }
-            if (ring.extra) {
-                const V3 q = tol_unpack(s_c[st][ring.ey][ring.ex]);
-                const V3 t = {q.x * rcp(1.0f + q.x), q.y * rcp(1.0f + q.y), q.z * rcp(1.0f + q.z)};
-                s_nb[ring.ey][ring.ex] = tol_nb_record(t.x + t.z, 0.5f * t.y, t.x - t.z);
-            }
-        }
-        __syncthreads();
-        if (x < W && yb < H) {
-            V3 mn[4], mx[4];
-            if (clamp_on) tol_neighbourhood(s_nb, tx, ty, mn, mx);
-            const float blend = REGULAR ? blend_reg : s_tb.blend;
-            const P2 b2 = splat(blend), ib2 = splat(1.0f - blend);
-            const uint32_t o00 = (uint32_t)yb * (uint32_t)W + (uint32_t)x;
-            if (REGULAR) {
-                const uint2* hb = &s_h[st][4 * ty + 1 + a.dy][tx + 1 + a.dx];
-                V3 ta[5], tb[5];
-#pragma unroll
-                for (int j = 0; j < 5; ++j) { ta[j] = tol_unpack(hb[j * kTolHaloW]); tb[j] = tol_unpack(hb[j * kTolHaloW + 1]); }
-                const P2 fx2 = splat(a.fx), ifx2 = splat(1.0f - a.fx), fy2 = splat(a.fy), ify2 = splat(1.0f - a.fy);
-                V3P hl[3];
-#pragma unroll
-                for (int j = 0; j < 3; ++j) {
-                    const V3P ta2 = pk3(ta[j], ta[j + 2]), tb2 = pk3(tb[j], tb[j + 2]);
-                    hl[j] = {fma(tb2.x, fx2, mul(ta2.x, ifx2)), fma(tb2.y, fx2, mul(ta2.y, ifx2)), fma(tb2.z, fx2, mul(ta2.z, ifx2))};
-                }
-#pragma unroll
-                for (int k = 0; k < 2; ++k) {            // lanes: lo = row yb + k, hi = row yb + k + 2
-                    if (yb + k >= H) break;
-                    const V3P h = {fma(hl[k + 1].x, fy2, mul(hl[k].x, ify2)), fma(hl[k + 1].y, fy2, mul(hl[k].y, ify2)),
-                                   fma(hl[k + 1].z, fy2, mul(hl[k].z, ify2))};
-                    tol_finish_pair<THRESH>(h, pk3(c[k], c[k + 2]), clamp_on, pk3(mn[k], mn[k + 2]), pk3(mx[k], mx[k + 2]), b2, ib2,
-                                            o00 + (uint32_t)k * (uint32_t)W, o00 + (uint32_t)(k + 2) * (uint32_t)W, yb + k + 2 < H, out, thr, a.threshold);
-                }
-            } else {
-                const TolTap col = s_tb.col[tx];
-                const P2 fx2 = splat(col.f), ifx2 = splat(1.0f - col.f);
-                const char* hb = reinterpret_cast<const char*>(&s_h[st][0][0]);
-#pragma unroll
-                for (int k = 0; k < 2; ++k) {
-                    if (yb + k >= H) break;
-                    const TolTap ra = s_tb.row[4 * ty + k], rb = s_tb.row[4 * ty + k + 2];
-                    auto tap = [&](int ro, int co) { return tol_unpack(*reinterpret_cast<const uint2*>(hb + ro + co)); };
-                    const V3P t00 = pk3(tap(ra.i0, col.i0), tap(rb.i0, col.i0)), t01 = pk3(tap(ra.i0, col.i1), tap(rb.i0, col.i1));
-                    const V3P t10 = pk3(tap(ra.i1, col.i0), tap(rb.i1, col.i0)), t11 = pk3(tap(ra.i1, col.i1), tap(rb.i1, col.i1));
-                    const P2 fy = pk(ra.f, rb.f), ify = sub(splat(1.0f), fy);
-                    const V3P top = {fma(t01.x, fx2, mul(t00.x, ifx2)), fma(t01.y, fx2, mul(t00.y, ifx2)), fma(t01.z, fx2, mul(t00.z, ifx2))};
-                    const V3P bot = {fma(t11.x, fx2, mul(t10.x, ifx2)), fma(t11.y, fx2, mul(t10.y, ifx2)), fma(t11.z, fx2, mul(t10.z, ifx2))};
-                    const V3P h = {fma(bot.x, fy, mul(top.x, ify)), fma(bot.y, fy, mul(top.y, ify)), fma(bot.z, fy, mul(top.z, ify))};
-                    tol_finish_pair<THRESH>(h, pk3(c[k], c[k + 2]), clamp_on, pk3(mn[k], mn[k + 2]), pk3(mx[k], mx[k + 2]), b2, ib2,
-                                            o00 + (uint32_t)k * (uint32_t)W, o00 + (uint32_t)(k + 2) * (uint32_t)W, yb + k + 2 < H, out, thr, a.threshold);
-                }
-            }
-        }
-        if (next >= n_tiles) break;
-        tile = next; bx = nbx; by = nby;
-    }
-}
-
-#ifndef ASH_TOL_PIPE
-#define ASH_TOL_PIPE 1                                   // 1: persistent double-buffered kernel; 0: one CTA per tile
-#endif
+// A persistent, cp.async double-buffered variant of this kernel (tile t + 1's raw texels travelling into a second
+// shared-memory stage while tile t is resolved; commit 'k_taa_tol_pipe') was measured SLOWER: 81.9 vs 75.7 us at 4K.
+// It hides the DRAM wait at the head of each CTA (27 % of the stall samples here) but pays 12 % more instructions
+// (own texels re-read from shared memory, per-tile address arithmetic in every thread) and a second barrier per tile.
 static const void* tol_kernel(bool thresh, bool regular) {
-#if ASH_TOL_PIPE
-    return thresh ? (regular ? reinterpret_cast<const void*>(&k_taa_tol_pipe<true, true>) : reinterpret_cast<const void*>(&k_taa_tol_pipe<true, false>))
-                  : (regular ? reinterpret_cast<const void*>(&k_taa_tol_pipe<false, true>) : reinterpret_cast<const void*>(&k_taa_tol_pipe<false, false>));
-#else
     return thresh ? (regular ? reinterpret_cast<const void*>(&k_taa_tol<true, true>) : reinterpret_cast<const void*>(&k_taa_tol<true, false>))
                   : (regular ? reinterpret_cast<const void*>(&k_taa_tol<false, true>) : reinterpret_cast<const void*>(&k_taa_tol<false, false>));
-#endif
 }
 
-// graph replay: argument 4 of k_taa_tol[_pipe] is the per-view TaaTolArgs
+// graph replay: argument 4 of k_taa_tol is the per-view TaaTolArgs
 void taa_tol_patch(bool thresh, const TaaTolArgs& a, PatchArg* out) {
     out->func = tol_kernel(thresh, a.regular != 0);
-    out->arg_index = 4; out->n_args = ASH_TOL_PIPE ? 7 : 5;
+    out->arg_index = 4; out->n_args = 5;
     static_assert(sizeof(TaaTolArgs) <= sizeof(out->value), "PatchArg too small");
     std::memcpy(out->value, &a, sizeof(a));
 }
@@ -441,19 +322,12 @@ void taa_tol_patch(bool thresh, const TaaTolArgs& a, PatchArg* out) {
 cudaError_t launch_taa_tol(const void* cur, const void* hist, void* out, void* thr_or_null, const TaaTolArgs& a, const Launch& L) {
     const int W = (int)a.pc.screen_params[0], H = (int)a.pc.screen_params[1];
     Tex16 c{static_cast<const uint2*>(cur), W, H}, h{static_cast<const uint2*>(hist), W, H};
-    int tiles_x = (W + kTolW - 1) / kTolW, n_tiles = tiles_x * ((H + kTolH - 1) / kTolH);
     uint2* o = static_cast<uint2*>(out);
     uint2* t = static_cast<uint2*>(thr_or_null);
     TaaTolArgs args = a;
-    void* params[7] = {&c, &h, &o, &t, &args, &tiles_x, &n_tiles};
+    void* params[5] = {&c, &h, &o, &t, &args};
     Timed timed(L, thr_or_null ? ASH_KERNEL_TAA_THRESHOLD : ASH_KERNEL_TAA);
-#if ASH_TOL_PIPE
-    static int n_sm = 0;
-    if (!n_sm) { int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev); }
-    const dim3 grid((unsigned)std::min(n_tiles, n_sm * ASH_TOL_CTAS));
-#else
-    const dim3 grid(tiles_x, (H + kTolH - 1) / kTolH);
-#endif
+    const dim3 grid((W + kTolW - 1) / kTolW, (H + kTolH - 1) / kTolH);
     return cudaLaunchKernel(tol_kernel(t != nullptr, a.regular != 0), grid, dim3(kTolThreads), params, 0, L.s);
 }
 
