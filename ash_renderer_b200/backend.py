@@ -26,7 +26,7 @@ EXPORTS = [
     "ashcuda_default_config", "ashcuda_create", "ashcuda_destroy", "ashcuda_set_stream",
     "ashcuda_set_depth", "ashcuda_set_objects", "ashcuda_set_lights", "ashcuda_set_camera",
     "ashcuda_set_color", "ashcuda_taa_reset_history", "ashcuda_hiz_build", "ashcuda_occlusion_cull",
-    "ashcuda_light_cull", "ashcuda_taa_resolve", "ashcuda_bloom", "ashcuda_tonemap",
+    "ashcuda_light_cull", "ashcuda_taa_resolve", "ashcuda_bloom", "ashcuda_tonemap", "ashcuda_set_tonemap_operator",
     "ashcuda_view_run", "ashcuda_get", "ashcuda_readback", "ashcuda_readback_async", "ashcuda_sync",
     "ashcuda_hiz_level_count", "ashcuda_mip_extent", "ashcuda_kernel_launches", "ashcuda_graph_stats", "ashcuda_last_error",
     "ashcuda_version", "ashcuda_profile_kernels", "ashcuda_kernel_time_ms", "ashcuda_upload_view", "ashcuda_download_view", "ashcuda_download_view_packed",
@@ -74,6 +74,7 @@ def load_library():
         "ashcuda_taa_resolve": (i32, [vp, vp]),
         "ashcuda_bloom": (i32, [vp, vp]),
         "ashcuda_tonemap": (i32, [vp, vp]),
+        "ashcuda_set_tonemap_operator": (i32, [vp, u32]),
         "ashcuda_view_run": (i32, [vp, vp]),
         "ashcuda_get": (i32, [vp, i32, C.POINTER(vp), C.POINTER(C.c_size_t)]),
         "ashcuda_readback": (i32, [vp, i32, vp, C.c_size_t]),
@@ -220,6 +221,9 @@ class Context:
     def bloom(self, params):
         bp = np.ascontiguousarray(params, T.BLOOM_PARAMS)
         self._ck(self._lib.ashcuda_bloom(self._h, bp.ctypes.data))
+
+    def set_tonemap_operator(self, op):          # TonemappingFeature::set_operator, tonemapping.rs:92-94
+        self._ck(self._lib.ashcuda_set_tonemap_operator(self._h, int(op)))
 
     def tonemap(self, pc):
         pc = np.ascontiguousarray(pc, T.POST_PC)

@@ -90,7 +90,7 @@ struct GraphKey {
     AshLightCullingPushConstants light;
     float    taa_screen[4];
     AshBloomParams bloom; AshPostProcessPushConstants post;
-    uint32_t in_halo, tol_variant, taa_cur, history_valid, taa_ran, have_color, have_depth, have_instancing, concurrent, have_pyramid;
+    uint32_t in_halo, tol_variant, tonemap_op, taa_cur, history_valid, taa_ran, have_color, have_depth, have_instancing, concurrent, have_pyramid;
     AshForwardParams fwd;
 };
 struct ViewGraph {
@@ -204,6 +204,7 @@ struct ashcuda_ctx {
     ash::BloomChain bloom{};
     bool        bloom_valid = false;
     void*       ldr8 = nullptr;
+    uint32_t    tonemap_op = ASH_TONEMAP_ACES;  // TonemappingConfig.operator (features/tonemapping.rs:9-20)
     bool        center_exact = false;          // (x+0.5)/W taps hit texel x exactly (exact_taps.cu)
     float       taa_chk[4] = {0, 0, 0, 0};     // screen_params the TAA tap check was last run for
     bool        taa_exact = false;
@@ -216,7 +217,7 @@ namespace ash {
 cudaError_t launch_depth_pyramid(const Pyramid& p, uint32_t* tile_minmax, uint32_t tiles_x,
                                  uint32_t* depth_range, uint32_t* ticket, const Launch& L);
 cudaError_t launch_occlusion_cull(const AshCullObjectData* objs, const AshIndirectDrawCommand* draws_in,
-                                  const AshCullingPushConstants& pc, const Pyramid& p,
+                                  uint32_t n_draws, const AshCullingPushConstants& pc, const Pyramid& p,
                                   uint32_t* visibility, uint32_t* vis_bits, uint32_t* cta_counts,
                                   AshIndirectDrawCommand* draws_out, uint32_t* visible_count,
                                   AshViewStats* stats, AshCullingStats* cstats, int phase, bool no_occlusion,
@@ -266,7 +267,7 @@ cudaError_t launch_bloom_downsample(const void* src, uint32_t sw, uint32_t sh, v
 cudaError_t launch_bloom_upsample_add(const void* src, uint32_t sw, uint32_t sh, void* dst, uint32_t dw,
                                       uint32_t dh, float intensity, const Launch& L);
 cudaError_t launch_tonemap(const void* hdr, const void* bloom_or_null, void* ldr8, uint32_t W, uint32_t H,
-                           const AshPostProcessPushConstants& pc, bool center, const Launch& L);
+                           const AshPostProcessPushConstants& pc, bool center, uint32_t op, const Launch& L);
 
 // ---- fast post kernels (post_fast.cu): bit-identical to the general ones, valid when the exact-tap
 //      checks below hold for the extents involved

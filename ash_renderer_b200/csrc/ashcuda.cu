@@ -325,15 +325,15 @@ int ashcuda_occlusion_cull(ashcuda_ctx* c, const AshCullingPushConstants* pc) {
     if (!c || !pc) return fail(c, ASH_ERR_INVALID, "occlusion_cull: null");
     if (!c->have_depth) return fail(c, ASH_ERR_NOT_INITIALIZED, "occlusion_cull: no depth buffer set");
     if (pc->object_count > c->n_objs) return fail(c, ASH_ERR_INVALID, "occlusion_cull: objectCount > uploaded objects");
-    if (pc->hiz_levels == 0 || (int)pc->hiz_levels > c->pyr.levels)
-        return fail(c, ASH_ERR_INVALID, "occlusion_cull: hizLevels outside [1, levels_built]");
+    // hizLevels above the pyramid's own level count is legal (the reference always pushes 10): the sampler clamps
+    if (pc->hiz_levels == 0) return fail(c, ASH_ERR_INVALID, "occlusion_cull: hizLevels == 0");
     ASH_CUDA(c, cudaSetDevice(c->device));
     if (!c->have_pyramid) { int rc = ashcuda_hiz_build(c); if (rc) return rc; }
     if (pc->object_count == 0) {     // PIN-8: visibleCount is zeroed before each dispatch
         ASH_CUDA(c, cudaMemsetAsync(c->visible_count, 0, 4, c->stream));
         return ASH_OK;
     }
-    ASH_CUDA(c, launch_occlusion_cull(c->objs, c->draws_in, *pc, c->pyr, c->visibility, c->vis_bits,
+    ASH_CUDA(c, launch_occlusion_cull(c->objs, c->draws_in, c->n_draws, *pc, c->pyr, c->visibility, c->vis_bits,
                                       c->cta_counts, c->draws_out, c->visible_count, c->stats, c->culling_stats,
                                       0, false, nullptr, c->L()));
     return ASH_OK;
@@ -443,10 +443,17 @@ int ashcuda_tonemap(ashcuda_ctx* c, const AshPostProcessPushConstants* pc) {
     if (!c->have_color) return fail(c, ASH_ERR_NOT_INITIALIZED, "tonemap: no colour buffer set");
     ASH_CUDA(c, cudaSetDevice(c->device));
     const void* bloom = c->bloom_valid ? c->bloom.d[0] : nullptr;
-    if (c->center_exact && ((size_t)c->W * c->H) % 2 == 0)
+    if (c->tonemap_op == ASH_TONEMAP_ACES && c->center_exact && ((size_t)c->W * c->H) % 2 == 0)
         ASH_CUDA(c, launch_tonemap_fast(resolved_color(c), bloom, c->ldr8, c->W, c->H, *pc, c->L()));
-    else
-        ASH_CUDA(c, launch_tonemap(resolved_color(c), bloom, c->ldr8, c->W, c->H, *pc, c->center_exact, c->L()));
+    else        // the operators without a reference shader (PIN-13) run the general kernel
+        ASH_CUDA(c, launch_tonemap(resolved_color(c), bloom, c->ldr8, c->W, c->H, *pc, c->center_exact, c->tonemap_op, c->L()));
+    return ASH_OK;
+}
+
+int ashcuda_set_tonemap_operator(ashcuda_ctx* c, uint32_t op) {      // TonemappingFeature::set_operator, tonemapping.rs:92-94
+    if (!c) return ASH_ERR_INVALID;
+    if (op > ASH_TONEMAP_NONE) return fail(c, ASH_ERR_INVALID, "set_tonemap_operator: unknown operator");
+    c->tonemap_op = op;
     return ASH_OK;
 }
 
@@ -470,7 +477,7 @@ static int view_post(ashcuda_ctx* c, const AshCudaViewParams* vp) {
         if (!thr_done)
             ASH_CUDA(c, launch_bloom_threshold(resolved_color(c), b.d[0], c->W, c->H, vp->bloom.threshold, c->center_exact, c->L()));
         rc = bloom_down(c, vp->bloom.mip_count); if (rc) return rc;
-        const bool fuse_last = (st & ASH_STAGE_TONEMAP) && vp->bloom.mip_count >= 1 && b.up_fast[0];
+        const bool fuse_last = (st & ASH_STAGE_TONEMAP) && vp->bloom.mip_count >= 1 && b.up_fast[0] && c->tonemap_op == ASH_TONEMAP_ACES;
         rc = bloom_up(c, &vp->bloom, fuse_last ? 1 : 0); if (rc) return rc;
         if (fuse_last) {
             const bool keep = (st & ASH_STAGE_KEEP_BLOOM) != 0;
@@ -555,9 +562,9 @@ int ash_view_run_eager(ashcuda_ctx* c, const AshCudaViewParams* vp) {
         c->stream = main_stream;
         if (!rc && e != cudaSuccess) { c->err = std::string("view_run: ") + cudaGetErrorString(e); rc = ASH_ERR_DEVICE; }
     }
-    if (rc) return rc;
-    rc = view_post(c, vp);
-    if (fork) {                                                              // join (also on the error path)
+    if (!rc) rc = view_post(c, vp);
+    if (fork) {                                                              // join, also on the error path: later main-stream work
+                                                                             // must not race kernels still running on front_stream
         cudaError_t e = cudaStreamWaitEvent(c->stream, c->ev_join, 0);
         if (!rc && e != cudaSuccess) { c->err = std::string("view_run: ") + cudaGetErrorString(e); rc = ASH_ERR_DEVICE; }
     }
@@ -726,7 +733,7 @@ static int two_phase_cull(ashcuda_ctx* c, const AshCudaViewParams* vp) {
     const AshCullingPushConstants* pc = &vp->cull;
     if (pc->object_count > c->n_objs) return fail(c, ASH_ERR_INVALID, "two_phase: objectCount > uploaded objects");
     if (pc->object_count == 0) return fail(c, ASH_ERR_INVALID, "two_phase: no objects");
-    if (pc->hiz_levels == 0 || (int)pc->hiz_levels > c->pyr.levels) return fail(c, ASH_ERR_INVALID, "two_phase: hizLevels outside [1, levels_built]");
+    if (pc->hiz_levels == 0) return fail(c, ASH_ERR_INVALID, "two_phase: hizLevels == 0");
     if (vp->camera.projection[2][3] != -1.0f || vp->camera.projection[3][3] != 0.0f)
         return fail(c, ASH_ERR_INVALID, "two_phase: projection is not a right-handed perspective (w_clip = -z_view)");
     if (c->W > 65535u || c->H > 65535u) return fail(c, ASH_ERR_INVALID, "two_phase: extent above 65535");
@@ -739,7 +746,7 @@ static int two_phase_cull(ashcuda_ctx* c, const AshCudaViewParams* vp) {
     ASH_CUDA(c, launch_forward_setup(vp->camera, c->fwd_params, c->objs, n, c->lights, c->n_lights, c->W, c->H, B, c->L()));
     c->depth = c->depth_owned; c->pyr.mip0 = c->depth;
     // phase 1: against the previous pyramid; draw the survivors; Hi-Z of what was drawn
-    ASH_CUDA(c, launch_occlusion_cull(c->objs, c->draws_in, *pc, c->pyr, c->visibility, c->vis_bits, c->cta_counts, c->draws_out,
+    ASH_CUDA(c, launch_occlusion_cull(c->objs, c->draws_in, c->n_draws, *pc, c->pyr, c->visibility, c->vis_bits, c->cta_counts, c->draws_out,
                                       c->visible_count, c->stats, c->culling_stats, 1, !have_prev, nullptr, c->L()));
     ASH_CUDA(c, launch_forward_splat(n, c->W, c->H, B, c->visibility, c->L()));
     ASH_CUDA(c, launch_forward_resolve(c->W, c->H, B, c->L()));
@@ -747,7 +754,7 @@ static int two_phase_cull(ashcuda_ctx* c, const AshCudaViewParams* vp) {
     rc = ashcuda_hiz_build(c);
     if (rc) return rc;
     // phase 2: everything phase 1 rejected, against the new pyramid; draw the late objects; final depth
-    ASH_CUDA(c, launch_occlusion_cull(c->objs, c->draws_in, *pc, c->pyr, c->visibility, c->vis_bits, c->cta_counts, c->draws_out,
+    ASH_CUDA(c, launch_occlusion_cull(c->objs, c->draws_in, c->n_draws, *pc, c->pyr, c->visibility, c->vis_bits, c->cta_counts, c->draws_out,
                                       c->visible_count, c->stats, c->culling_stats, 2, false, c->fwd_late, c->L()));
     ASH_CUDA(c, launch_forward_splat(n, c->W, c->H, B, c->fwd_late, c->L()));
     ASH_CUDA(c, launch_forward_resolve(c->W, c->H, B, c->L()));

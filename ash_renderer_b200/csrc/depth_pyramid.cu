@@ -167,7 +167,7 @@ k_depth_pyramid(Pyramid p, uint32_t* __restrict__ tile_minmax, uint32_t tiles_x,
 constexpr int kTailCap = 4096;     // texels of the first tail level that fit the shared-memory path
 __global__ void __launch_bounds__(1024)
 k_pyramid_tail(Pyramid p) {
-    __shared__ float s_a[kTailCap], s_b[kTailCap / 4 + 1];
+    __shared__ float s_a[kTailCap], s_b[kTailCap / 2];     // a level with one extent clamped to 1 only HALVES (4096x1 -> 2048x1)
     const int F = p.fast_levels;
     const float* src_g = (F == 0) ? p.mip0 : p.mips + p.off[F];
     int sw = (int)p.w[F], sh = (int)p.h[F];

@@ -114,7 +114,9 @@ k_occlusion_cull(const AshCullObjectData* __restrict__ objs, CullParams cp, Pyra
                     maxx = gclamp(maxx, 0.0f, 1.0f); maxy = gclamp(maxy, 0.0f, 1.0f);
                     const float ssx = fmul(fsub(maxx, minx), cp.screen_w);
                     const float ssy = fmul(fsub(maxy, miny), cp.screen_h);
-                    const int level = mip_from_size(gmax(ssx, ssy), (int)(cp.hiz_levels - 1u));
+                    // the image's own mip count bounds the sampler's level as well (textureLod clamps to the last mip):
+                    // the reference pushes HIZ_LEVELS = 10 whatever the extent (occlusion_culling.rs:21,262)
+                    const int level = mip_from_size(gmax(ssx, ssy), min((int)(cp.hiz_levels - 1u), pyr.levels - 1));
                     const float u = fmul(fadd(minx, maxx), 0.5f), v = fmul(fadd(miny, maxy), 0.5f);
                     const int lw = (int)pyr.w[level], lh = (int)pyr.h[level];
                     const float* base = level == 0 ? pyr.mip0 : pyr.mips + pyr.off[level];
@@ -151,7 +153,7 @@ k_occlusion_cull(const AshCullObjectData* __restrict__ objs, CullParams cp, Pyra
 // Ordered compaction (PIN-7): slot = #visible objects with a smaller index.
 __global__ void __launch_bounds__(kCullThreads)
 k_cull_compact(const AshCullObjectData* __restrict__ objs, const AshIndirectDrawCommand* __restrict__ draws_in,
-               uint32_t object_count, const uint32_t* __restrict__ vis_bits,
+               uint32_t n_draws, uint32_t object_count, const uint32_t* __restrict__ vis_bits,
                const uint32_t* __restrict__ cta_counts, AshIndirectDrawCommand* __restrict__ draws_out,
                uint32_t* __restrict__ visible_count, AshViewStats* __restrict__ stats,
                AshCullingStats* __restrict__ cstats) {
@@ -179,8 +181,10 @@ k_cull_compact(const AshCullObjectData* __restrict__ objs, const AshIndirectDraw
         const uint32_t di = objs[idx].draw_index;
         const uint32_t* src = reinterpret_cast<const uint32_t*>(draws_in + di);   // :229-232
         uint32_t* dst = reinterpret_cast<uint32_t*>(draws_out + slot);
+        // a drawIndex past the template buffer reads zeros, as Vulkan's robustBufferAccess returns for the shader's
+        // drawCommandsIn[obj.drawIndex] (an unchecked read would be a sticky illegal-address fault here)
 #pragma unroll
-        for (int k = 0; k < 5; ++k) dst[k] = __ldg(src + k);
+        for (int k = 0; k < 5; ++k) dst[k] = di < n_draws ? __ldg(src + k) : 0u;
     }
     if (blockIdx.x == gridDim.x - 1 && threadIdx.x == 0) {
         const uint32_t total = base + cta_counts[blockIdx.x];
@@ -215,7 +219,7 @@ void cull_patch(const AshCullingPushConstants& pc, int mode, PatchArg* out) {
 
 // phase: 0 = the reference dispatch + compaction; 1 = phase 1 (no compaction); 2 = phase 2 + compaction
 cudaError_t launch_occlusion_cull(const AshCullObjectData* objs, const AshIndirectDrawCommand* draws_in,
-                                  const AshCullingPushConstants& pc, const Pyramid& p,
+                                  uint32_t n_draws, const AshCullingPushConstants& pc, const Pyramid& p,
                                   uint32_t* visibility, uint32_t* vis_bits, uint32_t* cta_counts,
                                   AshIndirectDrawCommand* draws_out, uint32_t* visible_count,
                                   AshViewStats* stats, AshCullingStats* cstats, int phase, bool no_occlusion,
@@ -235,7 +239,7 @@ cudaError_t launch_occlusion_cull(const AshCullObjectData* objs, const AshIndire
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess || phase == 1) return e;
     Timed timed(L, ASH_KERNEL_CULL_COMPACT);
-    k_cull_compact<<<grid, kCullThreads, 0, L.s>>>(objs, draws_in, pc.object_count, vis_bits, cta_counts,
+    k_cull_compact<<<grid, kCullThreads, 0, L.s>>>(objs, draws_in, n_draws, pc.object_count, vis_bits, cta_counts,
                                                  draws_out, visible_count, stats, cstats);
     return cudaGetLastError();
 }

@@ -176,7 +176,7 @@ cudaError_t launch_bloom_upsample_add(const void* src, uint32_t sw, uint32_t sh,
 // ---------------------------------------------------------------- tonemap (tonemapping.frag:20-49, PIN-11)
 template <bool CENTER>
 __global__ void __launch_bounds__(256)
-k_tonemap(Tex16 hdr, Tex16 bloom, uint32_t* __restrict__ ldr8, AshPostProcessPushConstants pc) {
+k_tonemap(Tex16 hdr, Tex16 bloom, uint32_t* __restrict__ ldr8, AshPostProcessPushConstants pc, uint32_t op) {
     const int x = blockIdx.x * 32 + (threadIdx.x & 31), y = blockIdx.y * 8 + (threadIdx.x >> 5);
     if (x >= hdr.W || y >= hdr.H) return;
     V3 c, b = {0.0f, 0.0f, 0.0f};
@@ -191,19 +191,19 @@ k_tonemap(Tex16 hdr, Tex16 bloom, uint32_t* __restrict__ ldr8, AshPostProcessPus
     c = add3(c, scale3(b, pc.bloom_intensity));                                            // :38
     c = scale3(c, pc.exposure);                                                            // :41
     const float ig = fdiv(1.0f, pc.gamma);
-    const uint32_t r8 = to_unorm8(powf(aces(c.x), ig));                                    // :44-47
-    const uint32_t g8 = to_unorm8(powf(aces(c.y), ig));
-    const uint32_t b8 = to_unorm8(powf(aces(c.z), ig));
+    const uint32_t r8 = to_unorm8(powf(tonemap_curve(c.x, op), ig));                       // :44-47 (aces, or PIN-13)
+    const uint32_t g8 = to_unorm8(powf(tonemap_curve(c.y, op), ig));
+    const uint32_t b8 = to_unorm8(powf(tonemap_curve(c.z, op), ig));
     ldr8[(size_t)y * hdr.W + x] = r8 | (g8 << 8) | (b8 << 16) | 0xFF000000u;
 }
 
 cudaError_t launch_tonemap(const void* hdr, const void* bloom_or_null, void* ldr8, uint32_t W, uint32_t H,
-                           const AshPostProcessPushConstants& pc, bool center, const Launch& L) {
+                           const AshPostProcessPushConstants& pc, bool center, uint32_t op, const Launch& L) {
     const Tex16 h{static_cast<const uint2*>(hdr), (int)W, (int)H}, b{static_cast<const uint2*>(bloom_or_null), (int)W, (int)H};
     const dim3 grid((W + 31) / 32, (H + 7) / 8);
     Timed timed(L, ASH_KERNEL_TONEMAP);
-    if (center) k_tonemap<true><<<grid, 256, 0, L.s>>>(h, b, static_cast<uint32_t*>(ldr8), pc);
-    else k_tonemap<false><<<grid, 256, 0, L.s>>>(h, b, static_cast<uint32_t*>(ldr8), pc);
+    if (center) k_tonemap<true><<<grid, 256, 0, L.s>>>(h, b, static_cast<uint32_t*>(ldr8), pc, op);
+    else k_tonemap<false><<<grid, 256, 0, L.s>>>(h, b, static_cast<uint32_t*>(ldr8), pc, op);
     return cudaGetLastError();
 }
 

@@ -64,6 +64,19 @@ __device__ __forceinline__ V3 soft_threshold(V3 c, float threshold) {
 __device__ __forceinline__ float aces(float x) {                                           // :20-27
     return gclamp(fdiv(fmul(x, fadd(fmul(2.51f, x), 0.03f)), fadd(fmul(x, fadd(fmul(2.43f, x), 0.59f)), 0.14f)), 0.0f, 1.0f);
 }
+// TonemapOperator (features/tonemapping.rs:9-20); PIN-13 in include/ashcuda.h.  x = exposed HDR channel.
+__device__ __forceinline__ float hable(float x) {        // ((x (A x + C B) + D E) / (x (A x + B) + D F)) - E / F
+    const float A = 0.15f, B = 0.50f, C = 0.10f, D = 0.20f, E = 0.02f, F = 0.30f;
+    return fsub(fdiv(fadd(fmul(x, fadd(fmul(A, x), fmul(C, B))), fmul(D, E)), fadd(fmul(x, fadd(fmul(A, x), B)), fmul(D, F))), fdiv(E, F));
+}
+__device__ __forceinline__ float tonemap_curve(float x, uint32_t op) {
+    switch (op) {
+        case ASH_TONEMAP_REINHARD:   return gclamp(fdiv(x, fadd(1.0f, x)), 0.0f, 1.0f);
+        case ASH_TONEMAP_UNCHARTED2: return gclamp(fdiv(hable(fmul(2.0f, x)), hable(11.2f)), 0.0f, 1.0f);
+        case ASH_TONEMAP_NONE:       return gclamp(x, 0.0f, 1.0f);
+        default:                     return aces(x);
+    }
+}
 __device__ __forceinline__ uint32_t to_unorm8(float l) {
     return (uint32_t)floorf(fadd(fmul(gclamp(l, 0.0f, 1.0f), 255.0f), 0.5f));
 }

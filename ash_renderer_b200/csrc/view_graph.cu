@@ -55,6 +55,7 @@ GraphKey make_key(const ashcuda_ctx* c, const AshCudaViewParams* vp) {
     std::memcpy(k.taa_screen, vp->taa.screen_params, sizeof(k.taa_screen));
     k.bloom = vp->bloom; k.post = vp->post;
     k.in_halo = taa_in_halo(vp->taa) ? 1u : 0u;
+    k.tonemap_op = c->tonemap_op;
     if (c->cfg.precision == ASH_PRECISION_FAST && (vp->stages & ASH_STAGE_TAA) && k.in_halo) {   // which k_taa_tol instance the graph holds
         TaaTolArgs ta;
         k.tol_variant = 1u + ash_taa_tol_plan(const_cast<ashcuda_ctx*>(c), vp->taa, vp->bloom.threshold, &ta).regular;

@@ -359,10 +359,17 @@ class BloomConfig:
 
 
 class TonemappingConfig:
-    """features/tonemapping.rs:22-44 (only the ACES operator has a shader)."""
+    """features/tonemapping.rs:9-44.  `operator` is one of TonemapOperator's names; only Aces has a shader in the
+    reference, the others follow PIN-13 (include/ashcuda.h)."""
+    OPERATORS = {"Aces": T.TONEMAP_ACES, "Reinhard": T.TONEMAP_REINHARD, "Uncharted2": T.TONEMAP_UNCHARTED2, "None": T.TONEMAP_NONE}
 
-    def __init__(self, exposure=1.0, gamma=2.2):
-        self.operator, self.exposure, self.gamma = "Aces", exposure, gamma
+    def __init__(self, exposure=1.0, gamma=2.2, operator="Aces", enabled=True):
+        if operator not in self.OPERATORS:
+            raise ValueError(f"unknown TonemapOperator {operator!r}")
+        self.operator, self.exposure, self.gamma, self.enabled = operator, exposure, gamma, enabled
+
+    def operator_id(self):
+        return self.OPERATORS[self.operator]
 
     def push_constants(self, bloom_intensity):
         pc = np.zeros(1, T.POST_PC)
@@ -769,7 +776,8 @@ class CudaComputeFeature(RenderFeature):
                 st |= T.STAGE_TAA
             if self.bloom.enabled:
                 st |= T.STAGE_BLOOM
-            st |= T.STAGE_TONEMAP
+            if self.tonemapping.enabled:             # TonemappingFeature::render returns early when disabled (:127-129)
+                st |= T.STAGE_TONEMAP
         vp["stages"] = st
         return vp
 
@@ -778,6 +786,7 @@ class CudaComputeFeature(RenderFeature):
             from .backend import AshError, ASH_ERR_NOT_INITIALIZED
             raise AshError(ASH_ERR_NOT_INITIALIZED, "CudaComputeFeature used before on_added")
         self.taa.begin_frame()
+        self.ctx.set_tonemap_operator(self.tonemapping.operator_id())
         if self._scene_dirty:
             self.ctx.set_objects(self.culling.object_data(), self.draw_templates)
             self.ctx.upload_lights(self.lights.get_light_buffer_data())

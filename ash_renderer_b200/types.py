@@ -81,6 +81,8 @@ assert TAA_PC.itemsize == 48 and POST_PC.itemsize == 16 and BLOOM_PARAMS.itemsiz
 assert CONFIG.itemsize == 64 and VIEW_STATS.itemsize == 32
 assert VIEW_PARAMS.itemsize == 96 + 16 + 208 + 48 + 16 + 16 + 16
 
+TONEMAP_ACES, TONEMAP_REINHARD, TONEMAP_UNCHARTED2, TONEMAP_NONE = 0, 1, 2, 3   # TonemapOperator, tonemapping.rs:9-20
+
 TILE_SIZE = 16
 MAX_LIGHTS_PER_TILE = 256
 TILE_STRIDE = 257

@@ -376,6 +376,19 @@ int ashcuda_light_cull    (ashcuda_ctx*, const AshLightCullingPushConstants*);  
 int ashcuda_taa_resolve   (ashcuda_ctx*, const AshTaaPushConstants*);            /* taa_resolve.comp           */
 int ashcuda_bloom         (ashcuda_ctx*, const AshBloomParams*);                 /* bloom_{threshold,downsample,upsample}.frag */
 int ashcuda_tonemap       (ashcuda_ctx*, const AshPostProcessPushConstants*);    /* tonemapping.frag           */
+/* TonemappingConfig.operator / TonemappingFeature::set_operator (features/tonemapping.rs:9-20, 92-94).  The reference
+ * has a shader for Aces only (tonemapping.frag:20-27); the other three are the published closed forms, pinned here
+ * (PIN-13) and restated identically by the oracle, applied where tonemapping.frag:44 applies aces(), gamma after:
+ *   ASH_TONEMAP_REINHARD    clamp(x / (1 + x), 0, 1)
+ *   ASH_TONEMAP_UNCHARTED2  clamp(h(2 x) / h(11.2), 0, 1),  h(x) = (x (A x + C B) + D E) / (x (A x + B) + D F) - E / F
+ *                           with A .15, B .50, C .10, D .20, E .02, F .30 (Hable 2010: exposure bias 2, white point 11.2)
+ *   ASH_TONEMAP_NONE        clamp(x, 0, 1)
+ * Applies to ashcuda_tonemap and ashcuda_view_run from the next call on; default ASH_TONEMAP_ACES. */
+#define ASH_TONEMAP_ACES       0u
+#define ASH_TONEMAP_REINHARD   1u
+#define ASH_TONEMAP_UNCHARTED2 2u
+#define ASH_TONEMAP_NONE       3u
+int ashcuda_set_tonemap_operator(ashcuda_ctx*, uint32_t op);
 /* the whole view-frame in one call, fused kernels, same results as the staged calls */
 int ashcuda_view_run      (ashcuda_ctx*, const AshCudaViewParams*);
 

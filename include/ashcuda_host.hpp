@@ -268,8 +268,12 @@ struct BloomConfig {                                // features/bloom.rs:9-33 (s
     float threshold = 0.8f, intensity = 0.5f; uint32_t mip_count = 5; float soft_knee = 0.5f; bool enabled = true;
     AshBloomParams params() const { return AshBloomParams{threshold, 1.0f, mip_count, 0}; }
 };
-struct TonemappingConfig {                          // features/tonemapping.rs:22-44 (ACES is the only operator with a shader)
+enum class TonemapOperator : uint32_t { Aces = ASH_TONEMAP_ACES, Reinhard = ASH_TONEMAP_REINHARD,   // features/tonemapping.rs:9-20
+                                        Uncharted2 = ASH_TONEMAP_UNCHARTED2, None = ASH_TONEMAP_NONE };
+struct TonemappingConfig {                          // features/tonemapping.rs:22-44 (Aces has the shader; the others: PIN-13, ashcuda.h)
+    TonemapOperator op = TonemapOperator::Aces;
     float exposure = 1.0f, gamma = 2.2f;
+    bool enabled = true;
     AshPostProcessPushConstants push_constants(float bloom_intensity) const { return AshPostProcessPushConstants{exposure, gamma, bloom_intensity, 0.0f}; }
 };
 
@@ -596,6 +600,7 @@ public:
             if (!check(ashcuda_set_depth(ctx_, inputs_.depth, inputs_.on_device), "set_depth")) return;
             if (inputs_.hdr && !check(ashcuda_set_color(ctx_, inputs_.hdr, inputs_.velocity, inputs_.on_device), "set_color")) return;
         }
+        if (!check(ashcuda_set_tonemap_operator(ctx_, (uint32_t)tonemapping.op), "set_tonemap_operator")) return;
         const AshCudaViewParams vp = view_params();
         check(ashcuda_view_run(ctx_, &vp), "view_run");
     }
@@ -620,7 +625,7 @@ public:
         if (inputs_.hdr || produce_inputs) {
             if (taa.is_enabled()) st |= ASH_STAGE_TAA;
             if (bloom.enabled) st |= ASH_STAGE_BLOOM;
-            st |= ASH_STAGE_TONEMAP;
+            if (tonemapping.enabled) st |= ASH_STAGE_TONEMAP;
         }
         vp.stages = st;
         return vp;

@@ -233,9 +233,12 @@ static int mip_from_size(float s, int hi) {
     return k > hi ? hi : k;
 }
 
+extern "C" int ash_oracle_hiz_level_count(int W, int H);
 struct Pyramid { const float* depth; const float* mips; int W, H; };
 static float pyramid_fetch(const Pyramid& p, int level, float u, float v) {
     int w = p.W, h = p.H; const float* base = p.depth; size_t off = 0;
+    const int last = ash_oracle_hiz_level_count(p.W, p.H) - 1;     // textureLod clamps to the image's last mip
+    if (level > last) level = last;
     for (int l = 1; l <= level; ++l) {
         int nw = w / 2 > 0 ? w / 2 : 1, nh = h / 2 > 0 ? h / 2 : 1;
         if (l > 1) off += (size_t)w * h;
@@ -271,10 +274,11 @@ static bool occlusion_cull(vec3 center, vec3 e, const mat4& vp, const float scre
 }
 
 // returns visibleCount
-uint32_t ash_oracle_occlusion_cull(const AshCullObjectData* objs, const AshIndirectDrawCommand* draws_in,
-                                   const AshCullingPushConstants* pc, const float* depth,
-                                   const float* mips, int W, int H,
-                                   uint32_t* visibility, AshIndirectDrawCommand* draws_out) {
+// n_draws: size of drawCommandsIn; a drawIndex beyond it reads zeros (Vulkan robustBufferAccess)
+uint32_t ash_oracle_occlusion_cull_n(const AshCullObjectData* objs, const AshIndirectDrawCommand* draws_in, uint32_t n_draws,
+                                     const AshCullingPushConstants* pc, const float* depth,
+                                     const float* mips, int W, int H,
+                                     uint32_t* visibility, AshIndirectDrawCommand* draws_out) {
     mat4 vp = load_mat4(pc->view_proj);
     vec4 planes[6];
     extract_frustum_planes(vp, planes);            // same for every invocation (:207-208)
@@ -294,8 +298,16 @@ uint32_t ash_oracle_occlusion_cull(const AshCullObjectData* objs, const AshIndir
     }
     uint32_t count = 0;                              // PIN-7: compaction in ascending index order
     for (int i = 0; i < n; ++i)
-        if (visibility[i]) { if (draws_out) draws_out[count] = draws_in[objs[i].draw_index]; ++count; }
+        if (visibility[i]) {
+            if (draws_out) draws_out[count] = objs[i].draw_index < n_draws ? draws_in[objs[i].draw_index] : AshIndirectDrawCommand{};
+            ++count;
+        }
     return count;
+}
+uint32_t ash_oracle_occlusion_cull(const AshCullObjectData* objs, const AshIndirectDrawCommand* draws_in,
+                                   const AshCullingPushConstants* pc, const float* depth, const float* mips, int W, int H,
+                                   uint32_t* visibility, AshIndirectDrawCommand* draws_out) {
+    return ash_oracle_occlusion_cull_n(objs, draws_in, 0xFFFFFFFFu, pc, depth, mips, W, H, visibility, draws_out);
 }
 
 // ==========================================================================================
@@ -537,8 +549,23 @@ void ash_oracle_bloom_upsample_add(const uint16_t* srcp, int sw, int sh, uint16_
 // ==========================================================================================
 // Tonemap — shaders/tonemapping.frag:20-49, 8-bit store per PIN-11.
 // ==========================================================================================
-void ash_oracle_tonemap(const uint16_t* hdrp, const uint16_t* bloomp, int W, int H,
-                        const AshPostProcessPushConstants* pc, uint8_t* ldr8) {
+// TonemapOperator (src/renderer/features/tonemapping.rs:9-20): Aces = the shader's curve (:20-27); Reinhard, Uncharted2 and
+// None have no shader in the reference and follow PIN-13 (include/ashcuda.h): the published closed forms.
+static float hable(float x) {
+    const float A = 0.15f, B = 0.50f, C = 0.10f, D = 0.20f, E = 0.02f, F = 0.30f;
+    return ((x * (A * x + C * B) + D * E) / (x * (A * x + B) + D * F)) - E / F;
+}
+static float tonemap_curve(float xx, uint32_t op) {
+    switch (op) {
+        case ASH_TONEMAP_REINHARD:   return gclamp(xx / (1.0f + xx), 0.0f, 1.0f);
+        case ASH_TONEMAP_UNCHARTED2: return gclamp(hable(2.0f * xx) / hable(11.2f), 0.0f, 1.0f);
+        case ASH_TONEMAP_NONE:       return gclamp(xx, 0.0f, 1.0f);
+        default:                     return gclamp((xx * (2.51f * xx + 0.03f)) / (xx * (2.43f * xx + 0.59f) + 0.14f), 0.0f, 1.0f);   // :20-27
+    }
+}
+
+void ash_oracle_tonemap_op(const uint16_t* hdrp, const uint16_t* bloomp, int W, int H,
+                           const AshPostProcessPushConstants* pc, uint32_t op, uint8_t* ldr8) {
     const Img16 hdr{hdrp, W, H}, bloom{bloomp, W, H};
     const float inv_gamma = 1.0f / pc->gamma;
 #pragma omp parallel for schedule(static)
@@ -552,9 +579,7 @@ void ash_oracle_tonemap(const uint16_t* hdrp, const uint16_t* bloomp, int W, int
             float in[3] = {c.x, c.y, c.z};
             uint8_t* o = ldr8 + ((size_t)y * W + x) * 4;
             for (int k = 0; k < 3; ++k) {
-                float xx = in[k];
-                float l = (xx * (2.51f * xx + 0.03f)) / (xx * (2.43f * xx + 0.59f) + 0.14f);   // :20-27
-                l = gclamp(l, 0.0f, 1.0f);
+                float l = tonemap_curve(in[k], op);
                 l = powf(l, inv_gamma);                                           // :47
                 o[k] = (uint8_t)floorf(gclamp(l, 0.0f, 1.0f) * 255.0f + 0.5f);   // PIN-11
             }
@@ -565,6 +590,11 @@ void ash_oracle_tonemap(const uint16_t* hdrp, const uint16_t* bloomp, int W, int
 // PIN-6 weight model of the LINEAR sampler: 0 = 8-bit sub-texel weights (what the library implements),
 // 1 = exact fp32 weights (SURVEY.md PIN-6 as first written); tests/test_oracle_ref.py bounds the difference.
 void ash_oracle_set_weight_mode(int exact) { g_exact_weights = exact ? 1 : 0; }
+
+void ash_oracle_tonemap(const uint16_t* hdrp, const uint16_t* bloomp, int W, int H,
+                        const AshPostProcessPushConstants* pc, uint8_t* ldr8) {
+    ash_oracle_tonemap_op(hdrp, bloomp, W, H, pc, ASH_TONEMAP_ACES, ldr8);
+}
 
 // fp16 helpers exported for the tests (checked against numpy.float16)
 uint16_t ash_oracle_f2h(float f) { return f2h(f); }

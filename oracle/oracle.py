@@ -124,8 +124,9 @@ def occlusion_cull(objs, draws_in, pc, depth, mips_flat=None):
     n = int(pc["object_count"][0])
     vis = np.zeros(max(n, 1), np.uint32)
     draws_out = np.zeros(max(n, 1), DRAW_DTYPE)
-    cnt = lib().ash_oracle_occlusion_cull(_p(objs), _p(draws_in), _p(pc), _p(depth), _p(mips_flat),
-                                          W, H, _p(vis), _p(draws_out))
+    lib().ash_oracle_occlusion_cull_n.restype = C.c_uint32
+    cnt = lib().ash_oracle_occlusion_cull_n(_p(objs), _p(draws_in), C.c_uint32(len(draws_in.reshape(-1))), _p(pc), _p(depth),
+                                            _p(mips_flat), W, H, _p(vis), _p(draws_out))
     return vis[:n], draws_out[:cnt], int(cnt)
 
 
@@ -201,13 +202,16 @@ def bloom_chain(hdr, threshold=0.8, mip_count=5, intensity=1.0):
     return U, D
 
 
-def tonemap(hdr, bloom, pc):
+TONEMAP_ACES, TONEMAP_REINHARD, TONEMAP_UNCHARTED2, TONEMAP_NONE = range(4)
+
+
+def tonemap(hdr, bloom, pc, op=TONEMAP_ACES):
     hdr = _c(hdr, np.float16)
     bloom = None if bloom is None else _c(bloom, np.float16)
     pc = _c(pc, POST_PC_DTYPE).reshape(1)
     H, W, _ = hdr.shape
     out = np.empty((H, W, 4), np.uint8)
-    lib().ash_oracle_tonemap(_p(hdr), _p(bloom), W, H, _p(pc), _p(out))
+    lib().ash_oracle_tonemap_op(_p(hdr), _p(bloom), W, H, _p(pc), C.c_uint32(op), _p(out))
     return out
 
 

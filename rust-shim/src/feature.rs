@@ -104,6 +104,7 @@ impl RenderFeature for CudaComputeFeature {
     }
     unsafe fn render(&self, _ctx: &FeatureRenderContext<'_>) {
         if let (false, Some(vp)) = (self.ctx.is_null(), self.params.as_ref()) {
+            ashcuda_set_tonemap_operator(self.ctx, self.tonemapping.operator as u32);   // Aces, Reinhard, Uncharted2, None = 0..3
             if let Err(e) = check(self.ctx, ashcuda_view_run(self.ctx, vp)) { log::error!("ashcuda_view_run: {e}"); }
         }
     }

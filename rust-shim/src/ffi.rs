@@ -117,6 +117,7 @@ extern "C" {
     pub fn ashcuda_taa_resolve(ctx: *mut ashcuda_ctx, pc: *const TaaPushConstants) -> c_int;
     pub fn ashcuda_bloom(ctx: *mut ashcuda_ctx, bp: *const AshBloomParams) -> c_int;
     pub fn ashcuda_tonemap(ctx: *mut ashcuda_ctx, pc: *const PostProcessPushConstants) -> c_int;
+    pub fn ashcuda_set_tonemap_operator(ctx: *mut ashcuda_ctx, op: u32) -> c_int;
     pub fn ashcuda_view_run(ctx: *mut ashcuda_ctx, vp: *const AshCudaViewParams) -> c_int;
     pub fn ashcuda_set_instances(ctx: *mut ashcuda_ctx, instances: *const InstanceData, batch_id: *const u32, lod_mesh_id: *const u32, n: u32, on_device: c_int) -> c_int;
     pub fn ashcuda_set_lod_meshes(ctx: *mut ashcuda_ctx, meshes: *const AshLodMesh, n: u32, on_device: c_int) -> c_int;

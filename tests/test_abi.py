@@ -24,6 +24,19 @@ def test_header_symbols_match_binding_list():
     assert _declared() == sorted(backend.EXPORTS)
 
 
+def test_rust_shim_extern_block_matches_the_header():
+    """rust-shim/ cannot be built here (no cargo): keep its `extern "C"` list and its AshCudaConfig from drifting."""
+    ffi = open(os.path.join(ROOT, "rust-shim", "src", "ffi.rs")).read()
+    assert sorted(set(re.findall(r"pub fn (ashcuda_[a-z0-9_]+)\s*\(", ffi))) == _declared()
+    cfg = re.search(r"pub struct AshCudaConfig \{(.*?)\}", ffi, flags=re.S).group(1)
+    rust_fields = re.findall(r"pub (\w+):", cfg)
+    assert rust_fields == list(T.CONFIG.names), (rust_fields, T.CONFIG.names)
+    build_rs = open(os.path.join(ROOT, "rust-shim", "build.rs")).read()
+    makefile = open(os.path.join(ROOT, "ash_renderer_b200", "csrc", "Makefile")).read()
+    srcs = re.search(r"SRCS\s*:=\s*(.*)", makefile).group(1).split()
+    assert sorted(re.findall(r'"(\w+\.cu)"', build_rs)) == sorted(srcs)
+
+
 def test_library_exports_every_declared_symbol():
     lib = backend.load_library()
     for name in _declared():

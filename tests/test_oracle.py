@@ -449,6 +449,30 @@ def test_tonemap_known_values(oracle):
     assert np.all(np.abs(out2[0, :, 1].astype(np.int64) - ref2) <= 1)
 
 
+def test_tonemap_operators_match_the_published_closed_forms(oracle):
+    """TonemapOperator::{Reinhard, Uncharted2, None} (features/tonemapping.rs:9-20) have no shader in the reference:
+    PIN-13 pins the published closed forms; the oracle is checked against a float64 restatement of each."""
+    pc = np.zeros(1, T.POST_PC)
+    pc["exposure"], pc["gamma"], pc["bloom_intensity"] = 1.5, 2.2, 0.0
+    vals = np.concatenate([np.linspace(0, 4, 200), [8.0, 11.2, 50.0, 60000.0]]).astype(np.float16)
+    hdr = np.zeros((1, len(vals), 4), np.float16)
+    hdr[0, :, :3] = vals[:, None]
+    x = vals.astype(np.float64) * 1.5
+
+    def hable(v):
+        A, B, C, D, E, F = 0.15, 0.50, 0.10, 0.20, 0.02, 0.30
+        return ((v * (A * v + C * B) + D * E) / (v * (A * v + B) + D * F)) - E / F
+    curves = {oracle.TONEMAP_REINHARD: x / (1 + x), oracle.TONEMAP_UNCHARTED2: hable(2 * x) / hable(11.2), oracle.TONEMAP_NONE: x,
+              oracle.TONEMAP_ACES: (x * (2.51 * x + 0.03)) / (x * (2.43 * x + 0.59) + 0.14)}
+    for op, curve in curves.items():
+        out = oracle.tonemap(hdr, None, pc, op)
+        ref = np.floor(np.clip(curve, 0, 1) ** (1 / 2.2) * 255 + 0.5)
+        assert np.all(np.abs(out[0, :, 0].astype(np.int64) - ref) <= 1), op
+        assert np.all(out[..., 3] == 255) and np.all(np.diff(out[0, :, 1].astype(int)) >= 0)     # monotone curves
+    assert abs(hable(2 * 11.2 / 2) / hable(11.2) - 1.0) < 1e-12      # the white point maps to 1
+    assert np.array_equal(oracle.tonemap(hdr, None, pc), oracle.tonemap(hdr, None, pc, oracle.TONEMAP_ACES))
+
+
 # ------------------------------------------------------------------ committed regression vectors
 def test_golden_vectors(oracle):
     """The committed vectors are outputs of the reference's own GLSL (oracle/_ref, tests/golden/make_golden.py)."""

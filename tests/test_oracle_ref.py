@@ -164,6 +164,19 @@ def test_cull_levels_and_camera_inside_the_grid(oracle, hiz_levels):
     assert cnt == rcnt and np.array_equal(vis, rvis) and same(dout, rdout)
 
 
+def test_cull_hiz_levels_above_the_pyramid_clamps_like_the_sampler(oracle):
+    """The reference pushes hizLevels = 10 whatever the extent (occlusion_culling.rs:21,262); textureLod clamps."""
+    W, H = 200, 120                                  # 8 levels
+    cam = synth.Camera((0.0, 2.0, 22.0), (0, 0, 0), W, H)
+    objs, draws = synth.make_objects((7, 7, 7), seed=6, jitter=0.3)
+    depth = synth.splat_depth(objs, cam)
+    for levels in (10, 12, 99):
+        pc = cam.cull_pc(len(objs), levels)
+        vis, dout, cnt = oracle.occlusion_cull(objs, draws, pc, depth)
+        rvis, rdout, rcnt = ref.occlusion_cull(objs, draws, pc, depth)
+        assert cnt == rcnt and np.array_equal(vis, rvis) and same(dout, rdout)
+
+
 def test_cull_non_finite_and_degenerate_objects(oracle):
     W, H = 320, 180
     cam = synth.Camera((0.0, 2.0, 22.0), (0, 0, 0), W, H)

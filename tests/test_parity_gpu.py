@@ -453,6 +453,30 @@ def test_tonemap_within_one_lsb(backend, oracle, W, H):
         assert np.all(c.ldr8()[..., 3] == 255)
 
 
+@pytest.mark.parametrize("op", [T.TONEMAP_ACES, T.TONEMAP_REINHARD, T.TONEMAP_UNCHARTED2, T.TONEMAP_NONE])
+def test_tonemap_operators_within_one_lsb(backend, oracle, op):
+    """TonemappingConfig.operator (features/tonemapping.rs:9-20, row f-4): staged call and whole view, <= 1 LSB."""
+    W, H = 320, 180
+    hdr = synth.random_hdr(W, H, seed=15)
+    pc = _post_pc(exposure=1.3)
+    U, _ = oracle.bloom_chain(hdr, 0.8, 5)
+    with _ctx(backend, W, H) as c:
+        c.set_tonemap_operator(op)
+        c.set_color(hdr, None)
+        c.tonemap(pc)
+        d = np.abs(c.ldr8().astype(np.int16) - oracle.tonemap(hdr, None, pc, op).astype(np.int16))
+        assert d.max() <= 1 and (d > 0).mean() < 0.01
+        cam = synth.Camera((0.0, 2.0, 22.0), (0, 0, 0), W, H)
+        vp = _view_params(cam, 0, 0, 1, W, H, _taa_pc(W, H), stages=T.STAGE_BLOOM | T.STAGE_TONEMAP)
+        vp["post"] = pc
+        for _ in range(2):                                # second call replays the captured graph
+            c.view_run(vp)
+            d = np.abs(c.ldr8().astype(np.int16) - oracle.tonemap(hdr, U[0], pc, op).astype(np.int16))
+            assert d.max() <= 1 and (d > 0).mean() < 0.01
+        with pytest.raises(backend.AshError):
+            c.set_tonemap_operator(7)
+
+
 # ------------------------------------------------------------------ whole view
 def _view_params(cam, n_objs, n_lights, hiz_levels, W, H, taa_pc, stages=T.STAGE_ALL, view_id=7):
     vp = np.zeros(1, T.VIEW_PARAMS)
@@ -902,6 +926,154 @@ def test_post_chain_edge_sizes_bit_exact():
     assert mod.run(verbose=False) == 0
 
 
+# ------------------------------------------------------------------ BASELINE configs at their full sizes
+def test_config3_view_run_at_4k_matches_oracle(backend, oracle):
+    """BASELINE config 3 as written: 3840x2160, 10 000 instances (25x20x20 grid), 4096 lights, full 12-level pyramid,
+    occlusion cull + light cull, plus the post chain of the same view (two frames).  Everything against the oracle."""
+    from ash_renderer_b200.host import TemporalAA
+    W, H = 3840, 2160
+    cam = synth.Camera((0.0, 6.0, 70.0), (0, 0, 0), W, H, far=300.0)
+    objs, draws = synth.make_objects((25, 20, 20), seed=3, jitter=0.0, disabled_frac=0.02)
+    depth = synth.splat_depth(objs, cam)
+    lights = synth.make_lights(4096, extent=30.0, rmin=1.0, rmax=6.0, seed=3)
+    seq = synth.HdrSequence(W, H, seed=4, n_discs=200)
+    taa = TemporalAA()
+    frames, pcs = [], []
+    for _ in range(2):
+        taa.begin_frame()
+        j = taa.current_jitter()
+        frames.append(seq.frame(float(j[0]), float(j[1])))
+        pcs.append(taa.push_constants(W, H))
+    vis, dout, cnt, td, true_counts, taa_ref, bloom_ref, ldr_ref = _oracle_view(oracle, cam, objs, draws, lights, depth, frames, pcs, 12)
+    assert 0 < cnt < len(objs) and int(td[:, 0].sum()) > 10000
+    with _ctx(backend, W, H, hiz_levels=12) as c:
+        c.set_objects(objs, draws)
+        c.upload_lights(lights)
+        c.set_depth(depth)
+        for f, pc in zip(frames, pcs):
+            c.set_color(f, None)
+            c.view_run(_view_params(cam, len(objs), len(lights), 12, W, H, pc, stages=T.STAGE_ALL | T.STAGE_KEEP_BLOOM))
+        assert np.array_equal(c.visibility(), vis) and c.visible_count() == cnt and np.array_equal(c.draws_out(cnt), dout)
+        _compare_tile_lists(c.tile_data(), td)
+        mips, _ = oracle.hiz_build(depth)
+        for l in (1, 5, 11):
+            assert np.array_equal(c.hiz_mip(l), mips[l - 1])
+        _assert_half_images_equal(c.taa_out(), taa_ref, "taa")
+        _assert_half_images_equal(c.bloom_mip(0), bloom_ref, "bloom U_0")
+        assert np.abs(c.ldr8().astype(np.int16) - ldr_ref.astype(np.int16)).max() <= 1
+
+
+def test_config5_cull_100k_objects_at_4k(backend, oracle):
+    """BASELINE config 5's cull: 100 000 instances against the full pyramid of a 3840x2160 depth buffer."""
+    W, H = 3840, 2160
+    cam = synth.Camera((20.0, 25.0, 48.0), (2.0, -1.0, 3.0), W, H, near=0.5, far=200.0)
+    objs, draws = synth.make_objects((50, 50, 40), spacing=2.0, seed=5, jitter=0.4)
+    depth = synth.splat_depth(objs[::8], cam, shrink=0.7)
+    pc = cam.cull_pc(len(objs), 12)
+    vis, dout, cnt = oracle.occlusion_cull(objs, draws, pc, depth)
+    assert 1000 < cnt < len(objs) - 1000
+    with _ctx(backend, W, H, hiz_levels=12, enable_post=0) as c:
+        c.set_depth(depth)
+        c.set_objects(objs, draws)
+        c.occlusion_cull(pc)
+        assert np.array_equal(c.visibility(), vis) and c.visible_count() == cnt and np.array_equal(c.draws_out(cnt), dout)
+
+
+@pytest.mark.parametrize("precision", [T.PRECISION_EXACT, T.PRECISION_FAST])
+def test_config4_64_frame_sequence_at_4k(backend, oracle, precision):
+    """BASELINE config 4 as written: the 4K post chain over a 64-frame jittered sequence.  The frame
+    generator applies the Halton sub-pixel shift analytically; the library carries the TAA recurrence through all 64
+    frames.  Frames 0, 1, 15, 16 and 63 are checked against the oracle evaluated on the library's own history of that
+    frame (so the oracle runs 5 frames, not 64), then bloom U_0 and the 8-bit image of frame 63.
+    exact mode: bit-exact images, LDR8 <= 1 LSB; fast mode: every texel within 1 fp16 ulp, LDR8 <= 1 LSB."""
+    from ash_renderer_b200.host import TemporalAA
+    from tests.test_precision_fast_gpu import assert_within_ulps
+    W, H = 3840, 2160
+    seq = synth.HdrSequence(W, H, seed=4, n_discs=200)
+    taa = TemporalAA()
+    cam = synth.Camera((0.0, 2.0, 22.0), (0, 0, 0), W, H)
+    check = {0, 1, 15, 16, 63}
+    base = seq.frame(0.0, 0.0)
+    with _ctx(backend, W, H, precision=precision) as c:
+        prev = None
+        for t in range(64):
+            taa.begin_frame()
+            j = taa.current_jitter()
+            # full re-render only for the checked frames and their predecessors' inputs; the others reuse a cheap
+            # integer-shifted copy of the base frame (their resolves are inputs of the recurrence, not checked themselves)
+            f = seq.frame(float(j[0]), float(j[1])) if (t in check or t + 1 in check) else np.roll(base, t % 3 - 1, axis=1)
+            pc = taa.push_constants(W, H)
+            c.set_color(f, None)
+            vp = _view_params(cam, 0, 0, 1, W, H, pc, stages=T.STAGE_TAA | T.STAGE_BLOOM | T.STAGE_TONEMAP | T.STAGE_KEEP_BLOOM)
+            c.view_run(vp)
+            if t in check:
+                out = c.taa_out()
+                ref = oracle.taa_resolve(f, f if prev is None else prev, None, pc)
+                if precision == T.PRECISION_EXACT:
+                    _assert_half_images_equal(out, ref, f"frame {t}")
+                else:
+                    assert_within_ulps(out, ref, 1, f"frame {t}")
+                if t == 63:
+                    U, _ = oracle.bloom_chain(out, 0.8, 5)
+                    if precision == T.PRECISION_EXACT:
+                        _assert_half_images_equal(c.bloom_mip(0), U[0], "bloom U_0 of frame 63")
+                    else:
+                        # U_0 chains the fused threshold (<= 1 ulp of threshold(resolve)) through the bloom levels:
+                        # <= 2 ulp, beyond 1 ulp on fewer than one half in a million (measured: 1 of 33 M)
+                        assert_within_ulps(c.bloom_mip(0), U[0], 2, "bloom U_0 of frame 63", frac_beyond_one=1e-6)
+                    ldr = oracle.tonemap(out, U[0], _post_pc())
+                    assert np.abs(c.ldr8().astype(np.int16) - ldr.astype(np.int16)).max() <= 1
+            prev = c.taa_out() if (t + 1 in check) else None
+
+
+# ------------------------------------------------------------------ round-1 review findings (ADVICE.md)
+def test_reference_default_hiz_levels_on_a_small_extent(backend, oracle):
+    """OcclusionCulling::push_constants always sends HIZ_LEVELS = 10 (occlusion_culling.rs:21,262); at 320x180 the
+    pyramid has 9 levels.  textureLod clamps to the last mip: accepted, and equal to the oracle."""
+    W, H = 320, 180
+    cam, objs, draws, depth = _cull_scene(W, H, (8, 8, 8), seed=3)
+    assert len(oracle.mip_extents(W, H)) == 9
+    pc = cam.cull_pc(len(objs), 10)
+    vis, dout, cnt = oracle.occlusion_cull(objs, draws, pc, depth)
+    with _ctx(backend, W, H) as c:
+        c.set_depth(depth)
+        c.set_objects(objs, draws)
+        c.occlusion_cull(pc)
+        assert np.array_equal(c.visibility(), vis) and c.visible_count() == cnt and np.array_equal(c.draws_out(cnt), dout)
+
+
+def test_draw_index_past_the_template_buffer_reads_zeros(backend, oracle):
+    """drawCommandsIn[obj.drawIndex] with drawIndex >= the buffer's size: zeros (robustBufferAccess), not a fault."""
+    W, H = 320, 180
+    cam, objs, draws, depth = _cull_scene(W, H, (6, 6, 6), seed=4, disabled=0.0)
+    objs["draw_index"][::7] = len(draws) + 5
+    objs["draw_index"][3] = 0xFFFFFFFF
+    pc = cam.cull_pc(len(objs), 9)
+    vis, dout, cnt = oracle.occlusion_cull(objs, draws, pc, depth)
+    assert cnt > 20 and (dout["index_count"] == 0).any() and (dout["index_count"] != 0).any()
+    with _ctx(backend, W, H) as c:
+        c.set_depth(depth)
+        c.set_objects(objs, draws)
+        c.occlusion_cull(pc)
+        assert np.array_equal(c.visibility(), vis) and c.visible_count() == cnt and np.array_equal(c.draws_out(cnt), dout)
+        c.sync()                                           # no sticky error: the context still works
+        c.occlusion_cull(pc)
+        assert c.visible_count() == cnt
+
+
+@pytest.mark.parametrize("W,H", [(4096, 1), (8192, 2), (1, 4096), (3000, 1)])
+def test_hiz_degenerate_aspect_ratios(backend, oracle, W, H):
+    """Levels whose height is clamped to 1 only halve: the shared-memory tail of k_pyramid_tail must hold W / 2 texels."""
+    depth = synth.random_depth(W, H, seed=W + H)
+    mips, _ = oracle.hiz_build(depth)
+    with _ctx(backend, W, H, enable_post=0) as c:
+        c.set_depth(depth)
+        c.hiz_build()
+        assert c.hiz_level_count() == len(mips) + 1
+        for l, m in enumerate(mips, start=1):
+            assert np.array_equal(c.hiz_mip(l), m), f"mip {l}"
+
+
 # ------------------------------------------------------------------ error behaviour (AshError mirror)
 def test_error_codes(backend):
     W, H = 64, 64
@@ -925,8 +1097,9 @@ def test_error_codes(backend):
             c.get(12345)
         assert e.value.code == backend.ASH_ERR_NOT_FOUND
         with pytest.raises(backend.AshError) as e:
-            c.occlusion_cull(cam.cull_pc(0, 99))          # hizLevels > levels_built
+            c.occlusion_cull(cam.cull_pc(0, 0))           # hizLevels == 0
         assert e.value.code == backend.ASH_ERR_INVALID
+        c.occlusion_cull(cam.cull_pc(0, 99))              # hizLevels > levels_built is legal: the sampler clamps
     with _ctx(backend, W, H, enable_post=0) as c:
         with pytest.raises(backend.AshError) as e:
             c.set_color(synth.random_hdr(W, H), None)

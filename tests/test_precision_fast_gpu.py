@@ -23,9 +23,11 @@ def half_ulp_distance(got, ref):
     return np.abs(mono(g) - mono(r))
 
 
-def assert_within_ulps(got, ref, ulps, what, max_frac=None):
+def assert_within_ulps(got, ref, ulps, what, max_frac=None, frac_beyond_one=None):
     d = half_ulp_distance(got, ref)
     assert d.max() <= ulps, f"{what}: max {int(d.max())} fp16 ulp ({int((d > ulps).sum())} of {d.size} halfs beyond {ulps})"
+    if frac_beyond_one is not None:
+        assert (d > 1).mean() <= frac_beyond_one, f"{what}: {int((d > 1).sum())} of {d.size} halfs beyond 1 ulp"
     if max_frac is not None:
         assert (d > 0).mean() <= max_frac, f"{what}: {(d > 0).mean():.4f} of the halfs differ"
     return float((d > 0).mean())
@@ -121,7 +123,9 @@ def test_view_run_fast_mode(backend, oracle, W, H):
         assert d.max() <= 1, f"LDR8 differs by {int(d.max())} LSB"
         # bloom of the library's own resolve, stage by stage: U_0 within 1 ulp of the oracle chain on that resolve
         Uc, _ = oracle.bloom_chain(hist_c, 0.8, 5)
-        assert_within_ulps(c.bloom_mip(0), Uc[0], 1, "bloom U_0")
+        # two chained stages (the fused threshold, within 1 ulp of threshold(resolve), feeds the exact bloom chain):
+        # 2 ulp at most, and beyond 1 ulp on fewer than one texel in a million
+        assert_within_ulps(c.bloom_mip(0), Uc[0], 2, "bloom U_0", frac_beyond_one=1e-6)
 
 
 def test_fast_threshold_is_of_the_stored_texel(backend, oracle):
