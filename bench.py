@@ -1,10 +1,12 @@
 #!/usr/bin/env python
 """bench.py — 4K views/sec of the per-frame compute path (Hi-Z + cull + light cull + TAA + bloom + tonemap).
 
-One step = one frame of each of `--views` independent camera views of the BASELINE.json config-5
+One step = one frame of each of `--views` (32) independent camera views of the BASELINE.json config-5
 scene (3840x2160, 100k instances, 8192 lights), every view with its own depth buffer, HDR colour
 buffer and TAA history.  Views shard across GPUs (weak scaling: `--views` per GPU, no data-path
-collective; one all_gather of the 32-byte per-view stats records at the end).
+collective; one all_gather of the 32-byte per-view stats records at the end).  Beside the headline:
+config 5 as written (a fixed batch of 1024 views sharded by views.shard_views: strong scaling), the
+same step sustained for seconds, and a parity check of this very workload against the CPU oracle.
 
   value  : views/s with the per-view inputs already resident in HBM (CUDA events, max over ranks)
   e2e    : views/s through the host-buffer API: pinned host depth+HDR -> H2D -> view_run -> D2H of
@@ -128,6 +130,21 @@ def algorithmic_bytes(kclass, n_objs, n_lights, st):
     return float(table[kclass])
 
 
+def compulsory_bytes(n_objs, n_lights, st):
+    """SURVEY.md 8.4, the headline definition: every INPUT of the view once and every output the API exposes once
+    (depth, all Hi-Z mips, objects, lights, visibility, compacted draws, tile lists, current + history colour, the
+    resolve = next history, LDR8) — whatever the fused pipeline stages in between costs nothing here."""
+    P, c = W * H, 8
+    mips, w, h = [], W, H
+    while max(w, h) > 1:
+        w, h = max(1, w // 2), max(1, h // 2)
+        mips.append(w * h)
+    tiles = ((W + 15) // 16) * ((H + 15) // 16)
+    V, sum_l = int(st["visible_objects"]), int(st["sum_tile_lights"])
+    return float(4 * P + 4 * sum(mips) + 112 * n_objs + 64 * n_lights + 208 + 4 * n_objs + 20 * V + 4 + 4 * (tiles + sum_l)
+                 + 3 * c * P + 4 * P)
+
+
 KERNEL_NAMES = ["depth_pyramid", "occlusion_cull", "cull_compact", "light_prepass", "light_tiles", "taa_resolve",
                 "bloom_threshold", "bloom_downsample", "bloom_upsample", "tonemap", "taa_threshold_fused",
                 "upsample_tonemap_fused", "instancing", "forward_depth", "forward_shade"]
@@ -188,25 +205,51 @@ def oracle_view(oracle, objs, draws, lights, cam, depth, hdr, hist, taa_pc):
     pc = np.zeros(1, T.POST_PC)
     pc["exposure"], pc["gamma"], pc["bloom_intensity"] = 1.0, 2.2, 0.5
     ldr = oracle.tonemap(taa, U[0], pc)
-    return cnt, int(td[:, 0].sum()), taa, ldr
+    return vis, cnt, td, taa, ldr
 
 
 def cpu_oracle_rate(objs, draws, lights, views, taa_pc, max_views, budget_s):
-    """views/s of the OpenMP oracle on up to `max_views` full 4K views (bounded by `budget_s`)."""
+    """views/s of the OpenMP oracle on up to `max_views` full 4K views (bounded by `budget_s`), and what it computed
+    (kept: the CUDA results of the same views are checked against it, `parity_check`)."""
     from oracle import oracle
     oracle.build()
     if max_views <= 0:
-        return None, oracle.num_threads(), 0
-    times = []
+        return None, oracle.num_threads(), 0, []
+    times, results = [], []
     t_all = time.perf_counter()
     for i in range(max_views):
         cam, depth, hdr = views[i % len(views)]
         t0 = time.perf_counter()
-        oracle_view(oracle, objs, draws, lights, cam, depth, hdr, hdr, taa_pc)
+        results.append(oracle_view(oracle, objs, draws, lights, cam, depth, hdr, hdr, taa_pc))
         times.append(time.perf_counter() - t0)
         if time.perf_counter() - t_all > budget_s:
             break
-    return len(times) / sum(times), oracle.num_threads(), len(times)
+    return len(times) / sum(times), oracle.num_threads(), len(times), results
+
+
+def parity_check(slots, oracle_results, fast):
+    """The benchmark workload itself against the oracle: slot i re-runs view i from a fresh TAA history (first frame:
+    history = current colour, as the oracle arm ran it) and every output is compared — visibility, visible count and tile
+    light lists bit-exact; the TAA resolve bit-exact (exact mode) or within 1 fp16 ulp (fast mode); LDR8 within 1 LSB."""
+    n = 0
+    for s, (vis, cnt, td, taa, ldr) in zip(slots, oracle_results):
+        c = s["ctx"]
+        c.taa_reset_history()
+        c.set_depth(s["d_depth"])
+        c.set_color(s["d_hdr"], None)
+        c.view_run(s["vp"])
+        got_td = c.tile_data()
+        assert np.array_equal(c.visibility(), vis) and c.visible_count() == cnt, "bench workload: visibility differs from the oracle"
+        assert np.array_equal(got_td[:, 0], td[:, 0]), "bench workload: tile light counts differ from the oracle"
+        m = np.arange(td.shape[1])[None, :] < (1 + td[:, :1])
+        assert np.array_equal(got_td[m], td[m]), "bench workload: tile light lists differ from the oracle"
+        g = c.taa_out().view(np.uint16).astype(np.int32)
+        r = taa.view(np.uint16).astype(np.int32)
+        d = np.abs(np.where(g & 0x8000, -(g & 0x7FFF), g) - np.where(r & 0x8000, -(r & 0x7FFF), r))
+        assert d.max() <= (1 if fast else 0), f"bench workload: TAA differs from the oracle by {int(d.max())} fp16 ulp"
+        assert np.abs(c.ldr8().astype(np.int16) - ldr.astype(np.int16)).max() <= 1, "bench workload: LDR8 differs by more than 1 LSB"
+        n += 1
+    return n
 
 
 def taa_pc_default():
@@ -306,6 +349,9 @@ def run_cuda(args):
                       "d_mesh": torch.from_numpy(mesh.view(np.int32)).cuda(), "d_meshes": torch.from_numpy(meshes.view(np.uint8)).cuda()}
 
     fwd_params = synth.forward_params(near=0.5, flags=T.FWD_TILE_LIGHTS) if args.forward else None
+    # `distinct` inputs are generated on the host (seconds each); every slot then gets its OWN variant of one of them,
+    # shifted horizontally by a slot-specific amount on the device, so that no two views of a GPU share an input
+    # (SURVEY 8.4 cfg-5 allows 32 distinct buffers cycled over the 1024 views; B >= 32 gives that)
     host_views = [make_view_inputs(rank * B + v, max(total_views, 1024), objs) for v in range(distinct)]
     streams = [torch.cuda.Stream() for _ in range(args.streams)]
     slots = []
@@ -327,9 +373,11 @@ def run_cuda(args):
             vparams["stages"] |= T.STAGE_FORWARD_DEPTH | T.STAGE_FORWARD_SHADE
             if args.two_phase:
                 vparams["stages"] |= T.STAGE_TWO_PHASE
-        slot = {"ctx": c, "vp": vparams,
-                "d_depth": torch.from_numpy(depth).cuda(), "d_hdr": torch.from_numpy(hdr.view(np.uint16)).cuda(),
-                "h_depth": torch.from_numpy(depth).pin_memory(), "h_hdr": torch.from_numpy(hdr.view(np.uint16)).pin_memory()}
+        shift = (v // distinct) * 211                       # 0 for the first `distinct` slots (those the oracle arm also runs)
+        d_depth = torch.roll(torch.from_numpy(depth).cuda(), shift, dims=1).contiguous()
+        d_hdr = torch.roll(torch.from_numpy(hdr.view(np.int16)).cuda(), shift, dims=1).contiguous()     # (roll has no uint16 kernel)
+        slot = {"ctx": c, "vp": vparams, "d_depth": d_depth, "d_hdr": d_hdr,
+                "h_depth": d_depth.cpu().pin_memory(), "h_hdr": d_hdr.cpu().pin_memory()}
         tiles = ((W + 15) // 16) * ((H + 15) // 16)
         slot["o_vis"] = torch.empty(n_objs, dtype=torch.int32).pin_memory()
         slot["o_off"] = torch.empty(tiles + 1, dtype=torch.int32).pin_memory()      # tile light lists in CSR form:
@@ -414,6 +462,42 @@ def run_cuda(args):
     launches_per_step = (sum(s["ctx"].kernel_launches() for s in slots) - launches0) / (args.steps + 1)
     value = total_views * args.steps / (ms * 1e-3)
 
+    # ---- sustained: the same step looped for >= 3 s (the timed region above is tens of milliseconds), own clock sample
+    sustained = None
+    if args.sustain_s > 0:
+        n_sus = max(args.steps, int(np.ceil(args.sustain_s * 1e3 / (ms / args.steps))))
+        sampler2 = ClockSampler(local)
+        if rank == 0:
+            sampler2.start()
+        ms_sus = timed(step_resident, n_sus, 0)
+        clocks_sus = sampler2.stop() if rank == 0 else None
+        sustained = {"views_per_s": total_views * n_sus / (ms_sus * 1e-3), "seconds": ms_sus * 1e-3, "steps": n_sus, "clocks": clocks_sus}
+
+    # ---- BASELINE config 5 as written: a FIXED batch of 1024 independent camera views, sharded over the GPUs by
+    #      views.shard_views (strong scaling).  Every view has its own camera; slot v's depth / colour input serves the
+    #      views v, v + B, ... of this GPU's shard (B distinct inputs per GPU).
+    from ash_renderer_b200 import views as V
+    cfg5 = None
+    if args.total_views > 0 and not args.forward:
+        mine = V.shard_views(args.total_views, world, rank)
+        rng5 = np.random.default_rng(7)
+        cams = [fibonacci_camera(v, args.total_views, rng5) for v in range(args.total_views)]   # same sequence on every rank
+        vps = []
+        for i, v in enumerate(mine):
+            vp5 = slots[i % B]["vp"].copy()
+            vp5["cull"], vp5["light"], vp5["camera"], vp5["view_id"] = cams[v].cull_pc(n_objs, HIZ_LEVELS), cams[v].light_pc(n_lights), cams[v].camera_data(), v
+            vps.append(vp5)
+
+        def run_shard():
+            for i in range(len(mine)):
+                sl = slots[i % B]
+                sl["ctx"].set_depth(sl["d_depth"])
+                sl["ctx"].set_color(sl["d_hdr"], d_vel)
+                sl["ctx"].view_run(vps[i])
+        ms5 = timed(run_shard, 1, 1)
+        cfg5 = {"total_views": args.total_views, "views_this_rank": len(mine), "sharding": "views.shard_views (block)",
+                "distinct_inputs_per_gpu": B, "scaling": "strong", "ms": ms5, "views_per_s": args.total_views / (ms5 * 1e-3)}
+
     # ---- per-kernel device time: the same steps again in the same process, serialised (one stream,
     #      no fork) so that each CUDA-event pair recorded by the library brackets exactly one kernel
     for s in slots:
@@ -497,6 +581,17 @@ def run_cuda(args):
     # ---- end-to-end through host buffers
     e2e_ms = timed(step_e2e, args.steps, 2)
     e2e_value = total_views * args.steps / (e2e_ms * 1e-3)
+    # each rank's own copy rates in that pass (its own device time; the headline uses the max over ranks)
+    e2e_local = None
+    if world > 1:
+        tl = torch.zeros(world, device="cuda", dtype=torch.float64)
+        a_, b_ = fence_start(), None
+        step_e2e()
+        b_ = fence_stop()
+        torch.cuda.synchronize()
+        tl[rank] = a_.elapsed_time(b_)
+        dist.all_reduce(tl)
+        e2e_local = [float(x) for x in tl.tolist()]
     tiles = ((W + 15) // 16) * ((H + 15) // 16)
     h2d = B * (W * H * 4 + W * H * 8 + T.VIEW_PARAMS.itemsize)   # depth + HDR + the per-view parameter block
     if args.forward:
@@ -512,7 +607,6 @@ def run_cuda(args):
     assert np.array_equal(chk["o_tl"].numpy().view(np.uint32)[off[t_probe]:off[t_probe + 1]], table[t_probe, 1:1 + table[t_probe, 0]])
 
     # ---- stats all_gather (the only inter-GPU exchange; 32 B per view)
-    from ash_renderer_b200 import views as V
     st_all = V.stats_to_words(V.all_gather_stats(np.array(stats, T.VIEW_STATS), total_views, world, rank,
                                                  device="cuda" if world > 1 else None))
     assert len(st_all) == total_views, "stats all_gather lost views"
@@ -549,8 +643,11 @@ def run_cuda(args):
 
     # ---- CPU baseline (bounded sample: up to 2 full 4K views, ~10-30 s)
     # (rank 0 at N=1 only: under torchrun the other ranks would wait at exit and OMP is pinned to 1 thread)
-    cpu_v, cpu_cores, cpu_n = cpu_oracle_rate(objs, draws, lights, host_views, taa_pc,
-                                              max_views=args.cpu_views if world == 1 else 0, budget_s=20.0)
+    cpu_v, cpu_cores, cpu_n, oracle_results = cpu_oracle_rate(objs, draws, lights, host_views, taa_pc,
+                                                              max_views=args.cpu_views if world == 1 else 0, budget_s=20.0)
+    plain = not (args.forward or args.velocity or inst_scene)
+    parity_checked = parity_check(slots, oracle_results, args.precision == "fast") if plain else 0
+    comp_bytes = compulsory_bytes(n_objs, n_lights, st_mean)
 
     out = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
@@ -565,17 +662,35 @@ def run_cuda(args):
                    "graph_replay": bool(args.graph_replay), "precision": args.precision, "single_view_latency_ms": single_view_ms,
                    "kernel_timing": f"same {args.steps} steps repeated serialised (1 stream, no fork) with CUDA events around each launch: "
                                     f"{prof_ms / args.steps:.3f} ms/step", "l2": f"inputs larger than L2: {B} views x 99.5 MB of depth+HDR per step per GPU",
+                   "sustained_views_per_s": sustained["views_per_s"] if sustained else None, "sustained": sustained,
+                   "cfg5_1024_views": cfg5,
+                   "parity_checked_views": parity_checked,
+                   "parity_check": "the CUDA results of the views the CPU arm ran (this very workload) compared with the oracle's: "
+                                   "visibility, visible count, tile light lists bit-exact; TAA "
+                                   + ("within 1 fp16 ulp" if args.precision == "fast" else "bit-exact") + "; LDR8 within 1 LSB",
                    "visible_fraction_mean": st_mean["visible_objects"] / n_objs,
                    "candidate_lights_mean": st_mean["candidate_lights"],
                    "lights_per_tile_mean": st_mean["sum_tile_lights"] / tiles, "lights_per_tile_max": int(st_all[:, 5].max())},
         "clocks": clocks,
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
-                "ms_per_step": e2e_ms / args.steps},
+                "ms_per_step": e2e_ms / args.steps,
+                "h2d_gbs_per_gpu": h2d / (e2e_ms / args.steps * 1e-3) / 1e9, "d2h_gbs_per_gpu": d2h / (e2e_ms / args.steps * 1e-3) / 1e9,
+                "h2d_gbs_all_gpus": world * h2d / (e2e_ms / args.steps * 1e-3) / 1e9,
+                "one_step_ms_by_rank": e2e_local},
         "gpu_launches": int(round(launches_per_step * args.steps)),
         "roofline": {"bound": "hbm", "kernel": KERNEL_NAMES[dom], "achieved": dom_k["gbs"], "peak": peak, "unit": "GB/s",
                      "frac": dom_k["gbs"] / peak, "traffic": traffic, "traffic_source": NCU_DRAM_SOURCE if traffic else None,
                      "peak_source": peak_src, "frac_of_nominal_8000_gbs": dom_k["gbs"] / 8000.0,
-                     "whole_view": {"alg_bytes_per_view_staged": view_bytes, "gbs": view_bytes / per_view_s / 1e9,
+                     "whole_view": {"staged": {"definition": "sum over the launches of one view of each kernel's algorithmic bytes "
+                                                             "(intermediates between kernels counted once written, once read)",
+                                               "bytes_per_view": view_bytes, "gbs": view_bytes / per_view_s / 1e9,
+                                               "frac": view_bytes / per_view_s / 1e9 / peak},
+                                    "compulsory": {"definition": "SURVEY 8.4 headline: the view's inputs once + the outputs the API exposes "
+                                                                 "once (depth, mips, objects, lights, visibility, draws, tile lists, current, "
+                                                                 "history, resolve, LDR8)",
+                                                   "bytes_per_view": comp_bytes, "gbs": comp_bytes / per_view_s / 1e9,
+                                                   "frac": comp_bytes / per_view_s / 1e9 / peak},
+                                    "alg_bytes_per_view_staged": view_bytes, "gbs": view_bytes / per_view_s / 1e9,
                                     "frac": view_bytes / per_view_s / 1e9 / peak,
                                     "frac_of_nominal_8000_gbs": view_bytes / per_view_s / 1e9 / 8000.0}},
         "kernels": kernels,
@@ -609,10 +724,14 @@ def main():
     os.dup2(2, 1)                      # fd 1 -> stderr for the rest of the run
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=16)      # 16 steps x 16 views = 256 views per GPU
+    ap.add_argument("--steps", type=int, default=8)       # 8 steps x 32 views = 256 views per GPU
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="cuda", choices=["cuda", "reference"])
-    ap.add_argument("--views", type=int, default=16, help="views per GPU per step")
+    ap.add_argument("--views", type=int, default=32, help="views per GPU per step (each with its own depth / colour input and TAA history)")
+    ap.add_argument("--sustain-s", type=float, default=3.0, help="also loop the resident step for at least this many seconds (0: skip)")
+    ap.add_argument("--total-views", type=int, default=1024,
+                    help="BASELINE config 5 as written: a fixed batch of this many camera views sharded over the GPUs (strong scaling), "
+                         "reported under config.cfg5_1024_views beside the weak-scaling headline (0: skip)")
     ap.add_argument("--distinct", type=int, default=4, help="distinct synthetic depth/HDR inputs generated per GPU (host setup cost)")
     ap.add_argument("--streams", type=int, default=8)
     ap.add_argument("--cpu-views", type=int, default=2)
