@@ -51,6 +51,7 @@ struct Launch {
     cudaStream_t s;
     uint64_t*    launches;
     Profiler*    prof;
+    bool         fast = false;      // AshCudaConfig.precision == ASH_PRECISION_FAST: wrappers may pick the tolerance kernels
 };
 // RAII: counts the launch and brackets it with events when its class is being profiled.
 struct Timed {
@@ -116,7 +117,7 @@ struct ashcuda_ctx {
     std::string  err;
     uint64_t     launches = 0;
     ash::Profiler prof;
-    ash::Launch  L() { return ash::Launch{stream, &launches, &prof}; }
+    ash::Launch  L() { return ash::Launch{stream, &launches, &prof, cfg.precision == ASH_PRECISION_FAST}; }
 
     // depth + pyramid
     const float* depth = nullptr;      // current mip 0 (owned copy or borrowed)
@@ -290,9 +291,9 @@ cudaError_t launch_upsample_tonemap_fast(const void* src, uint32_t sw, uint32_t 
                                          bool store_u, const Launch& L);
 // post_up_pair.cu: the same two kernels with two source texels per thread on the packed fp32 pipe
 bool upsample_pair_applies(uint32_t sw, uint32_t sh);
-cudaError_t launch_upsample_pair(const void* src, uint32_t sw, uint32_t sh, void* dst, float intensity, cudaStream_t s);
+cudaError_t launch_upsample_pair(const void* src, uint32_t sw, uint32_t sh, void* dst, float intensity, bool tol, cudaStream_t s);
 cudaError_t launch_upsample_tonemap_pair(const void* src, uint32_t sw, uint32_t sh, void* dst, float intensity, const void* hdr,
-                                         void* ldr8, const AshPostProcessPushConstants& pc, bool store_u, cudaStream_t s);
+                                         void* ldr8, const AshPostProcessPushConstants& pc, bool store_u, bool tol, cudaStream_t s);
 cudaError_t launch_tonemap_fast(const void* hdr, const void* bloom_or_null, void* ldr8, uint32_t W, uint32_t H,
                                 const AshPostProcessPushConstants& pc, const Launch& L);
 // ---- exact-tap validation (exact_taps.cu), host side, O(n) per axis

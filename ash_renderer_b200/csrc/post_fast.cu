@@ -425,7 +425,7 @@ cudaError_t launch_bloom_upsample_fast(const void* src, uint32_t sw, uint32_t sh
                                        const Launch& L) {
     const dim3 grid((sw + 15) / 16, (sh + 15) / 16);
     Timed timed(L, ASH_KERNEL_BLOOM_UPSAMPLE);
-    if (ASH_UPS_PAIR && upsample_pair_applies(sw, sh)) return launch_upsample_pair(src, sw, sh, dst, intensity, L.s);
+    if (ASH_UPS_PAIR && upsample_pair_applies(sw, sh)) return launch_upsample_pair(src, sw, sh, dst, intensity, L.fast, L.s);
     k_upsample_fast<false, true><<<grid, 256, 0, L.s>>>(static_cast<const uint2*>(src), (int)sw, (int)sh,
                                                         static_cast<uint2*>(dst), intensity, nullptr, nullptr,
                                                         AshPostProcessPushConstants{});
@@ -438,7 +438,7 @@ cudaError_t launch_upsample_tonemap_fast(const void* src, uint32_t sw, uint32_t 
     const dim3 grid((sw + 15) / 16, (sh + 15) / 16);
     Timed timed(L, ASH_KERNEL_UPSAMPLE_TONEMAP);
     if (ASH_UPS_PAIR && upsample_pair_applies(sw, sh))
-        return launch_upsample_tonemap_pair(src, sw, sh, dst, intensity, hdr, ldr8, pc, store_u, L.s);
+        return launch_upsample_tonemap_pair(src, sw, sh, dst, intensity, hdr, ldr8, pc, store_u, L.fast, L.s);
     if (store_u)
         k_upsample_fast<true, true><<<grid, 256, 0, L.s>>>(static_cast<const uint2*>(src), (int)sw, (int)sh, static_cast<uint2*>(dst),
                                                            intensity, static_cast<const uint2*>(hdr), static_cast<uint32_t*>(ldr8), pc);

@@ -121,6 +121,54 @@ __device__ __forceinline__ void tonemap_pack8_pair(V3P c, V3P bloom, const AshPo
     o_hi = __byte_perm(__byte_perm(__float_as_uint(hi(r)), __float_as_uint(hi(g)), 0x0040), __float_as_uint(hi(b)), 0x5410);
 }
 
+// ---- TOLERANCE mode (AshCudaConfig.precision = FAST): the nine bilinear taps of bloom_upsample.frag:21-38 are linear in
+// the source texels, so for each destination parity (py, px) the whole tent is ONE 4x4 convolution of the source window
+// with constant weights (x 256, parity (0,0); the other parities mirror rows / columns):
+//      0  1  3  0
+//      1 28 46  9        13 non-zero weights: 13 FMAs per channel instead of the 9 x (2 horizontal + 1 vertical) lerps
+//      3 46 74 17        + 8 adds of the exact mode.  Same taps, same weights (the exact-tap check of the level still
+//      0  9 17  2        gates the kernel); only the order of the fp32 roundings differs: <= 1 fp16 ulp on the result.
+// (= [h0 (x) (4 v0 + v-2 + v2) + 2 (h-1 + h1) (x) (v-1 + v1) + (h-2 + h2) (x) v0] / 16 with the 1-D tap vectors of up_c0 / up_g75.)
+__host__ __device__ constexpr int up_tol_w00(int r, int c) {
+    constexpr int W[4][4] = {{0, 1, 3, 0}, {1, 28, 46, 9}, {3, 46, 74, 17}, {0, 9, 17, 2}};
+    return W[r][c];
+}
+__host__ __device__ constexpr int up_tol_w(int py, int px, int r, int c) { return up_tol_w00(py ? 3 - r : r, px ? 3 - c : c); }
+__host__ __device__ constexpr int up_tol_slot(int w) {      // index of a weight value in the 8-entry register table
+    return w == 1 ? 0 : w == 2 ? 1 : w == 3 ? 2 : w == 9 ? 3 : w == 17 ? 4 : w == 28 ? 5 : w == 46 ? 6 : 7;
+}
+__host__ __device__ constexpr float up_tol_value(int slot) { return slot == 0 ? 1.0f : slot == 1 ? 2.0f : slot == 2 ? 3.0f : slot == 3 ? 9.0f : slot == 4 ? 17.0f : slot == 5 ? 28.0f : slot == 6 ? 46.0f : 74.0f; }
+
+// all four parities of one source texel, both lanes: up[py][px] = intensity * conv4x4(window rows py.., cols px..)
+__device__ __forceinline__ void up_tol_conv(const UpSrcP& S, int tj, int ti, const P2 (&wv)[8], V3P (&up)[2][2]) {
+    const P2 z = splat(0.0f);
+#pragma unroll
+    for (int py = 0; py < 2; ++py)
+#pragma unroll
+        for (int px = 0; px < 2; ++px) up[py][px] = {z, z, z};
+#pragma unroll
+    for (int r = 0; r < 5; ++r) {
+        V3P t[5];
+#pragma unroll
+        for (int c = 0; c < 5; ++c) t[c] = up_window_(S, tj + r, ti + c);
+#pragma unroll
+        for (int py = 0; py < 2; ++py) {
+            const int rr = r - py;
+            if (rr < 0 || rr > 3) continue;
+#pragma unroll
+            for (int px = 0; px < 2; ++px)
+#pragma unroll
+                for (int c = 0; c < 4; ++c) {
+                    const int w = up_tol_w(py, px, rr, c);
+                    if (w == 0) continue;
+                    const P2 k = wv[up_tol_slot(w)];
+                    V3P& a = up[py][px];
+                    a = {ffma(t[c + px].x, k, a.x), ffma(t[c + px].y, k, a.y), ffma(t[c + px].z, k, a.z)};
+                }
+        }
+    }
+}
+
 template <bool TONEMAP>
 struct UpTileP {
     uint2 src[20][20];                       // 16x16 source texels + 2-texel halo
@@ -131,7 +179,7 @@ struct UpTileP {
 #ifndef ASH_UPS_PAIR_MINB
 #define ASH_UPS_PAIR_MINB 4
 #endif
-template <bool TONEMAP, bool STORE_U>
+template <bool TONEMAP, bool STORE_U, bool TOL>
 __global__ void __launch_bounds__(128, ASH_UPS_PAIR_MINB)
 k_upsample_pair(const uint2* __restrict__ src, int sw, int sh, uint2* __restrict__ dst, float intensity,
                 const uint2* __restrict__ hdr, uint32_t* __restrict__ ldr8, AshPostProcessPushConstants pc,
@@ -165,6 +213,9 @@ k_upsample_pair(const uint2* __restrict__ src, int sw, int sh, uint2* __restrict
     };
 
     const P2 k2 = splat(fmul(intensity, 0.00390625f));            // (R16 / 256) * intensity == R16 * (intensity / 256)
+    P2 wv[8];                                                     // TOL: the eight distinct tent weights, x intensity / 256
+#pragma unroll
+    for (int k = 0; k < 8; ++k) wv[k] = splat(TOL ? up_tol_value(k) * 0.00390625f * intensity : 0.0f);
     const float inv_gamma = TONEMAP ? __fdividef(1.0f, pc.gamma) : 0.0f;
     // tile coordinates advance by gridDim.x tiles per round without a division in the loop
     const int step_y = (int)gridDim.x / tiles_x, step_x = (int)gridDim.x - step_y * tiles_x;
@@ -196,17 +247,21 @@ k_upsample_pair(const uint2* __restrict__ src, int sw, int sh, uint2* __restrict
         if (i < sw && j < sh) {
             const bool hi_ok = j + kUpLane < sh;                  // lane hi past the last row: computed on the clamped tile, not stored
             V3P up[2][2];    // [py][px] upsampled value of both lanes, before the additive blend
-            {
-                UpHP h;
-                up_hlerps_p<0>(S, tj, ti, h);
-                up[0][0] = scale3(up_combine_p<0>(h), k2);
-                up[1][0] = scale3(up_combine_p<1>(h), k2);
-            }
-            {
-                UpHP h;
-                up_hlerps_p<1>(S, tj, ti, h);
-                up[0][1] = scale3(up_combine_p<0>(h), k2);
-                up[1][1] = scale3(up_combine_p<1>(h), k2);
+            if (TOL) {
+                up_tol_conv(S, tj, ti, wv, up);
+            } else {
+                {
+                    UpHP h;
+                    up_hlerps_p<0>(S, tj, ti, h);
+                    up[0][0] = scale3(up_combine_p<0>(h), k2);
+                    up[1][0] = scale3(up_combine_p<1>(h), k2);
+                }
+                {
+                    UpHP h;
+                    up_hlerps_p<1>(S, tj, ti, h);
+                    up[0][1] = scale3(up_combine_p<0>(h), k2);
+                    up[1][1] = scale3(up_combine_p<1>(h), k2);
+                }
             }
 #pragma unroll
             for (int py = 0; py < 2; ++py) {
@@ -225,8 +280,10 @@ k_upsample_pair(const uint2* __restrict__ src, int sw, int sh, uint2* __restrict
                 if (TONEMAP) {
                     const uint4 cl = T[b].hdr[rl][ti], ch = T[b].hdr[rh][ti];
                     uint32_t a_lo, a_hi, b_lo, b_hi;
-                    tonemap_pack8_pair(up_unpack2_(make_uint2(cl.x, cl.y), make_uint2(ch.x, ch.y)), up_unpack2_(u0l, u0h), pc, inv_gamma, a_lo, a_hi);
-                    tonemap_pack8_pair(up_unpack2_(make_uint2(cl.z, cl.w), make_uint2(ch.z, ch.w)), up_unpack2_(u1l, u1h), pc, inv_gamma, b_lo, b_hi);
+                    // the bloom operand is U_0 as stored (fp16); TOL feeds the value before that rounding (half an fp16 ulp: far
+                    // inside the 1-LSB bar of the 8-bit result)
+                    tonemap_pack8_pair(up_unpack2_(make_uint2(cl.x, cl.y), make_uint2(ch.x, ch.y)), TOL ? u0 : up_unpack2_(u0l, u0h), pc, inv_gamma, a_lo, a_hi);
+                    tonemap_pack8_pair(up_unpack2_(make_uint2(cl.z, cl.w), make_uint2(ch.z, ch.w)), TOL ? u1 : up_unpack2_(u1l, u1h), pc, inv_gamma, b_lo, b_hi);
                     *reinterpret_cast<uint2*>(ldr8 + ol) = make_uint2(a_lo, b_lo);
                     if (hi_ok) *reinterpret_cast<uint2*>(ldr8 + oh) = make_uint2(a_hi, b_hi);
                 }
@@ -237,14 +294,14 @@ k_upsample_pair(const uint2* __restrict__ src, int sw, int sh, uint2* __restrict
     cp_async_wait<0>();
 }
 
-template <bool TONEMAP, bool STORE_U>
+template <bool TONEMAP, bool STORE_U, bool TOL>
 static cudaError_t launch_pair_(const void* src, uint32_t sw, uint32_t sh, void* dst, float intensity,
                                 const void* hdr, void* ldr8, const AshPostProcessPushConstants& pc, cudaStream_t s) {
     const int tiles_x = (int)((sw + 15) / 16), ntiles = tiles_x * (int)((sh + 15) / 16);
     // resident CTAs per SM: launch bound, capped by 2 x sizeof(UpTileP) of shared memory
     const int per_sm = TONEMAP ? (ASH_UPS_PAIR_MINB < 5 ? ASH_UPS_PAIR_MINB : 5) : ASH_UPS_PAIR_MINB;
     const int grid = min(ntiles, 148 * per_sm);
-    k_upsample_pair<TONEMAP, STORE_U><<<grid, 128, 0, s>>>(static_cast<const uint2*>(src), (int)sw, (int)sh, static_cast<uint2*>(dst),
+    k_upsample_pair<TONEMAP, STORE_U, TOL><<<grid, 128, 0, s>>>(static_cast<const uint2*>(src), (int)sw, (int)sh, static_cast<uint2*>(dst),
                                                             intensity, static_cast<const uint2*>(hdr), static_cast<uint32_t*>(ldr8),
                                                             pc, tiles_x, ntiles);
     return cudaGetLastError();
@@ -255,14 +312,17 @@ bool upsample_pair_applies(uint32_t sw, uint32_t sh) {
     return ((sw + 15) / 16) * ((sh + 15) / 16) >= 148u * ASH_UPS_PAIR_MINB * 2u;
 }
 
-cudaError_t launch_upsample_pair(const void* src, uint32_t sw, uint32_t sh, void* dst, float intensity, cudaStream_t s) {
-    return launch_pair_<false, true>(src, sw, sh, dst, intensity, nullptr, nullptr, AshPostProcessPushConstants{}, s);
+cudaError_t launch_upsample_pair(const void* src, uint32_t sw, uint32_t sh, void* dst, float intensity, bool tol, cudaStream_t s) {
+    return tol ? launch_pair_<false, true, true>(src, sw, sh, dst, intensity, nullptr, nullptr, AshPostProcessPushConstants{}, s)
+               : launch_pair_<false, true, false>(src, sw, sh, dst, intensity, nullptr, nullptr, AshPostProcessPushConstants{}, s);
 }
 
 cudaError_t launch_upsample_tonemap_pair(const void* src, uint32_t sw, uint32_t sh, void* dst, float intensity, const void* hdr,
-                                         void* ldr8, const AshPostProcessPushConstants& pc, bool store_u, cudaStream_t s) {
-    return store_u ? launch_pair_<true, true>(src, sw, sh, dst, intensity, hdr, ldr8, pc, s)
-                   : launch_pair_<true, false>(src, sw, sh, dst, intensity, hdr, ldr8, pc, s);
+                                         void* ldr8, const AshPostProcessPushConstants& pc, bool store_u, bool tol, cudaStream_t s) {
+    if (tol) return store_u ? launch_pair_<true, true, true>(src, sw, sh, dst, intensity, hdr, ldr8, pc, s)
+                            : launch_pair_<true, false, true>(src, sw, sh, dst, intensity, hdr, ldr8, pc, s);
+    return store_u ? launch_pair_<true, true, false>(src, sw, sh, dst, intensity, hdr, ldr8, pc, s)
+                   : launch_pair_<true, false, false>(src, sw, sh, dst, intensity, hdr, ldr8, pc, s);
 }
 
 }  // namespace ash

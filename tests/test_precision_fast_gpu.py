@@ -128,6 +128,22 @@ def test_view_run_fast_mode(backend, oracle, W, H):
         assert_within_ulps(c.bloom_mip(0), Uc[0], 2, "bloom U_0", frac_beyond_one=1e-6)
 
 
+@pytest.mark.parametrize("W,H", [(1920, 1080), (3840, 2160), (1984, 1096), (200, 120)])
+def test_bloom_chain_fast_mode(backend, oracle, W, H):
+    """Staged bloom in fast mode: the large upsample levels run the 4x4-convolution form of the tent (post_up_pair.cu).
+    Every level within 2 fp16 ulp of the oracle's chain, beyond 1 ulp on fewer than 1e-5 of the halfs (the levels chain)."""
+    hdr = synth.random_hdr(W, H, seed=W + 1)
+    U, D = oracle.bloom_chain(hdr, 0.8, 5)
+    with _ctx(backend, W, H, **FAST) as c:
+        c.set_color(hdr, None)
+        c.bloom(_bloom_params(0.8, 5))
+        for k in range(5, -1, -1):
+            assert_within_ulps(c.bloom_mip(k), U[k], 2, f"U_{k}", frac_beyond_one=1e-5)
+        c.tonemap(_post_pc())
+        d = np.abs(c.ldr8().astype(np.int16) - oracle.tonemap(hdr, U[0], _post_pc()).astype(np.int16))
+        assert d.max() <= 1
+
+
 def test_fast_threshold_is_of_the_stored_texel(backend, oracle):
     """The fused bloom threshold reads the resolve as stored (fp16): D_0 within 1 ulp of threshold(resolve)."""
     W, H = 640, 360
