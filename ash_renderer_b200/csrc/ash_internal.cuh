@@ -90,8 +90,9 @@ struct GraphKey {
     uint32_t stages, n_objs, n_draws, n_lights, n_inst, n_lod_meshes, object_count, hiz_levels, lod_use_visibility;
     AshLightCullingPushConstants light;
     float    taa_screen[4];
+    float    inv_projection[4][4];                          // a graph without the k_tile_planes node is only valid for this matrix
     AshBloomParams bloom; AshPostProcessPushConstants post;
-    uint32_t in_halo, tol_variant, tonemap_op, taa_cur, history_valid, taa_ran, have_color, have_depth, have_instancing, concurrent, have_pyramid;
+    uint32_t in_halo, tol_variant, tonemap_op, planes_cached, taa_cur, history_valid, taa_ran, have_color, have_depth, have_instancing, concurrent, have_pyramid;
     AshForwardParams fwd;
 };
 struct ViewGraph {
@@ -152,6 +153,8 @@ struct ashcuda_ctx {
     uint32_t* cand_idx = nullptr;
     uint32_t* cand_count = nullptr;
     uint8_t*  light_scratch = nullptr;   // tile planes + per-cell candidate lists (light_cull.cu)
+    float     planes_ip[4][4] = {};      // invProjection the tile side planes in light_scratch were built from
+    bool      planes_valid = false;
 
     // instancing / LOD (instancing.cu); allocated on the first ashcuda_set_instances
     const AshInstanceData* inst = nullptr;      AshInstanceData* inst_owned = nullptr;
@@ -231,7 +234,7 @@ cudaError_t launch_light_cull(const AshGpuLight* lights, const AshLightCullingPu
                               const AshCullingCameraData* cam_dev, const uint32_t* tile_minmax,
                               uint32_t* depth_range, LightCand* cand, uint32_t* cand_idx,
                               uint32_t* cand_count, uint8_t* scratch, uint32_t max_lights,
-                              uint32_t* tile_data, AshViewStats* stats, const Launch& L);
+                              uint32_t* tile_data, AshViewStats* stats, bool build_planes, const Launch& L);
 cudaError_t launch_store_view(const AshCullingCameraData& cam, bool with_camera, uint32_t view_id, AshCullingCameraData* camera_dev,
                               AshViewStats* stats, const Launch& L);                                  // view_graph.cu
 size_t forward_consts_bytes();                                                                       // forward.cu

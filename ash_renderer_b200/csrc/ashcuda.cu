@@ -348,8 +348,12 @@ int ashcuda_light_cull(ashcuda_ctx* c, const AshLightCullingPushConstants* pc) {
     if (pc->light_count > c->n_lights) return fail(c, ASH_ERR_INVALID, "light_cull: lightCount > uploaded lights");
     ASH_CUDA(c, cudaSetDevice(c->device));
     if (!c->have_pyramid) { int rc = ashcuda_hiz_build(c); if (rc) return rc; }
+    // getTileFrustum's four side planes (light_culling.comp:71-95) depend on invProjection and the extent only
+    const bool build_planes = !c->planes_valid || memcmp(c->planes_ip, c->camera_host.inv_projection, sizeof(c->planes_ip)) != 0;
     ASH_CUDA(c, launch_light_cull(c->lights, *pc, c->camera_dev, c->tile_minmax, c->depth_range, c->cand,
-                                  c->cand_idx, c->cand_count, c->light_scratch, c->cfg.max_lights, c->tile_data, c->stats, c->L()));
+                                  c->cand_idx, c->cand_count, c->light_scratch, c->cfg.max_lights, c->tile_data, c->stats,
+                                  build_planes, c->L()));
+    if (pc->light_count != 0u) { memcpy(c->planes_ip, c->camera_host.inv_projection, sizeof(c->planes_ip)); c->planes_valid = true; }
     return ASH_OK;
 }
 

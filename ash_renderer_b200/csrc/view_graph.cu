@@ -56,6 +56,10 @@ GraphKey make_key(const ashcuda_ctx* c, const AshCudaViewParams* vp) {
     k.bloom = vp->bloom; k.post = vp->post;
     k.in_halo = taa_in_halo(vp->taa) ? 1u : 0u;
     k.tonemap_op = c->tonemap_op;
+    if (vp->stages & ASH_STAGE_LIGHTS) {
+        k.planes_cached = (c->planes_valid && std::memcmp(c->planes_ip, vp->camera.inv_projection, sizeof(c->planes_ip)) == 0) ? 1u : 0u;
+        std::memcpy(k.inv_projection, vp->camera.inv_projection, sizeof(k.inv_projection));
+    }
     if (c->cfg.precision == ASH_PRECISION_FAST && (vp->stages & ASH_STAGE_TAA) && k.in_halo) {   // which k_taa_tol instance the graph holds
         TaaTolArgs ta;
         k.tol_variant = 1u + ash_taa_tol_plan(const_cast<ashcuda_ctx*>(c), vp->taa, vp->bloom.threshold, &ta).regular;
@@ -144,7 +148,7 @@ void drop(ViewGraph& g) {
 
 struct StateSnap {
     int taa_cur; bool history_valid, taa_ran, bloom_valid, have_pyramid, have_camera; uint64_t launches; AshCullingCameraData camera_host;
-    float taa_chk[4]; bool taa_exact;
+    float taa_chk[4]; bool taa_exact; float planes_ip[4][4]; bool planes_valid;
     bool have_depth, have_color, have_forward; const float* depth; const void* color; const void* velocity;
 };
 StateSnap snap(const ashcuda_ctx* c) {
@@ -154,6 +158,7 @@ StateSnap snap(const ashcuda_ctx* c) {
     std::memcpy(s.taa_chk, c->taa_chk, sizeof(s.taa_chk));
     s.have_depth = c->have_depth; s.have_color = c->have_color; s.have_forward = c->have_forward;
     s.depth = c->depth; s.color = c->color; s.velocity = c->velocity;
+    std::memcpy(s.planes_ip, c->planes_ip, sizeof(s.planes_ip)); s.planes_valid = c->planes_valid;
     return s;
 }
 void restore(ashcuda_ctx* c, const StateSnap& s) {
@@ -162,6 +167,7 @@ void restore(ashcuda_ctx* c, const StateSnap& s) {
     std::memcpy(c->taa_chk, s.taa_chk, sizeof(s.taa_chk)); c->taa_exact = s.taa_exact;
     c->have_depth = s.have_depth; c->have_color = s.have_color; c->have_forward = s.have_forward;
     c->depth = s.depth; c->pyr.mip0 = c->depth; c->color = s.color; c->velocity = s.velocity;
+    std::memcpy(c->planes_ip, s.planes_ip, sizeof(c->planes_ip)); c->planes_valid = s.planes_valid;
 }
 
 }  // namespace
@@ -252,6 +258,9 @@ int ash_view_run_graph(ashcuda_ctx* c, const AshCudaViewParams* vp, bool* handle
     if (P.has_lod) ASH_CUDA(c, patch_node(g, g.n_lod, P.lod.n_args, P.lod.arg_index, P.lod.value));
     if (P.has_fwd) ASH_CUDA(c, patch_node(g, g.n_fwd, P.fwd.n_args, P.fwd.arg_index, P.fwd.value));
     ASH_CUDA(c, cudaGraphLaunch(g.exec, c->stream));
+    if ((st & ASH_STAGE_LIGHTS) && vp->light.light_count != 0u) {      // the tile side planes now match this invProjection
+        std::memcpy(c->planes_ip, vp->camera.inv_projection, sizeof(c->planes_ip)); c->planes_valid = true;
+    }
     if (g.taa_flip) c->taa_cur ^= 1;
     c->history_valid = g.history_valid; c->taa_ran = g.taa_ran; c->bloom_valid = g.bloom_valid;
     c->have_pyramid = g.have_pyramid; c->have_camera = g.have_camera;
