@@ -260,7 +260,7 @@ cudaError_t launch_instancing(const AshInstanceData* inst, const uint32_t* batch
                               uint32_t* offsets, uint32_t* totals, AshInstanceData* out, AshIndirectDrawCommand* draws,
                               AshInstancingStats* stats, const Launch& L);
 size_t light_cull_scratch_bytes(uint32_t W, uint32_t H, uint32_t max_lights, size_t* planes_off, size_t* list_off,
-                                size_t* count_off);
+                                size_t* count_off, size_t* cell_planes_off = nullptr);
 // `center`: the exact-tap checks passed, so centre / +-1 texel taps may be fetched directly
 cudaError_t launch_taa(const void* cur, const void* hist, const void* vel, void* out,
                        const AshTaaPushConstants& pc, bool center, const Launch& L);

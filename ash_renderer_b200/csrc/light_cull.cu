@@ -198,12 +198,14 @@ __device__ __forceinline__ V3 plane_n(const TilePlanes& p, int f) {
 }
 __device__ __forceinline__ float pdot(V3 a, V3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
 
+// What pass 3 needs from the tile side planes alone — per family the two end normals a, b, s_min, E and whether the
+// family may reject at all — depends on invProjection and the extent only, like the planes themselves: computed once
+// per projection (k_cell_planes, cached with k_tile_planes' output) instead of once per view (it was 2/3 of k_light_cells).
+struct CellPlanes { float fa[4][3], fb[4][3], smin[4], emax[4]; uint32_t fvalid, pad[3]; };
+
 __global__ void __launch_bounds__(kCellWarps * 32)
-k_light_cells(uint32_t tiles_x, uint32_t tiles_y, uint32_t cells_x, uint32_t cells,
-              const TilePlanes* __restrict__ planes, const uint32_t* __restrict__ tile_minmax,
-              const LightCand* __restrict__ cand, const uint32_t* __restrict__ cand_idx,
-              const uint32_t* __restrict__ cand_count, uint32_t* __restrict__ cell_list, uint32_t cell_stride,
-              uint32_t* __restrict__ cell_count) {
+k_cell_planes(uint32_t tiles_x, uint32_t tiles_y, uint32_t cells_x, uint32_t cells,
+              const TilePlanes* __restrict__ planes, CellPlanes* __restrict__ out) {
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const uint32_t cell = blockIdx.x * kCellWarps + warp;
     if (cell >= cells) return;
@@ -216,7 +218,6 @@ k_light_cells(uint32_t tiles_x, uint32_t tiles_y, uint32_t cells_x, uint32_t cel
     V3 fa[4], fb[4];
     float smin[4], emax[4];
     bool bad[4];
-    uint32_t mn = 0xFFFFFFFFu, mx = 0u, worst = 0u;
 #pragma unroll
     for (int f = 0; f < 4; ++f) {
         fa[f] = plane_n(p00, f);
@@ -226,10 +227,7 @@ k_light_cells(uint32_t tiles_x, uint32_t tiles_y, uint32_t cells_x, uint32_t cel
     for (uint32_t t = lane; t < (uint32_t)(kCellTiles * kCellTiles); t += 32) {
         const uint32_t tx = tx0 + (t % kCellTiles), ty = ty0 + (t / kCellTiles);
         if (tx > tx1 || ty > ty1) continue;
-        const size_t tile = (size_t)ty * tiles_x + tx;
-        const uint2 mm = __ldg(reinterpret_cast<const uint2*>(tile_minmax) + tile);
-        mn = min(mn, mm.x); mx = max(mx, mm.y); worst = max(worst, max(mm.x, mm.y));
-        const TilePlanes p = planes[tile];
+        const TilePlanes p = planes[(size_t)ty * tiles_x + tx];
 #pragma unroll
         for (int f = 0; f < 4; ++f) {
             const V3 n = plane_n(p, f), a = fa[f], b = fb[f];
@@ -248,21 +246,64 @@ k_light_cells(uint32_t tiles_x, uint32_t tiles_y, uint32_t cells_x, uint32_t cel
         }
     }
 #pragma unroll
-    for (int s = 16; s > 0; s >>= 1) {
-        mn = min(mn, __shfl_xor_sync(0xFFFFFFFFu, mn, s));
-        mx = max(mx, __shfl_xor_sync(0xFFFFFFFFu, mx, s));
-        worst = max(worst, __shfl_xor_sync(0xFFFFFFFFu, worst, s));
+    for (int s = 16; s > 0; s >>= 1)
 #pragma unroll
         for (int f = 0; f < 4; ++f) {
             smin[f] = fminf(smin[f], __shfl_xor_sync(0xFFFFFFFFu, smin[f], s));
             emax[f] = fmaxf(emax[f], __shfl_xor_sync(0xFFFFFFFFu, emax[f], s));
         }
+    uint32_t valid = 0;
+#pragma unroll
+    for (int f = 0; f < 4; ++f)
+        if (!__any_sync(0xFFFFFFFFu, bad[f]) && smin[f] > 0.0f) valid |= 1u << f;
+    if (lane == 0) {
+        CellPlanes c;
+#pragma unroll
+        for (int f = 0; f < 4; ++f) {
+            c.fa[f][0] = fa[f].x; c.fa[f][1] = fa[f].y; c.fa[f][2] = fa[f].z;
+            c.fb[f][0] = fb[f].x; c.fb[f][1] = fb[f].y; c.fb[f][2] = fb[f].z;
+            c.smin[f] = smin[f];
+            c.emax[f] = emax[f] + 4e-6f;      // rounding of e itself and of the shader's own dot product
+        }
+        c.fvalid = valid; c.pad[0] = c.pad[1] = c.pad[2] = 0u;
+        out[cell] = c;
     }
+}
+
+__global__ void __launch_bounds__(kCellWarps * 32)
+k_light_cells(uint32_t tiles_x, uint32_t tiles_y, uint32_t cells_x, uint32_t cells,
+              const CellPlanes* __restrict__ cell_planes, const uint32_t* __restrict__ tile_minmax,
+              const LightCand* __restrict__ cand, const uint32_t* __restrict__ cand_idx,
+              const uint32_t* __restrict__ cand_count, uint32_t* __restrict__ cell_list, uint32_t cell_stride,
+              uint32_t* __restrict__ cell_count) {
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t cell = blockIdx.x * kCellWarps + warp;
+    if (cell >= cells) return;
+    const uint32_t cx = cell % cells_x, cy = cell / cells_x;
+    const uint32_t tx0 = cx * kCellTiles, ty0 = cy * kCellTiles;
+    const uint32_t tx1 = min(tx0 + kCellTiles - 1, tiles_x - 1), ty1 = min(ty0 + kCellTiles - 1, tiles_y - 1);
+    const CellPlanes cp = cell_planes[cell];
+    V3 fa[4], fb[4];
+    float smin[4], emax[4];
     bool fvalid[4];
 #pragma unroll
     for (int f = 0; f < 4; ++f) {
-        fvalid[f] = !__any_sync(0xFFFFFFFFu, bad[f]) && smin[f] > 0.0f;
-        emax[f] += 4e-6f;      // rounding of e itself and of the shader's own dot product
+        fa[f] = {cp.fa[f][0], cp.fa[f][1], cp.fa[f][2]};
+        fb[f] = {cp.fb[f][0], cp.fb[f][1], cp.fb[f][2]};
+        smin[f] = cp.smin[f]; emax[f] = cp.emax[f]; fvalid[f] = (cp.fvalid >> f) & 1u;
+    }
+    uint32_t mn = 0xFFFFFFFFu, mx = 0u, worst = 0u;
+    for (uint32_t t = lane; t < (uint32_t)(kCellTiles * kCellTiles); t += 32) {
+        const uint32_t tx = tx0 + (t % kCellTiles), ty = ty0 + (t / kCellTiles);
+        if (tx > tx1 || ty > ty1) continue;
+        const uint2 mm = __ldg(reinterpret_cast<const uint2*>(tile_minmax) + (size_t)ty * tiles_x + tx);
+        mn = min(mn, mm.x); mx = max(mx, mm.y); worst = max(worst, max(mm.x, mm.y));
+    }
+#pragma unroll
+    for (int s = 16; s > 0; s >>= 1) {
+        mn = min(mn, __shfl_xor_sync(0xFFFFFFFFu, mn, s));
+        mx = max(mx, __shfl_xor_sync(0xFFFFFFFFu, mx, s));
+        worst = max(worst, __shfl_xor_sync(0xFFFFFFFFu, worst, s));
     }
     // uint order == float order only when every tile bound is a non-negative non-NaN float
     const bool zsane = worst <= 0x7F800000u && mn <= mx;
@@ -366,8 +407,10 @@ k_light_tiles(uint32_t tiles_x, uint32_t tiles, uint32_t cells_x, uint32_t light
     }
 }
 
+static size_t g_cell_planes_off_dummy;
 size_t light_cull_scratch_bytes(uint32_t W, uint32_t H, uint32_t max_lights, size_t* planes_off, size_t* list_off,
-                                size_t* count_off) {
+                                size_t* count_off, size_t* cell_planes_off) {
+    if (!cell_planes_off) cell_planes_off = &g_cell_planes_off_dummy;
     const uint32_t tiles_x = (W + 15u) / 16u, tiles_y = (H + 15u) / 16u;
     const uint32_t cells = ((tiles_x + kCellTiles - 1) / kCellTiles) * ((tiles_y + kCellTiles - 1) / kCellTiles);
     auto up = [](size_t v) { return (v + 255) & ~size_t(255); };
@@ -375,6 +418,7 @@ size_t light_cull_scratch_bytes(uint32_t W, uint32_t H, uint32_t max_lights, siz
     *planes_off = off; off = up(off + (size_t)tiles_x * tiles_y * sizeof(TilePlanes));
     *list_off = off;   off = up(off + (size_t)cells * max_lights * sizeof(uint32_t));
     *count_off = off;  off = up(off + (size_t)cells * sizeof(uint32_t));
+    *cell_planes_off = off; off = up(off + (size_t)cells * sizeof(CellPlanes));
     return off;
 }
 
@@ -387,8 +431,9 @@ cudaError_t launch_light_cull(const AshGpuLight* lights, const AshLightCullingPu
     const uint32_t tiles_x = (W + 15u) / 16u, tiles_y = (H + 15u) / 16u, tiles = tiles_x * tiles_y;
     const uint32_t cells_x = (tiles_x + kCellTiles - 1) / kCellTiles, cells_y = (tiles_y + kCellTiles - 1) / kCellTiles;
     const uint32_t cells = cells_x * cells_y;
-    size_t po, lo, co;
-    light_cull_scratch_bytes(W, H, max_lights, &po, &lo, &co);
+    size_t po, lo, co, cpo;
+    light_cull_scratch_bytes(W, H, max_lights, &po, &lo, &co, &cpo);
+    CellPlanes* cell_planes = reinterpret_cast<CellPlanes*>(scratch + cpo);
     TilePlanes* planes = reinterpret_cast<TilePlanes*>(scratch + po);
     uint32_t* cell_list = reinterpret_cast<uint32_t*>(scratch + lo);
     uint32_t* cell_count = reinterpret_cast<uint32_t*>(scratch + co);
@@ -402,10 +447,12 @@ cudaError_t launch_light_cull(const AshGpuLight* lights, const AshLightCullingPu
             if (build_planes) {          // the side planes depend on invProjection and the extent only: kept across views
                 k_tile_planes<<<(tiles + 127) / 128, 128, 0, L.s>>>(cam_dev, W, H, tiles_x, tiles, planes);
                 if ((e = cudaGetLastError()) != cudaSuccess) return e;
-                *L.launches += 1;
+                k_cell_planes<<<(cells + kCellWarps - 1) / kCellWarps, kCellWarps * 32, 0, L.s>>>(tiles_x, tiles_y, cells_x, cells, planes, cell_planes);
+                if ((e = cudaGetLastError()) != cudaSuccess) return e;
+                *L.launches += 2;
             }
             k_light_cells<<<(cells + kCellWarps - 1) / kCellWarps, kCellWarps * 32, 0, L.s>>>(
-                tiles_x, tiles_y, cells_x, cells, planes, tile_minmax, cand, cand_idx, cand_count, cell_list,
+                tiles_x, tiles_y, cells_x, cells, cell_planes, tile_minmax, cand, cand_idx, cand_count, cell_list,
                 max_lights, cell_count);
             if ((e = cudaGetLastError()) != cudaSuccess) return e;
             *L.launches += 1;                        // tile planes + cells ride in the prepass class
