@@ -67,6 +67,11 @@ struct Timed {
     ~Timed() { if (b) cudaEventRecord(b, L.s); }
 };
 
+// bloom level launches are accounted per size class (ASH_KERNEL_BLOOM_TAIL: destination below 2^20 texels)
+inline int bloom_class(int full_size_class, uint32_t dw, uint32_t dh) {
+    return (uint64_t)dw * dh < (1u << 20) ? ASH_KERNEL_BLOOM_TAIL : full_size_class;
+}
+
 // One by-value kernel argument that changes from view to view: which kernel, which argument, its new value.
 // CUDA-graph replay (view_graph.cu) patches exactly these nodes before each launch.
 struct PatchArg {

@@ -134,7 +134,7 @@ cudaError_t launch_bloom_downsample(const void* src, uint32_t sw, uint32_t sh, v
                                     uint32_t dh, const Launch& L) {
     const Tex16 t{static_cast<const uint2*>(src), (int)sw, (int)sh};
     const dim3 grid((dw + 31) / 32, (dh + 7) / 8);
-    Timed timed(L, ASH_KERNEL_BLOOM_DOWNSAMPLE);
+    Timed timed(L, bloom_class(ASH_KERNEL_BLOOM_DOWNSAMPLE, dw, dh));
     k_bloom_downsample<<<grid, 256, 0, L.s>>>(t, static_cast<uint2*>(dst), (int)dw, (int)dh);
     return cudaGetLastError();
 }
@@ -168,7 +168,7 @@ cudaError_t launch_bloom_upsample_add(const void* src, uint32_t sw, uint32_t sh,
                                       uint32_t dh, float intensity, const Launch& L) {
     const Tex16 t{static_cast<const uint2*>(src), (int)sw, (int)sh};
     const dim3 grid((dw + 31) / 32, (dh + 7) / 8);
-    Timed timed(L, ASH_KERNEL_BLOOM_UPSAMPLE);
+    Timed timed(L, bloom_class(ASH_KERNEL_BLOOM_UPSAMPLE, dw, dh));
     k_bloom_upsample_add<<<grid, 256, 0, L.s>>>(t, static_cast<uint2*>(dst), (int)dw, (int)dh, intensity);
     return cudaGetLastError();
 }

@@ -35,7 +35,15 @@ struct BoxTile {                              // component k of a box record: 0.
 struct BoxRec { P2 x, y, z, w; };
 
 // weighted record of one box from its 4x sum: luma, 1 / (1 + luma), colour x weight   (:87-101)
+// TOL (AshCudaConfig.precision = FAST): the dot product as an FMA chain, the reciprocal as MUFU.RCP (1 ulp of fp32)
+__device__ __forceinline__ float box_rcp_(float x) { float r; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+template <bool TOL>
 __device__ __forceinline__ BoxRec box_record_(V3P t4) {
+    if (TOL) {
+        const P2 d = ffma(t4.x, splat(0.25f * 0.2126f), ffma(t4.y, splat(0.25f * 0.7152f), ffma(t4.z, splat(0.25f * 0.0722f), splat(1.0f))));
+        const P2 w = pk(box_rcp_(lo(d)), box_rcp_(hi(d)));
+        return {fmul(t4.x, w), fmul(t4.y, w), fmul(t4.z, w), w};
+    }
     const P2 luma4 = fadd(fadd(fmul(t4.x, 0.2126f), fmul(t4.y, 0.7152f)), fmul(t4.z, 0.0722f));
     const P2 w = frcp_safe(ffma(luma4, splat(0.25f), splat(1.0f)));        // luma in [0, 65504]: safe domain
     return {fmul(t4.x, w), fmul(t4.y, w), fmul(t4.z, w), w};
@@ -52,6 +60,7 @@ __device__ __forceinline__ BoxRec box_load_(const BoxTile& B, bool odd, int r, i
 #ifndef ASH_DOWN_BOX_MINB
 #define ASH_DOWN_BOX_MINB 4
 #endif
+template <bool TOL>
 __global__ void __launch_bounds__(kBoxThreads, ASH_DOWN_BOX_MINB * 256 / kBoxThreads)
 k_downsample_box(const uint2* __restrict__ src, int sw, int sh, uint2* __restrict__ dst, int dw, int dh) {
     __shared__ __align__(16) BoxTile B;
@@ -100,13 +109,13 @@ k_downsample_box(const uint2* __restrict__ src, int sw, int sh, uint2* __restric
         for (int bj = 0; bj < 2; ++bj)
 #pragma unroll
             for (int bi = 0; bi < 2; ++bi) {
-                own[bj][bi] = box_record_(add3(hs[bj][bi], hs[bj + 1][bi]));
+                own[bj][bi] = box_record_<TOL>(add3(hs[bj][bi], hs[bj + 1][bi]));
                 box_store_(B, bi == 1, 2 * ty + bj, tx, own[bj][bi]);
             }
         if (extra) {
             const V3P h0 = add3(box_unpack2_(xa[0][0], xb[0][0]), box_unpack2_(xa[0][1], xb[0][1]));
             const V3P h1 = add3(box_unpack2_(xa[1][0], xb[1][0]), box_unpack2_(xa[1][1], xb[1][1]));
-            box_store_(B, (ec & 1) != 0, er, ec >> 1, box_record_(add3(h0, h1)));
+            box_store_(B, (ec & 1) != 0, er, ec >> 1, box_record_<TOL>(add3(h0, h1)));
         }
     }
     __syncthreads();
@@ -125,7 +134,13 @@ k_downsample_box(const uint2* __restrict__ src, int sw, int sh, uint2* __restric
     tap(0, 0, 0.0625f); tap(2, 0, 0.0625f); tap(0, 2, 0.0625f); tap(2, 2, 0.0625f);   // a b c d   :25-28
     tap(0, 1, 0.125f);  tap(2, 1, 0.125f);  tap(1, 0, 0.125f);  tap(1, 2, 0.125f);    // e f g h   :31-34
     // sum in [1.5e-5, 1], res in [0, 65504]: safe domain                                          :107
-    const V3P o = {fdiv_safe(res.x, sum), fdiv_safe(res.y, sum), fdiv_safe(res.z, sum)};
+    V3P o;
+    if (TOL) {
+        const P2 r = pk(box_rcp_(lo(sum)), box_rcp_(hi(sum)));
+        o = {fmul(res.x, r), fmul(res.y, r), fmul(res.z, r)};
+    } else {
+        o = {fdiv_safe(res.x, sum), fdiv_safe(res.y, sum), fdiv_safe(res.z, sum)};
+    }
     dst[(size_t)Y * dw + XA] = pack_rgba16f(lo(o.x), lo(o.y), lo(o.z), 1.0f);
     if (XB < dw) dst[(size_t)Y * dw + XB] = pack_rgba16f(hi(o.x), hi(o.y), hi(o.z), 1.0f);
 }
@@ -138,9 +153,11 @@ k_downsample_box(const uint2* __restrict__ src, int sw, int sh, uint2* __restric
 cudaError_t launch_bloom_downsample_box(const void* src, uint32_t sw, uint32_t sh, void* dst, uint32_t dw,
                                         uint32_t dh, const Launch& L) {
     const dim3 grid((dw + 63) / 64, (dh + kBH - 1) / kBH);
-    Timed timed(L, ASH_KERNEL_BLOOM_DOWNSAMPLE);
-    k_downsample_box<<<grid, kBoxThreads, 0, L.s>>>(static_cast<const uint2*>(src), (int)sw, (int)sh,
-                                            static_cast<uint2*>(dst), (int)dw, (int)dh);
+    Timed timed(L, bloom_class(ASH_KERNEL_BLOOM_DOWNSAMPLE, dw, dh));
+    if (L.fast) k_downsample_box<true><<<grid, kBoxThreads, 0, L.s>>>(static_cast<const uint2*>(src), (int)sw, (int)sh,
+                                                                       static_cast<uint2*>(dst), (int)dw, (int)dh);
+    else k_downsample_box<false><<<grid, kBoxThreads, 0, L.s>>>(static_cast<const uint2*>(src), (int)sw, (int)sh,
+                                                                static_cast<uint2*>(dst), (int)dw, (int)dh);
     return cudaGetLastError();
 }
 

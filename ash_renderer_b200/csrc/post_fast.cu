@@ -250,7 +250,7 @@ cudaError_t launch_bloom_downsample_fast(const void* src, uint32_t sw, uint32_t 
     if (ASH_DOWN_BOX && dw >= 64u && dw % 32u == 0u) return launch_bloom_downsample_box(src, sw, sh, dst, dw, dh, L);           // every box once, post_down_box.cu
     if (ASH_DOWN_PAIR && (dw & 1u) == 0u) return launch_bloom_downsample_pair(src, sw, sh, dst, dw, dh, L);    // two pixels per thread, post_pair.cu
     const dim3 grid((dw + 31) / 32, (dh + 7) / 8);
-    Timed timed(L, ASH_KERNEL_BLOOM_DOWNSAMPLE);
+    Timed timed(L, bloom_class(ASH_KERNEL_BLOOM_DOWNSAMPLE, dw, dh));
     k_downsample_fast<<<grid, 256, 0, L.s>>>(static_cast<const uint2*>(src), (int)sw, (int)sh,
                                              static_cast<uint2*>(dst), (int)dw, (int)dh);
     return cudaGetLastError();
@@ -424,7 +424,7 @@ k_upsample_fast(const uint2* __restrict__ src, int sw, int sh, uint2* __restrict
 cudaError_t launch_bloom_upsample_fast(const void* src, uint32_t sw, uint32_t sh, void* dst, float intensity,
                                        const Launch& L) {
     const dim3 grid((sw + 15) / 16, (sh + 15) / 16);
-    Timed timed(L, ASH_KERNEL_BLOOM_UPSAMPLE);
+    Timed timed(L, bloom_class(ASH_KERNEL_BLOOM_UPSAMPLE, 2u * sw, 2u * sh));
     if (ASH_UPS_PAIR && upsample_pair_applies(sw, sh)) return launch_upsample_pair(src, sw, sh, dst, intensity, L.fast, L.s);
     k_upsample_fast<false, true><<<grid, 256, 0, L.s>>>(static_cast<const uint2*>(src), (int)sw, (int)sh,
                                                         static_cast<uint2*>(dst), intensity, nullptr, nullptr,

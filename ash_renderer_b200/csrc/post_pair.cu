@@ -342,7 +342,7 @@ k_downsample_pair(const uint2* __restrict__ src, int sw, int sh, uint2* __restri
 cudaError_t launch_bloom_downsample_pair(const void* src, uint32_t sw, uint32_t sh, void* dst, uint32_t dw,
                                          uint32_t dh, const Launch& L) {
     const dim3 grid((dw / 2 + 31) / 32, (dh + 7) / 8);
-    Timed timed(L, ASH_KERNEL_BLOOM_DOWNSAMPLE);
+    Timed timed(L, bloom_class(ASH_KERNEL_BLOOM_DOWNSAMPLE, dw, dh));
     k_downsample_pair<<<grid, 256, 0, L.s>>>(static_cast<const uint2*>(src), (int)sw, (int)sh,
                                              static_cast<uint2*>(dst), (int)dw, (int)dh);
     return cudaGetLastError();

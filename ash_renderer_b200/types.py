@@ -111,5 +111,6 @@ def BUF_BLOOM_MIP(i):
 # kernel classes (ashcuda_profile_kernels / ashcuda_kernel_time_ms)
 (KERNEL_DEPTH_PYRAMID, KERNEL_OCCLUSION_CULL, KERNEL_CULL_COMPACT, KERNEL_LIGHT_PREPASS, KERNEL_LIGHT_TILES,
  KERNEL_TAA, KERNEL_BLOOM_THRESHOLD, KERNEL_BLOOM_DOWNSAMPLE, KERNEL_BLOOM_UPSAMPLE, KERNEL_TONEMAP,
- KERNEL_TAA_THRESHOLD, KERNEL_UPSAMPLE_TONEMAP, KERNEL_INSTANCING, KERNEL_FORWARD_DEPTH, KERNEL_FORWARD_SHADE) = range(15)
-KERNEL_COUNT = 15
+ KERNEL_TAA_THRESHOLD, KERNEL_UPSAMPLE_TONEMAP, KERNEL_INSTANCING, KERNEL_FORWARD_DEPTH, KERNEL_FORWARD_SHADE,
+ KERNEL_BLOOM_TAIL) = range(16)
+KERNEL_COUNT = 16

@@ -106,6 +106,8 @@ def algorithmic_bytes(kclass, n_objs, n_lights, st):
         w, h = max(1, w // 2), max(1, h // 2)
         bl.append(w * h)
     V, cand, sum_l = int(st["visible_objects"]), int(st["candidate_lights"]), int(st["sum_tile_lights"])
+    TAIL = 1 << 20
+    mean = lambda v: float(sum(v)) / max(len(v), 1)
     table = {
         0: 4 * P + 4 * sum(mips) + 8 * tiles,                                # depth read once, mips + tile min/max written
         1: 112 * n_objs + 4 * n_objs + 4 * n_objs + n_objs // 8,             # objects, visibility, one Hi-Z texel, bit mask
@@ -114,8 +116,10 @@ def algorithmic_bytes(kclass, n_objs, n_lights, st):
         4: 8 * tiles + 20 * cand + 4 * (tiles + sum_l),
         5: 3 * c * P,
         6: 2 * c * P,
-        7: c * sum(bl[k - 1] + bl[k] for k in range(1, 6)) / 5.0,            # mean per launch (5 launches)
-        8: c * sum(bl[k + 1] + 2 * bl[k] for k in range(0, 5)) / 5.0,
+        # bloom levels by size class (ASH_KERNEL_BLOOM_TAIL: destination below 2^20 texels): mean per launch of each class
+        7: mean([c * (bl[k - 1] + bl[k]) for k in range(1, 6) if bl[k] >= TAIL]),
+        8: mean([c * (bl[k + 1] + 2 * bl[k]) for k in range(1, 5) if bl[k] >= TAIL]),
+        15: mean([c * (bl[k - 1] + bl[k]) for k in range(1, 6) if bl[k] < TAIL] + [c * (bl[k + 1] + 2 * bl[k]) for k in range(1, 5) if bl[k] < TAIL]),
         9: 2 * c * P + 4 * P,
         10: 4 * c * P,                                                       # fused TAA + threshold: cur, hist in; out, T out
         11: c * (bl[1] + 2 * P) + 4 * P,                                     # fused last upsample + tonemap
@@ -147,7 +151,7 @@ def compulsory_bytes(n_objs, n_lights, st):
 
 KERNEL_NAMES = ["depth_pyramid", "occlusion_cull", "cull_compact", "light_prepass", "light_tiles", "taa_resolve",
                 "bloom_threshold", "bloom_downsample", "bloom_upsample", "tonemap", "taa_threshold_fused",
-                "upsample_tonemap_fused", "instancing", "forward_depth", "forward_shade"]
+                "upsample_tonemap_fused", "instancing", "forward_depth", "forward_shade", "bloom_tail_small_levels"]
 
 
 # ------------------------------------------------------------------ clocks sampling (B200_PROFILING.md)

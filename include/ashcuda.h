@@ -342,7 +342,9 @@ typedef struct AshCudaViewParams {
 #define ASH_KERNEL_INSTANCING       12 /* LOD select + bucket scan + instance scatter (3 launches)  */
 #define ASH_KERNEL_FORWARD_DEPTH    13 /* setup + clear + sphere splat (small, big) + depth resolve     */
 #define ASH_KERNEL_FORWARD_SHADE    14 /* tiled-forward shading from the tile light lists              */
-#define ASH_KERNEL_COUNT           15
+#define ASH_KERNEL_BLOOM_TAIL       15 /* bloom down / up launches whose destination has < 2^20 texels (levels >= 2 at 4K): a few MB
+                                       each, bound by launch latency, not by bandwidth; kept apart from the full-size levels */
+#define ASH_KERNEL_COUNT           16
 
 typedef struct ashcuda_ctx ashcuda_ctx;
 
