@@ -26,7 +26,7 @@ EXPORTS = [
     "ashcuda_default_config", "ashcuda_create", "ashcuda_destroy", "ashcuda_set_stream",
     "ashcuda_set_depth", "ashcuda_set_objects", "ashcuda_set_lights", "ashcuda_set_camera",
     "ashcuda_set_color", "ashcuda_taa_reset_history", "ashcuda_hiz_build", "ashcuda_occlusion_cull",
-    "ashcuda_light_cull", "ashcuda_taa_resolve", "ashcuda_bloom", "ashcuda_tonemap", "ashcuda_set_tonemap_operator",
+    "ashcuda_light_cull", "ashcuda_taa_resolve", "ashcuda_bloom", "ashcuda_tonemap", "ashcuda_set_tonemap_operator", "ashcuda_cull_compact_static",
     "ashcuda_view_run", "ashcuda_get", "ashcuda_readback", "ashcuda_readback_async", "ashcuda_sync",
     "ashcuda_hiz_level_count", "ashcuda_mip_extent", "ashcuda_kernel_launches", "ashcuda_graph_stats", "ashcuda_last_error",
     "ashcuda_version", "ashcuda_profile_kernels", "ashcuda_kernel_time_ms", "ashcuda_upload_view", "ashcuda_download_view", "ashcuda_download_view_packed",
@@ -75,6 +75,7 @@ def load_library():
         "ashcuda_bloom": (i32, [vp, vp]),
         "ashcuda_tonemap": (i32, [vp, vp]),
         "ashcuda_set_tonemap_operator": (i32, [vp, u32]),
+        "ashcuda_cull_compact_static": (i32, [i32, vp, vp, vp, u32, vp, u32, vp, vp, C.c_char_p, C.c_size_t]),
         "ashcuda_view_run": (i32, [vp, vp]),
         "ashcuda_get": (i32, [vp, i32, C.POINTER(vp), C.POINTER(C.c_size_t)]),
         "ashcuda_readback": (i32, [vp, i32, vp, C.c_size_t]),
@@ -393,6 +394,26 @@ class Context:
         ms, n = C.c_float(), C.c_uint64()
         self._ck(self._lib.ashcuda_kernel_time_ms(self._h, int(kernel_id), C.byref(ms), C.byref(n)))
         return ms.value, n.value
+
+
+STATIC_COMPACT_MAX_OBJECTS = 1 << 20          # ASH_STATIC_COMPACT_MAX_OBJECTS
+
+
+def cull_compact_static(objs, draws_in, visibility, object_count, draws_out, visible_count, device=0, stream=None):
+    """ashcuda_cull_compact_static (no counterpart in the reference; operators' request): the ordered draw-command
+    compaction without any allocation — scratch in a static 16 KB device array shared by every call on the GPU (calls
+    that overlap on a GPU race).  All arrays are device tensors the CALLER owns; enqueues on `stream` and returns."""
+    po, _ = _ptr(objs)
+    pd, _ = _ptr(draws_in)
+    pv, _ = _ptr(visibility)
+    pout, _ = _ptr(draws_out)
+    pcnt, _ = _ptr(visible_count)
+    n_draws = draws_in.numel() * draws_in.element_size() // T.DRAW_COMMAND.itemsize
+    err = C.create_string_buffer(256)
+    rc = load_library().ashcuda_cull_compact_static(int(device), C.c_void_p(stream) if stream else None, po, pd, n_draws, pv,
+                                                    int(object_count), pout, pcnt, err, len(err))
+    if rc != ASH_OK:
+        raise AshError(rc, err.value.decode())
 
 
 def version():

@@ -391,6 +391,24 @@ int ashcuda_tonemap       (ashcuda_ctx*, const AshPostProcessPushConstants*);   
 #define ASH_TONEMAP_UNCHARTED2 2u
 #define ASH_TONEMAP_NONE       3u
 int ashcuda_set_tonemap_operator(ashcuda_ctx*, uint32_t op);
+/* NO COUNTERPART IN THE REFERENCE — added for callers that cannot call cudaMalloc
+ * (code under CUDA-graph capture, tight serving loops, harnesses that forbid allocation).  The ordered draw-command
+ * compaction of ashcuda_occlusion_cull as a context-free call that ALLOCATES NOTHING: its scratch (visible objects per
+ * CTA of 256) is a file-scope static __device__ array of ASH_STATIC_COMPACT_MAX_OBJECTS / 256 words = 16 KB, which every
+ * GPU that loads the library holds until exit (csrc/cull_compact_static.cu).
+ *   in  (device pointers): objs[object_count], draws_in[n_draws], visibility[object_count] (non-zero = visible)
+ *   out (device pointers): draws_out[>= number of visible objects] = draws_in[objs[i].draw_index] of the visible objects in
+ *        ascending object index (zeros where draw_index >= n_draws), *visible_count — the values ashcuda_occlusion_cull
+ *        leaves in ASH_BUF_DRAWS_OUT / ASH_BUF_VISIBLE_COUNT for the same visibility.
+ * Enqueues on `cuda_stream` (a cudaStream_t, NULL = the default stream) of `device` and returns; the caller synchronises.
+ * object_count > ASH_STATIC_COMPACT_MAX_OBJECTS is rejected with ASH_ERR_INVALID.  err / err_len: optional buffer for the
+ * message (there is no context to ask).  All calls on a GPU SHARE the one array and find the previous call's contents in
+ * it (each call overwrites the entries it reads, nothing needs clearing); calls that OVERLAP on a GPU race: serialise. */
+#define ASH_STATIC_COMPACT_MAX_OBJECTS 1048576u
+int ashcuda_cull_compact_static(int device, void* cuda_stream, const AshCullObjectData* objs,
+                                const AshIndirectDrawCommand* draws_in, uint32_t n_draws, const uint32_t* visibility,
+                                uint32_t object_count, AshIndirectDrawCommand* draws_out, uint32_t* visible_count,
+                                char* err, size_t err_len);
 /* the whole view-frame in one call, fused kernels, same results as the staged calls */
 int ashcuda_view_run      (ashcuda_ctx*, const AshCudaViewParams*);
 
