@@ -38,8 +38,8 @@ HIZ_LEVELS = 12                    # "full pyramid" (PIN-4)
 METRIC, UNIT = "4k_views_per_sec", "views/s"
 # dram__bytes_read.sum + dram__bytes_write.sum per launch, from the committed `ncu --set full` captures of this
 # very workload (one launch each; re-captured whenever the kernel changes)
-NCU_DRAM_SOURCE = "profiles/r01_j_full_k_taa_pair.md (132.79 MB read + 93.82 MB write)"
-NCU_DRAM_BYTES = {"taa_threshold_fused": 132.792064e6 + 93.815296e6}
+NCU_DRAM_SOURCE = "profiles/r02_m_full_k_taa_tol.md (132.76 MB read + 94.68 MB write, precision fast); exact mode: profiles/r01_j_full_k_taa_pair.md"
+NCU_DRAM_BYTES = {("taa_threshold_fused", "fast"): 132.757760e6 + 94.679552e6, ("taa_threshold_fused", "exact"): 132.792064e6 + 93.815296e6}
 
 
 def workload_name():
@@ -639,7 +639,7 @@ def run_cuda(args):
     dom_k = kernels[KERNEL_NAMES[dom]]
     # DRAM bytes per launch of that kernel (dram__bytes_read.sum + dram__bytes_write.sum) from the committed
     # `ncu --set full` capture of this workload; null for any other workload or kernel.
-    traffic = NCU_DRAM_BYTES.get(KERNEL_NAMES[dom])          # the workload (cfg5, 4K) is fixed in this file
+    traffic = NCU_DRAM_BYTES.get((KERNEL_NAMES[dom], args.precision))          # the workload (cfg5, 4K) is fixed in this file
     # whole-view roofline: compulsory bytes of the staged path / measured time per view
     view_bytes = sum(algorithmic_bytes(k, n_objs, n_lights, st_mean) * kcount[k] / (B * (args.steps + 1))
                      for k in range(T.KERNEL_COUNT) if kcount[k])
