@@ -32,7 +32,7 @@ EXPORTS = [
     "ashcuda_version", "ashcuda_profile_kernels", "ashcuda_kernel_time_ms", "ashcuda_upload_view", "ashcuda_download_view", "ashcuda_download_view_packed",
     "ashcuda_debug_exact_taps",
     "ashcuda_set_instances", "ashcuda_set_lod_meshes", "ashcuda_set_lod_config", "ashcuda_instancing_finalize",
-    "ashcuda_set_forward_params", "ashcuda_forward_depth", "ashcuda_forward_shade", "ashcuda_debug_compute_utils",
+    "ashcuda_set_forward_params", "ashcuda_set_forward_reprojection", "ashcuda_forward_depth", "ashcuda_forward_shade", "ashcuda_debug_compute_utils",
 ]
 
 
@@ -98,6 +98,7 @@ def load_library():
         "ashcuda_set_lod_config": (i32, [vp, vp]),
         "ashcuda_instancing_finalize": (i32, [vp, vp]),
         "ashcuda_set_forward_params": (i32, [vp, vp]),
+        "ashcuda_set_forward_reprojection": (i32, [vp, vp]),
         "ashcuda_forward_depth": (i32, [vp, vp, u32]),
         "ashcuda_forward_shade": (i32, [vp]),
         "ashcuda_debug_compute_utils": (i32, [i32, i32, vp, u32, vp, vp]),
@@ -300,6 +301,17 @@ class Context:
 
     def draws_out(self, count):
         return self.readback(T.BUF_DRAWS_OUT, T.DRAW_COMMAND, count)
+
+    def set_forward_reprojection(self, reproj_cols=None):
+        """reproj = prevViewProj * inverse(view) as a (4,4) array of COLUMNS (None: no velocity output)."""
+        if reproj_cols is None:
+            self._ck(self._lib.ashcuda_set_forward_reprojection(self._h, None))
+        else:
+            m = np.ascontiguousarray(reproj_cols, np.float32).reshape(16)
+            self._ck(self._lib.ashcuda_set_forward_reprojection(self._h, m.ctypes.data))
+
+    def velocity(self):
+        return self.readback(T.BUF_VELOCITY, np.float16).reshape(self.H, self.W, 2)
 
     def tile_data(self):
         return self.readback(T.BUF_TILE_DATA, np.uint32).reshape(-1, T.TILE_STRIDE)

@@ -88,6 +88,7 @@ void taa_tol_patch(bool thresh, const TaaTolArgs& a, PatchArg* out);            
 bool taa_in_halo(const AshTaaPushConstants& pc);                                                     // post_fast.cu
 void lod_patch(const AshInstancingParams& ip, const AshLodConfig& cfg, PatchArg* out);               // instancing.cu
 void forward_setup_patch(const AshCullingCameraData& cam, PatchArg* out);                            // forward.cu
+void forward_velocity_patch(const float reproj[4][4], PatchArg* out);                                // forward.cu
 
 // What a captured view depends on besides the per-view values patched at replay (memcmp'd, zero-initialised).
 struct GraphKey {
@@ -97,12 +98,12 @@ struct GraphKey {
     float    taa_screen[4];
     float    inv_projection[4][4];                          // a graph without the k_tile_planes node is only valid for this matrix
     AshBloomParams bloom; AshPostProcessPushConstants post;
-    uint32_t in_halo, tol_variant, tonemap_op, planes_cached, taa_cur, history_valid, taa_ran, have_color, have_depth, have_instancing, concurrent, have_pyramid;
+    uint32_t in_halo, tol_variant, tonemap_op, planes_cached, fwd_velocity, taa_cur, history_valid, taa_ran, have_color, have_depth, have_instancing, concurrent, have_pyramid;
     AshForwardParams fwd;
 };
 struct ViewGraph {
     cudaGraph_t graph = nullptr; cudaGraphExec_t exec = nullptr;
-    cudaGraphNode_t n_store = nullptr, n_cull = nullptr, n_cull2 = nullptr, n_taa = nullptr, n_lod = nullptr, n_fwd = nullptr;
+    cudaGraphNode_t n_store = nullptr, n_cull = nullptr, n_cull2 = nullptr, n_taa = nullptr, n_lod = nullptr, n_fwd = nullptr, n_vel = nullptr;
     GraphKey key{}; bool valid = false;
     uint64_t launches = 0;                                  // kernels per replay
     bool taa_flip = false, history_valid = false, taa_ran = false, bloom_valid = false, have_pyramid = false, have_camera = false;
@@ -190,6 +191,8 @@ struct ashcuda_ctx {
     void*     fwd_consts = nullptr;
     uint32_t* fwd_late = nullptr;                // two-phase culling: objects newly visible in phase 2
     bool      have_forward = false;              // keys / spheres of the current view are valid
+    float     fwd_reproj[4][4] = {};             // prevViewProj * view^-1 (columns): forward_shade also writes RG16F velocity
+    bool      fwd_has_reproj = false;
 
     // CUDA-graph replay of view_run (view_graph.cu): one captured graph per TAA ping-pong parity
     ash::ViewGraph vgraph[2];
@@ -242,6 +245,8 @@ cudaError_t launch_light_cull(const AshGpuLight* lights, const AshLightCullingPu
                               uint32_t* tile_data, AshViewStats* stats, bool build_planes, const Launch& L);
 cudaError_t launch_store_view(const AshCullingCameraData& cam, bool with_camera, uint32_t view_id, AshCullingCameraData* camera_dev,
                               AshViewStats* stats, const Launch& L);                                  // view_graph.cu
+cudaError_t launch_forward_velocity(const unsigned long long* keys, const float4* spheres, const void* consts, const float* ray_x,
+                                    const float* ray_y, const float reproj[4][4], uint32_t W, uint32_t H, void* velocity, const Launch& L);
 size_t forward_consts_bytes();                                                                       // forward.cu
 struct ForwardBuffers {                       // forward.cu: everything the depth producer touches
     float4* spheres; int4* rects; uint32_t* big_list; uint32_t* big_count; float4* lights_view; float* ray_x; float* ray_y;

@@ -777,7 +777,19 @@ int ashcuda_forward_shade(ashcuda_ctx* c) {
                                      inst_color ? c->inst : nullptr, inst_color ? c->n_inst : 0u, c->fwd_consts, c->fwd_rays,
                                      c->fwd_rays + c->W, c->W, c->H, c->color_owned, c->L()));
     c->color = c->color_owned; c->velocity = nullptr;
+    if (c->fwd_has_reproj) {          // real motion vectors for taa_resolve.comp:94-102 (previous-frame transforms, static scene)
+        ASH_CUDA(c, launch_forward_velocity(c->fwd_keys, c->fwd_spheres, c->fwd_consts, c->fwd_rays, c->fwd_rays + c->W, c->fwd_reproj,
+                                            c->W, c->H, c->velocity_owned, c->L()));
+        c->velocity = c->velocity_owned;
+    }
     c->have_color = true; c->taa_ran = false; c->bloom_valid = false;
+    return ASH_OK;
+}
+
+int ashcuda_set_forward_reprojection(ashcuda_ctx* c, const float* reproj16) {
+    if (!c) return ASH_ERR_INVALID;
+    c->fwd_has_reproj = reproj16 != nullptr;
+    if (reproj16) std::memcpy(c->fwd_reproj, reproj16, sizeof(c->fwd_reproj));
     return ASH_OK;
 }
 
@@ -822,6 +834,7 @@ int ashcuda_get(ashcuda_ctx* c, int which, void** dev_ptr, size_t* bytes) {
         case ASH_BUF_INSTANCING_STATS: p = c->inst_stats; n = sizeof(AshInstancingStats); break;
         case ASH_BUF_FORWARD_KEYS:    p = c->fwd_keys; n = P * 8; break;
         case ASH_BUF_COLOR:           p = const_cast<void*>(c->color); n = P * 8; break;
+        case ASH_BUF_VELOCITY:        p = const_cast<void*>(c->velocity); n = c->velocity ? P * 4 : 0; if (!p) return fail(c, ASH_ERR_NOT_FOUND, "get: no velocity buffer"); break;
         case ASH_BUF_CULLING_STATS:   p = c->culling_stats; n = sizeof(AshCullingStats); break;
         default: return fail(c, ASH_ERR_NOT_FOUND, "get: unknown buffer id");
     }

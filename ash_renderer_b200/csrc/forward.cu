@@ -340,6 +340,57 @@ k_forward_shade(const unsigned long long* __restrict__ keys, const float4* __res
     hdr[p] = pack_rgba16f(color.x, color.y, color.z, 1.0f);
 }
 
+// ---------------------------------------------------------------------------------- velocity (RG16F)
+// The motion vector taa_resolve.comp:94-102 consumes: velocity = uv - prevUV, so that historyUV = uv - velocity is where
+// this pixel's surface point was on screen in the previous frame.  The scene is static (cull objects carry no previous
+// model matrix), so the point's previous clip position is reproj * (pos_view, 1) with reproj = prevViewProj * view^-1,
+// built by the caller like viewProj (float64, rounded once).  Pixels without a hit, or whose point was behind the previous
+// camera, get velocity 0 — the shader then falls back to the jitter delta (:97-99).  One thread per pixel; the hit is the
+// shade kernel's (same sphere, same ray tables, same t bits).
+struct Reproj { float m[4][4]; };
+__global__ void __launch_bounds__(256)
+k_forward_velocity(const unsigned long long* __restrict__ keys, const float4* __restrict__ spheres,
+                   const FwdConsts* __restrict__ consts, const float* __restrict__ ray_x, const float* __restrict__ ray_y,
+                   Reproj rp, __half2* __restrict__ vel) {
+    const FwdConsts k = *consts;
+    const int x = blockIdx.x * 32 + (threadIdx.x & 31), y = blockIdx.y * 8 + (threadIdx.x >> 5);
+    if (x >= (int)k.W || y >= (int)k.H) return;
+    const size_t p = (size_t)y * k.W + x;
+    const uint32_t id = (uint32_t)(keys[p] & 0xFFFFFFFFull);
+    float vx = 0.0f, vy = 0.0f;
+    if (id < k.object_count) {
+        const float dx = __ldg(ray_x + x), dy = __ldg(ray_y + y);
+        const float4 s = __ldg(spheres + id);
+        const float t = hit_t(s, sphere_cc(s), dx, dy, k.near_plane);
+        if (t >= 0.0f) {
+            const M4 m = load_m4(rp.m);
+            const V4 clip = mul4(m, fmul(dx, t), fmul(dy, t), -t, 1.0f);
+            if (clip.w > 0.0f) {
+                const float pu = fadd(fmul(fdiv(clip.x, clip.w), 0.5f), 0.5f), pv = fadd(fmul(fdiv(clip.y, clip.w), 0.5f), 0.5f);
+                vx = fsub(fdiv(fadd((float)x, 0.5f), (float)k.W), pu);
+                vy = fsub(fdiv(fadd((float)y, 0.5f), (float)k.H), pv);
+            }
+        }
+    }
+    vel[p] = __floats2half2_rn(vx, vy);
+}
+
+void forward_velocity_patch(const float reproj[4][4], PatchArg* out) {             // graph replay: argument 5 is the matrix
+    out->func = reinterpret_cast<const void*>(&k_forward_velocity);
+    out->arg_index = 5; out->n_args = 7;
+    std::memcpy(out->value, reproj, sizeof(Reproj));
+}
+
+cudaError_t launch_forward_velocity(const unsigned long long* keys, const float4* spheres, const void* consts, const float* ray_x,
+                                    const float* ray_y, const float reproj[4][4], uint32_t W, uint32_t H, void* velocity, const Launch& L) {
+    Reproj rp;
+    std::memcpy(rp.m, reproj, sizeof(rp.m));
+    Timed timed(L, ASH_KERNEL_FORWARD_SHADE);
+    k_forward_velocity<<<dim3((W + 31) / 32, (H + 7) / 8), 256, 0, L.s>>>(keys, spheres, static_cast<const FwdConsts*>(consts), ray_x, ray_y,
+                                                                            rp, static_cast<__half2*>(velocity));
+    return cudaGetLastError();
+}
+
 // ---------------------------------------------------------------------------------- launchers
 size_t forward_consts_bytes() { return sizeof(FwdConsts); }
 

@@ -56,6 +56,7 @@ GraphKey make_key(const ashcuda_ctx* c, const AshCudaViewParams* vp) {
     k.bloom = vp->bloom; k.post = vp->post;
     k.in_halo = taa_in_halo(vp->taa) ? 1u : 0u;
     k.tonemap_op = c->tonemap_op;
+    k.fwd_velocity = c->fwd_has_reproj ? 1u : 0u;
     if (vp->stages & ASH_STAGE_LIGHTS) {
         k.planes_cached = (c->planes_valid && std::memcmp(c->planes_ip, vp->camera.inv_projection, sizeof(c->planes_ip)) == 0) ? 1u : 0u;
         std::memcpy(k.inv_projection, vp->camera.inv_projection, sizeof(k.inv_projection));
@@ -72,7 +73,7 @@ GraphKey make_key(const ashcuda_ctx* c, const AshCudaViewParams* vp) {
 }
 
 // the per-view arguments of this view, in the order ViewGraph keeps the nodes
-struct Patches { PatchArg store, cull, cull2, taa, lod, fwd; bool has_cull, has_cull2, has_taa, has_lod, has_fwd; };
+struct Patches { PatchArg store, cull, cull2, taa, lod, fwd, vel; bool has_cull, has_cull2, has_taa, has_lod, has_fwd, has_vel; };
 
 void make_patches(const ashcuda_ctx* c, const AshCudaViewParams* vp, Patches* P) {
     const uint32_t st = vp->stages;
@@ -83,7 +84,7 @@ void make_patches(const ashcuda_ctx* c, const AshCudaViewParams* vp, Patches* P)
     if (P->has_cull) cull_patch(vp->cull, P->has_cull2 ? 1 : 0, &P->cull);
     if (P->has_cull2) cull_patch(vp->cull, 2, &P->cull2);
     if (P->has_taa) {
-        const bool vel = c->velocity != nullptr && !(st & ASH_STAGE_FORWARD_SHADE);
+        const bool vel = (st & ASH_STAGE_FORWARD_SHADE) ? c->fwd_has_reproj : c->velocity != nullptr;
         if (c->cfg.precision == ASH_PRECISION_FAST && !vel && taa_in_halo(vp->taa)) {
             TaaTolArgs ta;
             taa_tol_patch((st & ASH_STAGE_BLOOM) != 0, ash_taa_tol_plan(const_cast<ashcuda_ctx*>(c), vp->taa, vp->bloom.threshold, &ta), &P->taa);
@@ -100,6 +101,8 @@ void make_patches(const ashcuda_ctx* c, const AshCudaViewParams* vp, Patches* P)
     }
     P->has_fwd = (st & ASH_STAGE_FORWARD_DEPTH) != 0;
     if (P->has_fwd) forward_setup_patch(vp->camera, &P->fwd);
+    P->has_vel = (st & ASH_STAGE_FORWARD_SHADE) && c->fwd_has_reproj;
+    if (P->has_vel) forward_velocity_patch(c->fwd_reproj, &P->vel);
     P->store.func = reinterpret_cast<const void*>(&k_store_view);
     P->store.n_args = 5;
 }
@@ -191,7 +194,7 @@ int ash_view_run_graph(ashcuda_ctx* c, const AshCudaViewParams* vp, bool* handle
     const bool shaded = (st & ASH_STAGE_FORWARD_SHADE) != 0;                     // colour made inside the view, no velocity
     if (st & ASH_STAGE_TAA) {
         if (!(c->have_color || shaded) || !c->cfg.enable_post) return ASH_OK;    // eager path reports the error
-        if (!((c->velocity && !shaded) || taa_in_halo(vp->taa))) return ASH_OK;
+        if (!((shaded ? c->fwd_has_reproj : c->velocity != nullptr) || taa_in_halo(vp->taa))) return ASH_OK;
     }
     ViewGraph& g = c->vgraph[c->taa_cur & 1];
     const GraphKey key = make_key(c, vp);
@@ -218,6 +221,7 @@ int ash_view_run_graph(ashcuda_ctx* c, const AshCudaViewParams* vp, bool* handle
             if (ok && P.has_taa) ok = find_node(g.graph, P.taa.func, &g.n_taa) == cudaSuccess;     // absent: TAA taps not exact
             if (ok && P.has_lod) ok = find_node(g.graph, P.lod.func, &g.n_lod) == cudaSuccess;
             if (ok && P.has_fwd) ok = find_node(g.graph, P.fwd.func, &g.n_fwd) == cudaSuccess;
+            if (ok && P.has_vel) ok = find_node(g.graph, P.vel.func, &g.n_vel) == cudaSuccess;
         } else if (graph) cudaGraphDestroy(graph);
         if (!ok) {
             // an invalid view (rc != 0) is the caller's error, reported by the eager path below; a failed capture of a
@@ -257,6 +261,7 @@ int ash_view_run_graph(ashcuda_ctx* c, const AshCudaViewParams* vp, bool* handle
     if (P.has_taa) ASH_CUDA(c, patch_node(g, g.n_taa, P.taa.n_args, P.taa.arg_index, P.taa.value));
     if (P.has_lod) ASH_CUDA(c, patch_node(g, g.n_lod, P.lod.n_args, P.lod.arg_index, P.lod.value));
     if (P.has_fwd) ASH_CUDA(c, patch_node(g, g.n_fwd, P.fwd.n_args, P.fwd.arg_index, P.fwd.value));
+    if (P.has_vel) ASH_CUDA(c, patch_node(g, g.n_vel, P.vel.n_args, P.vel.arg_index, P.vel.value));
     ASH_CUDA(c, cudaGraphLaunch(g.exec, c->stream));
     if ((st & ASH_STAGE_LIGHTS) && vp->light.light_count != 0u) {      // the tile side planes now match this invProjection
         std::memcpy(c->planes_ip, vp->camera.inv_projection, sizeof(c->planes_ip)); c->planes_valid = true;

@@ -273,6 +273,12 @@ def instancing_params(cam, n):
     return ip
 
 
+def reprojection(cam, prev_cam):
+    """prevViewProj * inverse(view) as columns (float64 -> fp32 once): maps a view-space point of `cam` to the previous
+    frame's clip space (ashcuda_set_forward_reprojection)."""
+    return cols_mul(prev_cam.view_proj, cols_inverse(cam.view)).astype(np.float32)
+
+
 def forward_params(light_direction=(-0.3, -1.0, -0.2), light_color=(1.0, 0.95, 0.9), ambient=(0.03, 0.03, 0.04),
                    base_color=(0.8, 0.8, 0.8), emissive=(0.0, 0.0, 0.0), metallic=0.1, roughness=0.5,
                    background=(0.02, 0.02, 0.03), near=0.5, radius_scale=1.0, flags=T.FWD_TILE_LIGHTS):

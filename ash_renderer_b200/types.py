@@ -98,7 +98,7 @@ BUF_VISIBILITY, BUF_DRAWS_OUT, BUF_VISIBLE_COUNT, BUF_TILE_DATA = 1, 2, 3, 4
 BUF_TAA_OUT, BUF_LDR8, BUF_STATS, BUF_TILE_MINMAX, BUF_VISIBILITY_BITS = 5, 6, 7, 8, 9
 BUF_BLOOM_THRESHOLD = 10
 BUF_LOD_SELECTION, BUF_INSTANCES_OUT, BUF_BUCKET_OFFSETS, BUF_INSTANCE_DRAWS, BUF_INSTANCING_STATS = 11, 12, 13, 14, 15
-BUF_FORWARD_KEYS, BUF_COLOR, BUF_CULLING_STATS = 16, 17, 18
+BUF_FORWARD_KEYS, BUF_COLOR, BUF_CULLING_STATS, BUF_VELOCITY = 16, 17, 18, 19
 
 
 def BUF_HIZ_MIP(i):

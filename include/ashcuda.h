@@ -323,6 +323,7 @@ typedef struct AshCudaViewParams {
 #define ASH_BUF_INSTANCING_STATS 15 /* AshInstancingStats                                        */
 #define ASH_BUF_FORWARD_KEYS   16 /* u64 W x H: (depth bits << 32) | object index, ASH_FWD_NO_OBJECT where none */
 #define ASH_BUF_CULLING_STATS  18 /* AshCullingStats                                                              */
+#define ASH_BUF_VELOCITY      19    /* RG16F motion vectors: set_color's, or the forward pass's (ashcuda_set_forward_reprojection) */
 #define ASH_BUF_COLOR          17 /* RGBA16F W x H: the current HDR colour input (set_color / forward_shade)    */
 
 /* Kernel classes for ashcuda_profile_kernels / ashcuda_kernel_time_ms (device-time accounting;
@@ -435,6 +436,12 @@ int ashcuda_instancing_finalize(ashcuda_ctx*, const AshInstancingParams*);
  * for every light of the pixel's 16x16 tile list (the consumer light_culling.comp was written for and
  * frag.frag never got), and writes the HDR colour buffer (as set_color would). */
 int ashcuda_set_forward_params(ashcuda_ctx*, const AshForwardParams*);   /* NULL: defaults */
+/* Velocity output of the forward pass (the velocity buffer binding 2 of taa_resolve.comp:14 reads, :94-102): with a
+ * reprojection matrix set, ashcuda_forward_shade also writes RG16F velocity = uv - prevUV per pixel, prevUV from
+ * reproj * (view-space hit, 1), reproj = prevViewProj * inverse(view) as 16 floats in columns (the caller builds it like
+ * viewProj, renderer.rs:1645); the TAA of the same view then takes its velocity branch.  Static scene: CullObjectData
+ * carries no previous model matrix.  Pixels without a hit get 0 (jitter-delta fallback, :97-99).  NULL switches it off. */
+int ashcuda_set_forward_reprojection(ashcuda_ctx*, const float* reproj16_or_null);
 int ashcuda_forward_depth(ashcuda_ctx*, const AshCullingCameraData* cam, uint32_t object_count);
 int ashcuda_forward_shade(ashcuda_ctx*);   /* after forward_depth (and light_cull with ASH_FWD_TILE_LIGHTS) of the same view */
 

@@ -188,6 +188,36 @@ void ash_oracle_forward_depth(const AshCullObjectData* objs, uint32_t n, const A
     for (size_t i = 0; i < P; ++i) depth[i] = bitsf((uint32_t)(keys[i] >> 32));
 }
 
+// RG16F velocity of the forward pass (csrc/forward.cu: k_forward_velocity): velocity = uv - prevUV as
+// taa_resolve.comp:94-102 consumes it (historyUV = uv - velocity); prevUV from reproj * (view-space hit, 1),
+// reproj = prevViewProj * inverse(view) in columns.  No hit, or a point behind the previous camera: 0.
+void ash_oracle_forward_velocity(const uint64_t* keys, const AshCullObjectData* objs, uint32_t n,
+                                 const AshCullingCameraData* cam, const AshForwardParams* fp, const float reproj[4][4],
+                                 uint32_t W, uint32_t H, uint16_t* vel) {
+    std::vector<Sphere> spheres(n);
+    for (uint32_t i = 0; i < n; ++i) spheres[i] = sphere_of(objs[i], *cam, fp->radius_scale);
+#pragma omp parallel for schedule(static)
+    for (int y = 0; y < (int)H; ++y) {
+        const float dy = ray_coord(y, (int)H, cam->projection[1][1]);
+        for (int x = 0; x < (int)W; ++x) {
+            const size_t p = (size_t)y * W + x;
+            const uint32_t id = (uint32_t)(keys[p] & 0xFFFFFFFFu);
+            float vx = 0.0f, vy = 0.0f, t = -1.0f;
+            const float dx = ray_coord(x, (int)W, cam->projection[0][0]);
+            if (id < n) t = hit_t(spheres[id], dx, dy, fp->near_plane);
+            if (t >= 0.0f) {
+                const vec4 clip = mul(reproj, {dx * t, dy * t, -t, 1.0f});
+                if (clip.w > 0.0f) {
+                    const float pu = (clip.x / clip.w) * 0.5f + 0.5f, pv = (clip.y / clip.w) * 0.5f + 0.5f;
+                    vx = ((float)x + 0.5f) / (float)W - pu;
+                    vy = ((float)y + 0.5f) / (float)H - pv;
+                }
+            }
+            vel[p * 2] = f2h(vx); vel[p * 2 + 1] = f2h(vy);
+        }
+    }
+}
+
 void ash_oracle_forward_shade(const uint64_t* keys, const AshCullObjectData* objs, uint32_t n,
                               const AshGpuLight* lights, uint32_t n_lights, const uint32_t* tile_data,
                               const AshInstanceData* inst_or_null, uint32_t n_inst,

@@ -307,6 +307,19 @@ def two_phase_cull(objs, draws, cull_pc, cam, fp, W, H, prev_depth=None):
                 count=int(vis.sum()), draws_out=draws_out, keys=keys, depth=depth, depth_phase1=depth1)
 
 
+def forward_velocity(keys, objs, cam, fp, reproj_cols):
+    """RG16F velocity (H, W, 2) of the forward pass: uv - prevUV, prevUV from reproj * (view-space hit, 1)."""
+    H, W = keys.shape
+    k, o, c, p = _c(keys, np.uint64), _c(objs, OBJECT_DTYPE), _c(cam, CAMERA_DTYPE), _c(fp, FORWARD_PARAMS_DTYPE)
+    m = _c(reproj_cols, np.float32).reshape(4, 4)
+    vel = np.zeros((H, W, 2), np.float16)
+    f = lib().ash_oracle_forward_velocity
+    f.restype = None
+    f.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_void_p]
+    f(_p(k), _p(o), len(o.reshape(-1)), _p(c), _p(p), _p(m), W, H, _p(vel))
+    return vel
+
+
 def forward_shade(keys, objs, lights, tile_data, cam, fp, instances=None):
     """frag.frag's BRDF at every hit for the MVP light + the tile light lists: RGBA16F HxWx4."""
     H, W = keys.shape

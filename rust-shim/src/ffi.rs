@@ -118,6 +118,7 @@ extern "C" {
     pub fn ashcuda_bloom(ctx: *mut ashcuda_ctx, bp: *const AshBloomParams) -> c_int;
     pub fn ashcuda_tonemap(ctx: *mut ashcuda_ctx, pc: *const PostProcessPushConstants) -> c_int;
     pub fn ashcuda_set_tonemap_operator(ctx: *mut ashcuda_ctx, op: u32) -> c_int;
+    pub fn ashcuda_set_forward_reprojection(ctx: *mut ashcuda_ctx, reproj16_or_null: *const f32) -> c_int;
     /// no counterpart in the reference: allocation-free ordered compaction, static 16 KB scratch per GPU
     pub fn ashcuda_cull_compact_static(device: c_int, cuda_stream: *mut c_void, objs: *const CullObjectData, draws_in: *const IndirectDrawCommand,
                                        n_draws: u32, visibility: *const u32, object_count: u32, draws_out: *mut IndirectDrawCommand,

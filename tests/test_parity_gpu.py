@@ -746,6 +746,57 @@ def test_view_run_from_scene_to_ldr_with_forward_stages(backend, oracle, graph):
         assert (cap > 0 and rep > 0) if graph else (cap == 0 and rep == 0)
 
 
+@pytest.mark.parametrize("graph", [0, 1])
+def test_forward_pass_velocity_feeds_the_taa(backend, oracle, graph):
+    """Velocity output of the forward pass (RG16F, from previous-frame transforms) consumed by the TAA's velocity branch
+    (taa_resolve.comp:94-102), end to end through view_run with a moving camera: velocity bit-exact vs the oracle, the
+    resolve bit-exact vs the oracle's TAA fed with that velocity; the static-camera view yields velocity 0 on every hit."""
+    from ash_renderer_b200.host import TemporalAA
+    W, H = 640, 360
+    objs, draws = synth.make_objects((10, 8, 8), spacing=2.0, seed=61, jitter=0.3)
+    lights = synth.make_lights(200, extent=10.0, seed=62, center=(0.0, 2.0, 4.0))
+    fp = synth.forward_params(near=0.5, flags=T.FWD_TILE_LIGHTS)
+    taa = TemporalAA()
+    stages = T.STAGE_ALL | T.STAGE_FORWARD_DEPTH | T.STAGE_FORWARD_SHADE
+    eye = lambda t: (0.05 * t - 1.0, 2.0 + 0.02 * t, 22.0 - 0.08 * t) if t != 3 else eye(2)     # view 3 repeats view 2's camera
+    hist, prev_cam = None, None
+    with _ctx(backend, W, H, graph_replay=graph) as c:
+        c.set_objects(objs, draws)
+        c.upload_lights(lights)
+        c.set_forward_params(fp)
+        for t in range(5):
+            taa.begin_frame()
+            pc = taa.push_constants(W, H)
+            cam = synth.Camera(eye(t), (0, 0, 0), W, H, near=0.5)
+            reproj = synth.reprojection(cam, prev_cam if prev_cam is not None else cam)
+            c.set_forward_reprojection(reproj)
+            c.view_run(_view_params(cam, len(objs), len(lights), 9, W, H, pc, stages=stages, view_id=t))
+            keys = c.forward_keys()
+            vel = oracle.forward_velocity(keys, objs, cam.camera_data(), fp, reproj)
+            got = c.velocity()
+            assert np.array_equal(got.view(np.uint16), vel.view(np.uint16)), f"velocity of view {t}"
+            hit = (keys & np.uint64(0xFFFFFFFF)) != np.uint64(T.FWD_NO_OBJECT)
+            assert hit.mean() > 0.2
+            mag = np.abs(vel.astype(np.float32)).max(axis=2)
+            if t in (0, 3):                                        # same camera as the previous view: rounding noise only
+                assert (mag[hit] * W).max() < 0.02
+            else:                                                  # the camera moved: sub-pixel to few-pixel motion on the hits
+                assert (mag[hit] * W).max() > 0.5 and np.all(mag[~hit] == 0)
+            hdr = c.color()
+            ref = oracle.taa_resolve(hdr, hdr if hist is None else hist, vel, pc)
+            _assert_half_images_equal(c.taa_out(), ref, f"taa view {t}")
+            hist, prev_cam = ref, cam
+        cap, rep = c.graph_stats()
+        assert (cap > 0 and rep > 0) if graph else (cap == 0 and rep == 0)
+        c.set_forward_reprojection(None)                           # off again: the jitter-delta path, no velocity buffer
+        taa.begin_frame()
+        pc = taa.push_constants(W, H)
+        c.view_run(_view_params(cam, len(objs), len(lights), 9, W, H, pc, stages=stages, view_id=9))
+        _assert_half_images_equal(c.taa_out(), oracle.taa_resolve(c.color(), hist, None, pc), "taa without velocity")
+        with pytest.raises(backend.AshError):
+            c.velocity()
+
+
 @pytest.mark.parametrize("velocity", [False, True])
 def test_view_run_graph_replay_equals_eager(backend, velocity):
     """view_run through CUDA-graph replay (per-view kernel arguments patched) against the eager launches:
