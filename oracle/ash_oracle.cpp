@@ -116,9 +116,14 @@ inline int nearest_texel(float u, int W) {
     return (int)t;
 }
 
-struct Img16 { const uint16_t* p; int W, H; };  // RGBA16F, 4 halfs per texel
+// RGBA16F (4 halfs per texel) or, in the fp32_intermediates mode of PIN-6, RGBA32F (4 floats per texel, f32 = 1)
+struct Img16 { const uint16_t* p; int W, H; int f32 = 0; };
 
 inline vec4 fetch16(const Img16& im, int x, int y) {
+    if (im.f32) {
+        const float* t = reinterpret_cast<const float*>(im.p) + ((size_t)y * im.W + x) * 4;
+        return {t[0], t[1], t[2], t[3]};
+    }
     const uint16_t* t = im.p + ((size_t)y * im.W + x) * 4;
     return {h2f(t[0]), h2f(t[1]), h2f(t[2]), h2f(t[3])};
 }
@@ -145,7 +150,12 @@ inline vec4 texture16(const Img16& im, float u, float v) {
     return {lerp1(top.x, bot.x, fy), lerp1(top.y, bot.y, fy), lerp1(top.z, bot.z, fy),
             lerp1(top.w, bot.w, fy)};
 }
-inline void store16(uint16_t* img, int W, int x, int y, vec3 rgb, float a) {
+inline void store16(uint16_t* img, int W, int x, int y, vec3 rgb, float a, int f32 = 0) {
+    if (f32) {
+        float* t = reinterpret_cast<float*>(img) + ((size_t)y * W + x) * 4;
+        t[0] = rgb.x; t[1] = rgb.y; t[2] = rgb.z; t[3] = a;
+        return;
+    }
     uint16_t* t = img + ((size_t)y * W + x) * 4;
     t[0] = f2h(rgb.x); t[1] = f2h(rgb.y); t[2] = f2h(rgb.z); t[3] = f2h(a);
 }
@@ -416,11 +426,12 @@ static inline vec3 clip_aabb(vec3 mn, vec3 mx, vec3 hist) {      // :64-77 (igno
     return hist;
 }
 
-void ash_oracle_taa_resolve(const uint16_t* current, const uint16_t* history, const uint16_t* velocity,
-                            const AshTaaPushConstants* pc, uint16_t* output) {
+// fmt bits (fp32_intermediates mode, PIN-6): 1 = `current` is RGBA32F, 2 = `history` is, 4 = `output` is
+void ash_oracle_taa_resolve_fmt(const uint16_t* current, const uint16_t* history, const uint16_t* velocity,
+                                const AshTaaPushConstants* pc, uint16_t* output, int fmt) {
     const float sw = pc->screen_params[0], sh = pc->screen_params[1];
     const int W = (int)sw, H = (int)sh;
-    const Img16 cur{current, W, H}, hist{history, W, H};
+    const Img16 cur{current, W, H, fmt & 1}, hist{history, W, H, (fmt >> 1) & 1};
 #pragma omp parallel for schedule(static)
     for (int y = 0; y < H; ++y) {
         for (int x = 0; x < W; ++x) {
@@ -461,9 +472,13 @@ void ash_oracle_taa_resolve(const uint16_t* current, const uint16_t* history, co
             }
             if (hu < 0.0f || hu > 1.0f || hv < 0.0f || hv > 1.0f) blend = 0.0f;   // :153-156 (dead)
             vec3 r = c * (1.0f - blend) + h * blend;                              // :159 mix()
-            store16(output, W, x, y, r, 1.0f);                                    // :162
+            store16(output, W, x, y, r, 1.0f, (fmt >> 2) & 1);                    // :162
         }
     }
+}
+void ash_oracle_taa_resolve(const uint16_t* current, const uint16_t* history, const uint16_t* velocity,
+                            const AshTaaPushConstants* pc, uint16_t* output) {
+    ash_oracle_taa_resolve_fmt(current, history, velocity, pc, output, 0);
 }
 
 // HaltonSequence::halton — src/renderer/temporal_aa.rs:60-69
@@ -477,8 +492,8 @@ float ash_oracle_halton(uint32_t index, uint32_t base) {
 // Bloom — shaders/bloom_threshold.frag:18-35, bloom_downsample.frag:16-108,
 // bloom_upsample.frag:16-41; fragTexCoord = (p+0.5)/dstSize (postprocess.vert:8-14). PIN-9.
 // ==========================================================================================
-void ash_oracle_bloom_threshold(const uint16_t* hdr, int W, int H, float threshold, uint16_t* out) {
-    const Img16 src{hdr, W, H};
+void ash_oracle_bloom_threshold_fmt(const uint16_t* hdr, int W, int H, float threshold, uint16_t* out, int fmt) {   // 1 = src f32, 4 = dst f32
+    const Img16 src{hdr, W, H, fmt & 1};
     const float knee = 0.5f;                                                      // :32
 #pragma omp parallel for schedule(static)
     for (int y = 0; y < H; ++y)
@@ -490,12 +505,15 @@ void ash_oracle_bloom_threshold(const uint16_t* hdr, int W, int H, float thresho
             soft = soft * soft / (4.0f * knee + 0.00001f);
             float contrib = gmax(soft, br - threshold);
             contrib /= gmax(br, 0.00001f);
-            store16(out, W, x, y, c * contrib, 1.0f);
+            store16(out, W, x, y, c * contrib, 1.0f, (fmt >> 2) & 1);
         }
 }
+void ash_oracle_bloom_threshold(const uint16_t* hdr, int W, int H, float threshold, uint16_t* out) {
+    ash_oracle_bloom_threshold_fmt(hdr, W, H, threshold, out, 0);
+}
 
-void ash_oracle_bloom_downsample(const uint16_t* srcp, int sw, int sh, uint16_t* dst, int dw, int dh) {
-    const Img16 src{srcp, sw, sh};
+void ash_oracle_bloom_downsample_fmt(const uint16_t* srcp, int sw, int sh, uint16_t* dst, int dw, int dh, int f32) {
+    const Img16 src{srcp, sw, sh, f32};
     const float dx = 1.0f / (float)sw, dy = 1.0f / (float)sh;                     // texelSize (:11)
     const vec3 LUMA = {0.2126f, 0.7152f, 0.0722f};
 #pragma omp parallel for schedule(static)
@@ -513,14 +531,18 @@ void ash_oracle_bloom_downsample(const uint16_t* srcp, int sw, int sh, uint16_t*
                 res = res + (s * w) * wt[k];
                 sum += w * wt[k];
             }
-            store16(dst, dw, x, y, res / sum, 1.0f);                              // :107
+            store16(dst, dw, x, y, res / sum, 1.0f, f32);                         // :107
         }
+}
+void ash_oracle_bloom_downsample(const uint16_t* srcp, int sw, int sh, uint16_t* dst, int dw, int dh) {
+    ash_oracle_bloom_downsample_fmt(srcp, sw, sh, dst, dw, dh, 0);
 }
 
 // dst (dw x dh) = RN16( float(dst) + upsample(src) )   (additive blend, PIN-9)
-void ash_oracle_bloom_upsample_add(const uint16_t* srcp, int sw, int sh, uint16_t* dst, int dw, int dh,
-                                   float intensity) {
-    const Img16 src{srcp, sw, sh};
+void ash_oracle_bloom_upsample_add_fmt(const uint16_t* srcp, int sw, int sh, uint16_t* dst, int dw, int dh,
+                                       float intensity, int f32) {
+    const Img16 src{srcp, sw, sh, f32};
+    const Img16 dsti{dst, dw, dh, f32};
     const float dx = (1.0f / (float)sw) * 0.5f, dy = (1.0f / (float)sh) * 0.5f;   // :18
 #pragma omp parallel for schedule(static)
     for (int y = 0; y < dh; ++y)
@@ -540,10 +562,12 @@ void ash_oracle_bloom_upsample_add(const uint16_t* srcp, int sw, int sh, uint16_
             r = r + (((s0 + s2) + s4) + s6);
             r = r / 16.0f;
             r = r * intensity;
-            uint16_t* t = dst + ((size_t)y * dw + x) * 4;
-            vec3 d = {h2f(t[0]), h2f(t[1]), h2f(t[2])};
-            store16(dst, dw, x, y, r + d, 1.0f);
+            const vec3 d = xyz(fetch16(dsti, x, y));
+            store16(dst, dw, x, y, r + d, 1.0f, f32);
         }
+}
+void ash_oracle_bloom_upsample_add(const uint16_t* srcp, int sw, int sh, uint16_t* dst, int dw, int dh, float intensity) {
+    ash_oracle_bloom_upsample_add_fmt(srcp, sw, sh, dst, dw, dh, intensity, 0);
 }
 
 // ==========================================================================================
@@ -564,9 +588,9 @@ static float tonemap_curve(float xx, uint32_t op) {
     }
 }
 
-void ash_oracle_tonemap_op(const uint16_t* hdrp, const uint16_t* bloomp, int W, int H,
-                           const AshPostProcessPushConstants* pc, uint32_t op, uint8_t* ldr8) {
-    const Img16 hdr{hdrp, W, H}, bloom{bloomp, W, H};
+void ash_oracle_tonemap_fmt(const uint16_t* hdrp, const uint16_t* bloomp, int W, int H,
+                            const AshPostProcessPushConstants* pc, uint32_t op, uint8_t* ldr8, int fmt) {   // 1 = hdr f32, 2 = bloom f32
+    const Img16 hdr{hdrp, W, H, fmt & 1}, bloom{bloomp, W, H, (fmt >> 1) & 1};
     const float inv_gamma = 1.0f / pc->gamma;
 #pragma omp parallel for schedule(static)
     for (int y = 0; y < H; ++y)
@@ -591,6 +615,10 @@ void ash_oracle_tonemap_op(const uint16_t* hdrp, const uint16_t* bloomp, int W, 
 // 1 = exact fp32 weights (SURVEY.md PIN-6 as first written); tests/test_oracle_ref.py bounds the difference.
 void ash_oracle_set_weight_mode(int exact) { g_exact_weights = exact ? 1 : 0; }
 
+void ash_oracle_tonemap_op(const uint16_t* hdrp, const uint16_t* bloomp, int W, int H,
+                           const AshPostProcessPushConstants* pc, uint32_t op, uint8_t* ldr8) {
+    ash_oracle_tonemap_fmt(hdrp, bloomp, W, H, pc, op, ldr8, 0);
+}
 void ash_oracle_tonemap(const uint16_t* hdrp, const uint16_t* bloomp, int W, int H,
                         const AshPostProcessPushConstants* pc, uint8_t* ldr8) {
     ash_oracle_tonemap_op(hdrp, bloomp, W, H, pc, ASH_TONEMAP_ACES, ldr8);

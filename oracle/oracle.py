@@ -148,14 +148,25 @@ def light_cull(lights, pc, cam, depth):
 
 
 # ---------------------------------------------------------------- post chain
-def taa_resolve(current, history, velocity, pc):
-    """current/history: (H,W,4) float16; velocity: (H,W,2) float16 or None."""
-    current = _c(current, np.float16)
-    history = _c(history, np.float16)
+# Images are (H, W, 4) float16 — RGBA16F, the reference's render-target format — or float32: the fp32_intermediates mode of
+# PIN-6, where TAA output / history and the bloom targets are stored unrounded.  `out32` selects the output's storage.
+def _img(a):
+    a = np.asarray(a)
+    return np.ascontiguousarray(a, np.float32 if a.dtype == np.float32 else np.float16)
+
+
+def _is32(a):
+    return 1 if a.dtype == np.float32 else 0
+
+
+def taa_resolve(current, history, velocity, pc, out32=False):
+    """current/history: (H,W,4) float16 or float32; velocity: (H,W,2) float16 or None."""
+    current, history = _img(current), _img(history)
     velocity = None if velocity is None else _c(velocity, np.float16)
     pc = _c(pc, TAA_PC_DTYPE).reshape(1)
-    out = np.empty_like(current)
-    lib().ash_oracle_taa_resolve(_p(current), _p(history), _p(velocity), _p(pc), _p(out))
+    out = np.empty(current.shape, np.float32 if out32 else np.float16)
+    lib().ash_oracle_taa_resolve_fmt(_p(current), _p(history), _p(velocity), _p(pc), _p(out),
+                                     _is32(current) | (_is32(history) << 1) | (int(bool(out32)) << 2))
     return out
 
 
@@ -163,36 +174,36 @@ def halton(index, base):
     return float(lib().ash_oracle_halton(int(index), int(base)))
 
 
-def bloom_threshold(hdr, threshold):
-    hdr = _c(hdr, np.float16)
+def bloom_threshold(hdr, threshold, out32=False):
+    hdr = _img(hdr)
     H, W, _ = hdr.shape
-    out = np.empty_like(hdr)
-    lib().ash_oracle_bloom_threshold(_p(hdr), W, H, C.c_float(threshold), _p(out))
+    out = np.empty(hdr.shape, np.float32 if out32 else np.float16)
+    lib().ash_oracle_bloom_threshold_fmt(_p(hdr), W, H, C.c_float(threshold), _p(out), _is32(hdr) | (int(bool(out32)) << 2))
     return out
 
 
 def bloom_downsample(src):
-    src = _c(src, np.float16)
+    src = _img(src)
     sh, sw, _ = src.shape
     dw, dh = max(1, sw // 2), max(1, sh // 2)
-    dst = np.empty((dh, dw, 4), np.float16)
-    lib().ash_oracle_bloom_downsample(_p(src), sw, sh, _p(dst), dw, dh)
+    dst = np.empty((dh, dw, 4), src.dtype)
+    lib().ash_oracle_bloom_downsample_fmt(_p(src), sw, sh, _p(dst), dw, dh, _is32(src))
     return dst
 
 
 def bloom_upsample_add(src, dst, intensity=1.0):
-    """returns RN16(dst + upsample(src)); dst is not modified."""
-    src = _c(src, np.float16)
-    out = np.array(dst, dtype=np.float16, order="C", copy=True)
+    """returns RN(dst + upsample(src)) in the storage type of src; dst is not modified."""
+    src = _img(src)
+    out = np.array(dst, dtype=src.dtype, order="C", copy=True)
     sh, sw, _ = src.shape
     dh, dw, _ = out.shape
-    lib().ash_oracle_bloom_upsample_add(_p(src), sw, sh, _p(out), dw, dh, C.c_float(intensity))
+    lib().ash_oracle_bloom_upsample_add_fmt(_p(src), sw, sh, _p(out), dw, dh, C.c_float(intensity), _is32(src))
     return out
 
 
-def bloom_chain(hdr, threshold=0.8, mip_count=5, intensity=1.0):
-    """PIN-9 topology. Returns (U list [U_0..U_mip_count], D list [D_0..D_mip_count])."""
-    D = [bloom_threshold(hdr, threshold)]
+def bloom_chain(hdr, threshold=0.8, mip_count=5, intensity=1.0, out32=False):
+    """PIN-9 topology. Returns (U list [U_0..U_mip_count], D list [D_0..D_mip_count]); out32: fp32 bloom targets."""
+    D = [bloom_threshold(hdr, threshold, out32=out32)]
     for _ in range(mip_count):
         D.append(bloom_downsample(D[-1]))
     U = [None] * (mip_count + 1)
@@ -206,12 +217,13 @@ TONEMAP_ACES, TONEMAP_REINHARD, TONEMAP_UNCHARTED2, TONEMAP_NONE = range(4)
 
 
 def tonemap(hdr, bloom, pc, op=TONEMAP_ACES):
-    hdr = _c(hdr, np.float16)
-    bloom = None if bloom is None else _c(bloom, np.float16)
+    hdr = _img(hdr)
+    bloom = None if bloom is None else _img(bloom)
     pc = _c(pc, POST_PC_DTYPE).reshape(1)
     H, W, _ = hdr.shape
     out = np.empty((H, W, 4), np.uint8)
-    lib().ash_oracle_tonemap_op(_p(hdr), _p(bloom), W, H, _p(pc), C.c_uint32(op), _p(out))
+    fmt = _is32(hdr) | ((0 if bloom is None else _is32(bloom)) << 1)
+    lib().ash_oracle_tonemap_fmt(_p(hdr), _p(bloom), W, H, _p(pc), C.c_uint32(op), _p(out), fmt)
     return out
 
 

@@ -102,44 +102,44 @@ def light_cull(lights, pc, cam, depth):
     return tile_data.reshape(tiles, _o.TILE_STRIDE), true_counts
 
 
-def taa_resolve(current, history, velocity, pc):
-    current = _c(current, np.float16)
-    history = _c(history, np.float16)
+def taa_resolve(current, history, velocity, pc, out32=False):
+    current, history = _o._img(current), _o._img(history)
     velocity = None if velocity is None else _c(velocity, np.float16)
     pc = _c(pc, _o.TAA_PC_DTYPE).reshape(1)
-    out = np.zeros_like(current)
-    lib().ash_ref_taa_resolve(_p(current), _p(history), _p(velocity), _p(pc), _p(out))
+    out = np.zeros(current.shape, np.float32 if out32 else np.float16)
+    lib().ash_ref_taa_resolve_fmt(_p(current), _p(history), _p(velocity), _p(pc), _p(out),
+                                  _o._is32(current) | (_o._is32(history) << 1) | (int(bool(out32)) << 2))
     return out
 
 
-def bloom_threshold(hdr, threshold):
-    hdr = _c(hdr, np.float16)
+def bloom_threshold(hdr, threshold, out32=False):
+    hdr = _o._img(hdr)
     H, W, _ = hdr.shape
-    out = np.empty_like(hdr)
-    lib().ash_ref_bloom_threshold(_p(hdr), W, H, C.c_float(threshold), _p(out))
+    out = np.empty(hdr.shape, np.float32 if out32 else np.float16)
+    lib().ash_ref_bloom_threshold_fmt(_p(hdr), W, H, C.c_float(threshold), _p(out), _o._is32(hdr) | (int(bool(out32)) << 2))
     return out
 
 
 def bloom_downsample(src):
-    src = _c(src, np.float16)
+    src = _o._img(src)
     sh, sw, _ = src.shape
     dw, dh = max(1, sw // 2), max(1, sh // 2)
-    dst = np.empty((dh, dw, 4), np.float16)
-    lib().ash_ref_bloom_downsample(_p(src), sw, sh, _p(dst), dw, dh)
+    dst = np.empty((dh, dw, 4), src.dtype)
+    lib().ash_ref_bloom_downsample_fmt(_p(src), sw, sh, _p(dst), dw, dh, _o._is32(src))
     return dst
 
 
 def bloom_upsample_add(src, dst, intensity=1.0):
-    src = _c(src, np.float16)
-    out = np.array(dst, dtype=np.float16, order="C", copy=True)
+    src = _o._img(src)
+    out = np.array(dst, dtype=src.dtype, order="C", copy=True)
     sh, sw, _ = src.shape
     dh, dw, _ = out.shape
-    lib().ash_ref_bloom_upsample_add(_p(src), sw, sh, _p(out), dw, dh, C.c_float(intensity))
+    lib().ash_ref_bloom_upsample_add_fmt(_p(src), sw, sh, _p(out), dw, dh, C.c_float(intensity), _o._is32(src))
     return out
 
 
-def bloom_chain(hdr, threshold=0.8, mip_count=5, intensity=1.0):
-    D = [bloom_threshold(hdr, threshold)]
+def bloom_chain(hdr, threshold=0.8, mip_count=5, intensity=1.0, out32=False):
+    D = [bloom_threshold(hdr, threshold, out32=out32)]
     for _ in range(mip_count):
         D.append(bloom_downsample(D[-1]))
     U = [None] * (mip_count + 1)
@@ -150,10 +150,10 @@ def bloom_chain(hdr, threshold=0.8, mip_count=5, intensity=1.0):
 
 
 def tonemap(hdr, bloom, pc):
-    hdr = _c(hdr, np.float16)
-    bloom = None if bloom is None else _c(bloom, np.float16)
+    hdr = _o._img(hdr)
+    bloom = None if bloom is None else _o._img(bloom)
     pc = _c(pc, _o.POST_PC_DTYPE).reshape(1)
     H, W, _ = hdr.shape
     out = np.empty((H, W, 4), np.uint8)
-    lib().ash_ref_tonemap(_p(hdr), _p(bloom), W, H, _p(pc), _p(out))
+    lib().ash_ref_tonemap_fmt(_p(hdr), _p(bloom), W, H, _p(pc), _p(out), _o._is32(hdr) | ((0 if bloom is None else _o._is32(bloom)) << 1))
     return out

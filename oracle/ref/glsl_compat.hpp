@@ -185,7 +185,7 @@ inline float half_to_float(uint16_t h) { _Float16 v; memcpy(&v, &h, 2); return (
 inline uint16_t float_to_half(float f) { _Float16 v = (_Float16)f; uint16_t h; memcpy(&h, &v, 2); return h; }
 
 // ---- textures and images
-enum Format { FMT_R32F = 0, FMT_RGBA16F = 1, FMT_RG16F = 2, FMT_RGBA8 = 3 };
+enum Format { FMT_R32F = 0, FMT_RGBA16F = 1, FMT_RG16F = 2, FMT_RGBA8 = 3, FMT_RGBA32F = 4 };   // RGBA32F: fp32_intermediates mode (PIN-6)
 inline int g_exact_weights = 0;  // 1 = exact fp32 bilinear weights (SURVEY PIN-6), 0 = 8-bit sub-texel weights
 
 struct sampler2D {
@@ -206,6 +206,7 @@ inline vec4 texel_fetch(const sampler2D& s, int l, int x, int y) {
     size_t i = (size_t)y * s.w[l] + x;
     switch (s.format) {
     case FMT_R32F:    return vec4(((const float*)s.level[l])[i], 0.0f, 0.0f, 1.0f);
+    case FMT_RGBA32F: { const float* t = (const float*)s.level[l] + i * 4; return vec4(t[0], t[1], t[2], t[3]); }
     case FMT_RGBA16F: { const uint16_t* t = (const uint16_t*)s.level[l] + i * 4;
                         return vec4(half_to_float(t[0]), half_to_float(t[1]), half_to_float(t[2]), half_to_float(t[3])); }
     default:          { const uint16_t* t = (const uint16_t*)s.level[l] + i * 2;
@@ -258,6 +259,7 @@ inline void imageStore(const image2D& im, ivec2 p, vec4 v) {
     if (p.x < 0 || p.y < 0 || p.x >= im.w || p.y >= im.h) return;
     size_t i = (size_t)p.y * im.w + p.x;
     if (im.format == FMT_R32F) ((float*)im.p)[i] = v.x;
+    else if (im.format == FMT_RGBA32F) { float* t = (float*)im.p + i * 4; t[0] = v.x; t[1] = v.y; t[2] = v.z; t[3] = v.w; }
     else { uint16_t* t = (uint16_t*)im.p + i * 4;
            t[0] = float_to_half(v.x); t[1] = float_to_half(v.y); t[2] = float_to_half(v.z); t[3] = float_to_half(v.w); }
 }

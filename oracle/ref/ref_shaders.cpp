@@ -82,13 +82,19 @@ inline int div_up(int a, int b) { return (a + b - 1) / b; }
 
 // one fullscreen pass: fragTexCoord at the pixel centre (postprocess.vert:8-14 interpolated), RGBA16F target
 template <class Set, class Main, class Get>
-void fullscreen_rgba16f(int W, int H, uint16_t* dst, bool additive, Set set_uv, Main shader, Get get_color) {
+void fullscreen_rgba16f(int W, int H, uint16_t* dst, bool additive, Set set_uv, Main shader, Get get_color, int f32 = 0) {
 #pragma omp parallel for schedule(static)
     for (int y = 0; y < H; ++y)
         for (int x = 0; x < W; ++x) {
             set_uv(vec2(((float)x + 0.5f) / (float)W, ((float)y + 0.5f) / (float)H));
             shader();
             vec4 c = get_color();
+            if (f32) {                                     // RGBA32F target (fp32_intermediates): the same blend, no rounding
+                float* t = (float*)dst + ((size_t)y * W + x) * 4;
+                if (additive) { c.x = c.x + t[0]; c.y = c.y + t[1]; c.z = c.z + t[2]; }
+                t[0] = c.x; t[1] = c.y; t[2] = c.z; t[3] = c.w;
+                continue;
+            }
             uint16_t* t = dst + ((size_t)y * W + x) * 4;
             if (additive) {   // PIN-9: VK_BLEND_OP_ADD, ONE / ONE on colour; alpha written from the source
                 c.x = c.x + half_to_float(t[0]); c.y = c.y + half_to_float(t[1]); c.z = c.z + half_to_float(t[2]);
@@ -232,15 +238,22 @@ void ash_ref_light_cull(const AshGpuLight* lights_in, const AshLightCullingPushC
 }
 
 // shaders/taa_resolve.comp; local size 8x8; velocity == NULL binds a 1x1 zero texture (PIN-12)
+void ash_ref_taa_resolve_fmt(const uint16_t* current, const uint16_t* history, const uint16_t* velocity,
+                             const AshTaaPushConstants* pc, uint16_t* output, int fmt);
 void ash_ref_taa_resolve(const uint16_t* current, const uint16_t* history, const uint16_t* velocity,
                          const AshTaaPushConstants* pc, uint16_t* output) {
+    ash_ref_taa_resolve_fmt(current, history, velocity, pc, output, 0);
+}
+// fmt bits: 1 = `current` is RGBA32F, 2 = `history` is, 4 = `outputColor` is an rgba32f image
+void ash_ref_taa_resolve_fmt(const uint16_t* current, const uint16_t* history, const uint16_t* velocity,
+                             const AshTaaPushConstants* pc, uint16_t* output, int fmt) {
     using namespace sh_taa;
     const int W = (int)pc->screen_params[0], H = (int)pc->screen_params[1];
-    currentColor = make_sampler(current, W, H, FMT_RGBA16F, 1);
-    historyColor = make_sampler(history, W, H, FMT_RGBA16F, 1);
+    currentColor = make_sampler(current, W, H, (fmt & 1) ? FMT_RGBA32F : FMT_RGBA16F, 1);
+    historyColor = make_sampler(history, W, H, (fmt & 2) ? FMT_RGBA32F : FMT_RGBA16F, 1);
     velocityBuffer = velocity ? make_sampler(velocity, W, H, FMT_RG16F, 1) : make_sampler(kZeroTexel, 1, 1, FMT_RG16F, 1);
     depthBuffer = make_sampler(kZeroTexel, 1, 1, FMT_RG16F, 0);      // binding 3 is never read
-    outputColor = image2D{output, W, H, FMT_RGBA16F};
+    outputColor = image2D{output, W, H, (fmt & 4) ? FMT_RGBA32F : FMT_RGBA16F};
     memcpy(&sh_taa::pc, pc, sizeof(*pc));
     const int gy = div_up(H, 8) * 8, gx = div_up(W, 8) * 8;
 #pragma omp parallel for schedule(static)
@@ -252,37 +265,55 @@ void ash_ref_taa_resolve(const uint16_t* current, const uint16_t* history, const
 }
 
 // shaders/bloom_threshold.frag (push constants: fullscreen_pass.rs PostProcessPushConstants, .threshold in slot 3)
+void ash_ref_bloom_threshold_fmt(const uint16_t* hdr, int W, int H, float threshold, uint16_t* dst, int fmt);
 void ash_ref_bloom_threshold(const uint16_t* hdr, int W, int H, float threshold, uint16_t* dst) {
+    ash_ref_bloom_threshold_fmt(hdr, W, H, threshold, dst, 0);
+}
+void ash_ref_bloom_threshold_fmt(const uint16_t* hdr, int W, int H, float threshold, uint16_t* dst, int fmt) {   // 1 = src f32, 4 = dst f32
     using namespace sh_threshold;
-    hdrBuffer = make_sampler(hdr, W, H, FMT_RGBA16F, 1);
+    hdrBuffer = make_sampler(hdr, W, H, (fmt & 1) ? FMT_RGBA32F : FMT_RGBA16F, 1);
     sh_threshold::pc.exposure = 1.0f; sh_threshold::pc.gamma = 2.2f; sh_threshold::pc.bloomIntensity = 0.5f;
     sh_threshold::pc.threshold = threshold;
-    fullscreen_rgba16f(W, H, dst, false, [](vec2 uv) { fragTexCoord = uv; }, shader_main, [] { return outColor; });
+    fullscreen_rgba16f(W, H, dst, false, [](vec2 uv) { fragTexCoord = uv; }, shader_main, [] { return outColor; }, (fmt >> 2) & 1);
 }
 
 // shaders/bloom_downsample.frag; texelSize = 1 / size(source) (PIN-9)
+void ash_ref_bloom_downsample_fmt(const uint16_t* src, int sw, int sh, uint16_t* dst, int dw, int dh, int f32);
 void ash_ref_bloom_downsample(const uint16_t* src, int sw, int sh, uint16_t* dst, int dw, int dh) {
+    ash_ref_bloom_downsample_fmt(src, sw, sh, dst, dw, dh, 0);
+}
+void ash_ref_bloom_downsample_fmt(const uint16_t* src, int sw, int sh, uint16_t* dst, int dw, int dh, int f32) {
     using namespace sh_down;
-    sourceTexture = make_sampler(src, sw, sh, FMT_RGBA16F, 1);
+    sourceTexture = make_sampler(src, sw, sh, f32 ? FMT_RGBA32F : FMT_RGBA16F, 1);
     sh_down::pc.texelSize = vec2(1.0f / (float)sw, 1.0f / (float)sh);
-    fullscreen_rgba16f(dw, dh, dst, false, [](vec2 uv) { fragTexCoord = uv; }, shader_main, [] { return outColor; });
+    fullscreen_rgba16f(dw, dh, dst, false, [](vec2 uv) { fragTexCoord = uv; }, shader_main, [] { return outColor; }, f32);
 }
 
 // shaders/bloom_upsample.frag, additively blended onto dst (PIN-9)
+void ash_ref_bloom_upsample_add_fmt(const uint16_t* src, int sw, int sh, uint16_t* dst, int dw, int dh, float intensity, int f32);
 void ash_ref_bloom_upsample_add(const uint16_t* src, int sw, int sh, uint16_t* dst, int dw, int dh, float intensity) {
+    ash_ref_bloom_upsample_add_fmt(src, sw, sh, dst, dw, dh, intensity, 0);
+}
+void ash_ref_bloom_upsample_add_fmt(const uint16_t* src, int sw, int sh, uint16_t* dst, int dw, int dh, float intensity, int f32) {
     using namespace sh_up;
-    sourceTexture = make_sampler(src, sw, sh, FMT_RGBA16F, 1);
+    sourceTexture = make_sampler(src, sw, sh, f32 ? FMT_RGBA32F : FMT_RGBA16F, 1);
     sh_up::pc.texelSize = vec2(1.0f / (float)sw, 1.0f / (float)sh);
     sh_up::pc.intensity = intensity;
-    fullscreen_rgba16f(dw, dh, dst, true, [](vec2 uv) { fragTexCoord = uv; }, shader_main, [] { return outColor; });
+    fullscreen_rgba16f(dw, dh, dst, true, [](vec2 uv) { fragTexCoord = uv; }, shader_main, [] { return outColor; }, f32);
 }
 
 // shaders/tonemapping.frag into an R8G8B8A8_UNORM target (PIN-11); bloom == NULL binds a 1x1 zero texture
+void ash_ref_tonemap_fmt(const uint16_t* hdr, const uint16_t* bloom, int W, int H,
+                         const AshPostProcessPushConstants* pc, uint8_t* ldr8, int fmt);
 void ash_ref_tonemap(const uint16_t* hdr, const uint16_t* bloom, int W, int H,
                      const AshPostProcessPushConstants* pc, uint8_t* ldr8) {
+    ash_ref_tonemap_fmt(hdr, bloom, W, H, pc, ldr8, 0);
+}
+void ash_ref_tonemap_fmt(const uint16_t* hdr, const uint16_t* bloom, int W, int H,
+                         const AshPostProcessPushConstants* pc, uint8_t* ldr8, int fmt) {   // 1 = hdr f32, 2 = bloom f32
     using namespace sh_tonemap;
-    hdrBuffer = make_sampler(hdr, W, H, FMT_RGBA16F, 1);
-    bloomBuffer = bloom ? make_sampler(bloom, W, H, FMT_RGBA16F, 1) : make_sampler(kZeroTexel, 1, 1, FMT_RGBA16F, 1);
+    hdrBuffer = make_sampler(hdr, W, H, (fmt & 1) ? FMT_RGBA32F : FMT_RGBA16F, 1);
+    bloomBuffer = bloom ? make_sampler(bloom, W, H, (fmt & 2) ? FMT_RGBA32F : FMT_RGBA16F, 1) : make_sampler(kZeroTexel, 1, 1, FMT_RGBA16F, 1);
     memcpy(&sh_tonemap::pc, pc, sizeof(*pc));
 #pragma omp parallel for schedule(static)
     for (int y = 0; y < H; ++y)

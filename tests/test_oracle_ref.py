@@ -263,6 +263,32 @@ def test_bloom_chain_and_tonemap_odd_extents(oracle, W, H):
     assert np.array_equal(oracle.tonemap(hdr, None, post_pc()), ref.tonemap(hdr, None, post_pc()))
 
 
+# ------------------------------------------------------------------ fp32_intermediates storage (PIN-6, second mode)
+@pytest.mark.parametrize("W,H", [(200, 120), (135, 77)])
+def test_fp32_intermediates_mode(oracle, W, H):
+    """TAA output / history and the bloom targets stored as RGBA32F instead of RGBA16F (SURVEY PIN-6's fp32_intermediates):
+    the oracle equals the reference's shader text bit for bit in this mode too, over a 3-frame recurrence + bloom + tonemap;
+    rounding the fp32 first-frame resolve to fp16 gives the RGBA16F mode's resolve exactly."""
+    seq = synth.HdrSequence(W, H, seed=4, n_discs=25)
+    jit = [(0.0, -0.16666667), (-0.25, 0.16666667), (0.25, -0.38888889)]
+    hist = rhist = None
+    prev = (0.0, 0.0)
+    for t, j in enumerate(jit):
+        f = seq.frame(*j)
+        pc = taa_pc(W, H, jitter=j, prev=prev)
+        out = oracle.taa_resolve(f, f if hist is None else hist, None, pc, out32=True)
+        rout = ref.taa_resolve(f, f if rhist is None else rhist, None, pc, out32=True)
+        assert out.dtype == np.float32 and same(out, rout), t
+        if t == 0:
+            assert same(out.astype(np.float16), oracle.taa_resolve(f, f, None, pc))
+        hist, rhist, prev = out, rout, j
+    U, D = oracle.bloom_chain(hist, 0.8, 5, out32=True)
+    RU, RD = ref.bloom_chain(rhist, 0.8, 5, out32=True)
+    for k in range(6):
+        assert D[k].dtype == np.float32 and same(D[k], RD[k]) and same(U[k], RU[k]), k
+    assert np.array_equal(oracle.tonemap(hist, U[0], post_pc()), ref.tonemap(rhist, RU[0], post_pc()))
+
+
 # ------------------------------------------------------------------ the PIN-6 weight model (VERDICT r1, weak #2)
 def test_exact_weight_mode_also_matches_and_bounds_the_pin6_change(oracle):
     """SURVEY PIN-6 first pinned exact fp32 bilinear weights; the library pins 8-bit sub-texel weights.
