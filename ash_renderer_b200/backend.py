@@ -291,7 +291,7 @@ class Context:
 
     def bloom_mip(self, k):
         w, h = self.mip_extent(T.BUF_BLOOM_MIP(k))
-        return self.readback(T.BUF_BLOOM_MIP(k), np.float16).reshape(h, w, 4)
+        return self.readback(T.BUF_BLOOM_MIP(k), self._image_dtype()).reshape(h, w, 4)
 
     def visibility(self):
         return self.readback(T.BUF_VISIBILITY, np.uint32)
@@ -316,8 +316,11 @@ class Context:
     def tile_data(self):
         return self.readback(T.BUF_TILE_DATA, np.uint32).reshape(-1, T.TILE_STRIDE)
 
+    def _image_dtype(self):
+        return np.float32 if int(self.cfg["fp32_intermediates"][0]) else np.float16
+
     def taa_out(self):
-        return self.readback(T.BUF_TAA_OUT, np.float16).reshape(self.H, self.W, 4)
+        return self.readback(T.BUF_TAA_OUT, self._image_dtype()).reshape(self.H, self.W, 4)
 
     def ldr8(self):
         return self.readback(T.BUF_LDR8, np.uint8).reshape(self.H, self.W, 4)

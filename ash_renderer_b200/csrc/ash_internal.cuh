@@ -283,6 +283,17 @@ cudaError_t launch_bloom_upsample_add(const void* src, uint32_t sw, uint32_t sh,
 cudaError_t launch_tonemap(const void* hdr, const void* bloom_or_null, void* ldr8, uint32_t W, uint32_t H,
                            const AshPostProcessPushConstants& pc, bool center, uint32_t op, const Launch& L);
 
+// ---- fp32_intermediates storage mode (post_f32.cu): the general kernels over RGBA16F / RGBA32F textures (flag = 1: RGBA32F)
+cudaError_t launch_taa_f(const void* cur, int cur_f32, const void* hist, int hist_f32, const void* vel, void* out, int out_f32,
+                         const AshTaaPushConstants& pc, const Launch& L);
+cudaError_t launch_bloom_threshold_f(const void* hdr, int hdr_f32, void* out, int out_f32, uint32_t W, uint32_t H, float threshold,
+                                     const Launch& L);
+cudaError_t launch_bloom_downsample_f(const void* src, uint32_t sw, uint32_t sh, void* dst, uint32_t dw, uint32_t dh, int f32, const Launch& L);
+cudaError_t launch_bloom_upsample_add_f(const void* src, uint32_t sw, uint32_t sh, void* dst, uint32_t dw, uint32_t dh, float intensity,
+                                        int f32, const Launch& L);
+cudaError_t launch_tonemap_f(const void* hdr, int hdr_f32, const void* bloom_or_null, int bloom_f32, void* ldr8, uint32_t W, uint32_t H,
+                             const AshPostProcessPushConstants& pc, uint32_t op, const Launch& L);
+
 // ---- fast post kernels (post_fast.cu): bit-identical to the general ones, valid when the exact-tap
 //      checks below hold for the extents involved
 cudaError_t launch_taa_fast(const void* cur, const void* hist, const void* vel_or_null, void* out, void* thr_or_null,

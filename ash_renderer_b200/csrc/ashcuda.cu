@@ -160,9 +160,10 @@ static int create_impl(ashcuda_ctx* c) {
     if (c->cfg.enable_post) {
         ASH_CUDA(c, dmalloc(&c->color_owned, P * 8));
         ASH_CUDA(c, dmalloc(&c->velocity_owned, P * 4));
-        ASH_CUDA(c, dmalloc(&c->taa[0], P * 8));
-        ASH_CUDA(c, dmalloc(&c->taa[1], P * 8));
-        ASH_CUDA(c, dmalloc(&c->bloom_t, P * 8));
+        const size_t texel = c->cfg.fp32_intermediates ? 16 : 8;    // RGBA32F intermediates (PIN-6, second mode) or RGBA16F
+        ASH_CUDA(c, dmalloc(&c->taa[0], P * texel));
+        ASH_CUDA(c, dmalloc(&c->taa[1], P * texel));
+        ASH_CUDA(c, dmalloc(&c->bloom_t, P * texel));
         ASH_CUDA(c, dmalloc(&c->ldr8, P * 4));
         BloomChain& b = c->bloom;
         b.mips = c->cfg.bloom_mips;
@@ -170,7 +171,7 @@ static int create_impl(ashcuda_ctx* c) {
         for (uint32_t k = 1; k <= b.mips; ++k) {     // PIN-9: extent max(1, floor(prev/2))
             b.w[k] = b.w[k - 1] / 2 ? b.w[k - 1] / 2 : 1;
             b.h[k] = b.h[k - 1] / 2 ? b.h[k - 1] / 2 : 1;
-            ASH_CUDA(c, dmalloc(&b.d[k], (size_t)b.w[k] * b.h[k] * 8));
+            ASH_CUDA(c, dmalloc(&b.d[k], (size_t)b.w[k] * b.h[k] * texel));
         }
         // which levels may run the fast kernels: every sampler shortcut is validated here, per extent
         c->center_exact = axis_center_exact((int)W, (float)W) && axis_center_exact((int)H, (float)H);
@@ -208,7 +209,7 @@ int ashcuda_create(ashcuda_ctx** out, int device, uint32_t width, uint32_t heigh
     if (cfg_or_null) c->cfg = *cfg_or_null; else ashcuda_default_config(&c->cfg);
     if (c->cfg.max_batches == 0) c->cfg.max_batches = 64;          // configs written before the field existed
     if (c->cfg.bloom_mips > ASH_MAX_BLOOM_MIPS || c->cfg.hiz_levels == 0 || c->cfg.max_batches > 128 ||
-        c->cfg.precision > ASH_PRECISION_FAST) {
+        c->cfg.precision > ASH_PRECISION_FAST || c->cfg.fp32_intermediates > 1u) {
         g_create_error = "ashcuda_create: bad config"; delete c; return ASH_ERR_INVALID;
     }
     lod_config_default(&c->lod_cfg);
@@ -381,7 +382,9 @@ static int taa_resolve_impl(ashcuda_ctx* c, const AshTaaPushConstants* pc, void*
     void* out = c->taa[c->taa_cur ^ 1];
     const bool exact = taa_taps_exact(c, pc);
     *fused = false;
-    if (exact && c->cfg.precision == ASH_PRECISION_FAST && !c->velocity && taa_in_halo(*pc)) {
+    if (c->cfg.fp32_intermediates) {      // history is RGBA32F once a resolve exists, the colour input (first frame) RGBA16F
+        ASH_CUDA(c, launch_taa_f(c->color, 0, hist, c->history_valid ? 1 : 0, c->velocity, out, 1, *pc, c->L()));
+    } else if (exact && c->cfg.precision == ASH_PRECISION_FAST && !c->velocity && taa_in_halo(*pc)) {
         TaaTolArgs ta;
         ASH_CUDA(c, launch_taa_tol(c->color, hist, out, thr_or_null, ash_taa_tol_plan(c, *pc, threshold, &ta), c->L()));   // post_taa_tol.cu
         *fused = thr_or_null != nullptr;
@@ -408,10 +411,19 @@ int ashcuda_taa_resolve(ashcuda_ctx* c, const AshTaaPushConstants* pc) {
 
 static const void* resolved_color(const ashcuda_ctx* c) { return c->taa_ran ? c->taa[c->taa_cur] : c->color; }
 
+// T = threshold(resolved colour) into D_0; in the fp32_intermediates mode the source is RGBA32F iff a TAA resolve produced it
+static cudaError_t bloom_threshold_any(ashcuda_ctx* c, float threshold) {
+    BloomChain& b = c->bloom;
+    if (c->cfg.fp32_intermediates)
+        return launch_bloom_threshold_f(resolved_color(c), c->taa_ran ? 1 : 0, b.d[0], 1, c->W, c->H, threshold, c->L());
+    return launch_bloom_threshold(resolved_color(c), b.d[0], c->W, c->H, threshold, c->center_exact, c->L());
+}
+
 static int bloom_down(ashcuda_ctx* c, uint32_t mips) {          // D_k = downsample(D_{k-1}), PIN-9
     BloomChain& b = c->bloom;
     for (uint32_t k = 1; k <= mips; ++k) {
-        if (b.down_fast[k]) ASH_CUDA(c, launch_bloom_downsample_fast(b.d[k - 1], b.w[k - 1], b.h[k - 1], b.d[k], b.w[k], b.h[k], c->L()));
+        if (c->cfg.fp32_intermediates) ASH_CUDA(c, launch_bloom_downsample_f(b.d[k - 1], b.w[k - 1], b.h[k - 1], b.d[k], b.w[k], b.h[k], 1, c->L()));
+        else if (b.down_fast[k]) ASH_CUDA(c, launch_bloom_downsample_fast(b.d[k - 1], b.w[k - 1], b.h[k - 1], b.d[k], b.w[k], b.h[k], c->L()));
         else ASH_CUDA(c, launch_bloom_downsample(b.d[k - 1], b.w[k - 1], b.h[k - 1], b.d[k], b.w[k], b.h[k], c->L()));
     }
     return ASH_OK;
@@ -420,7 +432,9 @@ static int bloom_down(ashcuda_ctx* c, uint32_t mips) {          // D_k = downsam
 static int bloom_up(ashcuda_ctx* c, const AshBloomParams* bp, int last) {   // U_k = D_k + upsample(U_{k+1}), k >= last
     BloomChain& b = c->bloom;
     for (int k = (int)bp->mip_count - 1; k >= last; --k) {
-        if (b.up_fast[k]) ASH_CUDA(c, launch_bloom_upsample_fast(b.d[k + 1], b.w[k + 1], b.h[k + 1], b.d[k], bp->upsample_intensity, c->L()));
+        if (c->cfg.fp32_intermediates) ASH_CUDA(c, launch_bloom_upsample_add_f(b.d[k + 1], b.w[k + 1], b.h[k + 1], b.d[k], b.w[k], b.h[k],
+                                                                                  bp->upsample_intensity, 1, c->L()));
+        else if (b.up_fast[k]) ASH_CUDA(c, launch_bloom_upsample_fast(b.d[k + 1], b.w[k + 1], b.h[k + 1], b.d[k], bp->upsample_intensity, c->L()));
         else ASH_CUDA(c, launch_bloom_upsample_add(b.d[k + 1], b.w[k + 1], b.h[k + 1], b.d[k], b.w[k], b.h[k],
                                                    bp->upsample_intensity, c->L()));
     }
@@ -432,8 +446,7 @@ int ashcuda_bloom(ashcuda_ctx* c, const AshBloomParams* bp) {
     if (!c->have_color) return fail(c, ASH_ERR_NOT_INITIALIZED, "bloom: no colour buffer set");
     if (bp->mip_count > c->bloom.mips) return fail(c, ASH_ERR_INVALID, "bloom: mip_count > config bloom_mips");
     ASH_CUDA(c, cudaSetDevice(c->device));
-    BloomChain& b = c->bloom;
-    ASH_CUDA(c, launch_bloom_threshold(resolved_color(c), b.d[0], c->W, c->H, bp->threshold, c->center_exact, c->L()));
+    ASH_CUDA(c, bloom_threshold_any(c, bp->threshold));
     int rc = bloom_down(c, bp->mip_count);
     if (rc) return rc;
     rc = bloom_up(c, bp, 0);
@@ -447,7 +460,9 @@ int ashcuda_tonemap(ashcuda_ctx* c, const AshPostProcessPushConstants* pc) {
     if (!c->have_color) return fail(c, ASH_ERR_NOT_INITIALIZED, "tonemap: no colour buffer set");
     ASH_CUDA(c, cudaSetDevice(c->device));
     const void* bloom = c->bloom_valid ? c->bloom.d[0] : nullptr;
-    if (c->tonemap_op == ASH_TONEMAP_ACES && c->center_exact && ((size_t)c->W * c->H) % 2 == 0)
+    if (c->cfg.fp32_intermediates)
+        ASH_CUDA(c, launch_tonemap_f(resolved_color(c), c->taa_ran ? 1 : 0, bloom, 1, c->ldr8, c->W, c->H, *pc, c->tonemap_op, c->L()));
+    else if (c->tonemap_op == ASH_TONEMAP_ACES && c->center_exact && ((size_t)c->W * c->H) % 2 == 0)
         ASH_CUDA(c, launch_tonemap_fast(resolved_color(c), bloom, c->ldr8, c->W, c->H, *pc, c->L()));
     else        // the operators without a reference shader (PIN-13) run the general kernel
         ASH_CUDA(c, launch_tonemap(resolved_color(c), bloom, c->ldr8, c->W, c->H, *pc, c->center_exact, c->tonemap_op, c->L()));
@@ -479,9 +494,10 @@ static int view_post(ashcuda_ctx* c, const AshCudaViewParams* vp) {
         if (!c->have_color) return fail(c, ASH_ERR_NOT_INITIALIZED, "bloom: no colour buffer set");
         BloomChain& b = c->bloom;
         if (!thr_done)
-            ASH_CUDA(c, launch_bloom_threshold(resolved_color(c), b.d[0], c->W, c->H, vp->bloom.threshold, c->center_exact, c->L()));
+            ASH_CUDA(c, bloom_threshold_any(c, vp->bloom.threshold));
         rc = bloom_down(c, vp->bloom.mip_count); if (rc) return rc;
-        const bool fuse_last = (st & ASH_STAGE_TONEMAP) && vp->bloom.mip_count >= 1 && b.up_fast[0] && c->tonemap_op == ASH_TONEMAP_ACES;
+        const bool fuse_last = (st & ASH_STAGE_TONEMAP) && vp->bloom.mip_count >= 1 && b.up_fast[0] && c->tonemap_op == ASH_TONEMAP_ACES &&
+                               !c->cfg.fp32_intermediates;
         rc = bloom_up(c, &vp->bloom, fuse_last ? 1 : 0); if (rc) return rc;
         if (fuse_last) {
             const bool keep = (st & ASH_STAGE_KEEP_BLOOM) != 0;
@@ -810,7 +826,7 @@ int ashcuda_get(ashcuda_ctx* c, int which, void** dev_ptr, size_t* bytes) {
     if (which >= 0x200 && which <= 0x200 + (int)ASH_MAX_BLOOM_MIPS) {
         const int k = which - 0x200;
         if (!c->cfg.enable_post || k > (int)c->bloom.mips) return fail(c, ASH_ERR_NOT_FOUND, "get: no such bloom mip");
-        p = c->bloom.d[k]; n = (size_t)c->bloom.w[k] * c->bloom.h[k] * 8;
+        p = c->bloom.d[k]; n = (size_t)c->bloom.w[k] * c->bloom.h[k] * (c->cfg.fp32_intermediates ? 16 : 8);
     } else if (which >= 0x100 && which < 0x100 + kMaxMips) {
         const int l = which - 0x100;
         if (l >= c->pyr.levels) return fail(c, ASH_ERR_NOT_FOUND, "get: no such Hi-Z mip");
@@ -821,12 +837,12 @@ int ashcuda_get(ashcuda_ctx* c, int which, void** dev_ptr, size_t* bytes) {
         case ASH_BUF_DRAWS_OUT:       p = c->draws_out; n = (size_t)c->n_objs * sizeof(AshIndirectDrawCommand); break;
         case ASH_BUF_VISIBLE_COUNT:   p = c->visible_count; n = 4; break;
         case ASH_BUF_TILE_DATA:       p = c->tile_data; n = tiles * ASH_TILE_STRIDE * 4; break;
-        case ASH_BUF_TAA_OUT:         p = c->taa[c->taa_cur]; n = P * 8; break;
+        case ASH_BUF_TAA_OUT:         p = c->taa[c->taa_cur]; n = P * (c->cfg.fp32_intermediates ? 16 : 8); break;
         case ASH_BUF_LDR8:            p = c->ldr8; n = P * 4; break;
         case ASH_BUF_STATS:           p = c->stats; n = sizeof(AshViewStats); break;
         case ASH_BUF_TILE_MINMAX:     p = c->tile_minmax; n = tiles * 8; break;
         case ASH_BUF_VISIBILITY_BITS: p = c->vis_bits; n = (((size_t)c->n_objs + 31) / 32) * 4; break;
-        case ASH_BUF_BLOOM_THRESHOLD: p = c->bloom_t; n = P * 8; break;
+        case ASH_BUF_BLOOM_THRESHOLD: p = c->bloom_t; n = P * (c->cfg.fp32_intermediates ? 16 : 8); break;
         case ASH_BUF_LOD_SELECTION:   p = c->lod_sel; n = (size_t)c->n_inst * sizeof(AshLodSelection); break;
         case ASH_BUF_INSTANCES_OUT:   p = c->inst_out; n = (size_t)c->n_inst * sizeof(AshInstanceData); break;
         case ASH_BUF_BUCKET_OFFSETS:  p = c->bucket_offsets; n = ((size_t)c->n_buckets + 1) * 4; break;

@@ -189,7 +189,7 @@ void ash_view_graphs_destroy(ashcuda_ctx* c) {
 int ash_view_run_graph(ashcuda_ctx* c, const AshCudaViewParams* vp, bool* handled) {
     *handled = false;
     const uint32_t st = vp->stages;
-    if (!c->cfg.graph_replay || c->graphs_broken || c->prof.mask != 0) return ASH_OK;
+    if (!c->cfg.graph_replay || c->graphs_broken || c->prof.mask != 0 || c->cfg.fp32_intermediates) return ASH_OK;
     // the TAA node must be the pair kernel (post_fast.cu dispatch: exact taps and (velocity || jitter delta inside the halo))
     const bool shaded = (st & ASH_STAGE_FORWARD_SHADE) != 0;                     // colour made inside the view, no velocity
     if (st & ASH_STAGE_TAA) {

