@@ -214,7 +214,6 @@ struct ashcuda_ctx {
     bool        have_color = false, history_valid = false, taa_ran = false;
     void*       bloom_t = nullptr;             // T = D_0 for the staged path
     ash::BloomChain bloom{};
-    uint32_t* tail_sync = nullptr;       // k_bloom_tail counters (post_tail.cu)
     bool        bloom_valid = false;
     void*       ldr8 = nullptr;
     uint32_t    tonemap_op = ASH_TONEMAP_ACES;  // TonemappingConfig.operator (features/tonemapping.rs:9-20)
@@ -311,10 +310,6 @@ cudaError_t launch_bloom_downsample_box(const void* src, uint32_t sw, uint32_t s
                                         uint32_t dh, const Launch& L);                                     // post_down_box.cu
 cudaError_t launch_bloom_upsample_fast(const void* src, uint32_t sw, uint32_t sh, void* dst, float intensity,
                                        const Launch& L);
-// post_tail.cu: every level below 2^20 texels (D_first .. D_mips, U_{mips-1} .. U_first) as the stages of ONE persistent launch
-constexpr int kTailSyncWords = 2 + 2 * ASH_MAX_BLOOM_MIPS;       // ticket, CTAs gone, finished tiles per stage; zero between launches
-uint32_t bloom_tail_first_level(const BloomChain& b, uint32_t mips);
-cudaError_t launch_bloom_tail(const BloomChain& b, uint32_t mips, uint32_t first_down, float intensity, uint32_t* sync, const Launch& L);
 cudaError_t launch_upsample_tonemap_fast(const void* src, uint32_t sw, uint32_t sh, void* dst, float intensity,
                                          const void* hdr, void* ldr8, const AshPostProcessPushConstants& pc,
                                          bool store_u, const Launch& L);

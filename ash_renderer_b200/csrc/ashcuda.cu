@@ -85,7 +85,7 @@ void ashcuda_destroy(ashcuda_ctx* c) {
                      c->inst_owned, c->inst_batch_owned, c->inst_mesh_owned, c->lod_meshes_owned, c->batch_mesh,
                      c->lod_sel, c->bucket_of, c->cta_hist, c->bucket_offsets, c->bucket_totals, c->inst_out,
                      c->inst_draws, c->inst_stats, c->fwd_keys, c->fwd_spheres, c->fwd_rects, c->fwd_big,
-                     c->fwd_lights_view, c->fwd_rays, c->fwd_consts, c->fwd_late, c->culling_stats, c->tail_sync};
+                     c->fwd_lights_view, c->fwd_rays, c->fwd_consts, c->fwd_late, c->culling_stats};
     for (void* p : owned) if (p) cudaFree(p);
     for (uint32_t k = 1; k <= ASH_MAX_BLOOM_MIPS; ++k) if (c->bloom.d[k]) cudaFree(c->bloom.d[k]);
     c->prof.release_all();
@@ -173,8 +173,6 @@ static int create_impl(ashcuda_ctx* c) {
             b.h[k] = b.h[k - 1] / 2 ? b.h[k - 1] / 2 : 1;
             ASH_CUDA(c, dmalloc(&b.d[k], (size_t)b.w[k] * b.h[k] * texel));
         }
-        ASH_CUDA(c, dmalloc(&c->tail_sync, kTailSyncWords * sizeof(uint32_t)));
-        ASH_CUDA(c, cudaMemsetAsync(c->tail_sync, 0, kTailSyncWords * sizeof(uint32_t), c->stream));
         // which levels may run the fast kernels: every sampler shortcut is validated here, per extent
         c->center_exact = axis_center_exact((int)W, (float)W) && axis_center_exact((int)H, (float)H);
         for (uint32_t k = 0; k <= ASH_MAX_BLOOM_MIPS; ++k) b.down_fast[k] = b.up_fast[k] = false;
@@ -421,9 +419,16 @@ static cudaError_t bloom_threshold_any(ashcuda_ctx* c, float threshold) {
     return launch_bloom_threshold(resolved_color(c), b.d[0], c->W, c->H, threshold, c->center_exact, c->L());
 }
 
-static int bloom_down(ashcuda_ctx* c, uint32_t first, uint32_t last) {          // D_k = downsample(D_{k-1}), k = first .. last, PIN-9
+// One launch per level.  Collapsing the levels below 2^20 (or 2^18) texels into the stages of ONE persistent kernel — tiles
+// handed out by an atomic ticket in stage order, a stage waiting on the finished-tile count of the one before, the same
+// tile functions — was built and measured (commit eb64929, 'k_bloom_tail'): bit-identical, 20 -> 14 (16) launches per view,
+// and SLOWER on both counts: 6355 -> 5300 (5750..5930) views/s, because CTAs that wait for a stage hold registers the other
+// views' kernels would use, and single-view latency 0.206 -> 0.222 (0.217) ms, because a kernel boundary inside a CUDA
+// graph (~4.4 us per small level, launch to launch) is cheaper than ticket + acquire poll + fence + release (~6.6 us per
+// stage).  DESIGN.md section 5b has the table.
+static int bloom_down(ashcuda_ctx* c, uint32_t mips) {          // D_k = downsample(D_{k-1}), PIN-9
     BloomChain& b = c->bloom;
-    for (uint32_t k = first; k <= last; ++k) {
+    for (uint32_t k = 1; k <= mips; ++k) {
         if (c->cfg.fp32_intermediates) ASH_CUDA(c, launch_bloom_downsample_f(b.d[k - 1], b.w[k - 1], b.h[k - 1], b.d[k], b.w[k], b.h[k], 1, c->L()));
         else if (b.down_fast[k]) ASH_CUDA(c, launch_bloom_downsample_fast(b.d[k - 1], b.w[k - 1], b.h[k - 1], b.d[k], b.w[k], b.h[k], c->L()));
         else ASH_CUDA(c, launch_bloom_downsample(b.d[k - 1], b.w[k - 1], b.h[k - 1], b.d[k], b.w[k], b.h[k], c->L()));
@@ -431,9 +436,9 @@ static int bloom_down(ashcuda_ctx* c, uint32_t first, uint32_t last) {          
     return ASH_OK;
 }
 
-static int bloom_up(ashcuda_ctx* c, const AshBloomParams* bp, int first, int last) {   // U_k = D_k + upsample(U_{k+1}), k = first .. last (descending)
+static int bloom_up(ashcuda_ctx* c, const AshBloomParams* bp, int last) {   // U_k = D_k + upsample(U_{k+1}), k >= last
     BloomChain& b = c->bloom;
-    for (int k = first; k >= last; --k) {
+    for (int k = (int)bp->mip_count - 1; k >= last; --k) {
         if (c->cfg.fp32_intermediates) ASH_CUDA(c, launch_bloom_upsample_add_f(b.d[k + 1], b.w[k + 1], b.h[k + 1], b.d[k], b.w[k], b.h[k],
                                                                                   bp->upsample_intensity, 1, c->L()));
         else if (b.up_fast[k]) ASH_CUDA(c, launch_bloom_upsample_fast(b.d[k + 1], b.w[k + 1], b.h[k + 1], b.d[k], bp->upsample_intensity, c->L()));
@@ -443,31 +448,15 @@ static int bloom_up(ashcuda_ctx* c, const AshBloomParams* bp, int first, int las
     return ASH_OK;
 }
 
-#ifndef ASH_BLOOM_TAIL          // 0: every level its own launch (the A/B of DESIGN.md section 5b)
-#define ASH_BLOOM_TAIL 0
-#endif
-// D_1 .. D_mips, then U_{mips-1} .. U_last.  The levels below 2^20 texels run as the stages of one launch (post_tail.cu):
-// the same tile functions, the same texels.
-static int bloom_levels(ashcuda_ctx* c, const AshBloomParams* bp, int last) {
-    const uint32_t mips = bp->mip_count;
-    const uint32_t tail = (ASH_BLOOM_TAIL && !c->cfg.fp32_intermediates) ? bloom_tail_first_level(c->bloom, mips) : 0u;
-    if (!tail) {
-        int rc = bloom_down(c, 1, mips);
-        return rc ? rc : bloom_up(c, bp, (int)mips - 1, last);
-    }
-    int rc = bloom_down(c, 1, tail - 1);
-    if (rc) return rc;
-    ASH_CUDA(c, launch_bloom_tail(c->bloom, mips, tail, bp->upsample_intensity, c->tail_sync, c->L()));
-    return bloom_up(c, bp, (int)tail - 1, last);
-}
-
 int ashcuda_bloom(ashcuda_ctx* c, const AshBloomParams* bp) {
     if (!c || !bp) return fail(c, ASH_ERR_INVALID, "bloom: null");
     if (!c->have_color) return fail(c, ASH_ERR_NOT_INITIALIZED, "bloom: no colour buffer set");
     if (bp->mip_count > c->bloom.mips) return fail(c, ASH_ERR_INVALID, "bloom: mip_count > config bloom_mips");
     ASH_CUDA(c, cudaSetDevice(c->device));
     ASH_CUDA(c, bloom_threshold_any(c, bp->threshold));
-    int rc = bloom_levels(c, bp, 0);
+    int rc = bloom_down(c, bp->mip_count);
+    if (rc) return rc;
+    rc = bloom_up(c, bp, 0);
     if (rc) return rc;
     c->bloom_valid = true;
     return ASH_OK;
@@ -513,9 +502,10 @@ static int view_post(ashcuda_ctx* c, const AshCudaViewParams* vp) {
         BloomChain& b = c->bloom;
         if (!thr_done)
             ASH_CUDA(c, bloom_threshold_any(c, vp->bloom.threshold));
+        rc = bloom_down(c, vp->bloom.mip_count); if (rc) return rc;
         const bool fuse_last = (st & ASH_STAGE_TONEMAP) && vp->bloom.mip_count >= 1 && b.up_fast[0] && c->tonemap_op == ASH_TONEMAP_ACES &&
                                !c->cfg.fp32_intermediates;
-        rc = bloom_levels(c, &vp->bloom, fuse_last ? 1 : 0); if (rc) return rc;
+        rc = bloom_up(c, &vp->bloom, fuse_last ? 1 : 0); if (rc) return rc;
         if (fuse_last) {
             const bool keep = (st & ASH_STAGE_KEEP_BLOOM) != 0;
             ASH_CUDA(c, launch_upsample_tonemap_fast(b.d[1], b.w[1], b.h[1], b.d[0], vp->bloom.upsample_intensity,

@@ -112,7 +112,22 @@ __global__ void __launch_bounds__(256)
 k_bloom_downsample(Tex16 src, uint2* __restrict__ dst, int dw, int dh) {
     const int x = blockIdx.x * 32 + (threadIdx.x & 31), y = blockIdx.y * 8 + (threadIdx.x >> 5);
     if (x >= dw || y >= dh) return;
-    dst[(size_t)y * dw + x] = bloom_downsample_texel<true>(src, x, y, dw, dh);
+    const float dx = fdiv(1.0f, (float)src.W), dy = fdiv(1.0f, (float)src.H);              // texelSize, :11
+    const float u = fdiv(fadd((float)x, 0.5f), (float)dw), v = fdiv(fadd((float)y, 0.5f), (float)dh);
+    // tap order centre,a,b,c,d,e,f,g,h (:22-34), weights (:87-101)
+    const float ou[9] = {0.0f, -dx, dx, -dx, dx, -dx, dx, 0.0f, 0.0f};
+    const float ov[9] = {0.0f, -dy, -dy, dy, dy, 0.0f, 0.0f, -dy, dy};
+    const float wt[9] = {0.25f, 0.0625f, 0.0625f, 0.0625f, 0.0625f, 0.125f, 0.125f, 0.125f, 0.125f};
+    V3 res = {0.0f, 0.0f, 0.0f};
+    float sum = 0.0f;
+#pragma unroll
+    for (int k = 0; k < 9; ++k) {
+        const V3 s = rgb(texture16(src, fadd(u, ou[k]), fadd(v, ov[k])));
+        const float w = fdiv(1.0f, fadd(1.0f, dot3(s, v3(0.2126f, 0.7152f, 0.0722f))));
+        res = add3(res, scale3(scale3(s, w), wt[k]));
+        sum = fadd(sum, fmul(w, wt[k]));
+    }
+    dst[(size_t)y * dw + x] = pack_rgba16f(fdiv(res.x, sum), fdiv(res.y, sum), fdiv(res.z, sum), 1.0f);   // :107
 }
 
 cudaError_t launch_bloom_downsample(const void* src, uint32_t sw, uint32_t sh, void* dst, uint32_t dw,
@@ -129,7 +144,24 @@ __global__ void __launch_bounds__(256)
 k_bloom_upsample_add(Tex16 src, uint2* __restrict__ dst, int dw, int dh, float intensity) {
     const int x = blockIdx.x * 32 + (threadIdx.x & 31), y = blockIdx.y * 8 + (threadIdx.x >> 5);
     if (x >= dw || y >= dh) return;
-    dst[(size_t)y * dw + x] = bloom_upsample_add_texel<true>(src, dst[(size_t)y * dw + x], x, y, dw, dh, intensity);
+    const float dx = fmul(fdiv(1.0f, (float)src.W), 0.5f), dy = fmul(fdiv(1.0f, (float)src.H), 0.5f);   // :18
+    const float u = fdiv(fadd((float)x, 0.5f), (float)dw), v = fdiv(fadd((float)y, 0.5f), (float)dh);
+    const V3 s0 = rgb(texture16(src, fadd(u, fmul(-dx, 2.0f)), fadd(v, 0.0f)));            // :21-29
+    const V3 s1 = rgb(texture16(src, fadd(u, -dx), fadd(v, -dy)));
+    const V3 s2 = rgb(texture16(src, fadd(u, 0.0f), fadd(v, fmul(-dy, 2.0f))));
+    const V3 s3 = rgb(texture16(src, fadd(u, dx), fadd(v, -dy)));
+    const V3 s4 = rgb(texture16(src, fadd(u, fmul(dx, 2.0f)), fadd(v, 0.0f)));
+    const V3 s5 = rgb(texture16(src, fadd(u, dx), fadd(v, dy)));
+    const V3 s6 = rgb(texture16(src, fadd(u, 0.0f), fadd(v, fmul(dy, 2.0f))));
+    const V3 s7 = rgb(texture16(src, fadd(u, -dx), fadd(v, dy)));
+    const V3 s8 = rgb(texture16(src, u, v));
+    V3 r = scale3(s8, 4.0f);                                                               // :32-38
+    r = add3(r, scale3(add3(add3(add3(s1, s3), s5), s7), 2.0f));
+    r = add3(r, add3(add3(add3(s0, s2), s4), s6));
+    r = divs3(r, 16.0f);
+    r = scale3(r, intensity);
+    const V4 d = unpack_rgba16f(dst[(size_t)y * dw + x]);
+    dst[(size_t)y * dw + x] = pack_rgba16f(fadd(r.x, d.x), fadd(r.y, d.y), fadd(r.z, d.z), 1.0f);
 }
 
 cudaError_t launch_bloom_upsample_add(const void* src, uint32_t sw, uint32_t sh, void* dst, uint32_t dw,

@@ -7,31 +7,17 @@ namespace ash {
 
 struct Tex16 { const uint2* p; int W, H; };
 
-// NC = true: the texture is read-only for the lifetime of the kernel (ld.global.nc).  NC = false: the texels were
-// written earlier in the SAME launch by another CTA (k_bloom_tail, post_tail.cu): a plain coherent load, ordered after
-// the stage's acquire.
-template <bool NC> __device__ __forceinline__ uint2 ld_texel(const uint2* p) {
-    if (NC) return __ldg(p);
-    uint2 v; asm volatile("ld.global.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "l"(p) : "memory"); return v;
-}
-template <bool NC> __device__ __forceinline__ uint4 ld_texel2(const uint4* p) {
-    if (NC) return __ldg(p);
-    uint4 v; asm volatile("ld.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory"); return v;
-}
-template <bool NC = true>
 __device__ __forceinline__ V4 fetch16(const Tex16& t, int x, int y) {
-    return unpack_rgba16f(ld_texel<NC>(t.p + (size_t)y * t.W + x));
+    return unpack_rgba16f(__ldg(t.p + (size_t)y * t.W + x));
 }
-template <bool NC = true>
 __device__ __forceinline__ V4 fetch16_clamped(const Tex16& t, int x, int y) {
-    return fetch16<NC>(t, min(max(x, 0), t.W - 1), min(max(y, 0), t.H - 1));
+    return fetch16(t, min(max(x, 0), t.W - 1), min(max(y, 0), t.H - 1));
 }
-template <bool NC = true>
 __device__ __forceinline__ V4 texture16(const Tex16& t, float u, float v) {
     int x0, x1, y0, y1; float fx, fy;
     bilinear_setup(u, t.W, x0, x1, fx);
     bilinear_setup(v, t.H, y0, y1, fy);
-    const V4 a = fetch16<NC>(t, x0, y0), b = fetch16<NC>(t, x1, y0), c = fetch16<NC>(t, x0, y1), d = fetch16<NC>(t, x1, y1);
+    const V4 a = fetch16(t, x0, y0), b = fetch16(t, x1, y0), c = fetch16(t, x0, y1), d = fetch16(t, x1, y1);
     const V4 top = {lerp1(a.x, b.x, fx), lerp1(a.y, b.y, fx), lerp1(a.z, b.z, fx), lerp1(a.w, b.w, fx)};
     const V4 bot = {lerp1(c.x, d.x, fx), lerp1(c.y, d.y, fx), lerp1(c.z, d.z, fx), lerp1(c.w, d.w, fx)};
     return {lerp1(top.x, bot.x, fy), lerp1(top.y, bot.y, fy), lerp1(top.z, bot.z, fy), lerp1(top.w, bot.w, fy)};
@@ -93,50 +79,6 @@ __device__ __forceinline__ float tonemap_curve(float x, uint32_t op) {
 }
 __device__ __forceinline__ uint32_t to_unorm8(float l) {
     return (uint32_t)floorf(fadd(fmul(gclamp(l, 0.0f, 1.0f), 255.0f), 0.5f));
-}
-
-// ---------------------------------------------------------------- bloom levels, one texel, any pair of extents
-// bloom_downsample.frag:16-108: the stored texel of destination pixel (x, y)
-template <bool NC>
-__device__ __forceinline__ uint2 bloom_downsample_texel(const Tex16& src, int x, int y, int dw, int dh) {
-    const float dx = fdiv(1.0f, (float)src.W), dy = fdiv(1.0f, (float)src.H);              // texelSize, :11
-    const float u = fdiv(fadd((float)x, 0.5f), (float)dw), v = fdiv(fadd((float)y, 0.5f), (float)dh);
-    // tap order centre,a,b,c,d,e,f,g,h (:22-34), weights (:87-101)
-    const float ou[9] = {0.0f, -dx, dx, -dx, dx, -dx, dx, 0.0f, 0.0f};
-    const float ov[9] = {0.0f, -dy, -dy, dy, dy, 0.0f, 0.0f, -dy, dy};
-    const float wt[9] = {0.25f, 0.0625f, 0.0625f, 0.0625f, 0.0625f, 0.125f, 0.125f, 0.125f, 0.125f};
-    V3 res = {0.0f, 0.0f, 0.0f};
-    float sum = 0.0f;
-#pragma unroll
-    for (int k = 0; k < 9; ++k) {
-        const V3 s = rgb(texture16<NC>(src, fadd(u, ou[k]), fadd(v, ov[k])));
-        const float w = fdiv(1.0f, fadd(1.0f, dot3(s, v3(0.2126f, 0.7152f, 0.0722f))));
-        res = add3(res, scale3(scale3(s, w), wt[k]));
-        sum = fadd(sum, fmul(w, wt[k]));
-    }
-    return pack_rgba16f(fdiv(res.x, sum), fdiv(res.y, sum), fdiv(res.z, sum), 1.0f);      // :107
-}
-// bloom_upsample.frag:16-41 + the additive blend (PIN-9): the stored texel of destination pixel (x, y), `below` = its current value
-template <bool NC>
-__device__ __forceinline__ uint2 bloom_upsample_add_texel(const Tex16& src, uint2 below, int x, int y, int dw, int dh, float intensity) {
-    const float dx = fmul(fdiv(1.0f, (float)src.W), 0.5f), dy = fmul(fdiv(1.0f, (float)src.H), 0.5f);   // :18
-    const float u = fdiv(fadd((float)x, 0.5f), (float)dw), v = fdiv(fadd((float)y, 0.5f), (float)dh);
-    const V3 s0 = rgb(texture16<NC>(src, fadd(u, fmul(-dx, 2.0f)), fadd(v, 0.0f)));            // :21-29
-    const V3 s1 = rgb(texture16<NC>(src, fadd(u, -dx), fadd(v, -dy)));
-    const V3 s2 = rgb(texture16<NC>(src, fadd(u, 0.0f), fadd(v, fmul(-dy, 2.0f))));
-    const V3 s3 = rgb(texture16<NC>(src, fadd(u, dx), fadd(v, -dy)));
-    const V3 s4 = rgb(texture16<NC>(src, fadd(u, fmul(dx, 2.0f)), fadd(v, 0.0f)));
-    const V3 s5 = rgb(texture16<NC>(src, fadd(u, dx), fadd(v, dy)));
-    const V3 s6 = rgb(texture16<NC>(src, fadd(u, 0.0f), fadd(v, fmul(dy, 2.0f))));
-    const V3 s7 = rgb(texture16<NC>(src, fadd(u, -dx), fadd(v, dy)));
-    const V3 s8 = rgb(texture16<NC>(src, u, v));
-    V3 r = scale3(s8, 4.0f);                                                               // :32-38
-    r = add3(r, scale3(add3(add3(add3(s1, s3), s5), s7), 2.0f));
-    r = add3(r, add3(add3(add3(s0, s2), s4), s6));
-    r = divs3(r, 16.0f);
-    r = scale3(r, intensity);
-    const V4 d = unpack_rgba16f(below);
-    return pack_rgba16f(fadd(r.x, d.x), fadd(r.y, d.y), fadd(r.z, d.z), 1.0f);
 }
 
 // ---------------------------------------------------------------- 1:2 tent upsample tap tables (bloom_upsample.frag:16-41, PIN-9)

@@ -38,36 +38,10 @@ __device__ __forceinline__ P2 rcp_abs(P2 x) { return pk(rcp(fabsf(lo(x))), rcp(f
 struct V3P { P2 x, y, z; };
 __device__ __forceinline__ V3P pk3(V3 a, V3 b) { return {pk(a.x, b.x), pk(a.y, b.y), pk(a.z, b.z)}; }
 
-#ifndef ASH_TOL_RCP3
-#define ASH_TOL_RCP3 1
-#endif
-// (1/x, 1/y, 1/z) from ONE reciprocal: r = 1/(xyz), 1/z = r xy, 1/(xy) = r z, 1/x = y/(xy), 1/y = x/(xy).  MUFU.RCP is a
-// scalar, quarter-rate instruction (8 issue cycles of the SFU per warp) and was 9 % of the kernel's instructions; the six
-// packed multiplies that replace two of every three cost 12 cycles of the FMA pipe for BOTH pixels of a pair.  Callers
-// guarantee xyz is a normal fp32 number (every use below: factors in [1e-4, 65505]); 4 roundings instead of 1.
-__device__ __forceinline__ V3P rcp3(V3P d) {
-#if ASH_TOL_RCP3
-    const P2 xy = mul(d.x, d.y);
-    const P2 r = rcp(mul(xy, d.z));
-    const P2 t = mul(r, d.z);
-    return {mul(t, d.y), mul(t, d.x), mul(r, xy)};
-#else
-    return {rcp(d.x), rcp(d.y), rcp(d.z)};
-#endif
-}
-__device__ __forceinline__ V3 rcp3(V3 d) {
-#if ASH_TOL_RCP3
-    const float xy = d.x * d.y, r = rcp(xy * d.z), t = r * d.z;
-    return {t * d.y, t * d.x, r * xy};
-#else
-    return {rcp(d.x), rcp(d.y), rcp(d.z)};
-#endif
-}
 // c / (1 + c)                                                               taa_resolve.comp:55-57
 __device__ __forceinline__ V3P tonemap(V3P c) {
     const P2 one = splat(1.0f);
-    const V3P r = rcp3(V3P{add(c.x, one), add(c.y, one), add(c.z, one)});
-    return {mul(c.x, r.x), mul(c.y, r.y), mul(c.z, r.z)};
+    return {mul(c.x, rcp(add(c.x, one))), mul(c.y, rcp(add(c.y, one))), mul(c.z, rcp(add(c.z, one)))};
 }
 // (0.25 r + 0.5 g + 0.25 b, 0.5 r - 0.5 b, -0.25 r + 0.5 g - 0.25 b)        :34-40
 __device__ __forceinline__ V3P rgb_to_ycocg(V3P c) {
@@ -186,8 +160,7 @@ __device__ __forceinline__ void tol_stage(const Tex16& cur, const Tex16& hist, f
         }
         if (extra) {
             const V3 q = tol_unpack(ec);
-            const V3 r = rcp3(V3{1.0f + q.x, 1.0f + q.y, 1.0f + q.z});
-            const V3 t = {q.x * r.x, q.y * r.y, q.z * r.z};
+            const V3 t = {q.x * rcp(1.0f + q.x), q.y * rcp(1.0f + q.y), q.z * rcp(1.0f + q.z)};
             s_nb[ey][ex] = tol_nb_record(t.x + t.z, 0.5f * t.y, t.x - t.z);
         }
     }
@@ -224,21 +197,12 @@ __device__ __forceinline__ void tol_finish_pair(tol::V3P h, tol::V3P cp, bool cl
         const V3P half = {fma(sub(mx.x, mn.x), e125, eps), fma(sub(mx.y, mn.y), e125, eps), fma(sub(mx.z, mn.z), e125, eps)};
         const V3P hy = rgb_to_ycocg(tonemap(h));
         const V3P dl = {sub(hy.x, ctr.x), sub(hy.y, ctr.y), sub(hy.z, ctr.z)};
-#if ASH_TOL_RCP3
-        // s = 1 / max(1, maxV), maxV = max_i |delta_i| / half_i (:68-76; half_i in [0.001, 2]): 1 inside the box (history kept)
-        const V3P rh = rcp3(half);
-        const P2 vx = mul(dl.x, rh.x), vy = mul(dl.y, rh.y), vz = mul(dl.z, rh.z);
-        const P2 s = pk(rcp(fmaxf(fmaxf(fmaxf(fabsf(lo(vx)), fabsf(lo(vy))), fabsf(lo(vz))), 1.0f)),
-                        rcp(fmaxf(fmaxf(fmaxf(fabsf(hi(vx)), fabsf(hi(vy))), fabsf(hi(vz))), 1.0f)));
-#else
         // s = min(1, min_i half_i / |delta_i|): 1 inside the box (history kept), 1 / maxV outside (:68-76)
         const P2 sx = mul(half.x, rcp_abs(dl.x)), sy = mul(half.y, rcp_abs(dl.y)), sz = mul(half.z, rcp_abs(dl.z));
         const P2 s = pk(fminf(fminf(fminf(lo(sx), lo(sy)), lo(sz)), 1.0f), fminf(fminf(fminf(hi(sx), hi(sy)), hi(sz)), 1.0f));
-#endif
         const V3P q = ycocg_to_rgb(V3P{fma(dl.x, s, ctr.x), fma(dl.y, s, ctr.y), fma(dl.z, s, ctr.z)});
         const P2 k1 = splat(1.0001f);                                                                // (1 - c) + 1e-4, :59-61
-        const V3P rq = rcp3(V3P{sub(k1, q.x), sub(k1, q.y), sub(k1, q.z)});                          // q in [0, 1): factors in [1e-4, 1.0001]
-        h = {mul(q.x, rq.x), mul(q.y, rq.y), mul(q.z, rq.z)};
+        h = {mul(q.x, rcp(sub(k1, q.x))), mul(q.y, rcp(sub(k1, q.y))), mul(q.z, rcp(sub(k1, q.z)))};
     }
     const V3P o = {fma(h.x, b2, mul(cp.x, ib2)), fma(h.y, b2, mul(cp.y, ib2)), fma(h.z, b2, mul(cp.z, ib2))};       // mix(), :159
     const uint2 oa = pack_rgba16f(lo(o.x), lo(o.y), lo(o.z), one), ob = pack_rgba16f(hi(o.x), hi(o.y), hi(o.z), one);
@@ -338,6 +302,9 @@ k_taa_tol(Tex16 cur, Tex16 hist, uint2* __restrict__ out, uint2* __restrict__ th
     }
 }
 
+// One MUFU.RCP per colour TRIPLE (r = 1/(xyz), 1/x = r yz, ...: 13.8 -> 6.3 reciprocals per pixel, SFU 43 % -> 19 % busy, six
+// packed multiplies per pair in exchange; commit eb64929) was measured SLOWER: 70.8 vs 68.5 us.  The kernel waits on
+// dependent chains, not on the SFU: the longer chain in front of every reciprocal costs more than the issue slots freed.
 // A persistent, cp.async double-buffered variant of this kernel (tile t + 1's raw texels travelling into a second
 // shared-memory stage while tile t is resolved; commit 'k_taa_tol_pipe') was measured SLOWER: 81.9 vs 75.7 us at 4K.
 // It hides the DRAM wait at the head of each CTA (27 % of the stall samples here) but pays 12 % more instructions

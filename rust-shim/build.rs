@@ -9,7 +9,7 @@ fn main() {
     let nvcc = env::var("NVCC").unwrap_or_else(|_| "/usr/local/cuda/bin/nvcc".into());
     // the SRCS list of ash_renderer_b200/csrc/Makefile
     let sources = ["ashcuda.cu", "depth_pyramid.cu", "occlusion_cull.cu", "cull_compact_static.cu", "light_cull.cu", "post.cu", "post_f32.cu", "post_fast.cu", "post_pair.cu", "post_taa_tol.cu",
-                   "post_up_pair.cu", "post_down_box.cu", "post_tail.cu", "instancing.cu", "forward.cu", "compute_utils.cu", "view_graph.cu", "exact_taps.cu"];
+                   "post_up_pair.cu", "post_down_box.cu", "instancing.cu", "forward.cu", "compute_utils.cu", "view_graph.cu", "exact_taps.cu"];
     let mut objects = Vec::new();
     for s in sources {
         let obj = out.join(s).with_extension("o");
