@@ -83,9 +83,7 @@ void cull_patch(const AshCullingPushConstants& pc, int mode, PatchArg* out);    
 void taa_pair_patch(bool thresh, bool vel, const AshTaaPushConstants& pc, PatchArg* out);           // post_pair.cu
 // per-view argument block of k_taa_tol (post_taa_tol.cu, precision = FAST).  regular: the host verified that the history
 // taps of every column / row are texels clamp(p + d), clamp(p + d + 1) with one weight per axis (exact_taps.cu)
-// tma: the persistent TMA-fed kernel (k_taa_tma) runs instead of k_taa_tol<., true>: regular taps and an image TMA can address
-struct TaaTolArgs { AshTaaPushConstants pc; int dx, dy; float fx, fy, blend, threshold; uint32_t regular, tma; };
-struct TmapSlot { const void* img; alignas(64) unsigned char map[128]; };        // a CUtensorMap of one RGBA16F image (post_taa_tol.cu)
+struct TaaTolArgs { AshTaaPushConstants pc; int dx, dy; float fx, fy, blend, threshold; uint32_t regular; };
 void taa_tol_patch(bool thresh, const TaaTolArgs& a, PatchArg* out);                                // post_taa_tol.cu
 bool taa_in_halo(const AshTaaPushConstants& pc);                                                     // post_fast.cu
 void lod_patch(const AshInstancingParams& ip, const AshLodConfig& cfg, PatchArg* out);               // instancing.cu
@@ -222,7 +220,6 @@ struct ashcuda_ctx {
     bool        center_exact = false;          // (x+0.5)/W taps hit texel x exactly (exact_taps.cu)
     float       taa_chk[4] = {0, 0, 0, 0};     // screen_params the TAA tap check was last run for
     bool        taa_exact = false;
-    std::vector<ash::TmapSlot> tmaps;          // k_taa_tma: tensor maps of the colour input and the two history / output targets
     std::vector<ash::TaaTolArgs> tol_plans;    // precision = FAST: history-tap plans by push constants (a Halton period has 16)
 };
 
@@ -304,9 +301,7 @@ cudaError_t launch_taa_fast(const void* cur, const void* hist, const void* vel_o
 cudaError_t launch_taa_pair(const void* cur, const void* hist, const void* vel_or_null, void* out, void* thr_or_null,
                             const AshTaaPushConstants& pc, float threshold, const Launch& L);
 cudaError_t launch_taa_tol(const void* cur, const void* hist, void* out, void* thr_or_null, const TaaTolArgs& a,
-                           const Launch& L);
-bool taa_tma_usable(uint32_t W, const void* color);
-cudaError_t launch_taa_tma(ashcuda_ctx* c, const void* cur, const void* hist, void* out, void* thr_or_null, const TaaTolArgs& a, const Launch& L);                                                                 // post_taa_tol.cu (precision = FAST)
+                           const Launch& L);                                                                 // post_taa_tol.cu (precision = FAST)
 cudaError_t launch_bloom_downsample_fast(const void* src, uint32_t sw, uint32_t sh, void* dst, uint32_t dw,
                                          uint32_t dh, const Launch& L);
 cudaError_t launch_bloom_downsample_pair(const void* src, uint32_t sw, uint32_t sh, void* dst, uint32_t dw,

@@ -386,9 +386,7 @@ static int taa_resolve_impl(ashcuda_ctx* c, const AshTaaPushConstants* pc, void*
         ASH_CUDA(c, launch_taa_f(c->color, 0, hist, c->history_valid ? 1 : 0, c->velocity, out, 1, *pc, c->L()));
     } else if (exact && c->cfg.precision == ASH_PRECISION_FAST && !c->velocity && taa_in_halo(*pc)) {
         TaaTolArgs ta;
-        ash_taa_tol_plan(c, *pc, threshold, &ta);                                                 // post_taa_tol.cu
-        if (ta.tma) ASH_CUDA(c, launch_taa_tma(c, c->color, hist, out, thr_or_null, ta, c->L()));
-        else ASH_CUDA(c, launch_taa_tol(c->color, hist, out, thr_or_null, ta, c->L()));
+        ASH_CUDA(c, launch_taa_tol(c->color, hist, out, thr_or_null, ash_taa_tol_plan(c, *pc, threshold, &ta), c->L()));   // post_taa_tol.cu
         *fused = thr_or_null != nullptr;
     } else if (exact) {
         ASH_CUDA(c, launch_taa_fast(c->color, hist, c->velocity, out, thr_or_null, *pc, threshold, c->L()));

@@ -121,11 +121,7 @@ using namespace ash;
 // taps runs once per distinct (screenParams, jitter, prevJitter) and is cached (a Halton period has 16 of them)
 const TaaTolArgs& ash_taa_tol_plan(ashcuda_ctx* c, const AshTaaPushConstants& pc, float threshold, TaaTolArgs* scratch) {
     for (TaaTolArgs& p : c->tol_plans)
-        if (memcmp(&p.pc, &pc, sizeof(pc)) == 0) {
-            *scratch = p; scratch->threshold = threshold;
-            scratch->tma = (p.regular && taa_tma_usable(c->W, c->color)) ? 1u : 0u;       // depends on the colour buffer set now: not cached
-            return *scratch;
-        }
+        if (memcmp(&p.pc, &pc, sizeof(pc)) == 0) { *scratch = p; scratch->threshold = threshold; return *scratch; }
     TaaTolArgs a{};
     a.pc = pc;
     a.blend = taa_uniform_blend(pc);
@@ -135,7 +131,6 @@ const TaaTolArgs& ash_taa_tol_plan(ashcuda_ctx* c, const AshTaaPushConstants& pc
     if (c->tol_plans.size() >= 64) c->tol_plans.erase(c->tol_plans.begin());
     c->tol_plans.push_back(a);
     *scratch = a; scratch->threshold = threshold;
-    scratch->tma = (a.regular && taa_tma_usable(c->W, c->color)) ? 1u : 0u;
     return *scratch;
 }
 

@@ -22,7 +22,6 @@
 //   * history: raw fp16 tile + halo in shared memory, four taps per pixel through the per-tile coordinate tables.
 #include <algorithm>
 #include <cstring>
-#include <cuda.h>
 #include "ash_f32x2.cuh"
 #include "post_math.cuh"
 
@@ -303,155 +302,14 @@ k_taa_tol(Tex16 cur, Tex16 hist, uint2* __restrict__ out, uint2* __restrict__ th
     }
 }
 
-// =====================================================================================================
-// k_taa_tma: the REGULAR kernel above as a persistent CTA whose tiles arrive by TMA.
-//
-// ncu on k_taa_tol: the largest stall is the long scoreboard at the head of each CTA — every CTA starts with a DRAM round
-// trip that only the other resident CTAs can cover, and the register file caps those at 7.  Here a CTA walks tiles
-// blockIdx.x, + gridDim.x, ...; ONE thread issues two cp.async.bulk.tensor copies per tile (`current` and history, tile +
-// halo, 36 x 18 texels = 5184 bytes each) that complete on an mbarrier, and the copies of tile i + 1 are in
-// flight while tile i is resolved.  No thread computes a global load address or stores a raw texel to shared memory.
-// Two stages of (`current`, history): the copies of tile i + 1 are issued at the top of iteration i and have the whole
-// tile to land.  Phase A converts the thread's own `current` texels to fp32 and writes the tonemapped YCoCg of tile +
-// halo into s_nb; phase B is the resolve.
-// TMA fills out-of-image texels with zeros where the shader's sampler clamps to the edge: tiles that touch the border
-// (506 of 16 200 at 4K) rewrite those positions from the clamped position of the same tile before use.
-// Same arithmetic, same operation order as k_taa_tol<THRESH, true>: the outputs are bit-identical to it.
-// =====================================================================================================
-// The box origin of a bulk tensor copy must be 16-byte aligned in the innermost dimension (an odd texel offset traps with
-// "illegal instruction": tools/probe/tma_probe.cu), so the box starts TWO texels left of the tile and is 36 wide: halo
-// column lx of the tile is raw column lx + 1; raw columns 0 and 35 are never read.
-constexpr int kTolRawW = kTolHaloW + 2;
-struct __align__(128) TolRawTile { uint2 t[kTolHaloH][kTolRawW]; };
-constexpr uint32_t kTolRawBytes = kTolHaloH * kTolRawW * 8;
-
-__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
-__device__ __forceinline__ void mbar_init(unsigned long long* bar, uint32_t count) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" :: "r"(smem_u32(bar)), "r"(count) : "memory");
-}
-__device__ __forceinline__ void mbar_wait(unsigned long long* bar, uint32_t parity) {
-    asm volatile(
-        "{\n\t"
-        ".reg .pred P1;\n\t"
-        "TMA_WAIT:\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n\t"
-        "@P1 bra TMA_DONE;\n\t"
-        "bra TMA_WAIT;\n\t"
-        "TMA_DONE:\n\t"
-        "}" :: "r"(smem_u32(bar)), "r"(parity) : "memory");
-}
-// `current` and history of one tile + halo: box origin (x, y) in texels, may be negative / past the extent (zero fill)
-__device__ __forceinline__ void tma_tile_pair(TolRawTile* dc, TolRawTile* dh, const CUtensorMap* mc, const CUtensorMap* mh,
-                                              unsigned long long* bar, int x, int y) {
-    const uint32_t b = smem_u32(bar);
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(b), "r"(2u * kTolRawBytes) : "memory");
-    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
-                 :: "r"(smem_u32(dc)), "l"(mc), "r"(b), "r"(x), "r"(y) : "memory");
-    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
-                 :: "r"(smem_u32(dh)), "l"(mh), "r"(b), "r"(x), "r"(y) : "memory");
-}
-// CLAMP_TO_EDGE on a tile TMA filled with zeros outside the image: in-image positions are read, the others written
-__device__ __forceinline__ void tol_clamp_fixup(TolRawTile& T, int x0, int y0, int W, int H) {
-    for (int e = threadIdx.x; e < kTolHaloH * kTolRawW; e += kTolThreads) {
-        const int ly = e / kTolRawW, lx = e - ly * kTolRawW;
-        const int gx = x0 - 2 + lx, gy = y0 - 1 + ly;
-        if (gx < 0 || gx >= W || gy < 0 || gy >= H)
-            T.t[ly][lx] = T.t[min(max(gy, 0), H - 1) - (y0 - 1)][min(max(gx, 0), W - 1) - (x0 - 2)];
-    }
-}
-
-template <bool THRESH>
-__global__ void __launch_bounds__(kTolThreads, ASH_TOL_CTAS)
-k_taa_tma(const __grid_constant__ CUtensorMap map_cur, const __grid_constant__ CUtensorMap map_hist, uint2* __restrict__ out,
-          uint2* __restrict__ thr, TaaTolArgs a) {
-    using namespace tol;
-    __shared__ TolRawTile s_c[2], s_h[2];                         // stage = tile parity
-    __shared__ float4 s_nb[kTolHaloH][kTolHaloW];
-    __shared__ __align__(8) unsigned long long s_bar[2];          // one per stage: both copies of a tile complete on it
-    const int W = (int)a.pc.screen_params[0], H = (int)a.pc.screen_params[1];
-    const int tiles_x = (W + kTolW - 1) / kTolW, ntiles = tiles_x * ((H + kTolH - 1) / kTolH);
-    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
-    const bool clamp_on = a.pc.params[1] > 0.5f;
-    int tile = blockIdx.x;
-    if (tile >= ntiles) return;
-    if (threadIdx.x == 0) {
-        mbar_init(&s_bar[0], 1); mbar_init(&s_bar[1], 1);
-        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    }
-    __syncthreads();
-    const int step_y = (int)gridDim.x / tiles_x, step_x = (int)gridDim.x - step_y * tiles_x;
-    int cy = tile / tiles_x, cx = tile - cy * tiles_x;
-    if (threadIdx.x == 0) tma_tile_pair(&s_c[0], &s_h[0], &map_cur, &map_hist, &s_bar[0], cx * kTolW - 2, cy * kTolH - 1);
-    float one;                                           // alpha 1.0 kept in ONE register (see k_taa_tol)
-    asm volatile("mov.f32 %0, 0f3F800000;" : "=f"(one));
-    const uint32_t ring = c_tol_ring.v[threadIdx.x];
-    const int ex = (int)(ring & 0xFFu), ey = (int)(ring >> 8);
-    const bool extra = threadIdx.x < kTolExtras;
-
-    for (int i = 0; tile < ntiles; ++i, tile += gridDim.x) {
-        const int st = i & 1;
-        const int x0 = cx * kTolW, y0 = cy * kTolH;
-        int nx = cx + step_x, ny = cy + step_y;
-        if (nx >= tiles_x) { nx -= tiles_x; ++ny; }
-        const bool border = x0 == 0 || y0 == 0 || x0 + kTolW >= W || y0 + kTolH >= H;
-        // the next tile's copies: its stage was last read before the barrier that ended the previous iteration
-        if (threadIdx.x == 0 && tile + (int)gridDim.x < ntiles) {
-            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");      // generic-proxy accesses of the stage before the async writes
-            tma_tile_pair(&s_c[st ^ 1], &s_h[st ^ 1], &map_cur, &map_hist, &s_bar[st ^ 1], nx * kTolW - 2, ny * kTolH - 1);
-        }
-        // ---- phase A: `current` of tile + halo -> own texels as fp32, tonemapped YCoCg into s_nb   (:116-121, once per texel)
-        mbar_wait(&s_bar[st], (uint32_t)((i >> 1) & 1));
-        if (border) { tol_clamp_fixup(s_c[st], x0, y0, W, H); tol_clamp_fixup(s_h[st], x0, y0, W, H); __syncthreads(); }
-        V3 c[kTolS];
-#pragma unroll
-        for (int k = 0; k < kTolS; ++k) c[k] = tol_unpack(s_c[st].t[kTolS * ty + 1 + k][tx + 2]);
-        if (clamp_on) {
-#pragma unroll
-            for (int k = 0; k < kTolP; ++k) {
-                const V3P t = tonemap(pk3(c[k], c[k + kTolP]));
-                const P2 rb = add(t.x, t.z), hg = mul(t.y, splat(0.5f)), df = sub(t.x, t.z);
-                s_nb[kTolS * ty + 1 + k][tx + 1] = tol_nb_record(lo(rb), lo(hg), lo(df));
-                s_nb[kTolS * ty + 1 + kTolP + k][tx + 1] = tol_nb_record(hi(rb), hi(hg), hi(df));
-            }
-            if (extra) {
-                const V3 q = tol_unpack(s_c[st].t[ey][ex + 1]);
-                const V3 t = {q.x * rcp(1.0f + q.x), q.y * rcp(1.0f + q.y), q.z * rcp(1.0f + q.z)};
-                s_nb[ey][ex] = tol_nb_record(t.x + t.z, 0.5f * t.y, t.x - t.z);
-            }
-        }
-        __syncthreads();                                 // s_nb complete
-        // ---- phase B: neighbourhood box, history taps, clip, blend, store, threshold
-        const int x = x0 + tx, yb = y0 + kTolS * ty;
-        if (x < W && yb < H) {
-            V3 mn[kTolS], mx[kTolS];
-            if (clamp_on) tol_neighbourhood(s_nb, tx, ty, mn, mx);
-            const uint32_t o00 = (uint32_t)yb * (uint32_t)W + (uint32_t)x;
-            const P2 b2 = splat(a.blend), ib2 = splat(1.0f - a.blend);              // (from the constant bank, per tile: not carried in registers)
-            const P2 fx2 = splat(a.fx), ifx2 = splat(1.0f - a.fx), fy2 = splat(a.fy), ify2 = splat(1.0f - a.fy);
-            const uint2* hb = &s_h[st].t[kTolS * ty + 1 + a.dy][tx + 2 + a.dx];
-            V3 ta[kTolS + 1], tb[kTolS + 1];
-#pragma unroll
-            for (int j = 0; j < kTolS + 1; ++j) { ta[j] = tol_unpack(hb[j * kTolRawW]); tb[j] = tol_unpack(hb[j * kTolRawW + 1]); }
-            V3P hl[kTolP + 1];
-#pragma unroll
-            for (int j = 0; j < kTolP + 1; ++j) {
-                const V3P ta2 = pk3(ta[j], ta[j + kTolP]), tb2 = pk3(tb[j], tb[j + kTolP]);
-                hl[j] = {fma(tb2.x, fx2, mul(ta2.x, ifx2)), fma(tb2.y, fx2, mul(ta2.y, ifx2)), fma(tb2.z, fx2, mul(ta2.z, ifx2))};
-            }
-#pragma unroll
-            for (int k = 0; k < kTolP; ++k) {
-                if (yb + k >= H) break;
-                const V3P h = {fma(hl[k + 1].x, fy2, mul(hl[k].x, ify2)), fma(hl[k + 1].y, fy2, mul(hl[k].y, ify2)),
-                               fma(hl[k + 1].z, fy2, mul(hl[k].z, ify2))};
-                tol_finish_pair<THRESH>(h, pk3(c[k], c[k + kTolP]), clamp_on, pk3(mn[k], mn[k + kTolP]), pk3(mx[k], mx[k + kTolP]), b2, ib2,
-                                        o00 + (uint32_t)k * (uint32_t)W, o00 + (uint32_t)(k + kTolP) * (uint32_t)W, yb + k + kTolP < H, out, thr, a.threshold, one);
-            }
-        }
-        cx = nx; cy = ny;
-        __syncthreads();                                 // s_nb is rewritten by the next tile's phase A
-    }
-}
-
+// A persistent TMA-fed form (k_taa_tma, commit after eb64929: one thread issues two cp.async.bulk.tensor copies per tile
+// that complete on an mbarrier, tile i + 1 in flight while tile i is resolved; bit-identical outputs) was measured SLOWER
+// as well: 71.8 us under ncu against 64.8.  It does remove the DRAM wait (long scoreboard 2.31 -> 0.91 stalled warps per
+// issue) but executes 14 % more instructions (per-tile coordinates, mbarrier polls, own texels re-read from shared
+// memory) and stalls 0.9 on its two barriers per tile; with both inputs double-buffered (30.8 KB per CTA) 74.4 us and
+// -5.6 % views/s, the shared memory being taken from the other views' kernels.  What bounds this kernel is the length of
+// each warp's dependent chain at 7 warps per scheduler, not the memory system.  (TMA detail learnt on the way: the box
+// origin must be 16-byte aligned in the innermost dimension — tools/probe/tma_probe.cu — hence 36-texel boxes from x0 - 2.)
 // One MUFU.RCP per colour TRIPLE (r = 1/(xyz), 1/x = r yz, ...: 13.8 -> 6.3 reciprocals per pixel, SFU 43 % -> 19 % busy, six
 // packed multiplies per pair in exchange; commit eb64929) was measured SLOWER: 70.8 vs 68.5 us.  The kernel waits on
 // dependent chains, not on the SFU: the longer chain in front of every reciprocal costs more than the issue slots freed.
@@ -459,15 +317,14 @@ k_taa_tma(const __grid_constant__ CUtensorMap map_cur, const __grid_constant__ C
 // shared-memory stage while tile t is resolved; commit 'k_taa_tol_pipe') was measured SLOWER: 81.9 vs 75.7 us at 4K.
 // It hides the DRAM wait at the head of each CTA (27 % of the stall samples here) but pays 12 % more instructions
 // (own texels re-read from shared memory, per-tile address arithmetic in every thread) and a second barrier per tile.
-static const void* tol_kernel(bool thresh, bool regular, bool tma) {
-    if (tma) return thresh ? reinterpret_cast<const void*>(&k_taa_tma<true>) : reinterpret_cast<const void*>(&k_taa_tma<false>);
+static const void* tol_kernel(bool thresh, bool regular) {
     return thresh ? (regular ? reinterpret_cast<const void*>(&k_taa_tol<true, true>) : reinterpret_cast<const void*>(&k_taa_tol<true, false>))
                   : (regular ? reinterpret_cast<const void*>(&k_taa_tol<false, true>) : reinterpret_cast<const void*>(&k_taa_tol<false, false>));
 }
 
-// graph replay: argument 4 of k_taa_tol / k_taa_tma is the per-view TaaTolArgs
+// graph replay: argument 4 of k_taa_tol is the per-view TaaTolArgs
 void taa_tol_patch(bool thresh, const TaaTolArgs& a, PatchArg* out) {
-    out->func = tol_kernel(thresh, a.regular != 0, a.tma != 0);
+    out->func = tol_kernel(thresh, a.regular != 0);
     out->arg_index = 4; out->n_args = 5;
     static_assert(sizeof(TaaTolArgs) <= sizeof(out->value), "PatchArg too small");
     std::memcpy(out->value, &a, sizeof(a));
@@ -479,63 +336,10 @@ cudaError_t launch_taa_tol(const void* cur, const void* hist, void* out, void* t
     uint2* o = static_cast<uint2*>(out);
     uint2* t = static_cast<uint2*>(thr_or_null);
     TaaTolArgs args = a;
-    args.tma = 0;
     void* params[5] = {&c, &h, &o, &t, &args};
     Timed timed(L, thr_or_null ? ASH_KERNEL_TAA_THRESHOLD : ASH_KERNEL_TAA);
     const dim3 grid((W + kTolW - 1) / kTolW, (H + kTolH - 1) / kTolH);
-    return cudaLaunchKernel(tol_kernel(t != nullptr, a.regular != 0, false), grid, dim3(kTolThreads), params, 0, L.s);
-}
-
-// ---- k_taa_tma, host side: tensor maps through the driver entry point the runtime resolves (no link against libcuda)
-#ifndef ASH_TAA_TMA
-#define ASH_TAA_TMA 1
-#endif
-typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
-                                  const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-static EncodeTiledFn encode_tiled() {
-    static const EncodeTiledFn fn = [] {
-        void* p = nullptr;
-        cudaDriverEntryPointQueryResult q = cudaDriverEntryPointSymbolNotFound;
-        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess || q != cudaDriverEntryPointSuccess) p = nullptr;
-        return reinterpret_cast<EncodeTiledFn>(p);
-    }();
-    return fn;
-}
-// the row pitch of an RGBA16F image must be a multiple of 16 bytes and its base 16-byte aligned
-bool taa_tma_usable(uint32_t W, const void* color) {
-    return ASH_TAA_TMA && W % 2u == 0u && reinterpret_cast<uintptr_t>(color) % 16u == 0u && encode_tiled() != nullptr;
-}
-static_assert(sizeof(CUtensorMap) == sizeof(TmapSlot::map), "TmapSlot");
-static const CUtensorMap* tmap_of(ashcuda_ctx* c, const void* img, int W, int H) {
-    for (TmapSlot& s : c->tmaps) if (s.img == img) return reinterpret_cast<const CUtensorMap*>(s.map);
-    TmapSlot s{};
-    s.img = img;
-    const cuuint64_t dim[2] = {(cuuint64_t)W, (cuuint64_t)H}, pitch[1] = {(cuuint64_t)W * 8u};
-    const cuuint32_t box[2] = {(cuuint32_t)kTolRawW, (cuuint32_t)kTolHaloH}, one[2] = {1u, 1u};
-    if (encode_tiled()(reinterpret_cast<CUtensorMap*>(s.map), CU_TENSOR_MAP_DATA_TYPE_UINT64, 2, const_cast<void*>(img), dim, pitch, box, one,
-                       CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
-                       CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS) return nullptr;
-    if (c->tmaps.size() >= 8) c->tmaps.erase(c->tmaps.begin());
-    c->tmaps.push_back(s);
-    return reinterpret_cast<const CUtensorMap*>(c->tmaps.back().map);
-}
-
-cudaError_t launch_taa_tma(ashcuda_ctx* c, const void* cur, const void* hist, void* out, void* thr_or_null, const TaaTolArgs& a, const Launch& L) {
-    const int W = (int)a.pc.screen_params[0], H = (int)a.pc.screen_params[1];
-    const CUtensorMap* mc = tmap_of(c, cur, W, H);
-    CUtensorMap map_cur;
-    if (mc) map_cur = *mc;                                   // (the cache may reallocate on the second lookup)
-    const CUtensorMap* mh = tmap_of(c, hist, W, H);
-    if (!mc || !mh) return cudaErrorInvalidValue;
-    CUtensorMap map_hist = *mh;
-    uint2* o = static_cast<uint2*>(out);
-    uint2* t = static_cast<uint2*>(thr_or_null);
-    TaaTolArgs args = a;
-    void* params[5] = {&map_cur, &map_hist, &o, &t, &args};
-    Timed timed(L, thr_or_null ? ASH_KERNEL_TAA_THRESHOLD : ASH_KERNEL_TAA);
-    const int ntiles = ((W + kTolW - 1) / kTolW) * ((H + kTolH - 1) / kTolH);
-    const int grid = ntiles < 148 * ASH_TOL_CTAS ? ntiles : 148 * ASH_TOL_CTAS;
-    return cudaLaunchKernel(tol_kernel(t != nullptr, true, true), dim3(grid), dim3(kTolThreads), params, 0, L.s);
+    return cudaLaunchKernel(tol_kernel(t != nullptr, a.regular != 0), grid, dim3(kTolThreads), params, 0, L.s);
 }
 
 }  // namespace ash

@@ -63,8 +63,7 @@ GraphKey make_key(const ashcuda_ctx* c, const AshCudaViewParams* vp) {
     }
     if (c->cfg.precision == ASH_PRECISION_FAST && (vp->stages & ASH_STAGE_TAA) && k.in_halo) {   // which k_taa_tol instance the graph holds
         TaaTolArgs ta;
-        ash_taa_tol_plan(const_cast<ashcuda_ctx*>(c), vp->taa, vp->bloom.threshold, &ta);
-        k.tol_variant = 1u + ta.regular + 2u * ta.tma;
+        k.tol_variant = 1u + ash_taa_tol_plan(const_cast<ashcuda_ctx*>(c), vp->taa, vp->bloom.threshold, &ta).regular;
     }
     k.taa_cur = (uint32_t)c->taa_cur; k.history_valid = c->history_valid; k.taa_ran = c->taa_ran;
     k.have_color = c->have_color; k.have_depth = c->have_depth; k.have_instancing = c->have_instancing;
