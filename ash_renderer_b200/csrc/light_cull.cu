@@ -9,12 +9,12 @@
 //     monotone and tile min >= global min, tile max <= global max), so only survivors
 //     ("candidates") are kept, in ascending light index.
 //   k_tile_planes (1 thread per tile): the four side planes of every tile frustum (:71-98), once.
-//   k_light_cells (1 warp per 8x8-tile cell): a conservative prefilter — candidates that provably
+//   k_light_cells (1 CTA per 8x8-tile cell): a conservative prefilter — candidates that provably
 //     fail the shader's test in every tile of the cell are dropped, the rest form the cell's list.
-//   k_light_tiles (1 warp per tile): tile min/max come from the depth pyramid kernel (depth is not
-//     read again); lanes test 32 of the cell's survivors at a time with the shader's exact
-//     predicate (:101-109) and append by ballot + popc prefix, which yields ascending order and
-//     first-256-on-overflow (PIN-7) without atomics.
+//   k_light_tiles (1 CTA per cell, 1 warp per four tiles): tile min/max come from the depth pyramid
+//     kernel (depth is not read again); the cell's survivors are staged in shared memory once, lanes
+//     test 32 of them at a time with the shader's exact predicate (:101-109) and append by ballot +
+//     popc prefix, which yields ascending order and first-256-on-overflow (PIN-7) without atomics.
 //
 // Algorithmic bytes per launch group: 64*L (lights) + 208 (camera) + 8*tiles (tile min/max)
 // + 4*sum_tiles(1+count).
@@ -171,7 +171,7 @@ k_tile_planes(const AshCullingCameraData* __restrict__ cam, uint32_t W, uint32_t
     planes[tile] = p;
 }
 
-// ---- pass 3: conservative prefilter per cell of 8x8 tiles (128x128 px), one warp per cell.
+// ---- pass 3: conservative prefilter per cell of 8x8 tiles (128x128 px), one CTA per cell.
 // A candidate is dropped from a cell only if it provably fails the shader's test in EVERY tile of it:
 //  * planes 4/5: fadd(zdot, w) is monotone in w and the cell's [min,max] depth contains every tile's,
 //    so failing with the cell's bounds implies failing with each tile's (exact, no margin);
@@ -270,15 +270,25 @@ k_cell_planes(uint32_t tiles_x, uint32_t tiles_y, uint32_t cells_x, uint32_t cel
     }
 }
 
-__global__ void __launch_bounds__(kCellWarps * 32)
+// One CTA of 256 threads per cell.  (One WARP per cell walked the candidates 32 at a time through a dependent load ->
+// test -> ballot -> store chain: 14 us for the bench scene's 470 candidates, 120 us for a scene that keeps 7 760 of its
+// 8 192 lights — tools/light_stress.py.)  A round takes 8 x 256 candidates: thread t owns candidates start + it * 256 + t,
+// every load of the round is issued up front, and one scan over the 8 x 8 warp ballots gives each survivor its slot in
+// ascending candidate order (= ascending light index), as in k_light_prepass.
+#ifndef ASH_CELL_ITERS
+#define ASH_CELL_ITERS 8
+#endif
+constexpr int kCellThreads = 256, kCellIters = ASH_CELL_ITERS;
+__global__ void __launch_bounds__(kCellThreads)
 k_light_cells(uint32_t tiles_x, uint32_t tiles_y, uint32_t cells_x, uint32_t cells,
               const CellPlanes* __restrict__ cell_planes, const uint32_t* __restrict__ tile_minmax,
               const LightCand* __restrict__ cand, const uint32_t* __restrict__ cand_idx,
               const uint32_t* __restrict__ cand_count, uint32_t* __restrict__ cell_list, uint32_t cell_stride,
               uint32_t* __restrict__ cell_count) {
+    __shared__ uint32_t s_cnt[kCellIters * (kCellThreads / 32)];          // [it][warp] survivors, then exclusive offsets
+    __shared__ uint32_t s_base, s_total;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const uint32_t cell = blockIdx.x * kCellWarps + warp;
-    if (cell >= cells) return;
+    const uint32_t cell = blockIdx.x;
     const uint32_t cx = cell % cells_x, cy = cell / cells_x;
     const uint32_t tx0 = cx * kCellTiles, ty0 = cy * kCellTiles;
     const uint32_t tx1 = min(tx0 + kCellTiles - 1, tiles_x - 1), ty1 = min(ty0 + kCellTiles - 1, tiles_y - 1);
@@ -292,7 +302,7 @@ k_light_cells(uint32_t tiles_x, uint32_t tiles_y, uint32_t cells_x, uint32_t cel
         fb[f] = {cp.fb[f][0], cp.fb[f][1], cp.fb[f][2]};
         smin[f] = cp.smin[f]; emax[f] = cp.emax[f]; fvalid[f] = (cp.fvalid >> f) & 1u;
     }
-    uint32_t mn = 0xFFFFFFFFu, mx = 0u, worst = 0u;
+    uint32_t mn = 0xFFFFFFFFu, mx = 0u, worst = 0u;                      // every warp reduces the cell's 64 tile bounds itself
     for (uint32_t t = lane; t < (uint32_t)(kCellTiles * kCellTiles); t += 32) {
         const uint32_t tx = tx0 + (t % kCellTiles), ty = ty0 + (t / kCellTiles);
         if (tx > tx1 || ty > ty1) continue;
@@ -311,90 +321,170 @@ k_light_cells(uint32_t tiles_x, uint32_t tiles_y, uint32_t cells_x, uint32_t cel
 
     const uint32_t nc = *cand_count;
     uint32_t* list = cell_list + (size_t)cell * cell_stride;
-    uint32_t count = 0;
-    for (uint32_t base = 0; base < nc; base += 32) {
-        const uint32_t j = base + lane;
-        bool keep = false;
-        if (j < nc) {
-            const float4 q = __ldg(reinterpret_cast<const float4*>(cand) + j);
-            const uint4 zq = __ldg(reinterpret_cast<const uint4*>(cand_idx) + j);      // CandZ
-            const V3 c = {q.x, q.y, q.z};
-            const float nr = -q.w;
-            bool reject = false;
-            if (zsane) reject = (fadd(__uint_as_float(zq.x), w4) < nr) || (fadd(__uint_as_float(zq.y), w5) < nr);
-            const float clen = sqrtf(pdot(c, c)) * 1.000001f;
-            const float slack = 1e-6f * (fabsf(q.w) + clen);
+    if (threadIdx.x == 0) s_base = 0;
+    __syncthreads();
+    for (uint32_t start = 0; start < nc; start += kCellThreads * kCellIters) {
+        float4 q[kCellIters]; float2 z[kCellIters];
 #pragma unroll
-            for (int f = 0; f < 4; ++f) {
-                const float m = fmaxf(pdot(fa[f], c), pdot(fb[f], c));
-                // every comparison is false on NaN / inf operands, so those candidates are kept
-                if (fvalid[f] && m < 0.0f && smin[f] * m + emax[f] * clen + slack < nr) reject = true;
+        for (int it = 0; it < kCellIters; ++it) {
+            const uint32_t j = start + it * kCellThreads + threadIdx.x;
+            q[it] = make_float4(0.0f, 0.0f, 0.0f, 0.0f); z[it] = make_float2(0.0f, 0.0f);
+            if (j < nc) {
+                q[it] = __ldg(reinterpret_cast<const float4*>(cand) + j);
+                z[it] = __ldg(reinterpret_cast<const float2*>(reinterpret_cast<const uint4*>(cand_idx) + j));    // CandZ.zneg, .zpos
             }
-            keep = !reject;
         }
-        const uint32_t ballot = __ballot_sync(0xFFFFFFFFu, keep);
-        if (keep) list[count + __popc(ballot & ((1u << lane) - 1u))] = j;
-        count += __popc(ballot);
+        uint32_t ballots[kCellIters];
+#pragma unroll
+        for (int it = 0; it < kCellIters; ++it) {
+            const uint32_t j = start + it * kCellThreads + threadIdx.x;
+            bool keep = false;
+            if (j < nc) {
+                const V3 c = {q[it].x, q[it].y, q[it].z};
+                const float nr = -q[it].w;
+                bool reject = false;
+                if (zsane) reject = (fadd(z[it].x, w4) < nr) || (fadd(z[it].y, w5) < nr);
+                const float clen = sqrtf(pdot(c, c)) * 1.000001f;
+                const float slack = 1e-6f * (fabsf(q[it].w) + clen);
+#pragma unroll
+                for (int f = 0; f < 4; ++f) {
+                    const float m = fmaxf(pdot(fa[f], c), pdot(fb[f], c));
+                    // every comparison is false on NaN / inf operands, so those candidates are kept
+                    if (fvalid[f] && m < 0.0f && smin[f] * m + emax[f] * clen + slack < nr) reject = true;
+                }
+                keep = !reject;
+            }
+            ballots[it] = __ballot_sync(0xFFFFFFFFu, keep);
+            if (lane == 0) s_cnt[it * (kCellThreads / 32) + warp] = __popc(ballots[it]);
+        }
+        __syncthreads();
+        if (warp == 0) {                                   // exclusive scan of the counts, kCellIters / 4 consecutive entries per lane
+            constexpr int E = kCellIters * (kCellThreads / 32) / 32;
+            static_assert(E * 32 == kCellIters * (kCellThreads / 32), "counts per lane");
+            uint32_t v[E], sum = 0;
+#pragma unroll
+            for (int k = 0; k < E; ++k) { v[k] = s_cnt[lane * E + k]; sum += v[k]; }
+            uint32_t incl = sum;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) { const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, incl, d); if (lane >= d) incl += t; }
+            uint32_t run = incl - sum;
+#pragma unroll
+            for (int k = 0; k < E; ++k) { s_cnt[lane * E + k] = run; run += v[k]; }
+            if (lane == 31) s_total = incl;
+        }
+        __syncthreads();
+#pragma unroll
+        for (int it = 0; it < kCellIters; ++it)
+            if ((ballots[it] >> lane) & 1u)
+                list[s_base + s_cnt[it * (kCellThreads / 32) + warp] + __popc(ballots[it] & ((1u << lane) - 1u))] = start + it * kCellThreads + threadIdx.x;
+        __syncthreads();
+        if (threadIdx.x == 0) s_base += s_total;
+        __syncthreads();
     }
-    if (lane == 0) cell_count[cell] = count;
+    if (threadIdx.x == 0) cell_count[cell] = s_base;
 }
 
-// ---- pass 4: the shader's exact test (:101-109), one warp per tile, over its cell's survivors only
+// ---- pass 4: the shader's exact test (:101-109) over the cell's survivors only.  One CTA per cell of 8x8 tiles, one warp per
+// four tiles.  The survivors' records (view-space sphere, z dots, light index: 32 bytes) are staged in shared memory once
+// per cell, 512 at a time, instead of being fetched through list -> candidate (two dependent global loads) by each of the 64
+// tiles; the tiles' side planes and depth bounds are staged once as well.  Lanes test 32 survivors at a time and append by
+// ballot + popc prefix: ascending order and first-256-on-overflow (PIN-7) without atomics.
+constexpr int kTileChunk = kTileWarps * 32, kTilesPerWarp = kCellTiles * kCellTiles / kTileWarps;
 __global__ void __launch_bounds__(kTileWarps * 32)
-k_light_tiles(uint32_t tiles_x, uint32_t tiles, uint32_t cells_x, uint32_t light_count,
+k_light_tiles(uint32_t tiles_x, uint32_t tiles_y, uint32_t cells_x, uint32_t light_count,
               const TilePlanes* __restrict__ planes, const uint32_t* __restrict__ tile_minmax,
               const LightCand* __restrict__ cand, const uint32_t* __restrict__ cand_idx,
               const uint32_t* __restrict__ cell_list, uint32_t cell_stride,
               const uint32_t* __restrict__ cell_count, uint32_t* __restrict__ tile_data,
               AshViewStats* __restrict__ stats) {
+    __shared__ float4 s_q[kTileChunk];                         // view-space centre, radius
+    __shared__ float2 s_z[kTileChunk];                         // CandZ.zneg, .zpos
+    __shared__ uint32_t s_li[kTileChunk];                      // light index
+    __shared__ TilePlanes s_planes[kCellTiles * kCellTiles];
+    __shared__ float2 s_w[kCellTiles * kCellTiles];            // -tile min depth, tile max depth (:96-97)
+    __shared__ uint32_t s_cnt[kCellTiles * kCellTiles];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    __shared__ uint32_t s_cnt[kTileWarps];
-    const uint32_t tile = min(blockIdx.x * kTileWarps + warp, tiles - 1u);
-    const bool active = blockIdx.x * kTileWarps + warp < tiles;
-    uint32_t* out = tile_data + (size_t)tile * ASH_TILE_STRIDE;                  // :119
-    if (light_count == 0u) { if (lane == 0 && active) out[0] = 0u; return; }     // :160-165 (uniform)
-    const uint32_t tx = tile % tiles_x, ty = tile / tiles_x;
-    const uint32_t cell = (ty / kCellTiles) * cells_x + tx / kCellTiles;
-    const TilePlanes p = planes[tile];
-    const V3 n0 = {p.a.x, p.a.y, p.a.z}, n1 = {p.a.w, p.b.x, p.b.y}, n2 = {p.b.z, p.b.w, p.c.x}, n3 = {p.c.y, p.c.z, p.c.w};
-    const uint2 mm = __ldg(reinterpret_cast<const uint2*>(tile_minmax) + tile);
-    const float w4 = -__uint_as_float(mm.x), w5 = __uint_as_float(mm.y);       // :96-97
-    const uint32_t* list = cell_list + (size_t)cell * cell_stride;
-    const uint32_t nc = active ? cell_count[cell] : 0u;
-    uint32_t count = 0;
-    for (uint32_t base = 0; base < nc; base += 32) {
-        const uint32_t k = base + lane;
-        bool pass = false;
-        uint32_t li = 0;
-        if (k < nc) {
-            const uint32_t j = list[k];
-            const float4 q = __ldg(reinterpret_cast<const float4*>(cand) + j);
-            const uint4 zq = __ldg(reinterpret_cast<const uint4*>(cand_idx) + j);      // CandZ
-            li = zq.z;
-            const V3 c = {q.x, q.y, q.z};
-            const float nr = -q.w;
-            // sphereInFrustum, :101-109: dist = dot(plane.xyz, c) + plane.w ; reject if dist < -radius.
-            // Side planes have w = 0: (d + 0.0) < nr  <=>  d < nr.  Planes 4/5: the dot is precomputed per light.
-            pass = !(dot3(n0, c) < nr) && !(dot3(n1, c) < nr) && !(dot3(n2, c) < nr) && !(dot3(n3, c) < nr) &&
-                   !(fadd(__uint_as_float(zq.x), w4) < nr) && !(fadd(__uint_as_float(zq.y), w5) < nr);
+    const uint32_t cell = blockIdx.x;
+    const uint32_t cx = cell % cells_x, cy = cell / cells_x;
+    const uint32_t tx0 = cx * kCellTiles, ty0 = cy * kCellTiles;
+    if (threadIdx.x < kCellTiles * kCellTiles) {
+        const uint32_t tx = tx0 + (threadIdx.x % kCellTiles), ty = ty0 + (threadIdx.x / kCellTiles);
+        s_cnt[threadIdx.x] = 0xFFFFFFFFu;                      // tile outside the image
+        if (tx < tiles_x && ty < tiles_y) {
+            const uint32_t tile = ty * tiles_x + tx;
+            s_cnt[threadIdx.x] = 0u;
+            if (light_count != 0u) {
+                s_planes[threadIdx.x] = planes[tile];
+                const uint2 mm = __ldg(reinterpret_cast<const uint2*>(tile_minmax) + tile);
+                s_w[threadIdx.x] = make_float2(-__uint_as_float(mm.x), __uint_as_float(mm.y));
+            }
         }
-        const uint32_t ballot = __ballot_sync(0xFFFFFFFFu, pass);
-        if (pass) {
-            const uint32_t slot = count + __popc(ballot & ((1u << lane) - 1u));
-            if (slot < ASH_MAX_LIGHTS_PER_TILE) out[1 + slot] = li;              // :186-189
-        }
-        count += __popc(ballot);
     }
-    if (lane == 0) {
-        if (active) out[0] = min(count, ASH_MAX_LIGHTS_PER_TILE);                // :196-197
-        s_cnt[warp] = count;
+    const uint32_t nc = light_count != 0u ? cell_count[cell] : 0u;              // :160-165: no lights, every count is zero
+    const uint32_t* list = cell_list + (size_t)cell * cell_stride;
+    uint32_t count[kTilesPerWarp];
+#pragma unroll
+    for (int tt = 0; tt < kTilesPerWarp; ++tt) count[tt] = 0u;
+    for (uint32_t base = 0; base < nc; base += kTileChunk) {
+        __syncthreads();                                       // the previous chunk has been consumed (first pass: the tile staging is visible)
+        const uint32_t n = min((uint32_t)kTileChunk, nc - base);
+        if (threadIdx.x < n) {
+            const uint32_t j = list[base + threadIdx.x];
+            s_q[threadIdx.x] = __ldg(reinterpret_cast<const float4*>(cand) + j);
+            const uint4 zq = __ldg(reinterpret_cast<const uint4*>(cand_idx) + j);                  // CandZ
+            s_z[threadIdx.x] = make_float2(__uint_as_float(zq.x), __uint_as_float(zq.y));
+            s_li[threadIdx.x] = zq.z;
+        }
+        __syncthreads();
+#pragma unroll
+        for (int tt = 0; tt < kTilesPerWarp; ++tt) {
+            const int t = warp * kTilesPerWarp + tt;
+            if (s_cnt[t] == 0xFFFFFFFFu) continue;             // (uniform per warp)
+            const TilePlanes p = s_planes[t];
+            const V3 n0 = {p.a.x, p.a.y, p.a.z}, n1 = {p.a.w, p.b.x, p.b.y}, n2 = {p.b.z, p.b.w, p.c.x}, n3 = {p.c.y, p.c.z, p.c.w};
+            const float w4 = s_w[t].x, w5 = s_w[t].y;
+            uint32_t* out = tile_data + (size_t)((ty0 + t / kCellTiles) * tiles_x + tx0 + t % kCellTiles) * ASH_TILE_STRIDE;   // :119
+            for (uint32_t k0 = 0; k0 < n; k0 += 32) {
+                const uint32_t k = k0 + lane;
+                bool pass = false;
+                if (k < n) {
+                    const float4 q = s_q[k];
+                    const float2 z = s_z[k];
+                    const V3 c = {q.x, q.y, q.z};
+                    const float nr = -q.w;
+                    // sphereInFrustum, :101-109: dist = dot(plane.xyz, c) + plane.w ; reject if dist < -radius.
+                    // Side planes have w = 0: (d + 0.0) < nr  <=>  d < nr.  Planes 4/5: the dot is precomputed per light.
+                    pass = !(dot3(n0, c) < nr) && !(dot3(n1, c) < nr) && !(dot3(n2, c) < nr) && !(dot3(n3, c) < nr) &&
+                           !(fadd(z.x, w4) < nr) && !(fadd(z.y, w5) < nr);
+                }
+                const uint32_t ballot = __ballot_sync(0xFFFFFFFFu, pass);
+                if (pass) {
+                    const uint32_t slot = count[tt] + __popc(ballot & ((1u << lane) - 1u));
+                    if (slot < ASH_MAX_LIGHTS_PER_TILE) out[1 + slot] = s_li[k];             // :186-189
+                }
+                count[tt] += __popc(ballot);
+            }
+        }
     }
     __syncthreads();
-    if (warp == 0) {   // one set of stats atomics per CTA (16 tiles), not per tile
-        const uint32_t c = lane < kTileWarps ? s_cnt[lane] : 0u;
-        uint32_t sum = min(c, ASH_MAX_LIGHTS_PER_TILE), mx = sum, ovf = c > ASH_MAX_LIGHTS_PER_TILE ? 1u : 0u;
 #pragma unroll
-        for (int sft = 8; sft > 0; sft >>= 1) {
+    for (int tt = 0; tt < kTilesPerWarp; ++tt) {
+        const int t = warp * kTilesPerWarp + tt;
+        if (lane == 0 && s_cnt[t] != 0xFFFFFFFFu) {
+            tile_data[(size_t)((ty0 + t / kCellTiles) * tiles_x + tx0 + t % kCellTiles) * ASH_TILE_STRIDE] = min(count[tt], ASH_MAX_LIGHTS_PER_TILE);   // :196-197
+            s_cnt[t] = count[tt];
+        }
+    }
+    __syncthreads();
+    if (warp == 0 && light_count != 0u) {   // one set of stats atomics per cell (64 tiles), not per tile
+        uint32_t sum = 0, mx = 0, ovf = 0;
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            const uint32_t c = s_cnt[lane + 32 * h];
+            if (c != 0xFFFFFFFFu) { const uint32_t m = min(c, ASH_MAX_LIGHTS_PER_TILE); sum += m; mx = max(mx, m); ovf += c > ASH_MAX_LIGHTS_PER_TILE ? 1u : 0u; }
+        }
+#pragma unroll
+        for (int sft = 16; sft > 0; sft >>= 1) {
             sum += __shfl_xor_sync(0xFFFFFFFFu, sum, sft);
             mx = max(mx, __shfl_xor_sync(0xFFFFFFFFu, mx, sft));
             ovf += __shfl_xor_sync(0xFFFFFFFFu, ovf, sft);
@@ -451,7 +541,7 @@ cudaError_t launch_light_cull(const AshGpuLight* lights, const AshLightCullingPu
                 if ((e = cudaGetLastError()) != cudaSuccess) return e;
                 *L.launches += 2;
             }
-            k_light_cells<<<(cells + kCellWarps - 1) / kCellWarps, kCellWarps * 32, 0, L.s>>>(
+            k_light_cells<<<cells, kCellThreads, 0, L.s>>>(
                 tiles_x, tiles_y, cells_x, cells, cell_planes, tile_minmax, cand, cand_idx, cand_count, cell_list,
                 max_lights, cell_count);
             if ((e = cudaGetLastError()) != cudaSuccess) return e;
@@ -459,8 +549,8 @@ cudaError_t launch_light_cull(const AshGpuLight* lights, const AshLightCullingPu
         }
     }
     Timed timed(L, ASH_KERNEL_LIGHT_TILES);
-    k_light_tiles<<<(tiles + kTileWarps - 1) / kTileWarps, kTileWarps * 32, 0, L.s>>>(
-        tiles_x, tiles, cells_x, pc.light_count, planes, tile_minmax, cand, cand_idx, cell_list, max_lights,
+    k_light_tiles<<<cells, kTileWarps * 32, 0, L.s>>>(
+        tiles_x, tiles_y, cells_x, pc.light_count, planes, tile_minmax, cand, cand_idx, cell_list, max_lights,
         cell_count, tile_data, stats);
     return cudaGetLastError();
 }

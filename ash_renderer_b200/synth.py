@@ -128,6 +128,23 @@ def make_lights(n, extent=10.0, rmin=1.0, rmax=5.0, seed=2, n_directional=4, ena
     return lights
 
 
+def dense_light_scene(W, H, n_lights=8192, n_near=8000, rmax=0.52, seed=21):
+    """A view whose light lists are long: raw depth in [0, 1] bounds the z slab of light_culling.comp:96-97 to about one
+    unit around the eye, so `n_near` lights are spread laterally INSIDE that slab (view space x, y, z in [-1.6, 1.6] x
+    [-0.9, 0.9] x [-1.6, 0.3], radius up to `rmax`): ~228 lights per 16x16 tile at 4K, about a thousand tiles beyond 256."""
+    rng = np.random.default_rng(seed)
+    cam = Camera((0.0, 2.0, 22.0), (0, 0, 0), W, H)
+    objs, _ = make_objects((6, 6, 6), seed=3)
+    depth = splat_depth(objs, cam)
+    lights = make_lights(n_lights, extent=12.0, seed=5, center=(0, 0, 0))
+    cd = cam.camera_data()
+    vp = np.stack([rng.uniform(-1.6, 1.6, n_near), rng.uniform(-0.9, 0.9, n_near), rng.uniform(-1.6, 0.3, n_near), np.ones(n_near)], 1)
+    wp = (np.linalg.inv(cd["view"][0].astype(np.float64).T) @ vp.T).T
+    lights["position"][:n_near, :3] = wp[:, :3].astype(np.float32)
+    lights["position"][:n_near, 3] = rng.uniform(0.01, rmax, n_near).astype(np.float32)
+    return cam, lights, cd, depth
+
+
 def splat_depth(objs, cam, shrink=0.5, background=1.0):
     """Coherent occluder z-buffer: each instance's projected AABB rectangle, shrunk about its
     centre, filled with the FARTHEST corner's ndc z over a `background` clear."""

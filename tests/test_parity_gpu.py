@@ -354,6 +354,29 @@ def test_light_cull_prefilter_is_conservative(backend, oracle, case):
         assert ref[:, 0].min() < ref[:, 0].max()        # the side planes do separate tiles here
 
 
+def test_light_cull_dense_scene_at_4k_with_overflow_tiles(backend, oracle):
+    """The per-tile machinery at scale (the bench scene keeps ~5 lights per tile: most of its 8192 lights fall outside the
+    raw-depth near / far planes, light_culling.comp:96-97): 8000 of 8192 lights inside the z slab of a 4K view, ~228
+    per tile, about a thousand tiles past MAX_LIGHTS_PER_TILE = 256 (light_culling.comp:175-178) — lists, order and
+    the overflow count bit-exact."""
+    W, H = 3840, 2160
+    cam, lights, cd, depth = synth.dense_light_scene(W, H)
+    pc = cam.light_pc(len(lights))
+    ref, true_counts, _ = oracle.light_cull(lights, pc, cd, depth)
+    assert ref[:, 0].mean() > 150 and (true_counts > 256).sum() > 100 and ref[:, 0].max() == 256
+    with _ctx(backend, W, H, enable_post=0) as c:
+        c.set_depth(depth)
+        c.upload_lights(lights)
+        c.upload_camera(cd)
+        c.hiz_build()
+        for _ in range(2):                                # the second call runs with the tile planes cached
+            c.light_cull(pc)
+            _compare_tile_lists(c.tile_data(), ref)
+            st = c.stats()
+            assert st["sum_tile_lights"] == int(ref[:, 0].sum())
+            assert st["overflow_tiles"] == int((true_counts > 256).sum())
+
+
 def test_light_cull_overflow_zero_lights_and_disabled(backend, oracle):
     W, H = 64, 48
     cam = synth.Camera((0, 0, 5), (0, 0, 0), W, H)
