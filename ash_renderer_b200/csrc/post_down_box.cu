@@ -150,6 +150,8 @@ k_downsample_box(const uint2* __restrict__ src, int sw, int sh, uint2* __restric
 // 4K -> 1080p under ncu.  Its long-scoreboard stalls vanish (3.5 -> 0.3) but two CTA barriers per tile pair
 // (2.0 stalled warps per issue), the copy address arithmetic (+17 % instructions), 2-way bank conflicts of the
 // 8-byte window reads and 3 instead of 4 CTAs per SM (73 KB of shared memory) cost more than the latency hidden.
+// Box records as two 128-bit halves ({x, y}, {z, w}: 18 instead of 36 shared-memory instructions per thread) were measured
+// equal to slower: 29.8-30.1 vs 29.3-29.5 us.
 cudaError_t launch_bloom_downsample_box(const void* src, uint32_t sw, uint32_t sh, void* dst, uint32_t dw,
                                         uint32_t dh, const Launch& L) {
     const dim3 grid((dw + 63) / 64, (dh + kBH - 1) / kBH);
