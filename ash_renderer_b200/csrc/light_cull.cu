@@ -9,12 +9,13 @@
 //     monotone and tile min >= global min, tile max <= global max), so only survivors
 //     ("candidates") are kept, in ascending light index.
 //   k_tile_planes (1 thread per tile): the four side planes of every tile frustum (:71-98), once.
-//   k_light_cells (1 CTA per 8x8-tile cell): a conservative prefilter — candidates that provably
-//     fail the shader's test in every tile of the cell are dropped, the rest form the cell's list.
-//   k_light_tiles (1 CTA per cell, 1 warp per four tiles): tile min/max come from the depth pyramid
-//     kernel (depth is not read again); the cell's survivors are staged in shared memory once, lanes
-//     test 32 of them at a time with the shader's exact predicate (:101-109) and append by ballot +
-//     popc prefix, which yields ascending order and first-256-on-overflow (PIN-7) without atomics.
+//   k_cell_planes (cached with the tile planes): per 8x8-tile cell, what a conservative prefilter
+//     needs from the planes alone.
+//   k_light_cell_tiles (1 CTA per cell): the prefilter — candidates that provably fail the shader's
+//     test in every tile of the cell are dropped — then, over the survivors held in shared memory,
+//     the shader's exact predicate (:101-109) per tile; tile min/max come from the depth pyramid
+//     kernel (depth is not read again); lists are appended by ballot + popc prefix, which yields
+//     ascending order and first-256-on-overflow (PIN-7) without atomics.
 //
 // Algorithmic bytes per launch group: 64*L (lights) + 208 (camera) + 8*tiles (tile min/max)
 // + 4*sum_tiles(1+count).
@@ -24,7 +25,6 @@
 namespace ash {
 
 constexpr int kPrepassThreads = 1024;
-constexpr int kTileWarps = 16;
 
 // One candidate = 32 bytes: {view x, y, z, radius} {dot((0,0,-1),c), dot((0,0,1),c), light index bits, 0}.
 // The two z dots are the tile-independent parts of planes 4/5 (:96-97, :104), evaluated exactly as the
@@ -270,218 +270,209 @@ k_cell_planes(uint32_t tiles_x, uint32_t tiles_y, uint32_t cells_x, uint32_t cel
     }
 }
 
-// One CTA of 256 threads per cell.  (One WARP per cell walked the candidates 32 at a time through a dependent load ->
-// test -> ballot -> store chain: 14 us for the bench scene's 470 candidates, 120 us for a scene that keeps 7 760 of its
-// 8 192 lights — tools/light_stress.py.)  A round takes 8 x 256 candidates: thread t owns candidates start + it * 256 + t,
-// every load of the round is issued up front, and one scan over the 8 x 8 warp ballots gives each survivor its slot in
-// ascending candidate order (= ascending light index), as in k_light_prepass.
-#ifndef ASH_CELL_ITERS
-#define ASH_CELL_ITERS 8
+// ---- passes 3 + 4 in ONE launch, one CTA of 128 threads per cell.
+// Pass 3 (prefilter): a round takes 4 x 128 candidates — thread t owns candidates start + it * 128 + t, every load of the
+// round is issued up front — and one scan over the 4 x 4 warp ballots gives each survivor its slot in ascending candidate
+// order (= ascending light index), as in k_light_prepass.  The survivors' records (view-space sphere, z dots, light
+// index) go straight to SHARED memory, not to a per-cell list in global memory.
+// Pass 4 (the shader's exact test, :101-109): each warp runs 16 of the cell's 64 tiles over the round's survivors, 32 per
+// step, appending by ballot + popc prefix: ascending order and first-256-on-overflow (PIN-7) without atomics.  The
+// tiles' side planes and depth bounds are staged once per cell.
+// History: one warp per cell + one warp per tile (round 1: 18 + 15 us at 4K, and the tile kernel alone filled the GPU's
+// thread slots for 3.4 waves) -> one CTA per cell for each pass -> fused.  What this buys is not latency but footprint:
+// with other views' kernels running beside it (bench.py) the light group cost 11 us of GPU time per view
+// (tools/front_cost.sh), most of it thread slots held by warps waiting on the list -> candidate -> test chain of
+// dependent loads: 6350 -> 6510 views/s.  Survivors are buffered across rounds (kFuseBuf) so that a scene which keeps
+// most of its lights as candidates but few per cell runs the exact pass once, not once per round; the cell's prefilter
+// planes are re-read from shared memory each round instead of living in 32 registers across the exact pass.
+// tools/light_stress.py (7760 candidates at 4K; prefilter + exact pass, event-timed): 228 lights per tile 84 -> 88 us,
+// 3 lights per tile 57 -> 62 us — the price of 256 instead of 256 + 512 threads per cell; 128 threads: 95 / 59 us.
+#ifndef ASH_FUSE_THREADS
+#define ASH_FUSE_THREADS 256
 #endif
-constexpr int kCellThreads = 256, kCellIters = ASH_CELL_ITERS;
-__global__ void __launch_bounds__(kCellThreads)
-k_light_cells(uint32_t tiles_x, uint32_t tiles_y, uint32_t cells_x, uint32_t cells,
-              const CellPlanes* __restrict__ cell_planes, const uint32_t* __restrict__ tile_minmax,
-              const LightCand* __restrict__ cand, const uint32_t* __restrict__ cand_idx,
-              const uint32_t* __restrict__ cand_count, uint32_t* __restrict__ cell_list, uint32_t cell_stride,
-              uint32_t* __restrict__ cell_count) {
-    __shared__ uint32_t s_cnt[kCellIters * (kCellThreads / 32)];          // [it][warp] survivors, then exclusive offsets
-    __shared__ uint32_t s_base, s_total;
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const uint32_t cell = blockIdx.x;
-    const uint32_t cx = cell % cells_x, cy = cell / cells_x;
-    const uint32_t tx0 = cx * kCellTiles, ty0 = cy * kCellTiles;
-    const uint32_t tx1 = min(tx0 + kCellTiles - 1, tiles_x - 1), ty1 = min(ty0 + kCellTiles - 1, tiles_y - 1);
-    const CellPlanes cp = cell_planes[cell];
-    V3 fa[4], fb[4];
-    float smin[4], emax[4];
-    bool fvalid[4];
-#pragma unroll
-    for (int f = 0; f < 4; ++f) {
-        fa[f] = {cp.fa[f][0], cp.fa[f][1], cp.fa[f][2]};
-        fb[f] = {cp.fb[f][0], cp.fb[f][1], cp.fb[f][2]};
-        smin[f] = cp.smin[f]; emax[f] = cp.emax[f]; fvalid[f] = (cp.fvalid >> f) & 1u;
-    }
-    uint32_t mn = 0xFFFFFFFFu, mx = 0u, worst = 0u;                      // every warp reduces the cell's 64 tile bounds itself
-    for (uint32_t t = lane; t < (uint32_t)(kCellTiles * kCellTiles); t += 32) {
-        const uint32_t tx = tx0 + (t % kCellTiles), ty = ty0 + (t / kCellTiles);
-        if (tx > tx1 || ty > ty1) continue;
-        const uint2 mm = __ldg(reinterpret_cast<const uint2*>(tile_minmax) + (size_t)ty * tiles_x + tx);
-        mn = min(mn, mm.x); mx = max(mx, mm.y); worst = max(worst, max(mm.x, mm.y));
-    }
-#pragma unroll
-    for (int s = 16; s > 0; s >>= 1) {
-        mn = min(mn, __shfl_xor_sync(0xFFFFFFFFu, mn, s));
-        mx = max(mx, __shfl_xor_sync(0xFFFFFFFFu, mx, s));
-        worst = max(worst, __shfl_xor_sync(0xFFFFFFFFu, worst, s));
-    }
-    // uint order == float order only when every tile bound is a non-negative non-NaN float
-    const bool zsane = worst <= 0x7F800000u && mn <= mx;
-    const float w4 = -__uint_as_float(mn), w5 = __uint_as_float(mx);
-
-    const uint32_t nc = *cand_count;
-    uint32_t* list = cell_list + (size_t)cell * cell_stride;
-    if (threadIdx.x == 0) s_base = 0;
-    __syncthreads();
-    for (uint32_t start = 0; start < nc; start += kCellThreads * kCellIters) {
-        float4 q[kCellIters]; float2 z[kCellIters];
-#pragma unroll
-        for (int it = 0; it < kCellIters; ++it) {
-            const uint32_t j = start + it * kCellThreads + threadIdx.x;
-            q[it] = make_float4(0.0f, 0.0f, 0.0f, 0.0f); z[it] = make_float2(0.0f, 0.0f);
-            if (j < nc) {
-                q[it] = __ldg(reinterpret_cast<const float4*>(cand) + j);
-                z[it] = __ldg(reinterpret_cast<const float2*>(reinterpret_cast<const uint4*>(cand_idx) + j));    // CandZ.zneg, .zpos
-            }
-        }
-        uint32_t ballots[kCellIters];
-#pragma unroll
-        for (int it = 0; it < kCellIters; ++it) {
-            const uint32_t j = start + it * kCellThreads + threadIdx.x;
-            bool keep = false;
-            if (j < nc) {
-                const V3 c = {q[it].x, q[it].y, q[it].z};
-                const float nr = -q[it].w;
-                bool reject = false;
-                if (zsane) reject = (fadd(z[it].x, w4) < nr) || (fadd(z[it].y, w5) < nr);
-                const float clen = sqrtf(pdot(c, c)) * 1.000001f;
-                const float slack = 1e-6f * (fabsf(q[it].w) + clen);
-#pragma unroll
-                for (int f = 0; f < 4; ++f) {
-                    const float m = fmaxf(pdot(fa[f], c), pdot(fb[f], c));
-                    // every comparison is false on NaN / inf operands, so those candidates are kept
-                    if (fvalid[f] && m < 0.0f && smin[f] * m + emax[f] * clen + slack < nr) reject = true;
-                }
-                keep = !reject;
-            }
-            ballots[it] = __ballot_sync(0xFFFFFFFFu, keep);
-            if (lane == 0) s_cnt[it * (kCellThreads / 32) + warp] = __popc(ballots[it]);
-        }
-        __syncthreads();
-        if (warp == 0) {                                   // exclusive scan of the counts, kCellIters / 4 consecutive entries per lane
-            constexpr int E = kCellIters * (kCellThreads / 32) / 32;
-            static_assert(E * 32 == kCellIters * (kCellThreads / 32), "counts per lane");
-            uint32_t v[E], sum = 0;
-#pragma unroll
-            for (int k = 0; k < E; ++k) { v[k] = s_cnt[lane * E + k]; sum += v[k]; }
-            uint32_t incl = sum;
-#pragma unroll
-            for (int d = 1; d < 32; d <<= 1) { const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, incl, d); if (lane >= d) incl += t; }
-            uint32_t run = incl - sum;
-#pragma unroll
-            for (int k = 0; k < E; ++k) { s_cnt[lane * E + k] = run; run += v[k]; }
-            if (lane == 31) s_total = incl;
-        }
-        __syncthreads();
-#pragma unroll
-        for (int it = 0; it < kCellIters; ++it)
-            if ((ballots[it] >> lane) & 1u)
-                list[s_base + s_cnt[it * (kCellThreads / 32) + warp] + __popc(ballots[it] & ((1u << lane) - 1u))] = start + it * kCellThreads + threadIdx.x;
-        __syncthreads();
-        if (threadIdx.x == 0) s_base += s_total;
-        __syncthreads();
-    }
-    if (threadIdx.x == 0) cell_count[cell] = s_base;
-}
-
-// ---- pass 4: the shader's exact test (:101-109) over the cell's survivors only.  One CTA per cell of 8x8 tiles, one warp per
-// four tiles.  The survivors' records (view-space sphere, z dots, light index: 32 bytes) are staged in shared memory once
-// per cell, 512 at a time, instead of being fetched through list -> candidate (two dependent global loads) by each of the 64
-// tiles; the tiles' side planes and depth bounds are staged once as well.  Lanes test 32 survivors at a time and append by
-// ballot + popc prefix: ascending order and first-256-on-overflow (PIN-7) without atomics.
-constexpr int kTileChunk = kTileWarps * 32, kTilesPerWarp = kCellTiles * kCellTiles / kTileWarps;
-__global__ void __launch_bounds__(kTileWarps * 32)
-k_light_tiles(uint32_t tiles_x, uint32_t tiles_y, uint32_t cells_x, uint32_t light_count,
-              const TilePlanes* __restrict__ planes, const uint32_t* __restrict__ tile_minmax,
-              const LightCand* __restrict__ cand, const uint32_t* __restrict__ cand_idx,
-              const uint32_t* __restrict__ cell_list, uint32_t cell_stride,
-              const uint32_t* __restrict__ cell_count, uint32_t* __restrict__ tile_data,
-              AshViewStats* __restrict__ stats) {
-    __shared__ float4 s_q[kTileChunk];                         // view-space centre, radius
-    __shared__ float2 s_z[kTileChunk];                         // CandZ.zneg, .zpos
-    __shared__ uint32_t s_li[kTileChunk];                      // light index
+#ifndef ASH_FUSE_ITERS
+#define ASH_FUSE_ITERS 2
+#endif
+constexpr int kFuseThreads = ASH_FUSE_THREADS, kFuseWarps = kFuseThreads / 32, kFuseIters = ASH_FUSE_ITERS, kFuseRound = kFuseThreads * kFuseIters;
+constexpr int kFuseBuf = 1024;                                 // survivor records held in shared memory between two exact passes
+constexpr int kFuseTilesPerWarp = kCellTiles * kCellTiles / kFuseWarps;
+static_assert(kFuseIters * kFuseWarps <= 32, "one count per lane in the scan");
+static_assert(kFuseRound <= kFuseBuf, "a round's survivors must fit the buffer");
+#ifndef ASH_FUSE_MINB
+#define ASH_FUSE_MINB 4
+#endif
+__global__ void __launch_bounds__(kFuseThreads, ASH_FUSE_MINB)
+k_light_cell_tiles(uint32_t tiles_x, uint32_t tiles_y, uint32_t cells_x, uint32_t light_count,
+                   const CellPlanes* __restrict__ cell_planes, const TilePlanes* __restrict__ planes,
+                   const uint32_t* __restrict__ tile_minmax, const LightCand* __restrict__ cand,
+                   const uint32_t* __restrict__ cand_idx, const uint32_t* __restrict__ cand_count,
+                   uint32_t* __restrict__ tile_data, AshViewStats* __restrict__ stats) {
+    __shared__ float4 s_q[kFuseBuf];                           // buffered survivors: view-space centre, radius
+    __shared__ float2 s_z[kFuseBuf];                           //   CandZ.zneg, .zpos
+    __shared__ uint32_t s_li[kFuseBuf];                        //   light index
     __shared__ TilePlanes s_planes[kCellTiles * kCellTiles];
-    __shared__ float2 s_w[kCellTiles * kCellTiles];            // -tile min depth, tile max depth (:96-97)
-    __shared__ uint32_t s_cnt[kCellTiles * kCellTiles];
+    __shared__ uint2 s_mm[kCellTiles * kCellTiles];            // tile depth bounds as float bits
+    __shared__ uint32_t s_in[2];                               // bit t: tile t of the cell lies inside the image
+    __shared__ uint32_t s_tcnt[kCellTiles * kCellTiles];       // lights that pass in each tile so far (owned by one warp each)
+    __shared__ CellPlanes s_cp;                                // re-read per round: 32 registers less across the exact pass
+    __shared__ uint32_t s_cnt[kFuseIters * kFuseWarps], s_total;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const uint32_t cell = blockIdx.x;
     const uint32_t cx = cell % cells_x, cy = cell / cells_x;
     const uint32_t tx0 = cx * kCellTiles, ty0 = cy * kCellTiles;
     if (threadIdx.x < kCellTiles * kCellTiles) {
         const uint32_t tx = tx0 + (threadIdx.x % kCellTiles), ty = ty0 + (threadIdx.x / kCellTiles);
-        s_cnt[threadIdx.x] = 0xFFFFFFFFu;                      // tile outside the image
-        if (tx < tiles_x && ty < tiles_y) {
+        uint2 mm = make_uint2(0u, 0u);
+        const bool inside = tx < tiles_x && ty < tiles_y;
+        if (inside && light_count != 0u) {
             const uint32_t tile = ty * tiles_x + tx;
-            s_cnt[threadIdx.x] = 0u;
-            if (light_count != 0u) {
-                s_planes[threadIdx.x] = planes[tile];
-                const uint2 mm = __ldg(reinterpret_cast<const uint2*>(tile_minmax) + tile);
-                s_w[threadIdx.x] = make_float2(-__uint_as_float(mm.x), __uint_as_float(mm.y));
-            }
+            s_planes[threadIdx.x] = planes[tile];
+            mm = __ldg(reinterpret_cast<const uint2*>(tile_minmax) + tile);
         }
+        s_mm[threadIdx.x] = mm;
+        s_tcnt[threadIdx.x] = 0u;
+        const uint32_t in = __ballot_sync(0xFFFFFFFFu, inside);
+        if (lane == 0) s_in[warp] = in;
+    } else if (light_count != 0u && threadIdx.x - kCellTiles * kCellTiles < sizeof(CellPlanes) / 4) {
+        const uint32_t k = threadIdx.x - kCellTiles * kCellTiles;
+        reinterpret_cast<uint32_t*>(&s_cp)[k] = __ldg(reinterpret_cast<const uint32_t*>(cell_planes + cell) + k);
     }
-    const uint32_t nc = light_count != 0u ? cell_count[cell] : 0u;              // :160-165: no lights, every count is zero
-    const uint32_t* list = cell_list + (size_t)cell * cell_stride;
-    uint32_t count[kTilesPerWarp];
+    __syncthreads();
+    if (light_count != 0u) {                                                     // :160-165: no lights, every count is zero
+        uint32_t mn = 0xFFFFFFFFu, mx = 0u, worst = 0u;                          // the cell's depth bounds, per warp
 #pragma unroll
-    for (int tt = 0; tt < kTilesPerWarp; ++tt) count[tt] = 0u;
-    for (uint32_t base = 0; base < nc; base += kTileChunk) {
-        __syncthreads();                                       // the previous chunk has been consumed (first pass: the tile staging is visible)
-        const uint32_t n = min((uint32_t)kTileChunk, nc - base);
-        if (threadIdx.x < n) {
-            const uint32_t j = list[base + threadIdx.x];
-            s_q[threadIdx.x] = __ldg(reinterpret_cast<const float4*>(cand) + j);
-            const uint4 zq = __ldg(reinterpret_cast<const uint4*>(cand_idx) + j);                  // CandZ
-            s_z[threadIdx.x] = make_float2(__uint_as_float(zq.x), __uint_as_float(zq.y));
-            s_li[threadIdx.x] = zq.z;
+        for (int h = 0; h < 2; ++h) {
+            const uint2 mm = s_mm[lane + 32 * h];
+            if ((s_in[h] >> lane) & 1u) { mn = min(mn, mm.x); mx = max(mx, mm.y); worst = max(worst, max(mm.x, mm.y)); }
         }
-        __syncthreads();
 #pragma unroll
-        for (int tt = 0; tt < kTilesPerWarp; ++tt) {
-            const int t = warp * kTilesPerWarp + tt;
-            if (s_cnt[t] == 0xFFFFFFFFu) continue;             // (uniform per warp)
-            const TilePlanes p = s_planes[t];
-            const V3 n0 = {p.a.x, p.a.y, p.a.z}, n1 = {p.a.w, p.b.x, p.b.y}, n2 = {p.b.z, p.b.w, p.c.x}, n3 = {p.c.y, p.c.z, p.c.w};
-            const float w4 = s_w[t].x, w5 = s_w[t].y;
-            uint32_t* out = tile_data + (size_t)((ty0 + t / kCellTiles) * tiles_x + tx0 + t % kCellTiles) * ASH_TILE_STRIDE;   // :119
-            for (uint32_t k0 = 0; k0 < n; k0 += 32) {
-                const uint32_t k = k0 + lane;
-                bool pass = false;
-                if (k < n) {
-                    const float4 q = s_q[k];
-                    const float2 z = s_z[k];
-                    const V3 c = {q.x, q.y, q.z};
-                    const float nr = -q.w;
-                    // sphereInFrustum, :101-109: dist = dot(plane.xyz, c) + plane.w ; reject if dist < -radius.
-                    // Side planes have w = 0: (d + 0.0) < nr  <=>  d < nr.  Planes 4/5: the dot is precomputed per light.
-                    pass = !(dot3(n0, c) < nr) && !(dot3(n1, c) < nr) && !(dot3(n2, c) < nr) && !(dot3(n3, c) < nr) &&
-                           !(fadd(z.x, w4) < nr) && !(fadd(z.y, w5) < nr);
+        for (int sft = 16; sft > 0; sft >>= 1) {
+            mn = min(mn, __shfl_xor_sync(0xFFFFFFFFu, mn, sft));
+            mx = max(mx, __shfl_xor_sync(0xFFFFFFFFu, mx, sft));
+            worst = max(worst, __shfl_xor_sync(0xFFFFFFFFu, worst, sft));
+        }
+        // uint order == float order only when every tile bound is a non-negative non-NaN float
+        const bool zsane = worst <= 0x7F800000u && mn <= mx;
+        const float cw4 = -__uint_as_float(mn), cw5 = __uint_as_float(mx);
+        const uint32_t nc = *cand_count;
+        uint32_t n_buf = 0u;
+        for (uint32_t start = 0; start < nc; start += kFuseRound) {
+            // ---- pass 3 on candidates [start, start + kFuseRound)
+            float4 q[kFuseIters]; uint4 zq[kFuseIters];
+#pragma unroll
+            for (int it = 0; it < kFuseIters; ++it) {
+                const uint32_t j = start + it * kFuseThreads + threadIdx.x;
+                q[it] = make_float4(0.0f, 0.0f, 0.0f, 0.0f); zq[it] = make_uint4(0u, 0u, 0u, 0u);
+                if (j < nc) {
+                    q[it] = __ldg(reinterpret_cast<const float4*>(cand) + j);
+                    zq[it] = __ldg(reinterpret_cast<const uint4*>(cand_idx) + j);              // CandZ
                 }
-                const uint32_t ballot = __ballot_sync(0xFFFFFFFFu, pass);
-                if (pass) {
-                    const uint32_t slot = count[tt] + __popc(ballot & ((1u << lane) - 1u));
-                    if (slot < ASH_MAX_LIGHTS_PER_TILE) out[1 + slot] = s_li[k];             // :186-189
-                }
-                count[tt] += __popc(ballot);
             }
+            uint32_t ballots[kFuseIters];
+            {
+                V3 fa[4], fb[4];
+                float smin[4], emax[4];
+                bool fvalid[4];
+#pragma unroll
+                for (int f = 0; f < 4; ++f) {
+                    fa[f] = {s_cp.fa[f][0], s_cp.fa[f][1], s_cp.fa[f][2]};
+                    fb[f] = {s_cp.fb[f][0], s_cp.fb[f][1], s_cp.fb[f][2]};
+                    smin[f] = s_cp.smin[f]; emax[f] = s_cp.emax[f]; fvalid[f] = (s_cp.fvalid >> f) & 1u;
+                }
+#pragma unroll
+                for (int it = 0; it < kFuseIters; ++it) {
+                    const uint32_t j = start + it * kFuseThreads + threadIdx.x;
+                    bool keep = false;
+                    if (j < nc) {
+                        const V3 c = {q[it].x, q[it].y, q[it].z};
+                        const float nr = -q[it].w;
+                        bool reject = false;
+                        if (zsane) reject = (fadd(__uint_as_float(zq[it].x), cw4) < nr) || (fadd(__uint_as_float(zq[it].y), cw5) < nr);
+                        const float clen = sqrtf(pdot(c, c)) * 1.000001f;
+                        const float slack = 1e-6f * (fabsf(q[it].w) + clen);
+#pragma unroll
+                        for (int f = 0; f < 4; ++f) {
+                            const float m = fmaxf(pdot(fa[f], c), pdot(fb[f], c));
+                            // every comparison is false on NaN / inf operands, so those candidates are kept
+                            if (fvalid[f] && m < 0.0f && smin[f] * m + emax[f] * clen + slack < nr) reject = true;
+                        }
+                        keep = !reject;
+                    }
+                    ballots[it] = __ballot_sync(0xFFFFFFFFu, keep);
+                    if (lane == 0) s_cnt[it * kFuseWarps + warp] = __popc(ballots[it]);
+                }
+            }
+            __syncthreads();
+            if (warp == 0) {                               // exclusive scan of the kFuseIters x kFuseWarps counts, one per lane
+                const uint32_t v = lane < kFuseIters * kFuseWarps ? s_cnt[lane] : 0u;
+                uint32_t incl = v;
+#pragma unroll
+                for (int d = 1; d < 32; d <<= 1) { const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, incl, d); if (lane >= d) incl += t; }
+                if (lane < kFuseIters * kFuseWarps) s_cnt[lane] = incl - v;
+                if (lane == 31) s_total = incl;
+            }
+            __syncthreads();
+#pragma unroll
+            for (int it = 0; it < kFuseIters; ++it)
+                if ((ballots[it] >> lane) & 1u) {
+                    const uint32_t slot = n_buf + s_cnt[it * kFuseWarps + warp] + __popc(ballots[it] & ((1u << lane) - 1u));
+                    s_q[slot] = q[it];
+                    s_z[slot] = make_float2(__uint_as_float(zq[it].x), __uint_as_float(zq[it].y));
+                    s_li[slot] = zq[it].z;
+                }
+            n_buf += s_total;
+            __syncthreads();                               // survivors appended; s_cnt / s_total may be rewritten
+            // ---- pass 4 over the buffered survivors, once the buffer could not take another round (or at the end)
+            if (start + kFuseRound < nc && n_buf + kFuseRound <= kFuseBuf) continue;
+            for (int tt = 0; tt < kFuseTilesPerWarp; ++tt) {
+                const int t = warp * kFuseTilesPerWarp + tt;
+                if (!((s_in[t >> 5] >> (t & 31)) & 1u)) continue;       // outside the image (uniform per warp)
+                const uint2 mm = s_mm[t];
+                const TilePlanes p = s_planes[t];
+                const V3 n0 = {p.a.x, p.a.y, p.a.z}, n1 = {p.a.w, p.b.x, p.b.y}, n2 = {p.b.z, p.b.w, p.c.x}, n3 = {p.c.y, p.c.z, p.c.w};
+                const float w4 = -__uint_as_float(mm.x), w5 = __uint_as_float(mm.y);       // :96-97
+                uint32_t* out = tile_data + (size_t)((ty0 + t / kCellTiles) * tiles_x + tx0 + t % kCellTiles) * ASH_TILE_STRIDE;   // :119
+                uint32_t count = s_tcnt[t];
+                for (uint32_t k0 = 0; k0 < n_buf; k0 += 32) {
+                    const uint32_t k = k0 + lane;
+                    bool pass = false;
+                    if (k < n_buf) {
+                        const float4 sq = s_q[k];
+                        const float2 z = s_z[k];
+                        const V3 c = {sq.x, sq.y, sq.z};
+                        const float nr = -sq.w;
+                        // sphereInFrustum, :101-109: dist = dot(plane.xyz, c) + plane.w ; reject if dist < -radius.
+                        // Side planes have w = 0: (d + 0.0) < nr  <=>  d < nr.  Planes 4/5: the dot is precomputed per light.
+                        pass = !(dot3(n0, c) < nr) && !(dot3(n1, c) < nr) && !(dot3(n2, c) < nr) && !(dot3(n3, c) < nr) &&
+                               !(fadd(z.x, w4) < nr) && !(fadd(z.y, w5) < nr);
+                    }
+                    const uint32_t ballot = __ballot_sync(0xFFFFFFFFu, pass);
+                    if (pass) {
+                        const uint32_t slot = count + __popc(ballot & ((1u << lane) - 1u));
+                        if (slot < ASH_MAX_LIGHTS_PER_TILE) out[1 + slot] = s_li[k];         // :186-189
+                    }
+                    count += __popc(ballot);
+                }
+                __syncwarp();
+                if (lane == 0) s_tcnt[t] = count;
+                __syncwarp();
+            }
+            n_buf = 0u;
+            __syncthreads();                               // the buffer is rewritten by the next round
         }
     }
     __syncthreads();
-#pragma unroll
-    for (int tt = 0; tt < kTilesPerWarp; ++tt) {
-        const int t = warp * kTilesPerWarp + tt;
-        if (lane == 0 && s_cnt[t] != 0xFFFFFFFFu) {
-            tile_data[(size_t)((ty0 + t / kCellTiles) * tiles_x + tx0 + t % kCellTiles) * ASH_TILE_STRIDE] = min(count[tt], ASH_MAX_LIGHTS_PER_TILE);   // :196-197
-            s_cnt[t] = count[tt];
-        }
+    if (threadIdx.x < kCellTiles * kCellTiles) {
+        if ((s_in[threadIdx.x >> 5] >> (threadIdx.x & 31)) & 1u)
+            tile_data[(size_t)((ty0 + threadIdx.x / kCellTiles) * tiles_x + tx0 + threadIdx.x % kCellTiles) * ASH_TILE_STRIDE] =
+                min(s_tcnt[threadIdx.x], ASH_MAX_LIGHTS_PER_TILE);                                                              // :196-197
     }
-    __syncthreads();
     if (warp == 0 && light_count != 0u) {   // one set of stats atomics per cell (64 tiles), not per tile
         uint32_t sum = 0, mx = 0, ovf = 0;
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
-            const uint32_t c = s_cnt[lane + 32 * h];
-            if (c != 0xFFFFFFFFu) { const uint32_t m = min(c, ASH_MAX_LIGHTS_PER_TILE); sum += m; mx = max(mx, m); ovf += c > ASH_MAX_LIGHTS_PER_TILE ? 1u : 0u; }
+            const uint32_t c = s_tcnt[lane + 32 * h];
+            if ((s_in[h] >> lane) & 1u) { const uint32_t m = min(c, ASH_MAX_LIGHTS_PER_TILE); sum += m; mx = max(mx, m); ovf += c > ASH_MAX_LIGHTS_PER_TILE ? 1u : 0u; }
         }
 #pragma unroll
         for (int sft = 16; sft > 0; sft >>= 1) {
@@ -506,8 +497,8 @@ size_t light_cull_scratch_bytes(uint32_t W, uint32_t H, uint32_t max_lights, siz
     auto up = [](size_t v) { return (v + 255) & ~size_t(255); };
     size_t off = 0;
     *planes_off = off; off = up(off + (size_t)tiles_x * tiles_y * sizeof(TilePlanes));
-    *list_off = off;   off = up(off + (size_t)cells * max_lights * sizeof(uint32_t));
-    *count_off = off;  off = up(off + (size_t)cells * sizeof(uint32_t));
+    (void)max_lights;                  // (the per-cell survivor lists lived here until the prefilter and the exact pass were fused)
+    *list_off = off; *count_off = off;
     *cell_planes_off = off; off = up(off + (size_t)cells * sizeof(CellPlanes));
     return off;
 }
@@ -525,8 +516,6 @@ cudaError_t launch_light_cull(const AshGpuLight* lights, const AshLightCullingPu
     light_cull_scratch_bytes(W, H, max_lights, &po, &lo, &co, &cpo);
     CellPlanes* cell_planes = reinterpret_cast<CellPlanes*>(scratch + cpo);
     TilePlanes* planes = reinterpret_cast<TilePlanes*>(scratch + po);
-    uint32_t* cell_list = reinterpret_cast<uint32_t*>(scratch + lo);
-    uint32_t* cell_count = reinterpret_cast<uint32_t*>(scratch + co);
     cudaError_t e;
     {
         Timed timed(L, ASH_KERNEL_LIGHT_PREPASS);
@@ -541,17 +530,11 @@ cudaError_t launch_light_cull(const AshGpuLight* lights, const AshLightCullingPu
                 if ((e = cudaGetLastError()) != cudaSuccess) return e;
                 *L.launches += 2;
             }
-            k_light_cells<<<cells, kCellThreads, 0, L.s>>>(
-                tiles_x, tiles_y, cells_x, cells, cell_planes, tile_minmax, cand, cand_idx, cand_count, cell_list,
-                max_lights, cell_count);
-            if ((e = cudaGetLastError()) != cudaSuccess) return e;
-            *L.launches += 1;                        // tile planes + cells ride in the prepass class
         }
     }
     Timed timed(L, ASH_KERNEL_LIGHT_TILES);
-    k_light_tiles<<<cells, kTileWarps * 32, 0, L.s>>>(
-        tiles_x, tiles_y, cells_x, pc.light_count, planes, tile_minmax, cand, cand_idx, cell_list, max_lights,
-        cell_count, tile_data, stats);
+    k_light_cell_tiles<<<cells, kFuseThreads, 0, L.s>>>(tiles_x, tiles_y, cells_x, pc.light_count, cell_planes, planes, tile_minmax,
+                                                       cand, cand_idx, cand_count, tile_data, stats);
     return cudaGetLastError();
 }
 

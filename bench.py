@@ -85,7 +85,8 @@ def view_params(cam, n_objs, n_lights, taa_pc, view_id):
     vp["taa"] = taa_pc
     vp["bloom"]["threshold"], vp["bloom"]["upsample_intensity"], vp["bloom"]["mip_count"] = 0.8, 1.0, 5
     vp["post"]["exposure"], vp["post"]["gamma"], vp["post"]["bloom_intensity"] = 1.0, 2.2, 0.5
-    vp["view_id"], vp["stages"] = view_id, T.STAGE_ALL
+    # (ASH_BENCH_STAGES: experiments only — e.g. 0x38 times the post chain alone; the reported workload is always STAGE_ALL)
+    vp["view_id"], vp["stages"] = view_id, int(os.environ.get("ASH_BENCH_STAGES", "0"), 0) or T.STAGE_ALL
     return vp
 
 
