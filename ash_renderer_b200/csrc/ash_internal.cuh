@@ -318,12 +318,6 @@ bool upsample_pair_applies(uint32_t sw, uint32_t sh);
 cudaError_t launch_upsample_pair(const void* src, uint32_t sw, uint32_t sh, void* dst, float intensity, bool tol, cudaStream_t s);
 cudaError_t launch_upsample_tonemap_pair(const void* src, uint32_t sw, uint32_t sh, void* dst, float intensity, const void* hdr,
                                          void* ldr8, const AshPostProcessPushConstants& pc, bool store_u, bool tol, cudaStream_t s);
-// precision = FAST, whole-view path: D_0 = threshold(resolve) rebuilt on the fly by its two consumers instead of stored
-bool bloom_downsample_box_applies(uint32_t dw);
-cudaError_t launch_bloom_threshold_downsample_box(const void* resolve, uint32_t sw, uint32_t sh, void* dst, uint32_t dw,
-                                                  uint32_t dh, float threshold, const Launch& L);
-cudaError_t launch_upsample_tonemap_thresh(const void* src, uint32_t sw, uint32_t sh, float intensity, const void* hdr,
-                                           void* ldr8, const AshPostProcessPushConstants& pc, float threshold, const Launch& L);
 cudaError_t launch_tonemap_fast(const void* hdr, const void* bloom_or_null, void* ldr8, uint32_t W, uint32_t H,
                                 const AshPostProcessPushConstants& pc, const Launch& L);
 // ---- exact-tap validation (exact_taps.cu), host side, O(n) per axis
@@ -350,5 +344,4 @@ int  ash_view_run_eager(ashcuda_ctx* c, const AshCudaViewParams* vp);
 int  ash_view_run_graph(ashcuda_ctx* c, const AshCudaViewParams* vp, bool* handled);
 void ash_view_graphs_destroy(ashcuda_ctx* c);
 int  ash_forward_alloc(ashcuda_ctx* c);
-bool ash_view_skips_d0(const ashcuda_ctx* c, const AshCudaViewParams* vp);      // ashcuda.cu: view_post never materialises D_0
 const ash::TaaTolArgs& ash_taa_tol_plan(ashcuda_ctx* c, const AshTaaPushConstants& pc, float threshold, ash::TaaTolArgs* scratch);

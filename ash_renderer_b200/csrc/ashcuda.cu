@@ -419,6 +419,9 @@ static cudaError_t bloom_threshold_any(ashcuda_ctx* c, float threshold) {
     return launch_bloom_threshold(resolved_color(c), b.d[0], c->W, c->H, threshold, c->center_exact, c->L());
 }
 
+// D_0 is stored by the TAA kernel and read by the first downsample and the last upsample.  Rebuilding it in those two
+// from the resolve (fast mode; bit-identical; commit 'Experiment: D_0 never materialised') removed 132 MB per 4K view and
+// was SLOWER: TAA 68.4 -> 63.3 us but downsample 29.6 -> 40.5 us, 6505 -> 6358 views/s.  DESIGN.md section 5b.
 // One launch per level.  Collapsing the levels below 2^20 (or 2^18) texels into the stages of ONE persistent kernel — tiles
 // handed out by an atomic ticket in stage order, a stage waiting on the finished-tile count of the one before, the same
 // tile functions — was built and measured (commit eb64929, 'k_bloom_tail'): bit-identical, 20 -> 14 (16) launches per view,
@@ -426,9 +429,9 @@ static cudaError_t bloom_threshold_any(ashcuda_ctx* c, float threshold) {
 // views' kernels would use, and single-view latency 0.206 -> 0.222 (0.217) ms, because a kernel boundary inside a CUDA
 // graph (~4.4 us per small level, launch to launch) is cheaper than ticket + acquire poll + fence + release (~6.6 us per
 // stage).  DESIGN.md section 5b has the table.
-static int bloom_down(ashcuda_ctx* c, uint32_t first, uint32_t mips) {          // D_k = downsample(D_{k-1}), k = first .. mips, PIN-9
+static int bloom_down(ashcuda_ctx* c, uint32_t mips) {          // D_k = downsample(D_{k-1}), PIN-9
     BloomChain& b = c->bloom;
-    for (uint32_t k = first; k <= mips; ++k) {
+    for (uint32_t k = 1; k <= mips; ++k) {
         if (c->cfg.fp32_intermediates) ASH_CUDA(c, launch_bloom_downsample_f(b.d[k - 1], b.w[k - 1], b.h[k - 1], b.d[k], b.w[k], b.h[k], 1, c->L()));
         else if (b.down_fast[k]) ASH_CUDA(c, launch_bloom_downsample_fast(b.d[k - 1], b.w[k - 1], b.h[k - 1], b.d[k], b.w[k], b.h[k], c->L()));
         else ASH_CUDA(c, launch_bloom_downsample(b.d[k - 1], b.w[k - 1], b.h[k - 1], b.d[k], b.w[k], b.h[k], c->L()));
@@ -454,7 +457,7 @@ int ashcuda_bloom(ashcuda_ctx* c, const AshBloomParams* bp) {
     if (bp->mip_count > c->bloom.mips) return fail(c, ASH_ERR_INVALID, "bloom: mip_count > config bloom_mips");
     ASH_CUDA(c, cudaSetDevice(c->device));
     ASH_CUDA(c, bloom_threshold_any(c, bp->threshold));
-    int rc = bloom_down(c, 1, bp->mip_count);
+    int rc = bloom_down(c, bp->mip_count);
     if (rc) return rc;
     rc = bloom_up(c, bp, 0);
     if (rc) return rc;
@@ -483,25 +486,6 @@ int ashcuda_set_tonemap_operator(ashcuda_ctx* c, uint32_t op) {      // Tonemapp
     return ASH_OK;
 }
 
-#ifndef ASH_SKIP_D0             // 0: D_0 is always materialised (A/B)
-#define ASH_SKIP_D0 1
-#endif
-}  // extern "C"
-// precision = FAST and the whole post chain in one view_run, U_0 not kept: D_0 = threshold(resolve) is needed by exactly two
-// kernels, the first downsample and the last upsample, and both can rebuild it from the resolve they read (the last
-// upsample reads it anyway, as the tonemap's HDR input) with the very function the TAA kernel would have stored it with.
-// 66 MB less written and 66 MB less read per 4K view, for ~35 more instructions per texel pair in the two consumers: a
-// loss for each kernel timed alone, a gain with other views' kernels beside them, where DRAM is the shared resource.
-bool ash_view_skips_d0(const ashcuda_ctx* c, const AshCudaViewParams* vp) {
-    const uint32_t st = vp->stages, need = ASH_STAGE_TAA | ASH_STAGE_BLOOM | ASH_STAGE_TONEMAP;
-    const BloomChain& b = c->bloom;
-    return ASH_SKIP_D0 && c->cfg.precision == ASH_PRECISION_FAST && !c->cfg.fp32_intermediates && c->cfg.enable_post &&
-           (st & need) == need && !(st & ASH_STAGE_KEEP_BLOOM) && vp->bloom.mip_count >= 1 && vp->bloom.mip_count <= b.mips &&
-           c->tonemap_op == ASH_TONEMAP_ACES && b.up_fast[0] && b.down_fast[1] && bloom_downsample_box_applies(b.w[1]) &&
-           upsample_pair_applies(b.w[1], b.h[1]);
-}
-extern "C" {
-
 static int view_post(ashcuda_ctx* c, const AshCudaViewParams* vp) {
     int rc = ASH_OK;
     const uint32_t st = vp->stages;
@@ -510,9 +494,8 @@ static int view_post(ashcuda_ctx* c, const AshCudaViewParams* vp) {
     const bool want_bloom = (st & ASH_STAGE_BLOOM) != 0;
     if (want_bloom && vp->bloom.mip_count > c->bloom.mips) return fail(c, ASH_ERR_INVALID, "view_run: mip_count > config bloom_mips");
     bool thr_done = false;
-    const bool skip_d0 = want_bloom && ash_view_skips_d0(c, vp);
     if (st & ASH_STAGE_TAA) {
-        rc = taa_resolve_impl(c, &vp->taa, (want_bloom && !skip_d0) ? c->bloom.d[0] : nullptr, vp->bloom.threshold, &thr_done);
+        rc = taa_resolve_impl(c, &vp->taa, want_bloom ? c->bloom.d[0] : nullptr, vp->bloom.threshold, &thr_done);
         if (rc) return rc;
         c->taa_cur ^= 1; c->history_valid = true; c->taa_ran = true; c->bloom_valid = false;
     }
@@ -520,18 +503,9 @@ static int view_post(ashcuda_ctx* c, const AshCudaViewParams* vp) {
     if (want_bloom) {
         if (!c->have_color) return fail(c, ASH_ERR_NOT_INITIALIZED, "bloom: no colour buffer set");
         BloomChain& b = c->bloom;
-        if (skip_d0) {
-            ASH_CUDA(c, launch_bloom_threshold_downsample_box(resolved_color(c), c->W, c->H, b.d[1], b.w[1], b.h[1], vp->bloom.threshold, c->L()));
-            rc = bloom_down(c, 2, vp->bloom.mip_count); if (rc) return rc;
-            rc = bloom_up(c, &vp->bloom, 1); if (rc) return rc;
-            ASH_CUDA(c, launch_upsample_tonemap_thresh(b.d[1], b.w[1], b.h[1], vp->bloom.upsample_intensity, resolved_color(c), c->ldr8,
-                                                       vp->post, vp->bloom.threshold, c->L()));
-            c->bloom_valid = false;         // neither D_0 nor U_0 exists
-            return ASH_OK;
-        }
         if (!thr_done)
             ASH_CUDA(c, bloom_threshold_any(c, vp->bloom.threshold));
-        rc = bloom_down(c, 1, vp->bloom.mip_count); if (rc) return rc;
+        rc = bloom_down(c, vp->bloom.mip_count); if (rc) return rc;
         const bool fuse_last = (st & ASH_STAGE_TONEMAP) && vp->bloom.mip_count >= 1 && b.up_fast[0] && c->tonemap_op == ASH_TONEMAP_ACES &&
                                !c->cfg.fp32_intermediates;
         rc = bloom_up(c, &vp->bloom, fuse_last ? 1 : 0); if (rc) return rc;

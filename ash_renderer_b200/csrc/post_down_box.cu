@@ -17,7 +17,6 @@
 //   phase 2: thread (tx, ty) accumulates the nine taps of its pixel (four from its own registers, five from
 //            shared memory), divides, stores.
 #include "post_pair.cuh"
-#include "post_tol.cuh"
 
 namespace ash {
 
@@ -58,19 +57,12 @@ __device__ __forceinline__ BoxRec box_load_(const BoxTile& B, bool odd, int r, i
     return {P2{B.e[0][r][c]}, P2{B.e[1][r][c]}, P2{B.e[2][r][c]}, P2{B.e[3][r][c]}};
 }
 
-#ifndef ASH_DOWN_BOX_THRESH      // 0: D_0 is always materialised (A/B)
-#define ASH_DOWN_BOX_THRESH 1
-#endif
 #ifndef ASH_DOWN_BOX_MINB
 #define ASH_DOWN_BOX_MINB 4
 #endif
-// THRESH (precision = FAST, whole-view path): `src` is the RESOLVE and every texel loaded from it is replaced by its bloom
-// threshold as the TAA kernel would have stored it (tol_threshold_texels: same function, same bits) — D_0 is then never
-// written to or read from memory.  A thread thresholds the nine texels of each lane's 3x3 window (the texels shared
-// with neighbouring threads are recomputed, not exchanged).
-template <bool TOL, bool THRESH>
+template <bool TOL>
 __global__ void __launch_bounds__(kBoxThreads, ASH_DOWN_BOX_MINB * 256 / kBoxThreads)
-k_downsample_box(const uint2* __restrict__ src, int sw, int sh, uint2* __restrict__ dst, int dw, int dh, float threshold) {
+k_downsample_box(const uint2* __restrict__ src, int sw, int sh, uint2* __restrict__ dst, int dw, int dh) {
     __shared__ __align__(16) BoxTile B;
     const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
     const int X0 = blockIdx.x * 64, Y0 = blockIdx.y * kBH;
@@ -104,20 +96,6 @@ k_downsample_box(const uint2* __restrict__ src, int sw, int sh, uint2* __restric
         }
     }
 
-    if (THRESH) {
-        float one;
-        asm volatile("mov.f32 %0, 0f3F800000;" : "=f"(one));
-#pragma unroll
-        for (int r = 0; r < 3; ++r)
-#pragma unroll
-            for (int i = 0; i < 3; ++i) tol_threshold_texels(ra[r][i], rb[r][i], threshold, one, ra[r][i], rb[r][i]);
-        if (extra) {
-#pragma unroll
-            for (int j = 0; j < 2; ++j)
-#pragma unroll
-                for (int i = 0; i < 2; ++i) tol_threshold_texels(xa[j][i], xb[j][i], threshold, one, xa[j][i], xb[j][i]);
-        }
-    }
     // ---- phase 1: boxes.  4x box sum = (t[j][i] + t[j][i+1]) + (t[j+1][i] + t[j+1][i+1]), as k_downsample_pair
     BoxRec own[2][2];                        // [bj][bi]: this thread's boxes are also taps (i, j) = (bi, bj) of its own pixel
     {
@@ -178,21 +156,10 @@ cudaError_t launch_bloom_downsample_box(const void* src, uint32_t sw, uint32_t s
                                         uint32_t dh, const Launch& L) {
     const dim3 grid((dw + 63) / 64, (dh + kBH - 1) / kBH);
     Timed timed(L, bloom_class(ASH_KERNEL_BLOOM_DOWNSAMPLE, dw, dh));
-    if (L.fast) k_downsample_box<true, false><<<grid, kBoxThreads, 0, L.s>>>(static_cast<const uint2*>(src), (int)sw, (int)sh,
-                                                                              static_cast<uint2*>(dst), (int)dw, (int)dh, 0.0f);
-    else k_downsample_box<false, false><<<grid, kBoxThreads, 0, L.s>>>(static_cast<const uint2*>(src), (int)sw, (int)sh,
-                                                                       static_cast<uint2*>(dst), (int)dw, (int)dh, 0.0f);
-    return cudaGetLastError();
-}
-
-// D_1 straight from the resolve (precision = FAST): threshold on load, see k_downsample_box<., THRESH>
-bool bloom_downsample_box_applies(uint32_t dw) { return ASH_DOWN_BOX_THRESH && dw >= 64u && dw % 32u == 0u; }
-cudaError_t launch_bloom_threshold_downsample_box(const void* resolve, uint32_t sw, uint32_t sh, void* dst, uint32_t dw,
-                                                  uint32_t dh, float threshold, const Launch& L) {
-    const dim3 grid((dw + 63) / 64, (dh + kBH - 1) / kBH);
-    Timed timed(L, bloom_class(ASH_KERNEL_BLOOM_DOWNSAMPLE, dw, dh));
-    k_downsample_box<true, true><<<grid, kBoxThreads, 0, L.s>>>(static_cast<const uint2*>(resolve), (int)sw, (int)sh,
-                                                                 static_cast<uint2*>(dst), (int)dw, (int)dh, threshold);
+    if (L.fast) k_downsample_box<true><<<grid, kBoxThreads, 0, L.s>>>(static_cast<const uint2*>(src), (int)sw, (int)sh,
+                                                                       static_cast<uint2*>(dst), (int)dw, (int)dh);
+    else k_downsample_box<false><<<grid, kBoxThreads, 0, L.s>>>(static_cast<const uint2*>(src), (int)sw, (int)sh,
+                                                                static_cast<uint2*>(dst), (int)dw, (int)dh);
     return cudaGetLastError();
 }
 

@@ -13,7 +13,6 @@
 // next tile's source / destination / HDR blocks in flight (cp.async) while the current one is computed.
 // The source tile is converted to fp32 once per tile into the lane-paired layout the window reads use (UpSrcP).
 #include "post_pair.cuh"
-#include "post_tol.cuh"
 
 namespace ash {
 
@@ -170,26 +169,22 @@ __device__ __forceinline__ void up_tol_conv(const UpSrcP& S, int tj, int ti, con
     }
 }
 
-template <bool TONEMAP, bool DST_THRESH>
+template <bool TONEMAP>
 struct UpTileP {
     uint2 src[20][20];                       // 16x16 source texels + 2-texel halo
-    uint4 dst[DST_THRESH ? 1 : 32][16];      // 32x32 destination texels (the additive-blend operand)
+    uint4 dst[32][16];                       // 32x32 destination texels (the additive-blend operand)
     uint4 hdr[TONEMAP ? 32 : 1][16];         // 32x32 HDR texels (tonemap input)
 };
 
 #ifndef ASH_UPS_PAIR_MINB
 #define ASH_UPS_PAIR_MINB 4
 #endif
-// DST_THRESH (precision = FAST, last level of the whole-view path): the additive-blend operand D_0 is not read from `dst` but
-// rebuilt from the HDR texel the tonemap reads anyway — D_0 = threshold(resolve as stored), tol_threshold_texels, the
-// bits the TAA kernel would have stored — so D_0 is never written to or read from memory.
-template <bool TONEMAP, bool STORE_U, bool TOL, bool DST_THRESH>
+template <bool TONEMAP, bool STORE_U, bool TOL>
 __global__ void __launch_bounds__(128, ASH_UPS_PAIR_MINB)
 k_upsample_pair(const uint2* __restrict__ src, int sw, int sh, uint2* __restrict__ dst, float intensity,
                 const uint2* __restrict__ hdr, uint32_t* __restrict__ ldr8, AshPostProcessPushConstants pc,
-                int tiles_x, int ntiles, float threshold) {
-    static_assert(!DST_THRESH || (TONEMAP && TOL), "D_0 on the fly needs the HDR tile and the tolerance arithmetic");
-    __shared__ __align__(16) UpTileP<TONEMAP, DST_THRESH> T[2];
+                int tiles_x, int ntiles) {
+    __shared__ __align__(16) UpTileP<TONEMAP> T[2];
     __shared__ __align__(16) UpSrcP S;
     const int ti = threadIdx.x & 15, tj = threadIdx.x >> 4;          // tj in 0..7: lanes = source rows tj, tj + 8
     const int dw = 2 * sw, dh = 2 * sh;
@@ -210,7 +205,7 @@ k_upsample_pair(const uint2* __restrict__ src, int sw, int sh, uint2* __restrict
             for (int k = 0; k < 4; ++k) {
                 const int br = tj + 8 * k;
                 if (2 * j0 + br < dh) {
-                    if (!DST_THRESH) cp_async16(&T[b].dst[br][ti], dst + ((uint32_t)(2 * j0 + br) * (uint32_t)dw + col));
+                    cp_async16(&T[b].dst[br][ti], dst + ((uint32_t)(2 * j0 + br) * (uint32_t)dw + col));
                     if (TONEMAP) cp_async16(&T[b].hdr[br][ti], hdr + ((uint32_t)(2 * j0 + br) * (uint32_t)dw + col));
                 }
             }
@@ -222,8 +217,6 @@ k_upsample_pair(const uint2* __restrict__ src, int sw, int sh, uint2* __restrict
 #pragma unroll
     for (int k = 0; k < 8; ++k) wv[k] = splat(TOL ? up_tol_value(k) * 0.00390625f * intensity : 0.0f);
     const float inv_gamma = TONEMAP ? __fdividef(1.0f, pc.gamma) : 0.0f;
-    float one = 1.0f;
-    if (DST_THRESH) asm volatile("mov.f32 %0, 0f3F800000;" : "=f"(one));
     // tile coordinates advance by gridDim.x tiles per round without a division in the loop
     const int step_y = (int)gridDim.x / tiles_x, step_x = (int)gridDim.x - step_y * tiles_x;
     int tile = blockIdx.x, b = 0;
@@ -275,16 +268,7 @@ k_upsample_pair(const uint2* __restrict__ src, int sw, int sh, uint2* __restrict
                 const int rl = 2 * tj + py, rh = rl + 2 * kUpLane;                     // tile-local destination rows of the lanes
                 const uint32_t ol = (uint32_t)(2 * j + py) * (uint32_t)dw + 2u * (uint32_t)i;   // 16-byte aligned pair of texels
                 const uint32_t oh = ol + (uint32_t)(2 * kUpLane) * (uint32_t)dw;
-                uint4 dl, dhh;
-                if (DST_THRESH) {
-                    const uint4 cl = T[b].hdr[rl][ti], ch = T[b].hdr[rh][ti];
-                    uint2 a0, a1, b0, b1;
-                    tol_threshold_texels(make_uint2(cl.x, cl.y), make_uint2(ch.x, ch.y), threshold, one, a0, b0);
-                    tol_threshold_texels(make_uint2(cl.z, cl.w), make_uint2(ch.z, ch.w), threshold, one, a1, b1);
-                    dl = make_uint4(a0.x, a0.y, a1.x, a1.y); dhh = make_uint4(b0.x, b0.y, b1.x, b1.y);
-                } else {
-                    dl = T[b].dst[rl][ti]; dhh = T[b].dst[rh][ti];
-                }
+                const uint4 dl = T[b].dst[rl][ti], dhh = T[b].dst[rh][ti];
                 const V3P u0 = add3(up[py][0], up_unpack2_(make_uint2(dl.x, dl.y), make_uint2(dhh.x, dhh.y)));
                 const V3P u1 = add3(up[py][1], up_unpack2_(make_uint2(dl.z, dl.w), make_uint2(dhh.z, dhh.w)));
                 const uint2 u0l = pack_rgba16f(lo(u0.x), lo(u0.y), lo(u0.z), 1.0f), u0h = pack_rgba16f(hi(u0.x), hi(u0.y), hi(u0.z), 1.0f);
@@ -310,16 +294,16 @@ k_upsample_pair(const uint2* __restrict__ src, int sw, int sh, uint2* __restrict
     cp_async_wait<0>();
 }
 
-template <bool TONEMAP, bool STORE_U, bool TOL, bool DST_THRESH = false>
+template <bool TONEMAP, bool STORE_U, bool TOL>
 static cudaError_t launch_pair_(const void* src, uint32_t sw, uint32_t sh, void* dst, float intensity,
-                                const void* hdr, void* ldr8, const AshPostProcessPushConstants& pc, float threshold, cudaStream_t s) {
+                                const void* hdr, void* ldr8, const AshPostProcessPushConstants& pc, cudaStream_t s) {
     const int tiles_x = (int)((sw + 15) / 16), ntiles = tiles_x * (int)((sh + 15) / 16);
     // resident CTAs per SM: launch bound, capped by 2 x sizeof(UpTileP) of shared memory
     const int per_sm = TONEMAP ? (ASH_UPS_PAIR_MINB < 5 ? ASH_UPS_PAIR_MINB : 5) : ASH_UPS_PAIR_MINB;
     const int grid = min(ntiles, 148 * per_sm);
-    k_upsample_pair<TONEMAP, STORE_U, TOL, DST_THRESH><<<grid, 128, 0, s>>>(static_cast<const uint2*>(src), (int)sw, (int)sh, static_cast<uint2*>(dst),
-                                                                        intensity, static_cast<const uint2*>(hdr), static_cast<uint32_t*>(ldr8),
-                                                                        pc, tiles_x, ntiles, threshold);
+    k_upsample_pair<TONEMAP, STORE_U, TOL><<<grid, 128, 0, s>>>(static_cast<const uint2*>(src), (int)sw, (int)sh, static_cast<uint2*>(dst),
+                                                            intensity, static_cast<const uint2*>(hdr), static_cast<uint32_t*>(ldr8),
+                                                            pc, tiles_x, ntiles);
     return cudaGetLastError();
 }
 
@@ -329,23 +313,16 @@ bool upsample_pair_applies(uint32_t sw, uint32_t sh) {
 }
 
 cudaError_t launch_upsample_pair(const void* src, uint32_t sw, uint32_t sh, void* dst, float intensity, bool tol, cudaStream_t s) {
-    return tol ? launch_pair_<false, true, true>(src, sw, sh, dst, intensity, nullptr, nullptr, AshPostProcessPushConstants{}, 0.0f, s)
-               : launch_pair_<false, true, false>(src, sw, sh, dst, intensity, nullptr, nullptr, AshPostProcessPushConstants{}, 0.0f, s);
+    return tol ? launch_pair_<false, true, true>(src, sw, sh, dst, intensity, nullptr, nullptr, AshPostProcessPushConstants{}, s)
+               : launch_pair_<false, true, false>(src, sw, sh, dst, intensity, nullptr, nullptr, AshPostProcessPushConstants{}, s);
 }
 
 cudaError_t launch_upsample_tonemap_pair(const void* src, uint32_t sw, uint32_t sh, void* dst, float intensity, const void* hdr,
                                          void* ldr8, const AshPostProcessPushConstants& pc, bool store_u, bool tol, cudaStream_t s) {
-    if (tol) return store_u ? launch_pair_<true, true, true>(src, sw, sh, dst, intensity, hdr, ldr8, pc, 0.0f, s)
-                            : launch_pair_<true, false, true>(src, sw, sh, dst, intensity, hdr, ldr8, pc, 0.0f, s);
-    return store_u ? launch_pair_<true, true, false>(src, sw, sh, dst, intensity, hdr, ldr8, pc, 0.0f, s)
-                   : launch_pair_<true, false, false>(src, sw, sh, dst, intensity, hdr, ldr8, pc, 0.0f, s);
-}
-
-// last level, precision = FAST, U_0 not kept: D_0 rebuilt from the HDR tile (k_upsample_pair<., DST_THRESH>)
-cudaError_t launch_upsample_tonemap_thresh(const void* src, uint32_t sw, uint32_t sh, float intensity, const void* hdr,
-                                           void* ldr8, const AshPostProcessPushConstants& pc, float threshold, const Launch& L) {
-    Timed timed(L, ASH_KERNEL_UPSAMPLE_TONEMAP);
-    return launch_pair_<true, false, true, true>(src, sw, sh, nullptr, intensity, hdr, ldr8, pc, threshold, L.s);
+    if (tol) return store_u ? launch_pair_<true, true, true>(src, sw, sh, dst, intensity, hdr, ldr8, pc, s)
+                            : launch_pair_<true, false, true>(src, sw, sh, dst, intensity, hdr, ldr8, pc, s);
+    return store_u ? launch_pair_<true, true, false>(src, sw, sh, dst, intensity, hdr, ldr8, pc, s)
+                   : launch_pair_<true, false, false>(src, sw, sh, dst, intensity, hdr, ldr8, pc, s);
 }
 
 }  // namespace ash

@@ -85,12 +85,11 @@ void make_patches(const ashcuda_ctx* c, const AshCudaViewParams* vp, Patches* P)
     if (P->has_cull2) cull_patch(vp->cull, 2, &P->cull2);
     if (P->has_taa) {
         const bool vel = (st & ASH_STAGE_FORWARD_SHADE) ? c->fwd_has_reproj : c->velocity != nullptr;
-        const bool thresh = (st & ASH_STAGE_BLOOM) != 0 && !ash_view_skips_d0(c, vp);      // the TAA instance view_post launches
         if (c->cfg.precision == ASH_PRECISION_FAST && !vel && taa_in_halo(vp->taa)) {
             TaaTolArgs ta;
-            taa_tol_patch(thresh, ash_taa_tol_plan(const_cast<ashcuda_ctx*>(c), vp->taa, vp->bloom.threshold, &ta), &P->taa);
+            taa_tol_patch((st & ASH_STAGE_BLOOM) != 0, ash_taa_tol_plan(const_cast<ashcuda_ctx*>(c), vp->taa, vp->bloom.threshold, &ta), &P->taa);
         }
-        else taa_pair_patch(thresh, vel, vp->taa, &P->taa);
+        else taa_pair_patch((st & ASH_STAGE_BLOOM) != 0, vel, vp->taa, &P->taa);
     }
     if (P->has_lod) {
         AshInstancingParams ip{};
