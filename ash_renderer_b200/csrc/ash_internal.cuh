@@ -220,6 +220,7 @@ struct ashcuda_ctx {
     bool        center_exact = false;          // (x+0.5)/W taps hit texel x exactly (exact_taps.cu)
     float       taa_chk[4] = {0, 0, 0, 0};     // screen_params the TAA tap check was last run for
     bool        taa_exact = false;
+    AshCullingStats* prepass_cstats = nullptr;   // view_run: the light prepass stores CullingStats::lights_culled itself (no k_culling_stats_finish launch)
     std::vector<ash::TaaTolArgs> tol_plans;    // precision = FAST: history-tap plans by push constants (a Halton period has 16)
 };
 
@@ -242,7 +243,7 @@ cudaError_t launch_light_cull(const AshGpuLight* lights, const AshLightCullingPu
                               const AshCullingCameraData* cam_dev, const uint32_t* tile_minmax,
                               uint32_t* depth_range, LightCand* cand, uint32_t* cand_idx,
                               uint32_t* cand_count, uint8_t* scratch, uint32_t max_lights,
-                              uint32_t* tile_data, AshViewStats* stats, bool build_planes, const Launch& L);
+                              uint32_t* tile_data, AshViewStats* stats, bool build_planes, AshCullingStats* cstats_or_null, const Launch& L);
 cudaError_t launch_store_view(const AshCullingCameraData& cam, bool with_camera, uint32_t view_id, AshCullingCameraData* camera_dev,
                               AshViewStats* stats, const Launch& L);                                  // view_graph.cu
 cudaError_t launch_forward_velocity(const unsigned long long* keys, const float4* spheres, const void* consts, const float* ray_x,

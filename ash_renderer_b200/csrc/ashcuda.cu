@@ -353,7 +353,7 @@ int ashcuda_light_cull(ashcuda_ctx* c, const AshLightCullingPushConstants* pc) {
     const bool build_planes = !c->planes_valid || memcmp(c->planes_ip, c->camera_host.inv_projection, sizeof(c->planes_ip)) != 0;
     ASH_CUDA(c, launch_light_cull(c->lights, *pc, c->camera_dev, c->tile_minmax, c->depth_range, c->cand,
                                   c->cand_idx, c->cand_count, c->light_scratch, c->cfg.max_lights, c->tile_data, c->stats,
-                                  build_planes, c->L()));
+                                  build_planes, c->prepass_cstats, c->L()));
     if (pc->light_count != 0u) { memcpy(c->planes_ip, c->camera_host.inv_projection, sizeof(c->planes_ip)); c->planes_valid = true; }
     return ASH_OK;
 }
@@ -580,9 +580,17 @@ int ash_view_run_eager(ashcuda_ctx* c, const AshCudaViewParams* vp) {
         ip.object_count = vp->cull.object_count;
         rc = ashcuda_instancing_finalize(c, &ip);
     }
-    if (!rc && (st & ASH_STAGE_LIGHTS)) rc = ashcuda_light_cull(c, &vp->light);
+    // CullingStats: the fields other stages own.  lights_culled needs the candidate count only: the light prepass stores it;
+    // lod_triangles_saved (instancing) keeps the one-thread kernel at the end of the chain.
+    const bool finish = (st & ASH_STAGE_CULL) && vp->cull.object_count;
+    const bool finish_in_prepass = finish && (st & ASH_STAGE_LIGHTS) && !(st & ASH_STAGE_INSTANCING);
+    if (!rc && (st & ASH_STAGE_LIGHTS)) {
+        c->prepass_cstats = finish_in_prepass ? c->culling_stats : nullptr;
+        rc = ashcuda_light_cull(c, &vp->light);
+        c->prepass_cstats = nullptr;
+    }
     if (!rc && (st & ASH_STAGE_FORWARD_SHADE)) rc = ashcuda_forward_shade(c);
-    if (!rc && (st & ASH_STAGE_CULL) && vp->cull.object_count) {      // CullingStats: the fields other stages own
+    if (!rc && finish && !finish_in_prepass) {
         cudaError_t e = launch_culling_stats_finish(c->stats, (st & ASH_STAGE_INSTANCING) ? c->inst_stats : nullptr, vp->light.light_count,
                                                     (st & ASH_STAGE_LIGHTS) != 0, c->culling_stats, c->L());
         if (e != cudaSuccess) { c->err = std::string("view_run: ") + cudaGetErrorString(e); rc = ASH_ERR_DEVICE; }

@@ -40,7 +40,8 @@ __global__ void __launch_bounds__(kPrepassThreads)
 k_light_prepass(const AshGpuLight* __restrict__ lights, uint32_t light_count,
                 const AshCullingCameraData* __restrict__ cam, uint32_t* __restrict__ depth_range,
                 LightCand* __restrict__ cand, uint32_t* __restrict__ cand_idx,
-                uint32_t* __restrict__ cand_count, AshViewStats* __restrict__ stats, uint32_t tiles) {
+                uint32_t* __restrict__ cand_count, AshViewStats* __restrict__ stats, uint32_t tiles,
+                AshCullingStats* __restrict__ cstats) {
     __shared__ uint32_t s_cnt[kPrepassIters * (kPrepassThreads / 32)];     // [it][warp] survivors, then exclusive offsets
     __shared__ uint32_t s_base, s_total;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -123,6 +124,8 @@ k_light_prepass(const AshGpuLight* __restrict__ lights, uint32_t light_count,
         stats->sum_tile_lights = 0;
         stats->max_tile_lights = 0;
         stats->overflow_tiles = 0;
+        // CullingStats::lights_culled (view_run: what k_culling_stats_finish would store at the end of the front chain)
+        if (cstats) cstats->lights_culled = light_count - min(light_count, s_base);
     }
 }
 
@@ -507,7 +510,8 @@ cudaError_t launch_light_cull(const AshGpuLight* lights, const AshLightCullingPu
                               const AshCullingCameraData* cam_dev, const uint32_t* tile_minmax,
                               uint32_t* depth_range, LightCand* cand, uint32_t* cand_idx,
                               uint32_t* cand_count, uint8_t* scratch, uint32_t max_lights,
-                              uint32_t* tile_data, AshViewStats* stats, bool build_planes, const Launch& L) {
+                              uint32_t* tile_data, AshViewStats* stats, bool build_planes, AshCullingStats* cstats_or_null,
+                              const Launch& L) {
     const uint32_t W = pc.screen_size[0], H = pc.screen_size[1];
     const uint32_t tiles_x = (W + 15u) / 16u, tiles_y = (H + 15u) / 16u, tiles = tiles_x * tiles_y;
     const uint32_t cells_x = (tiles_x + kCellTiles - 1) / kCellTiles, cells_y = (tiles_y + kCellTiles - 1) / kCellTiles;
@@ -520,7 +524,7 @@ cudaError_t launch_light_cull(const AshGpuLight* lights, const AshLightCullingPu
     {
         Timed timed(L, ASH_KERNEL_LIGHT_PREPASS);
         k_light_prepass<<<1, kPrepassThreads, 0, L.s>>>(lights, pc.light_count, cam_dev, depth_range, cand,
-                                                      cand_idx, cand_count, stats, tiles);
+                                                      cand_idx, cand_count, stats, tiles, cstats_or_null);
         if ((e = cudaGetLastError()) != cudaSuccess) return e;
         if (pc.light_count != 0u) {
             if (build_planes) {          // the side planes depend on invProjection and the extent only: kept across views
