@@ -38,8 +38,8 @@ HIZ_LEVELS = 12                    # "full pyramid" (PIN-4)
 METRIC, UNIT = "4k_views_per_sec", "views/s"
 # dram__bytes_read.sum + dram__bytes_write.sum per launch, from the committed `ncu --set full` captures of this
 # very workload (one launch each; re-captured whenever the kernel changes)
-NCU_DRAM_SOURCE = "profiles/r02_m_full_k_taa_tol.md (132.76 MB read + 94.68 MB write, precision fast); exact mode: profiles/r01_j_full_k_taa_pair.md"
-NCU_DRAM_BYTES = {("taa_threshold_fused", "fast"): 132.757760e6 + 94.679552e6, ("taa_threshold_fused", "exact"): 132.792064e6 + 93.815296e6}
+NCU_DRAM_SOURCE = "profiles/r02_p_full_k_taa_tol.md (132.72 MB read + 91.63 MB write, precision fast); exact mode: profiles/r01_j_full_k_taa_pair.md"
+NCU_DRAM_BYTES = {("taa_threshold_fused", "fast"): 132.724736e6 + 91.633408e6, ("taa_threshold_fused", "exact"): 132.792064e6 + 93.815296e6}
 
 
 def workload_name():

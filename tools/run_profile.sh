@@ -11,7 +11,7 @@ $B > gpurun_out/plain_$TAG.json 2> gpurun_out/plain_$TAG.err && \
 ncu --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum --clock-control none -c 700 --csv --log-file gpurun_out/launches_$TAG.csv $B > gpurun_out/ncu_$TAG.log 2>&1
 # launch index captured per kernel: k_upsample_pair 5 = a fused upsample + tonemap instance (2 launches per view);
 # k_downsample_box 6 = a 4K -> 1080p level (3 launches per view)
-for KS in k_taa_tol:5 k_upsample_pair:5 k_downsample_box:6 k_depth_pyramid:5 k_light_prepass:5 k_light_cells:5 k_light_tiles:5 k_occlusion_cull:5; do
+for KS in k_taa_tol:5 k_upsample_pair:5 k_downsample_box:6 k_depth_pyramid:5 k_light_prepass:5 k_light_cell_tiles:5 k_occlusion_cull:5; do
   K=${KS%%:*}; S=${KS##*:}
   ncu --set full --clock-control none --import-source on -k regex:$K -s $S -c 1 -f -o gpurun_out/full_${TAG}_$K $B > gpurun_out/ncu_full_${TAG}_$K.log 2>&1
 done
