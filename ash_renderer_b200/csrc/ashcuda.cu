@@ -151,7 +151,9 @@ static int create_impl(ashcuda_ctx* c) {
     ASH_CUDA(c, dmalloc(&c->cand_count, 4));
     {
         size_t po, lo, co;
-        ASH_CUDA(c, dmalloc(&c->light_scratch, light_cull_scratch_bytes(c->W, c->H, c->cfg.max_lights, &po, &lo, &co)));
+        const size_t bytes = light_cull_scratch_bytes(c->W, c->H, c->cfg.max_lights, &po, &lo, &co);
+        ASH_CUDA(c, dmalloc(&c->light_scratch, bytes));
+        ASH_CUDA(c, cudaMemsetAsync(c->light_scratch, 0, bytes, c->stream));      // the prepass tickets start at zero
     }
     ASH_CUDA(c, dmalloc(&c->tile_data, tiles * ASH_TILE_STRIDE * 4));    // light_culling_pipeline.rs:55-56
     ASH_CUDA(c, dmalloc(&c->stats, sizeof(AshViewStats)));

@@ -3,11 +3,11 @@
 // Replaces shaders/light_culling.comp:111-203.  The shader re-reads depth per tile, transforms
 // every light to view space once per tile (tiles x lights mat-vecs) and appends through a shared
 // atomic in arbitrary order.  Here:
-//   k_light_prepass (1 CTA): view-space transform once per light per view (:181 is tile
-//     independent) and an exact global prefilter: a light that fails the near/far planes (:96-97)
-//     evaluated with the frame's global [min,max] depth fails them in every tile (rounding is
-//     monotone and tile min >= global min, tile max <= global max), so only survivors
-//     ("candidates") are kept, in ascending light index.
+//   k_light_prepass (1 CTA per 1024 lights, ordered across CTAs): view-space transform once per light
+//     per view (:181 is tile independent) and an exact global prefilter: a light that fails the
+//     near/far planes (:96-97) evaluated with the frame's global [min,max] depth fails them in every
+//     tile (rounding is monotone and tile min >= global min, tile max <= global max), so only
+//     survivors ("candidates") are kept, in ascending light index.
 //   k_tile_planes (1 thread per tile): the four side planes of every tile frustum (:71-98), once.
 //   k_cell_planes (cached with the tile planes): per 8x8-tile cell, what a conservative prefilter
 //     needs from the planes alone.
@@ -31,101 +31,104 @@ constexpr int kPrepassThreads = 1024;
 // shader does (so non-finite light positions behave identically) once per light instead of once per tile.
 struct CandZ { float zneg, zpos; uint32_t index, pad; };
 
-// Ordered compaction of up to 8 x 1024 lights per round: thread t owns lights start + it * 1024 + t, it = 0..7 — every
-// load of a round is coalesced and issued up front (one DRAM latency per round; the previous blocked assignment walked 8
-// dependent 64-byte-strided loads per thread: 15.7 us for 8192 lights, ncu long_scoreboard 23.9) — then ONE block scan
-// over the 8 x 32 warp ballots gives each survivor its slot in ascending light index (it-major, warp, lane).
-constexpr int kPrepassIters = 8;
+// Ordered compaction across CTAs.  CTA b (b = the order in which CTAs START, drawn from a ticket, so that every CTA a
+// running CTA waits for is itself running) owns lights [1024 b, 1024 b + 1024): one coalesced load per thread, the global
+// z-slab test, a block scan of the 32 warp ballots, then it PUBLISHES its survivor count (bit 31 = valid) and sums the
+// published counts of CTAs 0 .. b - 1 (threads poll one predecessor each) for its base slot: survivors land in
+// ascending light index.  The single-CTA form of this kernel ran 25 k warp-instructions on one SM: 11.8 us under ncu for
+// 8192 lights, the longest link of the front chain.  sync: [0] start ticket, [1] CTAs that have left, [2 + b] counts.
 __global__ void __launch_bounds__(kPrepassThreads)
 k_light_prepass(const AshGpuLight* __restrict__ lights, uint32_t light_count,
                 const AshCullingCameraData* __restrict__ cam, uint32_t* __restrict__ depth_range,
                 LightCand* __restrict__ cand, uint32_t* __restrict__ cand_idx,
                 uint32_t* __restrict__ cand_count, AshViewStats* __restrict__ stats, uint32_t tiles,
-                AshCullingStats* __restrict__ cstats) {
-    __shared__ uint32_t s_cnt[kPrepassIters * (kPrepassThreads / 32)];     // [it][warp] survivors, then exclusive offsets
-    __shared__ uint32_t s_base, s_total;
+                AshCullingStats* __restrict__ cstats, uint32_t* __restrict__ sync) {
+    __shared__ uint32_t s_cnt[kPrepassThreads / 32];     // per warp survivors, then exclusive offsets
+    __shared__ uint32_t s_red[kPrepassThreads / 32];
+    __shared__ uint32_t s_bid, s_total, s_base;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (threadIdx.x == 0) s_bid = atomicAdd(&sync[0], 1u);
+    __syncthreads();
+    const uint32_t bid = s_bid, nblk = gridDim.x;
     const M4 view = load_m4(cam->view);
     const uint32_t gmn = depth_range[0], gmx = ~depth_range[1];
     // uint order == float order only for non-negative, non-NaN depth (PIN-2); otherwise keep all
     const bool sane = gmx <= 0x7F800000u && gmn <= gmx;
     const float gmin_d = __uint_as_float(gmn), gmax_d = __uint_as_float(gmx);
     CandZ* candz = reinterpret_cast<CandZ*>(cand_idx);
-    if (threadIdx.x == 0) s_base = 0;
+
+    const uint32_t i = bid * kPrepassThreads + threadIdx.x;
+    float4 q = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+    float enabled = 0.0f;
+    if (i < light_count) {
+        q = __ldg(reinterpret_cast<const float4*>(lights[i].position));
+        enabled = __ldg(&lights[i].params[3]);
+    }
+    bool keep = i < light_count && !(enabled < 0.5f);                                      // :178
+    const V4 pv = mul4(view, q.x, q.y, q.z, 1.0f);                                         // :181
+    if (keep && sane) {
+        // planes 4/5 with the global slab: a light failing them here fails them in every tile
+        const float d4 = fadd(dot3(v3(0.0f, 0.0f, -1.0f), v3(pv.x, pv.y, pv.z)), -gmin_d);
+        const float d5 = fadd(dot3(v3(0.0f, 0.0f, 1.0f), v3(pv.x, pv.y, pv.z)), gmax_d);
+        if (d4 < -q.w || d5 < -q.w) keep = false;
+    }
+    const uint32_t ballot = __ballot_sync(0xFFFFFFFFu, keep);
+    if (lane == 0) s_cnt[warp] = __popc(ballot);
     __syncthreads();
-    for (uint32_t start = 0; start < light_count; start += kPrepassThreads * kPrepassIters) {
-        float4 pos[kPrepassIters]; float enabled[kPrepassIters];
+    if (warp == 0) {                                       // exclusive scan of the 32 warp counts; publish the CTA's total
+        const uint32_t v = s_cnt[lane];
+        uint32_t incl = v;
 #pragma unroll
-        for (int it = 0; it < kPrepassIters; ++it) {
-            const uint32_t i = start + it * kPrepassThreads + threadIdx.x;
-            pos[it] = make_float4(0.0f, 0.0f, 0.0f, 0.0f); enabled[it] = 0.0f;
-            if (i < light_count) {
-                pos[it] = __ldg(reinterpret_cast<const float4*>(lights[i].position));
-                enabled[it] = __ldg(&lights[i].params[3]);
-            }
-        }
-        uint32_t ballots[kPrepassIters];
+        for (int d = 1; d < 32; d <<= 1) { const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, incl, d); if (lane >= d) incl += t; }
+        s_cnt[lane] = incl - v;
+        if (lane == 31) { s_total = incl; atomicExch(&sync[2 + bid], incl | 0x80000000u); }
+    }
+    // base slot = survivors of CTAs 0 .. bid - 1 (they started earlier and publish without waiting for anybody)
+    uint32_t part = 0;
+    for (uint32_t b = threadIdx.x; b < bid; b += kPrepassThreads) {
+        uint32_t v;
+        do { v = *reinterpret_cast<volatile uint32_t*>(&sync[2 + b]); } while (!(v & 0x80000000u));
+        part += v & 0x7FFFFFFFu;
+    }
 #pragma unroll
-        for (int it = 0; it < kPrepassIters; ++it) {
-            const uint32_t i = start + it * kPrepassThreads + threadIdx.x;
-            bool keep = i < light_count && !(enabled[it] < 0.5f);                          // :178
-            if (keep && sane) {
-                const float4 q = pos[it];
-                const float z = mrow(view.c[0].z, view.c[1].z, view.c[2].z, view.c[3].z, q.x, q.y, q.z, 1.0f);
-                const float x = mrow(view.c[0].x, view.c[1].x, view.c[2].x, view.c[3].x, q.x, q.y, q.z, 1.0f);
-                const float y = mrow(view.c[0].y, view.c[1].y, view.c[2].y, view.c[3].y, q.x, q.y, q.z, 1.0f);
-                // planes 4/5 with the global slab: a light failing them here fails them in every tile
-                const float d4 = fadd(dot3(v3(0.0f, 0.0f, -1.0f), v3(x, y, z)), -gmin_d);
-                const float d5 = fadd(dot3(v3(0.0f, 0.0f, 1.0f), v3(x, y, z)), gmax_d);
-                if (d4 < -q.w || d5 < -q.w) keep = false;
-            }
-            ballots[it] = __ballot_sync(0xFFFFFFFFu, keep);
-            if (lane == 0) s_cnt[it * (kPrepassThreads / 32) + warp] = __popc(ballots[it]);
-        }
-        __syncthreads();
-        if (warp == 0) {                                   // exclusive scan of the 256 counts, 8 consecutive entries per lane
-            uint32_t v[8], sum = 0;
+    for (int sft = 16; sft > 0; sft >>= 1) part += __shfl_xor_sync(0xFFFFFFFFu, part, sft);
+    if (lane == 0) s_red[warp] = part;
+    __syncthreads();
+    if (warp == 0) {
+        uint32_t v = s_red[lane];
 #pragma unroll
-            for (int k = 0; k < 8; ++k) { v[k] = s_cnt[lane * 8 + k]; sum += v[k]; }
-            uint32_t incl = sum;
-#pragma unroll
-            for (int d = 1; d < 32; d <<= 1) { const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, incl, d); if (lane >= d) incl += t; }
-            uint32_t run = incl - sum;
-#pragma unroll
-            for (int k = 0; k < 8; ++k) { s_cnt[lane * 8 + k] = run; run += v[k]; }
-            if (lane == 31) s_total = incl;
-        }
-        __syncthreads();
-#pragma unroll
-        for (int it = 0; it < kPrepassIters; ++it) {
-            if ((ballots[it] >> lane) & 1u) {
-                const uint32_t i = start + it * kPrepassThreads + threadIdx.x;
-                const uint32_t slot = s_base + s_cnt[it * (kPrepassThreads / 32) + warp] + __popc(ballots[it] & ((1u << lane) - 1u));
-                const float4 q = pos[it];
-                const V4 pv = mul4(view, q.x, q.y, q.z, 1.0f);                             // :181
-                *reinterpret_cast<float4*>(cand + slot) = make_float4(pv.x, pv.y, pv.z, q.w);
-                CandZ cz;
-                cz.zneg = dot3(v3(0.0f, 0.0f, -1.0f), v3(pv.x, pv.y, pv.z));
-                cz.zpos = dot3(v3(0.0f, 0.0f, 1.0f), v3(pv.x, pv.y, pv.z));
-                cz.index = i; cz.pad = 0;
-                *reinterpret_cast<uint4*>(candz + slot) = *reinterpret_cast<const uint4*>(&cz);
-            }
-        }
-        __syncthreads();
-        if (threadIdx.x == 0) s_base += s_total;
-        __syncthreads();
+        for (int sft = 16; sft > 0; sft >>= 1) v += __shfl_xor_sync(0xFFFFFFFFu, v, sft);
+        if (lane == 0) s_base = v;
+    }
+    __syncthreads();
+    if (keep) {
+        const uint32_t slot = s_base + s_cnt[warp] + __popc(ballot & ((1u << lane) - 1u));
+        *reinterpret_cast<float4*>(cand + slot) = make_float4(pv.x, pv.y, pv.z, q.w);
+        CandZ cz;
+        cz.zneg = dot3(v3(0.0f, 0.0f, -1.0f), v3(pv.x, pv.y, pv.z));
+        cz.zpos = dot3(v3(0.0f, 0.0f, 1.0f), v3(pv.x, pv.y, pv.z));
+        cz.index = i; cz.pad = 0;
+        *reinterpret_cast<uint4*>(candz + slot) = *reinterpret_cast<const uint4*>(&cz);
     }
     if (threadIdx.x == 0) {
-        *cand_count = s_base;
-        depth_range[0] = 0xFFFFFFFFu;       // consumed: reset for the next frame's depth kernel
-        depth_range[1] = 0xFFFFFFFFu;
-        stats->tiles = tiles;
-        stats->candidate_lights = s_base;
-        stats->sum_tile_lights = 0;
-        stats->max_tile_lights = 0;
-        stats->overflow_tiles = 0;
-        // CullingStats::lights_culled (view_run: what k_culling_stats_finish would store at the end of the front chain)
-        if (cstats) cstats->lights_culled = light_count - min(light_count, s_base);
+        if (bid == nblk - 1u) {                            // the CTA of the last lights knows the total
+            const uint32_t total = s_base + s_total;
+            *cand_count = total;
+            stats->tiles = tiles;
+            stats->candidate_lights = total;
+            stats->sum_tile_lights = 0;
+            stats->max_tile_lights = 0;
+            stats->overflow_tiles = 0;
+            // CullingStats::lights_culled (view_run: what k_culling_stats_finish would store at the end of the front chain)
+            if (cstats) cstats->lights_culled = light_count - min(light_count, total);
+        }
+        __threadfence();
+        if (atomicAdd(&sync[1], 1u) == nblk - 1u) {        // last CTA out: every CTA has read depth_range and every count it needs
+            depth_range[0] = 0xFFFFFFFFu;                  // consumed: reset for the next frame's depth kernel
+            depth_range[1] = 0xFFFFFFFFu;
+            sync[0] = 0u; sync[1] = 0u;
+            for (uint32_t b = 0; b < nblk; ++b) sync[2 + b] = 0u;
+        }
     }
 }
 
@@ -500,8 +503,8 @@ size_t light_cull_scratch_bytes(uint32_t W, uint32_t H, uint32_t max_lights, siz
     auto up = [](size_t v) { return (v + 255) & ~size_t(255); };
     size_t off = 0;
     *planes_off = off; off = up(off + (size_t)tiles_x * tiles_y * sizeof(TilePlanes));
-    (void)max_lights;                  // (the per-cell survivor lists lived here until the prefilter and the exact pass were fused)
-    *list_off = off; *count_off = off;
+    // (the per-cell survivor lists lived here until the prefilter and the exact pass were fused)
+    *list_off = off; *count_off = off;  off = up(off + (2 + (max_lights + kPrepassThreads - 1) / kPrepassThreads + 1) * sizeof(uint32_t));   // k_light_prepass sync words (zeroed once)
     *cell_planes_off = off; off = up(off + (size_t)cells * sizeof(CellPlanes));
     return off;
 }
@@ -523,8 +526,9 @@ cudaError_t launch_light_cull(const AshGpuLight* lights, const AshLightCullingPu
     cudaError_t e;
     {
         Timed timed(L, ASH_KERNEL_LIGHT_PREPASS);
-        k_light_prepass<<<1, kPrepassThreads, 0, L.s>>>(lights, pc.light_count, cam_dev, depth_range, cand,
-                                                      cand_idx, cand_count, stats, tiles, cstats_or_null);
+        const uint32_t nblk = pc.light_count ? (pc.light_count + kPrepassThreads - 1) / kPrepassThreads : 1u;
+        k_light_prepass<<<nblk, kPrepassThreads, 0, L.s>>>(lights, pc.light_count, cam_dev, depth_range, cand, cand_idx, cand_count,
+                                                         stats, tiles, cstats_or_null, reinterpret_cast<uint32_t*>(scratch + co));
         if ((e = cudaGetLastError()) != cudaSuccess) return e;
         if (pc.light_count != 0u) {
             if (build_planes) {          // the side planes depend on invProjection and the extent only: kept across views
