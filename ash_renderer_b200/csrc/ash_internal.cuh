@@ -220,6 +220,7 @@ struct ashcuda_ctx {
     bool        center_exact = false;          // (x+0.5)/W taps hit texel x exactly (exact_taps.cu)
     float       taa_chk[4] = {0, 0, 0, 0};     // screen_params the TAA tap check was last run for
     bool        taa_exact = false;
+    bool warned_general = false;                 // the one-line stderr note of ashcuda.cu: note_general_kernel
     AshCullingStats* prepass_cstats = nullptr;   // view_run: the light prepass stores CullingStats::lights_culled itself (no k_culling_stats_finish launch)
     std::vector<ash::TaaTolArgs> tol_plans;    // precision = FAST: history-tap plans by push constants (a Halton period has 16)
 };

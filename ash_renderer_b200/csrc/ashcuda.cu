@@ -360,6 +360,15 @@ int ashcuda_light_cull(ashcuda_ctx* c, const AshLightCullingPushConstants* pc) {
     return ASH_OK;
 }
 
+// the general kernels of post.cu are correct for any extent but several times slower: say so ONCE per context when a level
+// of 2^20 texels or more runs them (the caller's screenParams / extents do not pass the exact-tap checks of exact_taps.cu)
+static void note_general_kernel(ashcuda_ctx* c, const char* what, uint32_t w, uint32_t h) {
+    if (c->warned_general || (uint64_t)w * h < (1u << 20)) return;
+    c->warned_general = true;
+    fprintf(stderr, "ashcuda: %s at %ux%u runs the general one-thread-per-pixel kernel (post.cu): its sampler taps are not "
+                    "texel-exact for these extents / screenParams; results are the same, throughput is lower\n", what, w, h);
+}
+
 static bool taa_extent_ok(const ashcuda_ctx* c, const AshTaaPushConstants* pc) {
     return (uint32_t)pc->screen_params[0] == c->W && (uint32_t)pc->screen_params[1] == c->H;
 }
@@ -394,6 +403,7 @@ static int taa_resolve_impl(ashcuda_ctx* c, const AshTaaPushConstants* pc, void*
         ASH_CUDA(c, launch_taa_fast(c->color, hist, c->velocity, out, thr_or_null, *pc, threshold, c->L()));
         *fused = thr_or_null != nullptr;
     } else {
+        note_general_kernel(c, "TAA resolve", c->W, c->H);
         ASH_CUDA(c, launch_taa(c->color, hist, c->velocity, out, *pc, exact, c->L()));
     }
     return ASH_OK;
@@ -436,7 +446,10 @@ static int bloom_down(ashcuda_ctx* c, uint32_t mips) {          // D_k = downsam
     for (uint32_t k = 1; k <= mips; ++k) {
         if (c->cfg.fp32_intermediates) ASH_CUDA(c, launch_bloom_downsample_f(b.d[k - 1], b.w[k - 1], b.h[k - 1], b.d[k], b.w[k], b.h[k], 1, c->L()));
         else if (b.down_fast[k]) ASH_CUDA(c, launch_bloom_downsample_fast(b.d[k - 1], b.w[k - 1], b.h[k - 1], b.d[k], b.w[k], b.h[k], c->L()));
-        else ASH_CUDA(c, launch_bloom_downsample(b.d[k - 1], b.w[k - 1], b.h[k - 1], b.d[k], b.w[k], b.h[k], c->L()));
+        else {
+            note_general_kernel(c, "bloom downsample", b.w[k], b.h[k]);
+            ASH_CUDA(c, launch_bloom_downsample(b.d[k - 1], b.w[k - 1], b.h[k - 1], b.d[k], b.w[k], b.h[k], c->L()));
+        }
     }
     return ASH_OK;
 }
@@ -447,8 +460,11 @@ static int bloom_up(ashcuda_ctx* c, const AshBloomParams* bp, int last) {   // U
         if (c->cfg.fp32_intermediates) ASH_CUDA(c, launch_bloom_upsample_add_f(b.d[k + 1], b.w[k + 1], b.h[k + 1], b.d[k], b.w[k], b.h[k],
                                                                                   bp->upsample_intensity, 1, c->L()));
         else if (b.up_fast[k]) ASH_CUDA(c, launch_bloom_upsample_fast(b.d[k + 1], b.w[k + 1], b.h[k + 1], b.d[k], bp->upsample_intensity, c->L()));
-        else ASH_CUDA(c, launch_bloom_upsample_add(b.d[k + 1], b.w[k + 1], b.h[k + 1], b.d[k], b.w[k], b.h[k],
+        else {
+            note_general_kernel(c, "bloom upsample", b.w[k], b.h[k]);
+            ASH_CUDA(c, launch_bloom_upsample_add(b.d[k + 1], b.w[k + 1], b.h[k + 1], b.d[k], b.w[k], b.h[k],
                                                    bp->upsample_intensity, c->L()));
+        }
     }
     return ASH_OK;
 }

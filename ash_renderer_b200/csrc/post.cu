@@ -1,5 +1,8 @@
-// post.cu — TAA resolve, bloom threshold / downsample / upsample, ACES tonemap (staged path:
-// one kernel per reference shader dispatch; the fused per-view pipeline lives in post_fused.cu).
+// post.cu — TAA resolve, bloom threshold / downsample / upsample, tonemap: the GENERAL kernels, one thread per pixel and one
+// kernel per reference shader dispatch, valid for any extent and any sampler position.  They are the fallback: at the
+// extents the benchmark runs, ashcuda.cu dispatches to post_fast.cu / post_pair.cu / post_taa_tol.cu / post_up_pair.cu /
+// post_down_box.cu whenever exact_taps.cu validates their sampler shortcuts, and says so once on stderr when a level of
+// 2^20 texels or more falls back here.
 //
 // All colour targets are RGBA16F (8 B / texel, renderer/hdr_framebuffer.rs:34, taa_resolve.comp:19),
 // sampled LINEAR + CLAMP_TO_EDGE with 8-bit sub-texel weights (PIN-6).  A tap that lands on a
