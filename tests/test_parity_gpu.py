@@ -377,6 +377,35 @@ def test_light_cull_dense_scene_at_4k_with_overflow_tiles(backend, oracle):
             assert st["overflow_tiles"] == int((true_counts > 256).sum())
 
 
+@pytest.mark.parametrize("n_lights", [1, 1023, 1025, 3072, 20000, 65537])
+def test_light_prepass_orders_candidates_across_ctas(backend, oracle, n_lights):
+    """k_light_prepass is one CTA per 1024 lights with a look-back over the published counts of the CTAs before it: the
+    candidates must come out in ascending light index whatever the CTA count (1 .. 65) and however full the last CTA is —
+    the tile lists (PIN-7 order), the candidate count and lights_culled say so.  Three calls in a row: the tickets reset."""
+    W, H = 320, 180
+    cam = synth.Camera((0.0, 2.0, 22.0), (0, 0, 0), W, H)
+    objs, _ = synth.make_objects((6, 6, 6), seed=3)
+    depth = synth.splat_depth(objs, cam)
+    lights = synth.make_lights(n_lights, extent=12.0, seed=n_lights, center=(0, 0, 0), n_directional=min(4, n_lights))
+    half = n_lights // 2                                   # half the lights near the eye: inside the raw-depth slab
+    lights["position"][:half, :3] = (lights["position"][:half, :3] * np.float32(0.05) + np.asarray((0.0, 2.0, 22.0), np.float32))
+    lights["position"][:half, 3] *= np.float32(0.1)
+    pc, cd = cam.light_pc(n_lights), cam.camera_data()
+    ref, true_counts, _ = oracle.light_cull(lights, pc, cd, depth)
+    with _ctx(backend, W, H, enable_post=0, max_lights=max(n_lights, 16)) as c:
+        c.set_depth(depth)
+        c.upload_lights(lights)
+        c.upload_camera(cd)
+        c.hiz_build()
+        for _ in range(3):
+            c.light_cull(pc)
+            _compare_tile_lists(c.tile_data(), ref)
+            st = c.stats()
+            assert st["sum_tile_lights"] == int(ref[:, 0].sum())
+            assert st["overflow_tiles"] == int((true_counts > 256).sum())
+            assert 0 < int(st["candidate_lights"]) <= n_lights
+
+
 def test_light_cull_overflow_zero_lights_and_disabled(backend, oracle):
     W, H = 64, 48
     cam = synth.Camera((0, 0, 5), (0, 0, 0), W, H)
